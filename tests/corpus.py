@@ -1,0 +1,365 @@
+"""Seeded synthetic corpora for the parity tests, the golden fixtures and bench.py.
+
+Shapes follow SURVEY.md §8d: C2 RFQ CSV (8 columns, quoted description with `,` and `""`,
+80 % empty notes), C3 Google-Sheets-style sheet XML + sharedStrings, C4 e-mail / PDF-extracted
+text bodies (30 % CRLF, 1 % invalid UTF-8, blank lines around), C5 mixed.
+"""
+from __future__ import annotations
+
+import random
+
+import numpy as np
+
+CSV_HEADER = "part_number,description,quantity,target_price,currency,delivery_date,supplier,notes"
+_CURR = ["USD", "EUR", "INR", "GBP"]
+_SUPP = ["Amphenol", "TE Connectivity", "Molex", "Hirose", "JAE", "Samtec", "Würth", "3M"]
+_DESC = ["Circular MIL Spec Connector, 12 Pin", "RJ Field Ethernet Connector, IP67",
+         "Flexible Coax Cable Assembly, 3 Meters", "D-Sub Connector, 25 Pin, Female",
+         "Backshell, \"\"Straight\"\" type", "Heat shrink boot, size 14", "SMA Male to SMA Male",
+         "Panel Mount, \"\"IP68\"\", black"]
+_NOTE = ["urgent", "RoHS required", "quote MOQ", "alt part ok", "ship to Chennai"]
+
+
+def rfq_csv(n_rows: int, seed: int = 0, newline: str = "\n") -> bytes:
+    """Config C2: `n_rows` x 8 RFQ CSV."""
+    rs = np.random.RandomState(seed)
+    qty = rs.randint(1, 5001, size=n_rows)
+    cents = rs.randint(1, 100000, size=n_rows)
+    cur = rs.randint(0, len(_CURR), size=n_rows)
+    day = rs.randint(1, 31, size=n_rows)
+    sup = rs.randint(0, len(_SUPP), size=n_rows)
+    dsc = rs.randint(0, len(_DESC), size=n_rows)
+    dnum = rs.randint(0, 100, size=n_rows)
+    note = rs.randint(0, 5 * len(_NOTE), size=n_rows)  # 80 % empty
+    lines = [CSV_HEADER]
+    ap = lines.append
+    for i in range(n_rows):
+        n = note[i]
+        ap('PRT-%07d-A,"%s %d",%d,%d.%02d,%s,2025-09-%02d,%s,%s' % (
+            i, _DESC[dsc[i]], dnum[i], qty[i], cents[i] // 100, cents[i] % 100, _CURR[cur[i]],
+            day[i], _SUPP[sup[i]], _NOTE[n] if n < len(_NOTE) else ""))
+    return (newline.join(lines) + newline).encode("utf-8")
+
+
+# ------------------------------------------------------------------ CSV fuzz
+_NA = ["", "#N/A", "#N/A N/A", "#NA", "-1.#IND", "-1.#QNAN", "-NaN", "-nan", "1.#IND", "1.#QNAN",
+       "<NA>", "N/A", "NA", "NULL", "NaN", "None", "n/a", "nan", "null"]
+_WORDS = ["abc", "x y", "PRT-001", "₹500", "日本語", "Würth", "a\"b", "-", "N.A.", "TRUE", "true",
+          "False", "1,200", "0x10", "1_000", "inf", "-inf", "Infinity", "+5", "007", "-0", ".5",
+          "5.", "1e3", "1E-2", " 8", "9 ", "1.50", "2.50", "12:30", "2025-09-01", "é", "naïve",
+          "tab\there", "NAN", "nan ", "1e", "e5", "--1", "+-1", "1.2.3", "1e400", "1e-400",
+          "123456789012345678", "9223372036854775807", "0.000001", "0.0000001", "1234567.891",
+          "99999999.999999", "1e6", "1000001", "0.1", "0.25", "3.14159265358979"]
+
+
+def _rand_cell(r: random.Random, kind: str) -> str:
+    if kind == "int":
+        return str(r.randint(-10000, 100000))
+    if kind == "float2":
+        return "%.2f" % (r.randint(0, 10 ** 7) / 100)
+    if kind == "float":
+        return repr(r.uniform(-1e4, 1e4))
+    if kind == "floatwild":
+        return r.choice(["%g", "%e", "%.10f", "%.3f"]) % (r.uniform(-1, 1) * 10 ** r.randint(-9, 12))
+    if kind == "bool":
+        return r.choice(["True", "False", "true", "false", "TRUE", "FALSE"])
+    if kind == "word":
+        return r.choice(_WORDS)
+    if kind == "na":
+        return r.choice(_NA)
+    if kind == "text":
+        n = r.randint(1, 4)
+        return " ".join(r.choice(["conn", "pin", "M12", "IP67", "Ω", "µm", "ok", "10", "x"]) for _ in range(n))
+    return ""
+
+
+def fuzz_csv(seed: int, max_rows: int = 40) -> bytes:
+    """A small random CSV exercising quoting, NA strings, ragged rows, mixed dtypes, CRLF,
+    blank lines, non-ASCII, separators other than ','."""
+    r = random.Random(seed)
+    sep = r.choice([",", ",", ",", ";", "\t"])
+    nl = r.choice(["\n", "\n", "\r\n", "\r"]) if r.random() < 0.3 else "\n"
+    ncols = r.randint(2, 7)
+    nrows = r.randint(0, max_rows)
+    kinds = [r.choice(["int", "float2", "float", "floatwild", "bool", "word", "text", "na", "mix"])
+             for _ in range(ncols)]
+    na_rate = [r.choice([0, 0, 0.1, 0.5]) for _ in range(ncols)]
+    header = []
+    for c in range(ncols):
+        h = r.choice(["part", "qty", "price", "desc", "a", "b", "Sl No", "Ünit", "", "qty"])
+        header.append(h)
+
+    def quote(s: str, force: bool = False) -> str:
+        if force or sep in s or '"' in s or "\n" in s or "\r" in s:
+            return '"' + s.replace('"', '""') + '"'
+        return s
+
+    lines = [sep.join(quote(h) for h in header)]
+    for _ in range(nrows):
+        row = []
+        for c in range(ncols):
+            k = kinds[c]
+            if k == "mix":
+                k = r.choice(["int", "float2", "word", "na", "bool", "text"])
+            if r.random() < na_rate[c]:
+                k = "na"
+            s = _rand_cell(r, k)
+            if r.random() < 0.03:
+                s = s + r.choice([sep, "\n", '"', " "])
+            row.append(quote(s, force=r.random() < 0.1))
+        x = r.random()
+        if x < 0.04 and ncols > 2:
+            row = row[: r.randint(1, ncols - 1)]  # short row -> NaN fill
+        elif x < 0.05:
+            row.append(_rand_cell(r, "word"))  # long row -> ParserError (unless first data row)
+        lines.append(sep.join(row))
+        if r.random() < 0.03:
+            lines.append(r.choice(["", " ", "  \t" if sep != "\t" else "  "]))
+    body = nl.join(lines)
+    if r.random() < 0.8:
+        body += nl
+    data = body.encode("utf-8")
+    if r.random() < 0.03:
+        data = data.replace(b"a", b"\xe9", 1)  # latin-1 byte -> utf-8 attempt fails
+    if r.random() < 0.03:
+        data = b"\xef\xbb\xbf" + data
+    return data
+
+
+def csv_golden_cases():
+    """(name, bytes, nrows) — hand-written edge cases + seeded fuzz."""
+    E = []
+
+    def add(name, s, nrows=1000):
+        E.append((name, s if isinstance(s, bytes) else s.encode("utf-8"), nrows))
+
+    add("basic", "a,b,c\n1,2,3\n4,5,6\n")
+    add("no_trailing_newline", "a,b\n1,2\n3,4")
+    add("crlf", "a,b\r\n1,x\r\n2,y\r\n")
+    add("bare_cr", "a,b\r1,x\r2,y\r")
+    add("blank_lines", "a,b\n\n1,2\n   \n\n3,4\n\n")
+    add("quoted", 'a,b\n"x,1","he said ""hi"""\n"multi\nline",2\n')
+    add("quote_mid_field", 'a,b\nx"y"z,1\n"x"y,2\n')
+    add("crlf_in_quotes", 'a,b\n"l1\r\nl2",1\n')
+    add("tab_in_cell", 'a,b\n"x\ty",1\n')
+    add("floats_trim", "p,q\n20.00,a\n25.75,b\n146.50,c\n")
+    add("floats_3dec", "p,q\n0.1,a\n0.25,b\n1234567.891,c\n")
+    add("floats_sci_small", "p,q\n1.5,a\n2,b\n1e-7,c\n")
+    add("floats_sci_large", "p,q\n1.5,a\n2,b\n12345678.1234,c\n")
+    add("floats_large_ok", "p,q\n1.5,a\n2,b\n1234567.5,c\n")
+    add("float_obj_holes", "p,q\n1.5,a\n,b\n1e-7,c\n0.1,d\n-2.25,e\n")
+    add("int_na_float", "p,q\n1,a\n,b\n3,c\n")
+    add("bool_col", "p,q\nTrue,1\nFalse,2\n")
+    add("bool_na", "p,q\nTrue,1\n,2\nfalse,3\n")
+    add("bool_mixed_case", "p,q\nTRUE,1\nfalse,2\nTrue,3\n")
+    add("na_strings", "p,q\nNA,1\nN/A,2\nnull,3\nx,4\nNaN,5\n-,6\n")
+    add("all_na_col", "p,q\n,1\n,2\n")
+    add("all_na_row", "p,q\n1,2\n,\n3,4\n")
+    add("numeric_forms", "p,q\n 8,+5\n9 ,007\n-0,12\n")
+    add("float_forms", "p,q\n.5,1e3\n5.,1E-2\ninf,-inf\n")
+    add("not_numbers", "p,q\n0x10,1_000\n\"1,200\",1e\n")
+    add("uint64", "p,q\n9223372036854775808,1\n1,2\n")
+    add("too_big", "p,q\n18446744073709551616,1\n1,2\n")
+    add("int64_edge", "p,q\n9223372036854775807,-9223372036854775808\n1,2\n")
+    add("mixed_keep_text", "p,q\n2.50,1\nabc,2\n1.50,3\n")
+    add("short_rows", "a,b,c\n1,2\n3\n4,5,6\n")
+    add("long_row_error", "a,b\n1,2\n3,4,5\n")
+    add("implicit_index", "a,b\nx,1,2\ny,3,4\n")
+    add("trailing_delim_rows", "a,b\n1,2,\n3,4,\n")
+    add("first_row_longer_only", "a,b\nx,1,2\ny,3\n")
+    add("header_only", "a,b,c\n")
+    add("header_only_nonl", "a,b,c")
+    add("empty", "")
+    add("only_blank", "\n\n  \n")
+    add("one_column", "a\n1\n2\n")
+    add("semicolon", "a;b\n1,5;x\n2,5;y\n")
+    add("tab", "a\tb\n1\tx\n2\ty\n")
+    add("comma_first", "a,x;b,y\n1,2;3,4\n")
+    add("dup_names", "a,a,b,a\n1,2,3,4\n")
+    add("unnamed", "a,,b,\n1,2,3,4\n")
+    add("bom", b"\xef\xbb\xbfa,b\n1,2\n")
+    add("latin1", b"a,b\ncaf\xe9,1\n")
+    add("latin1_semicolon", b"a;b\ncaf\xe9;1\n")
+    add("unicode", "näme,₹\n日本語,₹500\nWürth,1\n")
+    add("unterminated_quote", 'a,b\n"x,1\n2,3\n')
+    add("nul_byte", b"a,b\nx\x00y,1\n")
+    add("nrows_cap", "a,b\n" + "".join(f"{i},{i * 1.5}\n" for i in range(50)), 10)
+    add("nrows_hides_bad_row", "a,b\n1,2\n3,4\n5,6,7,8\n", 2)
+    add("nrows_hides_bad_utf8", b"a,b\n1,x\n2,y\n3,\xff\n", 2)
+    add("ws_line_then_data", "a,b\n  x,1\n \n  ,2\n")
+    add("neg_floats", "a,b\n-1.5,x\n2.25,y\n-0.0,z\n")
+    add("big_ints_as_float", "a,b\n123456789012345678,x\n,y\n")
+    add("exp_forms", "a,b\n1e5,x\n2.5E+3,y\n-3e-2,z\n")
+    add("long_digits", "a,b\n0.12345678901234567890123,x\n123456789012345678901234567890,y\n")
+    add("inf_col", "a,b\ninf,x\n1.5,y\n")
+    add("str_numeric_header", "1,2\n3,4\n")
+    add("spaces_in_cells", "a,b\n x ,1\n  ,2\n")
+    add("quoted_empty", 'a,b\n"",1\n"NA",2\nx,3\n')
+    add("escapes", 'a,b\n"l1\nl2\tq\rz",1\n')
+    for seed in range(120):
+        add(f"fuzz{seed}", fuzz_csv(seed), 1000)
+    for seed in range(120, 140):
+        add(f"fuzz{seed}_n5", fuzz_csv(seed), 5)
+    add("rfq200", rfq_csv(200, seed=1), 1000)
+    add("rfq2000_cap", rfq_csv(2000, seed=2), 1000)
+    return E
+
+
+# ------------------------------------------------------------------ text bodies (C4)
+_BODY_SEEDS = [
+    "hello amphenol,\n\npls send ur best prices for below. shipment to chennai by 10-sep is needed.\n\n"
+    "- part no: 62GB-56T-16-8S  \n  qty: 750  \n  desc: Circular connector\n",
+    "Dear Team,\n\nWe are looking to receive a quotation for the following components for our\n"
+    "July production batch.\n\nCompany: ABC Manufacturing Ltd.\nPhone: +91 98765 43210\n",
+    "Request for Quotation (RFQ)\nTo: sales@example.com\nSubject: RFQ - RF Components\n",
+]
+_WS_EDGE = ["", " ", "\n", "\r\n", "\t", "\x0b\x0c", "\x1c\x1d\x1e\x1f", "", " ",
+            " ", "   ", "  ", " ", " ", "　",
+            "​", "﻿", "\x00"]
+
+
+def text_body(seed: int) -> bytes:
+    r = random.Random(seed)
+    parts = [r.choice(_WS_EDGE) for _ in range(r.randint(0, 3))]
+    body = r.choice(_BODY_SEEDS)
+    for i in range(r.randint(0, 30)):
+        body += "%d) part %s qty: %d @ ₹%d/pc, total %s\n" % (
+            i + 1, "MP-%04d" % r.randint(0, 9999), r.randint(1, 5000), r.randint(1, 999),
+            format(r.randint(1000, 99999), ","))
+    parts.append(body)
+    parts += [r.choice(_WS_EDGE) for _ in range(r.randint(0, 3))]
+    s = "".join(parts)
+    if r.random() < 0.3:
+        s = s.replace("\n", "\r\n")
+    elif r.random() < 0.1:
+        s = s.replace("\n", "\r")
+    data = s.encode("utf-8")
+    if r.random() < 0.2 and data:
+        # sprinkle invalid UTF-8
+        bad = [b"\xff", b"\xc0\xaf", b"\xed\xa0\x80", b"\xf4\x90\x80\x80", b"\xe2\x82", b"\x80",
+               b"\xf0\x9f", b"\xc3"]
+        ba = bytearray(data)
+        for _ in range(r.randint(1, 4)):
+            p = r.randint(0, len(ba))
+            ba[p:p] = r.choice(bad)
+        data = bytes(ba)
+    return data
+
+
+def txt_golden_cases():
+    E = []
+
+    def add(name, b):
+        E.append((name, b if isinstance(b, bytes) else b.encode("utf-8")))
+
+    add("empty", b"")
+    add("only_ws", " \n\t\r\n ")
+    add("plain", "hello\nworld")
+    add("crlf", "  a\r\nb\rc\r\n\r\n")
+    add("cr_at_end", "abc\r")
+    add("bom_kept", b"\xef\xbb\xbfhello ")
+    add("invalid", b"a\xc0\xafb\xed\xa0\x80c\xf4\x90\x80\x80d")
+    add("truncated_tail", b"abc\xe2\x82")
+    add("truncated_then_ascii", b"abc\xe2\x82def\xf0\x9f\x98x")
+    add("nul_not_stripped", b"\x00 a \x00")
+    add("zwsp_not_stripped", "​ a ​")
+    add("unicode_ws", "　  x     ")
+    add("fs_gs", "\x1c\x1d\x1e\x1fx\x1f")
+    add("vt_ff", "\x0b\x0cx\x0c\x0b")
+    add("interior_kept", "a  \n\n  b\t　c")
+    add("all_invalid", b"\xff\xfe\x80")
+    add("ws_after_invalid", b" \xff x \xff ")
+    add("four_byte", "😀 ok 😀")
+    add("cr_split_invalid", b"a\r\xff\nb")
+    add("e0_overlong", b"x\xe0\x80\x80y\xe0\xa0\x80z")
+    add("f0_overlong", b"x\xf0\x80\x80\x80y\xf0\x90\x80\x80z")
+    add("lead_then_lead", b"\xe2\xe2\x82\xacx")
+    for seed in range(60):
+        add(f"body{seed}", text_body(seed))
+    return E
+
+
+# ------------------------------------------------------------------ sheet XML (C3)
+_XML_HEAD = ('<?xml version="1.0" encoding="UTF-8" standalone="yes"?>\n'
+             '<worksheet xmlns="http://schemas.openxmlformats.org/spreadsheetml/2006/main" '
+             'xmlns:r="http://schemas.openxmlformats.org/officeDocument/2006/relationships">'
+             '<sheetPr><pageSetUpPr/></sheetPr><sheetViews><sheetView workbookViewId="0"/>'
+             '</sheetViews><sheetFormatPr customHeight="1" defaultColWidth="14.43" '
+             'defaultRowHeight="15.0"/><sheetData>')
+_XML_TAIL = '</sheetData><drawing r:id="rId1"/></worksheet>'
+
+
+def col_letters(c: int) -> str:
+    s = ""
+    c += 1
+    while c:
+        c, rem = divmod(c - 1, 26)
+        s = chr(65 + rem) + s
+    return s
+
+
+def xml_escape(s: str) -> str:
+    return s.replace("&", "&amp;").replace("<", "&lt;").replace(">", "&gt;")
+
+
+def sheet_xml_doc(seed: int, min_rows: int = 5, max_rows: int = 60):
+    """One Google-Sheets-style worksheet + its sharedStrings. Returns (sheet_xml, sst_xml)."""
+    r = random.Random(seed)
+    ncols = r.randint(4, 12)
+    nrows = r.randint(min_rows, max_rows)
+    strings, index = [], {}
+
+    def sid(s):
+        if s not in index:
+            index[s] = len(strings)
+            strings.append(s)
+        return index[s]
+
+    kinds = [r.choice(["str", "int", "price", "float", "str", "mixed"]) for _ in range(ncols)]
+    names = ["Sl No", "Part Number", "Description", "Quantity", "Target Price (INR)",
+             "Required Delivery Date", "Supplier & Co", "Notes <x>", "Ünit", "Lead", "MOQ", "UOM"]
+    out = [_XML_HEAD, '<row r="1">']
+    for c in range(ncols):
+        out.append('<c r="%s1" s="1" t="s"><v>%d</v></c>' % (col_letters(c), sid(names[c])))
+    out.append("</row>")
+    rownum = 1
+    for i in range(nrows):
+        rownum += 1
+        if r.random() < 0.05:
+            rownum += r.randint(1, 3)  # sparse: missing rows
+        if r.random() < 0.03:
+            out.append('<row r="%d" ht="15.75" customHeight="1"/>' % rownum)
+            continue
+        out.append('<row r="%d">' % rownum)
+        for c in range(ncols):
+            if r.random() < 0.08:
+                if r.random() < 0.5:
+                    continue  # missing cell
+                out.append('<c r="%s%d" s="2"/>' % (col_letters(c), rownum))
+                continue
+            k = kinds[c]
+            if k == "mixed":
+                k = r.choice(["str", "int", "price"])
+            ref = "%s%d" % (col_letters(c), rownum)
+            if k == "str":
+                s = r.choice(["RJF544", "62IN-56T12-8S", "Circular MIL Spec Connector, 12 Pin",
+                              "R&D sample", "a<b", "Würth Elektronik", "日本語", "25-Sep-2025",
+                              "D-Sub Connector, 25 Pin, Female, Solder Cup", "x %d" % r.randint(0, 50)])
+                out.append('<c r="%s" s="2" t="s"><v>%d</v></c>' % (ref, sid(s)))
+            elif k == "int":
+                out.append('<c r="%s" s="2"><v>%d.0</v></c>' % (ref, r.randint(1, 5000)))
+            elif k == "price":
+                out.append('<c r="%s" s="2"><v>%s</v></c>' % (ref, repr(r.randint(1, 10 ** 6) / 100)))
+            else:
+                out.append('<c r="%s" s="2"><v>%s</v></c>' % (ref, repr(r.uniform(0, 1000))))
+        out.append("</row>")
+    for rr in range(rownum + 1, rownum + 1 + r.randint(0, 30)):
+        out.append('<row r="%d" ht="15.75" customHeight="1"/>' % rr)
+    out.append(_XML_TAIL)
+    sst = ['<?xml version="1.0" encoding="UTF-8" standalone="yes"?>\n'
+           '<sst xmlns="http://schemas.openxmlformats.org/spreadsheetml/2006/main" '
+           'count="%d" uniqueCount="%d">' % (len(strings), len(strings))]
+    for s in strings:
+        sst.append("<si><t>%s</t></si>" % xml_escape(s))
+    sst.append("</sst>")
+    return "".join(out).encode("utf-8"), "".join(sst).encode("utf-8")
