@@ -1,0 +1,109 @@
+/* rfq_parse.h — C ABI of the B200 (sm_100a) document→text engine.
+ *
+ * Drop-in boundary for the ONE hot path of Replisense-rfq: `FileParser` in
+ * app/file_parser.py (bytes of CSV / XLSX sheet XML / raw text → one normalised `raw_text`
+ * per document).  The reference has no FFI of its own; these entry points are
+ * what a ctypes binding placed at the reference's three `run_in_executor(self.thread_pool,
+ * self._parse_*_sync, …)` seams (app/file_parser.py:163,216,290) and at `_parse_txt_async`
+ * (app/file_parser.py:143) binds.  INTEGRATION.md shows that binding.
+ *
+ * Conventions
+ *   - plain pointers and sizes, no C++/torch types; every function returns an int error code
+ *     (RFQ_OK = 0) except accessors; nothing throws across the ABI; rfq_last_error() gives text.
+ *   - a batch is a packed byte arena + per-document offsets/lengths.  Offsets that are multiples
+ *     of 16 let the library DMA straight out of the caller's buffer (use rfq_host_alloc() for
+ *     pinned memory); other offsets are accepted and repacked through a pinned staging buffer.
+ *   - outputs are library-owned pinned host buffers, valid until the next run on the same ctx.
+ *   - one ctx = one device + one stream; a ctx is not re-entrant (use one per thread), distinct
+ *     ctxs are independent.  There is NO CPU fallback: without a CUDA device rfq_create fails.
+ */
+#ifndef RFQ_PARSE_H_
+#define RFQ_PARSE_H_
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RFQ_OK 0
+#define RFQ_ERR_CUDA (-1)
+#define RFQ_ERR_ARG (-2)
+#define RFQ_ERR_STATE (-3)
+
+/* per-document status codes (rfq_out_status) */
+#define RFQ_DOC_OK 0
+/* every (encoding, separator) attempt failed → the reference raises FileParsingError("CSV
+ * parsing failed: Unable to parse CSV with any supported encoding/separator combination"),
+ * app/file_parser.py:310,313 */
+#define RFQ_DOC_CSV_UNPARSEABLE 1
+/* input uses a construct this build does not decode on the GPU (reported, never guessed) */
+#define RFQ_DOC_UNSUPPORTED 2
+/* sheet produced an empty frame (reference skips it: app/file_parser.py:228-229) */
+#define RFQ_DOC_EMPTY_SHEET 3
+
+typedef struct rfq_ctx rfq_ctx;
+
+/* lifetime — replaces FileParser.__init__'s thread pool (app/file_parser.py:30-42) */
+int rfq_create(int device, rfq_ctx** out);
+void rfq_destroy(rfq_ctx* ctx);
+const char* rfq_last_error(const rfq_ctx* ctx);
+const char* rfq_version(void);
+int rfq_device_count(void);
+/* run on a caller-owned CUDA stream (e.g. torch's current stream) instead of the ctx's own */
+int rfq_set_stream(rfq_ctx* ctx, void* cuda_stream);
+void* rfq_get_stream(rfq_ctx* ctx);
+/* pinned host memory for input arenas */
+void* rfq_host_alloc(rfq_ctx* ctx, uint64_t bytes);
+void rfq_host_free(rfq_ctx* ctx, void* p);
+
+/* ---- staging: host → device copy of one batch (kept resident until the next rfq_stage) ---- */
+int rfq_stage(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets,
+              const uint64_t* lengths, uint32_t n_docs);
+
+/* ---- text path: replaces FileParser._parse_txt_async (app/file_parser.py:143-159):
+ * UTF-8 decode errors='ignore', universal newlines, str.strip().  Kernels only; the staged
+ * batch is the input and the result stays on the device until rfq_fetch(). */
+int rfq_text_run(rfq_ctx* ctx);
+
+/* ---- CSV path: replaces FileParser._parse_csv_sync (app/file_parser.py:288-313): the
+ * (utf-8, latin-1, cp1252) x (',', ';', TAB) trial loop around pd.read_csv(nrows=max_rows),
+ * dropna(how='all'), fillna(''), banner + to_string(index=False).  max_rows[d] is the
+ * reference's `max_excel_rows` (NULL → 1000 for every document). */
+int rfq_csv_run(rfq_ctx* ctx, const int64_t* max_rows);
+
+/* ---- device → host copy of the last run's output ---- */
+int rfq_fetch(rfq_ctx* ctx);
+
+/* convenience: stage + run + fetch */
+int rfq_text_parse(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets,
+                   const uint64_t* lengths, uint32_t n_docs);
+int rfq_csv_parse(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets,
+                  const uint64_t* lengths, uint32_t n_docs, const int64_t* max_rows);
+
+/* ---- results of the last run (host pointers, valid after rfq_fetch) ---- */
+uint32_t rfq_out_count(const rfq_ctx* ctx);
+const uint8_t* rfq_out_text(const rfq_ctx* ctx);     /* UTF-8, all documents */
+const uint64_t* rfq_out_offsets(const rfq_ctx* ctx); /* [n] start of document d in out_text */
+const uint64_t* rfq_out_lengths(const rfq_ctx* ctx); /* [n] bytes of document d */
+const int32_t* rfq_out_status(const rfq_ctx* ctx);   /* [n] RFQ_DOC_* */
+uint64_t rfq_out_total_bytes(const rfq_ctx* ctx);
+/* per-document table shape of the last CSV / sheet run: rows (after dropna) and columns */
+const uint32_t* rfq_out_rows(const rfq_ctx* ctx);
+const uint32_t* rfq_out_cols(const rfq_ctx* ctx);
+/* CSV: winning attempt, encoding index (0 utf-8, 1 latin-1, 2 cp1252) * 3 + separator index */
+const uint8_t* rfq_out_attempt(const rfq_ctx* ctx);
+
+/* ---- measurement helpers (bench.py): device time of the last *_run, and launch counters ---- */
+float rfq_last_run_ms(const rfq_ctx* ctx);
+uint64_t rfq_launch_count(const rfq_ctx* ctx);
+/* name/ms of the dominant kernel family of the last CSV run, timed with CUDA events on the
+ * ctx stream when profiling is enabled with rfq_set_profile(ctx, 1) */
+int rfq_set_profile(rfq_ctx* ctx, int on);
+int rfq_profile_count(const rfq_ctx* ctx);
+const char* rfq_profile_name(const rfq_ctx* ctx, int i);
+float rfq_profile_ms(const rfq_ctx* ctx, int i);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RFQ_PARSE_H_ */

@@ -1,0 +1,7 @@
+"""B200-native document→text engine behind the `FileParser` interface of Replisense-rfq."""
+from .file_parser import (FileParser, FileParsingError, HAS_PYMUPDF, get_supported_extensions,
+                          parse_file_async)
+from .engine import Engine, EngineError, default_engine
+
+__all__ = ["FileParser", "FileParsingError", "HAS_PYMUPDF", "get_supported_extensions",
+           "parse_file_async", "Engine", "EngineError", "default_engine"]

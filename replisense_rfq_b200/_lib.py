@@ -1,0 +1,69 @@
+"""ctypes binding of the C ABI declared in include/rfq_parse.h.
+
+There is no CPU fallback: if the CUDA library is missing or no device is present, loading or
+creating an engine raises — callers never get a silently slower path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+LIB_PATH = HERE / "librfqparse.so"
+
+RFQ_OK = 0
+DOC_OK, DOC_CSV_UNPARSEABLE, DOC_UNSUPPORTED, DOC_EMPTY_SHEET = 0, 1, 2, 3
+
+_lib = None
+
+# name -> (restype, argtypes); mirrors include/rfq_parse.h one to one
+SIGNATURES = {
+    "rfq_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
+    "rfq_destroy": (None, [C.c_void_p]),
+    "rfq_last_error": (C.c_char_p, [C.c_void_p]),
+    "rfq_version": (C.c_char_p, []),
+    "rfq_device_count": (C.c_int, []),
+    "rfq_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "rfq_get_stream": (C.c_void_p, [C.c_void_p]),
+    "rfq_host_alloc": (C.c_void_p, [C.c_void_p, C.c_uint64]),
+    "rfq_host_free": (None, [C.c_void_p, C.c_void_p]),
+    "rfq_stage": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),
+    "rfq_text_run": (C.c_int, [C.c_void_p]),
+    "rfq_csv_run": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "rfq_fetch": (C.c_int, [C.c_void_p]),
+    "rfq_text_parse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),
+    "rfq_csv_parse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32,
+                                C.c_void_p]),
+    "rfq_out_count": (C.c_uint32, [C.c_void_p]),
+    "rfq_out_text": (C.c_void_p, [C.c_void_p]),
+    "rfq_out_offsets": (C.c_void_p, [C.c_void_p]),
+    "rfq_out_lengths": (C.c_void_p, [C.c_void_p]),
+    "rfq_out_status": (C.c_void_p, [C.c_void_p]),
+    "rfq_out_total_bytes": (C.c_uint64, [C.c_void_p]),
+    "rfq_out_rows": (C.c_void_p, [C.c_void_p]),
+    "rfq_out_cols": (C.c_void_p, [C.c_void_p]),
+    "rfq_out_attempt": (C.c_void_p, [C.c_void_p]),
+    "rfq_last_run_ms": (C.c_float, [C.c_void_p]),
+    "rfq_launch_count": (C.c_uint64, [C.c_void_p]),
+    "rfq_set_profile": (C.c_int, [C.c_void_p, C.c_int]),
+    "rfq_profile_count": (C.c_int, [C.c_void_p]),
+    "rfq_profile_name": (C.c_char_p, [C.c_void_p, C.c_int]),
+    "rfq_profile_ms": (C.c_float, [C.c_void_p, C.c_int]),
+}
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `python -m replisense_rfq_b200.build` "
+            "(there is no CPU fallback)")
+    lib = C.CDLL(str(LIB_PATH))
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the .so does not export the symbol
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib

@@ -1,0 +1,134 @@
+// The context behind the opaque rfq_ctx handle: one device, one stream, grow-only buffers.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#include "launch.h"
+#include "pipeline.h"
+#include "rfq_common.cuh"
+
+#define RFQ_CK(c, call)                                                            \
+  do {                                                                             \
+    cudaError_t e_ = (call);                                                       \
+    if (e_ != cudaSuccess) {                                                       \
+      (c)->err = std::string(#call) + ": " + cudaGetErrorString(e_);               \
+      cudaGetLastError();                                                          \
+      return RFQ_ERR_CUDA;                                                         \
+    }                                                                              \
+  } while (0)
+
+namespace rfq {
+
+// grow-only device buffer
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t reserve(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+// grow-only pinned host buffer
+struct HostBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t reserve(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFreeHost(p);
+    p = nullptr; cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaHostAlloc(&p, want, cudaHostAllocDefault);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+// Per-run scratch: bump allocation out of chunks; chunks are merged into one at reset() so a
+// steady-state run performs no cudaMalloc at all.
+struct DevPool {
+  struct Chunk { uint8_t* p; size_t cap; };
+  std::vector<Chunk> chunks;
+  size_t used = 0;       // in the last chunk
+  size_t total_used = 0; // across the run
+  bool failed = false;
+  void reset() {
+    failed = false;
+    if (chunks.size() > 1 || (chunks.size() == 1 && total_used > chunks[0].cap)) {
+      size_t want = 0;
+      for (auto& c : chunks) { want += c.cap; cudaFree(c.p); }
+      chunks.clear();
+      uint8_t* p = nullptr;
+      if (cudaMalloc((void**)&p, want) == cudaSuccess) chunks.push_back({p, want});
+      else cudaGetLastError();
+    }
+    used = 0; total_used = 0;
+  }
+  void* alloc_bytes(size_t bytes) {
+    bytes = (bytes + 255) & ~(size_t)255;
+    if (bytes == 0) bytes = 256;
+    if (chunks.empty() || used + bytes > chunks.back().cap) {
+      size_t want = bytes * 2 > (size_t)(8u << 20) ? bytes * 2 : (size_t)(8u << 20);
+      uint8_t* p = nullptr;
+      if (cudaMalloc((void**)&p, want) != cudaSuccess) { cudaGetLastError(); failed = true; return nullptr; }
+      chunks.push_back({p, want});
+      used = 0;
+    }
+    void* r = chunks.back().p + used;
+    used += bytes; total_used += bytes;
+    return r;
+  }
+  template <class T> T* alloc(size_t n) { return (T*)alloc_bytes(n * sizeof(T)); }
+  void release() { for (auto& c : chunks) cudaFree(c.p); chunks.clear(); used = 0; }
+};
+
+}  // namespace rfq
+
+struct rfq_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr, own_stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  std::string err;
+  rfq::Prof prof;
+  rfq::DevPool pool;
+  // staged batch
+  bool staged = false;
+  uint32_t n_docs = 0, n_tiles = 0;
+  uint64_t arena_bytes = 0;
+  const uint8_t* h_arena = nullptr;  // host copy of the packed arena (caller's or h_stage)
+  std::vector<uint32_t> h_doc_off, h_doc_len, h_tile_base;
+  rfq::DevBuf d_arena, d_doctab, d_out, d_arena2;
+  rfq::HostBuf h_stage, h_doctab, h_out, h_tabs, h_small;
+  uint32_t *d_doc_off = nullptr, *d_doc_len = nullptr, *d_tile_base = nullptr;
+  // last run
+  bool have_output = false, timed = false, fetched = false;
+  uint64_t out_total = 0;
+  unsigned long long *d_out_off = nullptr, *d_out_len = nullptr;
+  int32_t* d_status = nullptr;
+  uint32_t *d_rows = nullptr, *d_cols = nullptr;
+  uint8_t* d_attempt = nullptr;
+  uint64_t* h_out_off = nullptr; uint64_t* h_out_len = nullptr;
+  int32_t* h_status = nullptr; uint32_t* h_rows = nullptr; uint32_t* h_cols = nullptr;
+  uint8_t* h_attempt = nullptr;
+  float last_ms = 0.f;
+  uint64_t h2d_bytes = 0, d2h_bytes = 0;
+
+  unsigned long long* h_scalar() {
+    if (!h_small.p) h_small.reserve(4096);
+    return (unsigned long long*)h_small.p;
+  }
+  void release_all() {
+    pool.release();
+    d_arena.release(); d_doctab.release(); d_out.release(); d_arena2.release();
+    h_stage.release(); h_doctab.release(); h_out.release(); h_tabs.release(); h_small.release();
+  }
+};

@@ -1,0 +1,305 @@
+// C-ABI layer (include/rfq_parse.h): context, device/pinned memory pools, staging, fetch.
+// Host-side orchestration only; every byte of parsing happens in the kernels.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "../../include/rfq_parse.h"
+#include "ctx.h"
+
+namespace rfq {
+std::atomic<uint64_t> g_launch_count{0};
+}
+
+using namespace rfq;
+
+extern "C" {
+
+const char* rfq_version(void) { return "rfq-parse-b200 0.1 (sm_100a)"; }
+
+int rfq_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int rfq_create(int device, rfq_ctx** out) {
+  if (!out) return RFQ_ERR_ARG;
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0 || device < 0 || device >= n) {
+    cudaGetLastError();
+    fprintf(stderr, "rfq_create: no usable CUDA device %d (%s); there is no CPU fallback\n",
+            device, e != cudaSuccess ? cudaGetErrorString(e) : "bad index");
+    return RFQ_ERR_CUDA;
+  }
+  rfq_ctx* c = new rfq_ctx();
+  c->device = device;
+  if (cudaSetDevice(device) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) {
+    cudaGetLastError();
+    delete c;
+    return RFQ_ERR_CUDA;
+  }
+  c->stream = c->own_stream;
+  *out = c;
+  return RFQ_OK;
+}
+
+void rfq_destroy(rfq_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  c->release_all();
+  if (c->ev0) cudaEventDestroy(c->ev0);
+  if (c->ev1) cudaEventDestroy(c->ev1);
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  delete c;
+}
+
+const char* rfq_last_error(const rfq_ctx* c) { return c ? c->err.c_str() : "null ctx"; }
+
+int rfq_set_stream(rfq_ctx* c, void* s) {
+  if (!c) return RFQ_ERR_ARG;
+  c->stream = s ? (cudaStream_t)s : c->own_stream;
+  return RFQ_OK;
+}
+void* rfq_get_stream(rfq_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+void* rfq_host_alloc(rfq_ctx* c, uint64_t bytes) {
+  if (!c) return nullptr;
+  cudaSetDevice(c->device);
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+    c->err = "cudaHostAlloc failed";
+    cudaGetLastError();
+    return nullptr;
+  }
+  return p;
+}
+void rfq_host_free(rfq_ctx* c, void* p) {
+  if (c && p) { cudaSetDevice(c->device); cudaFreeHost(p); }
+}
+
+int rfq_stage(rfq_ctx* c, const uint8_t* arena, const uint64_t* offsets, const uint64_t* lengths,
+              uint32_t n) {
+  if (!c || (n && (!arena || !offsets || !lengths))) return RFQ_ERR_ARG;
+  RFQ_CK(c, cudaSetDevice(c->device));
+  RFQ_CK(c, cudaStreamSynchronize(c->stream));  // previous run must be done before buffers move
+  c->n_docs = n;
+  c->staged = false;
+  c->have_output = false;
+  bool aligned = true;
+  uint64_t span = 0;
+  for (uint32_t d = 0; d < n; ++d) {
+    if (offsets[d] % RFQ_ALIGN) aligned = false;
+    if (d && offsets[d] < offsets[d - 1] + lengths[d - 1]) aligned = false;  // overlapping/unordered
+    span = std::max<uint64_t>(span, offsets[d] + lengths[d]);
+  }
+  c->h_doc_off.resize(n); c->h_doc_len.resize(n); c->h_tile_base.resize(n + 1);
+  uint64_t total = 0, tiles = 0;
+  if (aligned) {
+    total = (span + RFQ_ALIGN - 1) / RFQ_ALIGN * RFQ_ALIGN;
+    for (uint32_t d = 0; d < n; ++d) {
+      c->h_doc_off[d] = (uint32_t)offsets[d];
+      c->h_doc_len[d] = (uint32_t)lengths[d];
+    }
+  } else {
+    for (uint32_t d = 0; d < n; ++d) {
+      c->h_doc_off[d] = (uint32_t)total;
+      c->h_doc_len[d] = (uint32_t)lengths[d];
+      total += (lengths[d] + RFQ_ALIGN - 1) / RFQ_ALIGN * RFQ_ALIGN;
+    }
+  }
+  if (total + 64 >= (1ull << 32)) {
+    c->err = "batch arena must be < 4 GiB (split the batch)";
+    return RFQ_ERR_ARG;
+  }
+  for (uint32_t d = 0; d < n; ++d) {
+    c->h_tile_base[d] = (uint32_t)tiles;
+    tiles += (lengths[d] + RFQ_TILE - 1) / RFQ_TILE;
+  }
+  c->h_tile_base[n] = (uint32_t)tiles;
+  c->n_tiles = (uint32_t)tiles;
+  c->arena_bytes = total;
+  // device arena with 64 bytes of zeroed slack so vector loads past a document's end are safe
+  RFQ_CK(c, c->d_arena.reserve(total + 64));
+  RFQ_CK(c, cudaMemsetAsync((uint8_t*)c->d_arena.p + total, 0, 64, c->stream));
+  if (aligned) {
+    c->h_arena = arena;
+    if (total) {
+      uint64_t ncopy = std::min<uint64_t>(span, total);
+      RFQ_CK(c, cudaMemcpyAsync(c->d_arena.p, arena, ncopy, cudaMemcpyHostToDevice, c->stream));
+      if (ncopy < total)
+        RFQ_CK(c, cudaMemsetAsync((uint8_t*)c->d_arena.p + ncopy, 0, total - ncopy, c->stream));
+    }
+  } else {
+    RFQ_CK(c, c->h_stage.reserve(total + 64));
+    uint8_t* st = (uint8_t*)c->h_stage.p;
+    for (uint32_t d = 0; d < n; ++d) {
+      memcpy(st + c->h_doc_off[d], arena + offsets[d], lengths[d]);
+      uint64_t pad = (RFQ_ALIGN - lengths[d] % RFQ_ALIGN) % RFQ_ALIGN;
+      memset(st + c->h_doc_off[d] + lengths[d], 0, pad);
+    }
+    c->h_arena = st;
+    if (total)
+      RFQ_CK(c, cudaMemcpyAsync(c->d_arena.p, st, total, cudaMemcpyHostToDevice, c->stream));
+  }
+  c->h2d_bytes = total;
+  // document tables
+  size_t tab = sizeof(uint32_t) * (3ull * n + 1);
+  RFQ_CK(c, c->d_doctab.reserve(tab));
+  RFQ_CK(c, c->h_doctab.reserve(tab));
+  uint32_t* ht = (uint32_t*)c->h_doctab.p;
+  if (n) {
+    memcpy(ht, c->h_doc_off.data(), 4ull * n);
+    memcpy(ht + n, c->h_doc_len.data(), 4ull * n);
+  }
+  memcpy(ht + 2ull * n, c->h_tile_base.data(), 4ull * (n + 1));
+  RFQ_CK(c, cudaMemcpyAsync(c->d_doctab.p, ht, tab, cudaMemcpyHostToDevice, c->stream));
+  c->d_doc_off = (uint32_t*)c->d_doctab.p;
+  c->d_doc_len = c->d_doc_off + n;
+  c->d_tile_base = c->d_doc_len + n;
+  c->h2d_bytes += tab;
+  c->staged = true;
+  return RFQ_OK;
+}
+
+int rfq_text_run(rfq_ctx* c) {
+  if (!c) return RFQ_ERR_ARG;
+  if (!c->staged) { c->err = "rfq_text_run: nothing staged"; return RFQ_ERR_STATE; }
+  RFQ_CK(c, cudaSetDevice(c->device));
+  cudaStream_t s = c->stream;
+  uint32_t n = c->n_docs, nt = c->n_tiles;
+  c->prof.begin();
+  RFQ_CK(c, cudaEventRecord(c->ev0, s));
+  c->pool.reset();
+  TxtArgs a{};
+  a.arena = (const uint8_t*)c->d_arena.p;
+  a.doc_off = c->d_doc_off; a.doc_len = c->d_doc_len; a.tile_base = c->d_tile_base;
+  a.n_docs = n; a.n_tiles = nt;
+  a.tile_cnt = c->pool.alloc<uint32_t>(nt + 1);
+  a.tile_pre = c->pool.alloc<uint32_t>(nt + 1);
+  a.first_pos = c->pool.alloc<uint32_t>(n + 1);
+  a.last_end = c->pool.alloc<uint32_t>(n + 1);
+  a.out_len = c->pool.alloc<unsigned long long>(n + 1);
+  a.out_off = c->pool.alloc<unsigned long long>(n + 1);
+  a.out_total = c->pool.alloc<unsigned long long>(1);
+  a.skip = c->pool.alloc<uint32_t>(n + 1);
+  a.scan_tmp32 = c->pool.alloc<uint32_t>(scan_partials_needed(nt));
+  a.scan_tmp64 = c->pool.alloc<unsigned long long>(scan_partials_needed(n));
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  c->prof.mark("txt_count+extent", s);
+  txt_pipeline(a, s);
+  unsigned long long total = 0;
+  if (n) {
+    RFQ_CK(c, cudaMemcpyAsync(c->h_scalar(), a.out_total, 8, cudaMemcpyDeviceToHost, s));
+    RFQ_CK(c, cudaStreamSynchronize(s));
+    total = *c->h_scalar();
+  }
+  RFQ_CK(c, c->d_out.reserve(total + 16));
+  c->prof.mark("txt_emit", s);
+  txt_emit(a, (uint8_t*)c->d_out.p, s);
+  c->prof.mark("end", s);
+  RFQ_CK(c, cudaEventRecord(c->ev1, s));
+  RFQ_CK(c, cudaGetLastError());
+  c->out_total = total;
+  c->d_out_off = a.out_off; c->d_out_len = a.out_len;
+  c->d_status = nullptr; c->d_rows = nullptr; c->d_cols = nullptr; c->d_attempt = nullptr;
+  c->have_output = true;
+  c->timed = true;
+  return RFQ_OK;
+}
+
+int rfq_fetch(rfq_ctx* c) {
+  if (!c) return RFQ_ERR_ARG;
+  if (!c->have_output) { c->err = "rfq_fetch: no run to fetch"; return RFQ_ERR_STATE; }
+  RFQ_CK(c, cudaSetDevice(c->device));
+  cudaStream_t s = c->stream;
+  uint32_t n = c->n_docs;
+  RFQ_CK(c, c->h_out.reserve(c->out_total + 16));
+  RFQ_CK(c, c->h_tabs.reserve((8ull + 8 + 4 + 4 + 4 + 1) * (n + 1) + 64));
+  uint8_t* base = (uint8_t*)c->h_tabs.p;
+  c->h_out_off = (uint64_t*)base;
+  c->h_out_len = (uint64_t*)(base + 8ull * (n + 1));
+  c->h_status = (int32_t*)(base + 16ull * (n + 1));
+  c->h_rows = (uint32_t*)(base + 20ull * (n + 1));
+  c->h_cols = (uint32_t*)(base + 24ull * (n + 1));
+  c->h_attempt = (uint8_t*)(base + 28ull * (n + 1));
+  memset(c->h_status, 0, 4ull * (n + 1) * 3 + (n + 1));
+  if (c->out_total)
+    RFQ_CK(c, cudaMemcpyAsync(c->h_out.p, c->d_out.p, c->out_total, cudaMemcpyDeviceToHost, s));
+  c->d2h_bytes = c->out_total;
+  if (n) {
+    RFQ_CK(c, cudaMemcpyAsync(c->h_out_off, c->d_out_off, 8ull * n, cudaMemcpyDeviceToHost, s));
+    RFQ_CK(c, cudaMemcpyAsync(c->h_out_len, c->d_out_len, 8ull * n, cudaMemcpyDeviceToHost, s));
+    c->d2h_bytes += 16ull * n;
+    if (c->d_status) {
+      RFQ_CK(c, cudaMemcpyAsync(c->h_status, c->d_status, 4ull * n, cudaMemcpyDeviceToHost, s));
+      c->d2h_bytes += 4ull * n;
+    }
+    if (c->d_rows) {
+      RFQ_CK(c, cudaMemcpyAsync(c->h_rows, c->d_rows, 4ull * n, cudaMemcpyDeviceToHost, s));
+      RFQ_CK(c, cudaMemcpyAsync(c->h_cols, c->d_cols, 4ull * n, cudaMemcpyDeviceToHost, s));
+      c->d2h_bytes += 8ull * n;
+    }
+    if (c->d_attempt) {
+      RFQ_CK(c, cudaMemcpyAsync(c->h_attempt, c->d_attempt, n, cudaMemcpyDeviceToHost, s));
+      c->d2h_bytes += n;
+    }
+  }
+  RFQ_CK(c, cudaStreamSynchronize(s));
+  if (c->timed) {
+    cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
+    c->prof.finish();
+    c->timed = false;
+  }
+  c->fetched = true;
+  return RFQ_OK;
+}
+
+int rfq_text_parse(rfq_ctx* c, const uint8_t* arena, const uint64_t* offsets,
+                   const uint64_t* lengths, uint32_t n) {
+  int r = rfq_stage(c, arena, offsets, lengths, n);
+  if (r) return r;
+  r = rfq_text_run(c);
+  if (r) return r;
+  return rfq_fetch(c);
+}
+
+int rfq_csv_parse(rfq_ctx* c, const uint8_t* arena, const uint64_t* offsets,
+                  const uint64_t* lengths, uint32_t n, const int64_t* max_rows) {
+  int r = rfq_stage(c, arena, offsets, lengths, n);
+  if (r) return r;
+  r = rfq_csv_run(c, max_rows);
+  if (r) return r;
+  return rfq_fetch(c);
+}
+
+uint32_t rfq_out_count(const rfq_ctx* c) { return c ? c->n_docs : 0; }
+const uint8_t* rfq_out_text(const rfq_ctx* c) { return c ? (const uint8_t*)c->h_out.p : nullptr; }
+const uint64_t* rfq_out_offsets(const rfq_ctx* c) { return c ? c->h_out_off : nullptr; }
+const uint64_t* rfq_out_lengths(const rfq_ctx* c) { return c ? c->h_out_len : nullptr; }
+const int32_t* rfq_out_status(const rfq_ctx* c) { return c ? c->h_status : nullptr; }
+uint64_t rfq_out_total_bytes(const rfq_ctx* c) { return c ? c->out_total : 0; }
+const uint32_t* rfq_out_rows(const rfq_ctx* c) { return c ? c->h_rows : nullptr; }
+const uint32_t* rfq_out_cols(const rfq_ctx* c) { return c ? c->h_cols : nullptr; }
+const uint8_t* rfq_out_attempt(const rfq_ctx* c) { return c ? c->h_attempt : nullptr; }
+
+float rfq_last_run_ms(const rfq_ctx* c) { return c ? c->last_ms : 0.f; }
+uint64_t rfq_launch_count(const rfq_ctx*) { return g_launch_count.load(); }
+int rfq_set_profile(rfq_ctx* c, int on) { if (!c) return RFQ_ERR_ARG; c->prof.on = on != 0; return RFQ_OK; }
+int rfq_profile_count(const rfq_ctx* c) { return c ? (int)c->prof.ms.size() : 0; }
+const char* rfq_profile_name(const rfq_ctx* c, int i) {
+  return (c && i >= 0 && i < (int)c->prof.names.size()) ? c->prof.names[i].c_str() : "";
+}
+float rfq_profile_ms(const rfq_ctx* c, int i) {
+  return (c && i >= 0 && i < (int)c->prof.ms.size()) ? c->prof.ms[i] : 0.f;
+}
+
+}  // extern "C"

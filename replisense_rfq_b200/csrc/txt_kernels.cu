@@ -1,0 +1,272 @@
+// Text path (raw e-mail bodies / PDF-extracted text): UTF-8 decode with errors='ignore',
+// universal newlines, str.strip() — reference app/file_parser.py:143-148.
+//
+// Layout: documents packed in one arena, each starting on a 16-byte boundary. A warp owns one
+// 512-byte tile of one document (32 lanes x one 16-byte vector load); tiles never span
+// documents. Three launches over the tiles:
+//   txt_count_kernel   per-tile emitted-byte count + per-document first/last non-space char
+//   (exclusive scan of tile counts)
+//   txt_extent_kernel  per-document output length and rank of its first emitted byte
+//   (exclusive scan of document lengths)
+//   txt_emit_kernel    compaction through shared memory, coalesced stores
+// HBM-bound byte work: no tensor cores.
+#include <cuda_runtime.h>
+#include "rfq_common.cuh"
+#include "utf8.cuh"
+#include "scan.cuh"
+#include "pipeline.h"
+
+namespace rfq {
+
+// 16 own bytes + 4 halo bytes on each side, in registers.
+struct Win {
+  uint32_t w[6];  // w[0] = bytes -4..-1, w[1..4] = own, w[5] = bytes 16..19
+  __device__ __forceinline__ uint32_t operator()(int64_t i) const {  // i in [-4, 20)
+    int j = (int)i + 4;
+    return (w[j >> 2] >> ((j & 3) * 8)) & 0xFFu;
+  }
+};
+
+struct GlobalAcc {  // slow path: doc-relative accessor into global memory
+  const uint8_t* p;
+  int64_t len;
+  __device__ __forceinline__ uint32_t operator()(int64_t i) const {
+    return (i >= 0 && i < len) ? p[i] : 0u;
+  }
+};
+
+__device__ __forceinline__ uint32_t mask_word(uint32_t v, int64_t pos, int64_t len) {
+  // zero the bytes of a 4-byte word at doc-relative `pos` that lie outside [0, len)
+  if (pos >= 0 && pos + 4 <= len) return v;
+  uint32_t m = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    if (pos + k >= 0 && pos + k < len) m |= 0xFFu << (8 * k);
+  return v & m;
+}
+
+// Evaluate one lane's 16 bytes. `doc` points at the document start (16-byte aligned).
+// emit: bit k = byte k is emitted; nsp: bit k = byte k starts an emitted non-space character.
+__device__ __forceinline__ void txt_lane_eval(const uint8_t* __restrict__ doc, uint32_t len,
+                                              uint32_t tile, int lane, Win& win, uint32_t& emit,
+                                              uint32_t& nsp) {
+  int64_t base = (int64_t)tile * RFQ_TILE + lane * 16;
+  uint4 v = make_uint4(0, 0, 0, 0);
+  if (base < len) v = __ldg(reinterpret_cast<const uint4*>(doc + base));
+  v.x = mask_word(v.x, base, len);
+  v.y = mask_word(v.y, base + 4, len);
+  v.z = mask_word(v.z, base + 8, len);
+  v.w = mask_word(v.w, base + 12, len);
+  uint32_t prev = __shfl_up_sync(0xffffffffu, v.w, 1);
+  uint32_t next = __shfl_down_sync(0xffffffffu, v.x, 1);
+  if (lane == 0)
+    prev = base >= 4 ? __ldg(reinterpret_cast<const uint32_t*>(doc + base - 4)) : 0u;
+  if (lane == 31) {
+    next = 0u;
+    if (base + 16 < len)
+      next = mask_word(__ldg(reinterpret_cast<const uint32_t*>(doc + base + 16)), base + 16, len);
+  }
+  win.w[0] = prev; win.w[1] = v.x; win.w[2] = v.y; win.w[3] = v.z; win.w[4] = v.w;
+  win.w[5] = next;
+  emit = 0; nsp = 0;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    if (base + k >= len) break;
+    uint32_t b = win(k);
+    bool e;
+    if (b < 0x80u) {
+      e = true;
+      if (b == '\n') {
+        uint32_t pb = win(k - 1);
+        if (pb == '\r') e = false;
+        else if (pb >= 0x80u) {  // rare: dropped bytes between CR and LF
+          GlobalAcc g{doc, (int64_t)len};
+          e = !u8_lf_swallowed(g, base + k);
+        }
+      }
+      if (e && !u8_is_space_at(win, k)) nsp |= 1u << k;
+    } else {
+      e = u8_keep(win, k);
+      if (e && !u8_is_cont(b) && !u8_is_space_at(win, k)) nsp |= 1u << k;
+    }
+    if (e) emit |= 1u << k;
+  }
+}
+
+__device__ __forceinline__ uint32_t find_doc(const uint32_t* __restrict__ tile_base, uint32_t n,
+                                             uint32_t t) {
+  // largest d with tile_base[d] <= t  (tile_base has n+1 entries, ascending)
+  uint32_t lo = 0, hi = n;
+  while (hi - lo > 1) {
+    uint32_t mid = (lo + hi) >> 1;
+    if (__ldg(tile_base + mid) <= t) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+__global__ void __launch_bounds__(256) txt_count_kernel(
+    const uint8_t* __restrict__ arena, const uint32_t* __restrict__ doc_off,
+    const uint32_t* __restrict__ doc_len, const uint32_t* __restrict__ tile_base, uint32_t n_docs,
+    uint32_t n_tiles, uint32_t* __restrict__ tile_cnt, uint32_t* __restrict__ first_pos,
+    uint32_t* __restrict__ last_end) {
+  uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
+  int lane = threadIdx.x & 31;
+  if (t >= n_tiles) return;
+  uint32_t d = find_doc(tile_base, n_docs, t);
+  uint32_t tile = t - tile_base[d];
+  uint32_t len = doc_len[d];
+  const uint8_t* doc = arena + doc_off[d];
+  Win win; uint32_t emit, nsp;
+  txt_lane_eval(doc, len, tile, lane, win, emit, nsp);
+  uint32_t cnt = __popc(emit);
+  uint32_t base = tile * RFQ_TILE + lane * 16;
+  uint32_t fp = 0xFFFFFFFFu, le = 0u;
+  if (nsp) {
+    fp = base + (__ffs(nsp) - 1);
+    int k = 31 - __clz(nsp);
+    uint32_t b = win(k);
+    int cl = b < 0x80u ? 1 : u8_lead_len(b);
+    le = base + k + cl;
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    fp = min(fp, __shfl_xor_sync(0xffffffffu, fp, o));
+    le = max(le, __shfl_xor_sync(0xffffffffu, le, o));
+  }
+  if (lane == 0) {
+    tile_cnt[t] = cnt;
+    if (fp != 0xFFFFFFFFu) {
+      atomicMin(first_pos + d, fp);
+      atomicMax(last_end + d, le);
+    }
+  }
+}
+
+// rank (number of emitted bytes before doc-relative position p) inside document d
+__device__ __forceinline__ uint32_t txt_rank_before(const uint8_t* doc, uint32_t len,
+                                                    const uint32_t* __restrict__ tile_pre,
+                                                    uint32_t tb, uint32_t p, int lane) {
+  uint32_t tile = p / RFQ_TILE;
+  if (tile * RFQ_TILE >= len) return 0xFFFFFFFFu;  // caller handles p == end-of-last-tile
+  Win win; uint32_t emit, nsp;
+  txt_lane_eval(doc, len, tile, lane, win, emit, nsp);
+  uint32_t base = tile * RFQ_TILE + lane * 16;
+  uint32_t c = 0;
+  if (p > base) c = (p - base >= 16) ? __popc(emit) : __popc(emit & ((1u << (p - base)) - 1u));
+#pragma unroll
+  for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  return tile_pre[tb + tile] + c;
+}
+
+// One warp per document: out_len and skip (global rank of the first emitted output byte).
+__global__ void __launch_bounds__(256) txt_extent_kernel(
+    const uint8_t* __restrict__ arena, const uint32_t* __restrict__ doc_off,
+    const uint32_t* __restrict__ doc_len, const uint32_t* __restrict__ tile_base, uint32_t n_docs,
+    const uint32_t* __restrict__ tile_pre, const uint32_t* __restrict__ tile_cnt,
+    const uint32_t* __restrict__ first_pos, const uint32_t* __restrict__ last_end,
+    unsigned long long* __restrict__ out_len, uint32_t* __restrict__ skip) {
+  uint32_t d = blockIdx.x * 8 + (threadIdx.x >> 5);
+  int lane = threadIdx.x & 31;
+  if (d >= n_docs) return;
+  uint32_t fp = first_pos[d];
+  if (fp == 0xFFFFFFFFu) {
+    if (lane == 0) { out_len[d] = 0; skip[d] = 0; }
+    return;
+  }
+  uint32_t len = doc_len[d], tb = tile_base[d];
+  const uint8_t* doc = arena + doc_off[d];
+  uint32_t r0 = txt_rank_before(doc, len, tile_pre, tb, fp, lane);
+  uint32_t le = last_end[d];
+  uint32_t r1;
+  if (le >= len && (le % RFQ_TILE) == 0) {  // ends exactly at the end of the last tile
+    uint32_t lt = tile_base[d + 1] - 1;
+    r1 = tile_pre[lt] + tile_cnt[lt];
+  } else {
+    r1 = txt_rank_before(doc, len, tile_pre, tb, le, lane);
+  }
+  if (lane == 0) { out_len[d] = r1 - r0; skip[d] = r0; }
+}
+
+__global__ void __launch_bounds__(256) txt_emit_kernel(
+    const uint8_t* __restrict__ arena, const uint32_t* __restrict__ doc_off,
+    const uint32_t* __restrict__ doc_len, const uint32_t* __restrict__ tile_base, uint32_t n_docs,
+    uint32_t n_tiles, const uint32_t* __restrict__ tile_pre,
+    const uint32_t* __restrict__ first_pos, const uint32_t* __restrict__ last_end,
+    const unsigned long long* __restrict__ out_off, const uint32_t* __restrict__ skip,
+    uint8_t* __restrict__ out) {
+  __shared__ uint8_t stage[8][RFQ_TILE];
+  int wib = threadIdx.x >> 5;
+  uint32_t t = blockIdx.x * 8 + wib;
+  int lane = threadIdx.x & 31;
+  if (t >= n_tiles) return;
+  uint32_t d = find_doc(tile_base, n_docs, t);
+  uint32_t fp = first_pos[d];
+  if (fp == 0xFFFFFFFFu) return;
+  uint32_t le = last_end[d];
+  uint32_t tile = t - tile_base[d];
+  uint32_t tb0 = tile * RFQ_TILE;
+  if (tb0 + RFQ_TILE <= fp || tb0 >= le) return;  // tile entirely stripped
+  uint32_t len = doc_len[d];
+  const uint8_t* doc = arena + doc_off[d];
+  Win win; uint32_t emit, nsp;
+  txt_lane_eval(doc, len, tile, lane, win, emit, nsp);
+  uint32_t base = tb0 + lane * 16;
+  // restrict to [fp, le)
+  uint32_t keep = emit;
+  if (base < fp) keep &= (fp - base >= 16) ? 0u : ~((1u << (fp - base)) - 1u);
+  if (base + 16 > le) keep &= (le <= base) ? 0u : ((1u << (le - base)) - 1u);
+  uint32_t c = __popc(keep), incl = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t x = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += x;
+  }
+  uint32_t excl = incl - c;
+  uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+  // rank of this tile's first kept byte within the document's output
+  // emitted bytes in this tile that precede fp (non-zero only in the tile containing fp)
+  uint32_t stripped_lead = 0u;
+  if (base < fp)
+    stripped_lead = (fp - base >= 16) ? __popc(emit) : __popc(emit & ((1u << (fp - base)) - 1u));
+#pragma unroll
+  for (int o = 16; o; o >>= 1) stripped_lead += __shfl_xor_sync(0xffffffffu, stripped_lead, o);
+  uint8_t* st = stage[wib];
+  uint32_t pos = excl;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    if (keep & (1u << k)) {
+      uint32_t b = win(k);
+      st[pos++] = (uint8_t)(b == '\r' ? '\n' : b);
+    }
+  }
+  __syncwarp();
+  unsigned long long dst0 = out_off[d] + (unsigned long long)(tile_pre[t] + stripped_lead - skip[d]);
+  for (uint32_t i = lane; i < total; i += 32) out[dst0 + i] = st[i];
+}
+
+// ---------------------------------------------------------------------------------------------
+void txt_pipeline(const TxtArgs& a, cudaStream_t s) {
+  if (a.n_docs == 0) return;
+  cudaMemsetAsync(a.first_pos, 0xFF, sizeof(uint32_t) * a.n_docs, s);
+  cudaMemsetAsync(a.last_end, 0, sizeof(uint32_t) * a.n_docs, s);
+  if (a.n_tiles) {
+    uint32_t nb = (a.n_tiles + 7) / 8;
+    RFQ_LAUNCH(txt_count_kernel, nb, 256, 0, s, a.arena, a.doc_off, a.doc_len, a.tile_base,
+               a.n_docs, a.n_tiles, a.tile_cnt, a.first_pos, a.last_end);
+    exclusive_scan<SumU32>(a.tile_cnt, a.tile_pre, a.n_tiles, a.scan_tmp32, nullptr, s);
+  }
+  RFQ_LAUNCH(txt_extent_kernel, (a.n_docs + 7) / 8, 256, 0, s, a.arena, a.doc_off, a.doc_len,
+             a.tile_base, a.n_docs, a.tile_pre, a.tile_cnt, a.first_pos, a.last_end, a.out_len,
+             a.skip);
+  exclusive_scan<SumU64>(a.out_len, a.out_off, a.n_docs, a.scan_tmp64, a.out_total, s);
+}
+
+void txt_emit(const TxtArgs& a, uint8_t* out, cudaStream_t s) {
+  if (a.n_tiles == 0) return;
+  uint32_t nb = (a.n_tiles + 7) / 8;
+  RFQ_LAUNCH(txt_emit_kernel, nb, 256, 0, s, a.arena, a.doc_off, a.doc_len, a.tile_base, a.n_docs,
+             a.n_tiles, a.tile_pre, a.first_pos, a.last_end, a.out_off, a.skip, out);
+}
+
+}  // namespace rfq

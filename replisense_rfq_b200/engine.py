@@ -1,0 +1,207 @@
+"""Batched many-documents entry point over the C ABI (SURVEY.md §8b "new entry point")."""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+from typing import Sequence
+
+import numpy as np
+
+from . import _lib
+
+ENCODINGS = ["utf-8", "latin-1", "cp1252"]  # app/file_parser.py:298
+SEPARATORS = [",", ";", "\t"]  # app/file_parser.py:299
+
+
+class EngineError(RuntimeError):
+    pass
+
+
+class PinnedArena:
+    """Pinned host memory the caller packs documents into (16-byte aligned starts)."""
+
+    def __init__(self, engine: "Engine", capacity: int):
+        self.engine = engine
+        self.capacity = max(int(capacity), 16)
+        self.ptr = engine.lib.rfq_host_alloc(engine.ctx, self.capacity)
+        if not self.ptr:
+            raise EngineError("pinned allocation failed")
+        self.view = np.ctypeslib.as_array((C.c_uint8 * self.capacity).from_address(self.ptr))
+
+    def pack(self, docs: Sequence[bytes]):
+        n = len(docs)
+        lengths = np.fromiter((len(d) for d in docs), dtype=np.uint64, count=n)
+        padded = (lengths + np.uint64(15)) & ~np.uint64(15)
+        offsets = np.zeros(n, dtype=np.uint64)
+        if n > 1:
+            np.cumsum(padded[:-1], out=offsets[1:])
+        total = int(padded.sum())
+        if total > self.capacity:
+            raise EngineError("arena too small")
+        v = self.view
+        for d, o in zip(docs, offsets.tolist()):
+            if d:
+                v[o:o + len(d)] = np.frombuffer(d, dtype=np.uint8)
+        return offsets, lengths, total
+
+    def free(self):
+        if self.ptr:
+            self.view = None
+            self.engine.lib.rfq_host_free(self.engine.ctx, self.ptr)
+            self.ptr = None
+
+
+class BatchResult:
+    """Views over the library-owned pinned output of the last run (valid until the next run)."""
+
+    def __init__(self, eng: "Engine"):
+        lib, ctx = eng.lib, eng.ctx
+        n = lib.rfq_out_count(ctx)
+        self.n = n
+        self.total = lib.rfq_out_total_bytes(ctx)
+        self.text_ptr = lib.rfq_out_text(ctx)
+
+        def arr(ptr, ctype, dtype):
+            if n == 0 or not ptr:
+                return np.zeros(0, dtype=dtype)
+            return np.ctypeslib.as_array((ctype * n).from_address(ptr)).copy()
+
+        self.offsets = arr(lib.rfq_out_offsets(ctx), C.c_uint64, np.uint64)
+        self.lengths = arr(lib.rfq_out_lengths(ctx), C.c_uint64, np.uint64)
+        self.status = arr(lib.rfq_out_status(ctx), C.c_int32, np.int32)
+        self.rows = arr(lib.rfq_out_rows(ctx), C.c_uint32, np.uint32)
+        self.cols = arr(lib.rfq_out_cols(ctx), C.c_uint32, np.uint32)
+        self.attempt = arr(lib.rfq_out_attempt(ctx), C.c_uint8, np.uint8)
+
+    def doc_bytes(self, d: int) -> bytes:
+        ln = int(self.lengths[d])
+        if ln == 0:
+            return b""
+        return C.string_at(self.text_ptr + int(self.offsets[d]), ln)
+
+    def doc_str(self, d: int) -> str:
+        return self.doc_bytes(d).decode("utf-8")
+
+
+class Engine:
+    """One CUDA device, one stream. Thread-safe (calls are serialised per engine)."""
+
+    def __init__(self, device: int = 0):
+        self.lib = _lib.load()
+        h = C.c_void_p()
+        rc = self.lib.rfq_create(device, C.byref(h))
+        if rc != 0 or not h:
+            raise EngineError(
+                f"rfq_create(device={device}) failed: no CUDA device — there is no CPU fallback")
+        self.ctx = h
+        self.device = device
+        self.lock = threading.Lock()
+        self._arena = None
+
+    # -- helpers
+    def _check(self, rc: int, what: str):
+        if rc != 0:
+            raise EngineError(f"{what} failed ({rc}): {self.lib.rfq_last_error(self.ctx).decode()}")
+
+    def arena(self, nbytes: int) -> PinnedArena:
+        if self._arena is None or self._arena.capacity < nbytes:
+            if self._arena is not None:
+                self._arena.free()
+            self._arena = PinnedArena(self, int(nbytes * 1.25) + 4096)
+        return self._arena
+
+    def _pack(self, docs: Sequence[bytes]):
+        need = sum((len(d) + 15) & ~15 for d in docs) + 64
+        a = self.arena(need)
+        offsets, lengths, total = a.pack(docs)
+        return a, offsets, lengths
+
+    def stage(self, arena: PinnedArena, offsets: np.ndarray, lengths: np.ndarray):
+        self._check(self.lib.rfq_stage(self.ctx, arena.ptr, offsets.ctypes.data,
+                                       lengths.ctypes.data, len(offsets)), "rfq_stage")
+
+    def set_stream(self, stream_ptr: int | None):
+        self._check(self.lib.rfq_set_stream(self.ctx, stream_ptr), "rfq_set_stream")
+
+    # -- text
+    def text_batch(self, docs: Sequence[bytes]) -> BatchResult:
+        with self.lock:
+            a, off, ln = self._pack(docs)
+            self._check(self.lib.rfq_text_parse(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data,
+                                                len(docs)), "rfq_text_parse")
+            return BatchResult(self)
+
+    def parse_text_many(self, docs: Sequence[bytes]) -> "list[str]":
+        with self.lock:
+            a, off, ln = self._pack(docs)
+            self._check(self.lib.rfq_text_parse(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data,
+                                                len(docs)), "rfq_text_parse")
+            r = BatchResult(self)
+            return [r.doc_str(d) for d in range(r.n)]
+
+    # -- csv
+    def csv_batch(self, docs: Sequence[bytes], max_rows=1000) -> BatchResult:
+        n = len(docs)
+        if np.isscalar(max_rows):
+            mr = np.full(n, int(max_rows), dtype=np.int64)
+        else:
+            mr = np.asarray(max_rows, dtype=np.int64)
+        with self.lock:
+            a, off, ln = self._pack(docs)
+            self._check(self.lib.rfq_csv_parse(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data,
+                                               n, mr.ctypes.data), "rfq_csv_parse")
+            return BatchResult(self)
+
+    def parse_csv_many(self, docs: Sequence[bytes], max_rows=1000) -> "list[str | None]":
+        """raw_text per document; None where every (encoding, separator) attempt failed (the
+        caller raises the reference's FileParsingError)."""
+        with self.lock:
+            pass
+        r = self.csv_batch(docs, max_rows)
+        out = []
+        for d in range(r.n):
+            st = int(r.status[d])
+            if st == _lib.DOC_OK:
+                out.append(r.doc_str(d))
+            elif st == _lib.DOC_CSV_UNPARSEABLE:
+                out.append(None)
+            else:
+                raise EngineError(f"document {d}: unsupported construct on the GPU path (status {st})")
+        return out
+
+    # -- measurement
+    def last_run_ms(self) -> float:
+        return float(self.lib.rfq_last_run_ms(self.ctx))
+
+    def launch_count(self) -> int:
+        return int(self.lib.rfq_launch_count(self.ctx))
+
+    def profile(self) -> "list[tuple[str, float]]":
+        k = self.lib.rfq_profile_count(self.ctx)
+        return [(self.lib.rfq_profile_name(self.ctx, i).decode(), float(self.lib.rfq_profile_ms(self.ctx, i)))
+                for i in range(k)]
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            if self._arena is not None:
+                self._arena.free()
+                self._arena = None
+            self.lib.rfq_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_default = {}
+_default_lock = threading.Lock()
+
+
+def default_engine(device: int = 0) -> Engine:
+    with _default_lock:
+        if device not in _default:
+            _default[device] = Engine(device)
+        return _default[device]

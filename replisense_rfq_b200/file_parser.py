@@ -1,0 +1,195 @@
+"""Host-side mirror of the reference's `FileParser` (app/file_parser.py:25-375) for the formats
+on the north-star path — .txt, .csv, .xlsx — with every byte of parsing done by the CUDA
+library behind include/rfq_parse.h.  Same constructor arguments, method names, result envelope
+and error behaviour as the reference, plus the batched `parse_many` entry point.
+
+Out of scope here: .pdf, .docx, .xls, .json — they are reported as unsupported
+file types rather than routed to a CPU implementation.
+"""
+from __future__ import annotations
+
+import asyncio
+import hashlib
+import logging
+from concurrent.futures import ThreadPoolExecutor
+from pathlib import Path
+from typing import Any, Dict, Optional, Sequence
+
+from . import _lib
+from .engine import Engine, EngineError, default_engine
+
+logger = logging.getLogger(__name__)
+
+HAS_PYMUPDF = False  # PDF extraction (MuPDF layout engine) is not part of this build
+
+_SUPPORTED = {".txt", ".xlsx", ".csv"}
+
+_CSV_FAIL = "Unable to parse CSV with any supported encoding/separator combination"
+_EXCEL_EMPTY = "Excel file appears to be empty or unreadable"
+
+
+class FileParsingError(Exception):
+    """Same role as app/file_parser.py:25-27."""
+
+
+class FileParser:
+    """Drop-in for app/file_parser.py:29 (`FileParser(max_file_size_mb=10, max_excel_rows=1000)`)."""
+
+    def __init__(self, max_file_size_mb: int = 10, max_excel_rows: int = 1000,
+                 device: int = 0, engine: Optional[Engine] = None):
+        self.max_file_size = max_file_size_mb * 1024 * 1024
+        self.max_excel_rows = max_excel_rows
+        self.thread_pool = ThreadPoolExecutor(max_workers=4)  # app/file_parser.py:33
+        self.supported_extensions = set(_SUPPORTED)
+        self._device = device
+        self._engine = engine
+
+    @property
+    def engine(self) -> Engine:
+        if self._engine is None:
+            self._engine = default_engine(self._device)  # raises without a CUDA device
+        return self._engine
+
+    # ------------------------------------------------------------------ envelope (:44-99)
+    async def parse_file_async(self, file_path: str) -> Dict[str, Any]:
+        file_path = Path(file_path)
+        await self._validate_file_async(file_path)
+        file_hash = await self._get_file_hash_async(file_path)
+        cached = self._get_cached_result(file_hash)
+        if cached:
+            return cached
+        suffix = file_path.suffix.lower()
+        try:
+            if suffix == ".txt":
+                text = await self._parse_txt_async(file_path)
+            elif suffix == ".xlsx":
+                text = await self._parse_excel_async(file_path)
+            elif suffix == ".csv":
+                text = await self._parse_csv_async(file_path)
+            else:
+                raise FileParsingError(f"Unsupported file format: {file_path.suffix}")
+            result = {
+                "raw_text": text,
+                "source_file": str(file_path.name),
+                "file_size": file_path.stat().st_size,
+                "file_hash": file_hash,
+                "parsing_method": f"async_{suffix[1:]}",
+            }
+            self._cache_result(file_hash, result)
+            return result
+        except Exception as e:  # the reference wraps everything from the dispatch (:93-95)
+            raise FileParsingError(f"Failed to parse {file_path.name}: {str(e)}")
+
+    def parse_file(self, file_path: str) -> Dict[str, Any]:
+        return asyncio.run(self.parse_file_async(file_path))
+
+    async def _validate_file_async(self, file_path: Path) -> None:
+        """app/file_parser.py:101-120: FileNotFoundError escapes un-wrapped."""
+        if not file_path.exists():
+            raise FileNotFoundError(f"File not found: {file_path}")
+        file_size = file_path.stat().st_size
+        if file_size > self.max_file_size:
+            raise FileParsingError(
+                f"File too large: {file_size / 1024 / 1024:.1f}MB "
+                f"(max: {self.max_file_size / 1024 / 1024}MB)")
+        if file_path.suffix.lower() not in self.supported_extensions:
+            raise FileParsingError(f"Unsupported file type: {file_path.suffix}")
+        try:
+            with open(file_path, "rb") as f:
+                f.read(1)
+        except PermissionError:
+            raise FileParsingError(f"Permission denied reading file: {file_path}")
+
+    async def _get_file_hash_async(self, file_path: Path) -> str:
+        """MD5 stays on the host (app/file_parser.py:122-130)."""
+        h = hashlib.md5()
+        with open(file_path, "rb") as f:
+            for chunk in iter(lambda: f.read(1 << 20), b""):
+                h.update(chunk)
+        return h.hexdigest()
+
+    def _get_cached_result(self, file_hash: str) -> Optional[Dict[str, Any]]:
+        return None  # the reference's cache hooks are no-ops (:132-141)
+
+    def _cache_result(self, file_hash: str, result: Dict[str, Any]) -> None:
+        pass
+
+    # ------------------------------------------------------------------ text (:143-159)
+    async def _parse_txt_async(self, file_path: Path) -> str:
+        data = Path(file_path).read_bytes()
+        return self.engine.parse_text_many([data])[0]
+
+    # ------------------------------------------------------------------ csv (:288-313)
+    async def _parse_csv_async(self, file_path: Path) -> str:
+        return await asyncio.get_event_loop().run_in_executor(
+            self.thread_pool, self._parse_csv_sync, file_path)
+
+    def _parse_csv_sync(self, file_path: Path) -> str:
+        try:
+            data = Path(file_path).read_bytes()
+            text = self.engine.parse_csv_many([data], self.max_excel_rows)[0]
+            if text is None:
+                raise FileParsingError(_CSV_FAIL)
+            return text
+        except Exception as e:
+            raise FileParsingError(f"CSV parsing failed: {str(e)}")
+
+    # ------------------------------------------------------------------ excel (:214-252)
+    async def _parse_excel_async(self, file_path: Path) -> str:
+        return await asyncio.get_event_loop().run_in_executor(
+            self.thread_pool, self._parse_excel_sync, file_path)
+
+    def _parse_excel_sync(self, file_path: Path) -> str:
+        try:
+            from . import xlsx_host
+            parts = xlsx_host.open_workbook(Path(file_path).read_bytes())
+            return xlsx_host.parse_workbooks(self.engine, [parts], self.max_excel_rows)[0]
+        except Exception as e:
+            raise FileParsingError(f"Excel parsing failed: {str(e)}")
+
+    # ------------------------------------------------------------------ batched entry point
+    def parse_many(self, docs: Sequence[bytes], kinds: Sequence[str]) -> "list[str | FileParsingError]":
+        """Many documents in one go. `kinds[i]` in {'txt', 'csv', 'xlsx'}; returns raw_text or the
+        FileParsingError the reference would have raised for that document, in input order."""
+        out: "list[Any]" = [None] * len(docs)
+        by_kind: "dict[str, list[int]]" = {}
+        for i, k in enumerate(kinds):
+            by_kind.setdefault(k.lower().lstrip("."), []).append(i)
+        for k, idx in by_kind.items():
+            batch = [docs[i] for i in idx]
+            if k == "txt":
+                res = self.engine.parse_text_many(batch)
+            elif k == "csv":
+                res = [r if r is not None else FileParsingError(f"CSV parsing failed: {_CSV_FAIL}")
+                       for r in self.engine.parse_csv_many(batch, self.max_excel_rows)]
+            elif k == "xlsx":
+                from . import xlsx_host
+                res = []
+                books = []
+                for b in batch:
+                    try:
+                        books.append(xlsx_host.open_workbook(b))
+                    except Exception as e:  # noqa: BLE001
+                        books.append(FileParsingError(f"Excel parsing failed: {e}"))
+                good = [b for b in books if not isinstance(b, Exception)]
+                texts = iter(xlsx_host.parse_workbooks(self.engine, good, self.max_excel_rows))
+                res = [b if isinstance(b, Exception) else next(texts) for b in books]
+            else:
+                res = [FileParsingError(f"Unsupported file type: .{k}")] * len(batch)
+            for i, r in zip(idx, res):
+                out[i] = r
+        return out
+
+    def __del__(self):
+        if hasattr(self, "thread_pool"):
+            self.thread_pool.shutdown(wait=False)
+
+
+async def parse_file_async(file_path: str, max_file_size_mb: int = 10) -> Dict[str, Any]:
+    """app/file_parser.py:365-368."""
+    return await FileParser(max_file_size_mb=max_file_size_mb).parse_file_async(file_path)
+
+
+def get_supported_extensions() -> set:
+    """app/file_parser.py:370-375, restricted to the formats this build parses."""
+    return set(_SUPPORTED)
