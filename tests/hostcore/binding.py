@@ -1,0 +1,73 @@
+"""ctypes access to the TEST-ONLY host build of the device core headers (tests/hostcore)."""
+import ctypes as C
+import subprocess
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+
+
+class HcCell(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("is_na", "int_status", "uint_status", "uint_neg", "uint_gt",
+                                         "float_ok", "bool_tok", "inf_tok")] + [
+        ("ival", C.c_int64), ("uval", C.c_uint64), ("fval", C.c_double),
+        ("nbytes", C.c_uint32), ("ncp", C.c_uint32), ("nesc", C.c_uint32),
+        ("utf8_ok", C.c_int32), ("has_fchar", C.c_int32)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        so = HERE / "libhostcore.so"
+        srcs = [HERE / "hostcore.cpp"] + sorted((HERE.parent.parent / "replisense_rfq_b200/csrc").glob("*.cuh"))
+        if not so.exists() or any(s.stat().st_mtime > so.stat().st_mtime for s in srcs):
+            subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-ffp-contract=off",
+                                   "-o", str(so), str(HERE / "hostcore.cpp")])
+        _lib = C.CDLL(str(so))
+        _lib.hc_txt.restype = C.c_int64
+        _lib.hc_txt.argtypes = [C.c_char_p, C.c_int64, C.c_char_p]
+        _lib.hc_fixed.argtypes = [C.c_double, C.c_int, C.c_int, C.c_char_p]
+        _lib.hc_objfloat.argtypes = [C.c_double, C.c_char_p]
+        _lib.hc_sci.argtypes = [C.c_double, C.c_char_p]
+        _lib.hc_fixed_info.argtypes = [C.c_double] + [C.POINTER(C.c_int32)] * 3
+    return _lib
+
+
+def parse_cell(b: bytes, csv: bool = True) -> HcCell:
+    o = HcCell()
+    lib().hc_parse_cell(b, len(b), int(csv), C.byref(o))
+    return o
+
+
+def fixed(v: float, dec: int, space: bool = False) -> str:
+    buf = C.create_string_buffer(400)
+    n = lib().hc_fixed(v, dec, int(space), buf)
+    return buf.raw[:n].decode()
+
+
+def objfloat(v: float) -> str:
+    buf = C.create_string_buffer(400)
+    n = lib().hc_objfloat(v, buf)
+    assert n > 0, "objfloat_len mismatch"
+    return buf.raw[:n].decode()
+
+
+def sci(v: float) -> str:
+    buf = C.create_string_buffer(64)
+    n = lib().hc_sci(v, buf)
+    assert n > 0, "sci_len mismatch"
+    return buf.raw[:n].decode()
+
+
+def fixed_info(v: float):
+    a, b, c = C.c_int32(), C.c_int32(), C.c_int32()
+    lib().hc_fixed_info(v, C.byref(a), C.byref(b), C.byref(c))
+    return a.value, b.value, c.value
+
+
+def txt(b: bytes) -> bytes:
+    buf = C.create_string_buffer(len(b) + 16)
+    n = lib().hc_txt(b, len(b), buf)
+    return buf.raw[:n]

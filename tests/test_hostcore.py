@@ -1,0 +1,154 @@
+"""CPU checks of the device core functions (same headers the kernels compile) against CPython
+and pandas: float formatting is compared with Python's correctly rounded `format`, the numeric
+parsers with pd.read_csv itself, the text rules with the oracle."""
+import math
+import random
+import struct
+import warnings
+
+import numpy as np
+import pandas as pd
+import pytest
+
+from oracle import file_parser_oracle as O
+from tests import corpus
+from tests.hostcore import binding as H
+
+
+def _rand_doubles(n, seed):
+    r = random.Random(seed)
+    out = [0.0, -0.0, 1.0, -1.0, 0.5, 1e-6, 9.9999995e-7, 1e-7, 999999.9999995, 0.0000005, 1.5e-6,
+           2.5e-6, 0.1, 0.25, 1234567.891, 20.0, 25.75, 146.5, 1e15, 1e16, 2.0 ** 53, 2.0 ** 63,
+           2.0 ** 64, 1e22, 1e23, 1.7976931348623157e308, 5e-324, 2.2250738585072014e-308,
+           123456789012345678.0, 0.000001, 0.0000015, 99999999.999999, 1e6, 1000001.0,
+           9.9999995, 9.9999994999, 0.9999995, 0.99999949999, 8.5e-7, 1e21, 1e100, 1.2345675e10]
+    for _ in range(n):
+        x = r.random()
+        if x < 0.3:
+            out.append(r.randint(0, 10 ** 8) / 100)
+        elif x < 0.5:
+            out.append(r.uniform(-1, 1) * 10 ** r.randint(-12, 20))
+        elif x < 0.7:
+            out.append(struct.unpack("<d", struct.pack("<Q", r.getrandbits(64)))[0])
+        elif x < 0.85:
+            out.append(r.randint(1, 10 ** 7) / 10 ** r.randint(0, 7) + r.choice([0, 5e-7, 5e-8]))
+        else:
+            out.append(float(r.randint(-10 ** 6, 10 ** 6)) + r.choice([0.5, 0.25, 0.125, 0.0000005]))
+    return [v for v in out if not (math.isnan(v))]
+
+
+def test_fixed_matches_python_format():
+    for v in _rand_doubles(20000, 1):
+        if math.isinf(v):
+            continue
+        want = f"{v:.6f}"
+        assert H.fixed(v, 6) == want, (v, want)
+        tz, ipd, big = H.fixed_info(v)
+        frac = want.split(".")[1]
+        assert tz == len(frac) - len(frac.rstrip("0")), v
+        assert ipd == len(want.split(".")[0].lstrip("-")), v
+
+
+def test_objfloat_matches_pandas_rule():
+    for v in _rand_doubles(20000, 2) + [float("inf"), float("-inf")]:
+        s = f"{v: .6f}".rstrip("0")
+        if s.endswith("."):
+            s += "0"
+        assert H.objfloat(v) == s, v
+
+
+def test_sci_matches_python_format():
+    for v in _rand_doubles(20000, 3) + [float("inf"), float("-inf")]:
+        assert H.sci(v) == f"{v:.6e}", v
+
+
+def _tokens(seed, n):
+    r = random.Random(seed)
+    toks = []
+    for _ in range(n):
+        k = r.random()
+        if k < 0.25:
+            toks.append("%.2f" % (r.randint(0, 10 ** 7) / 100))
+        elif k < 0.4:
+            toks.append(repr(r.uniform(-1e6, 1e6)))
+        elif k < 0.55:
+            toks.append(("%." + str(r.randint(0, 25)) + "f") % (r.uniform(-1, 1) * 10 ** r.randint(-8, 18)))
+        elif k < 0.7:
+            toks.append("%de%d" % (r.randint(-10 ** 18, 10 ** 18), r.randint(-340, 320)))
+        elif k < 0.8:
+            toks.append(("%." + str(r.randint(0, 20)) + "e") % (r.uniform(-10, 10) * 10 ** r.randint(-320, 308)))
+        elif k < 0.9:
+            toks.append("".join(r.choice("0123456789") for _ in range(r.randint(1, 40))) + "." +
+                        "".join(r.choice("0123456789") for _ in range(r.randint(0, 40))))
+        else:
+            toks.append(r.choice([" ", "", "+", "-"]).strip() + str(r.randint(0, 10 ** 6)) + r.choice(["", ".", ".0", "e0", "E+2", " "]))
+    return toks
+
+
+def test_parse_double_matches_read_csv(tmp_path):
+    toks = [t for t in _tokens(5, 30000) if t.strip() not in ("", "+", "-")]
+    toks.append("0.5")  # make sure the column is float, not int
+    p = tmp_path / "f.csv"
+    p.write_text("a,b\n" + "".join(f"{t},x\n" for t in toks))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        col = pd.read_csv(p)["a"]
+    assert col.dtype == np.float64
+    vals = col.to_numpy()
+    for t, want in zip(toks, vals):
+        c = H.parse_cell(t.encode())
+        ours = c.fval if c.float_ok else (math.inf * c.inf_tok if c.inf_tok else None)
+        assert ours is not None, t
+        assert struct.pack("<d", ours) == struct.pack("<d", float(want)), (t, ours, want)
+
+
+@pytest.mark.parametrize("tok,kind", [
+    ("1e", "str"), ("1e+", "str"), (".", "str"), ("- 1", "str"), ("1 2", "str"), ("0x10", "str"),
+    ("1_000", "str"), ("NAN", "str"), (" inf", "str"), ("inf ", "str"), ("1e309", "float"),
+    ("-1e400", "float"), ("0e400", "float"), ("1.e5", "float"), ("+.5", "float"), ("5.", "float"),
+    ("\t1.5\t", "float"), ("infinity", "float"), ("-Infinity", "float"), ("+INF", "float"),
+    ("+5", "int"), ("007", "int"), ("-0", "int"), (" 8", "int"), ("9 ", "int"),
+    ("9223372036854775807", "int"), ("-9223372036854775808", "int"), ("1e-400", "float"),
+    ("00000000000000000000000000000001.5", "float"), ("1234567890123456789e-5", "float"),
+    ("infinit", "str"), ("in", "str"), ("+infinity", "float"), ("--1", "str"), ("1-", "str"),
+])
+def test_single_token_classification(tmp_path, tok, kind):
+    p = tmp_path / "t.csv"
+    p.write_text(f"a,b\n{tok},x\n")
+    col = pd.read_csv(p)["a"]
+    c = H.parse_cell(tok.encode())
+    if kind == "int":
+        assert col.dtype == np.int64 and c.int_status == 0 and c.ival == int(col[0])
+    elif kind == "float":
+        assert col.dtype == np.float64
+        ours = c.fval if c.float_ok else (math.inf * c.inf_tok if c.inf_tok else None)
+        assert ours is not None and struct.pack("<d", ours) == struct.pack("<d", float(col[0]))
+        assert c.int_status != 0
+    else:
+        assert col.dtype != np.float64 and col.dtype != np.int64
+        assert c.int_status != 0 and not c.float_ok and not c.inf_tok
+
+
+def test_na_tokens():
+    na = ["", "#N/A", "#N/A N/A", "#NA", "-1.#IND", "-1.#QNAN", "-NaN", "-nan", "1.#IND", "1.#QNAN",
+          "<NA>", "N/A", "NA", "NULL", "NaN", "None", "n/a", "nan", "null"]
+    for t in na:
+        assert H.parse_cell(t.encode()).is_na, t
+    for t in ["-", "na", "NAN", "Null", "N/a", " NA", "NA ", "#N/A N/", "#N/A N/A ", "none", "1.#INDx"]:
+        assert not H.parse_cell(t.encode()).is_na, t
+    assert H.parse_cell(b'""').is_na and H.parse_cell(b'"NA"').is_na
+
+
+def test_txt_core_matches_oracle():
+    for name, data in corpus.txt_golden_cases():
+        assert H.txt(data).decode("utf-8") == O.parse_txt_bytes(data), name
+    for seed in range(5000, 5400):
+        d = corpus.text_body(seed)
+        assert H.txt(d).decode("utf-8") == O.parse_txt_bytes(d), seed
+    r = random.Random(9)
+    alphabet = [b"a", b" ", b"\r", b"\n", b"\xc3", b"\xa9", b"\xe2", b"\x82", b"\xac", b"\xf0", b"\x9f",
+                b"\x98", b"\x80", b"\xff", b"\xc0", b"\xed", b"\xa0", b"\xe0", b"\xf4", b"\x90", b"\xc2",
+                b"\x85", b"\t", b"\xe3", b"\x81"]
+    for _ in range(3000):
+        d = b"".join(r.choice(alphabet) for _ in range(r.randint(0, 24)))
+        assert H.txt(d).decode("utf-8") == O.parse_txt_bytes(d), d
