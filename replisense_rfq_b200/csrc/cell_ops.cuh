@@ -1,0 +1,256 @@
+// The three per-cell operations of the table pipeline — classify, measure, print — as
+// host/device functions over a decoded-byte iterator factory, so the CSV kernels, the sheet-XML
+// kernels and the CPU test harness run the very same code.
+#pragma once
+#include "cell_format.cuh"
+#include "cell_parse.cuh"
+#include "col_decide.cuh"
+
+namespace rfq {
+
+// A cell source: where the token bytes live and how to decode them.
+struct CellSrc {
+  const uint8_t* p;
+  uint32_t n;
+  uint8_t mode;     // 0 = CSV field (quote rules), 1 = raw bytes
+  bool missing;     // short row: pandas pads with an empty token
+};
+
+#define RFQ_WITH_ITER(src, expr_csv, expr_raw) ((src).mode == 0 ? (expr_csv) : (expr_raw))
+
+RFQ_HD TextInfo cell_text(const CellSrc& s) {
+  if (s.missing) { TextInfo t; t.nbytes = t.ncp = t.nesc = 0; t.first8 = 0; t.utf8_ok = true; t.has_fchar = false; return t; }
+  return RFQ_WITH_ITER(s, scan_text(CsvIter(s.p, s.n)), scan_text(RawIter(s.p, s.n)));
+}
+RFQ_HD int cell_int64(const CellSrc& s, int64_t* v) {
+  return RFQ_WITH_ITER(s, parse_int64(CsvIter(s.p, s.n), v), parse_int64(RawIter(s.p, s.n), v));
+}
+RFQ_HD int cell_uint64(const CellSrc& s, UintTok* v) {
+  return RFQ_WITH_ITER(s, parse_uint64(CsvIter(s.p, s.n), v), parse_uint64(RawIter(s.p, s.n), v));
+}
+RFQ_HD bool cell_double(const CellSrc& s, double* v) {
+  if (RFQ_WITH_ITER(s, parse_double(CsvIter(s.p, s.n), v), parse_double(RawIter(s.p, s.n), v))) return true;
+  int k = RFQ_WITH_ITER(s, inf_token(CsvIter(s.p, s.n)), inf_token(RawIter(s.p, s.n)));
+  if (k == 0) return false;
+#ifdef __CUDA_ARCH__
+  *v = k > 0 ? __longlong_as_double(0x7FF0000000000000LL) : __longlong_as_double(0xFFF0000000000000LL);
+#else
+  *v = k > 0 ? __builtin_huge_val() : -__builtin_huge_val();
+#endif
+  return true;
+}
+
+// ---- 1. classify: SF_* flags of this cell + int64 status -----------------------------------
+RFQ_HD uint32_t classify_cell(const CellSrc& s, int* int_status) {
+  TextInfo t = cell_text(s);
+  *int_status = INT_OK;
+  if (is_na_token(t.nbytes, t.first8)) return SF_ANY_NA;
+  uint32_t f = SF_ANY_NONNA;
+  if (!t.utf8_ok) f |= SF_BAD_UTF8;
+  int64_t iv;
+  int st = cell_int64(s, &iv);
+  *int_status = st;
+  if (st == INT_OK) {
+    // still needed for the uint64 pass of a column that overflows elsewhere
+    if (iv < 0) f |= SF_NEG;
+    else if (iv == 0) {  // "-0" is negative for str_to_uint64
+      UintTok u; cell_uint64(s, &u);
+      if (u.neg) f |= SF_NEG;
+    }
+    f |= SF_BOOL_BAD;
+    return f;
+  }
+  UintTok u;
+  int us = cell_uint64(s, &u);
+  if (us == INT_INVALID) f |= SF_UINT_INVALID;
+  else if (us == INT_OVERFLOW) f |= SF_UINT_OVF;
+  else { if (u.neg) f |= SF_NEG; if (u.gt_i64) f |= SF_GT_I64; }
+  double dv;
+  if (!cell_double(s, &dv)) f |= SF_FLOAT_BAD;
+  if (bool_token(t.nbytes, t.first8) < 0) f |= SF_BOOL_BAD;
+  return f;
+}
+
+// ---- value of a numeric cell under its chunk type ---------------------------------------------
+RFQ_HD double cell_as_double(const CellSrc& s, int ctype) {
+  double v = 0.;
+  if (ctype == CT_INT || ctype == CT_INTNA) {
+    int64_t iv = 0; cell_int64(s, &iv);
+#ifdef __CUDA_ARCH__
+    v = __ll2double_rn(iv);
+#else
+    v = (double)iv;
+#endif
+  } else {
+    cell_double(s, &v);
+  }
+  return v;
+}
+
+RFQ_HD int sci_len_of(double v) {
+  // len of "%.6e": exact exponent digit count needs sci7 only next to the 1e100 / 1e-99 borders
+  if (dbl_is_inf(v)) return v < 0 ? 4 : 3;
+  bool neg = (dbl_bits(v) >> 63) != 0;
+  double a = v < 0 ? -v : v;
+  if (a == 0.) return neg + 12;
+  if (a >= 1e-98 && a < 9e99) return neg + 12;
+  if (a >= 1.1e100 || a < 9e-100) return neg + 13;
+  return sci_len(sci7(v));
+}
+
+// ---- 2. measure ---------------------------------------------------------------------------------
+struct CellMeasure {
+  bool is_nan;          // prints '' after fillna
+  uint32_t plain_len, ip_len, tz, inf_len, obj_len, sci_len, fl;
+  uint32_t extra_bytes; // printed bytes - printed code points (non-ASCII strings only)
+};
+
+RFQ_HD CellMeasure measure_cell(const CellSrc& s, int ctype) {
+  CellMeasure m;
+  m.is_nan = false; m.plain_len = 0; m.ip_len = 0; m.tz = 6; m.inf_len = 0; m.obj_len = 0;
+  m.sci_len = 0; m.fl = 0; m.extra_bytes = 0;
+  TextInfo t = cell_text(s);
+  bool na = is_na_token(t.nbytes, t.first8);
+  if (na && ctype != CT_STRNF) { m.is_nan = true; return m; }
+  if (ctype == CT_STR || ctype == CT_STRNF) {
+    m.plain_len = t.ncp + t.nesc;
+    m.extra_bytes = t.nbytes - t.ncp;
+    return m;
+  }
+  if (ctype == CT_BOOL || ctype == CT_BOOLNA) {
+    m.plain_len = bool_token(t.nbytes, t.first8) == 1 ? 4 : 5;
+    return m;
+  }
+  if (ctype == CT_UINT) {
+    UintTok u; cell_uint64(s, &u);
+    m.plain_len = (uint32_t)ndigits_u64(u.v);
+    return m;
+  }
+  if (ctype == CT_INT || ctype == CT_INTNA) {
+    int64_t iv = 0; cell_int64(s, &iv);
+    m.plain_len = (uint32_t)int64_len(iv);
+  }
+  double v = cell_as_double(s, ctype);
+  Fixed6 f = fixed6(v);
+  double a = v < 0 ? -v : v;
+  if (f.inf) {
+    m.inf_len = 3 + f.neg; m.obj_len = 4; m.sci_len = m.inf_len; m.fl = MF_LARGE;
+  } else {
+    m.ip_len = f.neg + f.ip_digits; m.tz = f.tz; m.obj_len = objfloat_len(f);
+    m.fl = MF_FINITE | (a > 1e6 ? MF_LARGE : 0) | ((a < 1e-6 && a > 0.) ? MF_SMALL : 0);
+    m.sci_len = (uint32_t)sci_len_of(v);
+  }
+  return m;
+}
+
+// ---- 3. print -----------------------------------------------------------------------------------
+// How a cell prints given the class of its column and the type of its chunk.
+enum { PR_EMPTY = 0, PR_INT, PR_UINT, PR_FIXED, PR_SCI, PR_OBJFLOAT, PR_BOOL, PR_STR };
+
+RFQ_HD int print_kind(int cls, int ctype, bool sci) {
+  switch (cls) {
+    case CC_INT: return PR_INT;
+    case CC_UINT: return PR_UINT;
+    case CC_FLOAT: return sci ? PR_SCI : PR_FIXED;
+    case CC_BOOL: return PR_BOOL;
+    case CC_STR: return PR_STR;
+    case CC_OBJF: return PR_OBJFLOAT;
+    default:
+      switch (ctype) {
+        case CT_INT: return PR_INT;
+        case CT_UINT: return PR_UINT;
+        case CT_INTNA: case CT_FLOAT: return PR_OBJFLOAT;
+        case CT_BOOL: case CT_BOOLNA: return PR_BOOL;
+        default: return PR_STR;
+      }
+  }
+}
+
+// Printed length in code points and bytes (for right-justification), without writing.
+RFQ_HD void printed_size(const CellSrc& s, int ctype, int kind, int dec, uint32_t* ncp,
+                         uint32_t* nbytes) {
+  *ncp = 0; *nbytes = 0;
+  TextInfo t = cell_text(s);
+  if (ctype != CT_STRNF && is_na_token(t.nbytes, t.first8)) return;
+  uint32_t n = 0;
+  switch (kind) {
+    case PR_STR: *ncp = t.ncp + t.nesc; *nbytes = t.nbytes + t.nesc; return;
+    case PR_BOOL: n = bool_token(t.nbytes, t.first8) == 1 ? 4 : 5; break;
+    case PR_INT: { int64_t iv = 0; cell_int64(s, &iv); n = (uint32_t)int64_len(iv); break; }
+    case PR_UINT: { UintTok u; cell_uint64(s, &u); n = (uint32_t)ndigits_u64(u.v); break; }
+    case PR_FIXED: { Fixed6 f = fixed6(cell_as_double(s, ctype)); n = (uint32_t)fixed_len(f, dec); break; }
+    case PR_OBJFLOAT: { Fixed6 f = fixed6(cell_as_double(s, ctype)); n = (uint32_t)objfloat_len(f); break; }
+    case PR_SCI: n = (uint32_t)sci_len_of(cell_as_double(s, ctype)); break;
+    default: break;
+  }
+  *ncp = n; *nbytes = n;
+}
+
+// Write the printed form at `out` (exactly the bytes printed_size reported). Returns bytes.
+RFQ_HD uint32_t print_cell(const CellSrc& s, int ctype, int kind, int dec, uint8_t* out) {
+  if (kind == PR_STR) {
+    TextInfo t = cell_text(s);
+    if (ctype != CT_STRNF && is_na_token(t.nbytes, t.first8)) return 0;
+    uint32_t k = 0;
+    int c;
+    if (s.mode == 0) {
+      CsvIter it(s.p, s.n);
+      while ((c = it.next()) >= 0) {
+        if (c == '\t') { out[k++] = '\\'; out[k++] = 't'; }
+        else if (c == '\n') { out[k++] = '\\'; out[k++] = 'n'; }
+        else if (c == '\r') { out[k++] = '\\'; out[k++] = 'r'; }
+        else out[k++] = (uint8_t)c;
+      }
+    } else {
+      RawIter it(s.p, s.n);
+      while ((c = it.next()) >= 0) {
+        if (c == '\t') { out[k++] = '\\'; out[k++] = 't'; }
+        else if (c == '\n') { out[k++] = '\\'; out[k++] = 'n'; }
+        else if (c == '\r') { out[k++] = '\\'; out[k++] = 'r'; }
+        else out[k++] = (uint8_t)c;
+      }
+    }
+    return k;
+  }
+  TextInfo t = cell_text(s);
+  if (is_na_token(t.nbytes, t.first8)) return 0;
+  switch (kind) {
+    case PR_BOOL: {
+      const char* w = bool_token(t.nbytes, t.first8) == 1 ? "True" : "False";
+      uint32_t k = 0;
+      while (w[k]) { out[k] = (uint8_t)w[k]; ++k; }
+      return k;
+    }
+    case PR_INT: {
+      int64_t iv = 0; cell_int64(s, &iv);
+      uint32_t n = (uint32_t)int64_len(iv);
+      uint64_t mag = iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv;
+      write_u64_rev(mag, out + n);
+      if (iv < 0) out[0] = '-';
+      return n;
+    }
+    case PR_UINT: {
+      UintTok u; cell_uint64(s, &u);
+      uint32_t n = (uint32_t)ndigits_u64(u.v);
+      write_u64_rev(u.v, out + n);
+      return n;
+    }
+    case PR_FIXED: {
+      double v = cell_as_double(s, ctype);
+      Fixed6 f = fixed6(v);
+      return (uint32_t)fixed_write(f, v, dec, false, out);
+    }
+    case PR_OBJFLOAT: {
+      double v = cell_as_double(s, ctype);
+      Fixed6 f = fixed6(v);
+      return (uint32_t)fixed_write(f, v, objfloat_dec(f), true, out);
+    }
+    case PR_SCI: {
+      double v = cell_as_double(s, ctype);
+      return (uint32_t)sci_write(sci7(v), out);
+    }
+    default: return 0;
+  }
+}
+
+}  // namespace rfq

@@ -1,0 +1,105 @@
+// Host-side (C++) handling of the header record of a CSV document: tokenise the first record,
+// unescape, name blank columns, de-duplicate — what pandas' TextReader._get_header does
+// (pandas/_libs/parsers.pyx; reached from app/file_parser.py:301) — and render the
+// "Empty DataFrame" text of pandas/io/formats/string.py:56-62.  O(columns) per document; the
+// data rows never pass through here.
+#pragma once
+#include <stdint.h>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "cell_parse.cuh"
+#include "csv_dfa.cuh"
+
+namespace rfq {
+
+struct HeaderInfo {
+  bool found = false;                 // a header record exists
+  bool utf8_ok = true;
+  std::vector<std::string> names;     // final (mangled) column names
+  std::vector<uint32_t> ncp;          // code points of each name
+};
+
+inline bool utf8_valid_count(const std::string& s, uint32_t* ncp) {
+  TextInfo t = scan_text(RawIter((const uint8_t*)s.data(), (uint32_t)s.size()));
+  *ncp = t.ncp;
+  return t.utf8_ok;
+}
+
+// Tokenise the first record of `doc` with the same DFA the kernels run.
+inline HeaderInfo parse_header(const uint8_t* doc, uint64_t len, uint32_t sep) {
+  HeaderInfo h;
+  uint64_t i = 0;
+  if (len >= 3 && doc[0] == 0xEF && doc[1] == 0xBB && doc[2] == 0xBF) i = 3;
+  int st = ST_R;
+  std::vector<std::pair<uint64_t, uint64_t>> spans;
+  uint64_t fstart = 0, ws_start = 0;
+  bool open = false, done = false;
+  for (; i <= len && !done; ++i) {
+    int cl = (i == len) ? CL_LF : csv_class(doc[i], sep);
+    int ev = csv_events(st, cl);
+    if (st != ST_W && csv_next(st, cl) == ST_W) ws_start = i;
+    if (ev & EV_REC_START) { open = true; fstart = i; }
+    if (ev & EV_REC_START_WS) { open = true; fstart = ws_start; }
+    if (ev & EV_FIELD_END) { spans.push_back({fstart, i}); fstart = i + 1; }
+    if (ev & EV_LINE_END) done = true;
+    st = csv_next(st, cl);
+  }
+  if (!done || !open) return h;
+  h.found = true;
+  std::vector<std::string> raw;
+  std::vector<size_t> unnamed;
+  for (size_t k = 0; k < spans.size(); ++k) {
+    CsvIter it(doc + spans[k].first, (uint32_t)(spans[k].second - spans[k].first));
+    std::string s;
+    int c;
+    while ((c = it.next()) >= 0) s.push_back((char)c);
+    if (s.empty()) { s = "Unnamed: " + std::to_string(k); unnamed.push_back(k); }
+    raw.push_back(s);
+  }
+  // de-duplicate: named columns first, then the unnamed ones
+  std::vector<size_t> order;
+  {
+    std::vector<bool> is_un(raw.size(), false);
+    for (size_t k : unnamed) is_un[k] = true;
+    for (size_t k = 0; k < raw.size(); ++k) if (!is_un[k]) order.push_back(k);
+    for (size_t k : unnamed) order.push_back(k);
+  }
+  std::unordered_map<std::string, int> counts;
+  auto in_header = [&](const std::string& s) {
+    for (auto& x : raw) if (x == s) return true;
+    return false;
+  };
+  for (size_t i2 : order) {
+    std::string col = raw[i2], old_col = col;
+    int cur = 0;
+    auto f = counts.find(col);
+    if (f != counts.end()) cur = f->second;
+    while (cur > 0) {
+      counts[old_col] = cur + 1;
+      col = old_col + "." + std::to_string(cur);
+      if (in_header(col)) cur += 1;
+      else { auto g = counts.find(col); cur = g == counts.end() ? 0 : g->second; }
+    }
+    raw[i2] = col;
+    counts[col] = cur + 1;
+  }
+  h.names = raw;
+  h.ncp.resize(raw.size());
+  for (size_t k = 0; k < raw.size(); ++k)
+    if (!utf8_valid_count(raw[k], &h.ncp[k])) h.utf8_ok = false;
+  return h;
+}
+
+// "Empty DataFrame\nColumns: [a, b]\nIndex: []" (display.max_seq_items = 100)
+inline std::string empty_frame_text(const std::vector<std::string>& names) {
+  std::string s = "Empty DataFrame\nColumns: [";
+  size_t n = names.size(), lim = n < 100 ? n : 100;
+  for (size_t k = 0; k < lim; ++k) { if (k) s += ", "; s += names[k]; }
+  if (n > lim) s += ", ...";
+  s += "]\nIndex: []";
+  return s;
+}
+
+}  // namespace rfq

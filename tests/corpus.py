@@ -115,6 +115,13 @@ def fuzz_csv(seed: int, max_rows: int = 40) -> bytes:
         lines.append(sep.join(row))
         if r.random() < 0.03:
             lines.append(r.choice(["", " ", "  \t" if sep != "\t" else "  "]))
+    if nl == "\r":
+        # pandas' tokenizer mis-handles a record that starts with a non-delimiter blank after a
+        # bare-CR terminator (its whitespace-line backtrack runs to the previous '\n' or to the
+        # start of the current tokenize call, re-reading earlier rows; outcome depends on
+        # internal buffer positions).  Documented divergence: not generated.
+        blanks = " " if sep == "\t" else " \t"
+        lines = [ln.lstrip(blanks) if ln.strip(blanks) else ln for ln in lines]
     body = nl.join(lines)
     if r.random() < 0.8:
         body += nl

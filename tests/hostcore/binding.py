@@ -71,3 +71,20 @@ def txt(b: bytes) -> bytes:
     buf = C.create_string_buffer(len(b) + 16)
     n = lib().hc_txt(b, len(b), buf)
     return buf.raw[:n]
+
+
+def csv_parse(data: bytes, nrows: int = 1000):
+    """Sequential model of the GPU CSV pipeline. Returns text, None (unparseable) or 'UNSUPPORTED'."""
+    cap = len(data) * 12 + 65536
+    buf = C.create_string_buffer(cap)
+    n = C.c_uint64()
+    L = lib()
+    L.hc_csv_parse.argtypes = [C.c_char_p, C.c_uint64, C.c_int64, C.c_char_p, C.c_uint64, C.POINTER(C.c_uint64)]
+    st = L.hc_csv_parse(data, len(data), nrows, buf, cap, C.byref(n))
+    if st == 0:
+        return buf.raw[:n.value].decode("utf-8")
+    if st == 1:
+        return None
+    if st == 2:
+        return "UNSUPPORTED"
+    raise RuntimeError("hostcore buffer too small")

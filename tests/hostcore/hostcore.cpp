@@ -85,3 +85,192 @@ int64_t hc_txt(const uint8_t* p, int64_t len, uint8_t* out) {
 }
 
 }  // extern "C"
+
+// ================================================================================================
+// Sequential model of the whole CSV table pipeline built from the SAME host/device functions the
+// kernels call (DFA, classify/measure/print, column decisions, header naming).  It exists so the
+// semantics can be fuzzed against pandas on the CPU; the kernels add only the parallel plumbing.
+#include <string>
+#include <vector>
+#include "../../replisense_rfq_b200/csrc/cell_ops.cuh"
+#include "../../replisense_rfq_b200/csrc/header_names.h"
+
+namespace {
+
+struct Rec { uint64_t start; uint32_t f0, f1; };
+
+// status: 0 ok, 1 attempt fails (exception or <= 1 column), 2 unsupported on the GPU path
+int csv_attempt(const uint8_t* doc, uint64_t len, uint32_t sep, int64_t nrows, std::string& out) {
+  std::vector<uint64_t> fend;
+  std::vector<Rec> recs;
+  uint64_t i = 0;
+  if (len >= 3 && doc[0] == 0xEF && doc[1] == 0xBB && doc[2] == 0xBF) i = 3;
+  int st = ST_R;
+  uint64_t ws_start = 0, cur_start = 0;
+  uint32_t cur_f0 = 0;
+  bool stopped = false;
+  for (; i <= len; ++i) {
+    int cl = (i == len) ? CL_LF : csv_class(doc[i], sep);
+    int ev = csv_events(st, cl);
+    int ns = csv_next(st, cl);
+    if (st != ST_W && ns == ST_W) ws_start = i;
+    if (ev & EV_REC_START) { cur_start = i; cur_f0 = (uint32_t)fend.size(); }
+    if (ev & EV_REC_START_WS) { cur_start = ws_start; cur_f0 = (uint32_t)fend.size(); }
+    if (ev & EV_FIELD_END) fend.push_back(i);
+    if (ev & EV_LINE_END) {
+      recs.push_back({cur_start, cur_f0, (uint32_t)fend.size()});
+      if ((int64_t)recs.size() == nrows + 1) { stopped = true; st = ns; break; }
+    }
+    st = ns;
+  }
+  if (!stopped && st == ST_Q) return 1;  // EOF inside string
+  if (recs.empty()) return 1;            // EmptyDataError
+  HeaderInfo hdr = parse_header(doc, len, sep);
+  if (!hdr.found || !hdr.utf8_ok) return 1;
+  uint32_t h = (uint32_t)hdr.names.size();
+  uint32_t W = h;
+  if (recs.size() >= 2) { uint32_t f1 = recs[1].f1 - recs[1].f0; if (f1 > W) W = f1; }
+  for (size_t r = 2; r < recs.size(); ++r)
+    if (recs[r].f1 - recs[r].f0 > W) return 1;  // "Expected N fields, saw M"
+  if (h <= 1) return 1;
+  uint32_t lead = W - h;
+  uint32_t ndata = (uint32_t)recs.size() - 1;
+  uint32_t bl = chunk_rows_for_width(W);
+  uint32_t nch = (ndata + bl - 1) / bl;
+  auto cell = [&](uint32_t row, uint32_t c) {
+    const Rec& R = recs[row + 1];
+    CellSrc s; s.mode = 0; s.missing = false; s.p = doc; s.n = 0;
+    uint32_t nf = R.f1 - R.f0;
+    if (c >= nf) { s.missing = true; return s; }
+    uint64_t a = c == 0 ? R.start : fend[R.f0 + c - 1] + 1;
+    uint64_t b = fend[R.f0 + c];
+    s.p = doc + a; s.n = (uint32_t)(b - a);
+    return s;
+  };
+  std::vector<ChunkStat> stat((size_t)nch * W, ChunkStat{0, RFQ_NO_ROW, RFQ_NO_ROW, 0});
+  std::vector<uint32_t> row_na(ndata, 0);
+  for (uint32_t r = 0; r < ndata; ++r)
+    for (uint32_t c = 0; c < W; ++c) {
+      int is;
+      uint32_t f = classify_cell(cell(r, c), &is);
+      ChunkStat& S = stat[(size_t)(r / bl) * W + c];
+      S.flags |= f;
+      if (is != INT_OK) {
+        if (r < S.int_bad_min) S.int_bad_min = r;
+        if (is == INT_OVERFLOW && r < S.int_ovf_min) S.int_ovf_min = r;
+      }
+      if ((f & SF_ANY_NA) && c >= lead) row_na[r]++;
+    }
+  std::vector<uint8_t> ctype((size_t)nch * W);
+  std::vector<bool> chunk_has_nf(nch, false);
+  for (size_t k = 0; k < stat.size(); ++k) {
+    if (stat[k].flags & SF_BAD_UTF8) return 1;  // UnicodeDecodeError
+    ctype[k] = (uint8_t)decide_chunk_type(stat[k]);
+    if (ctype[k] == CT_STRNF && (k % W) >= lead) chunk_has_nf[k / W] = true;
+  }
+  std::vector<bool> keep(ndata);
+  uint32_t nkeep = 0;
+  for (uint32_t r = 0; r < ndata; ++r) {
+    keep[r] = !(row_na[r] == h && !chunk_has_nf[r / bl]);
+    nkeep += keep[r];
+  }
+  std::vector<ChunkMeasure> meas((size_t)nch * W, ChunkMeasure{0, 0, 6, 0, 0, 0, 0, 0});
+  for (uint32_t r = 0; r < ndata; ++r) {
+    if (!keep[r]) continue;
+    for (uint32_t c = lead; c < W; ++c) {
+      size_t k = (size_t)(r / bl) * W + c;
+      CellMeasure m = measure_cell(cell(r, c), ctype[k]);
+      ChunkMeasure& M = meas[k];
+      if (m.is_nan) { M.nan_left = 1; continue; }
+      if (m.plain_len > M.plain_len) M.plain_len = m.plain_len;
+      if (m.ip_len > M.ip_len) M.ip_len = m.ip_len;
+      if (m.tz < M.min_tz) M.min_tz = m.tz;
+      if (m.inf_len > M.inf_len) M.inf_len = m.inf_len;
+      if (m.obj_len > M.obj_len) M.obj_len = m.obj_len;
+      if (m.sci_len > M.sci_len) M.sci_len = m.sci_len;
+      M.fl |= m.fl;
+    }
+  }
+  const char* encs = "utf-8";
+  out = std::string("=== CSV Data (using ") + encs + ", separator '" + (char)sep + "') ===\n";
+  if (nkeep == 0) { out += empty_frame_text(hdr.names); return 0; }
+  std::vector<ColumnLayout> lay(h);
+  for (uint32_t j = 0; j < h; ++j) {
+    uint32_t c = lead + j;
+    bool nan_left = false;
+    for (uint32_t k = 0; k < nch; ++k) nan_left |= meas[(size_t)k * W + c].nan_left != 0;
+    int cls = fold_column_class(&ctype[c], nch, W, nan_left);
+    if (cls == CC_UNSUP) return 2;
+    lay[j] = layout_column(cls, &meas[c], &ctype[c], nch, W, hdr.ncp[j]);
+  }
+  // header line
+  for (uint32_t j = 0; j < h; ++j) {
+    bool numeric = lay[j].cls == CC_INT || lay[j].cls == CC_UINT || lay[j].cls == CC_FLOAT || lay[j].cls == CC_BOOL;
+    uint32_t cp = hdr.ncp[j] + (numeric ? 1 : 0);
+    if (j) out += ' ';
+    out.append(lay[j].width - cp, ' ');
+    if (numeric) out += ' ';
+    out += hdr.names[j];
+  }
+  std::vector<uint8_t> buf;
+  for (uint32_t r = 0; r < ndata; ++r) {
+    if (!keep[r]) continue;
+    out += '\n';
+    for (uint32_t j = 0; j < h; ++j) {
+      uint32_t c = lead + j;
+      int ct = ctype[(size_t)(r / bl) * W + c];
+      int kind = print_kind(lay[j].cls, ct, lay[j].sci);
+      CellSrc s = cell(r, c);
+      uint32_t ncp, nb;
+      printed_size(s, ct, kind, lay[j].dec, &ncp, &nb);
+      if (j) out += ' ';
+      out.append(lay[j].width - ncp, ' ');
+      buf.resize(nb + 400);
+      uint32_t wrote = print_cell(s, ct, kind, lay[j].dec, buf.data());
+      if (wrote != nb) { out += "<<SIZE MISMATCH>>"; }
+      out.append((const char*)buf.data(), wrote);
+    }
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+// Full reference trial loop restricted to what can differ structurally: utf-8 then latin-1, each
+// with ',', ';', TAB (cp1252 can never win where latin-1 failed: same bytes, same structure).
+// returns status (0 ok / 1 unparseable / 2 unsupported); *out_len bytes written to out (cap).
+int hc_csv_parse(const uint8_t* doc, uint64_t len, int64_t nrows, uint8_t* out, uint64_t cap,
+                 uint64_t* out_len) {
+  static const uint32_t seps[3] = {',', ';', '\t'};
+  std::string text;
+  *out_len = 0;
+  for (int enc = 0; enc < 2; ++enc) {
+    std::vector<uint8_t> tr;
+    const uint8_t* d = doc; uint64_t n = len;
+    if (enc == 1) {  // latin-1 -> UTF-8 transcode of the stream
+      tr.reserve(len * 2);
+      for (uint64_t i = 0; i < len; ++i) {
+        uint8_t b = doc[i];
+        if (b < 0x80) tr.push_back(b);
+        else { tr.push_back((uint8_t)(0xC0 | (b >> 6))); tr.push_back((uint8_t)(0x80 | (b & 0x3F))); }
+      }
+      d = tr.data(); n = tr.size();
+    }
+    for (int k = 0; k < 3; ++k) {
+      int st = csv_attempt(d, n, seps[k], nrows, text);
+      if (st == 2) return 2;
+      if (st == 0) {
+        if (enc == 1) text.replace(text.find("utf-8"), 5, "latin-1");
+        if (text.size() > cap) return -1;
+        memcpy(out, text.data(), text.size());
+        *out_len = text.size();
+        return 0;
+      }
+    }
+  }
+  return 1;
+}
+
+}  // extern "C"

@@ -152,3 +152,34 @@ def test_txt_core_matches_oracle():
     for _ in range(3000):
         d = b"".join(r.choice(alphabet) for _ in range(r.randint(0, 24)))
         assert H.txt(d).decode("utf-8") == O.parse_txt_bytes(d), d
+
+
+def test_csv_model_matches_reference_goldens():
+    """The sequential model (same DFA / cell / column functions as the kernels) against the
+    committed outputs of the reference's own _parse_csv_sync."""
+    import base64
+    import json
+    from pathlib import Path
+    cases = json.loads((Path(__file__).parent / "golden" / "ref_csv.json").read_text())
+    bad = []
+    for c in cases:
+        got = H.csv_parse(base64.b64decode(c["data"]), c["nrows"])
+        if got == "UNSUPPORTED":
+            assert c["name"] == "too_big"  # Python-int object column: reported, not guessed
+            continue
+        if got != c.get("text"):
+            bad.append(c["name"])
+    assert not bad, bad
+
+
+def test_csv_model_fuzz_vs_pandas():
+    bad = []
+    for seed in range(20000, 20400):
+        data = corpus.fuzz_csv(seed)
+        try:
+            want = O.parse_csv_bytes(data, 1000)
+        except O.OracleParsingError:
+            want = None
+        if H.csv_parse(data, 1000) != want:
+            bad.append(seed)
+    assert not bad, bad
