@@ -1,0 +1,350 @@
+// rfq_csv_run: host orchestration of the reference's (encoding x separator) trial loop
+// (app/file_parser.py:298-308) over a staged batch.  Per attempt the host only does
+// O(documents + columns) bookkeeping (header names, table shapes, buffer carving); every pass
+// over document bytes or cells is a kernel.
+#include <cuda_runtime.h>
+#include <string.h>
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "../../include/rfq_parse.h"
+#include "col_decide.cuh"
+#include "csv_dfa.cuh"
+#include "ctx.h"
+#include "header_names.h"
+
+using namespace rfq;
+
+namespace {
+
+const uint32_t kSeps[3] = {',', ';', '\t'};
+const char* kEncNames[3] = {"utf-8", "latin-1", "cp1252"};
+
+// bump writer into a pinned upload buffer; returns offsets so device pointers can be derived
+struct Uploader {
+  uint8_t* h; size_t used = 0;
+  explicit Uploader(uint8_t* p) : h(p) {}
+  template <class T> size_t put(const T* src, size_t n) {
+    used = (used + 255) & ~(size_t)255;
+    size_t o = used;
+    if (n) memcpy(h + o, src, n * sizeof(T));
+    used += n * sizeof(T);
+    return o;
+  }
+};
+
+struct AttemptDoc {
+  uint32_t doc;            // index in the staged batch
+  HeaderInfo hdr;
+  bool active = false;
+  int fail = 0;            // 1 = attempt fails, 2 = unsupported
+};
+
+uint32_t pow2_floor(uint32_t x) { uint32_t p = 1; while ((uint64_t)p * 2 <= x) p *= 2; return p; }
+
+}  // namespace
+
+// One (encoding, separator) attempt over `sel` (indices into the staged batch).
+// arena/off/len describe the documents for THIS encoding. Marks successes in ctx->r_*.
+static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8_t* d_arena,
+                       const std::vector<uint32_t>& off, const std::vector<uint32_t>& len,
+                       int enc, int sep_i, const std::vector<int64_t>& max_rows,
+                       std::vector<uint8_t>& resolved) {
+  cudaStream_t s = c->stream;
+  const uint32_t m = (uint32_t)sel.size();
+  const uint32_t sep = kSeps[sep_i];
+  // ---- 1. document tables for the tokenizer
+  std::vector<uint32_t> a_off(m), a_len(m), a_tb(m + 1), a_mr(m);
+  uint64_t tiles = 0;
+  for (uint32_t i = 0; i < m; ++i) {
+    a_off[i] = off[sel[i]]; a_len[i] = len[sel[i]];
+    a_tb[i] = (uint32_t)tiles;
+    tiles += ((uint64_t)a_len[i] + 1 + RFQ_TILE - 1) / RFQ_TILE;
+    int64_t mr = max_rows[sel[i]];
+    a_mr[i] = (uint32_t)std::min<int64_t>(std::max<int64_t>(mr, 0), 0x7FFFFFF0);
+  }
+  a_tb[m] = (uint32_t)tiles;
+  const uint32_t nt = (uint32_t)tiles;
+  RFQ_CK(c, c->h_up.reserve(16ull * (m + 2) + 4096));
+  Uploader up((uint8_t*)c->h_up.p);
+  size_t o_off = up.put(a_off.data(), m), o_len = up.put(a_len.data(), m);
+  size_t o_tb = up.put(a_tb.data(), m + 1), o_mr = up.put(a_mr.data(), m);
+  uint8_t* d_up = c->pool.alloc<uint8_t>(up.used + 256);
+  ScanArgs sa{};
+  sa.arena = d_arena;
+  sa.n_docs = m; sa.n_tiles = nt; sa.sep = sep;
+  sa.tile_fn = c->pool.alloc<uint32_t>(nt + 1);
+  sa.tile_fn_pre = c->pool.alloc<uint32_t>(nt + 1);
+  sa.lane_state = c->pool.alloc<uint32_t>(3ull * nt + 1);
+  sa.tile_nf = c->pool.alloc<uint32_t>(nt + 1);
+  sa.tile_nl = c->pool.alloc<uint32_t>(nt + 1);
+  sa.tile_nf_pre = c->pool.alloc<uint32_t>(nt + 1);
+  sa.tile_nl_pre = c->pool.alloc<uint32_t>(nt + 1);
+  sa.doc_final = c->pool.alloc<uint32_t>(m + 1);
+  sa.scan_tmp = c->pool.alloc<uint32_t>(scan_partials_needed(nt + 1));
+  DocShape* d_shape = c->pool.alloc<DocShape>(m + 1);
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  RFQ_CK(c, cudaMemcpyAsync(d_up, c->h_up.p, up.used, cudaMemcpyHostToDevice, s));
+  sa.doc_off = (const uint32_t*)(d_up + o_off);
+  sa.doc_len = (const uint32_t*)(d_up + o_len);
+  sa.tile_base = (const uint32_t*)(d_up + o_tb);
+  const uint32_t* d_mr = (const uint32_t*)(d_up + o_mr);
+  RFQ_CK(c, cudaMemsetAsync(sa.doc_final, 0, 4ull * (m + 1), s));
+  c->prof.mark("csv_scan_count", s);
+  csv_scan_count(sa, s);
+  RFQ_CK(c, c->h_down.reserve(sizeof(DocShape) * (m + 1) + 32ull * (m + 1) + 4096));
+  uint32_t* h_tot = (uint32_t*)c->h_down.p;
+  RFQ_CK(c, cudaMemcpyAsync(h_tot, sa.tile_nf_pre + nt, 4, cudaMemcpyDeviceToHost, s));
+  RFQ_CK(c, cudaMemcpyAsync(h_tot + 1, sa.tile_nl_pre + nt, 4, cudaMemcpyDeviceToHost, s));
+  // ---- header names on the host while the scan runs (first record only)
+  std::vector<AttemptDoc> ad(m);
+  for (uint32_t i = 0; i < m; ++i) {
+    ad[i].doc = sel[i];
+    ad[i].hdr = parse_header(c->h_arena + c->h_doc_off[sel[i]], c->h_doc_len[sel[i]], sep, enc == 1);
+  }
+  RFQ_CK(c, cudaStreamSynchronize(s));
+  const uint32_t NF = h_tot[0], NL = h_tot[1];
+  const uint32_t n_slots = NL + m;
+  // ---- 2. index pass + record shapes
+  sa.fend = c->pool.alloc<uint32_t>((size_t)NF + 1);
+  sa.rec_fend = c->pool.alloc<uint32_t>((size_t)n_slots + 1);
+  sa.rec_start = c->pool.alloc<uint32_t>((size_t)n_slots + 1);
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  c->prof.mark("csv_scan_index", s);
+  csv_scan_index(sa, s);
+  csv_doc_shape(sa, d_mr, d_shape, n_slots, s);
+  DocShape* h_shape = (DocShape*)((uint8_t*)c->h_down.p + 256);
+  RFQ_CK(c, cudaMemcpyAsync(h_shape, d_shape, sizeof(DocShape) * m, cudaMemcpyDeviceToHost, s));
+  RFQ_CK(c, cudaStreamSynchronize(s));
+  // ---- 3. validate shapes, carve the table arrays
+  std::vector<TDoc> td(m);
+  std::vector<uint32_t> item_base(m + 1), slot_r0(m + 1);
+  std::vector<uint32_t> name_off, name_len, name_cp;
+  std::string names;
+  uint64_t n_stat = 0, n_cols = 0, n_items = 0;
+  for (uint32_t i = 0; i < m; ++i) {
+    const DocShape& sh = h_shape[i];
+    AttemptDoc& A = ad[i];
+    TDoc& T = td[i];
+    memset(&T, 0, sizeof(T));
+    T.off = a_off[i]; T.len = a_len[i]; T.r0 = sh.r0; T.f0 = sh.f0;
+    slot_r0[i] = sh.r0;
+    item_base[i] = (uint32_t)n_items;
+    uint32_t nrows = a_mr[i];
+    uint32_t h = (uint32_t)A.hdr.names.size();
+    if (sh.n_rec == 0 || !A.hdr.found || !A.hdr.utf8_ok) A.fail = 1;                  // EmptyDataError / decode
+    else if (sh.final_state == ST_Q && (uint64_t)sh.n_rec < (uint64_t)nrows + 1) A.fail = 1;  // EOF inside string
+    else if (h != sh.hdr_nf) A.fail = 2;                                                // internal mismatch: never guess
+    else {
+      uint32_t W = h;
+      if (sh.n_rec >= 2 && sh.first_nf > W) W = sh.first_nf;
+      if (sh.max_nf > W) A.fail = 1;             // "Expected N fields in line K, saw M"
+      else if (h <= 1) A.fail = 1;               // len(df.columns) > 1 is false
+      else if (W > 1024) A.fail = 2;
+      else {
+        T.W = W; T.lead = W - h; T.h = h;
+        T.n_data = std::min<uint32_t>(sh.n_rec - 1, nrows);
+        T.bl = chunk_rows_for_width(W);
+        T.n_chunks = (T.n_data + T.bl - 1) / T.bl;
+        T.rb = std::min<uint32_t>(pow2_floor(std::max<uint32_t>(1, 2048 / W)), T.bl);
+        T.stat_base = (uint32_t)n_stat; n_stat += (uint64_t)T.n_chunks * W;
+        T.col_base = (uint32_t)n_cols; n_cols += h;
+        n_items += (T.n_data + T.rb - 1) / T.rb;
+        std::string banner = std::string("=== CSV Data (using ") + kEncNames[enc] + ", separator '" +
+                             (char)sep + "') ===\n";
+        T.banner_off = (uint32_t)names.size(); T.banner_len = (uint32_t)banner.size();
+        names += banner;
+        std::string empty = empty_frame_text(A.hdr.names);
+        T.empty_off = (uint32_t)names.size(); T.empty_len = (uint32_t)empty.size();
+        names += empty;
+        for (uint32_t j = 0; j < h; ++j) {
+          name_off.push_back((uint32_t)names.size());
+          name_len.push_back((uint32_t)A.hdr.names[j].size());
+          name_cp.push_back(A.hdr.ncp[j]);
+          T.hdr_extra += (uint32_t)A.hdr.names[j].size() - A.hdr.ncp[j];
+          names += A.hdr.names[j];
+        }
+        T.active = 1; A.active = true;
+      }
+    }
+    T.item_base = item_base[i];
+  }
+  item_base[m] = (uint32_t)n_items;
+  slot_r0[m] = n_slots;
+  if (n_stat >= (1ull << 31) || n_items >= (1ull << 31)) { c->err = "batch too large"; return RFQ_ERR_ARG; }
+  // ---- 4. upload the table description
+  RFQ_CK(c, c->h_up.reserve(sizeof(TDoc) * (m + 1) + 8ull * (m + 2) + 12ull * (n_cols + 1) +
+                            names.size() + 8192));
+  Uploader up2((uint8_t*)c->h_up.p);
+  size_t o_td = up2.put(td.data(), m), o_ib = up2.put(item_base.data(), m + 1);
+  size_t o_sr = up2.put(slot_r0.data(), m + 1);
+  size_t o_no = up2.put(name_off.data(), name_off.size());
+  size_t o_nl = up2.put(name_len.data(), name_len.size());
+  size_t o_nc = up2.put(name_cp.data(), name_cp.size());
+  size_t o_nm = up2.put(names.data(), names.size());
+  uint8_t* d_up2 = c->pool.alloc<uint8_t>(up2.used + 256);
+  TableArgs ta{};
+  ta.arena = d_arena;
+  ta.n_docs = m; ta.n_items = (uint32_t)n_items;
+  ta.fend = sa.fend; ta.rec_fend = sa.rec_fend; ta.rec_start = sa.rec_start;
+  ta.n_slots = n_slots;
+  ta.n_stat = (uint32_t)n_stat; ta.n_cols = (uint32_t)n_cols;
+  ta.stat = c->pool.alloc<ChunkStat>(n_stat + 1);
+  ta.meas = c->pool.alloc<ChunkMeasure>(n_stat + 1);
+  ta.ctype = c->pool.alloc<uint8_t>(n_stat + 1);
+  ta.chunk_nf = c->pool.alloc<uint8_t>(n_stat + 1);
+  ta.row_na = c->pool.alloc<uint32_t>((size_t)n_slots + 1);
+  ta.row_extra = c->pool.alloc<uint32_t>((size_t)n_slots + 1);
+  ta.row_bytes = c->pool.alloc<unsigned long long>((size_t)n_slots + 2);
+  ta.row_off = c->pool.alloc<unsigned long long>((size_t)n_slots + 2);
+  ta.n_keep = c->pool.alloc<uint32_t>(m + 1);
+  ta.doc_flags = c->pool.alloc<int32_t>(m + 1);
+  ta.doc_linew = c->pool.alloc<uint32_t>(m + 1);
+  ta.col = c->pool.alloc<ColOut>(n_cols + 1);
+  ta.scan_tmp64 = c->pool.alloc<unsigned long long>(scan_partials_needed((uint64_t)n_slots + 1));
+  ta.doc_out_off = c->pool.alloc<unsigned long long>(m + 1);
+  ta.doc_out_len = c->pool.alloc<unsigned long long>(m + 1);
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  RFQ_CK(c, cudaMemcpyAsync(d_up2, c->h_up.p, up2.used, cudaMemcpyHostToDevice, s));
+  ta.docs = (const TDoc*)(d_up2 + o_td);
+  ta.item_doc_base = (const uint32_t*)(d_up2 + o_ib);
+  ta.slot_doc_r0 = (const uint32_t*)(d_up2 + o_sr);
+  ta.name_off = (const uint32_t*)(d_up2 + o_no);
+  ta.name_len = (const uint32_t*)(d_up2 + o_nl);
+  ta.name_cp = (const uint32_t*)(d_up2 + o_nc);
+  ta.names = d_up2 + o_nm;
+  RFQ_CK(c, cudaMemsetAsync(ta.row_na, 0, 4ull * (n_slots + 1), s));
+  RFQ_CK(c, cudaMemsetAsync(ta.row_extra, 0, 4ull * (n_slots + 1), s));
+  RFQ_CK(c, cudaMemsetAsync(ta.chunk_nf, 0, n_stat + 1, s));
+  RFQ_CK(c, cudaMemsetAsync(ta.n_keep, 0, 4ull * (m + 1), s));
+  RFQ_CK(c, cudaMemsetAsync(ta.doc_flags, 0, 4ull * (m + 1), s));
+  RFQ_CK(c, cudaMemsetAsync(ta.doc_linew, 0, 4ull * (m + 1), s));
+  // ---- 5. classify, decide, measure, layout, sizes
+  c->prof.mark("csv_classify", s);
+  csv_table_classify(ta, s);
+  c->prof.mark("csv_measure+layout", s);
+  csv_table_measure(ta, s);
+  uint8_t* hd = (uint8_t*)c->h_down.p;
+  unsigned long long* h_total = (unsigned long long*)hd;
+  unsigned long long* h_ooff = (unsigned long long*)(hd + 256);
+  unsigned long long* h_olen = h_ooff + (m + 1);
+  uint32_t* h_keep = (uint32_t*)(h_olen + (m + 1));
+  int32_t* h_flags = (int32_t*)(h_keep + (m + 1));
+  RFQ_CK(c, cudaMemcpyAsync(h_total, ta.row_off + n_slots, 8, cudaMemcpyDeviceToHost, s));
+  RFQ_CK(c, cudaMemcpyAsync(h_ooff, ta.doc_out_off, 8ull * m, cudaMemcpyDeviceToHost, s));
+  RFQ_CK(c, cudaMemcpyAsync(h_olen, ta.doc_out_len, 8ull * m, cudaMemcpyDeviceToHost, s));
+  RFQ_CK(c, cudaMemcpyAsync(h_keep, ta.n_keep, 4ull * m, cudaMemcpyDeviceToHost, s));
+  RFQ_CK(c, cudaMemcpyAsync(h_flags, ta.doc_flags, 4ull * m, cudaMemcpyDeviceToHost, s));
+  RFQ_CK(c, cudaStreamSynchronize(s));
+  const uint64_t total = *h_total;
+  // ---- 6. emit
+  uint8_t* d_text = c->pool.alloc<uint8_t>(total + 64);
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  c->prof.mark("csv_emit", s);
+  if (total) csv_table_emit(ta, d_text, s);
+  c->prof.mark("csv_attempt_end", s);
+  RFQ_CK(c, cudaGetLastError());
+  const uint64_t host_base = c->out_total;
+  c->segs.push_back({d_text, total, host_base});
+  c->out_total += total;
+  for (uint32_t i = 0; i < m; ++i) {
+    uint32_t d = sel[i];
+    int fail = ad[i].fail;
+    if (!fail && (h_flags[i] & 1)) fail = 1;   // UnicodeDecodeError in a cell
+    if (!fail && (h_flags[i] & 2)) fail = 2;
+    if (fail == 1) continue;                    // next (encoding, separator)
+    resolved[d] = 1;
+    if (fail == 2) { c->r_status[d] = RFQ_DOC_UNSUPPORTED; continue; }
+    c->r_status[d] = RFQ_DOC_OK;
+    c->r_off[d] = host_base + h_ooff[i];
+    c->r_len[d] = h_olen[i];
+    c->r_rows[d] = h_keep[i];
+    c->r_cols[d] = td[i].h;
+    c->r_attempt[d] = (uint8_t)(enc * 3 + sep_i);
+  }
+  return RFQ_OK;
+}
+
+extern "C" int rfq_csv_run(rfq_ctx* c, const int64_t* max_rows_in) {
+  if (!c) return RFQ_ERR_ARG;
+  if (!c->staged) { c->err = "rfq_csv_run: nothing staged"; return RFQ_ERR_STATE; }
+  RFQ_CK(c, cudaSetDevice(c->device));
+  cudaStream_t s = c->stream;
+  const uint32_t n = c->n_docs;
+  c->prof.begin();
+  RFQ_CK(c, cudaEventRecord(c->ev0, s));
+  c->pool.reset();
+  c->segs.clear();
+  c->out_total = 0;
+  c->host_tables = true;
+  c->r_off.assign(n, 0); c->r_len.assign(n, 0);
+  c->r_status.assign(n, RFQ_DOC_CSV_UNPARSEABLE);
+  c->r_rows.assign(n, 0); c->r_cols.assign(n, 0); c->r_attempt.assign(n, 0xFF);
+  std::vector<int64_t> max_rows(n, 1000);
+  if (max_rows_in) for (uint32_t d = 0; d < n; ++d) max_rows[d] = max_rows_in[d];
+  std::vector<uint8_t> resolved(n, 0);
+  std::vector<uint32_t> pending(n);
+  for (uint32_t d = 0; d < n; ++d) pending[d] = d;
+  // latin-1 view of the pending documents (built only if the utf-8 attempts leave any)
+  std::vector<uint32_t> l_off, l_len;
+  const uint8_t* d_latin = nullptr;
+  for (int enc = 0; enc < 2 && !pending.empty(); ++enc) {
+    const uint8_t* arena = (const uint8_t*)c->d_arena.p;
+    const std::vector<uint32_t>* off = &c->h_doc_off;
+    const std::vector<uint32_t>* len = &c->h_doc_len;
+    if (enc == 1) {
+      const uint32_t m = (uint32_t)pending.size();
+      std::vector<uint32_t> p_off(m), p_len(m);
+      for (uint32_t i = 0; i < m; ++i) { p_off[i] = c->h_doc_off[pending[i]]; p_len[i] = c->h_doc_len[pending[i]]; }
+      RFQ_CK(c, c->h_up.reserve(16ull * (m + 2) + 4096));
+      Uploader up((uint8_t*)c->h_up.p);
+      size_t o_off = up.put(p_off.data(), m), o_len = up.put(p_len.data(), m);
+      uint8_t* d_up = c->pool.alloc<uint8_t>(up.used + 256);
+      uint32_t* d_hi = c->pool.alloc<uint32_t>(m + 1);
+      if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+      RFQ_CK(c, cudaMemcpyAsync(d_up, c->h_up.p, up.used, cudaMemcpyHostToDevice, s));
+      c->prof.mark("latin1_transcode", s);
+      latin1_count(arena, (const uint32_t*)(d_up + o_off), (const uint32_t*)(d_up + o_len), m, d_hi, s);
+      RFQ_CK(c, c->h_down.reserve(4ull * (m + 1) + 4096));
+      uint32_t* h_hi = (uint32_t*)c->h_down.p;
+      RFQ_CK(c, cudaMemcpyAsync(h_hi, d_hi, 4ull * m, cudaMemcpyDeviceToHost, s));
+      RFQ_CK(c, cudaStreamSynchronize(s));
+      l_off.assign(n, 0); l_len.assign(n, 0);
+      std::vector<uint32_t> n_off(m);
+      uint64_t total = 0;
+      for (uint32_t i = 0; i < m; ++i) {
+        uint64_t nl = (uint64_t)p_len[i] + h_hi[i];
+        n_off[i] = (uint32_t)total;
+        l_off[pending[i]] = (uint32_t)total; l_len[pending[i]] = (uint32_t)nl;
+        total += (nl + RFQ_ALIGN - 1) / RFQ_ALIGN * RFQ_ALIGN;
+      }
+      if (total + 64 >= (1ull << 32)) { c->err = "latin-1 arena must be < 4 GiB"; return RFQ_ERR_ARG; }
+      RFQ_CK(c, c->d_arena2.reserve(total + 64));
+      RFQ_CK(c, cudaMemsetAsync(c->d_arena2.p, 0, total + 64, s));
+      Uploader up2((uint8_t*)c->h_up.p);
+      size_t o_no = up2.put(n_off.data(), m);
+      uint32_t* d_no = c->pool.alloc<uint32_t>(m + 64);
+      if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+      RFQ_CK(c, cudaMemcpyAsync(d_no, (uint8_t*)c->h_up.p + o_no, 4ull * m, cudaMemcpyHostToDevice, s));
+      latin1_expand(arena, (const uint32_t*)(d_up + o_off), (const uint32_t*)(d_up + o_len), d_no, m,
+                    (uint8_t*)c->d_arena2.p, s);
+      RFQ_CK(c, cudaStreamSynchronize(s));  // h_up is reused by the attempts below
+      d_latin = (const uint8_t*)c->d_arena2.p;
+      arena = d_latin; off = &l_off; len = &l_len;
+    }
+    for (int sep_i = 0; sep_i < 3 && !pending.empty(); ++sep_i) {
+      int rc = csv_attempt(c, pending, arena, *off, *len, enc, sep_i, max_rows, resolved);
+      if (rc) return rc;
+      std::vector<uint32_t> next;
+      for (uint32_t d : pending) if (!resolved[d]) next.push_back(d);
+      pending.swap(next);
+    }
+  }
+  c->prof.mark("end", s);
+  RFQ_CK(c, cudaEventRecord(c->ev1, s));
+  c->d_out_off = nullptr; c->d_out_len = nullptr;
+  c->have_output = true;
+  c->timed = true;
+  return RFQ_OK;
+}

@@ -1,0 +1,280 @@
+// Delimiter / quote-state scan and row / field splitter (SURVEY.md §7.1b K1 + K2).
+//
+// pandas' tokenizer state machine (csv_dfa.cuh) run in parallel: every lane turns its 16 bytes
+// into a state->state transition function (8 states packed as nibbles, composed with PRMT),
+// functions are composed across the warp (one 512-byte tile), tile functions are scanned across
+// the arena, and a second sweep replays the DFA from the now-known start states to count and
+// then index field ends, record ends and record starts.  Documents start on 16-byte boundaries
+// and tiles never span documents; the end of each document is a virtual LF.
+// HBM-bound byte work (the input is read three times, from L2 when it fits): no tensor cores.
+#include <cuda_runtime.h>
+#include "csv_dfa.cuh"
+#include "launch.h"
+#include "pipeline.h"
+#include "rfq_common.cuh"
+#include "scan.cuh"
+
+namespace rfq {
+
+struct FnCompose {
+  typedef uint32_t T;
+  __device__ static T identity() { return RFQ_FN_IDENTITY; }
+  __device__ static T op(T a, T b) { return fn_compose(a, b); }  // a happens before b
+};
+
+__device__ __forceinline__ uint32_t scan_find_doc(const uint32_t* __restrict__ tile_base,
+                                                  uint32_t n, uint32_t t) {
+  uint32_t lo = 0, hi = n;
+  while (hi - lo > 1) {
+    uint32_t mid = (lo + hi) >> 1;
+    if (__ldg(tile_base + mid) <= t) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// classes of this lane's 16 bytes, 4 bits each, in a 64-bit word
+struct LaneBytes {
+  unsigned long long cls;  // nibble k = class of byte k
+};
+
+__device__ __forceinline__ LaneBytes load_lane_classes(const uint8_t* __restrict__ doc,
+                                                       uint32_t len, uint32_t base, uint32_t sep,
+                                                       bool bom) {
+  uint4 v = make_uint4(0, 0, 0, 0);
+  if (base < len) v = __ldg(reinterpret_cast<const uint4*>(doc + base));
+  uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  unsigned long long cls = 0;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    uint32_t pos = base + k;
+    uint32_t b = (w[k >> 2] >> ((k & 3) * 8)) & 0xFFu;
+    int c;
+    if (pos < len) c = (bom && pos < 3) ? CL_PAD : csv_class(b, sep);
+    else c = (pos == len) ? CL_LF : CL_PAD;
+    cls |= (unsigned long long)c << (4 * k);
+  }
+  return LaneBytes{cls};
+}
+
+// lane function by reverse composition: G <- G o t_k, running G kept as a byte table
+__device__ __forceinline__ uint32_t lane_function(unsigned long long cls,
+                                                  const uint32_t* __restrict__ class_fn) {
+  uint32_t glo = 0x03020100u, ghi = 0x07060504u;
+#pragma unroll
+  for (int k = 15; k >= 0; --k) {
+    uint32_t sel = class_fn[(cls >> (4 * k)) & 0xFu];
+    uint32_t nlo = __byte_perm(glo, ghi, sel & 0xFFFFu);
+    uint32_t nhi = __byte_perm(glo, ghi, sel >> 16);
+    glo = nlo; ghi = nhi;
+  }
+  uint32_t p0 = glo | (glo >> 4), p1 = ghi | (ghi >> 4);
+  uint32_t lo = (p0 & 0xFFu) | ((p0 >> 8) & 0xFF00u);
+  uint32_t hi = (p1 & 0xFFu) | ((p1 >> 8) & 0xFF00u);
+  return lo | (hi << 16);
+}
+
+__device__ __forceinline__ bool doc_has_bom(const uint8_t* __restrict__ doc, uint32_t len) {
+  return len >= 3 && doc[0] == 0xEF && doc[1] == 0xBB && doc[2] == 0xBF;
+}
+
+#define RFQ_INIT_CLASS_FN()                                         \
+  __shared__ uint32_t class_fn[8];                                  \
+  if (threadIdx.x < 8) class_fn[threadIdx.x] = threadIdx.x < N_CLASSES ? csv_class_fn(threadIdx.x) : RFQ_FN_IDENTITY; \
+  __syncthreads();
+
+// ---- pass 1: transition function of every tile ------------------------------------------------
+__global__ void __launch_bounds__(256) csv_tilefn_kernel(ScanArgs a) {
+  RFQ_INIT_CLASS_FN();
+  uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
+  int lane = threadIdx.x & 31;
+  if (t >= a.n_tiles) return;
+  uint32_t d = scan_find_doc(a.tile_base, a.n_docs, t);
+  uint32_t tile = t - a.tile_base[d];
+  uint32_t len = a.doc_len[d];
+  const uint8_t* doc = a.arena + a.doc_off[d];
+  bool bom = tile == 0 && doc_has_bom(doc, len);
+  LaneBytes lb = load_lane_classes(doc, len, tile * RFQ_TILE + lane * 16, a.sep, bom);
+  uint32_t f = lane_function(lb.cls, class_fn);
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t g = __shfl_down_sync(0xffffffffu, f, o);
+    if ((lane & (2 * o - 1)) == 0) f = fn_compose(f, g);
+  }
+  if (lane == 0) a.tile_fn[t] = tile == 0 ? fn_const(fn_apply(f, ST_R)) : f;
+}
+
+// walk 16 bytes from a known state; calls ev(k, events, state_before) for bytes with events
+template <class F>
+__device__ __forceinline__ int lane_walk(unsigned long long cls, int st, F&& ev) {
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    int c = (int)((cls >> (4 * k)) & 0xFu);
+    int e = csv_events(st, c);
+    if (e) ev(k, e, st);
+    st = csv_next(st, c);
+  }
+  return st;
+}
+
+// ---- pass 2: lane start states + per-tile counts ----------------------------------------------
+__global__ void __launch_bounds__(256) csv_count_kernel(ScanArgs a) {
+  RFQ_INIT_CLASS_FN();
+  uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
+  int lane = threadIdx.x & 31;
+  if (t >= a.n_tiles) return;
+  uint32_t d = scan_find_doc(a.tile_base, a.n_docs, t);
+  uint32_t tile = t - a.tile_base[d];
+  uint32_t len = a.doc_len[d];
+  const uint8_t* doc = a.arena + a.doc_off[d];
+  bool bom = tile == 0 && doc_has_bom(doc, len);
+  uint32_t base = tile * RFQ_TILE + lane * 16;
+  LaneBytes lb = load_lane_classes(doc, len, base, a.sep, bom);
+  uint32_t f = lane_function(lb.cls, class_fn);
+  // inclusive scan of lane functions, then shift to exclusive
+  uint32_t incl = f;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t g = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl = fn_compose(g, incl);
+  }
+  uint32_t excl = __shfl_up_sync(0xffffffffu, incl, 1);
+  if (lane == 0) excl = RFQ_FN_IDENTITY;
+  int tile_start = tile == 0 ? ST_R : fn_apply(a.tile_fn_pre[t], ST_R);
+  int st = fn_apply(excl, tile_start);
+  uint32_t b0 = __ballot_sync(0xffffffffu, st & 1);
+  uint32_t b1 = __ballot_sync(0xffffffffu, st & 2);
+  uint32_t b2 = __ballot_sync(0xffffffffu, st & 4);
+  if (lane == 0) {
+    a.lane_state[3 * t] = b0; a.lane_state[3 * t + 1] = b1; a.lane_state[3 * t + 2] = b2;
+  }
+  uint32_t nf = 0, nl = 0;
+  uint32_t eof_k = (len >= base && len < base + 16) ? len - base : 0xFFu;
+  int final_state = -1;
+  lane_walk(lb.cls, st, [&](int k, int e, int sb) {
+    nf += (e & EV_FIELD_END) ? 1u : 0u;
+    nl += (e & EV_LINE_END) ? 1u : 0u;
+  });
+  if (eof_k != 0xFFu) {  // state just before the virtual LF
+    int s2 = st;
+    for (uint32_t k = 0; k < eof_k; ++k) s2 = csv_next(s2, (int)((lb.cls >> (4 * k)) & 0xFu));
+    final_state = s2;
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    nf += __shfl_xor_sync(0xffffffffu, nf, o);
+    nl += __shfl_xor_sync(0xffffffffu, nl, o);
+  }
+  if (lane == 0) { a.tile_nf[t] = nf; a.tile_nl[t] = nl; }
+  if (final_state >= 0) a.doc_final[d] = (uint32_t)final_state;
+}
+
+// ---- pass 3: write field ends / record ends / record starts -----------------------------------
+__global__ void __launch_bounds__(256) csv_index_kernel(ScanArgs a) {
+  uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
+  int lane = threadIdx.x & 31;
+  if (t >= a.n_tiles) return;
+  uint32_t d = scan_find_doc(a.tile_base, a.n_docs, t);
+  uint32_t tile = t - a.tile_base[d];
+  uint32_t len = a.doc_len[d];
+  const uint8_t* doc = a.arena + a.doc_off[d];
+  bool has_bom = doc_has_bom(doc, len);
+  bool bom = tile == 0 && has_bom;
+  uint32_t base = tile * RFQ_TILE + lane * 16;
+  LaneBytes lb = load_lane_classes(doc, len, base, a.sep, bom);
+  uint32_t b0 = a.lane_state[3 * t], b1 = a.lane_state[3 * t + 1], b2 = a.lane_state[3 * t + 2];
+  int st = (int)(((b0 >> lane) & 1u) | (((b1 >> lane) & 1u) << 1) | (((b2 >> lane) & 1u) << 2));
+  // this lane's counts, then exclusive prefix inside the warp
+  uint32_t nf = 0, nl = 0;
+  lane_walk(lb.cls, st, [&](int k, int e, int sb) {
+    nf += (e & EV_FIELD_END) ? 1u : 0u;
+    nl += (e & EV_LINE_END) ? 1u : 0u;
+  });
+  uint32_t pf = nf, pl = nl;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t x = __shfl_up_sync(0xffffffffu, pf, o);
+    uint32_t y = __shfl_up_sync(0xffffffffu, pl, o);
+    if (lane >= o) { pf += x; pl += y; }
+  }
+  uint32_t g = a.tile_nf_pre[t] + pf - nf;          // global index of this lane's first field end
+  uint32_t r = a.tile_nl_pre[t] + pl - nl + d;      // record slot currently open at this lane
+  uint32_t doc_begin = has_bom ? 3u : 0u;
+  lane_walk(lb.cls, st, [&](int k, int e, int sb) {
+    uint32_t pos = base + k;
+    if (e & EV_REC_START) a.rec_start[r] = pos;
+    if (e & EV_REC_START_WS) {
+      // the blanks that opened this line belong to its first field: walk back over them
+      uint32_t p = pos;
+      while (p > doc_begin) {
+        uint32_t c = doc[p - 1];
+        if ((c == ' ' || c == '\t') && c != a.sep) --p; else break;
+      }
+      a.rec_start[r] = p;
+    }
+    if (e & EV_FIELD_END) a.fend[g++] = pos;
+    if (e & EV_LINE_END) a.rec_fend[r++] = g;
+  });
+}
+
+// ---- record shapes per document ---------------------------------------------------------------
+__global__ void __launch_bounds__(256) csv_shape_init_kernel(ScanArgs a, DocShape* shape) {
+  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= a.n_docs) return;
+  uint32_t t0 = a.tile_base[d], t1 = a.tile_base[d + 1];
+  DocShape s;
+  s.n_rec = a.tile_nl_pre[t1] - a.tile_nl_pre[t0];
+  s.hdr_nf = 0; s.first_nf = 0; s.max_nf = 0;
+  s.final_state = a.doc_final[d];
+  s.r0 = a.tile_nl_pre[t0] + d;
+  s.f0 = a.tile_nf_pre[t0];
+  s.pad = 0;
+  shape[d] = s;
+}
+
+__global__ void __launch_bounds__(256) csv_shape_kernel(ScanArgs a, const uint32_t* __restrict__ max_rows,
+                                                        DocShape* shape, uint32_t n_slots) {
+  uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot >= n_slots) return;
+  // slot -> document: largest d with r0[d] <= slot
+  uint32_t lo = 0, hi = a.n_docs;
+  while (hi - lo > 1) {
+    uint32_t mid = (lo + hi) >> 1;
+    if (shape[mid].r0 <= slot) lo = mid; else hi = mid;
+  }
+  uint32_t d = lo;
+  uint32_t L = slot - shape[d].r0;
+  if (L >= shape[d].n_rec || L > max_rows[d]) return;  // spare slot or beyond nrows
+  uint32_t fbeg = L == 0 ? shape[d].f0 : a.rec_fend[slot - 1];
+  uint32_t nf = a.rec_fend[slot] - fbeg;
+  if (L == 0) shape[d].hdr_nf = nf;
+  else if (L == 1) shape[d].first_nf = nf;
+  else atomicMax(&shape[d].max_nf, nf);
+}
+
+// ---------------------------------------------------------------------------------------------
+void csv_scan_count(const ScanArgs& a, cudaStream_t s) {
+  if (a.n_tiles == 0) return;
+  uint32_t nb = (a.n_tiles + 7) / 8;
+  RFQ_LAUNCH(csv_tilefn_kernel, nb, 256, 0, s, a);
+  exclusive_scan<FnCompose>(a.tile_fn, a.tile_fn_pre, a.n_tiles, a.scan_tmp, nullptr, s);
+  cudaMemsetAsync(a.tile_nf + a.n_tiles, 0, 4, s);
+  cudaMemsetAsync(a.tile_nl + a.n_tiles, 0, 4, s);
+  RFQ_LAUNCH(csv_count_kernel, nb, 256, 0, s, a);
+  exclusive_scan<SumU32>(a.tile_nf, a.tile_nf_pre, a.n_tiles + 1, a.scan_tmp, nullptr, s);
+  exclusive_scan<SumU32>(a.tile_nl, a.tile_nl_pre, a.n_tiles + 1, a.scan_tmp, nullptr, s);
+}
+
+void csv_scan_index(const ScanArgs& a, cudaStream_t s) {
+  if (a.n_tiles == 0) return;
+  RFQ_LAUNCH(csv_index_kernel, (a.n_tiles + 7) / 8, 256, 0, s, a);
+}
+
+void csv_doc_shape(const ScanArgs& a, const uint32_t* max_rows32, DocShape* shape, uint32_t n_slots,
+                   cudaStream_t s) {
+  if (a.n_docs == 0) return;
+  RFQ_LAUNCH(csv_shape_init_kernel, (a.n_docs + 255) / 256, 256, 0, s, a, shape);
+  if (n_slots)
+    RFQ_LAUNCH(csv_shape_kernel, (n_slots + 255) / 256, 256, 0, s, a, max_rows32, shape, n_slots);
+}
+
+}  // namespace rfq

@@ -1,0 +1,362 @@
+// Cell typing + numeric parse, column decisions, and the fixed-width formatter / emitter
+// (SURVEY.md §7.1b K3, K4, K5): everything `pd.read_csv` does after tokenising plus
+// `dropna(how='all').fillna('')` and `to_string(index=False)` (app/file_parser.py:301-305).
+//
+// Work item = a block of `rb` consecutive data rows of one document that never crosses a
+// low_memory chunk boundary; a CTA takes items grid-stride, one thread per cell (adjacent lanes
+// = adjacent cells, so token bytes are read nearly coalesced).  Column statistics are reduced in
+// shared memory per item and merged into global memory with one atomic per column per item.
+// Three sweeps over the cells: classify -> (decide) -> measure -> (layout, row offsets) -> emit.
+// Tokens are re-parsed in each sweep instead of being materialised: the bytes stay in L2 and a
+// typed copy would cost more HBM traffic than the re-parse costs issue slots.
+#include <cuda_runtime.h>
+#include "cell_ops.cuh"
+#include "launch.h"
+#include "pipeline.h"
+#include "scan.cuh"
+
+namespace rfq {
+
+#define RFQ_MAX_W 1024
+
+__device__ __forceinline__ uint32_t ub_search(const uint32_t* __restrict__ base, uint32_t n,
+                                              uint32_t x) {
+  // largest i in [0, n) with base[i] <= x
+  uint32_t lo = 0, hi = n;
+  while (hi - lo > 1) {
+    uint32_t mid = (lo + hi) >> 1;
+    if (__ldg(base + mid) <= x) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+__device__ __forceinline__ CellSrc fetch_cell(const TableArgs& a, const TDoc& D, uint32_t slot,
+                                              uint32_t c) {
+  CellSrc s;
+  s.mode = 0; s.missing = false; s.p = a.arena; s.n = 0;
+  uint32_t fbeg = __ldg(a.rec_fend + slot - 1);
+  uint32_t nf = __ldg(a.rec_fend + slot) - fbeg;
+  if (c >= nf) { s.missing = true; return s; }
+  uint32_t st = c == 0 ? __ldg(a.rec_start + slot) : __ldg(a.fend + fbeg + c - 1) + 1;
+  uint32_t en = __ldg(a.fend + fbeg + c);
+  s.p = a.arena + D.off + st;
+  s.n = en - st;
+  return s;
+}
+
+struct ItemCtx {
+  uint32_t d, row0, nrows, chunk;
+};
+__device__ __forceinline__ ItemCtx item_ctx(const TableArgs& a, uint32_t item, uint32_t* s_doc) {
+  if (threadIdx.x == 0) *s_doc = ub_search(a.item_doc_base, a.n_docs, item);
+  __syncthreads();
+  ItemCtx c;
+  c.d = *s_doc;
+  const TDoc& D = a.docs[c.d];
+  c.row0 = (item - D.item_base) * D.rb;
+  c.nrows = min(D.rb, D.n_data - c.row0);
+  c.chunk = c.row0 / D.bl;
+  return c;
+}
+
+// ---- sweep 1: classify --------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) csv_classify_kernel(TableArgs a) {
+  __shared__ uint32_t s_flags[RFQ_MAX_W], s_bad[RFQ_MAX_W], s_ovf[RFQ_MAX_W];
+  __shared__ uint32_t s_doc;
+  ChunkStat* stat = (ChunkStat*)a.stat;
+  for (uint32_t item = blockIdx.x; item < a.n_items; item += gridDim.x) {
+    ItemCtx ic = item_ctx(a, item, &s_doc);
+    const TDoc D = a.docs[ic.d];
+    uint32_t W = D.W;
+    for (uint32_t c = threadIdx.x; c < W; c += blockDim.x) {
+      s_flags[c] = 0; s_bad[c] = RFQ_NO_ROW; s_ovf[c] = RFQ_NO_ROW;
+    }
+    __syncthreads();
+    uint32_t ncell = ic.nrows * W;
+    for (uint32_t idx = threadIdx.x; idx < ncell; idx += blockDim.x) {
+      uint32_t rr = idx / W, c = idx - rr * W;
+      uint32_t row = ic.row0 + rr;
+      uint32_t slot = D.r0 + 1 + row;
+      CellSrc src = fetch_cell(a, D, slot, c);
+      int is;
+      uint32_t f = classify_cell(src, &is);
+      if ((s_flags[c] & f) != f) atomicOr(&s_flags[c], f);
+      if (is != INT_OK) {
+        if (row < s_bad[c]) atomicMin(&s_bad[c], row);
+        if (is == INT_OVERFLOW && row < s_ovf[c]) atomicMin(&s_ovf[c], row);
+      }
+      if ((f & SF_ANY_NA) && c >= D.lead) atomicAdd(a.row_na + slot, 1u);
+    }
+    __syncthreads();
+    for (uint32_t c = threadIdx.x; c < W; c += blockDim.x) {
+      ChunkStat* S = stat + D.stat_base + ic.chunk * W + c;
+      if (s_flags[c]) atomicOr(&S->flags, s_flags[c]);
+      if (s_bad[c] != RFQ_NO_ROW) atomicMin(&S->int_bad_min, s_bad[c]);
+      if (s_ovf[c] != RFQ_NO_ROW) atomicMin(&S->int_ovf_min, s_ovf[c]);
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(256) csv_stat_init_kernel(ChunkStat* stat, ChunkMeasure* meas,
+                                                            uint32_t n) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  stat[i] = ChunkStat{0u, RFQ_NO_ROW, RFQ_NO_ROW, 0u};
+  ChunkMeasure m;
+  m.plain_len = 0; m.ip_len = 0; m.min_tz = 6; m.inf_len = 0; m.obj_len = 0; m.sci_len = 0;
+  m.fl = 0; m.nan_left = 0;
+  meas[i] = m;
+}
+
+// ---- decide chunk types (one thread per document; entries are few) ----------------------------
+__global__ void __launch_bounds__(128) csv_decide_kernel(TableArgs a) {
+  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= a.n_docs) return;
+  const TDoc D = a.docs[d];
+  if (!D.active) return;
+  const ChunkStat* stat = (const ChunkStat*)a.stat;
+  int flags = 0;
+  for (uint32_t k = 0; k < D.n_chunks; ++k) {
+    bool nf = false;
+    for (uint32_t c = 0; c < D.W; ++c) {
+      uint32_t e = D.stat_base + k * D.W + c;
+      ChunkStat S = stat[e];
+      if (S.flags & SF_BAD_UTF8) flags |= 1;
+      int t = decide_chunk_type(S);
+      a.ctype[e] = (uint8_t)t;
+      if (t == CT_STRNF && c >= D.lead) nf = true;
+    }
+    a.chunk_nf[D.stat_base + k * D.W] = nf ? 1 : 0;
+  }
+  if (flags) atomicOr(a.doc_flags + d, flags);
+}
+
+// ---- sweep 2: measure ---------------------------------------------------------------------------
+__device__ __forceinline__ bool row_kept(const TableArgs& a, const TDoc& D, uint32_t slot,
+                                         uint32_t chunk) {
+  return !(__ldg(a.row_na + slot) == D.h && !a.chunk_nf[D.stat_base + chunk * D.W]);
+}
+
+__global__ void __launch_bounds__(256) csv_measure_kernel(TableArgs a) {
+  __shared__ uint32_t s_m[8][RFQ_MAX_W];  // plain, ip, tz(min), inf, obj, sci, fl(or), nan_left(or)
+  __shared__ uint32_t s_doc, s_keep;
+  ChunkMeasure* meas = (ChunkMeasure*)a.meas;
+  for (uint32_t item = blockIdx.x; item < a.n_items; item += gridDim.x) {
+    ItemCtx ic = item_ctx(a, item, &s_doc);
+    const TDoc D = a.docs[ic.d];
+    uint32_t W = D.W;
+    for (uint32_t c = threadIdx.x; c < W; c += blockDim.x) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) s_m[q][c] = q == 2 ? 6u : 0u;
+    }
+    if (threadIdx.x == 0) s_keep = 0;
+    __syncthreads();
+    if (!(a.doc_flags[ic.d] & 1)) {
+      uint32_t ncell = ic.nrows * W;
+      for (uint32_t idx = threadIdx.x; idx < ncell; idx += blockDim.x) {
+        uint32_t rr = idx / W, c = idx - rr * W;
+        uint32_t row = ic.row0 + rr;
+        uint32_t slot = D.r0 + 1 + row;
+        if (c < D.lead || !row_kept(a, D, slot, ic.chunk)) continue;
+        if (c == D.lead) atomicAdd(&s_keep, 1u);
+        int ct = a.ctype[D.stat_base + ic.chunk * W + c];
+        CellMeasure m = measure_cell(fetch_cell(a, D, slot, c), ct);
+        if (m.is_nan) { if (!s_m[7][c]) s_m[7][c] = 1; continue; }
+        if (m.plain_len > s_m[0][c]) atomicMax(&s_m[0][c], m.plain_len);
+        if (m.ip_len > s_m[1][c]) atomicMax(&s_m[1][c], m.ip_len);
+        if (m.tz < s_m[2][c]) atomicMin(&s_m[2][c], m.tz);
+        if (m.inf_len > s_m[3][c]) atomicMax(&s_m[3][c], m.inf_len);
+        if (m.obj_len > s_m[4][c]) atomicMax(&s_m[4][c], m.obj_len);
+        if (m.sci_len > s_m[5][c]) atomicMax(&s_m[5][c], m.sci_len);
+        if ((s_m[6][c] & m.fl) != m.fl) atomicOr(&s_m[6][c], m.fl);
+        if (m.extra_bytes) atomicAdd(a.row_extra + slot, m.extra_bytes);
+      }
+    }
+    __syncthreads();
+    for (uint32_t c = threadIdx.x + D.lead; c < W; c += blockDim.x) {
+      ChunkMeasure* M = meas + D.stat_base + ic.chunk * W + c;
+      if (s_m[0][c]) atomicMax(&M->plain_len, s_m[0][c]);
+      if (s_m[1][c]) atomicMax(&M->ip_len, s_m[1][c]);
+      if (s_m[2][c] < 6) atomicMin(&M->min_tz, s_m[2][c]);
+      if (s_m[3][c]) atomicMax(&M->inf_len, s_m[3][c]);
+      if (s_m[4][c]) atomicMax(&M->obj_len, s_m[4][c]);
+      if (s_m[5][c]) atomicMax(&M->sci_len, s_m[5][c]);
+      if (s_m[6][c]) atomicOr(&M->fl, s_m[6][c]);
+      if (s_m[7][c]) atomicOr(&M->nan_left, 1u);
+    }
+    if (threadIdx.x == 0 && s_keep) atomicAdd(a.n_keep + ic.d, s_keep);
+    __syncthreads();
+  }
+}
+
+// ---- layout: class, width, decimals of every output column; line width -----------------------
+__global__ void __launch_bounds__(128) csv_layout_kernel(TableArgs a) {
+  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= a.n_docs) return;
+  const TDoc D = a.docs[d];
+  if (!D.active) return;
+  const ChunkMeasure* meas = (const ChunkMeasure*)a.meas;
+  ColOut* col = (ColOut*)a.col;
+  uint32_t off = 0;
+  int flags = 0;
+  for (uint32_t j = 0; j < D.h; ++j) {
+    uint32_t c = D.lead + j;
+    uint32_t e0 = D.stat_base + c;
+    bool nan_left = false;
+    for (uint32_t k = 0; k < D.n_chunks; ++k) nan_left |= meas[e0 + (size_t)k * D.W].nan_left != 0;
+    int cls = fold_column_class(a.ctype + e0, D.n_chunks, D.W, nan_left);
+    if (cls == CC_UNSUP) { flags |= 2; cls = CC_OBJ; }
+    ColumnLayout L = layout_column(cls, meas + e0, a.ctype + e0, D.n_chunks, D.W,
+                                   a.name_cp[D.col_base + j]);
+    ColOut o;
+    o.cls = L.cls; o.dec = L.dec; o.sci = L.sci ? 1 : 0; o.width = L.width; o.cp_off = off;
+    col[D.col_base + j] = o;
+    off += L.width + 1;
+  }
+  a.doc_linew[d] = off ? off - 1 : 0;
+  if (flags) atomicOr(a.doc_flags + d, flags);
+}
+
+// ---- bytes of every output line (indexed by record slot; slot r0 = banner + header line) ------
+__global__ void __launch_bounds__(256) csv_rowbytes_kernel(TableArgs a) {
+  uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot > a.n_slots) return;
+  unsigned long long b = 0;
+  if (slot < a.n_slots) {
+    uint32_t d = ub_search(a.slot_doc_r0, a.n_docs, slot);
+    const TDoc D = a.docs[d];
+    if (D.active && a.doc_flags[d] == 0) {
+      uint32_t L = slot - D.r0;
+      uint32_t keep = a.n_keep[d];
+      if (L == 0) b = D.banner_len + (keep ? a.doc_linew[d] + D.hdr_extra : D.empty_len);
+      else if (L <= D.n_data && keep) {
+        uint32_t chunk = (L - 1) / D.bl;
+        if (row_kept(a, D, slot, chunk)) b = 1ull + a.doc_linew[d] + a.row_extra[slot];
+      }
+    }
+  }
+  a.row_bytes[slot] = b;
+}
+
+__global__ void __launch_bounds__(128) csv_docout_kernel(TableArgs a) {
+  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= a.n_docs) return;
+  unsigned long long o0 = a.row_off[a.slot_doc_r0[d]], o1 = a.row_off[a.slot_doc_r0[d + 1]];
+  a.doc_out_off[d] = o0;
+  a.doc_out_len[d] = o1 - o0;
+}
+
+// ---- sweep 3: emit -------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) csv_emit_kernel(TableArgs a, uint8_t* __restrict__ out) {
+  __shared__ uint32_t s_doc;
+  const ColOut* col = (const ColOut*)a.col;
+  for (uint32_t item = blockIdx.x; item < a.n_items; item += gridDim.x) {
+    ItemCtx ic = item_ctx(a, item, &s_doc);
+    const TDoc D = a.docs[ic.d];
+    if (a.doc_flags[ic.d] == 0 && a.n_keep[ic.d] != 0) {
+      uint32_t W = D.W;
+      uint32_t ncell = ic.nrows * W;
+      for (uint32_t idx = threadIdx.x; idx < ncell; idx += blockDim.x) {
+        uint32_t rr = idx / W, c = idx - rr * W;
+        uint32_t row = ic.row0 + rr;
+        uint32_t slot = D.r0 + 1 + row;
+        if (c < D.lead || !row_kept(a, D, slot, ic.chunk)) continue;
+        uint32_t j = c - D.lead;
+        ColOut co = col[D.col_base + j];
+        const uint8_t* ctrow = a.ctype + D.stat_base + ic.chunk * W;
+        int ct = ctrow[c];
+        int kind = print_kind(co.cls, ct, co.sci != 0);
+        CellSrc src = fetch_cell(a, D, slot, c);
+        uint32_t ncp, nb;
+        printed_size(src, ct, kind, co.dec, &ncp, &nb);
+        uint32_t xb = 0;  // extra bytes of the columns to the left (rows with non-ASCII text only)
+        if (j && __ldg(a.row_extra + slot)) {
+          for (uint32_t c2 = D.lead; c2 < c; ++c2) {
+            ColOut c2o = col[D.col_base + c2 - D.lead];
+            int ct2 = ctrow[c2];
+            int k2 = print_kind(c2o.cls, ct2, c2o.sci != 0);
+            if (k2 != PR_STR) continue;
+            uint32_t cp2, nb2;
+            printed_size(fetch_cell(a, D, slot, c2), ct2, k2, c2o.dec, &cp2, &nb2);
+            xb += nb2 - cp2;
+          }
+        }
+        uint8_t* p = out + a.row_off[slot];
+        if (j == 0) { *p = '\n'; p += 1; }
+        else { p += co.cp_off + xb; *p = ' '; p += 1; }
+        uint32_t pad = co.width - ncp;
+        for (uint32_t q = 0; q < pad; ++q) p[q] = ' ';
+        print_cell(src, ct, kind, co.dec, p + pad);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// banner + header line (or the "Empty DataFrame" text): one warp per document
+__global__ void __launch_bounds__(256) csv_header_emit_kernel(TableArgs a, uint8_t* __restrict__ out) {
+  uint32_t d = blockIdx.x * 8 + (threadIdx.x >> 5);
+  int lane = threadIdx.x & 31;
+  if (d >= a.n_docs) return;
+  const TDoc D = a.docs[d];
+  if (!D.active || a.doc_flags[d] != 0) return;
+  const ColOut* col = (const ColOut*)a.col;
+  uint8_t* p = out + a.doc_out_off[d];
+  for (uint32_t i = lane; i < D.banner_len; i += 32) p[i] = a.names[D.banner_off + i];
+  p += D.banner_len;
+  if (a.n_keep[d] == 0) {
+    for (uint32_t i = lane; i < D.empty_len; i += 32) p[i] = a.names[D.empty_off + i];
+    return;
+  }
+  for (uint32_t j = lane; j < D.h; j += 32) {
+    ColOut co = col[D.col_base + j];
+    uint32_t xb = 0;
+    for (uint32_t j2 = 0; j2 < j; ++j2) xb += a.name_len[D.col_base + j2] - a.name_cp[D.col_base + j2];
+    bool numeric = co.cls == CC_INT || co.cls == CC_UINT || co.cls == CC_FLOAT || co.cls == CC_BOOL;
+    uint32_t cp = a.name_cp[D.col_base + j] + (numeric ? 1u : 0u);
+    uint8_t* q = p + co.cp_off + xb;
+    if (j) q[-1] = ' ';
+    uint32_t pad = co.width - cp;
+    for (uint32_t i = 0; i < pad; ++i) q[i] = ' ';
+    q += pad;
+    if (numeric) *q++ = ' ';
+    const uint8_t* nm = a.names + a.name_off[D.col_base + j];
+    uint32_t nl = a.name_len[D.col_base + j];
+    for (uint32_t i = 0; i < nl; ++i) q[i] = nm[i];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+static int table_grid(uint32_t n_items) {
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  uint32_t g = (uint32_t)sms * 8u;  // 8 resident CTAs of 256 threads per SM
+  return (int)(n_items < g ? n_items : g);
+}
+
+void csv_table_classify(const TableArgs& a, cudaStream_t s) {
+  if (a.n_stat)
+    RFQ_LAUNCH(csv_stat_init_kernel, (a.n_stat + 255) / 256, 256, 0, s, (ChunkStat*)a.stat,
+               (ChunkMeasure*)a.meas, a.n_stat);
+  if (a.n_items) RFQ_LAUNCH(csv_classify_kernel, table_grid(a.n_items), 256, 0, s, a);
+}
+
+void csv_table_measure(const TableArgs& a, cudaStream_t s) {
+  if (a.n_docs == 0) return;
+  RFQ_LAUNCH(csv_decide_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
+  if (a.n_items) RFQ_LAUNCH(csv_measure_kernel, table_grid(a.n_items), 256, 0, s, a);
+  RFQ_LAUNCH(csv_layout_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
+  RFQ_LAUNCH(csv_rowbytes_kernel, (a.n_slots + 1 + 255) / 256, 256, 0, s, a);
+  exclusive_scan<SumU64>(a.row_bytes, a.row_off, a.n_slots + 1, a.scan_tmp64, nullptr, s);
+  RFQ_LAUNCH(csv_docout_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
+}
+
+void csv_table_emit(const TableArgs& a, uint8_t* out, cudaStream_t s) {
+  if (a.n_docs == 0) return;
+  RFQ_LAUNCH(csv_header_emit_kernel, (a.n_docs + 7) / 8, 256, 0, s, a, out);
+  if (a.n_items) RFQ_LAUNCH(csv_emit_kernel, table_grid(a.n_items), 256, 0, s, a, out);
+}
+
+}  // namespace rfq

@@ -119,6 +119,15 @@ struct rfq_ctx {
   uint64_t* h_out_off = nullptr; uint64_t* h_out_len = nullptr;
   int32_t* h_status = nullptr; uint32_t* h_rows = nullptr; uint32_t* h_cols = nullptr;
   uint8_t* h_attempt = nullptr;
+  // CSV/table runs keep their per-document tables on the host and their text in segments
+  struct OutSeg { const uint8_t* d; uint64_t bytes; uint64_t host_base; };
+  std::vector<OutSeg> segs;
+  bool host_tables = false;
+  std::vector<uint64_t> r_off, r_len;
+  std::vector<int32_t> r_status;
+  std::vector<uint32_t> r_rows, r_cols;
+  std::vector<uint8_t> r_attempt;
+  rfq::HostBuf h_up, h_down;   // per-attempt upload / download staging
   float last_ms = 0.f;
   uint64_t h2d_bytes = 0, d2h_bytes = 0;
 
@@ -129,6 +138,6 @@ struct rfq_ctx {
   void release_all() {
     pool.release();
     d_arena.release(); d_doctab.release(); d_out.release(); d_arena2.release();
-    h_stage.release(); h_doctab.release(); h_out.release(); h_tabs.release(); h_small.release();
+    h_stage.release(); h_doctab.release(); h_out.release(); h_tabs.release(); h_small.release(); h_up.release(); h_down.release();
   }
 };

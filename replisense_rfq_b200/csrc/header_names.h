@@ -28,10 +28,12 @@ inline bool utf8_valid_count(const std::string& s, uint32_t* ncp) {
 }
 
 // Tokenise the first record of `doc` with the same DFA the kernels run.
-inline HeaderInfo parse_header(const uint8_t* doc, uint64_t len, uint32_t sep) {
+// latin1: the document bytes are latin-1 (the stream pandas tokenises is their UTF-8 transcode:
+// same ASCII structure, no BOM possible, high bytes become two-byte sequences in the names).
+inline HeaderInfo parse_header(const uint8_t* doc, uint64_t len, uint32_t sep, bool latin1 = false) {
   HeaderInfo h;
   uint64_t i = 0;
-  if (len >= 3 && doc[0] == 0xEF && doc[1] == 0xBB && doc[2] == 0xBF) i = 3;
+  if (!latin1 && len >= 3 && doc[0] == 0xEF && doc[1] == 0xBB && doc[2] == 0xBF) i = 3;
   int st = ST_R;
   std::vector<std::pair<uint64_t, uint64_t>> spans;
   uint64_t fstart = 0, ws_start = 0;
@@ -54,7 +56,10 @@ inline HeaderInfo parse_header(const uint8_t* doc, uint64_t len, uint32_t sep) {
     CsvIter it(doc + spans[k].first, (uint32_t)(spans[k].second - spans[k].first));
     std::string s;
     int c;
-    while ((c = it.next()) >= 0) s.push_back((char)c);
+    while ((c = it.next()) >= 0) {
+      if (latin1 && c >= 0x80) { s.push_back((char)(0xC0 | (c >> 6))); s.push_back((char)(0x80 | (c & 0x3F))); }
+      else s.push_back((char)c);
+    }
     if (s.empty()) { s = "Unnamed: " + std::to_string(k); unnamed.push_back(k); }
     raw.push_back(s);
   }

@@ -29,4 +29,102 @@ struct TxtArgs {
 void txt_pipeline(const TxtArgs& a, cudaStream_t s);   // sizes: fills out_len/out_off/out_total
 void txt_emit(const TxtArgs& a, uint8_t* out, cudaStream_t s);
 
+// ------------------------------------------------------------------------------------------
+// CSV / table pipeline
+
+// tokeniser (csv_scan.cu): one attempt = one separator over a set of documents
+struct ScanArgs {
+  const uint8_t* arena;
+  const uint32_t* doc_off;    // [n_docs]
+  const uint32_t* doc_len;    // [n_docs]
+  const uint32_t* tile_base;  // [n_docs+1] prefix of ceil((len+1)/512): the virtual LF at `len` has a tile
+  uint32_t n_docs, n_tiles, sep;
+  uint32_t* tile_fn;          // [n_tiles+1] transition function of each tile (nibble form)
+  uint32_t* tile_fn_pre;      // [n_tiles+1] exclusive composition
+  uint32_t* lane_state;       // [n_tiles*3] bit planes of the 32 lane start states
+  uint32_t* tile_nf;          // [n_tiles+1] field ends per tile      (last = 0)
+  uint32_t* tile_nl;          // [n_tiles+1] line ends per tile       (last = 0)
+  uint32_t* tile_nf_pre;      // [n_tiles+1] exclusive prefix, last = total
+  uint32_t* tile_nl_pre;      // [n_tiles+1]
+  uint32_t* doc_final;        // [n_docs] DFA state before the virtual LF (ST_Q = EOF in string)
+  uint32_t* scan_tmp;         // scan partials
+  // outputs of the index pass (allocated after the totals are known)
+  uint32_t* fend;             // [n_fields] doc-relative position of each field-end byte
+  uint32_t* rec_fend;         // [n_lines + n_docs] one-past-last global field index of each record
+  uint32_t* rec_start;        // [n_lines + n_docs] doc-relative position where each record starts
+};
+void csv_scan_count(const ScanArgs& a, cudaStream_t s);  // tile fns, states, counts, prefixes
+void csv_scan_index(const ScanArgs& a, cudaStream_t s);  // fend / rec_fend / rec_start
+
+// per-document record shape (device -> host after the index pass)
+struct DocShape {
+  uint32_t n_rec;      // complete records
+  uint32_t hdr_nf;     // fields of record 0
+  uint32_t first_nf;   // fields of record 1 (0 if none)
+  uint32_t max_nf;     // max fields over records 2..nrows
+  uint32_t final_state;
+  uint32_t r0;         // global record slot of record 0
+  uint32_t f0;         // global field index of the document's first field
+  uint32_t pad;
+};
+void csv_doc_shape(const ScanArgs& a, const uint32_t* max_rows32, DocShape* shape, uint32_t n_slots,
+                   cudaStream_t s);
+
+// table description handed back to the device by the host after it validated the shapes
+struct TDoc {
+  uint32_t off, len;          // document bytes in the arena
+  uint32_t r0, f0;            // global record slot of the header, first field index
+  uint32_t W, lead, h;        // table width, implicit-index columns, output columns
+  uint32_t n_data;            // data rows used (<= nrows)
+  uint32_t bl, rb, n_chunks;  // low_memory chunk rows, rows per work item, chunks
+  uint32_t stat_base;         // (chunk, col) arrays: stat_base + chunk * W + col
+  uint32_t col_base;          // per output column arrays: col_base + j
+  uint32_t item_base;         // work items of this document start here
+  uint32_t banner_len;        // bytes of "=== CSV Data (...) ===\n"
+  uint32_t hdr_extra;         // header-name bytes minus code points
+  uint32_t empty_off, empty_len;  // "Empty DataFrame..." text in the names arena
+  uint32_t banner_off;        // banner text in the names arena
+  uint32_t active;            // 0 = attempt already failed on the host side (skip)
+};
+
+struct TableArgs {
+  const uint8_t* arena;
+  const TDoc* docs; uint32_t n_docs;
+  const uint32_t* item_doc_base;  // [n_docs+1] prefix of items
+  uint32_t n_items;
+  const uint32_t* fend; const uint32_t* rec_fend; const uint32_t* rec_start;
+  uint32_t n_slots;               // record slots (lines + docs)
+  const uint32_t* slot_doc_r0;    // [n_docs+1] r0 of each document (for slot -> doc search)
+  // (chunk, col)
+  void* stat;        // ChunkStat[n_stat]
+  void* meas;        // ChunkMeasure[n_stat]
+  uint8_t* ctype;    // [n_stat]
+  uint8_t* chunk_nf; // [n_stat] (slot of column 0 of each chunk row): chunk has a CT_STRNF output column
+  uint32_t n_stat;
+  // rows (indexed by record slot)
+  uint32_t* row_na; uint32_t* row_extra;
+  unsigned long long* row_bytes; unsigned long long* row_off;  // [n_slots+1]
+  // per document
+  uint32_t* n_keep; int32_t* doc_flags;  // bit0 decode error, bit1 unsupported
+  uint32_t* doc_linew;            // code points of one output line
+  // per output column
+  void* col;         // ColOut[n_cols]
+  const uint32_t* name_off; const uint32_t* name_len; const uint32_t* name_cp;  // [n_cols]
+  const uint8_t* names;  // names / banner / empty-frame text arena
+  uint32_t n_cols;
+  unsigned long long* scan_tmp64; unsigned long long* out_total;
+  unsigned long long* doc_out_off; unsigned long long* doc_out_len;  // [n_docs]
+};
+struct ColOut { int32_t cls, dec, sci; uint32_t width, cp_off; };
+
+void csv_table_classify(const TableArgs& a, cudaStream_t s);
+void csv_table_measure(const TableArgs& a, cudaStream_t s);   // decide + measure + layout + sizes
+void csv_table_emit(const TableArgs& a, uint8_t* out, cudaStream_t s);
+
+// latin-1 -> UTF-8 stream transcode (second encoding of the trial loop)
+void latin1_count(const uint8_t* arena, const uint32_t* doc_off, const uint32_t* doc_len,
+                  uint32_t n_docs, uint32_t* hi_count, cudaStream_t s);
+void latin1_expand(const uint8_t* arena, const uint32_t* doc_off, const uint32_t* doc_len,
+                   const uint32_t* new_off, uint32_t n_docs, uint8_t* out, cudaStream_t s);
+
 }  // namespace rfq

@@ -202,9 +202,13 @@ int rfq_text_run(rfq_ctx* c) {
     RFQ_CK(c, cudaStreamSynchronize(s));
     total = *c->h_scalar();
   }
-  RFQ_CK(c, c->d_out.reserve(total + 16));
+  uint8_t* d_text = c->pool.alloc<uint8_t>(total + 16);
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
   c->prof.mark("txt_emit", s);
-  txt_emit(a, (uint8_t*)c->d_out.p, s);
+  txt_emit(a, d_text, s);
+  c->segs.clear();
+  c->segs.push_back({d_text, total, 0});
+  c->host_tables = false;
   c->prof.mark("end", s);
   RFQ_CK(c, cudaEventRecord(c->ev1, s));
   RFQ_CK(c, cudaGetLastError());
@@ -232,10 +236,21 @@ int rfq_fetch(rfq_ctx* c) {
   c->h_cols = (uint32_t*)(base + 24ull * (n + 1));
   c->h_attempt = (uint8_t*)(base + 28ull * (n + 1));
   memset(c->h_status, 0, 4ull * (n + 1) * 3 + (n + 1));
-  if (c->out_total)
-    RFQ_CK(c, cudaMemcpyAsync(c->h_out.p, c->d_out.p, c->out_total, cudaMemcpyDeviceToHost, s));
+  for (auto& sg : c->segs)
+    if (sg.bytes)
+      RFQ_CK(c, cudaMemcpyAsync((uint8_t*)c->h_out.p + sg.host_base, sg.d, sg.bytes,
+                                cudaMemcpyDeviceToHost, s));
   c->d2h_bytes = c->out_total;
-  if (n) {
+  if (c->host_tables) {
+    if (n) {
+      memcpy(c->h_out_off, c->r_off.data(), 8ull * n);
+      memcpy(c->h_out_len, c->r_len.data(), 8ull * n);
+      memcpy(c->h_status, c->r_status.data(), 4ull * n);
+      memcpy(c->h_rows, c->r_rows.data(), 4ull * n);
+      memcpy(c->h_cols, c->r_cols.data(), 4ull * n);
+      memcpy(c->h_attempt, c->r_attempt.data(), n);
+    }
+  } else if (n) {
     RFQ_CK(c, cudaMemcpyAsync(c->h_out_off, c->d_out_off, 8ull * n, cudaMemcpyDeviceToHost, s));
     RFQ_CK(c, cudaMemcpyAsync(c->h_out_len, c->d_out_len, 8ull * n, cudaMemcpyDeviceToHost, s));
     c->d2h_bytes += 16ull * n;

@@ -155,8 +155,6 @@ class Engine:
     def parse_csv_many(self, docs: Sequence[bytes], max_rows=1000) -> "list[str | None]":
         """raw_text per document; None where every (encoding, separator) attempt failed (the
         caller raises the reference's FileParsingError)."""
-        with self.lock:
-            pass
         r = self.csv_batch(docs, max_rows)
         out = []
         for d in range(r.n):

@@ -1,0 +1,99 @@
+"""GPU parity: CSV path vs the reference's committed outputs and vs the oracle (pandas), through
+the C ABI.  Bit-exact or it fails."""
+import base64
+import json
+from pathlib import Path
+
+import pytest
+
+from oracle import file_parser_oracle as O
+from tests import corpus
+
+pytestmark = pytest.mark.gpu
+G = Path(__file__).parent / "golden"
+
+# Python-int object column (value beyond uint64): reported as unsupported, never guessed
+UNSUPPORTED_GOLDENS = {"too_big"}
+
+
+@pytest.fixture(scope="module")
+def eng():
+    from replisense_rfq_b200 import Engine, build
+    build.build()
+    return Engine(0)
+
+
+def oracle(data, nrows=1000):
+    try:
+        return O.parse_csv_bytes(data, nrows)
+    except O.OracleParsingError:
+        return None
+
+
+def test_csv_reference_goldens(eng):
+    cases = [c for c in json.loads((G / "ref_csv.json").read_text())
+             if c["name"] not in UNSUPPORTED_GOLDENS]
+    docs = [base64.b64decode(c["data"]) for c in cases]
+    got = eng.parse_csv_many(docs, [c["nrows"] for c in cases])
+    bad = [c["name"] for c, g in zip(cases, got) if g != c.get("text")]
+    assert not bad, bad
+
+
+def test_csv_unsupported_is_loud(eng):
+    from replisense_rfq_b200 import EngineError
+    with pytest.raises(EngineError):
+        eng.parse_csv_many([b"p,q\n18446744073709551616,1\n1,2\n"], 1000)
+
+
+def test_csv_fuzz_batch(eng):
+    docs = [corpus.fuzz_csv(s) for s in range(30000, 31500)]
+    got = eng.parse_csv_many(docs, 1000)
+    bad = [30000 + i for i, (g, d) in enumerate(zip(got, docs)) if g != oracle(d)]
+    assert not bad, bad[:20]
+
+
+def test_csv_one_by_one_equals_batched(eng):
+    docs = [corpus.fuzz_csv(s) for s in range(40000, 40060)]
+    batched = eng.parse_csv_many(docs, 1000)
+    single = [eng.parse_csv_many([d], 1000)[0] for d in docs]
+    assert batched == single
+
+
+def test_csv_rfq_sizes(eng):
+    for n, cap in [(1, 1000), (7, 1000), (300, 1000), (2500, 1000), (2500, 10 ** 6), (70000, 10 ** 6)]:
+        d = corpus.rfq_csv(n, seed=n)
+        assert eng.parse_csv_many([d], cap)[0] == oracle(d, cap), (n, cap)
+
+
+def test_csv_low_memory_chunk_boundary(eng):
+    """A non-numeric token after the first buffer_lines rows: earlier chunks were already
+    converted ('1.50' prints 1.5), SURVEY.md App. C."""
+    for ncols, k in [(2, 300000), (8, 65536), (8, 65535), (16, 40000)]:
+        rows = ["1.50" + ",x" * (ncols - 1)] * (k + 3)
+        rows[k] = "abc" + ",x" * (ncols - 1)
+        d = (",".join("c%d" % i for i in range(ncols)) + "\n" + "\n".join(rows) + "\n").encode()
+        assert eng.parse_csv_many([d], 10 ** 7)[0] == oracle(d, 10 ** 7), (ncols, k)
+
+
+def test_csv_crlf_and_wide(eng):
+    d1 = corpus.rfq_csv(5000, seed=5, newline="\r\n")
+    wide = (",".join("c%d" % i for i in range(300)) + "\n" +
+            "\n".join(",".join(str((r * 7 + c) % 1000 / 4) for c in range(300)) for r in range(50)) + "\n").encode()
+    for d in (d1, wide):
+        assert eng.parse_csv_many([d], 10 ** 6)[0] == oracle(d, 10 ** 6)
+
+
+def test_csv_file_parser_api(eng, tmp_path):
+    from replisense_rfq_b200 import FileParser, FileParsingError
+    import asyncio
+    fp = FileParser(engine=eng)
+    p = tmp_path / "ok.csv"
+    data = corpus.rfq_csv(50, seed=9)
+    p.write_bytes(data)
+    res = asyncio.run(fp.parse_file_async(str(p)))
+    assert res["raw_text"] == oracle(data) and res["parsing_method"] == "async_csv"
+    assert res["source_file"] == "ok.csv" and res["file_size"] == len(data) and len(res["file_hash"]) == 32
+    bad = tmp_path / "bad.csv"
+    bad.write_bytes(b"a\n1\n2\n")
+    with pytest.raises(FileParsingError, match="Failed to parse bad.csv: CSV parsing failed: Unable to parse CSV"):
+        asyncio.run(fp.parse_file_async(str(bad)))
