@@ -1,0 +1,288 @@
+"""bench.py — BASELINE.json's metric on config C2 (synthetic RFQ CSV, 1M rows x 8 cols, 1 B200 per
+rank): parsed input MB/s (+ cells/s) through the CSV hot path, beside the reference's CPU path.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--rows R]
+
+One step = one pass of the whole CSV path (tokenise, type, dropna/fillna, to_string) over one
+1M-row document per rank.  `value` = device-resident throughput (input already in HBM, CUDA
+events around every step, L2 flushed between steps); `e2e` = the same through the C-ABI call
+rfq_csv_parse with HOST (pinned) buffers: H2D + kernels + D2H inside the timed region.
+N > 1: one process per GPU (torchrun), independent documents per rank, no data-path collective
+(weak scaling); time = max over ranks.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "csv_parsed_input_MB_per_s"
+UNIT = "MB/s"
+
+
+def peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([x.strip() for x in out.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        sm, mx, reasons = [], 0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = max(mx, float(r[1]))
+            except Exception:
+                continue
+            for n, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_doc(rows: int, seed: int) -> bytes:
+    from tests import corpus
+    return corpus.rfq_csv(rows, seed=seed)
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's own CPU path (oracle port of _parse_csv_sync over the
+    same pandas) on all host cores, a bounded sample of the same workload per step."""
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    cores = os.cpu_count() or 1
+    sample_rows = max(1000, min(args.rows, args.ref_sample_rows))
+    doc = make_doc(sample_rows, 0)
+    with mp.get_context("fork").Pool(cores) as pool:
+        for _ in range(args.warmup):
+            pool.map(_ref_one, [(doc, sample_rows)] * cores)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            pool.map(_ref_one, [(doc, sample_rows)] * cores)
+        dt = time.perf_counter() - t0
+    mb = len(doc) * cores * args.steps / 1e6
+    val = mb / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic", "config": config_dict(args, sample_rows),
+        "cells_per_s": sample_rows * 8 * cores * args.steps / dt,
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{cores} processes x one {sample_rows}-row slice of the C2 CSV per step "
+                                   "(oracle port of FileParser._parse_csv_sync over pandas)"},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def _ref_one(a):
+    from oracle import file_parser_oracle as O
+    doc, rows = a
+    return len(O.parse_csv_bytes(doc, rows))
+
+
+def config_dict(args, rows):
+    return {"workload": f"C2: synthetic RFQ CSV, {rows} rows x 8 cols (part_number, description[quoted, "
+                        "embedded , and \"\"], quantity, target_price, currency, delivery_date, supplier, "
+                        "notes[80% empty]), one document per GPU, FileParser(max_file_size_mb=4096, "
+                        f"max_excel_rows={rows})",
+            "rows": rows, "cols": 8, "l2": "flushed between timed steps (256 MiB device write)",
+            "parallelism": f"documents sharded across {args.gpus} GPU(s), no collective"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rows", type=int, default=1_000_000)
+    ap.add_argument("--ref-sample-rows", type=int, default=20_000)
+    ap.add_argument("--cpu-sample-rows", type=int, default=100_000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from replisense_rfq_b200 import Engine, build
+    from replisense_rfq_b200.engine import PinnedArena
+
+    if rank == 0 or world == 1:
+        build.build()
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist.barrier()
+    build.build()
+    eng = Engine(local_rank)
+    eng.set_stream(torch.cuda.current_stream().cuda_stream)
+
+    doc = make_doc(args.rows, seed=rank)
+    nbytes = len(doc)
+    arena = PinnedArena(eng, nbytes + 4096)
+    offsets, lengths, _ = arena.pack([doc])
+    mr = np.array([args.rows], dtype=np.int64)
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- parity gate on a slice before any timing counts
+    from oracle import file_parser_oracle as O
+    if rank == 0:
+        small = make_doc(2000, seed=rank)
+        assert eng.parse_csv_many([small], 2000)[0] == O.parse_csv_bytes(small, 2000), "parity gate"
+
+    # ---- device-resident: stage once, time K runs with CUDA events, L2 flushed between steps
+    eng.stage(arena, offsets, lengths)
+    for _ in range(args.warmup):
+        eng.csv_run(1, mr)
+    res = eng.fetch()
+    assert int(res.status[0]) == 0
+    out_bytes = int(res.lengths[0])
+    n_rows_out = int(res.rows[0])
+    eng.set_profile(True)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier()
+    l0 = eng.launch_count()
+    step_ms = []
+    prof_acc = {}
+    for _ in range(args.steps):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        eng.csv_run(1, mr)
+        e1.record()
+        torch.cuda.synchronize()
+        step_ms.append(e0.elapsed_time(e1))
+        eng.lib.rfq_fetch(eng.ctx)  # finalises the per-kernel profile of this run (outside the timing)
+        for name, ms in eng.profile():
+            prof_acc[name] = prof_acc.get(name, 0.0) + ms
+    launches = eng.launch_count() - l0
+    barrier()
+    sampler.stop_flag = True
+    sampler.join()
+    eng.set_profile(False)
+    t_dev = sum(step_ms) / 1e3
+    tt = torch.tensor([t_dev], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    t_dev = float(tt.item())
+
+    # ---- end to end through the C-ABI call with host (pinned) buffers
+    for _ in range(2):
+        eng.csv_parse_arena(arena, offsets, lengths, mr)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        r = eng.csv_parse_arena(arena, offsets, lengths, mr)
+    torch.cuda.synchronize()
+    t_e2e = time.perf_counter() - t0
+    te = torch.tensor([t_e2e], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    t_e2e = float(te.item())
+    # and once more all the way to a Python str (what FileParser._parse_csv_sync returns)
+    t0 = time.perf_counter()
+    txt = eng.csv_parse_arena(arena, offsets, lengths, mr).doc_str(0)
+    t_str = time.perf_counter() - t0
+    assert len(txt.encode("utf-8")) == out_bytes
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+    total_mb = nbytes * world * args.steps / 1e6
+    value = total_mb / t_dev
+    hbm, hbm_src = peaks()
+    # dominant kernel (live CUDA-event timing on the launching stream, averaged per launch)
+    kern = {k: v / args.steps for k, v in prof_acc.items() if k.endswith("_kernel")}
+    dom = max(kern, key=kern.get)
+    alg = {"csv_emit_kernel": nbytes + out_bytes, "csv_measure_kernel": nbytes,
+           "csv_classify_kernel": nbytes, "csv_tilefn_kernel": nbytes, "csv_count_kernel": nbytes,
+           "csv_index_kernel": nbytes}.get(dom, nbytes)
+    achieved = alg / (kern[dom] / 1e3) / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": t_dev / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": config_dict(args, args.rows),
+        "cells_per_s": args.rows * 8 * world * args.steps / t_dev,
+        "input_bytes_per_doc": nbytes, "output_bytes_per_doc": out_bytes, "rows_out": n_rows_out,
+        "pipeline_algorithmic_GBps": (nbytes + out_bytes) * world * args.steps / t_dev / 1e9,
+        "pipeline_frac_of_hbm": (nbytes + out_bytes) * args.steps / t_dev / 1e9 / hbm,
+        "e2e": {"value": total_mb / t_e2e, "unit": UNIT, "h2d_bytes_per_step": nbytes,
+                "d2h_bytes_per_step": out_bytes + 64, "ms_per_step": t_e2e / args.steps * 1e3,
+                "to_python_str_ms": t_str * 1e3},
+        "gpu_launches": launches,
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "unit": "GB/s",
+                     "frac": achieved / hbm, "traffic": None, "peak_source": hbm_src,
+                     "algorithmic_bytes_per_launch": alg, "kernel_ms": kern[dom]},
+        "kernel_ms_per_step": {k: round(v / args.steps, 4) for k, v in sorted(prof_acc.items(), key=lambda x: -x[1])},
+        "clocks": sampler.summary(),
+    }
+    if not args.no_cpu_baseline:
+        rows = min(args.cpu_sample_rows, args.rows)
+        sample = make_doc(rows, seed=0)
+        t0 = time.perf_counter()
+        O.parse_csv_bytes(sample, rows)
+        dt = time.perf_counter() - t0
+        line["cpu_baseline"] = {"value": len(sample) / 1e6 / dt, "unit": UNIT, "cores": 1, "kind": "port",
+                                "sample": f"first {rows} rows of the C2 CSV through the oracle port of "
+                                          "FileParser._parse_csv_sync (pandas read_csv + to_string), "
+                                          f"{dt:.2f} s on one host core of {os.cpu_count()}",
+                                "cells_per_s": rows * 8 / dt}
+    print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -91,7 +91,6 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
   sa.tile_base = (const uint32_t*)(d_up + o_tb);
   const uint32_t* d_mr = (const uint32_t*)(d_up + o_mr);
   RFQ_CK(c, cudaMemsetAsync(sa.doc_final, 0, 4ull * (m + 1), s));
-  c->prof.mark("csv_scan_count", s);
   csv_scan_count(sa, s);
   RFQ_CK(c, c->h_down.reserve(sizeof(DocShape) * (m + 1) + 32ull * (m + 1) + 4096));
   uint32_t* h_tot = (uint32_t*)c->h_down.p;
@@ -111,7 +110,6 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
   sa.rec_fend = c->pool.alloc<uint32_t>((size_t)n_slots + 1);
   sa.rec_start = c->pool.alloc<uint32_t>((size_t)n_slots + 1);
   if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
-  c->prof.mark("csv_scan_index", s);
   csv_scan_index(sa, s);
   csv_doc_shape(sa, d_mr, d_shape, n_slots, s);
   DocShape* h_shape = (DocShape*)((uint8_t*)c->h_down.p + 256);
@@ -221,9 +219,7 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
   RFQ_CK(c, cudaMemsetAsync(ta.doc_flags, 0, 4ull * (m + 1), s));
   RFQ_CK(c, cudaMemsetAsync(ta.doc_linew, 0, 4ull * (m + 1), s));
   // ---- 5. classify, decide, measure, layout, sizes
-  c->prof.mark("csv_classify", s);
   csv_table_classify(ta, s);
-  c->prof.mark("csv_measure+layout", s);
   csv_table_measure(ta, s);
   uint8_t* hd = (uint8_t*)c->h_down.p;
   unsigned long long* h_total = (unsigned long long*)hd;
@@ -241,9 +237,8 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
   // ---- 6. emit
   uint8_t* d_text = c->pool.alloc<uint8_t>(total + 64);
   if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
-  c->prof.mark("csv_emit", s);
   if (total) csv_table_emit(ta, d_text, s);
-  c->prof.mark("csv_attempt_end", s);
+  c->prof.mark("host+sync", s);
   RFQ_CK(c, cudaGetLastError());
   const uint64_t host_base = c->out_total;
   c->segs.push_back({d_text, total, host_base});
@@ -273,6 +268,8 @@ extern "C" int rfq_csv_run(rfq_ctx* c, const int64_t* max_rows_in) {
   cudaStream_t s = c->stream;
   const uint32_t n = c->n_docs;
   c->prof.begin();
+  g_prof = &c->prof;
+  struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
   RFQ_CK(c, cudaEventRecord(c->ev0, s));
   c->pool.reset();
   c->segs.clear();

@@ -255,26 +255,34 @@ __global__ void __launch_bounds__(256) csv_shape_kernel(ScanArgs a, const uint32
 void csv_scan_count(const ScanArgs& a, cudaStream_t s) {
   if (a.n_tiles == 0) return;
   uint32_t nb = (a.n_tiles + 7) / 8;
+  prof_mark("csv_tilefn_kernel", s);
   RFQ_LAUNCH(csv_tilefn_kernel, nb, 256, 0, s, a);
+  prof_mark("scan(tile_fn)", s);
   exclusive_scan<FnCompose>(a.tile_fn, a.tile_fn_pre, a.n_tiles, a.scan_tmp, nullptr, s);
   cudaMemsetAsync(a.tile_nf + a.n_tiles, 0, 4, s);
   cudaMemsetAsync(a.tile_nl + a.n_tiles, 0, 4, s);
+  prof_mark("csv_count_kernel", s);
   RFQ_LAUNCH(csv_count_kernel, nb, 256, 0, s, a);
+  prof_mark("scan(counts)", s);
   exclusive_scan<SumU32>(a.tile_nf, a.tile_nf_pre, a.n_tiles + 1, a.scan_tmp, nullptr, s);
   exclusive_scan<SumU32>(a.tile_nl, a.tile_nl_pre, a.n_tiles + 1, a.scan_tmp, nullptr, s);
+  prof_mark("host+sync", s);
 }
 
 void csv_scan_index(const ScanArgs& a, cudaStream_t s) {
   if (a.n_tiles == 0) return;
+  prof_mark("csv_index_kernel", s);
   RFQ_LAUNCH(csv_index_kernel, (a.n_tiles + 7) / 8, 256, 0, s, a);
 }
 
 void csv_doc_shape(const ScanArgs& a, const uint32_t* max_rows32, DocShape* shape, uint32_t n_slots,
                    cudaStream_t s) {
   if (a.n_docs == 0) return;
+  prof_mark("csv_shape_kernels", s);
   RFQ_LAUNCH(csv_shape_init_kernel, (a.n_docs + 255) / 256, 256, 0, s, a, shape);
   if (n_slots)
     RFQ_LAUNCH(csv_shape_kernel, (n_slots + 255) / 256, 256, 0, s, a, max_rows32, shape, n_slots);
+  prof_mark("host+sync", s);
 }
 
 }  // namespace rfq

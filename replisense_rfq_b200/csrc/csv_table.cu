@@ -337,25 +337,33 @@ static int table_grid(uint32_t n_items) {
 }
 
 void csv_table_classify(const TableArgs& a, cudaStream_t s) {
+  prof_mark("csv_stat_init_kernel", s);
   if (a.n_stat)
     RFQ_LAUNCH(csv_stat_init_kernel, (a.n_stat + 255) / 256, 256, 0, s, (ChunkStat*)a.stat,
                (ChunkMeasure*)a.meas, a.n_stat);
+  prof_mark("csv_classify_kernel", s);
   if (a.n_items) RFQ_LAUNCH(csv_classify_kernel, table_grid(a.n_items), 256, 0, s, a);
 }
 
 void csv_table_measure(const TableArgs& a, cudaStream_t s) {
   if (a.n_docs == 0) return;
+  prof_mark("csv_decide_kernel", s);
   RFQ_LAUNCH(csv_decide_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
+  prof_mark("csv_measure_kernel", s);
   if (a.n_items) RFQ_LAUNCH(csv_measure_kernel, table_grid(a.n_items), 256, 0, s, a);
+  prof_mark("csv_layout+rowbytes+scan", s);
   RFQ_LAUNCH(csv_layout_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
   RFQ_LAUNCH(csv_rowbytes_kernel, (a.n_slots + 1 + 255) / 256, 256, 0, s, a);
   exclusive_scan<SumU64>(a.row_bytes, a.row_off, a.n_slots + 1, a.scan_tmp64, nullptr, s);
   RFQ_LAUNCH(csv_docout_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
+  prof_mark("host+sync", s);
 }
 
 void csv_table_emit(const TableArgs& a, uint8_t* out, cudaStream_t s) {
   if (a.n_docs == 0) return;
+  prof_mark("csv_header_emit_kernel", s);
   RFQ_LAUNCH(csv_header_emit_kernel, (a.n_docs + 7) / 8, 256, 0, s, a, out);
+  prof_mark("csv_emit_kernel", s);
   if (a.n_items) RFQ_LAUNCH(csv_emit_kernel, table_grid(a.n_items), 256, 0, s, a, out);
 }
 

@@ -42,4 +42,9 @@ struct Prof {
   ~Prof() { for (auto e : ev) cudaEventDestroy(e); }
 };
 
+// profiler of the run in progress on this thread (set by the C-ABI layer), so kernel files can
+// mark individual launches
+extern thread_local Prof* g_prof;
+inline void prof_mark(const char* name, cudaStream_t s) { if (g_prof) g_prof->mark(name, s); }
+
 }  // namespace rfq

@@ -12,6 +12,7 @@
 
 namespace rfq {
 std::atomic<uint64_t> g_launch_count{0};
+thread_local Prof* g_prof = nullptr;
 }
 
 using namespace rfq;

@@ -167,6 +167,41 @@ class Engine:
                 raise EngineError(f"document {d}: unsupported construct on the GPU path (status {st})")
         return out
 
+    # -- pre-packed pinned arena (no Python-side copies): what a high-throughput caller uses
+    def _mr(self, n, max_rows):
+        if np.isscalar(max_rows):
+            return np.full(n, int(max_rows), dtype=np.int64)
+        return np.ascontiguousarray(max_rows, dtype=np.int64)
+
+    def csv_parse_arena(self, arena: PinnedArena, offsets, lengths, max_rows=1000) -> BatchResult:
+        mr = self._mr(len(offsets), max_rows)
+        with self.lock:
+            self._check(self.lib.rfq_csv_parse(self.ctx, arena.ptr, offsets.ctypes.data,
+                                               lengths.ctypes.data, len(offsets), mr.ctypes.data),
+                        "rfq_csv_parse")
+            return BatchResult(self)
+
+    def text_parse_arena(self, arena: PinnedArena, offsets, lengths) -> BatchResult:
+        with self.lock:
+            self._check(self.lib.rfq_text_parse(self.ctx, arena.ptr, offsets.ctypes.data,
+                                                lengths.ctypes.data, len(offsets)), "rfq_text_parse")
+            return BatchResult(self)
+
+    def csv_run(self, n, max_rows=1000):
+        """Kernels only, on the staged (device-resident) batch."""
+        mr = self._mr(n, max_rows)
+        self._check(self.lib.rfq_csv_run(self.ctx, mr.ctypes.data), "rfq_csv_run")
+
+    def text_run(self):
+        self._check(self.lib.rfq_text_run(self.ctx), "rfq_text_run")
+
+    def fetch(self) -> BatchResult:
+        self._check(self.lib.rfq_fetch(self.ctx), "rfq_fetch")
+        return BatchResult(self)
+
+    def set_profile(self, on: bool):
+        self.lib.rfq_set_profile(self.ctx, int(on))
+
     # -- measurement
     def last_run_ms(self) -> float:
         return float(self.lib.rfq_last_run_ms(self.ctx))
