@@ -155,7 +155,12 @@ def main():
         dist.barrier()
     build.build()
     eng = Engine(local_rank)
-    eng.set_stream(torch.cuda.current_stream().cuda_stream)
+    # the kernels and the timing events must share ONE stream: a non-default torch stream (the
+    # legacy default stream has handle 0, which rfq_set_stream reads as "use the ctx's own")
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
+    eng.set_stream(stream.cuda_stream)
 
     doc = make_doc(args.rows, seed=rank)
     nbytes = len(doc)
