@@ -29,6 +29,7 @@ extern "C" {
 #define RFQ_ERR_CUDA (-1)
 #define RFQ_ERR_ARG (-2)
 #define RFQ_ERR_STATE (-3)
+#define RFQ_ERR_TOO_LARGE (-4)
 
 /* per-document status codes (rfq_out_status) */
 #define RFQ_DOC_OK 0
@@ -102,6 +103,36 @@ int rfq_set_profile(rfq_ctx* ctx, int on);
 int rfq_profile_count(const rfq_ctx* ctx);
 const char* rfq_profile_name(const rfq_ctx* ctx, int i);
 float rfq_profile_ms(const rfq_ctx* ctx, int i);
+
+/* ---- text path without any GPU memory allocation -------------------------------------------
+ * No counterpart in the reference: added for embedders that must not allocate on the GPU — a
+ * plugin living inside another process's memory budget (a serving stack whose allocator owns the
+ * whole device), a handler on a latency-critical path where cudaMalloc's implicit device-wide
+ * synchronisation is unacceptable, or a host that froze its memory map after start-up.
+ *
+ * Same result as the text path above (UTF-8 decode errors='ignore', universal newlines,
+ * str.strip(); app/file_parser.py:143-148) for ONE document of at most RFQ_NOALLOC_MAX_BYTES
+ * bytes; larger input is refused with RFQ_ERR_TOO_LARGE (and a message on stderr).  All scratch
+ * lives in a fixed RFQ_NOALLOC_SCRATCH_BYTES array inside the library image, so every GPU that
+ * loads the library carries that much until the process exits, and the call performs no
+ * cudaMalloc / cudaFree / allocating library call of any kind.
+ *
+ *   device      CUDA device ordinal the pointers belong to
+ *   d_in        DEVICE pointer, 16-byte aligned, readable up to len rounded up to 16 bytes
+ *   len         document bytes
+ *   d_out       DEVICE pointer with room for len bytes (the result is never longer than the input)
+ *   d_out_len   DEVICE pointer, 8-byte aligned: receives the number of bytes written to d_out
+ *   cuda_stream stream to run on (NULL = the default stream); the call only enqueues work —
+ *               synchronise the stream before reading d_out / d_out_len
+ *
+ * The first call on each device also resolves the device address of the scratch array (a
+ * one-off, host-side set-up step), so make that first call before starting any stream capture.
+ * Every call on a device shares the one array: calls whose GPU work can overlap (different
+ * streams, or different threads without ordering between them) race on it — serialise them. */
+#define RFQ_NOALLOC_MAX_BYTES (4u << 20)
+#define RFQ_NOALLOC_SCRATCH_BYTES (96u << 10)
+int rfq_text_normalise_noalloc(int device, const uint8_t* d_in, uint64_t len, uint8_t* d_out,
+                               uint64_t* d_out_len, void* cuda_stream);
 
 #ifdef __cplusplus
 }

@@ -49,7 +49,11 @@ SIGNATURES = {
     "rfq_profile_count": (C.c_int, [C.c_void_p]),
     "rfq_profile_name": (C.c_char_p, [C.c_void_p, C.c_int]),
     "rfq_profile_ms": (C.c_float, [C.c_void_p, C.c_int]),
+    "rfq_text_normalise_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
+                                             C.c_void_p]),
 }
+NOALLOC_MAX_BYTES = 4 << 20
+ERR_TOO_LARGE = -4
 
 
 def load():
