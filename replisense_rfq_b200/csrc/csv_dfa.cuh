@@ -106,6 +106,12 @@ RFQ_HD uint32_t csv_class_fn(int cl) {
   for (int s = 0; s < 8; ++s) f |= (uint32_t)csv_next(s, cl) << (4 * s);
   return f;
 }
+// events of a class for every state, 4 bits per state
+RFQ_HD uint32_t csv_class_ev(int cl) {
+  uint32_t f = 0;
+  for (int s = 0; s < 8; ++s) f |= (uint32_t)csv_events(s, cl) << (4 * s);
+  return f;
+}
 #define RFQ_FN_IDENTITY 0x76543210u
 
 // (a then b)(s) = b(a(s))

@@ -78,8 +78,11 @@ __device__ __forceinline__ bool doc_has_bom(const uint8_t* __restrict__ doc, uin
 }
 
 #define RFQ_INIT_CLASS_FN()                                         \
-  __shared__ uint32_t class_fn[8];                                  \
-  if (threadIdx.x < 8) class_fn[threadIdx.x] = threadIdx.x < N_CLASSES ? csv_class_fn(threadIdx.x) : RFQ_FN_IDENTITY; \
+  __shared__ uint32_t class_fn[8], class_ev[8];                     \
+  if (threadIdx.x < 8) {                                            \
+    class_fn[threadIdx.x] = threadIdx.x < N_CLASSES ? csv_class_fn(threadIdx.x) : RFQ_FN_IDENTITY; \
+    class_ev[threadIdx.x] = threadIdx.x < N_CLASSES ? csv_class_ev(threadIdx.x) : 0u;              \
+  }                                                                 \
   __syncthreads();
 
 // ---- pass 1: transition function of every tile ------------------------------------------------
@@ -104,14 +107,17 @@ __global__ void __launch_bounds__(256) csv_tilefn_kernel(ScanArgs a) {
 }
 
 // walk 16 bytes from a known state; calls ev(k, events, state_before) for bytes with events
+// (table driven: next state and events are nibble look-ups in shared memory, no branches)
 template <class F>
-__device__ __forceinline__ int lane_walk(unsigned long long cls, int st, F&& ev) {
+__device__ __forceinline__ int lane_walk(unsigned long long cls, int st,
+                                         const uint32_t* __restrict__ class_fn,
+                                         const uint32_t* __restrict__ class_ev, F&& ev) {
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
-    int c = (int)((cls >> (4 * k)) & 0xFu);
-    int e = csv_events(st, c);
+    uint32_t c = (uint32_t)((cls >> (4 * k)) & 0xFu);
+    int e = (int)((class_ev[c] >> (4 * st)) & 0xFu);
     if (e) ev(k, e, st);
-    st = csv_next(st, c);
+    st = (int)((class_fn[c] >> (4 * st)) & 0xFu);
   }
   return st;
 }
@@ -150,13 +156,13 @@ __global__ void __launch_bounds__(256) csv_count_kernel(ScanArgs a) {
   uint32_t nf = 0, nl = 0;
   uint32_t eof_k = (len >= base && len < base + 16) ? len - base : 0xFFu;
   int final_state = -1;
-  lane_walk(lb.cls, st, [&](int k, int e, int sb) {
+  lane_walk(lb.cls, st, class_fn, class_ev, [&](int k, int e, int sb) {
     nf += (e & EV_FIELD_END) ? 1u : 0u;
     nl += (e & EV_LINE_END) ? 1u : 0u;
   });
   if (eof_k != 0xFFu) {  // state just before the virtual LF
     int s2 = st;
-    for (uint32_t k = 0; k < eof_k; ++k) s2 = csv_next(s2, (int)((lb.cls >> (4 * k)) & 0xFu));
+    for (uint32_t k = 0; k < eof_k; ++k) s2 = (int)((class_fn[(lb.cls >> (4 * k)) & 0xFu] >> (4 * s2)) & 0xFu);
     final_state = s2;
   }
 #pragma unroll
@@ -170,6 +176,7 @@ __global__ void __launch_bounds__(256) csv_count_kernel(ScanArgs a) {
 
 // ---- pass 3: write field ends / record ends / record starts -----------------------------------
 __global__ void __launch_bounds__(256) csv_index_kernel(ScanArgs a) {
+  RFQ_INIT_CLASS_FN();
   uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
   int lane = threadIdx.x & 31;
   if (t >= a.n_tiles) return;
@@ -185,7 +192,7 @@ __global__ void __launch_bounds__(256) csv_index_kernel(ScanArgs a) {
   int st = (int)(((b0 >> lane) & 1u) | (((b1 >> lane) & 1u) << 1) | (((b2 >> lane) & 1u) << 2));
   // this lane's counts, then exclusive prefix inside the warp
   uint32_t nf = 0, nl = 0;
-  lane_walk(lb.cls, st, [&](int k, int e, int sb) {
+  lane_walk(lb.cls, st, class_fn, class_ev, [&](int k, int e, int sb) {
     nf += (e & EV_FIELD_END) ? 1u : 0u;
     nl += (e & EV_LINE_END) ? 1u : 0u;
   });
@@ -199,7 +206,7 @@ __global__ void __launch_bounds__(256) csv_index_kernel(ScanArgs a) {
   uint32_t g = a.tile_nf_pre[t] + pf - nf;          // global index of this lane's first field end
   uint32_t r = a.tile_nl_pre[t] + pl - nl + d;      // record slot currently open at this lane
   uint32_t doc_begin = has_bom ? 3u : 0u;
-  lane_walk(lb.cls, st, [&](int k, int e, int sb) {
+  lane_walk(lb.cls, st, class_fn, class_ev, [&](int k, int e, int sb) {
     uint32_t pos = base + k;
     if (e & EV_REC_START) a.rec_start[r] = pos;
     if (e & EV_REC_START_WS) {
@@ -248,7 +255,7 @@ __global__ void __launch_bounds__(256) csv_shape_kernel(ScanArgs a, const uint32
   uint32_t nf = a.rec_fend[slot] - fbeg;
   if (L == 0) shape[d].hdr_nf = nf;
   else if (L == 1) shape[d].first_nf = nf;
-  else atomicMax(&shape[d].max_nf, nf);
+  else if (nf > shape[d].max_nf) atomicMax(&shape[d].max_nf, nf);  // read first: rows rarely differ
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -248,7 +248,78 @@ __global__ void __launch_bounds__(128) csv_docout_kernel(TableArgs a) {
 }
 
 // ---- sweep 3: emit -------------------------------------------------------------------------------
+// A work item's rows are one contiguous byte range of the output.  The CTA builds that range in
+// shared memory (pre-filled with the padding blanks, so a cell only writes its own characters),
+// then streams it out with aligned 16-byte stores.  Ranges that do not fit (very long cells)
+// take the direct path: same formatting, byte stores to global memory.
+#define RFQ_EMIT_SMEM (80u << 10)
+
+// number -> text in a small local buffer; returns length, or -1 when the value needs the
+// big-integer path (|v| >= 2^63 printed in fixed notation)
+__device__ __forceinline__ int format_number(const CellSrc& s, int ct, int kind, int dec,
+                                             const TextInfo& t, uint8_t* buf) {
+  switch (kind) {
+    case PR_BOOL: {
+      const char* w = bool_token(t.nbytes, t.first8) == 1 ? "True" : "False";
+      int k = 0;
+      while (w[k]) { buf[k] = (uint8_t)w[k]; ++k; }
+      return k;
+    }
+    case PR_INT: {
+      int64_t iv = 0; cell_int64(s, &iv);
+      int n = int64_len(iv);
+      uint64_t mag = iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv;
+      write_u64_rev(mag, buf + n);
+      if (iv < 0) buf[0] = '-';
+      return n;
+    }
+    case PR_UINT: {
+      UintTok u; cell_uint64(s, &u);
+      int n = ndigits_u64(u.v);
+      write_u64_rev(u.v, buf + n);
+      return n;
+    }
+    case PR_FIXED: case PR_OBJFLOAT: {
+      double v = cell_as_double(s, ct);
+      Fixed6 f = fixed6(v);
+      if (f.big) return -1;
+      return fixed_write(f, v, kind == PR_FIXED ? dec : objfloat_dec(f), kind == PR_OBJFLOAT, buf);
+    }
+    case PR_SCI: return sci_write(sci7(cell_as_double(s, ct)), buf);
+    default: return 0;
+  }
+}
+
+// writes the cell right-justified into its field; `field` points at the first byte of the
+// column's field inside the row; `fill` = also write the padding blanks (direct path)
+__device__ __forceinline__ void emit_cell(const CellSrc& src, int ct, int kind, int dec,
+                                          uint32_t width, uint8_t* field, bool fill) {
+  TextInfo t = cell_text(src);
+  bool na = is_na_token(t.nbytes, t.first8) && ct != CT_STRNF;
+  if (na) { if (fill) for (uint32_t q = 0; q < width; ++q) field[q] = ' '; return; }
+  if (kind == PR_STR) {
+    uint32_t ncp = t.ncp + t.nesc, pad = width - ncp;
+    if (fill) for (uint32_t q = 0; q < pad; ++q) field[q] = ' ';
+    print_cell(src, ct, kind, dec, field + pad);
+    return;
+  }
+  uint8_t buf[40];
+  int n = format_number(src, ct, kind, dec, t, buf);
+  if (n < 0) {  // rare: huge value in fixed notation
+    uint32_t ncp, nb;
+    printed_size(src, ct, kind, dec, &ncp, &nb);
+    uint32_t pad = width - ncp;
+    if (fill) for (uint32_t q = 0; q < pad; ++q) field[q] = ' ';
+    print_cell(src, ct, kind, dec, field + pad);
+    return;
+  }
+  uint32_t pad = width - (uint32_t)n;
+  if (fill) for (uint32_t q = 0; q < pad; ++q) field[q] = ' ';
+  for (int q = 0; q < n; ++q) field[pad + q] = buf[q];
+}
+
 __global__ void __launch_bounds__(256) csv_emit_kernel(TableArgs a, uint8_t* __restrict__ out) {
+  extern __shared__ __align__(16) uint8_t s_buf[];
   __shared__ uint32_t s_doc;
   const ColOut* col = (const ColOut*)a.col;
   for (uint32_t item = blockIdx.x; item < a.n_items; item += gridDim.x) {
@@ -256,11 +327,22 @@ __global__ void __launch_bounds__(256) csv_emit_kernel(TableArgs a, uint8_t* __r
     const TDoc D = a.docs[ic.d];
     if (a.doc_flags[ic.d] == 0 && a.n_keep[ic.d] != 0) {
       uint32_t W = D.W;
+      uint32_t slot0 = D.r0 + 1 + ic.row0;
+      unsigned long long g0 = a.row_off[slot0], g1 = a.row_off[slot0 + ic.nrows];
+      unsigned long long nbytes = g1 - g0;
+      uint32_t mis = (uint32_t)((uintptr_t)(out + g0) & 15u);  // keep smem and global co-aligned
+      bool staged = nbytes + mis + 16 <= RFQ_EMIT_SMEM;
+      if (staged) {
+        uint32_t nvec = (uint32_t)((mis + nbytes + 15) >> 4);
+        uint4 sp = make_uint4(0x20202020u, 0x20202020u, 0x20202020u, 0x20202020u);
+        for (uint32_t i = threadIdx.x; i < nvec; i += blockDim.x) reinterpret_cast<uint4*>(s_buf)[i] = sp;
+        __syncthreads();
+      }
+      uint8_t* base = staged ? s_buf + mis : out + g0;   // base[x] <-> out[g0 + x]
       uint32_t ncell = ic.nrows * W;
       for (uint32_t idx = threadIdx.x; idx < ncell; idx += blockDim.x) {
         uint32_t rr = idx / W, c = idx - rr * W;
-        uint32_t row = ic.row0 + rr;
-        uint32_t slot = D.r0 + 1 + row;
+        uint32_t slot = slot0 + rr;
         if (c < D.lead || !row_kept(a, D, slot, ic.chunk)) continue;
         uint32_t j = c - D.lead;
         ColOut co = col[D.col_base + j];
@@ -268,8 +350,6 @@ __global__ void __launch_bounds__(256) csv_emit_kernel(TableArgs a, uint8_t* __r
         int ct = ctrow[c];
         int kind = print_kind(co.cls, ct, co.sci != 0);
         CellSrc src = fetch_cell(a, D, slot, c);
-        uint32_t ncp, nb;
-        printed_size(src, ct, kind, co.dec, &ncp, &nb);
         uint32_t xb = 0;  // extra bytes of the columns to the left (rows with non-ASCII text only)
         if (j && __ldg(a.row_extra + slot)) {
           for (uint32_t c2 = D.lead; c2 < c; ++c2) {
@@ -282,12 +362,23 @@ __global__ void __launch_bounds__(256) csv_emit_kernel(TableArgs a, uint8_t* __r
             xb += nb2 - cp2;
           }
         }
-        uint8_t* p = out + a.row_off[slot];
+        uint8_t* p = base + (a.row_off[slot] - g0);
         if (j == 0) { *p = '\n'; p += 1; }
-        else { p += co.cp_off + xb; *p = ' '; p += 1; }
-        uint32_t pad = co.width - ncp;
-        for (uint32_t q = 0; q < pad; ++q) p[q] = ' ';
-        print_cell(src, ct, kind, co.dec, p + pad);
+        else { p += co.cp_off + xb; if (!staged) *p = ' '; p += 1; }
+        emit_cell(src, ct, kind, co.dec, co.width, p, !staged);
+      }
+      if (staged) {
+        __syncthreads();
+        // head bytes up to the first 16-byte boundary, aligned body, tail bytes
+        uint8_t* g = out + g0;
+        uint32_t head = mis ? min((unsigned long long)(16 - mis), nbytes) : 0u;
+        if (threadIdx.x < head) g[threadIdx.x] = s_buf[mis + threadIdx.x];
+        unsigned long long body = (nbytes - head) >> 4;
+        const uint4* sv = reinterpret_cast<const uint4*>(s_buf + mis + head);
+        uint4* gv = reinterpret_cast<uint4*>(g + head);
+        for (unsigned long long i = threadIdx.x; i < body; i += blockDim.x) gv[i] = sv[i];
+        uint32_t tail = (uint32_t)((nbytes - head) & 15u);
+        if (threadIdx.x < tail) g[head + body * 16 + threadIdx.x] = s_buf[mis + head + body * 16 + threadIdx.x];
       }
     }
     __syncthreads();
@@ -364,7 +455,12 @@ void csv_table_emit(const TableArgs& a, uint8_t* out, cudaStream_t s) {
   prof_mark("csv_header_emit_kernel", s);
   RFQ_LAUNCH(csv_header_emit_kernel, (a.n_docs + 7) / 8, 256, 0, s, a, out);
   prof_mark("csv_emit_kernel", s);
-  if (a.n_items) RFQ_LAUNCH(csv_emit_kernel, table_grid(a.n_items), 256, 0, s, a, out);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(csv_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, RFQ_EMIT_SMEM);
+    attr_set = true;
+  }
+  if (a.n_items) RFQ_LAUNCH(csv_emit_kernel, table_grid(a.n_items), 256, RFQ_EMIT_SMEM, s, a, out);
 }
 
 }  // namespace rfq
