@@ -3,8 +3,10 @@
 // `dropna(how='all').fillna('')` and `to_string(index=False)` (app/file_parser.py:301-305).
 //
 // Work item = a block of `rb` consecutive data rows of one document that never crosses a
-// low_memory chunk boundary; a CTA takes items grid-stride, one thread per cell (adjacent lanes
-// = adjacent cells, so token bytes are read nearly coalesced).  Column statistics are reduced in
+// low_memory chunk boundary; a CTA takes items grid-stride, one thread per cell; a warp works on
+// consecutive rows of ONE column, so its lanes run the same parser on tokens of similar length
+// (mixing columns in a warp left 6 of 32 lanes active: profiles/r01_emit_v1_*); the item's bytes
+// are shared by its warps through L1.  Column statistics are reduced in
 // shared memory per item and merged into global memory with one atomic per column per item.
 // Three sweeps over the cells: classify -> (decide) -> measure -> (layout, row offsets) -> emit.
 // Tokens are re-parsed in each sweep instead of being materialised: the bytes stay in L2 and a
@@ -74,7 +76,7 @@ __global__ void __launch_bounds__(256) csv_classify_kernel(TableArgs a) {
     __syncthreads();
     uint32_t ncell = ic.nrows * W;
     for (uint32_t idx = threadIdx.x; idx < ncell; idx += blockDim.x) {
-      uint32_t rr = idx / W, c = idx - rr * W;
+      uint32_t c = idx / ic.nrows, rr = idx - c * ic.nrows;  // lanes = consecutive rows of ONE column
       uint32_t row = ic.row0 + rr;
       uint32_t slot = D.r0 + 1 + row;
       CellSrc src = fetch_cell(a, D, slot, c);
@@ -155,7 +157,7 @@ __global__ void __launch_bounds__(256) csv_measure_kernel(TableArgs a) {
     if (!(a.doc_flags[ic.d] & 1)) {
       uint32_t ncell = ic.nrows * W;
       for (uint32_t idx = threadIdx.x; idx < ncell; idx += blockDim.x) {
-        uint32_t rr = idx / W, c = idx - rr * W;
+        uint32_t c = idx / ic.nrows, rr = idx - c * ic.nrows;  // lanes = consecutive rows of ONE column
         uint32_t row = ic.row0 + rr;
         uint32_t slot = D.r0 + 1 + row;
         if (c < D.lead || !row_kept(a, D, slot, ic.chunk)) continue;
@@ -341,7 +343,7 @@ __global__ void __launch_bounds__(256) csv_emit_kernel(TableArgs a, uint8_t* __r
       uint8_t* base = staged ? s_buf + mis : out + g0;   // base[x] <-> out[g0 + x]
       uint32_t ncell = ic.nrows * W;
       for (uint32_t idx = threadIdx.x; idx < ncell; idx += blockDim.x) {
-        uint32_t rr = idx / W, c = idx - rr * W;
+        uint32_t c = idx / ic.nrows, rr = idx - c * ic.nrows;  // lanes = consecutive rows of ONE column
         uint32_t slot = slot0 + rr;
         if (c < D.lead || !row_kept(a, D, slot, ic.chunk)) continue;
         uint32_t j = c - D.lead;
