@@ -44,6 +44,11 @@ struct Big {
     }
     if (carry && n < W) w[n++] = (uint32_t)carry;
   }
+  RFQ_HD void add_small(uint32_t a) {
+    uint64_t carry = a;
+    for (int i = 0; i < n && carry; ++i) { uint64_t t = (uint64_t)w[i] + carry; w[i] = (uint32_t)t; carry = t >> 32; }
+    if (carry && n < W) w[n++] = (uint32_t)carry;
+  }
   RFQ_HD void mul_pow10(int p) {
     while (p >= 9) { mul_small(1000000000u); p -= 9; }
     uint32_t m = 1;

@@ -5,32 +5,67 @@
 #include "cell_format.cuh"
 #include "cell_parse.cuh"
 #include "col_decide.cuh"
+#include "xlsx_core.cuh"
 
 namespace rfq {
 
 // A cell source: where the token bytes live and how to decode them.
+// Text modes carry a byte span; typed modes (sheet cells already typed by the XML: numbers,
+// booleans, empty / error cells) carry their value in `bits`.
+enum { CM_CSV = 0, CM_RAW = 1, CM_INT = 2, CM_FLOAT = 3, CM_BOOL = 4, CM_XML = 5, CM_NULL = 6 };
 struct CellSrc {
   const uint8_t* p;
   uint32_t n;
-  uint8_t mode;     // 0 = CSV field (quote rules), 1 = raw bytes
+  uint8_t mode;     // CM_*
   bool missing;     // short row: pandas pads with an empty token
+  uint64_t bits;    // CM_INT: int64, CM_FLOAT: double bits, CM_BOOL: 0/1
 };
+RFQ_HD bool cell_is_text(const CellSrc& s) { return s.mode == CM_CSV || s.mode == CM_RAW || s.mode == CM_XML; }
+RFQ_HD double bits_as_double(uint64_t b) {
+#ifdef __CUDA_ARCH__
+  return __longlong_as_double((long long)b);
+#else
+  double d; __builtin_memcpy(&d, &b, 8); return d;
+#endif
+}
 
-#define RFQ_WITH_ITER(src, expr_csv, expr_raw) ((src).mode == 0 ? (expr_csv) : (expr_raw))
+#define RFQ_WITH_ITER(src, F, ...)                                            \
+  ((src).mode == CM_CSV ? F(CsvIter((src).p, (src).n), ##__VA_ARGS__)         \
+   : (src).mode == CM_XML ? F(XmlIter((src).p, (src).n), ##__VA_ARGS__)       \
+                          : F(RawIter((src).p, (src).n), ##__VA_ARGS__))
 
 RFQ_HD TextInfo cell_text(const CellSrc& s) {
-  if (s.missing) { TextInfo t; t.nbytes = t.ncp = t.nesc = 0; t.first8 = 0; t.utf8_ok = true; t.has_fchar = false; return t; }
-  return RFQ_WITH_ITER(s, scan_text(CsvIter(s.p, s.n)), scan_text(RawIter(s.p, s.n)));
+  if (s.missing || !cell_is_text(s)) {
+    TextInfo t; t.nbytes = t.ncp = t.nesc = 0; t.first8 = 0; t.utf8_ok = true; t.has_fchar = false;
+    if (!s.missing && s.mode != CM_NULL) { t.nbytes = 1; t.ncp = 1; t.first8 = '#'; }  // typed value: never an NA token
+    return t;
+  }
+  return RFQ_WITH_ITER(s, scan_text);
 }
 RFQ_HD int cell_int64(const CellSrc& s, int64_t* v) {
-  return RFQ_WITH_ITER(s, parse_int64(CsvIter(s.p, s.n), v), parse_int64(RawIter(s.p, s.n), v));
+  if (s.mode == CM_INT) { *v = (int64_t)s.bits; return INT_OK; }
+  if (s.mode == CM_BOOL) { *v = (int64_t)(s.bits & 1); return INT_OK; }
+  if (!cell_is_text(s)) return INT_INVALID;
+  return RFQ_WITH_ITER(s, parse_int64, v);
 }
 RFQ_HD int cell_uint64(const CellSrc& s, UintTok* v) {
-  return RFQ_WITH_ITER(s, parse_uint64(CsvIter(s.p, s.n), v), parse_uint64(RawIter(s.p, s.n), v));
+  if (!cell_is_text(s)) { v->v = 0; v->neg = false; v->gt_i64 = false; return INT_INVALID; }
+  return RFQ_WITH_ITER(s, parse_uint64, v);
 }
 RFQ_HD bool cell_double(const CellSrc& s, double* v) {
-  if (RFQ_WITH_ITER(s, parse_double(CsvIter(s.p, s.n), v), parse_double(RawIter(s.p, s.n), v))) return true;
-  int k = RFQ_WITH_ITER(s, inf_token(CsvIter(s.p, s.n)), inf_token(RawIter(s.p, s.n)));
+  if (s.mode == CM_FLOAT) { *v = bits_as_double(s.bits); return true; }
+  if (s.mode == CM_INT) {
+#ifdef __CUDA_ARCH__
+    *v = __ll2double_rn((long long)s.bits);
+#else
+    *v = (double)(int64_t)s.bits;
+#endif
+    return true;
+  }
+  if (s.mode == CM_BOOL) { *v = (s.bits & 1) ? 1.0 : 0.0; return true; }
+  if (!cell_is_text(s)) return false;
+  if (RFQ_WITH_ITER(s, parse_double, v)) return true;
+  int k = RFQ_WITH_ITER(s, inf_token);
   if (k == 0) return false;
 #ifdef __CUDA_ARCH__
   *v = k > 0 ? __longlong_as_double(0x7FF0000000000000LL) : __longlong_as_double(0xFFF0000000000000LL);
@@ -38,6 +73,28 @@ RFQ_HD bool cell_double(const CellSrc& s, double* v) {
   *v = k > 0 ? __builtin_huge_val() : -__builtin_huge_val();
 #endif
   return true;
+}
+
+// True/False of a boolean cell (typed, or one of pandas' bool words)
+RFQ_HD int cell_bool(const CellSrc& s, const TextInfo& t) {
+  if (s.mode == CM_BOOL) return (int)(s.bits & 1);
+  return bool_token(t.nbytes, t.first8);
+}
+// does the cell print '' (NaN after fillna) under chunk type `ctype`?
+RFQ_HD bool cell_is_nan(const CellSrc& s, const TextInfo& t, int ctype) {
+  if (s.missing || s.mode == CM_NULL) return true;
+  if (s.mode == CM_FLOAT) return dbl_is_nan(bits_as_double(s.bits));
+  if (!cell_is_text(s)) return false;
+  return ctype != CT_STRNF && is_na_token(t.nbytes, t.first8);
+}
+// chunk type a cell prints as inside a mixed object column of a sheet (CT_XOBJ)
+RFQ_HD int cell_own_ctype(const CellSrc& s) {
+  switch (s.mode) {
+    case CM_INT: return CT_INT;
+    case CM_FLOAT: return CT_FLOAT;
+    case CM_BOOL: return CT_BOOL;
+    default: return CT_STR;
+  }
 }
 
 // ---- 1. classify: SF_* flags of this cell + int64 status -----------------------------------
@@ -110,15 +167,16 @@ RFQ_HD CellMeasure measure_cell(const CellSrc& s, int ctype) {
   m.is_nan = false; m.plain_len = 0; m.ip_len = 0; m.tz = 6; m.inf_len = 0; m.obj_len = 0;
   m.sci_len = 0; m.fl = 0; m.extra_bytes = 0;
   TextInfo t = cell_text(s);
-  bool na = is_na_token(t.nbytes, t.first8);
-  if (na && ctype != CT_STRNF) { m.is_nan = true; return m; }
+  const bool xobj = ctype == CT_XOBJ;
+  if (xobj) ctype = cell_own_ctype(s);
+  if (cell_is_nan(s, t, ctype)) { m.is_nan = true; return m; }
   if (ctype == CT_STR || ctype == CT_STRNF) {
     m.plain_len = t.ncp + t.nesc;
     m.extra_bytes = t.nbytes - t.ncp;
     return m;
   }
   if (ctype == CT_BOOL || ctype == CT_BOOLNA) {
-    m.plain_len = bool_token(t.nbytes, t.first8) == 1 ? 4 : 5;
+    m.plain_len = cell_bool(s, t) == 1 ? 4 : 5;
     return m;
   }
   if (ctype == CT_UINT) {
@@ -140,6 +198,7 @@ RFQ_HD CellMeasure measure_cell(const CellSrc& s, int ctype) {
     m.fl = MF_FINITE | (a > 1e6 ? MF_LARGE : 0) | ((a < 1e-6 && a > 0.) ? MF_SMALL : 0);
     m.sci_len = (uint32_t)sci_len_of(v);
   }
+  if (xobj && ctype == CT_INT) m.obj_len = 0;  // an int inside a mixed object column prints as int
   return m;
 }
 
@@ -171,11 +230,11 @@ RFQ_HD void printed_size(const CellSrc& s, int ctype, int kind, int dec, uint32_
                          uint32_t* nbytes) {
   *ncp = 0; *nbytes = 0;
   TextInfo t = cell_text(s);
-  if (ctype != CT_STRNF && is_na_token(t.nbytes, t.first8)) return;
+  if (cell_is_nan(s, t, ctype)) return;
   uint32_t n = 0;
   switch (kind) {
     case PR_STR: *ncp = t.ncp + t.nesc; *nbytes = t.nbytes + t.nesc; return;
-    case PR_BOOL: n = bool_token(t.nbytes, t.first8) == 1 ? 4 : 5; break;
+    case PR_BOOL: n = cell_bool(s, t) == 1 ? 4 : 5; break;
     case PR_INT: { int64_t iv = 0; cell_int64(s, &iv); n = (uint32_t)int64_len(iv); break; }
     case PR_UINT: { UintTok u; cell_uint64(s, &u); n = (uint32_t)ndigits_u64(u.v); break; }
     case PR_FIXED: { Fixed6 f = fixed6(cell_as_double(s, ctype)); n = (uint32_t)fixed_len(f, dec); break; }
@@ -190,10 +249,18 @@ RFQ_HD void printed_size(const CellSrc& s, int ctype, int kind, int dec, uint32_
 RFQ_HD uint32_t print_cell(const CellSrc& s, int ctype, int kind, int dec, uint8_t* out) {
   if (kind == PR_STR) {
     TextInfo t = cell_text(s);
-    if (ctype != CT_STRNF && is_na_token(t.nbytes, t.first8)) return 0;
+    if (cell_is_nan(s, t, ctype)) return 0;
     uint32_t k = 0;
     int c;
-    if (s.mode == 0) {
+    if (s.mode == CM_XML) {
+      XmlIter it(s.p, s.n);
+      while ((c = it.next()) >= 0) {
+        if (c == '\t') { out[k++] = '\\'; out[k++] = 't'; }
+        else if (c == '\n') { out[k++] = '\\'; out[k++] = 'n'; }
+        else if (c == '\r') { out[k++] = '\\'; out[k++] = 'r'; }
+        else out[k++] = (uint8_t)c;
+      }
+    } else if (s.mode == CM_CSV) {
       CsvIter it(s.p, s.n);
       while ((c = it.next()) >= 0) {
         if (c == '\t') { out[k++] = '\\'; out[k++] = 't'; }
@@ -213,10 +280,10 @@ RFQ_HD uint32_t print_cell(const CellSrc& s, int ctype, int kind, int dec, uint8
     return k;
   }
   TextInfo t = cell_text(s);
-  if (is_na_token(t.nbytes, t.first8)) return 0;
+  if (cell_is_nan(s, t, ctype)) return 0;
   switch (kind) {
     case PR_BOOL: {
-      const char* w = bool_token(t.nbytes, t.first8) == 1 ? "True" : "False";
+      const char* w = cell_bool(s, t) == 1 ? "True" : "False";
       uint32_t k = 0;
       while (w[k]) { out[k] = (uint8_t)w[k]; ++k; }
       return k;

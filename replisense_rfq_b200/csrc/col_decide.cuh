@@ -23,7 +23,8 @@ enum {
   CT_BOOLNA = 5,  // object: True / False / NaN
   CT_STR = 6,     // str, NA -> NaN
   CT_STRNF = 7,   // str with the NA filter off (uint64 conflict): nothing is NaN
-  CT_UNSUP = 8    // Python-int object columns (beyond uint64) — not produced on the GPU path
+  CT_UNSUP = 8,   // Python-int object columns (beyond uint64) — not produced on the GPU path
+  CT_XOBJ = 9     // sheet column of mixed Python objects: every cell prints as its own type
 };
 
 // printing class of a whole column
@@ -162,6 +163,7 @@ RFQ_HD ColumnLayout layout_column(int cls, const ChunkMeasure* m, const uint8_t*
       int t = ctypes[(size_t)k * stride];
       bool as_float = (cls == CC_OBJF) || t == CT_INTNA || t == CT_FLOAT;
       uint32_t l = as_float ? c.obj_len : c.plain_len;
+      if (t == CT_XOBJ && cls != CC_OBJF && c.obj_len > l) l = c.obj_len;
       if (l > w) w = l;
     }
   }

@@ -350,17 +350,20 @@ __global__ void __launch_bounds__(256) csv_emit_kernel(TableArgs a, uint8_t* __r
         ColOut co = col[D.col_base + j];
         const uint8_t* ctrow = a.ctype + D.stat_base + ic.chunk * W;
         int ct = ctrow[c];
-        int kind = print_kind(co.cls, ct, co.sci != 0);
         CellSrc src = fetch_cell(a, D, slot, c);
+        if (ct == CT_XOBJ) ct = cell_own_ctype(src);
+        int kind = print_kind(co.cls, ct, co.sci != 0);
         uint32_t xb = 0;  // extra bytes of the columns to the left (rows with non-ASCII text only)
         if (j && __ldg(a.row_extra + slot)) {
           for (uint32_t c2 = D.lead; c2 < c; ++c2) {
             ColOut c2o = col[D.col_base + c2 - D.lead];
             int ct2 = ctrow[c2];
+            CellSrc s2 = fetch_cell(a, D, slot, c2);
+            if (ct2 == CT_XOBJ) ct2 = cell_own_ctype(s2);
             int k2 = print_kind(c2o.cls, ct2, c2o.sci != 0);
             if (k2 != PR_STR) continue;
             uint32_t cp2, nb2;
-            printed_size(fetch_cell(a, D, slot, c2), ct2, k2, c2o.dec, &cp2, &nb2);
+            printed_size(s2, ct2, k2, c2o.dec, &cp2, &nb2);
             xb += nb2 - cp2;
           }
         }

@@ -1,0 +1,245 @@
+// Per-element decoders of the sheet path (host/device): one <si> of sharedStrings, one <row>,
+// one <c>, and the python-engine column inference pandas applies to the cell objects
+// (pandas/io/parsers/base_parser.py:449-563 `_infer_types` -> lib.maybe_convert_numeric /
+// ops.maybe_convert_bool; pandas/io/excel/_base.py:913-937).
+#pragma once
+#include "cell_ops.cuh"
+#include "xlsx_core.cuh"
+
+namespace rfq {
+
+// document-level problems (never guessed: the sheet is reported RFQ_DOC_UNSUPPORTED)
+enum {
+  XU_BANG = 1u << 0,        // comment / CDATA / doctype inside the part
+  XU_NO_REF = 1u << 1,      // <row> or <c> without r=
+  XU_ORDER = 1u << 2,       // rows / columns not strictly increasing
+  XU_DATE = 1u << 3,        // date-styled number or t="d"
+  XU_RICH_INLINE = 1u << 4, // inline string with rich-text runs
+  XU_BAD_NUMBER = 1u << 5,  // numeric literal we cannot type exactly (overflow, nan, malformed)
+  XU_BAD_SST = 1u << 6,     // shared-string index out of range / no table
+  XU_ENTITY = 1u << 7,      // unknown entity
+  XU_TYPE = 1u << 8,        // unknown t=
+  XU_X005F = 1u << 9        // 'x005F_' escape inside a shared string
+};
+
+struct XCell {
+  uint32_t col;     // 1-based column
+  uint32_t mode;    // CM_*
+  uint64_t bits;    // value, or (offset << 32 | length) for text: offset into the string arena
+                    // (CM_RAW) or into the document arena (CM_XML)
+};
+
+// ---- <si>: text of its <t> children and of the <t> of its <r> runs; phonetic runs excluded ----
+// p points at "<si"; e = end of the document. Writes decoded bytes to out when non-null.
+// Returns decoded length.
+RFQ_HD uint32_t sst_decode_si(const uint8_t* p, const uint8_t* e, uint8_t* out, uint32_t* flags) {
+  uint32_t n = 0;
+  const uint8_t* q = p + 3;
+  // self-closing <si/> ?
+  while (q < e && *q != '>') ++q;
+  if (q >= e) return 0;
+  if (q[-1] == '/') return 0;
+  ++q;
+  int in_rph = 0;
+  uint32_t x5 = 0;  // progress of the literal "x005F_" in the decoded stream
+  while (q < e) {
+    if (*q != '<') { ++q; continue; }   // text outside <t> is ignored
+    int tg = xml_classify(q, e);
+    if (tg == XT_SI_END) break;
+    if (tg == XT_BANG) { *flags |= XU_BANG; }
+    if (tg == XT_RPH) { const uint8_t* g = q; while (g < e && *g != '>') ++g; if (!(g < e && g[-1] == '/')) in_rph = 1; q = g; continue; }
+    if (tg == XT_RPH_END) { in_rph = 0; ++q; continue; }
+    if (tg == XT_T && !in_rph) {
+      const uint8_t* g = q;
+      while (g < e && *g != '>') ++g;
+      if (g >= e) break;
+      if (g[-1] == '/') { q = g; continue; }  // <t/>
+      const uint8_t* tb = g + 1;
+      const uint8_t* te = tb;
+      while (te < e && *te != '<') ++te;
+      XmlIter it(tb, (uint32_t)(te - tb));
+      int c;
+      while ((c = it.next()) >= 0) {
+        if (c == "x005F_"[x5]) { if (++x5 == 6) { *flags |= XU_X005F; x5 = 0; } }
+        else x5 = (c == 'x') ? 1 : 0;
+        if (out) out[n] = (uint8_t)c;
+        ++n;
+      }
+      if (it.bad) *flags |= XU_ENTITY;
+      q = te;
+      continue;
+    }
+    ++q;
+  }
+  return n;
+}
+
+// ---- <row ...>: its r= number ------------------------------------------------------------------
+RFQ_HD uint32_t xlsx_row_number(const uint8_t* p, const uint8_t* e, uint32_t* flags) {
+  const uint8_t* g = p;
+  while (g < e && *g != '>') ++g;
+  const uint8_t* vb; uint32_t vn;
+  if (!xml_attr(p, g, 'r', &vb, &vn) || vn == 0 || vn > 9) { *flags |= XU_NO_REF; return 0; }
+  uint32_t r = 0;
+  for (uint32_t i = 0; i < vn; ++i) { uint32_t d = vb[i] - '0'; if (d > 9) { *flags |= XU_NO_REF; return 0; } r = r * 10 + d; }
+  return r;
+}
+
+struct SstView {             // shared-string table of the workbook this sheet belongs to
+  const uint32_t* off;       // [n] offset of string i in the string arena
+  const uint32_t* len;       // [n]
+  uint32_t n;
+};
+
+// ---- <c ...>...</c> -----------------------------------------------------------------------------
+// doc/len: the sheet part; cpos: offset of "<c". date_ids: sorted style ids that are dates.
+RFQ_HD XCell xlsx_parse_cell(const uint8_t* doc, uint32_t len, uint32_t cpos, const SstView& sst,
+                             const uint32_t* date_ids, uint32_t n_date, uint32_t* flags) {
+  XCell x; x.col = 0; x.mode = CM_NULL; x.bits = 0;
+  const uint8_t* p = doc + cpos;
+  const uint8_t* e = doc + len;
+  const uint8_t* g = p;
+  while (g < e && *g != '>') ++g;
+  if (g >= e) return x;
+  const uint8_t* vb; uint32_t vn;
+  uint32_t row = 0;
+  if (!xml_attr(p, g, 'r', &vb, &vn) || !a1_parse(vb, vn, &x.col, &row)) { *flags |= XU_NO_REF; return x; }
+  // type
+  int ty = 'n';
+  if (xml_attr(p, g, 't', &vb, &vn)) {
+    if (vn == 1) ty = vb[0];                                   // n s b e d
+    else if (vn == 3 && vb[0] == 's' && vb[1] == 't' && vb[2] == 'r') ty = 'S';
+    else if (vn == 9 && vb[0] == 'i') ty = 'I';               // inlineStr
+    else { *flags |= XU_TYPE; return x; }
+  }
+  uint32_t style = 0;
+  if (xml_attr(p, g, 's', &vb, &vn)) for (uint32_t i = 0; i < vn; ++i) style = style * 10 + (vb[i] - '0');
+  if (g[-1] == '/') return x;  // <c .../> : no value
+  // children until </c>
+  const uint8_t* q = g + 1;
+  const uint8_t* val_b = nullptr; uint32_t val_n = 0; bool have_v = false;
+  const uint8_t* is_b = nullptr; uint32_t is_n = 0; int n_t = 0; bool in_is = false;
+  while (q < e) {
+    if (*q != '<') { ++q; continue; }
+    int tg = xml_classify(q, e);
+    if (tg == XT_C_END || tg == XT_C || tg == XT_ROW_END) break;
+    if (tg == XT_BANG) *flags |= XU_BANG;
+    const uint8_t* h = q;
+    while (h < e && *h != '>') ++h;
+    if (h >= e) break;
+    if (tg == XT_V && !have_v) {
+      have_v = true;
+      if (h[-1] != '/') { val_b = h + 1; const uint8_t* t2 = val_b; while (t2 < e && *t2 != '<') ++t2; val_n = (uint32_t)(t2 - val_b); }
+    } else if (tg == XT_IS) { in_is = h[-1] != '/'; }
+    else if (tg == XT_R && in_is) { *flags |= XU_RICH_INLINE; }
+    else if (tg == XT_T && in_is) {
+      if (h[-1] != '/' && n_t == 0) { is_b = h + 1; const uint8_t* t2 = is_b; while (t2 < e && *t2 != '<') ++t2; is_n = (uint32_t)(t2 - is_b); }
+      ++n_t;
+    }
+    q = h + 1;
+  }
+  if (ty == 'I') {
+    // value = Text.content of <is>; openpyxl sets it only when <is> exists; "" stays ""
+    if (n_t > 1) *flags |= XU_RICH_INLINE;
+    if (is_b && is_n) { x.mode = CM_XML; x.bits = ((uint64_t)(uint32_t)(is_b - doc) << 32) | is_n; }
+    return x;
+  }
+  if (!val_b || val_n == 0) return x;  // findtext(...) or None -> None -> ""
+  switch (ty) {
+    case 'n': {
+      for (uint32_t i = 0; i < n_date; ++i) if (date_ids[i] == style) { *flags |= XU_DATE; return x; }
+      bool is_float = false;
+      for (uint32_t i = 0; i < val_n; ++i) if (val_b[i] == '.' || val_b[i] == 'e' || val_b[i] == 'E') is_float = true;
+      if (!is_float) {
+        int64_t iv;
+        if (parse_int64(RawIter(val_b, val_n), &iv) != INT_OK) { *flags |= XU_BAD_NUMBER; return x; }
+        x.mode = CM_INT; x.bits = (uint64_t)iv;
+        return x;
+      }
+      double v;
+      if (!strtod_exact(val_b, val_n, &v) || dbl_is_inf(v) || dbl_is_nan(v)) { *flags |= XU_BAD_NUMBER; return x; }
+      // pandas _convert_cell: integral floats become ints
+      if (v > -9.2e18 && v < 9.2e18) {
+        int64_t iv = (int64_t)v;
+        if ((double)iv == v) { x.mode = CM_INT; x.bits = (uint64_t)iv; return x; }
+      } else { *flags |= XU_BAD_NUMBER; return x; }  // would be a Python big int
+      x.mode = CM_FLOAT; x.bits = dbl_bits(v);
+      return x;
+    }
+    case 's': {
+      int64_t idx;
+      if (parse_int64(RawIter(val_b, val_n), &idx) != INT_OK || idx < 0 || (uint64_t)idx >= sst.n) { *flags |= XU_BAD_SST; return x; }
+      uint32_t l = sst.len[idx];
+      if (l == 0) return x;  // "" prints and trims like an empty cell
+      x.mode = CM_RAW; x.bits = ((uint64_t)sst.off[idx] << 32) | l;
+      return x;
+    }
+    case 'S': x.mode = CM_XML; x.bits = ((uint64_t)(uint32_t)(val_b - doc) << 32) | val_n; return x;
+    case 'b': {
+      int64_t iv;
+      if (parse_int64(RawIter(val_b, val_n), &iv) != INT_OK) { *flags |= XU_BAD_NUMBER; return x; }
+      x.mode = CM_BOOL; x.bits = iv != 0;
+      return x;
+    }
+    case 'e': x.mode = CM_FLOAT; x.bits = 0x7FF8000000000000ull; return x;  // np.nan
+    case 'd': *flags |= XU_DATE; return x;
+    default: *flags |= XU_TYPE; return x;
+  }
+}
+
+// is the converted value "" (trimmed from the right of a row / from the bottom of the sheet)?
+RFQ_HD bool xcell_is_empty(const XCell& x) { return x.mode == CM_NULL; }
+
+// ---- python-engine inference ----------------------------------------------------------------
+enum {
+  XF_NULL = 1u << 0,          // "", NaN, NA string
+  XF_FLOAT = 1u << 1,         // float object or float-looking string
+  XF_INT = 1u << 2,           // int object or int-looking string
+  XF_BOOL = 1u << 3,          // bool object
+  XF_STR_NONNUM = 1u << 4,    // string that floatify rejects
+  XF_TYPED_NUM = 1u << 5,     // int / float object (not bool-like for maybe_convert_bool)
+  XF_STR_NOT_BOOLWORD = 1u << 6,
+  XF_NON_STR = 1u << 7,       // any non-null non-string object
+  XF_FIRST_IS_INT = 1u << 8,  // first data row holds a Python int (or bool)
+  XF_BAD_UTF8 = 1u << 9,
+  XF_ENTITY = 1u << 10,
+  XF_BIG = 1u << 11           // int-looking string beyond int64
+};
+
+RFQ_HD uint32_t xclassify_cell(const CellSrc& s, bool first_row) {
+  if (s.missing || s.mode == CM_NULL) return XF_NULL;
+  if (s.mode == CM_INT) return XF_INT | XF_TYPED_NUM | XF_NON_STR | (first_row ? XF_FIRST_IS_INT : 0);
+  if (s.mode == CM_BOOL) return XF_BOOL | XF_NON_STR | (first_row ? XF_FIRST_IS_INT : 0);
+  if (s.mode == CM_FLOAT) {
+    if (dbl_is_nan(bits_as_double(s.bits))) return XF_NULL;
+    return XF_FLOAT | XF_TYPED_NUM | XF_NON_STR;
+  }
+  TextInfo t = cell_text(s);
+  uint32_t f = 0;
+  if (!t.utf8_ok) f |= XF_BAD_UTF8;
+  if (is_na_token(t.nbytes, t.first8)) return f | XF_NULL;
+  if (bool_token(t.nbytes, t.first8) < 0) f |= XF_STR_NOT_BOOLWORD;
+  int64_t iv;
+  int is = cell_int64(s, &iv);
+  if (is == INT_OK) return f | XF_INT;
+  double dv;
+  if (cell_double(s, &dv)) return f | (is == INT_OVERFLOW ? XF_BIG : 0) | (dbl_is_nan(dv) ? XF_NULL : XF_FLOAT);
+  return f | XF_STR_NONNUM;
+}
+
+RFQ_HD int xdecide_column(uint32_t f) {
+  if (f & XF_BIG) return CT_UNSUP;
+  if (!(f & XF_STR_NONNUM)) {            // lib.maybe_convert_numeric succeeds
+    if (f & (XF_NULL | XF_FLOAT)) return CT_FLOAT;
+    if (f & XF_INT) return CT_INT;
+    if (f & XF_BOOL) return CT_BOOL;
+    return CT_FLOAT;
+  }
+  // object column; ops.maybe_convert_bool unless the first value is a Python int
+  if (!(f & XF_FIRST_IS_INT) && !(f & (XF_TYPED_NUM | XF_STR_NOT_BOOLWORD)))
+    return (f & XF_NULL) ? CT_BOOLNA : CT_BOOL;
+  if (!(f & XF_NON_STR)) return CT_STR;  // all strings (or NaN): str dtype
+  return CT_XOBJ;
+}
+
+}  // namespace rfq

@@ -370,3 +370,105 @@ def sheet_xml_doc(seed: int, min_rows: int = 5, max_rows: int = 60):
         sst.append("<si><t>%s</t></si>" % xml_escape(s))
     sst.append("</sst>")
     return "".join(out).encode("utf-8"), "".join(sst).encode("utf-8")
+
+
+def sheet_xml_fuzz(seed: int):
+    """A small adversarial worksheet: every cell type openpyxl distinguishes (n, s, str,
+    inlineStr, b, e), entities, numeric-looking and NA strings, duplicate / blank / numeric
+    headers, sparse rows and columns, 17-digit numbers. Returns (sheet_xml, sst_xml)."""
+    r = random.Random(seed)
+    ncols = r.randint(2, 7)
+    nrows = r.randint(0, 25)
+    strings, index = [], {}
+
+    def sid(s):
+        if s not in index:
+            index[s] = len(strings)
+            strings.append(s)
+        return index[s]
+
+    def cell(ref, kind):
+        if kind == "empty":
+            return '<c r="%s" s="2"/>' % ref
+        if kind == "emptyv":
+            return '<c r="%s" t="s"><v></v></c>' % ref
+        if kind == "int":
+            return '<c r="%s"><v>%d</v></c>' % (ref, r.randint(-1000, 100000))
+        if kind == "intf":
+            return '<c r="%s" s="2"><v>%d.0</v></c>' % (ref, r.randint(0, 5000))
+        if kind == "price":
+            return '<c r="%s"><v>%s</v></c>' % (ref, repr(r.randint(1, 10 ** 7) / 100))
+        if kind == "float":
+            return '<c r="%s"><v>%s</v></c>' % (ref, repr(r.uniform(-1, 1) * 10 ** r.randint(-8, 9)))
+        if kind == "float17":
+            return '<c r="%s"><v>%.17g</v></c>' % (ref, r.uniform(0, 1000))
+        if kind == "sci":
+            return '<c r="%s"><v>%sE%d</v></c>' % (ref, r.randint(1, 999) / 100, r.randint(-10, 10))
+        if kind == "bool":
+            return '<c r="%s" t="b"><v>%d</v></c>' % (ref, r.randint(0, 1))
+        if kind == "err":
+            return '<c r="%s" t="e"><v>#DIV/0!</v></c>' % ref
+        words = ["RJF544", "a & b", "x<y>z", "Würth", "日本語", "12", "4.50", "NA", "N/A", "true", "False",
+                 "TRUE", "inf", "", "  pad ", "line1\nline2", "tab\there", "1e5", "nan", "-", "0x1F",
+                 "quote\"s", "it's", "₹500", "null"]
+        w = r.choice(words)
+        if kind == "sst":
+            return '<c r="%s" t="s"><v>%d</v></c>' % (ref, sid(w))
+        if kind == "str":
+            return '<c r="%s" t="str"><f>A1&amp;"x"</f><v>%s</v></c>' % (ref, xml_escape(w).replace("\n", "&#10;"))
+        if kind == "inline":
+            return '<c r="%s" t="inlineStr"><is><t>%s</t></is></c>' % (ref, xml_escape(w))
+        raise ValueError(kind)
+
+    col_kinds = [r.choice(["int", "intf", "price", "float", "bool", "sst", "mixed", "numstr", "boolish",
+                           "float17", "sci"]) for _ in range(ncols)]
+    out = [_XML_HEAD]
+    rownum = 0
+    hdr_words = ["Sl No", "Part", "Part", "Qty", "", "a&b", "Ünit", "Qty", "2024"]
+    for i in range(nrows + 1):
+        rownum += 1
+        if r.random() < 0.08:
+            rownum += r.randint(1, 2)
+        if i and r.random() < 0.05:
+            out.append('<row r="%d" ht="15.75" customHeight="1"/>' % rownum)
+            continue
+        out.append('<row r="%d" spans="1:%d">' % (rownum, ncols))
+        for c in range(ncols):
+            ref = "%s%d" % (col_letters(c), rownum)
+            if r.random() < 0.1:
+                continue
+            if i == 0 and rownum == 1:
+                k = r.random()
+                if k < 0.97:
+                    out.append('<c r="%s" t="s"><v>%d</v></c>' % (ref, sid(r.choice(hdr_words))))
+                elif k < 0.98:
+                    out.append(cell(ref, "int"))
+                elif k < 0.99:
+                    out.append(cell(ref, "price"))
+                else:
+                    out.append(cell(ref, "bool"))
+                continue
+            k = col_kinds[c]
+            if k == "mixed":
+                k = r.choice(["int", "price", "sst", "bool", "err", "inline", "str", "empty", "emptyv"])
+            elif k == "numstr":
+                k = r.choice(["sst", "int", "price"])
+            elif k == "boolish":
+                k = r.choice(["bool", "bool", "empty"])
+            if r.random() < 0.05:
+                k = r.choice(["empty", "err", "emptyv"])
+            out.append(cell(ref, k))
+        out.append("</row>")
+    out.append(_XML_TAIL)
+    sst = ['<?xml version="1.0" encoding="UTF-8" standalone="yes"?>\r\n'
+           '<sst xmlns="http://schemas.openxmlformats.org/spreadsheetml/2006/main" '
+           'count="%d" uniqueCount="%d">' % (len(strings), len(strings))]
+    for i, s in enumerate(strings):
+        if i % 7 == 3 and s:
+            h = len(s) // 2
+            sst.append('<si><r><rPr><b/></rPr><t xml:space="preserve">%s</t></r><r><t>%s</t></r>'
+                       '<rPh sb="0" eb="1"><t>PHON</t></rPh></si>' % (xml_escape(s[:h]), xml_escape(s[h:])))
+        else:
+            sst.append("<si><t>%s</t></si>" % xml_escape(s))
+    sst.append("</sst>")
+    return "".join(out).encode("utf-8"), "".join(sst).encode("utf-8")

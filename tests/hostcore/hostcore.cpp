@@ -274,3 +274,215 @@ int hc_csv_parse(const uint8_t* doc, uint64_t len, int64_t nrows, uint8_t* out, 
 }
 
 }  // extern "C"
+
+// ---- sheet XML primitives ---------------------------------------------------------------------
+#include "../../replisense_rfq_b200/csrc/xlsx_core.cuh"
+extern "C" {
+int hc_strtod(const uint8_t* s, uint32_t n, double* out) { return rfq::strtod_exact(s, n, out) ? 1 : 0; }
+int hc_xml_decode(const uint8_t* p, uint32_t n, uint8_t* out) {
+  rfq::XmlIter it(p, n); int c, k = 0;
+  while ((c = it.next()) >= 0) out[k++] = (uint8_t)c;
+  return it.bad ? -1 : k;
+}
+}
+
+// ================================================================================================
+// Sequential model of the sheet pipeline (same per-element functions as the kernels).
+#include "../../replisense_rfq_b200/csrc/xlsx_cells.cuh"
+namespace {
+// python-engine header names: str() of the first-row values, blanks -> Unnamed: k, de-duplicated
+std::string py_repr_double(double v) {
+  char buf[64];
+  for (int prec = 1; prec <= 17; ++prec) {
+    snprintf(buf, sizeof buf, "%.*e", prec - 1, v);
+    if (strtod(buf, nullptr) == v) break;
+  }
+  // buf = d.ddddde[+-]XX ; re-render with Python's repr rules
+  std::string m(buf);
+  size_t epos = m.find('e');
+  int ex = atoi(m.c_str() + epos + 1);
+  std::string digits;
+  bool neg = m[0] == '-';
+  for (size_t i = neg ? 1 : 0; i < epos; ++i) if (m[i] != '.') digits.push_back(m[i]);
+  std::string out = neg ? "-" : "";
+  if (ex < -4 || ex >= 16) {
+    out += digits.substr(0, 1);
+    if (digits.size() > 1) { out += "."; out += digits.substr(1); }
+    char eb[16]; snprintf(eb, sizeof eb, "e%c%02d", ex < 0 ? '-' : '+', ex < 0 ? -ex : ex);
+    out += eb;
+  } else if (ex < 0) {
+    out += "0."; out.append(-ex - 1, '0'); out += digits;
+  } else {
+    if ((int)digits.size() <= ex + 1) { out += digits; out.append(ex + 1 - digits.size(), '0'); out += ".0"; }
+    else { out += digits.substr(0, ex + 1); out += "."; out += digits.substr(ex + 1); }
+  }
+  return out;
+}
+}  // namespace
+
+extern "C" {
+// status: 0 ok, 2 unsupported, 3 empty sheet (df.empty -> skipped by the reference)
+int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uint32_t sst_len,
+                   const uint32_t* date_ids, uint32_t n_date, int64_t nrows, uint8_t* out, uint64_t cap,
+                   uint64_t* out_len) {
+  *out_len = 0;
+  uint32_t flags = 0;
+  // shared strings
+  std::vector<uint32_t> s_off, s_len; std::vector<uint8_t> s_arena;
+  if (sst_doc) {
+    const uint8_t* e = sst_doc + sst_len;
+    for (uint32_t i = 0; i + 3 < sst_len; ++i) {
+      if (sst_doc[i] != '<') continue;
+      int tg = xml_classify(sst_doc + i, e);
+      if (tg == XT_BANG) flags |= XU_BANG;
+      if (tg != XT_SI) continue;
+      uint32_t n = sst_decode_si(sst_doc + i, e, nullptr, &flags);
+      s_off.push_back((uint32_t)s_arena.size()); s_len.push_back(n);
+      s_arena.resize(s_arena.size() + n);
+      if (n) sst_decode_si(sst_doc + i, e, s_arena.data() + s_off.back(), &flags);
+    }
+  }
+  SstView sv{s_off.data(), s_len.data(), (uint32_t)s_off.size()};
+  // rows / cells in document order
+  struct RowE { uint32_t r; uint32_t c0, c1; };
+  std::vector<RowE> rows; std::vector<XCell> cells;
+  const uint8_t* e = doc + len;
+  for (uint32_t i = 0; i + 2 < len; ++i) {
+    if (doc[i] != '<') continue;
+    int tg = xml_classify(doc + i, e);
+    if (tg == XT_BANG) flags |= XU_BANG;
+    if (tg == XT_ROW) {
+      if (!rows.empty()) rows.back().c1 = (uint32_t)cells.size();
+      rows.push_back({xlsx_row_number(doc + i, e, &flags), (uint32_t)cells.size(), (uint32_t)cells.size()});
+    } else if (tg == XT_C) {
+      cells.push_back(xlsx_parse_cell(doc, len, i, sv, date_ids, n_date, &flags));
+    }
+  }
+  if (!rows.empty()) rows.back().c1 = (uint32_t)cells.size();
+  uint32_t cap_rows = (uint32_t)std::min<int64_t>(nrows, 0x7FFFFFF0) + 1;  // file_rows_needed
+  uint32_t W = 0, lastrow = 0, prev_r = 0;
+  for (auto& R : rows) {
+    if (R.r <= prev_r) flags |= XU_ORDER;
+    prev_r = R.r;
+    uint32_t pc = 0;
+    for (uint32_t k = R.c0; k < R.c1; ++k) {
+      if (cells[k].col <= pc) flags |= XU_ORDER;
+      pc = cells[k].col;
+      if (R.r <= cap_rows && !xcell_is_empty(cells[k])) { W = std::max(W, cells[k].col); lastrow = std::max(lastrow, R.r); }
+    }
+  }
+  if (flags) return 2;
+  if (lastrow <= 1) return 3;  // no data rows -> empty frame -> sheet skipped
+  uint32_t ndata = lastrow - 1;
+  std::vector<int> r2e(lastrow + 1, -1);
+  for (size_t k = 0; k < rows.size(); ++k) if (rows[k].r <= lastrow) r2e[rows[k].r] = (int)k;
+  auto cell = [&](uint32_t r, uint32_t c) {  // r 1-based sheet row, c 0-based column
+    CellSrc s; s.p = nullptr; s.n = 0; s.mode = CM_NULL; s.missing = false; s.bits = 0;
+    int k = r2e[r];
+    if (k < 0) return s;
+    for (uint32_t q = rows[k].c0; q < rows[k].c1; ++q) if (cells[q].col == c + 1) {
+      const XCell& x = cells[q];
+      s.mode = (uint8_t)x.mode; s.bits = x.bits;
+      if (x.mode == CM_RAW) { s.p = s_arena.data() + (x.bits >> 32); s.n = (uint32_t)x.bits; }
+      if (x.mode == CM_XML) { s.p = doc + (x.bits >> 32); s.n = (uint32_t)x.bits; }
+      break;
+    }
+    return s;
+  };
+  // header
+  std::vector<std::string> raw(W); std::vector<size_t> unnamed;
+  for (uint32_t c = 0; c < W; ++c) {
+    CellSrc s = cell(1, c);
+    std::string nm;
+    if (s.mode == CM_INT || s.mode == CM_BOOL || s.mode == CM_FLOAT) return 2;  // non-string column labels: pandas formats the Index as a whole
+    else if (s.mode == CM_RAW) nm.assign((const char*)s.p, s.n);
+    else if (s.mode == CM_XML) { XmlIter it(s.p, s.n); int ch; while ((ch = it.next()) >= 0) nm.push_back((char)ch); }
+    if (s.mode == CM_NULL) { nm = "Unnamed: " + std::to_string(c); unnamed.push_back(c); }
+    raw[c] = nm;
+  }
+  {
+    std::vector<size_t> order; std::vector<bool> un(W, false);
+    for (size_t k : unnamed) un[k] = true;
+    for (size_t k = 0; k < W; ++k) if (!un[k]) order.push_back(k);
+    for (size_t k : unnamed) order.push_back(k);
+    std::unordered_map<std::string, int> counts;
+    for (size_t i2 : order) {
+      std::string col = raw[i2], old = col; int cur = 0;
+      auto f = counts.find(col); if (f != counts.end()) cur = f->second;
+      while (cur > 0) {
+        counts[old] = cur + 1;
+        col = old + "." + std::to_string(cur);
+        bool in = false; for (auto& x : raw) if (x == col) in = true;
+        if (in) cur += 1; else { auto g = counts.find(col); cur = g == counts.end() ? 0 : g->second; }
+      }
+      raw[i2] = col; counts[col] = cur + 1;
+    }
+  }
+  std::vector<uint32_t> ncp(W);
+  for (uint32_t c = 0; c < W; ++c) utf8_valid_count(raw[c], &ncp[c]);
+  // inference
+  std::vector<uint32_t> xf(W, 0); std::vector<uint32_t> row_na(ndata, 0);
+  for (uint32_t r = 0; r < ndata; ++r)
+    for (uint32_t c = 0; c < W; ++c) {
+      uint32_t f = xclassify_cell(cell(r + 2, c), r == 0);
+      xf[c] |= f;
+      if (f & XF_NULL) row_na[r]++;
+    }
+  std::vector<uint8_t> ctype(W);
+  for (uint32_t c = 0; c < W; ++c) { ctype[c] = (uint8_t)xdecide_column(xf[c]); if (ctype[c] == CT_UNSUP || (xf[c] & (XF_BAD_UTF8 | XF_ENTITY))) return 2; }
+  std::vector<bool> keep(ndata); uint32_t nkeep = 0;
+  for (uint32_t r = 0; r < ndata; ++r) { keep[r] = row_na[r] != W; nkeep += keep[r]; }
+  std::string text;
+  if (nkeep == 0) text = empty_frame_text(raw);
+  else {
+    std::vector<ChunkMeasure> meas(W, ChunkMeasure{0, 0, 6, 0, 0, 0, 0, 0});
+    for (uint32_t r = 0; r < ndata; ++r) {
+      if (!keep[r]) continue;
+      for (uint32_t c = 0; c < W; ++c) {
+        CellMeasure m = measure_cell(cell(r + 2, c), ctype[c]);
+        ChunkMeasure& M = meas[c];
+        if (m.is_nan) { M.nan_left = 1; continue; }
+        M.plain_len = std::max(M.plain_len, m.plain_len); M.ip_len = std::max(M.ip_len, m.ip_len);
+        M.min_tz = std::min(M.min_tz, m.tz); M.inf_len = std::max(M.inf_len, m.inf_len);
+        M.obj_len = std::max(M.obj_len, m.obj_len); M.sci_len = std::max(M.sci_len, m.sci_len); M.fl |= m.fl;
+      }
+    }
+    std::vector<ColumnLayout> lay(W);
+    for (uint32_t c = 0; c < W; ++c) {
+      int cls = fold_column_class(&ctype[c], 1, W, meas[c].nan_left != 0);
+      lay[c] = layout_column(cls, &meas[c], &ctype[c], 1, W, ncp[c]);
+    }
+    for (uint32_t c = 0; c < W; ++c) {
+      bool numeric = lay[c].cls == CC_INT || lay[c].cls == CC_UINT || lay[c].cls == CC_FLOAT || lay[c].cls == CC_BOOL;
+      uint32_t cp = ncp[c] + (numeric ? 1 : 0);
+      if (c) text += ' ';
+      text.append(lay[c].width - cp, ' ');
+      if (numeric) text += ' ';
+      text += raw[c];
+    }
+    std::vector<uint8_t> buf;
+    for (uint32_t r = 0; r < ndata; ++r) {
+      if (!keep[r]) continue;
+      text += '\n';
+      for (uint32_t c = 0; c < W; ++c) {
+        CellSrc s = cell(r + 2, c);
+        int ct = ctype[c];
+        if (ct == CT_XOBJ) ct = cell_own_ctype(s);
+        int kind = print_kind(lay[c].cls, ct, lay[c].sci);
+        uint32_t cp, nb;
+        printed_size(s, ct, kind, lay[c].dec, &cp, &nb);
+        if (c) text += ' ';
+        text.append(lay[c].width - cp, ' ');
+        buf.resize(nb + 400);
+        uint32_t wrote = print_cell(s, ct, kind, lay[c].dec, buf.data());
+        if (wrote != nb) text += "<<SIZE MISMATCH>>";
+        text.append((const char*)buf.data(), wrote);
+      }
+    }
+  }
+  if (text.size() > cap) return -1;
+  memcpy(out, text.data(), text.size());
+  *out_len = text.size();
+  return 0;
+}
+}

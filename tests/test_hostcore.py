@@ -183,3 +183,60 @@ def test_csv_model_fuzz_vs_pandas():
         if H.csv_parse(data, 1000) != want:
             bad.append(seed)
     assert not bad, bad
+
+
+def _sheet_oracle(sx, ss, nrows=1000):
+    from oracle import xlsx_reader as X
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        df = X.table_to_frame(X.sheet_table(sx, X.read_string_table(ss), nrows=nrows), nrows)
+        return None if df.empty else O.frame_to_text(df)
+
+
+def test_sheet_model_c1_golden():
+    import base64
+    import json
+    from pathlib import Path
+    g = Path(__file__).parent / "golden"
+    parts = json.loads((g / "attachment_parts.json").read_text())
+    gold = json.loads((g / "cache_rows.json").read_text())["12"]
+    st, text = H.sheet_parse(base64.b64decode(parts["sheets"][0]), base64.b64decode(parts["sst"]))
+    assert st == 0 and "=== Sheet: Sheet1 ===\n" + text == gold
+
+
+def test_sheet_model_fuzz_vs_oracle():
+    bad, unsup = [], 0
+    for seed in range(500):
+        sx, ss = corpus.sheet_xml_fuzz(seed) if seed % 2 else corpus.sheet_xml_doc(seed)
+        st, got = H.sheet_parse(sx, ss)
+        if st == 2:
+            unsup += 1
+            continue
+        if (None if st == 3 else got) != _sheet_oracle(sx, ss):
+            bad.append(seed)
+    assert not bad, bad
+    assert unsup < 60
+
+
+def test_strtod_exact_matches_python_float():
+    import ctypes as C
+    L = H.lib()
+    L.hc_strtod.argtypes = [C.c_char_p, C.c_uint32, C.POINTER(C.c_double)]
+    r = random.Random(4)
+    toks = ["285.0", "0.1", "1e23", "9007199254740993", "0.30000000000000004", "4.9e-324",
+            "2.4703282292062327e-324", "2.4703282292062328e-324", "1.7976931348623157e308",
+            "2.2250738585072011e-308", "123456789012345678901234567890", "1e-400"]
+    for _ in range(20000):
+        k = r.random()
+        if k < 0.4:
+            toks.append(repr(struct.unpack("<d", struct.pack("<Q", r.getrandbits(64)))[0]))
+        elif k < 0.7:
+            toks.append("%d.%d" % (r.randint(0, 10 ** r.randint(1, 18)), r.randint(0, 10 ** r.randint(1, 18))))
+        else:
+            toks.append("%.17g" % (r.uniform(-1, 1) * 10 ** r.randint(-30, 30)))
+    for t in toks:
+        if "nan" in t or "inf" in t:
+            continue
+        d = C.c_double()
+        assert L.hc_strtod(t.encode(), len(t), C.byref(d)), t
+        assert struct.pack("<d", d.value) == struct.pack("<d", float(t)), t
