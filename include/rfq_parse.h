@@ -72,6 +72,22 @@ int rfq_text_run(rfq_ctx* ctx);
  * reference's `max_excel_rows` (NULL → 1000 for every document). */
 int rfq_csv_run(rfq_ctx* ctx, const int64_t* max_rows);
 
+/* ---- sheet path: the GPU side of FileParser._parse_excel_sync (app/file_parser.py:214-252 →
+ * pd.read_excel → openpyxl read-only reader → pandas TextParser → dropna/fillna/to_string).
+ * The staged batch mixes worksheet parts (kind 0) and sharedStrings parts (kind 1) that the host
+ * inflated from the .xlsx zip; sst_of[d] is the batch index of the sharedStrings part of sheet d
+ * (-1 = none); max_rows[d] = the reference's max_excel_rows; date_ids[date_off[d]..date_off[d+1])
+ * are the cellXfs indices of sheet d's workbook whose number format is a date (styles.xml, read
+ * on the host).  Output per sheet = df.to_string(index=False) (the host adds the
+ * "=== Sheet: name ===" banner and joins sheets); status RFQ_DOC_EMPTY_SHEET where the reference
+ * skips the sheet (df.empty), RFQ_DOC_UNSUPPORTED for constructs not decoded on the GPU. */
+int rfq_sheets_run(rfq_ctx* ctx, const uint8_t* kind, const int32_t* sst_of, const int64_t* max_rows,
+                   const uint32_t* date_off, const uint32_t* date_ids);
+int rfq_sheets_parse(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets,
+                     const uint64_t* lengths, uint32_t n_docs, const uint8_t* kind,
+                     const int32_t* sst_of, const int64_t* max_rows, const uint32_t* date_off,
+                     const uint32_t* date_ids);
+
 /* ---- device → host copy of the last run's output ---- */
 int rfq_fetch(rfq_ctx* ctx);
 

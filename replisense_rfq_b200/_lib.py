@@ -31,6 +31,8 @@ SIGNATURES = {
     "rfq_text_run": (C.c_int, [C.c_void_p]),
     "rfq_csv_run": (C.c_int, [C.c_void_p, C.c_void_p]),
     "rfq_fetch": (C.c_int, [C.c_void_p]),
+    "rfq_sheets_run": (C.c_int, [C.c_void_p] * 6),
+    "rfq_sheets_parse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32] + [C.c_void_p] * 5),
     "rfq_text_parse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),
     "rfq_csv_parse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32,
                                 C.c_void_p]),

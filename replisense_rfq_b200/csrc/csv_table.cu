@@ -16,6 +16,7 @@
 #include "launch.h"
 #include "pipeline.h"
 #include "scan.cuh"
+#include "xlsx_fetch.cuh"
 
 namespace rfq {
 
@@ -34,8 +35,9 @@ __device__ __forceinline__ uint32_t ub_search(const uint32_t* __restrict__ base,
 
 __device__ __forceinline__ CellSrc fetch_cell(const TableArgs& a, const TDoc& D, uint32_t slot,
                                               uint32_t c) {
+  if (a.xcells) return xfetch(a, D, slot - D.r0 + 1, c);  // sheet mode: slot r0+1+row <-> sheet row row+2
   CellSrc s;
-  s.mode = 0; s.missing = false; s.p = a.arena; s.n = 0;
+  s.mode = 0; s.missing = false; s.p = a.arena; s.n = 0; s.bits = 0;
   uint32_t fbeg = __ldg(a.rec_fend + slot - 1);
   uint32_t nf = __ldg(a.rec_fend + slot) - fbeg;
   if (c >= nf) { s.missing = true; return s; }
@@ -432,6 +434,12 @@ static int table_grid(uint32_t n_items) {
   return (int)(n_items < g ? n_items : g);
 }
 
+void table_stat_init(const TableArgs& a, cudaStream_t s) {
+  if (a.n_stat)
+    RFQ_LAUNCH(csv_stat_init_kernel, (a.n_stat + 255) / 256, 256, 0, s, (ChunkStat*)a.stat,
+               (ChunkMeasure*)a.meas, a.n_stat);
+}
+
 void csv_table_classify(const TableArgs& a, cudaStream_t s) {
   prof_mark("csv_stat_init_kernel", s);
   if (a.n_stat)
@@ -444,7 +452,7 @@ void csv_table_classify(const TableArgs& a, cudaStream_t s) {
 void csv_table_measure(const TableArgs& a, cudaStream_t s) {
   if (a.n_docs == 0) return;
   prof_mark("csv_decide_kernel", s);
-  RFQ_LAUNCH(csv_decide_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
+  if (!a.xcells) RFQ_LAUNCH(csv_decide_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
   prof_mark("csv_measure_kernel", s);
   if (a.n_items) RFQ_LAUNCH(csv_measure_kernel, table_grid(a.n_items), 256, 0, s, a);
   prof_mark("csv_layout+rowbytes+scan", s);

@@ -27,6 +27,37 @@ inline bool utf8_valid_count(const std::string& s, uint32_t* ncp) {
   return t.utf8_ok;
 }
 
+// pandas' duplicate-name mangling (`a`, `a.1`, ...): named columns first, then the unnamed ones
+// (pandas/_libs/parsers.pyx _get_header; pandas/io/parsers/python_parser.py _infer_columns)
+inline void dedupe_names(std::vector<std::string>& raw, const std::vector<size_t>& unnamed) {
+  std::vector<size_t> order;
+  {
+    std::vector<bool> is_un(raw.size(), false);
+    for (size_t k : unnamed) is_un[k] = true;
+    for (size_t k = 0; k < raw.size(); ++k) if (!is_un[k]) order.push_back(k);
+    for (size_t k : unnamed) order.push_back(k);
+  }
+  std::unordered_map<std::string, int> counts;
+  auto in_header = [&](const std::string& s) {
+    for (auto& x : raw) if (x == s) return true;
+    return false;
+  };
+  for (size_t i2 : order) {
+    std::string col = raw[i2], old_col = col;
+    int cur = 0;
+    auto f = counts.find(col);
+    if (f != counts.end()) cur = f->second;
+    while (cur > 0) {
+      counts[old_col] = cur + 1;
+      col = old_col + "." + std::to_string(cur);
+      if (in_header(col)) cur += 1;
+      else { auto g = counts.find(col); cur = g == counts.end() ? 0 : g->second; }
+    }
+    raw[i2] = col;
+    counts[col] = cur + 1;
+  }
+}
+
 // Tokenise the first record of `doc` with the same DFA the kernels run.
 // latin1: the document bytes are latin-1 (the stream pandas tokenises is their UTF-8 transcode:
 // same ASCII structure, no BOM possible, high bytes become two-byte sequences in the names).
@@ -63,33 +94,7 @@ inline HeaderInfo parse_header(const uint8_t* doc, uint64_t len, uint32_t sep, b
     if (s.empty()) { s = "Unnamed: " + std::to_string(k); unnamed.push_back(k); }
     raw.push_back(s);
   }
-  // de-duplicate: named columns first, then the unnamed ones
-  std::vector<size_t> order;
-  {
-    std::vector<bool> is_un(raw.size(), false);
-    for (size_t k : unnamed) is_un[k] = true;
-    for (size_t k = 0; k < raw.size(); ++k) if (!is_un[k]) order.push_back(k);
-    for (size_t k : unnamed) order.push_back(k);
-  }
-  std::unordered_map<std::string, int> counts;
-  auto in_header = [&](const std::string& s) {
-    for (auto& x : raw) if (x == s) return true;
-    return false;
-  };
-  for (size_t i2 : order) {
-    std::string col = raw[i2], old_col = col;
-    int cur = 0;
-    auto f = counts.find(col);
-    if (f != counts.end()) cur = f->second;
-    while (cur > 0) {
-      counts[old_col] = cur + 1;
-      col = old_col + "." + std::to_string(cur);
-      if (in_header(col)) cur += 1;
-      else { auto g = counts.find(col); cur = g == counts.end() ? 0 : g->second; }
-    }
-    raw[i2] = col;
-    counts[col] = cur + 1;
-  }
+  dedupe_names(raw, unnamed);
   h.names = raw;
   h.ncp.resize(raw.size());
   for (size_t k = 0; k < raw.size(); ++k)

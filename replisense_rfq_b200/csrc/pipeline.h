@@ -114,12 +114,58 @@ struct TableArgs {
   uint32_t n_cols;
   unsigned long long* scan_tmp64; unsigned long long* out_total;
   unsigned long long* doc_out_off; unsigned long long* doc_out_len;  // [n_docs]
+  // sheet mode (xcells != nullptr): cells are typed records instead of CSV fields
+  const void* xcells;             // XCell[]
+  const uint32_t* x_row_c0;       // [n_row_elems+1] first cell of each <row> element
+  const uint32_t* x_r2elem;       // per document (TDoc.f0 + sheet row r) -> <row> element, ~0u = none
+  const uint8_t* x_str_arena;     // decoded shared strings
+  uint32_t* x_colflags;           // [n_cols] XF_* per output column
 };
+
 struct ColOut { int32_t cls, dec, sci; uint32_t width, cp_off; };
 
+void table_stat_init(const TableArgs& a, cudaStream_t s);
 void csv_table_classify(const TableArgs& a, cudaStream_t s);
 void csv_table_measure(const TableArgs& a, cudaStream_t s);   // decide + measure + layout + sizes
 void csv_table_emit(const TableArgs& a, uint8_t* out, cudaStream_t s);
+
+// ------------------------------------------------------------------------------------------
+// sheet XML / sharedStrings (xlsx_kernels.cu)
+struct XDocShape {
+  uint32_t n_rows, n_cells, n_si;        // <row>, <c>, <si> elements of the document
+  uint32_t row_base, cell_base, si_base; // global indices of its first element of each kind
+  uint32_t flags;                        // XU_* problems
+  uint32_t W, lastrow;                   // table width / last sheet row with data (within the cap)
+  uint32_t pad[3];
+};
+struct XmlArgs {
+  const uint8_t* arena;
+  const uint32_t* doc_off; const uint32_t* doc_len; const uint32_t* tile_base;  // ceil(len/512) tiles
+  uint32_t n_docs, n_tiles;
+  const uint8_t* kind;          // [n_docs] 0 = sheet, 1 = sharedStrings
+  const int32_t* sst_of;        // [n_docs] sharedStrings document of a sheet, -1 = none
+  const uint32_t* cap_rows;     // [n_docs] 1 + nrows (file_rows_needed)
+  const uint32_t* date_off;     // [n_docs+1] into date_ids
+  const uint32_t* date_ids;
+  uint32_t* tile_cnt[3];        // [n_tiles+1] per tile: rows, cells, si
+  uint32_t* tile_pre[3];        // [n_tiles+1]
+  uint32_t* scan_tmp;
+  XDocShape* shape;             // [n_docs]
+  uint32_t* row_base; uint32_t* cell_base; uint32_t* si_base;  // [n_docs+1] (for element -> doc search)
+  // after the totals are known
+  uint32_t n_rows, n_cells, n_si;
+  uint32_t* rowpos; uint32_t* row_c0; uint32_t* rownum;  // [n_rows+1]
+  uint32_t* cpos;                                        // [n_cells]
+  void* xcells;                                          // XCell[n_cells]
+  uint32_t* sipos; uint32_t* si_len; uint32_t* si_off;   // [n_si+1]
+  uint8_t* str_arena;                                    // decoded shared strings
+};
+void xml_count(const XmlArgs& a, cudaStream_t s);    // tile counts, prefixes, per-document bases
+void xml_decode(const XmlArgs& a, cudaStream_t s);   // positions, strings, rows, cells, W / lastrow
+void xlsx_table_classify(const TableArgs& a, cudaStream_t s);
+void xlsx_header_cells(const TableArgs& a, uint8_t* hdr_buf /* n_cols * 256 */, uint32_t* hdr_meta /* n_cols * 2 */,
+                       cudaStream_t s);
+void xlsx_scatter_rows(const XmlArgs& x, const uint32_t* r2_base /* [n_docs] */, uint32_t* r2elem, cudaStream_t s);
 
 // latin-1 -> UTF-8 stream transcode (second encoding of the trial loop)
 void latin1_count(const uint8_t* arena, const uint32_t* doc_off, const uint32_t* doc_len,

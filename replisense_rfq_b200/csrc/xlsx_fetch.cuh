@@ -1,0 +1,30 @@
+// Cell access of the sheet path for the shared table kernels (measure / emit): sheet row ->
+// <row> element -> typed cell record -> CellSrc.
+#pragma once
+#include "pipeline.h"
+#include "xlsx_cells.cuh"
+
+namespace rfq {
+
+__device__ __forceinline__ CellSrc xfetch(const TableArgs& a, const TDoc& D, uint32_t sheet_row, uint32_t c) {
+  CellSrc s; s.p = a.arena; s.n = 0; s.mode = CM_NULL; s.missing = false; s.bits = 0;
+  uint32_t e = __ldg(a.x_r2elem + D.f0 + sheet_row);
+  if (e == 0xFFFFFFFFu) return s;
+  uint32_t c0 = __ldg(a.x_row_c0 + e), c1 = __ldg(a.x_row_c0 + e + 1);
+  const XCell* xc = (const XCell*)a.xcells;
+  uint32_t k = c0 + c;
+  if (!(k < c1 && xc[k].col == c + 1)) {   // sparse row: binary search on the column
+    uint32_t lo = c0, hi = c1;
+    while (lo < hi) { uint32_t mid = (lo + hi) >> 1; if (xc[mid].col < c + 1) lo = mid + 1; else hi = mid; }
+    if (lo >= c1 || xc[lo].col != c + 1) return s;
+    k = lo;
+  }
+  XCell x = xc[k];
+  s.mode = (uint8_t)x.mode; s.bits = x.bits;
+  if (x.mode == CM_RAW) { s.p = a.x_str_arena + (uint32_t)(x.bits >> 32); s.n = (uint32_t)x.bits; }
+  else if (x.mode == CM_XML) { s.p = a.arena + D.off + (uint32_t)(x.bits >> 32); s.n = (uint32_t)x.bits; }
+  return s;
+}
+
+
+}  // namespace rfq

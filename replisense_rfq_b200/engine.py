@@ -167,6 +167,28 @@ class Engine:
                 raise EngineError(f"document {d}: unsupported construct on the GPU path (status {st})")
         return out
 
+    # -- sheets
+    def sheets_batch(self, docs: Sequence[bytes], kind, sst_of, max_rows=1000, date_ids=None) -> BatchResult:
+        """docs: worksheet XML parts (kind 0) and sharedStrings parts (kind 1); sst_of[d] = index of
+        the sharedStrings part of sheet d or -1; date_ids[d] = iterable of date style ids."""
+        n = len(docs)
+        kind = np.ascontiguousarray(kind, dtype=np.uint8)
+        sst_of = np.ascontiguousarray(sst_of, dtype=np.int32)
+        mr = self._mr(n, max_rows)
+        doff = np.zeros(n + 1, dtype=np.uint32)
+        flat = []
+        for d in range(n):
+            ids = sorted(date_ids[d]) if date_ids is not None and date_ids[d] else []
+            flat.extend(ids)
+            doff[d + 1] = len(flat)
+        dids = np.asarray(flat if flat else [0], dtype=np.uint32)
+        with self.lock:
+            a, off, ln = self._pack(docs)
+            self._check(self.lib.rfq_sheets_parse(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data, n,
+                                                  kind.ctypes.data, sst_of.ctypes.data, mr.ctypes.data,
+                                                  doff.ctypes.data, dids.ctypes.data), "rfq_sheets_parse")
+            return BatchResult(self)
+
     # -- pre-packed pinned arena (no Python-side copies): what a high-throughput caller uses
     def _mr(self, n, max_rows):
         if np.isscalar(max_rows):

@@ -143,7 +143,10 @@ class FileParser:
         try:
             from . import xlsx_host
             parts = xlsx_host.open_workbook(Path(file_path).read_bytes())
-            return xlsx_host.parse_workbooks(self.engine, [parts], self.max_excel_rows)[0]
+            text = xlsx_host.parse_workbooks(self.engine, [parts], self.max_excel_rows)[0]
+            if isinstance(text, Exception):
+                raise text
+            return text
         except Exception as e:
             raise FileParsingError(f"Excel parsing failed: {str(e)}")
 
@@ -174,6 +177,8 @@ class FileParser:
                 good = [b for b in books if not isinstance(b, Exception)]
                 texts = iter(xlsx_host.parse_workbooks(self.engine, good, self.max_excel_rows))
                 res = [b if isinstance(b, Exception) else next(texts) for b in books]
+                res = [FileParsingError(f"Excel parsing failed: {r}") if isinstance(r, EngineError) else r
+                       for r in res]
             else:
                 res = [FileParsingError(f"Unsupported file type: .{k}")] * len(batch)
             for i, r in zip(idx, res):

@@ -1,0 +1,115 @@
+"""Host side of the .xlsx path: zip container + workbook plumbing (SURVEY.md §8 a7.1 — stays on
+the host), then batches of inflated worksheet / sharedStrings parts to the GPU, then the
+reference's own assembly of the per-sheet texts (app/file_parser.py:227-252).
+
+What stays here mirrors openpyxl's ExcelReader (openpyxl/reader/excel.py): workbook.xml sheet
+names + order, workbook.xml.rels targets, the sharedStrings part, and which cellXfs of styles.xml
+carry a date number format (openpyxl/styles/numbers.py is_date_format) — O(parts) work on small
+XML files.  Cell decoding, type inference and formatting all happen on the device.
+"""
+from __future__ import annotations
+
+import io
+import posixpath
+import re
+import zipfile
+import xml.etree.ElementTree as ET
+
+from . import _lib
+
+_NS = "http://schemas.openxmlformats.org/spreadsheetml/2006/main"
+_NS_REL = "http://schemas.openxmlformats.org/officeDocument/2006/relationships"
+_NS_PKG = "http://schemas.openxmlformats.org/package/2006/relationships"
+_EMPTY = "Excel file appears to be empty or unreadable"  # app/file_parser.py:250
+
+_BUILTIN_DATE_IDS = set(range(14, 23)) | {45, 46, 47}
+_STRIP = re.compile(r"\"[^\"]*\"|\[(?!hh?\]|mm?\]|ss?\])[^\]]*\]")
+
+
+def _is_date_format(code) -> bool:
+    if code is None:
+        return False
+    code = _STRIP.sub("", code.split(";")[0])
+    return re.search(r"(?<![_\\])[dmhysDMHYS]", code) is not None
+
+
+def _date_style_ids(styles_xml) -> "set[int]":
+    if not styles_xml:
+        return set()
+    root = ET.fromstring(styles_xml)
+    custom = {}
+    nf = root.find("{%s}numFmts" % _NS)
+    if nf is not None:
+        for el in nf.findall("{%s}numFmt" % _NS):
+            custom[int(el.get("numFmtId"))] = el.get("formatCode")
+    out = set()
+    xfs = root.find("{%s}cellXfs" % _NS)
+    if xfs is not None:
+        for idx, xf in enumerate(xfs.findall("{%s}xf" % _NS)):
+            fid = int(xf.get("numFmtId", "0"))
+            if (fid in custom and _is_date_format(custom[fid])) or (fid not in custom and fid in _BUILTIN_DATE_IDS):
+                out.add(idx)
+    return out
+
+
+class Workbook:
+    __slots__ = ("sheet_names", "sheets", "sst", "date_styles")
+
+    def __init__(self, sheet_names, sheets, sst, date_styles):
+        self.sheet_names, self.sheets, self.sst, self.date_styles = sheet_names, sheets, sst, date_styles
+
+
+def open_workbook(data: bytes) -> Workbook:
+    z = zipfile.ZipFile(io.BytesIO(data))
+    names = set(z.namelist())
+    rels = {}
+    if "xl/_rels/workbook.xml.rels" in names:
+        for r in ET.fromstring(z.read("xl/_rels/workbook.xml.rels")).findall("{%s}Relationship" % _NS_PKG):
+            t = r.get("Target")
+            t = t[1:] if t.startswith("/") else posixpath.normpath(posixpath.join("xl", t))
+            rels[r.get("Id")] = (r.get("Type"), t)
+    root = ET.fromstring(z.read("xl/workbook.xml"))
+    sheet_names, sheets = [], []
+    for sh in root.find("{%s}sheets" % _NS).findall("{%s}sheet" % _NS):
+        typ, target = rels[sh.get("{%s}id" % _NS_REL)]
+        if not typ.endswith("/worksheet"):
+            continue
+        sheet_names.append(sh.get("name"))
+        sheets.append(z.read(target))
+    sst = None
+    for typ, target in rels.values():
+        if typ.endswith("/sharedStrings") and target in names:
+            sst = z.read(target)
+    if sst is None and "xl/sharedStrings.xml" in names:
+        sst = z.read("xl/sharedStrings.xml")
+    styles = z.read("xl/styles.xml") if "xl/styles.xml" in names else None
+    return Workbook(sheet_names, sheets, sst, _date_style_ids(styles))
+
+
+def parse_workbooks(engine, books, max_rows: int = 1000) -> "list":
+    """raw_text of every workbook (one GPU batch for all their parts); an EngineError instance in
+    place of the text where a sheet uses a construct that is not decoded on the GPU path."""
+    docs, kind, sst_of, dates, owner = [], [], [], [], []
+    for b, wb in enumerate(books):
+        sst_idx = -1
+        if wb.sst is not None:
+            sst_idx = len(docs)
+            docs.append(wb.sst); kind.append(1); sst_of.append(-1); dates.append(()); owner.append((b, None))
+        for k, xml in enumerate(wb.sheets):
+            docs.append(xml); kind.append(0); sst_of.append(sst_idx); dates.append(wb.date_styles)
+            owner.append((b, k))
+    res = engine.sheets_batch(docs, kind, sst_of, max_rows, dates) if docs else None
+    from .engine import EngineError
+    parts = [[] for _ in books]
+    failed = {}
+    for d, (b, k) in enumerate(owner):
+        if k is None:
+            continue
+        st = int(res.status[d])
+        if st == _lib.DOC_EMPTY_SHEET:
+            continue  # `if df.empty: continue` (app/file_parser.py:228-229)
+        if st != _lib.DOC_OK:
+            failed[b] = EngineError(f"sheet {books[b].sheet_names[k]!r}: construct not decoded on the GPU path")
+            continue
+        parts[b].append(f"=== Sheet: {books[b].sheet_names[k]} ===\n" + res.doc_str(d))
+    return [failed[b] if b in failed else ("\n\n".join(p) if p else _EMPTY) for b, p in enumerate(parts)]

@@ -1,0 +1,128 @@
+"""GPU parity: sheet XML + sharedStrings path vs the cache.db goldens and the oracle."""
+import base64
+import io
+import json
+import warnings
+import zipfile
+from pathlib import Path
+
+import pytest
+
+from oracle import file_parser_oracle as O
+from oracle import xlsx_reader as X
+from tests import corpus
+
+pytestmark = pytest.mark.gpu
+G = Path(__file__).parent / "golden"
+
+
+@pytest.fixture(scope="module")
+def eng():
+    from replisense_rfq_b200 import Engine, build
+    build.build()
+    return Engine(0)
+
+
+def _oracle(sx, ss, nrows=1000):
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        df = X.table_to_frame(X.sheet_table(sx, X.read_string_table(ss), nrows=nrows), nrows)
+        return None if df.empty else O.frame_to_text(df)
+
+
+def _parts():
+    p = json.loads((G / "attachment_parts.json").read_text())
+    return {k: ([base64.b64decode(x) for x in v] if isinstance(v, list) and k == "sheets" else v)
+            for k, v in p.items()}
+
+
+def test_c1_golden_sheet(eng):
+    """Config C1: the reference's own xlsx asset, pinned by .cache/42/cache.db row 12."""
+    p = _parts()
+    gold = json.loads((G / "cache_rows.json").read_text())["12"]
+    r = eng.sheets_batch([base64.b64decode(p["sst"]), p["sheets"][0]], [1, 0], [-1, 0], 1000)
+    assert int(r.status[1]) == 0
+    assert "=== Sheet: Sheet1 ===\n" + r.doc_str(1) == gold
+
+
+def test_c1_through_file_parser(eng, tmp_path):
+    """The same asset as an .xlsx file through FileParser.parse_file_async (zip rebuilt from the
+    committed parts)."""
+    import asyncio
+    from replisense_rfq_b200 import FileParser
+    p = _parts()
+    path = tmp_path / "email_4 attachment.xlsx"
+    with zipfile.ZipFile(path, "w", zipfile.ZIP_DEFLATED) as z:
+        z.writestr("xl/workbook.xml", base64.b64decode(p["workbook"]))
+        z.writestr("xl/_rels/workbook.xml.rels", base64.b64decode(p["rels"]))
+        z.writestr("xl/styles.xml", base64.b64decode(p["styles"]))
+        z.writestr("xl/sharedStrings.xml", base64.b64decode(p["sst"]))
+        z.writestr("xl/worksheets/sheet1.xml", p["sheets"][0])
+    res = asyncio.run(FileParser(engine=eng).parse_file_async(str(path)))
+    assert res["raw_text"] == json.loads((G / "cache_rows.json").read_text())["12"]
+    assert res["parsing_method"] == "async_xlsx" and res["source_file"] == "email_4 attachment.xlsx"
+    assert res["raw_text"] == O.parse_excel_path(path, 1000)
+
+
+def test_row14_golden(eng):
+    """cache.db row 14: 23-row sheet with a float column (20.00 ... 146.50)."""
+    gold = json.loads((G / "cache_rows.json").read_text())["14"]
+    strings, rows = [], []
+
+    def sid(s):
+        strings.append(s)
+        return len(strings) - 1
+    hdr = ["Part Number", "Description", "Quantity", "Target Price (INR)"]
+    rows.append("".join('<c r="%s1" t="s"><v>%d</v></c>' % (corpus.col_letters(c), sid(h)) for c, h in enumerate(hdr)))
+    for i in range(23):
+        r = i + 2
+        rows.append('<c r="A%d" t="s"><v>%d</v></c><c r="B%d" t="s"><v>%d</v></c><c r="C%d"><v>%d</v></c>'
+                    '<c r="D%d"><v>%s</v></c>' % (r, sid(f"MP-{1000 + i}"), r,
+                                                   sid(f"Dummy Part {i + 1} - Industrial component"), r,
+                                                   100 * (i + 1), r, repr(20 + 5.75 * i)))
+    sx = ('<worksheet xmlns="http://schemas.openxmlformats.org/spreadsheetml/2006/main"><sheetData>' +
+          "".join('<row r="%d">%s</row>' % (i + 1, x) for i, x in enumerate(rows)) + "</sheetData></worksheet>").encode()
+    ss = ('<sst xmlns="http://schemas.openxmlformats.org/spreadsheetml/2006/main">' +
+          "".join("<si><t>%s</t></si>" % corpus.xml_escape(s) for s in strings) + "</sst>").encode()
+    r = eng.sheets_batch([ss, sx], [1, 0], [-1, 0], 1000)
+    assert int(r.status[1]) == 0 and "=== Sheet: Sheet1 ===\n" + r.doc_str(1) == gold
+
+
+def _batch(eng, pairs, nrows=1000):
+    docs, kind, sst_of = [], [], []
+    for sx, ss in pairs:
+        docs += [ss, sx]; kind += [1, 0]; sst_of += [-1, len(docs) - 2]
+    r = eng.sheets_batch(docs, kind, sst_of, nrows)
+    out = []
+    for i in range(len(pairs)):
+        st = int(r.status[2 * i + 1])
+        out.append((st, r.doc_str(2 * i + 1) if st == 0 else None))
+    return out
+
+
+def test_sheet_corpus_c3_style(eng):
+    pairs = [corpus.sheet_xml_doc(s, 5, 300) for s in range(400)]
+    got = _batch(eng, pairs)
+    bad = [i for i, ((st, g), (sx, ss)) in enumerate(zip(got, pairs)) if (None if st == 3 else g) != _oracle(sx, ss) or st == 2]
+    assert not bad, bad[:10]
+
+
+def test_sheet_fuzz(eng):
+    pairs = [corpus.sheet_xml_fuzz(s) for s in range(1500)]
+    got = _batch(eng, pairs)
+    bad, unsup = [], 0
+    for i, ((st, g), (sx, ss)) in enumerate(zip(got, pairs)):
+        if st == 2:
+            unsup += 1
+            continue
+        if (None if st == 3 else g) != _oracle(sx, ss):
+            bad.append(i)
+    assert not bad, bad[:10]
+    assert unsup < 0.2 * len(pairs)
+
+
+def test_sheet_nrows_cap(eng):
+    sx, ss = corpus.sheet_xml_doc(7, 200, 300)
+    for cap in (1, 10, 57):
+        (st, g), = _batch(eng, [(sx, ss)], cap)
+        assert (None if st == 3 else g) == _oracle(sx, ss, cap), cap
