@@ -264,7 +264,7 @@ __device__ __forceinline__ int format_number(const CellSrc& s, int ct, int kind,
                                              const TextInfo& t, uint8_t* buf) {
   switch (kind) {
     case PR_BOOL: {
-      const char* w = bool_token(t.nbytes, t.first8) == 1 ? "True" : "False";
+      const char* w = cell_bool(s, t) == 1 ? "True" : "False";
       int k = 0;
       while (w[k]) { buf[k] = (uint8_t)w[k]; ++k; }
       return k;
@@ -299,7 +299,7 @@ __device__ __forceinline__ int format_number(const CellSrc& s, int ct, int kind,
 __device__ __forceinline__ void emit_cell(const CellSrc& src, int ct, int kind, int dec,
                                           uint32_t width, uint8_t* field, bool fill) {
   TextInfo t = cell_text(src);
-  bool na = is_na_token(t.nbytes, t.first8) && ct != CT_STRNF;
+  bool na = cell_is_nan(src, t, ct);
   if (na) { if (fill) for (uint32_t q = 0; q < width; ++q) field[q] = ' '; return; }
   if (kind == PR_STR) {
     uint32_t ncp = t.ncp + t.nesc, pad = width - ncp;

@@ -131,6 +131,8 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
     slot_r0[d] = (uint32_t)n_slots; r2_base[d] = (uint32_t)n_r2; item_base[d] = (uint32_t)n_items;
     T.item_base = (uint32_t)n_items;
     if (kind[d] == 1) { n_slots += 1; continue; }           // sharedStrings part: no output of its own
+    n_r2 += (uint64_t)sh.lastrow + 1;                       // every sheet owns its row map (the scatter
+                                                            // kernel writes it for all unflagged sheets)
     uint32_t fl = sh.flags;
     if (sst_of[d] >= 0) fl |= h_shape[sst_of[d]].flags;
     if (fl || sh.W > 1024) { c->r_status[d] = RFQ_DOC_UNSUPPORTED; n_slots += 1; continue; }
@@ -143,7 +145,6 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
     n_cols += T.W;
     n_items += (T.n_data + T.rb - 1) / T.rb;
     n_slots += (uint64_t)T.n_data + 2;
-    n_r2 += (uint64_t)sh.lastrow + 1;
   }
   item_base[n] = (uint32_t)n_items; slot_r0[n] = (uint32_t)n_slots; r2_base[n] = (uint32_t)n_r2;
   if (n_slots >= (1ull << 31) || n_items >= (1ull << 31)) { c->err = "batch too large"; return RFQ_ERR_ARG; }
