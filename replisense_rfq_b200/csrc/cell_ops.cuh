@@ -18,8 +18,58 @@ struct CellSrc {
   uint32_t n;
   uint8_t mode;     // CM_*
   bool missing;     // short row: pandas pads with an empty token
+  bool clean;       // text known to be plain ASCII without control bytes (set by csv_simplify)
   uint64_t bits;    // CM_INT: int64, CM_FLOAT: double bits, CM_BOOL: 0/1
 };
+
+// 8 bytes at p (little endian), bytes at index >= rem forced to zero. On the device this is two
+// aligned 8-byte loads + a funnel shift (the arenas carry 64 bytes of slack, so reading up to 15
+// bytes past p is safe); on the host a bounded byte loop.
+RFQ_HD uint64_t load8_masked(const uint8_t* p, uint32_t rem) {
+  uint64_t x;
+#ifdef __CUDA_ARCH__
+  const unsigned long long* q = (const unsigned long long*)((uintptr_t)p & ~(uintptr_t)7);
+  uint32_t sh = (uint32_t)((uintptr_t)p & 7u) * 8u;
+  x = __ldg(q);
+  if (sh) x = (x >> sh) | ((uint64_t)__ldg(q + 1) << (64u - sh));
+#else
+  x = 0;
+  for (uint32_t i = 0; i < 8 && i < rem; ++i) x |= (uint64_t)p[i] << (8 * i);
+#endif
+  if (rem < 8) x &= (1ull << (8 * rem)) - 1ull;
+  return x;
+}
+
+// true iff every one of the n bytes at p is ASCII >= 0x0E and none equals `forbid`
+RFQ_HD bool span_is_clean(const uint8_t* p, uint32_t n, uint32_t forbid) {
+  const uint64_t ones = 0x0101010101010101ull, highs = 0x8080808080808080ull;
+  for (uint32_t i = 0; i < n; i += 8) {
+    uint32_t rem = n - i;
+    uint64_t x = load8_masked(p + i, rem);
+    if (rem < 8) x |= 0x2020202020202020ull & ~((1ull << (8 * rem)) - 1ull);  // padding = blanks
+    uint64_t bad = x & highs;                              // non-ASCII
+    bad |= (x - ones * 0x0E) & ~x & highs;                 // a byte < 0x0E (NUL, \t, \n, \r, ...)
+    uint64_t y = x ^ (ones * forbid);
+    bad |= (y - ones) & ~y & highs;                        // a byte == forbid
+    if (bad) return false;
+  }
+  return true;
+}
+
+// Turn a CSV field into a plain span when no quote processing can change it: unquoted clean
+// ASCII, or "..." around clean ASCII without inner quotes.  Everything downstream (NA match,
+// parsers, widths, copy-out) then runs without the quote state machine.
+RFQ_HD void csv_simplify(CellSrc& s) {
+  if (s.mode != CM_CSV || s.missing) return;
+  if (s.n == 0) { s.mode = CM_RAW; s.clean = true; return; }
+  if (s.p[0] != '"') {
+    if (span_is_clean(s.p, s.n, 0xFF)) { s.mode = CM_RAW; s.clean = true; }
+    return;
+  }
+  if (s.n >= 2 && s.p[s.n - 1] == '"' && span_is_clean(s.p + 1, s.n - 2, '"')) {
+    s.p += 1; s.n -= 2; s.mode = CM_RAW; s.clean = true;
+  }
+}
 RFQ_HD bool cell_is_text(const CellSrc& s) { return s.mode == CM_CSV || s.mode == CM_RAW || s.mode == CM_XML; }
 RFQ_HD double bits_as_double(uint64_t b) {
 #ifdef __CUDA_ARCH__
@@ -38,6 +88,11 @@ RFQ_HD TextInfo cell_text(const CellSrc& s) {
   if (s.missing || !cell_is_text(s)) {
     TextInfo t; t.nbytes = t.ncp = t.nesc = 0; t.first8 = 0; t.utf8_ok = true; t.has_fchar = false;
     if (!s.missing && s.mode != CM_NULL) { t.nbytes = 1; t.ncp = 1; t.first8 = '#'; }  // typed value: never an NA token
+    return t;
+  }
+  if (s.clean) {
+    TextInfo t; t.nbytes = s.n; t.ncp = s.n; t.nesc = 0; t.utf8_ok = true; t.has_fchar = false;
+    t.first8 = s.n ? load8_masked(s.p, s.n) : 0;
     return t;
   }
   return RFQ_WITH_ITER(s, scan_text);
@@ -252,6 +307,14 @@ RFQ_HD uint32_t print_cell(const CellSrc& s, int ctype, int kind, int dec, uint8
     if (cell_is_nan(s, t, ctype)) return 0;
     uint32_t k = 0;
     int c;
+    if (s.clean) {
+      for (uint32_t i = 0; i < s.n; i += 8) {
+        uint64_t x = load8_masked(s.p + i, s.n - i);
+        uint32_t m = s.n - i < 8 ? s.n - i : 8;
+        for (uint32_t q = 0; q < m; ++q) out[i + q] = (uint8_t)(x >> (8 * q));
+      }
+      return s.n;
+    }
     if (s.mode == CM_XML) {
       XmlIter it(s.p, s.n);
       while ((c = it.next()) >= 0) {

@@ -37,7 +37,7 @@ __device__ __forceinline__ CellSrc fetch_cell(const TableArgs& a, const TDoc& D,
                                               uint32_t c) {
   if (a.xcells) return xfetch(a, D, slot - D.r0 + 1, c);  // sheet mode: slot r0+1+row <-> sheet row row+2
   CellSrc s;
-  s.mode = 0; s.missing = false; s.p = a.arena; s.n = 0; s.bits = 0;
+  s.mode = 0; s.missing = false; s.clean = false; s.p = a.arena; s.n = 0; s.bits = 0;
   uint32_t fbeg = __ldg(a.rec_fend + slot - 1);
   uint32_t nf = __ldg(a.rec_fend + slot) - fbeg;
   if (c >= nf) { s.missing = true; return s; }
@@ -45,6 +45,7 @@ __device__ __forceinline__ CellSrc fetch_cell(const TableArgs& a, const TDoc& D,
   uint32_t en = __ldg(a.fend + fbeg + c);
   s.p = a.arena + D.off + st;
   s.n = en - st;
+  csv_simplify(s);
   return s;
 }
 

@@ -7,7 +7,7 @@
 namespace rfq {
 
 __device__ __forceinline__ CellSrc xfetch(const TableArgs& a, const TDoc& D, uint32_t sheet_row, uint32_t c) {
-  CellSrc s; s.p = a.arena; s.n = 0; s.mode = CM_NULL; s.missing = false; s.bits = 0;
+  CellSrc s; s.p = a.arena; s.n = 0; s.mode = CM_NULL; s.missing = false; s.clean = false; s.bits = 0;
   uint32_t e = __ldg(a.x_r2elem + D.f0 + sheet_row);
   if (e == 0xFFFFFFFFu) return s;
   uint32_t c0 = __ldg(a.x_row_c0 + e), c1 = __ldg(a.x_row_c0 + e + 1);

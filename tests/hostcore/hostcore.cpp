@@ -139,12 +139,13 @@ int csv_attempt(const uint8_t* doc, uint64_t len, uint32_t sep, int64_t nrows, s
   uint32_t nch = (ndata + bl - 1) / bl;
   auto cell = [&](uint32_t row, uint32_t c) {
     const Rec& R = recs[row + 1];
-    CellSrc s; s.mode = 0; s.missing = false; s.p = doc; s.n = 0;
+    CellSrc s; s.mode = 0; s.missing = false; s.clean = false; s.bits = 0; s.p = doc; s.n = 0;
     uint32_t nf = R.f1 - R.f0;
     if (c >= nf) { s.missing = true; return s; }
     uint64_t a = c == 0 ? R.start : fend[R.f0 + c - 1] + 1;
     uint64_t b = fend[R.f0 + c];
     s.p = doc + a; s.n = (uint32_t)(b - a);
+    csv_simplify(s);
     return s;
   };
   std::vector<ChunkStat> stat((size_t)nch * W, ChunkStat{0, RFQ_NO_ROW, RFQ_NO_ROW, 0});
@@ -377,7 +378,7 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
   std::vector<int> r2e(lastrow + 1, -1);
   for (size_t k = 0; k < rows.size(); ++k) if (rows[k].r <= lastrow) r2e[rows[k].r] = (int)k;
   auto cell = [&](uint32_t r, uint32_t c) {  // r 1-based sheet row, c 0-based column
-    CellSrc s; s.p = nullptr; s.n = 0; s.mode = CM_NULL; s.missing = false; s.bits = 0;
+    CellSrc s; s.p = nullptr; s.n = 0; s.mode = CM_NULL; s.missing = false; s.clean = false; s.bits = 0;
     int k = r2e[r];
     if (k < 0) return s;
     for (uint32_t q = rows[k].c0; q < rows[k].c1; ++q) if (cells[q].col == c + 1) {
