@@ -12,7 +12,22 @@ namespace rfq {
 // A cell source: where the token bytes live and how to decode them.
 // Text modes carry a byte span; typed modes (sheet cells already typed by the XML: numbers,
 // booleans, empty / error cells) carry their value in `bits`.
-enum { CM_CSV = 0, CM_RAW = 1, CM_INT = 2, CM_FLOAT = 3, CM_BOOL = 4, CM_XML = 5, CM_NULL = 6 };
+// CM_CSVQ: inside of a quoted CSV field that is clean ASCII and whose only quotes are "" pairs
+// (span = between the outer quotes, bits = decoded length)
+enum { CM_CSV = 0, CM_RAW = 1, CM_INT = 2, CM_FLOAT = 3, CM_BOOL = 4, CM_XML = 5, CM_NULL = 6, CM_CSVQ = 7 };
+
+// decoded bytes of a CM_CSVQ span: every "" is one "
+struct PairIter {
+  const uint8_t* p;
+  const uint8_t* e;
+  RFQ_HD PairIter(const uint8_t* b, uint32_t n) : p(b), e(b + n) {}
+  RFQ_HD int next() {
+    if (p >= e) return -1;
+    int c = *p++;
+    if (c == '"') ++p;
+    return c;
+  }
+};
 struct CellSrc {
   const uint8_t* p;
   uint32_t n;
@@ -66,11 +81,18 @@ RFQ_HD void csv_simplify(CellSrc& s) {
     if (span_is_clean(s.p, s.n, 0xFF)) { s.mode = CM_RAW; s.clean = true; }
     return;
   }
-  if (s.n >= 2 && s.p[s.n - 1] == '"' && span_is_clean(s.p + 1, s.n - 2, '"')) {
-    s.p += 1; s.n -= 2; s.mode = CM_RAW; s.clean = true;
+  if (s.n < 2 || s.p[s.n - 1] != '"') return;
+  if (span_is_clean(s.p + 1, s.n - 2, '"')) { s.p += 1; s.n -= 2; s.mode = CM_RAW; s.clean = true; return; }
+  if (!span_is_clean(s.p + 1, s.n - 2, 0xFF)) return;
+  // clean ASCII with quotes inside: fine iff they all come as "" pairs
+  uint32_t pairs = 0;
+  for (uint32_t i = 1; i + 1 < s.n; ++i) {
+    if (s.p[i] != '"') continue;
+    if (i + 2 < s.n && s.p[i + 1] == '"') { ++pairs; ++i; } else return;
   }
+  s.p += 1; s.n -= 2; s.mode = CM_CSVQ; s.bits = s.n - pairs;
 }
-RFQ_HD bool cell_is_text(const CellSrc& s) { return s.mode == CM_CSV || s.mode == CM_RAW || s.mode == CM_XML; }
+RFQ_HD bool cell_is_text(const CellSrc& s) { return s.mode == CM_CSV || s.mode == CM_RAW || s.mode == CM_XML || s.mode == CM_CSVQ; }
 RFQ_HD double bits_as_double(uint64_t b) {
 #ifdef __CUDA_ARCH__
   return __longlong_as_double((long long)b);
@@ -82,6 +104,7 @@ RFQ_HD double bits_as_double(uint64_t b) {
 #define RFQ_WITH_ITER(src, F, ...)                                            \
   ((src).mode == CM_CSV ? F(CsvIter((src).p, (src).n), ##__VA_ARGS__)         \
    : (src).mode == CM_XML ? F(XmlIter((src).p, (src).n), ##__VA_ARGS__)       \
+   : (src).mode == CM_CSVQ ? F(PairIter((src).p, (src).n), ##__VA_ARGS__)     \
                           : F(RawIter((src).p, (src).n), ##__VA_ARGS__))
 
 RFQ_HD TextInfo cell_text(const CellSrc& s) {
@@ -93,6 +116,13 @@ RFQ_HD TextInfo cell_text(const CellSrc& s) {
   if (s.clean) {
     TextInfo t; t.nbytes = s.n; t.ncp = s.n; t.nesc = 0; t.utf8_ok = true; t.has_fchar = false;
     t.first8 = s.n ? load8_masked(s.p, s.n) : 0;
+    return t;
+  }
+  if (s.mode == CM_CSVQ) {
+    TextInfo t; t.nbytes = (uint32_t)s.bits; t.ncp = t.nbytes; t.nesc = 0; t.utf8_ok = true; t.has_fchar = false;
+    t.first8 = 0;
+    PairIter it(s.p, s.n);
+    for (int k = 0; k < 8; ++k) { int c = it.next(); if (c < 0) break; t.first8 |= (uint64_t)c << (8 * k); }
     return t;
   }
   return RFQ_WITH_ITER(s, scan_text);
@@ -314,6 +344,11 @@ RFQ_HD uint32_t print_cell(const CellSrc& s, int ctype, int kind, int dec, uint8
         for (uint32_t q = 0; q < m; ++q) out[i + q] = (uint8_t)(x >> (8 * q));
       }
       return s.n;
+    }
+    if (s.mode == CM_CSVQ) {
+      PairIter it(s.p, s.n);
+      while ((c = it.next()) >= 0) out[k++] = (uint8_t)c;
+      return k;
     }
     if (s.mode == CM_XML) {
       XmlIter it(s.p, s.n);
