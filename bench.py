@@ -147,6 +147,12 @@ def main():
     from replisense_rfq_b200 import Engine, build
     from replisense_rfq_b200.engine import PinnedArena
 
+    # stdout must carry exactly ONE JSON line: anything libraries print while we work (NCCL prints
+    # its version banner on stdout) goes to stderr until the result is ready
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
+
     if rank == 0 or world == 1:
         build.build()
     torch.cuda.set_device(local_rank)
@@ -253,6 +259,10 @@ def main():
            "csv_classify_kernel": nbytes, "csv_tilefn_kernel": nbytes, "csv_count_kernel": nbytes,
            "csv_index_kernel": nbytes}.get(dom, nbytes)
     achieved = alg / (kern[dom] / 1e3) / 1e9
+    traffic = None
+    tf = ROOT / "profiles" / "traffic_r01.json"
+    if tf.exists() and args.rows == 1_000_000:
+        traffic = json.loads(tf.read_text()).get(dom)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": t_dev / args.steps * 1e3, "higher_is_better": True,
@@ -267,7 +277,7 @@ def main():
                 "to_python_str_ms": t_str * 1e3},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "unit": "GB/s",
-                     "frac": achieved / hbm, "traffic": None, "peak_source": hbm_src,
+                     "frac": achieved / hbm, "traffic": traffic, "peak_source": hbm_src,
                      "algorithmic_bytes_per_launch": alg, "kernel_ms": kern[dom]},
         "kernel_ms_per_step": {k: round(v / args.steps, 4) for k, v in sorted(prof_acc.items(), key=lambda x: -x[1])},
         "clocks": sampler.summary(),
@@ -283,8 +293,12 @@ def main():
                                           "FileParser._parse_csv_sync (pandas read_csv + to_string), "
                                           f"{dt:.2f} s on one host core of {os.cpu_count()}",
                                 "cells_per_s": rows * 8 / dt}
-    print(json.dumps(line))
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
+    os.close(saved_stdout)
+    print(json.dumps(line), flush=True)
     if world > 1:
+        os.dup2(2, 1)
         dist.barrier()
         dist.destroy_process_group()
 

@@ -232,16 +232,49 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
   RFQ_CK(c, cudaMemcpyAsync(h_olen, ta.doc_out_len, 8ull * m, cudaMemcpyDeviceToHost, s));
   RFQ_CK(c, cudaMemcpyAsync(h_keep, ta.n_keep, 4ull * m, cudaMemcpyDeviceToHost, s));
   RFQ_CK(c, cudaMemcpyAsync(h_flags, ta.doc_flags, 4ull * m, cudaMemcpyDeviceToHost, s));
+  // slice boundaries for the overlapped device->host copy (e2e path): K slices of work items, the
+  // output offset where each slice starts is row_off of its first row
+  const int K = 4;
+  const bool overlap = c->overlap_fetch && c->segs.empty() && c->copy_stream && n_items >= 64;
+  uint32_t cut_item[K + 1];
+  unsigned long long* h_cut = (unsigned long long*)(hd + 128);
+  if (overlap) {
+    for (int k = 0; k <= K; ++k) cut_item[k] = (uint32_t)(n_items * k / K);
+    for (int k = 1; k < K; ++k) {
+      uint32_t it = cut_item[k];
+      uint32_t d = (uint32_t)(std::upper_bound(item_base.begin(), item_base.begin() + m, it) - item_base.begin()) - 1;
+      uint32_t slot = td[d].r0 + 1 + (it - item_base[d]) * td[d].rb;
+      RFQ_CK(c, cudaMemcpyAsync(h_cut + k, ta.row_off + slot, 8, cudaMemcpyDeviceToHost, s));
+    }
+  }
   RFQ_CK(c, cudaStreamSynchronize(s));
   const uint64_t total = *h_total;
   // ---- 6. emit
   uint8_t* d_text = c->pool.alloc<uint8_t>(total + 64);
   if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
-  if (total) csv_table_emit(ta, d_text, s);
+  const uint64_t host_base = c->out_total;
+  bool copied = false;
+  if (total && overlap && total >= (4u << 20)) {
+    RFQ_CK(c, c->h_out.reserve(total + 16));
+    h_cut[0] = 0; h_cut[K] = total;
+    csv_table_emit_header(ta, d_text, s);
+    for (int k = 0; k < K; ++k) {
+      csv_table_emit_items(ta, d_text, cut_item[k], cut_item[k + 1], s);
+      RFQ_CK(c, cudaEventRecord(c->ev_slice[k], s));
+      RFQ_CK(c, cudaStreamWaitEvent(c->copy_stream, c->ev_slice[k], 0));
+      uint64_t b0 = h_cut[k], b1 = h_cut[k + 1];
+      if (b1 > b0)
+        RFQ_CK(c, cudaMemcpyAsync((uint8_t*)c->h_out.p + b0, d_text + b0, b1 - b0, cudaMemcpyDeviceToHost,
+                                  c->copy_stream));
+    }
+    copied = true;
+  } else if (total) {
+    csv_table_emit(ta, d_text, s);
+  }
   c->prof.mark("host+sync", s);
   RFQ_CK(c, cudaGetLastError());
-  const uint64_t host_base = c->out_total;
   c->segs.push_back({d_text, total, host_base});
+  c->segs.back().copied = copied;
   c->out_total += total;
   for (uint32_t i = 0; i < m; ++i) {
     uint32_t d = sel[i];

@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(256) csv_emit_kernel(TableArgs a, uint8_t* __r
   extern __shared__ __align__(16) uint8_t s_buf[];
   __shared__ uint32_t s_doc;
   const ColOut* col = (const ColOut*)a.col;
-  for (uint32_t item = blockIdx.x; item < a.n_items; item += gridDim.x) {
+  for (uint32_t item = a.item_lo + blockIdx.x; item < a.item_hi; item += gridDim.x) {
     ItemCtx ic = item_ctx(a, item, &s_doc);
     const TDoc D = a.docs[ic.d];
     if (a.doc_flags[ic.d] == 0 && a.n_keep[ic.d] != 0) {
@@ -464,17 +464,28 @@ void csv_table_measure(const TableArgs& a, cudaStream_t s) {
   prof_mark("host+sync", s);
 }
 
-void csv_table_emit(const TableArgs& a, uint8_t* out, cudaStream_t s) {
+void csv_table_emit_header(const TableArgs& a, uint8_t* out, cudaStream_t s) {
   if (a.n_docs == 0) return;
   prof_mark("csv_header_emit_kernel", s);
   RFQ_LAUNCH(csv_header_emit_kernel, (a.n_docs + 7) / 8, 256, 0, s, a, out);
-  prof_mark("csv_emit_kernel", s);
+}
+
+void csv_table_emit_items(const TableArgs& a0, uint8_t* out, uint32_t lo, uint32_t hi, cudaStream_t s) {
+  if (hi <= lo) return;
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(csv_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, RFQ_EMIT_SMEM);
     attr_set = true;
   }
-  if (a.n_items) RFQ_LAUNCH(csv_emit_kernel, table_grid(a.n_items), 256, RFQ_EMIT_SMEM, s, a, out);
+  TableArgs a = a0;
+  a.item_lo = lo; a.item_hi = hi;
+  prof_mark("csv_emit_kernel", s);
+  RFQ_LAUNCH(csv_emit_kernel, table_grid(hi - lo), 256, RFQ_EMIT_SMEM, s, a, out);
+}
+
+void csv_table_emit(const TableArgs& a, uint8_t* out, cudaStream_t s) {
+  csv_table_emit_header(a, out, s);
+  csv_table_emit_items(a, out, 0, a.n_items, s);
 }
 
 }  // namespace rfq

@@ -120,7 +120,10 @@ struct rfq_ctx {
   int32_t* h_status = nullptr; uint32_t* h_rows = nullptr; uint32_t* h_cols = nullptr;
   uint8_t* h_attempt = nullptr;
   // CSV/table runs keep their per-document tables on the host and their text in segments
-  struct OutSeg { const uint8_t* d; uint64_t bytes; uint64_t host_base; };
+  struct OutSeg { const uint8_t* d; uint64_t bytes; uint64_t host_base; bool copied = false; };
+  cudaStream_t copy_stream = nullptr;   // D2H of finished output slices while later slices are still being emitted
+  cudaEvent_t ev_slice[8] = {};
+  bool overlap_fetch = false;
   std::vector<OutSeg> segs;
   bool host_tables = false;
   std::vector<uint64_t> r_off, r_len;

@@ -120,6 +120,7 @@ struct TableArgs {
   const uint32_t* x_r2elem;       // per document (TDoc.f0 + sheet row r) -> <row> element, ~0u = none
   const uint8_t* x_str_arena;     // decoded shared strings
   uint32_t* x_colflags;           // [n_cols] XF_* per output column
+  uint32_t item_lo, item_hi;      // emit: work-item range of this launch (0, n_items = all)
 };
 
 struct ColOut { int32_t cls, dec, sci; uint32_t width, cp_off; };
@@ -128,6 +129,8 @@ void table_stat_init(const TableArgs& a, cudaStream_t s);
 void csv_table_classify(const TableArgs& a, cudaStream_t s);
 void csv_table_measure(const TableArgs& a, cudaStream_t s);   // decide + measure + layout + sizes
 void csv_table_emit(const TableArgs& a, uint8_t* out, cudaStream_t s);
+void csv_table_emit_header(const TableArgs& a, uint8_t* out, cudaStream_t s);
+void csv_table_emit_items(const TableArgs& a, uint8_t* out, uint32_t lo, uint32_t hi, cudaStream_t s);
 
 // ------------------------------------------------------------------------------------------
 // sheet XML / sharedStrings (xlsx_kernels.cu)

@@ -48,6 +48,8 @@ int rfq_create(int device, rfq_ctx** out) {
     return RFQ_ERR_CUDA;
   }
   c->stream = c->own_stream;
+  cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+  for (auto& e : c->ev_slice) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
   *out = c;
   return RFQ_OK;
 }
@@ -60,6 +62,8 @@ void rfq_destroy(rfq_ctx* c) {
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+  for (auto e : c->ev_slice) if (e) cudaEventDestroy(e);
   delete c;
 }
 
@@ -227,6 +231,13 @@ int rfq_fetch(rfq_ctx* c) {
   RFQ_CK(c, cudaSetDevice(c->device));
   cudaStream_t s = c->stream;
   uint32_t n = c->n_docs;
+  bool pre = false;
+  for (auto& sg : c->segs) pre |= sg.copied;
+  if (pre && c->h_out.cap < c->out_total + 16) {   // must grow: the early copies are void
+    RFQ_CK(c, cudaStreamSynchronize(c->copy_stream));
+    for (auto& sg : c->segs) sg.copied = false;
+    pre = false;
+  }
   RFQ_CK(c, c->h_out.reserve(c->out_total + 16));
   RFQ_CK(c, c->h_tabs.reserve((8ull + 8 + 4 + 4 + 4 + 1) * (n + 1) + 64));
   uint8_t* base = (uint8_t*)c->h_tabs.p;
@@ -238,7 +249,7 @@ int rfq_fetch(rfq_ctx* c) {
   c->h_attempt = (uint8_t*)(base + 28ull * (n + 1));
   memset(c->h_status, 0, 4ull * (n + 1) * 3 + (n + 1));
   for (auto& sg : c->segs)
-    if (sg.bytes)
+    if (sg.bytes && !sg.copied)
       RFQ_CK(c, cudaMemcpyAsync((uint8_t*)c->h_out.p + sg.host_base, sg.d, sg.bytes,
                                 cudaMemcpyDeviceToHost, s));
   c->d2h_bytes = c->out_total;
@@ -270,6 +281,7 @@ int rfq_fetch(rfq_ctx* c) {
     }
   }
   RFQ_CK(c, cudaStreamSynchronize(s));
+  if (pre) RFQ_CK(c, cudaStreamSynchronize(c->copy_stream));
   if (c->timed) {
     cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
     c->prof.finish();
@@ -292,7 +304,9 @@ int rfq_csv_parse(rfq_ctx* c, const uint8_t* arena, const uint64_t* offsets,
                   const uint64_t* lengths, uint32_t n, const int64_t* max_rows) {
   int r = rfq_stage(c, arena, offsets, lengths, n);
   if (r) return r;
+  c->overlap_fetch = true;   // stream finished output slices to the host while the rest is emitted
   r = rfq_csv_run(c, max_rows);
+  c->overlap_fetch = false;
   if (r) return r;
   return rfq_fetch(c);
 }

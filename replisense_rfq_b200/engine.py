@@ -17,6 +17,11 @@ class EngineError(RuntimeError):
     pass
 
 
+_decode_utf8 = C.pythonapi.PyUnicode_DecodeUTF8
+_decode_utf8.restype = C.py_object
+_decode_utf8.argtypes = [C.c_void_p, C.c_ssize_t, C.c_char_p]
+
+
 class PinnedArena:
     """Pinned host memory the caller packs documents into (16-byte aligned starts)."""
 
@@ -80,7 +85,11 @@ class BatchResult:
         return C.string_at(self.text_ptr + int(self.offsets[d]), ln)
 
     def doc_str(self, d: int) -> str:
-        return self.doc_bytes(d).decode("utf-8")
+        ln = int(self.lengths[d])
+        if ln == 0:
+            return ""
+        # decode straight out of the pinned buffer (no intermediate bytes object)
+        return _decode_utf8(self.text_ptr + int(self.offsets[d]), ln, None)
 
 
 class Engine:
