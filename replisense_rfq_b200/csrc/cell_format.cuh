@@ -129,7 +129,7 @@ struct Fixed6 {
   int tz;               // trailing decimal zeros of frac (0..6)
 };
 
-RFQ_HD int big_int_digits(uint64_t m, int e, uint8_t* out /* may be null */) {
+RFQ_HD_COLD int big_int_digits(uint64_t m, int e, uint8_t* out /* may be null */) {
   // decimal digits of m << e (e >= 0); returns count, writes digits to out[0..count) if out
   Big b; b.set_u64(m); b.shl(e);
   // count digits: peel 9 at a time into a local buffer (max 309 digits + slack)
@@ -225,7 +225,7 @@ RFQ_HD int approx_log10(uint64_t m, int e) {
   return (int)k;
 }
 
-RFQ_HD Sci7 sci7(double v) {
+RFQ_HD_COLD Sci7 sci7(double v) {
   Sci7 s; s.inf = dbl_is_inf(v); s.digits = 0; s.exp10 = 0;
   uint64_t m; int e;
   dbl_decompose(v, &m, &e, &s.neg);

@@ -143,7 +143,7 @@ __device__ __forceinline__ bool row_kept(const TableArgs& a, const TDoc& D, uint
   return !(__ldg(a.row_na + slot) == D.h && !a.chunk_nf[D.stat_base + chunk * D.W]);
 }
 
-__global__ void __launch_bounds__(256) csv_measure_kernel(TableArgs a) {
+__global__ void __launch_bounds__(256, 3) csv_measure_kernel(TableArgs a) {
   __shared__ uint32_t s_m[8][RFQ_MAX_W];  // plain, ip, tz(min), inf, obj, sci, fl(or), nan_left(or)
   __shared__ uint32_t s_doc, s_keep;
   ChunkMeasure* meas = (ChunkMeasure*)a.meas;

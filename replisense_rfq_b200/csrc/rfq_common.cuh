@@ -6,9 +6,13 @@
 #ifdef __CUDACC__
 #define RFQ_HD __host__ __device__ __forceinline__
 #define RFQ_D __device__ __forceinline__
+// rare, register-hungry paths (big-integer formatting, exact strtod): kept out of line so they
+// do not set the register count of the kernels that call them
+#define RFQ_HD_COLD static __host__ __device__ __noinline__
 #else
 #define RFQ_HD inline
 #define RFQ_D inline
+#define RFQ_HD_COLD inline
 #endif
 
 // Exact IEEE double ops with NO fma contraction (nvcc contracts a*b+c by default, which would

@@ -188,15 +188,24 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
     if (!T.active) continue;
     std::vector<std::string> raw(T.W);
     std::vector<size_t> unnamed;
-    bool ok = true;
+    bool ok = true, all_int = true;
     for (uint32_t j = 0; j < T.W; ++j) {
       uint32_t g = T.col_base + j, mode = h_hmeta[2 * g], len = h_hmeta[2 * g + 1];
+      if (mode != CM_INT) all_int = false;
       if (mode == CM_NULL) { raw[j] = "Unnamed: " + std::to_string(j); unnamed.push_back(j); }
-      else if ((mode == CM_RAW || mode == CM_XML) && len != 0xFFFFFFFFu) raw[j].assign((const char*)h_hdr + (size_t)g * 256, len);
-      else ok = false;  // numeric / boolean / oversized labels: pandas formats the Index as a whole
+      else if ((mode == CM_RAW || mode == CM_XML || mode == CM_INT) && len != 0xFFFFFFFFu)
+        raw[j].assign((const char*)h_hdr + (size_t)g * 256, len);
+      else ok = false;  // float / boolean / oversized labels: pandas formats the Index as a whole
     }
     if (!ok) { T.active = 0; c->r_status[d] = RFQ_DOC_UNSUPPORTED; continue; }
+    std::vector<std::string> before = raw;
     dedupe_names(raw, unnamed);
+    if (all_int && before == raw) {
+      // an all-integer header is an Int64 Index: pandas left-justifies its labels to one width
+      size_t mx = 0;
+      for (auto& x : raw) mx = std::max(mx, x.size());
+      for (auto& x : raw) x.append(mx - x.size(), ' ');
+    }
     std::string empty = empty_frame_text(raw);
     T.empty_off = (uint32_t)names.size(); T.empty_len = (uint32_t)empty.size();
     names += empty;

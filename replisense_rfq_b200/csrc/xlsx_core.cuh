@@ -126,7 +126,7 @@ RFQ_HD bool a1_parse(const uint8_t* s, uint32_t n, uint32_t* col, uint32_t* row)
 
 // ---- correctly rounded decimal -> double (what Python's float(str) gives) -------------------
 // digits/exponent from a plain numeric literal [sign] digits [. digits] [(e|E) [sign] digits]
-RFQ_HD bool strtod_exact(const uint8_t* s, uint32_t n, double* out) {
+RFQ_HD_COLD bool strtod_exact(const uint8_t* s, uint32_t n, double* out) {
   uint32_t i = 0;
   bool neg = false;
   if (i < n && (s[i] == '-' || s[i] == '+')) { neg = s[i] == '-'; ++i; }

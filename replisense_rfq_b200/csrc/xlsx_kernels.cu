@@ -209,6 +209,13 @@ __global__ void __launch_bounds__(128) xheader_kernel(TableArgs a, uint8_t* __re
     while ((ch = it.next()) >= 0) { if (n < 256) o[n] = (uint8_t)ch; ++n; }
     if (n > 256 || it.bad) n = 0xFFFFFFFFu;
   }
+  else if (s.mode == CM_INT) {   // integer column label: its decimal digits
+    int64_t iv = (int64_t)s.bits;
+    n = (uint32_t)int64_len(iv);
+    uint64_t mag = iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv;
+    write_u64_rev(mag, o + n);
+    if (iv < 0) o[0] = '-';
+  }
   hdr_meta[2 * j] = s.mode;
   hdr_meta[2 * j + 1] = n;
 }

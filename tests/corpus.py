@@ -425,6 +425,7 @@ def sheet_xml_fuzz(seed: int):
     out = [_XML_HEAD]
     rownum = 0
     hdr_words = ["Sl No", "Part", "Part", "Qty", "", "a&b", "Ünit", "Qty", "2024"]
+    int_header = r.random() < 0.12
     for i in range(nrows + 1):
         rownum += 1
         if r.random() < 0.08:
@@ -439,7 +440,9 @@ def sheet_xml_fuzz(seed: int):
                 continue
             if i == 0 and rownum == 1:
                 k = r.random()
-                if k < 0.97:
+                if int_header:
+                    out.append('<c r="%s"><v>%d</v></c>' % (ref, r.choice([2024, 2025, 2026, 7, 12345, 2024])))
+                elif k < 0.95:
                     out.append('<c r="%s" t="s"><v>%d</v></c>' % (ref, sid(r.choice(hdr_words))))
                 elif k < 0.98:
                     out.append(cell(ref, "int"))

@@ -392,10 +392,13 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
   };
   // header
   std::vector<std::string> raw(W); std::vector<size_t> unnamed;
+  bool all_int = true;
   for (uint32_t c = 0; c < W; ++c) {
     CellSrc s = cell(1, c);
     std::string nm;
-    if (s.mode == CM_INT || s.mode == CM_BOOL || s.mode == CM_FLOAT) return 2;  // non-string column labels: pandas formats the Index as a whole
+    if (s.mode == CM_BOOL || s.mode == CM_FLOAT) return 2;  // float / bool labels: pandas formats the Index as a whole
+    if (s.mode != CM_INT) all_int = false;
+    if (s.mode == CM_INT) nm = std::to_string((long long)s.bits);
     else if (s.mode == CM_RAW) nm.assign((const char*)s.p, s.n);
     else if (s.mode == CM_XML) { XmlIter it(s.p, s.n); int ch; while ((ch = it.next()) >= 0) nm.push_back((char)ch); }
     if (s.mode == CM_NULL) { nm = "Unnamed: " + std::to_string(c); unnamed.push_back(c); }
@@ -417,6 +420,17 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
         if (in) cur += 1; else { auto g = counts.find(col); cur = g == counts.end() ? 0 : g->second; }
       }
       raw[i2] = col; counts[col] = cur + 1;
+    }
+  }
+  if (all_int) {  // Int64 Index: labels left-justified to one width (only if dedupe changed nothing)
+    bool distinct = true;
+    for (uint32_t a = 0; a < W; ++a) for (uint32_t b = a + 1; b < W; ++b) if (raw[a] == raw[b]) distinct = false;
+    bool digits_only = true;
+    for (auto& x : raw) for (char ch : x) if (!((ch >= '0' && ch <= '9') || ch == '-')) digits_only = false;
+    if (distinct && digits_only) {
+      size_t mx = 0;
+      for (auto& x : raw) mx = std::max(mx, x.size());
+      for (auto& x : raw) x.append(mx - x.size(), ' ');
     }
   }
   std::vector<uint32_t> ncp(W);
