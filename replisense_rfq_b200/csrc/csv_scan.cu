@@ -37,11 +37,31 @@ struct LaneBytes {
   unsigned long long cls;  // nibble k = class of byte k
 };
 
+// classes of 4 bytes at once: byte-wise compares (__vcmpeq4 gives 0xFF per equal byte) select
+// the class code of each byte; then the 4 class bytes are squeezed into 4 nibbles
+__device__ __forceinline__ uint32_t classes_of_word(uint32_t w, uint32_t sep4) {
+  uint32_t mD = __vcmpeq4(w, sep4);
+  uint32_t mQ = __vcmpeq4(w, 0x22222222u);
+  uint32_t mLF = __vcmpeq4(w, 0x0A0A0A0Au);
+  uint32_t mCR = __vcmpeq4(w, 0x0D0D0D0Du);
+  uint32_t mWS = (__vcmpeq4(w, 0x20202020u) | __vcmpeq4(w, 0x09090909u)) & ~mD;
+  uint32_t c = (mD & 0x01010101u) | (mQ & ~mD & 0x02020202u) | (mLF & ~mD & 0x03030303u) |
+               (mCR & ~mD & 0x04040404u) | (mWS & 0x05050505u);
+  uint32_t p = c | (c >> 4);                         // byte0 = n0 | n1 << 4, byte2 = n2 | n3 << 4
+  return (p & 0xFFu) | ((p >> 8) & 0xFF00u);         // 4 nibbles
+}
+
 __device__ __forceinline__ LaneBytes load_lane_classes(const uint8_t* __restrict__ doc,
                                                        uint32_t len, uint32_t base, uint32_t sep,
                                                        bool bom) {
   uint4 v = make_uint4(0, 0, 0, 0);
   if (base < len) v = __ldg(reinterpret_cast<const uint4*>(doc + base));
+  if (base + 16 <= len && !bom) {   // whole vector inside the document: no positional special cases
+    uint32_t sep4 = sep * 0x01010101u;
+    unsigned long long lo = classes_of_word(v.x, sep4) | (classes_of_word(v.y, sep4) << 16);
+    unsigned long long hi = classes_of_word(v.z, sep4) | (classes_of_word(v.w, sep4) << 16);
+    return LaneBytes{lo | (hi << 32)};
+  }
   uint32_t w[4] = {v.x, v.y, v.z, v.w};
   unsigned long long cls = 0;
 #pragma unroll
