@@ -145,7 +145,7 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
         T.n_data = std::min<uint32_t>(sh.n_rec - 1, nrows);
         T.bl = chunk_rows_for_width(W);
         T.n_chunks = (T.n_data + T.bl - 1) / T.bl;
-        T.rb = std::min<uint32_t>(pow2_floor(std::max<uint32_t>(1, 2048 / W)), T.bl);
+        T.rb = std::min<uint32_t>(std::min<uint32_t>(256, pow2_floor(std::max<uint32_t>(1, 2048 / W))), T.bl);
         T.stat_base = (uint32_t)n_stat; n_stat += (uint64_t)T.n_chunks * W;
         T.col_base = (uint32_t)n_cols; n_cols += h;
         n_items += (T.n_data + T.rb - 1) / T.rb;

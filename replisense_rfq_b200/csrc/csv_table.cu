@@ -49,6 +49,30 @@ __device__ __forceinline__ CellSrc fetch_cell(const TableArgs& a, const TDoc& D,
   return s;
 }
 
+// per-row state hoisted out of the column loop (a thread walks the cells of ONE row)
+struct RowCur { uint32_t slot, fbeg, nf, start0; };
+__device__ __forceinline__ RowCur row_open(const TableArgs& a, uint32_t slot) {
+  RowCur r; r.slot = slot; r.fbeg = 0; r.nf = 0; r.start0 = 0;
+  if (!a.xcells) {
+    r.fbeg = __ldg(a.rec_fend + slot - 1);
+    r.nf = __ldg(a.rec_fend + slot) - r.fbeg;
+    r.start0 = __ldg(a.rec_start + slot);
+  }
+  return r;
+}
+__device__ __forceinline__ CellSrc row_cell(const TableArgs& a, const TDoc& D, const RowCur& r, uint32_t c) {
+  if (a.xcells) return xfetch(a, D, r.slot - D.r0 + 1, c);
+  CellSrc s;
+  s.mode = 0; s.missing = false; s.clean = false; s.p = a.arena; s.n = 0; s.bits = 0;
+  if (c >= r.nf) { s.missing = true; return s; }
+  uint32_t st = c == 0 ? r.start0 : __ldg(a.fend + r.fbeg + c - 1) + 1;
+  uint32_t en = __ldg(a.fend + r.fbeg + c);
+  s.p = a.arena + D.off + st;
+  s.n = en - st;
+  csv_simplify(s);
+  return s;
+}
+
 struct ItemCtx {
   uint32_t d, row0, nrows, chunk;
 };
@@ -297,16 +321,17 @@ __device__ __forceinline__ int format_number(const CellSrc& s, int ct, int kind,
 
 // writes the cell right-justified into its field; `field` points at the first byte of the
 // column's field inside the row; `fill` = also write the padding blanks (direct path)
-__device__ __forceinline__ void emit_cell(const CellSrc& src, int ct, int kind, int dec,
-                                          uint32_t width, uint8_t* field, bool fill) {
+// returns printed bytes - printed code points (non-zero only for non-ASCII strings)
+__device__ __forceinline__ uint32_t emit_cell(const CellSrc& src, int ct, int kind, int dec,
+                                              uint32_t width, uint8_t* field, bool fill) {
   TextInfo t = cell_text(src);
   bool na = cell_is_nan(src, t, ct);
-  if (na) { if (fill) for (uint32_t q = 0; q < width; ++q) field[q] = ' '; return; }
+  if (na) { if (fill) for (uint32_t q = 0; q < width; ++q) field[q] = ' '; return 0; }
   if (kind == PR_STR) {
     uint32_t ncp = t.ncp + t.nesc, pad = width - ncp;
     if (fill) for (uint32_t q = 0; q < pad; ++q) field[q] = ' ';
     print_cell(src, ct, kind, dec, field + pad);
-    return;
+    return t.nbytes - t.ncp;
   }
   uint8_t buf[40];
   int n = format_number(src, ct, kind, dec, t, buf);
@@ -316,11 +341,12 @@ __device__ __forceinline__ void emit_cell(const CellSrc& src, int ct, int kind, 
     uint32_t pad = width - ncp;
     if (fill) for (uint32_t q = 0; q < pad; ++q) field[q] = ' ';
     print_cell(src, ct, kind, dec, field + pad);
-    return;
+    return 0;
   }
   uint32_t pad = width - (uint32_t)n;
   if (fill) for (uint32_t q = 0; q < pad; ++q) field[q] = ' ';
   for (int q = 0; q < n; ++q) field[pad + q] = buf[q];
+  return 0;
 }
 
 __global__ void __launch_bounds__(256) csv_emit_kernel(TableArgs a, uint8_t* __restrict__ out) {
@@ -344,36 +370,46 @@ __global__ void __launch_bounds__(256) csv_emit_kernel(TableArgs a, uint8_t* __r
         __syncthreads();
       }
       uint8_t* base = staged ? s_buf + mis : out + g0;   // base[x] <-> out[g0 + x]
-      uint32_t ncell = ic.nrows * W;
-      for (uint32_t idx = threadIdx.x; idx < ncell; idx += blockDim.x) {
-        uint32_t c = idx / ic.nrows, rr = idx - c * ic.nrows;  // lanes = consecutive rows of ONE column
-        uint32_t slot = slot0 + rr;
-        if (c < D.lead || !row_kept(a, D, slot, ic.chunk)) continue;
-        uint32_t j = c - D.lead;
-        ColOut co = col[D.col_base + j];
+      // A thread owns one row and walks its columns; a warp therefore works on 32 consecutive
+      // rows of the SAME column at any moment.  Items with fewer rows than threads split the
+      // columns over thread groups.
+      uint32_t rbp = 32;
+      while (rbp < ic.nrows) rbp <<= 1;
+      const uint32_t ngrp = blockDim.x / rbp, rr = threadIdx.x % rbp, grp = threadIdx.x / rbp;
+      const uint32_t slot = slot0 + rr;
+      if (rr < ic.nrows && grp < ngrp && row_kept(a, D, slot, ic.chunk)) {
+        const RowCur rc = row_open(a, slot);
+        uint8_t* rowp = base + (a.row_off[slot] - g0);
+        const uint32_t extra = __ldg(a.row_extra + slot);
         const uint8_t* ctrow = a.ctype + D.stat_base + ic.chunk * W;
-        int ct = ctrow[c];
-        CellSrc src = fetch_cell(a, D, slot, c);
-        if (ct == CT_XOBJ) ct = cell_own_ctype(src);
-        int kind = print_kind(co.cls, ct, co.sci != 0);
         uint32_t xb = 0;  // extra bytes of the columns to the left (rows with non-ASCII text only)
-        if (j && __ldg(a.row_extra + slot)) {
-          for (uint32_t c2 = D.lead; c2 < c; ++c2) {
-            ColOut c2o = col[D.col_base + c2 - D.lead];
-            int ct2 = ctrow[c2];
-            CellSrc s2 = fetch_cell(a, D, slot, c2);
-            if (ct2 == CT_XOBJ) ct2 = cell_own_ctype(s2);
-            int k2 = print_kind(c2o.cls, ct2, c2o.sci != 0);
-            if (k2 != PR_STR) continue;
-            uint32_t cp2, nb2;
-            printed_size(s2, ct2, k2, c2o.dec, &cp2, &nb2);
-            xb += nb2 - cp2;
+        for (uint32_t c = D.lead + grp; c < W; c += ngrp) {
+          uint32_t j = c - D.lead;
+          ColOut co = col[D.col_base + j];
+          int ct = ctrow[c];
+          CellSrc src = row_cell(a, D, rc, c);
+          if (ct == CT_XOBJ) ct = cell_own_ctype(src);
+          int kind = print_kind(co.cls, ct, co.sci != 0);
+          if (ngrp > 1 && j && extra) {   // columns are split over groups: recompute the shift
+            xb = 0;
+            for (uint32_t c2 = D.lead; c2 < c; ++c2) {
+              ColOut c2o = col[D.col_base + c2 - D.lead];
+              int ct2 = ctrow[c2];
+              CellSrc s2 = row_cell(a, D, rc, c2);
+              if (ct2 == CT_XOBJ) ct2 = cell_own_ctype(s2);
+              int k2 = print_kind(c2o.cls, ct2, c2o.sci != 0);
+              if (k2 != PR_STR) continue;
+              uint32_t cp2, nb2;
+              printed_size(s2, ct2, k2, c2o.dec, &cp2, &nb2);
+              xb += nb2 - cp2;
+            }
           }
+          uint8_t* p = rowp;
+          if (j == 0) { *p = '\n'; p += 1; }
+          else { p += co.cp_off + xb; if (!staged) *p = ' '; p += 1; }
+          uint32_t ex = emit_cell(src, ct, kind, co.dec, co.width, p, !staged);
+          if (ngrp == 1) xb += ex;
         }
-        uint8_t* p = base + (a.row_off[slot] - g0);
-        if (j == 0) { *p = '\n'; p += 1; }
-        else { p += co.cp_off + xb; if (!staged) *p = ' '; p += 1; }
-        emit_cell(src, ct, kind, co.dec, co.width, p, !staged);
       }
       if (staged) {
         __syncthreads();

@@ -140,7 +140,7 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
     T.W = sh.W; T.h = sh.W; T.lead = 0;
     T.n_data = sh.lastrow - 1;
     T.bl = std::max<uint32_t>(T.n_data, 1); T.n_chunks = 1;   // the python engine infers over the whole column
-    T.rb = p2floor(std::max<uint32_t>(1, 2048 / T.W));
+    T.rb = std::min<uint32_t>(256, p2floor(std::max<uint32_t>(1, 2048 / T.W)));
     T.active = 1;
     n_cols += T.W;
     n_items += (T.n_data + T.rb - 1) / T.rb;
