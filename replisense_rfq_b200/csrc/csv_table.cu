@@ -101,20 +101,27 @@ __global__ void __launch_bounds__(256) csv_classify_kernel(TableArgs a) {
       s_flags[c] = 0; s_bad[c] = RFQ_NO_ROW; s_ovf[c] = RFQ_NO_ROW;
     }
     __syncthreads();
-    uint32_t ncell = ic.nrows * W;
-    for (uint32_t idx = threadIdx.x; idx < ncell; idx += blockDim.x) {
-      uint32_t c = idx / ic.nrows, rr = idx - c * ic.nrows;  // lanes = consecutive rows of ONE column
-      uint32_t row = ic.row0 + rr;
-      uint32_t slot = D.r0 + 1 + row;
-      CellSrc src = fetch_cell(a, D, slot, c);
-      int is;
-      uint32_t f = classify_cell(src, &is);
-      if ((s_flags[c] & f) != f) atomicOr(&s_flags[c], f);
-      if (is != INT_OK) {
-        if (row < s_bad[c]) atomicMin(&s_bad[c], row);
-        if (is == INT_OVERFLOW && row < s_ovf[c]) atomicMin(&s_ovf[c], row);
+    // a thread owns one row and walks its columns (a warp = 32 rows of the same column)
+    uint32_t rbp = 32;
+    while (rbp < ic.nrows) rbp <<= 1;
+    const uint32_t ngrp = blockDim.x / rbp, rr = threadIdx.x % rbp, grp = threadIdx.x / rbp;
+    if (rr < ic.nrows && grp < ngrp) {
+      const uint32_t row = ic.row0 + rr, slot = D.r0 + 1 + row;
+      const RowCur rc = row_open(a, slot);
+      uint32_t na = 0;
+      for (uint32_t c = grp; c < W; c += ngrp) {
+        CellSrc src = row_cell(a, D, rc, c);
+        int is;
+        uint32_t f = classify_cell(src, &is);
+        if ((s_flags[c] & f) != f) atomicOr(&s_flags[c], f);
+        if (is != INT_OK) {
+          if (row < s_bad[c]) atomicMin(&s_bad[c], row);
+          if (is == INT_OVERFLOW && row < s_ovf[c]) atomicMin(&s_ovf[c], row);
+        }
+        if ((f & SF_ANY_NA) && c >= D.lead) ++na;
       }
-      if ((f & SF_ANY_NA) && c >= D.lead) atomicAdd(a.row_na + slot, 1u);
+      if (ngrp == 1) a.row_na[slot] = na;
+      else if (na) atomicAdd(a.row_na + slot, na);
     }
     __syncthreads();
     for (uint32_t c = threadIdx.x; c < W; c += blockDim.x) {
@@ -182,24 +189,28 @@ __global__ void __launch_bounds__(256, 3) csv_measure_kernel(TableArgs a) {
     if (threadIdx.x == 0) s_keep = 0;
     __syncthreads();
     if (!(a.doc_flags[ic.d] & 1)) {
-      uint32_t ncell = ic.nrows * W;
-      for (uint32_t idx = threadIdx.x; idx < ncell; idx += blockDim.x) {
-        uint32_t c = idx / ic.nrows, rr = idx - c * ic.nrows;  // lanes = consecutive rows of ONE column
-        uint32_t row = ic.row0 + rr;
-        uint32_t slot = D.r0 + 1 + row;
-        if (c < D.lead || !row_kept(a, D, slot, ic.chunk)) continue;
-        if (c == D.lead) atomicAdd(&s_keep, 1u);
-        int ct = a.ctype[D.stat_base + ic.chunk * W + c];
-        CellMeasure m = measure_cell(fetch_cell(a, D, slot, c), ct);
-        if (m.is_nan) { if (!s_m[7][c]) s_m[7][c] = 1; continue; }
-        if (m.plain_len > s_m[0][c]) atomicMax(&s_m[0][c], m.plain_len);
-        if (m.ip_len > s_m[1][c]) atomicMax(&s_m[1][c], m.ip_len);
-        if (m.tz < s_m[2][c]) atomicMin(&s_m[2][c], m.tz);
-        if (m.inf_len > s_m[3][c]) atomicMax(&s_m[3][c], m.inf_len);
-        if (m.obj_len > s_m[4][c]) atomicMax(&s_m[4][c], m.obj_len);
-        if (m.sci_len > s_m[5][c]) atomicMax(&s_m[5][c], m.sci_len);
-        if ((s_m[6][c] & m.fl) != m.fl) atomicOr(&s_m[6][c], m.fl);
-        if (m.extra_bytes) atomicAdd(a.row_extra + slot, m.extra_bytes);
+      uint32_t rbp = 32;
+      while (rbp < ic.nrows) rbp <<= 1;
+      const uint32_t ngrp = blockDim.x / rbp, rr = threadIdx.x % rbp, grp = threadIdx.x / rbp;
+      const uint32_t slot = D.r0 + 1 + ic.row0 + rr;
+      if (rr < ic.nrows && grp < ngrp && row_kept(a, D, slot, ic.chunk)) {
+        const RowCur rc = row_open(a, slot);
+        if (grp == 0) atomicAdd(&s_keep, 1u);
+        uint32_t extra = 0;
+        for (uint32_t c = D.lead + grp; c < W; c += ngrp) {
+          int ct = a.ctype[D.stat_base + ic.chunk * W + c];
+          CellMeasure m = measure_cell(row_cell(a, D, rc, c), ct);
+          if (m.is_nan) { if (!s_m[7][c]) s_m[7][c] = 1; continue; }
+          if (m.plain_len > s_m[0][c]) atomicMax(&s_m[0][c], m.plain_len);
+          if (m.ip_len > s_m[1][c]) atomicMax(&s_m[1][c], m.ip_len);
+          if (m.tz < s_m[2][c]) atomicMin(&s_m[2][c], m.tz);
+          if (m.inf_len > s_m[3][c]) atomicMax(&s_m[3][c], m.inf_len);
+          if (m.obj_len > s_m[4][c]) atomicMax(&s_m[4][c], m.obj_len);
+          if (m.sci_len > s_m[5][c]) atomicMax(&s_m[5][c], m.sci_len);
+          if ((s_m[6][c] & m.fl) != m.fl) atomicOr(&s_m[6][c], m.fl);
+          extra += m.extra_bytes;
+        }
+        if (extra) { if (ngrp == 1) a.row_extra[slot] = extra; else atomicAdd(a.row_extra + slot, extra); }
       }
     }
     __syncthreads();

@@ -237,13 +237,18 @@ __global__ void __launch_bounds__(256) xclassify_kernel(TableArgs a) {
     uint32_t nrows = min(D.rb, D.n_data - row0);
     for (uint32_t c = threadIdx.x; c < W; c += blockDim.x) s_flags[c] = 0;
     __syncthreads();
-    uint32_t ncell = nrows * W;
-    for (uint32_t idx = threadIdx.x; idx < ncell; idx += blockDim.x) {
-      uint32_t c = idx / nrows, rr = idx - c * nrows;
-      uint32_t row = row0 + rr;
-      uint32_t f = xclassify_cell(xfetch(a, D, row + 2, c), row == 0);
-      if ((s_flags[c] & f) != f) atomicOr(&s_flags[c], f);
-      if (f & XF_NULL) atomicAdd(a.row_na + D.r0 + 1 + row, 1u);
+    uint32_t rbp = 32;
+    while (rbp < nrows) rbp <<= 1;
+    const uint32_t ngrp = blockDim.x / rbp, rr = threadIdx.x % rbp, grp = threadIdx.x / rbp;
+    if (rr < nrows && grp < ngrp) {
+      const uint32_t row = row0 + rr;
+      uint32_t na = 0;
+      for (uint32_t c = grp; c < W; c += ngrp) {
+        uint32_t f = xclassify_cell(xfetch(a, D, row + 2, c), row == 0);
+        if ((s_flags[c] & f) != f) atomicOr(&s_flags[c], f);
+        if (f & XF_NULL) ++na;
+      }
+      if (na) atomicAdd(a.row_na + D.r0 + 1 + row, na);
     }
     __syncthreads();
     for (uint32_t c = threadIdx.x; c < W; c += blockDim.x)
