@@ -210,6 +210,13 @@ RFQ_HD uint32_t classify_cell(const CellSrc& s, int* int_status) {
   double dv;
   if (!cell_double(s, &dv)) f |= SF_FLOAT_BAD;
   if (bool_token(t.nbytes, t.first8) < 0) f |= SF_BOOL_BAD;
+  // Python-int fallback (only matters for columns that overflow uint64): a plain non-negative
+  // uint64 token is int()-parsable; a token that cannot even start an integer is not
+  if (!(us == INT_OK && !u.neg)) {
+    uint32_t c0 = (uint32_t)(t.first8 & 0xFF);
+    bool may = is_digit_ascii((int)c0) || c0 == '+' || c0 == '-' || is_space_ascii((int)c0);
+    if (!may || !RFQ_WITH_ITER(s, parse_pyint).ok) f |= SF_PYINT_BAD;
+  }
   return f;
 }
 
@@ -269,6 +276,11 @@ RFQ_HD CellMeasure measure_cell(const CellSrc& s, int ctype) {
     m.plain_len = (uint32_t)ndigits_u64(u.v);
     return m;
   }
+  if (ctype == CT_PYINT) {
+    PyInt pi = RFQ_WITH_ITER(s, parse_pyint);
+    m.plain_len = pi.ndig + (pi.neg ? 1u : 0u);
+    return m;
+  }
   if (ctype == CT_INT || ctype == CT_INTNA) {
     int64_t iv = 0; cell_int64(s, &iv);
     m.plain_len = (uint32_t)int64_len(iv);
@@ -289,7 +301,7 @@ RFQ_HD CellMeasure measure_cell(const CellSrc& s, int ctype) {
 
 // ---- 3. print -----------------------------------------------------------------------------------
 // How a cell prints given the class of its column and the type of its chunk.
-enum { PR_EMPTY = 0, PR_INT, PR_UINT, PR_FIXED, PR_SCI, PR_OBJFLOAT, PR_BOOL, PR_STR };
+enum { PR_EMPTY = 0, PR_INT, PR_UINT, PR_FIXED, PR_SCI, PR_OBJFLOAT, PR_BOOL, PR_STR, PR_PYINT };
 
 RFQ_HD int print_kind(int cls, int ctype, bool sci) {
   switch (cls) {
@@ -305,6 +317,7 @@ RFQ_HD int print_kind(int cls, int ctype, bool sci) {
         case CT_UINT: return PR_UINT;
         case CT_INTNA: case CT_FLOAT: return PR_OBJFLOAT;
         case CT_BOOL: case CT_BOOLNA: return PR_BOOL;
+        case CT_PYINT: return PR_PYINT;
         default: return PR_STR;
       }
   }
@@ -322,6 +335,7 @@ RFQ_HD void printed_size(const CellSrc& s, int ctype, int kind, int dec, uint32_
     case PR_BOOL: n = cell_bool(s, t) == 1 ? 4 : 5; break;
     case PR_INT: { int64_t iv = 0; cell_int64(s, &iv); n = (uint32_t)int64_len(iv); break; }
     case PR_UINT: { UintTok u; cell_uint64(s, &u); n = (uint32_t)ndigits_u64(u.v); break; }
+    case PR_PYINT: { PyInt pi = RFQ_WITH_ITER(s, parse_pyint); n = pi.ndig + (pi.neg ? 1u : 0u); break; }
     case PR_FIXED: { Fixed6 f = fixed6(cell_as_double(s, ctype)); n = (uint32_t)fixed_len(f, dec); break; }
     case PR_OBJFLOAT: { Fixed6 f = fixed6(cell_as_double(s, ctype)); n = (uint32_t)objfloat_len(f); break; }
     case PR_SCI: n = (uint32_t)sci_len_of(cell_as_double(s, ctype)); break;
@@ -400,6 +414,7 @@ RFQ_HD uint32_t print_cell(const CellSrc& s, int ctype, int kind, int dec, uint8
       write_u64_rev(u.v, out + n);
       return n;
     }
+    case PR_PYINT: return RFQ_WITH_ITER(s, write_pyint, out);
     case PR_FIXED: {
       double v = cell_as_double(s, ctype);
       Fixed6 f = fixed6(v);

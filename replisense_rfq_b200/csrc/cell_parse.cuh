@@ -196,6 +196,57 @@ RFQ_HD int parse_uint64(It it, UintTok* out) {
   return INT_OK;
 }
 
+// Python's int(str): [space]* [+-] digit (_? digit)* [space]*  (what pandas falls back to for
+// integer columns beyond uint64).  ndig = digits of the canonical form (no leading zeros).
+struct PyInt { bool ok, neg; uint32_t ndig; };
+template <class It>
+RFQ_HD PyInt parse_pyint(It it) {
+  PyInt r; r.ok = false; r.neg = false; r.ndig = 0;
+  int c = it.next();
+  while (c >= 0 && is_space_ascii(c)) c = it.next();
+  if (c == '-') { r.neg = true; c = it.next(); }
+  else if (c == '+') c = it.next();
+  if (!is_digit_ascii(c)) return r;
+  bool nonzero = false, prev_us = false;
+  uint32_t nd = 0;
+  while (c >= 0) {
+    if (is_digit_ascii(c)) {
+      if (c != '0') nonzero = true;
+      if (nonzero) ++nd;
+      prev_us = false;
+    } else if (c == '_') {
+      if (prev_us) return r;
+      prev_us = true;
+    } else break;
+    c = it.next();
+  }
+  if (prev_us) return r;
+  while (c >= 0 && is_space_ascii(c)) c = it.next();
+  if (c >= 0) return r;
+  r.ok = true;
+  if (!nonzero) { r.neg = false; nd = 1; }
+  r.ndig = nd;
+  return r;
+}
+// writes str(int(token)); returns bytes
+template <class It>
+RFQ_HD uint32_t write_pyint(It it, uint8_t* out) {
+  uint32_t k = 0;
+  int c = it.next();
+  while (c >= 0 && is_space_ascii(c)) c = it.next();
+  bool neg = false;
+  if (c == '-') { neg = true; c = it.next(); }
+  else if (c == '+') c = it.next();
+  if (neg) out[k++] = '-';
+  bool nonzero = false;
+  while (c >= 0 && (is_digit_ascii(c) || c == '_')) {
+    if (c != '_') { if (c != '0') nonzero = true; if (nonzero) out[k++] = (uint8_t)c; }
+    c = it.next();
+  }
+  if (!nonzero) { k = 0; out[k++] = '0'; }
+  return k;
+}
+
 // ---- doubles: precise_xstrtod -----------------------------------------------------------------
 template <class It>
 RFQ_HD bool parse_double(It it, double* out) {

@@ -24,7 +24,9 @@ enum {
   CT_STR = 6,     // str, NA -> NaN
   CT_STRNF = 7,   // str with the NA filter off (uint64 conflict): nothing is NaN
   CT_UNSUP = 8,   // Python-int object columns (beyond uint64) — not produced on the GPU path
-  CT_XOBJ = 9     // sheet column of mixed Python objects: every cell prints as its own type
+  CT_XOBJ = 9,    // sheet column of mixed Python objects: every cell prints as its own type
+  CT_PYINT = 10   // object column of Python ints (a value beyond uint64 / a negative next to an overflow):
+                  // every token is int()-parsable and prints as str(int(token)); NA -> NaN
 };
 
 // printing class of a whole column
@@ -41,7 +43,8 @@ enum {
   SF_UINT_OVF = 1u << 5,     // > UINT64_MAX
   SF_NEG = 1u << 6,          // a non-NA token whose first non-space char is '-'
   SF_GT_I64 = 1u << 7,       // a valid unsigned value > INT64_MAX
-  SF_BAD_UTF8 = 1u << 8      // a non-NA token that is not valid UTF-8
+  SF_BAD_UTF8 = 1u << 8,     // a non-NA token that is not valid UTF-8
+  SF_PYINT_BAD = 1u << 9     // a non-NA token Python's int() rejects
 };
 #define RFQ_NO_ROW 0xFFFFFFFFu
 
@@ -49,7 +52,9 @@ struct ChunkStat {
   uint32_t flags;
   uint32_t int_bad_min;   // first row whose non-NA token is not an int64 (invalid OR overflow)
   uint32_t int_ovf_min;   // first row whose non-NA token overflows int64
-  uint32_t pad;
+  uint32_t uint_inv_min;  // first row whose non-NA token str_to_uint64 rejects as invalid
+  uint32_t uint_ovf_min;  // first row whose non-NA token exceeds UINT64_MAX
+  uint32_t pad[3];
 };
 
 RFQ_HD int decide_chunk_type(const ChunkStat& s) {
@@ -57,12 +62,20 @@ RFQ_HD int decide_chunk_type(const ChunkStat& s) {
   if (!(f & SF_ANY_NONNA)) return CT_FLOAT;  // every token NA: int64 pass succeeds, upcast to NaN
   if (s.int_bad_min == RFQ_NO_ROW) return (f & SF_ANY_NA) ? CT_INTNA : CT_INT;
   if (s.int_ovf_min == s.int_bad_min) {
-    // the int64 pass stopped on an overflow -> uint64 pass
-    if (f & (SF_UINT_INVALID | SF_UINT_OVF)) return CT_UNSUP;  // order-dependent corner, not taken
-    bool conflict = (f & SF_GT_I64) && (f & (SF_NEG | SF_ANY_NA));
-    if (conflict) return CT_STRNF;
-    if (f & SF_NEG) return CT_UNSUP;  // OverflowError -> Python ints
-    return CT_UINT;
+    // the int64 pass stopped on an overflow -> uint64 pass, which stops at ITS first failure:
+    // an invalid token sends the column on to the float pass, a value beyond uint64 raises
+    // OverflowError -> Python-int pass (str(int(token)) objects, or plain strings if any token is
+    // not int()-parsable)
+    bool fall_to_float = false;
+    if (s.uint_inv_min != RFQ_NO_ROW && s.uint_inv_min < s.uint_ovf_min) fall_to_float = true;
+    else if (s.uint_ovf_min != RFQ_NO_ROW) return (f & SF_PYINT_BAD) ? CT_STR : CT_PYINT;
+    else {
+      bool conflict = (f & SF_GT_I64) && (f & (SF_NEG | SF_ANY_NA));
+      if (conflict) return CT_STRNF;                       // ValueError: strings, NA filter off
+      if (f & SF_NEG) return (f & SF_PYINT_BAD) ? CT_STR : CT_PYINT;   // OverflowError
+      return CT_UINT;
+    }
+    (void)fall_to_float;
   }
   if (!(f & SF_FLOAT_BAD)) return CT_FLOAT;
   if (!(f & SF_BOOL_BAD)) return (f & SF_ANY_NA) ? CT_BOOLNA : CT_BOOL;

@@ -90,7 +90,7 @@ __device__ __forceinline__ ItemCtx item_ctx(const TableArgs& a, uint32_t item, u
 
 // ---- sweep 1: classify --------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) csv_classify_kernel(TableArgs a) {
-  __shared__ uint32_t s_flags[RFQ_MAX_W], s_bad[RFQ_MAX_W], s_ovf[RFQ_MAX_W];
+  __shared__ uint32_t s_flags[RFQ_MAX_W], s_bad[RFQ_MAX_W], s_ovf[RFQ_MAX_W], s_uinv[RFQ_MAX_W], s_uovf[RFQ_MAX_W];
   __shared__ uint32_t s_doc;
   ChunkStat* stat = (ChunkStat*)a.stat;
   for (uint32_t item = blockIdx.x; item < a.n_items; item += gridDim.x) {
@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(256) csv_classify_kernel(TableArgs a) {
     const TDoc D = a.docs[ic.d];
     uint32_t W = D.W;
     for (uint32_t c = threadIdx.x; c < W; c += blockDim.x) {
-      s_flags[c] = 0; s_bad[c] = RFQ_NO_ROW; s_ovf[c] = RFQ_NO_ROW;
+      s_flags[c] = 0; s_bad[c] = RFQ_NO_ROW; s_ovf[c] = RFQ_NO_ROW; s_uinv[c] = RFQ_NO_ROW; s_uovf[c] = RFQ_NO_ROW;
     }
     __syncthreads();
     // a thread owns one row and walks its columns (a warp = 32 rows of the same column)
@@ -117,6 +117,8 @@ __global__ void __launch_bounds__(256) csv_classify_kernel(TableArgs a) {
         if (is != INT_OK) {
           if (row < s_bad[c]) atomicMin(&s_bad[c], row);
           if (is == INT_OVERFLOW && row < s_ovf[c]) atomicMin(&s_ovf[c], row);
+          if ((f & SF_UINT_INVALID) && row < s_uinv[c]) atomicMin(&s_uinv[c], row);
+          if ((f & SF_UINT_OVF) && row < s_uovf[c]) atomicMin(&s_uovf[c], row);
         }
         if ((f & SF_ANY_NA) && c >= D.lead) ++na;
       }
@@ -129,6 +131,8 @@ __global__ void __launch_bounds__(256) csv_classify_kernel(TableArgs a) {
       if (s_flags[c]) atomicOr(&S->flags, s_flags[c]);
       if (s_bad[c] != RFQ_NO_ROW) atomicMin(&S->int_bad_min, s_bad[c]);
       if (s_ovf[c] != RFQ_NO_ROW) atomicMin(&S->int_ovf_min, s_ovf[c]);
+      if (s_uinv[c] != RFQ_NO_ROW) atomicMin(&S->uint_inv_min, s_uinv[c]);
+      if (s_uovf[c] != RFQ_NO_ROW) atomicMin(&S->uint_ovf_min, s_uovf[c]);
     }
     __syncthreads();
   }
@@ -138,7 +142,7 @@ __global__ void __launch_bounds__(256) csv_stat_init_kernel(ChunkStat* stat, Chu
                                                             uint32_t n) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  stat[i] = ChunkStat{0u, RFQ_NO_ROW, RFQ_NO_ROW, 0u};
+  stat[i] = ChunkStat{0u, RFQ_NO_ROW, RFQ_NO_ROW, RFQ_NO_ROW, RFQ_NO_ROW, {0u, 0u, 0u}};
   ChunkMeasure m;
   m.plain_len = 0; m.ip_len = 0; m.min_tz = 6; m.inf_len = 0; m.obj_len = 0; m.sci_len = 0;
   m.fl = 0; m.nan_left = 0;
@@ -326,6 +330,7 @@ __device__ __forceinline__ int format_number(const CellSrc& s, int ct, int kind,
       return fixed_write(f, v, kind == PR_FIXED ? dec : objfloat_dec(f), kind == PR_OBJFLOAT, buf);
     }
     case PR_SCI: return sci_write(sci7(cell_as_double(s, ct)), buf);
+    case PR_PYINT: return -1;   // arbitrary length: measured and written in place
     default: return 0;
   }
 }

@@ -148,7 +148,7 @@ int csv_attempt(const uint8_t* doc, uint64_t len, uint32_t sep, int64_t nrows, s
     csv_simplify(s);
     return s;
   };
-  std::vector<ChunkStat> stat((size_t)nch * W, ChunkStat{0, RFQ_NO_ROW, RFQ_NO_ROW, 0});
+  std::vector<ChunkStat> stat((size_t)nch * W, ChunkStat{0, RFQ_NO_ROW, RFQ_NO_ROW, RFQ_NO_ROW, RFQ_NO_ROW, {0, 0, 0}});
   std::vector<uint32_t> row_na(ndata, 0);
   for (uint32_t r = 0; r < ndata; ++r)
     for (uint32_t c = 0; c < W; ++c) {
@@ -159,6 +159,8 @@ int csv_attempt(const uint8_t* doc, uint64_t len, uint32_t sep, int64_t nrows, s
       if (is != INT_OK) {
         if (r < S.int_bad_min) S.int_bad_min = r;
         if (is == INT_OVERFLOW && r < S.int_ovf_min) S.int_ovf_min = r;
+        if ((f & SF_UINT_INVALID) && r < S.uint_inv_min) S.uint_inv_min = r;
+        if ((f & SF_UINT_OVF) && r < S.uint_ovf_min) S.uint_ovf_min = r;
       }
       if ((f & SF_ANY_NA) && c >= lead) row_na[r]++;
     }

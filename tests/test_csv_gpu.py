@@ -12,8 +12,7 @@ from tests import corpus
 pytestmark = pytest.mark.gpu
 G = Path(__file__).parent / "golden"
 
-# Python-int object column (value beyond uint64): reported as unsupported, never guessed
-UNSUPPORTED_GOLDENS = {"too_big"}
+UNSUPPORTED_GOLDENS = set()
 
 
 @pytest.fixture(scope="module")
@@ -41,8 +40,24 @@ def test_csv_reference_goldens(eng):
 
 def test_csv_unsupported_is_loud(eng):
     from replisense_rfq_b200 import EngineError
-    with pytest.raises(EngineError):
-        eng.parse_csv_many([b"p,q\n18446744073709551616,1\n1,2\n"], 1000)
+    wide = (",".join("c%d" % i for i in range(1100)) + "\n" + ",".join("1" for _ in range(1100)) + "\n").encode()
+    with pytest.raises(EngineError):   # > 1024 columns: reported, never routed to a CPU path
+        eng.parse_csv_many([wide], 1000)
+
+
+def test_csv_big_integer_columns(eng):
+    """int64 overflow -> uint64 pass -> Python-int objects / strings, in pandas' order-dependent way."""
+    cols = [["18446744073709551616", "1"], ["1", "18446744073709551616"], ["18446744073709551616", "NA", "2"],
+            ["18446744073709551616", " 7 ", "+3", "-0", "007"], ["18446744073709551616", "1.5"],
+            ["-9223372036854775809", "5"], ["-9223372036854775809", "9223372036854775808"],
+            ["99999999999999999999999999999999999999", "-5"], ["1_000", "18446744073709551616"],
+            ["18446744073709551616", "1_000"], ["9223372036854775808", "-1", "18446744073709551616"],
+            ["9223372036854775808", "abc", "18446744073709551616"], ["9223372036854775808", "1"],
+            ["9223372036854775808", ""], ["18446744073709551616", "1__0"]]
+    docs = [("a,b\n" + "".join(f"{v},x\n" for v in c)).encode() for c in cols]
+    got = eng.parse_csv_many(docs, 1000)
+    bad = [c for c, g, d in zip(cols, got, docs) if g != oracle(d)]
+    assert not bad, bad
 
 
 def test_csv_fuzz_batch(eng):

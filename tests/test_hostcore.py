@@ -164,9 +164,6 @@ def test_csv_model_matches_reference_goldens():
     bad = []
     for c in cases:
         got = H.csv_parse(base64.b64decode(c["data"]), c["nrows"])
-        if got == "UNSUPPORTED":
-            assert c["name"] == "too_big"  # Python-int object column: reported, not guessed
-            continue
         if got != c.get("text"):
             bad.append(c["name"])
     assert not bad, bad
