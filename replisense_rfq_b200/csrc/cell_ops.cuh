@@ -213,9 +213,8 @@ RFQ_HD uint32_t classify_cell(const CellSrc& s, int* int_status) {
   // Python-int fallback (only matters for columns that overflow uint64): a plain non-negative
   // uint64 token is int()-parsable; a token that cannot even start an integer is not
   if (!(us == INT_OK && !u.neg)) {
-    uint32_t c0 = (uint32_t)(t.first8 & 0xFF);
-    bool may = is_digit_ascii((int)c0) || c0 == '+' || c0 == '-' || is_space_ascii((int)c0);
-    if (!may || !RFQ_WITH_ITER(s, parse_pyint).ok) f |= SF_PYINT_BAD;
+    int pp = pyint_prefix(t.first8, t.nbytes);   // dates, decimals, words: decided in registers
+    if (pp == 0 || (pp == 2 && !RFQ_WITH_ITER(s, parse_pyint).ok)) f |= SF_PYINT_BAD;
   }
   return f;
 }

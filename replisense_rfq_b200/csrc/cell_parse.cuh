@@ -228,6 +228,28 @@ RFQ_HD PyInt parse_pyint(It it) {
   r.ndig = nd;
   return r;
 }
+// parse_pyint's state machine over the first min(n, 8) decoded bytes of a token (TextInfo.first8):
+// 0 = rejected, 1 = accepted (n <= 8), 2 = the first 8 bytes are a valid prefix, run parse_pyint
+RFQ_HD int pyint_prefix(uint64_t w, uint32_t n) {
+#define RFQ_B8(k) ((int)((w >> (8 * (k))) & 0xFFu))
+  uint32_t m = n < 8 ? n : 8, i = 0;
+  while (i < m && is_space_ascii(RFQ_B8(i))) ++i;
+  if (i < m && (RFQ_B8(i) == '-' || RFQ_B8(i) == '+')) ++i;
+  if (i == m) return n > 8 ? 2 : 0;
+  if (!is_digit_ascii(RFQ_B8(i))) return 0;
+  bool prev_us = false;
+  for (; i < m; ++i) {
+    int c = RFQ_B8(i);
+    if (is_digit_ascii(c)) prev_us = false;
+    else if (c == '_') { if (prev_us) return 0; prev_us = true; }
+    else break;
+  }
+  if (i == m) return n > 8 ? 2 : (prev_us ? 0 : 1);
+  if (prev_us) return 0;
+  for (; i < m; ++i) if (!is_space_ascii(RFQ_B8(i))) return 0;
+#undef RFQ_B8
+  return n > 8 ? 2 : 1;
+}
 // writes str(int(token)); returns bytes
 template <class It>
 RFQ_HD uint32_t write_pyint(It it, uint8_t* out) {

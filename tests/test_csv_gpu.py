@@ -112,3 +112,13 @@ def test_csv_file_parser_api(eng, tmp_path):
     bad.write_bytes(b"a\n1\n2\n")
     with pytest.raises(FileParsingError, match="Failed to parse bad.csv: CSV parsing failed: Unable to parse CSV"):
         asyncio.run(fp.parse_file_async(str(bad)))
+
+
+def test_csv_c2_full_size_bit_exact(eng):
+    """BASELINE config C2 at its full size (1 M rows x 8 columns, 16 low_memory chunks): the GPU
+    text equals the oracle's byte for byte (about a minute of pandas on one host core)."""
+    d = corpus.rfq_csv(1_000_000, seed=0)
+    got = eng.parse_csv_many([d], 10 ** 6)[0]
+    want = oracle(d, 10 ** 6)
+    assert len(got) == len(want)
+    assert got == want
