@@ -74,11 +74,13 @@ int rfq_csv_run(rfq_ctx* ctx, const int64_t* max_rows);
 
 /* ---- sheet path: the GPU side of FileParser._parse_excel_sync (app/file_parser.py:214-252 →
  * pd.read_excel → openpyxl read-only reader → pandas TextParser → dropna/fillna/to_string).
- * The staged batch mixes worksheet parts (kind 0) and sharedStrings parts (kind 1) that the host
- * inflated from the .xlsx zip; sst_of[d] is the batch index of the sharedStrings part of sheet d
+ * The staged batch mixes worksheet parts (kind 0; kind 2 = a worksheet of a workbook with
+ * <workbookPr date1904="1">) and sharedStrings parts (kind 1) that the host inflated from the
+ * .xlsx zip; sst_of[d] is the batch index of the sharedStrings part of sheet d
  * (-1 = none); max_rows[d] = the reference's max_excel_rows; date_ids[date_off[d]..date_off[d+1])
  * are the cellXfs indices of sheet d's workbook whose number format is a date (styles.xml, read
- * on the host).  Output per sheet = df.to_string(index=False) (the host adds the
+ * on the host; bit 31 set = a timedelta format such as [h]:mm:ss).  Date-styled numbers become
+ * datetimes / times exactly as openpyxl's from_excel makes them.  Output per sheet = df.to_string(index=False) (the host adds the
  * "=== Sheet: name ===" banner and joins sheets); status RFQ_DOC_EMPTY_SHEET where the reference
  * skips the sheet (df.empty), RFQ_DOC_UNSUPPORTED for constructs not decoded on the GPU. */
 int rfq_sheets_run(rfq_ctx* ctx, const uint8_t* kind, const int32_t* sst_of, const int64_t* max_rows,

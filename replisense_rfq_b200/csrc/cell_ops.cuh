@@ -5,6 +5,7 @@
 #include "cell_format.cuh"
 #include "cell_parse.cuh"
 #include "col_decide.cuh"
+#include "datetime_fmt.cuh"
 #include "xlsx_core.cuh"
 
 namespace rfq {
@@ -14,7 +15,8 @@ namespace rfq {
 // booleans, empty / error cells) carry their value in `bits`.
 // CM_CSVQ: inside of a quoted CSV field that is clean ASCII and whose only quotes are "" pairs
 // (span = between the outer quotes, bits = decoded length)
-enum { CM_CSV = 0, CM_RAW = 1, CM_INT = 2, CM_FLOAT = 3, CM_BOOL = 4, CM_XML = 5, CM_NULL = 6, CM_CSVQ = 7 };
+enum { CM_CSV = 0, CM_RAW = 1, CM_INT = 2, CM_FLOAT = 3, CM_BOOL = 4, CM_XML = 5, CM_NULL = 6, CM_CSVQ = 7,
+       CM_DATE = 8, CM_TIME = 9 };   // sheet cells: ms since 0001-01-01 / ms of the day (datetime_fmt.cuh)
 
 // decoded bytes of a CM_CSVQ span: every "" is one "
 struct PairIter {
@@ -178,6 +180,8 @@ RFQ_HD int cell_own_ctype(const CellSrc& s) {
     case CM_INT: return CT_INT;
     case CM_FLOAT: return CT_FLOAT;
     case CM_BOOL: return CT_BOOL;
+    case CM_DATE: return CT_DATE;
+    case CM_TIME: return CT_TIME;
     default: return CT_STR;
   }
 }
@@ -270,6 +274,13 @@ RFQ_HD CellMeasure measure_cell(const CellSrc& s, int ctype) {
     m.plain_len = cell_bool(s, t) == 1 ? 4 : 5;
     return m;
   }
+  if (ctype == CT_DATE || ctype == CT_TIME) {
+    int64_t ms = (int64_t)s.bits;
+    if (ctype == CT_TIME) { m.plain_len = pytime_len(ms); return m; }
+    m.plain_len = pydatetime_len(ms);
+    m.fl = MF_FINITE | ((ms % RFQ_MS_PER_DAY) ? MF_DT_TIME : 0) | ((ms % 1000) ? MF_DT_MS : 0);
+    return m;
+  }
   if (ctype == CT_UINT) {
     UintTok u; cell_uint64(s, &u);
     m.plain_len = (uint32_t)ndigits_u64(u.v);
@@ -300,7 +311,8 @@ RFQ_HD CellMeasure measure_cell(const CellSrc& s, int ctype) {
 
 // ---- 3. print -----------------------------------------------------------------------------------
 // How a cell prints given the class of its column and the type of its chunk.
-enum { PR_EMPTY = 0, PR_INT, PR_UINT, PR_FIXED, PR_SCI, PR_OBJFLOAT, PR_BOOL, PR_STR, PR_PYINT };
+enum { PR_EMPTY = 0, PR_INT, PR_UINT, PR_FIXED, PR_SCI, PR_OBJFLOAT, PR_BOOL, PR_STR, PR_PYINT,
+       PR_DATE64, PR_DATETIME, PR_TIME };   // datetime64 column (dec = resolution) / str(datetime) / str(time)
 
 RFQ_HD int print_kind(int cls, int ctype, bool sci) {
   switch (cls) {
@@ -310,6 +322,7 @@ RFQ_HD int print_kind(int cls, int ctype, bool sci) {
     case CC_BOOL: return PR_BOOL;
     case CC_STR: return PR_STR;
     case CC_OBJF: return PR_OBJFLOAT;
+    case CC_DATE: return PR_DATE64;
     default:
       switch (ctype) {
         case CT_INT: return PR_INT;
@@ -317,6 +330,8 @@ RFQ_HD int print_kind(int cls, int ctype, bool sci) {
         case CT_INTNA: case CT_FLOAT: return PR_OBJFLOAT;
         case CT_BOOL: case CT_BOOLNA: return PR_BOOL;
         case CT_PYINT: return PR_PYINT;
+        case CT_DATE: return PR_DATETIME;
+        case CT_TIME: return PR_TIME;
         default: return PR_STR;
       }
   }
@@ -327,9 +342,12 @@ RFQ_HD void printed_size(const CellSrc& s, int ctype, int kind, int dec, uint32_
                          uint32_t* nbytes) {
   *ncp = 0; *nbytes = 0;
   TextInfo t = cell_text(s);
-  if (cell_is_nan(s, t, ctype)) return;
+  if (cell_is_nan(s, t, ctype)) { if (kind == PR_DATE64) { *ncp = 3; *nbytes = 3; } return; }   // NaT
   uint32_t n = 0;
   switch (kind) {
+    case PR_DATE64: n = date64_len(dec); break;
+    case PR_DATETIME: n = pydatetime_len((int64_t)s.bits); break;
+    case PR_TIME: n = pytime_len((int64_t)s.bits); break;
     case PR_STR: *ncp = t.ncp + t.nesc; *nbytes = t.nbytes + t.nesc; return;
     case PR_BOOL: n = cell_bool(s, t) == 1 ? 4 : 5; break;
     case PR_INT: { int64_t iv = 0; cell_int64(s, &iv); n = (uint32_t)int64_len(iv); break; }
@@ -391,8 +409,15 @@ RFQ_HD uint32_t print_cell(const CellSrc& s, int ctype, int kind, int dec, uint8
     return k;
   }
   TextInfo t = cell_text(s);
-  if (cell_is_nan(s, t, ctype)) return 0;
+  if (cell_is_nan(s, t, ctype)) {
+    if (kind != PR_DATE64) return 0;
+    out[0] = 'N'; out[1] = 'a'; out[2] = 'T';
+    return 3;
+  }
   switch (kind) {
+    case PR_DATE64: return date64_write((int64_t)s.bits, dec, out);
+    case PR_DATETIME: return pydatetime_write((int64_t)s.bits, out);
+    case PR_TIME: return pytime_write((int64_t)s.bits, out);
     case PR_BOOL: {
       const char* w = cell_bool(s, t) == 1 ? "True" : "False";
       uint32_t k = 0;

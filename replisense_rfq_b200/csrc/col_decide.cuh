@@ -25,13 +25,15 @@ enum {
   CT_STRNF = 7,   // str with the NA filter off (uint64 conflict): nothing is NaN
   CT_UNSUP = 8,   // Python-int object columns (beyond uint64) — not produced on the GPU path
   CT_XOBJ = 9,    // sheet column of mixed Python objects: every cell prints as its own type
+  CT_DATE = 11,   // sheet column whose non-blank cells are all datetimes: datetime64, blanks NaT
+  CT_TIME = 12,   // (cell level only) a datetime.time inside a mixed object column
   CT_PYINT = 10   // object column of Python ints (a value beyond uint64 / a negative next to an overflow):
                   // every token is int()-parsable and prints as str(int(token)); NA -> NaN
 };
 
 // printing class of a whole column
 // CC_OBJF: float64 column with holes after fillna('') -> object column whose cells are all floats
-enum { CC_INT = 0, CC_UINT = 1, CC_FLOAT = 2, CC_BOOL = 3, CC_STR = 4, CC_OBJ = 5, CC_OBJF = 6, CC_UNSUP = 7 };
+enum { CC_INT = 0, CC_UINT = 1, CC_FLOAT = 2, CC_BOOL = 3, CC_STR = 4, CC_OBJ = 5, CC_OBJF = 6, CC_UNSUP = 7, CC_DATE = 8 };
 
 // per (chunk, column) classification flags, OR-reduced over the cells
 enum {
@@ -95,7 +97,7 @@ RFQ_HD uint32_t chunk_rows_for_width(uint32_t width) {
 RFQ_HD int fold_column_class(const uint8_t* ctypes, uint32_t n_chunks, uint32_t stride,
                              bool any_nan_left) {
   bool all_int = true, all_uint = true, all_num = true, all_bool = true, all_str = true;
-  bool unsup = false, any_uint = false;
+  bool unsup = false, any_uint = false, all_date = true;
   for (uint32_t k = 0; k < n_chunks; ++k) {
     int t = ctypes[(size_t)k * stride];
     if (t == CT_UNSUP) unsup = true;
@@ -105,6 +107,7 @@ RFQ_HD int fold_column_class(const uint8_t* ctypes, uint32_t n_chunks, uint32_t 
     if (!(t == CT_INT || t == CT_INTNA || t == CT_FLOAT)) all_num = false;
     if (t != CT_BOOL) all_bool = false;
     if (t != CT_STR) all_str = false;
+    if (t != CT_DATE) all_date = false;
   }
   if (unsup) return CC_UNSUP;
   if (n_chunks == 0) return CC_OBJ;  // no data rows: dtype object, prints nothing
@@ -114,6 +117,7 @@ RFQ_HD int fold_column_class(const uint8_t* ctypes, uint32_t n_chunks, uint32_t 
   if (all_num) return any_nan_left ? CC_OBJF : CC_FLOAT;
   if (all_bool) return CC_BOOL;
   if (all_str) return CC_STR;
+  if (all_date) return CC_DATE;
   return CC_OBJ;
 }
 
@@ -128,7 +132,7 @@ struct ChunkMeasure {
   uint32_t fl;            // bit0 any |v| > 1e6 (incl. inf), bit1 any 0 < |v| < 1e-6, bit2 any finite
   uint32_t nan_left;      // a NaN cell in a row that survives dropna
 };
-enum { MF_LARGE = 1, MF_SMALL = 2, MF_FINITE = 4 };
+enum { MF_LARGE = 1, MF_SMALL = 2, MF_FINITE = 4, MF_DT_TIME = 8, MF_DT_MS = 16 };  // MF_DT_*: datetime cells
 
 struct ColumnLayout {
   int cls;
@@ -167,6 +171,12 @@ RFQ_HD ColumnLayout layout_column(int cls, const ChunkMeasure* m, const uint8_t*
     for (uint32_t k = 0; k < n_chunks; ++k)
       if (m[(size_t)k * stride].plain_len > w) w = m[(size_t)k * stride].plain_len;
     header_cp += 1;
+  } else if (cls == CC_DATE) {
+    // one format for the column, from the finest resolution present (NaT never sets the width)
+    uint32_t fl = 0, nat = 0;
+    for (uint32_t k = 0; k < n_chunks; ++k) { fl |= m[(size_t)k * stride].fl; nat |= m[(size_t)k * stride].nan_left; }
+    L.dec = (fl & MF_DT_MS) ? 2 : (fl & MF_DT_TIME) ? 1 : 0;
+    w = (fl & MF_FINITE) ? (L.dec == 0 ? 10u : L.dec == 1 ? 19u : 23u) : (nat ? 3u : 0u);
   } else if (cls == CC_STR) {
     for (uint32_t k = 0; k < n_chunks; ++k)
       if (m[(size_t)k * stride].plain_len > w) w = m[(size_t)k * stride].plain_len;

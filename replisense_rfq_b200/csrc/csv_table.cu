@@ -331,6 +331,9 @@ __device__ __forceinline__ int format_number(const CellSrc& s, int ct, int kind,
     }
     case PR_SCI: return sci_write(sci7(cell_as_double(s, ct)), buf);
     case PR_PYINT: return -1;   // arbitrary length: measured and written in place
+    case PR_DATE64: return (int)date64_write((int64_t)s.bits, dec, buf);
+    case PR_DATETIME: return (int)pydatetime_write((int64_t)s.bits, buf);
+    case PR_TIME: return (int)pytime_write((int64_t)s.bits, buf);
     default: return 0;
   }
 }
@@ -342,7 +345,11 @@ __device__ __forceinline__ uint32_t emit_cell(const CellSrc& src, int ct, int ki
                                               uint32_t width, uint8_t* field, bool fill) {
   TextInfo t = cell_text(src);
   bool na = cell_is_nan(src, t, ct);
-  if (na) { if (fill) for (uint32_t q = 0; q < width; ++q) field[q] = ' '; return 0; }
+  if (na) {
+    if (fill) for (uint32_t q = 0; q < width; ++q) field[q] = ' ';
+    if (kind == PR_DATE64) { field[width - 3] = 'N'; field[width - 2] = 'a'; field[width - 1] = 'T'; }
+    return 0;
+  }
   if (kind == PR_STR) {
     uint32_t ncp = t.ncp + t.nesc, pad = width - ncp;
     if (fill) for (uint32_t q = 0; q < pad; ++q) field[q] = ' ';

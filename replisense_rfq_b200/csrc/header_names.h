@@ -102,6 +102,27 @@ inline HeaderInfo parse_header(const uint8_t* doc, uint64_t len, uint32_t sep, b
   return h;
 }
 
+// Header row of a sheet: labels keep their Python type (pandas/io/parsers/python_parser.py
+// _infer_columns).  kind per label: 0 str (or blank -> "Unnamed: k"), 1 int, 2 bool, 3 datetime,
+// 4 time, anything else = a type whose Index formatting is not restated (float, NaN).
+// Supported: all labels int (an Int64 Index), or at least one str label next to int / bool /
+// datetime / time labels (an object Index: every label prints as str(label)).  Declined: Index
+// dtypes pandas formats as a whole (all bool, all datetime, ...), bool next to int (True == 1 is one
+// dict key for the de-duplication), and equal text under different types (2024 vs "2024").
+inline bool sheet_labels_supported(const std::vector<int>& kind, const std::vector<std::string>& text) {
+  bool has_str = false, has_int = false, has_bool = false, has_other = false;
+  for (int k : kind) {
+    if (k == 0) has_str = true; else if (k == 1) has_int = true; else if (k == 2) has_bool = true;
+    else if (k == 3 || k == 4) has_other = true; else return false;
+  }
+  if ((has_bool || has_other) && !has_str) return false;
+  if (has_bool && has_int) return false;
+  for (size_t i = 0; i < kind.size(); ++i)
+    for (size_t j = i + 1; j < kind.size(); ++j)
+      if (kind[i] != kind[j] && text[i] == text[j]) return false;
+  return true;
+}
+
 // "Empty DataFrame\nColumns: [a, b]\nIndex: []" (display.max_seq_items = 100)
 inline std::string empty_frame_text(const std::vector<std::string>& names) {
   std::string s = "Empty DataFrame\nColumns: [";

@@ -57,7 +57,7 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
     int64_t mr = max_rows ? max_rows[d] : 1000;
     cap[d] = (uint32_t)std::min<int64_t>(std::max<int64_t>(mr, 0), 0x7FFFFFF0) + 1;  // file_rows_needed
     if (date_off) doff[d + 1] = date_off[d + 1];
-    if (kind[d] == 0 && sst_of[d] >= 0 && ((uint32_t)sst_of[d] >= n || kind[sst_of[d]] != 1)) {
+    if (!(kind[d] & 1) && sst_of[d] >= 0 && ((uint32_t)sst_of[d] >= n || !(kind[sst_of[d]] & 1))) {
       c->err = "rfq_sheets_run: sst_of must point at a sharedStrings document";
       return RFQ_ERR_ARG;
     }
@@ -102,7 +102,7 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
   xa.n_rows = h_tot[0]; xa.n_cells = h_tot[1]; xa.n_si = h_tot[2];
   // ---- 2. positions, shared strings, rows, cells
   uint64_t sst_bytes = 0;
-  for (uint32_t d = 0; d < n; ++d) if (kind[d] == 1) sst_bytes += c->h_doc_len[d];
+  for (uint32_t d = 0; d < n; ++d) if (kind[d] & 1) sst_bytes += c->h_doc_len[d];
   xa.rowpos = c->pool.alloc<uint32_t>((size_t)xa.n_rows + 1);
   xa.row_c0 = c->pool.alloc<uint32_t>((size_t)xa.n_rows + 1);
   xa.rownum = c->pool.alloc<uint32_t>((size_t)xa.n_rows + 1);
@@ -130,12 +130,12 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
     T.col_base = (uint32_t)n_cols; T.stat_base = (uint32_t)n_cols;
     slot_r0[d] = (uint32_t)n_slots; r2_base[d] = (uint32_t)n_r2; item_base[d] = (uint32_t)n_items;
     T.item_base = (uint32_t)n_items;
-    if (kind[d] == 1) { n_slots += 1; continue; }           // sharedStrings part: no output of its own
+    if (kind[d] & 1) { n_slots += 1; continue; }           // sharedStrings part: no output of its own
     n_r2 += (uint64_t)sh.lastrow + 1;                       // every sheet owns its row map (the scatter
                                                             // kernel writes it for all unflagged sheets)
     uint32_t fl = sh.flags;
     if (sst_of[d] >= 0) fl |= h_shape[sst_of[d]].flags;
-    if (fl || sh.W > 1024) { c->r_status[d] = RFQ_DOC_UNSUPPORTED; n_slots += 1; continue; }
+    if (xu_problem(fl) || sh.W > 1024) { c->r_status[d] = RFQ_DOC_UNSUPPORTED; n_slots += 1; continue; }
     if (sh.lastrow <= 1) { c->r_status[d] = RFQ_DOC_EMPTY_SHEET; n_slots += 1; continue; }
     T.W = sh.W; T.h = sh.W; T.lead = 0;
     T.n_data = sh.lastrow - 1;
@@ -189,14 +189,17 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
     std::vector<std::string> raw(T.W);
     std::vector<size_t> unnamed;
     bool ok = true, all_int = true;
+    std::vector<int> lkind(T.W, 0);
     for (uint32_t j = 0; j < T.W; ++j) {
       uint32_t g = T.col_base + j, mode = h_hmeta[2 * g], len = h_hmeta[2 * g + 1];
       if (mode != CM_INT) all_int = false;
+      lkind[j] = mode == CM_INT ? 1 : mode == CM_BOOL ? 2 : mode == CM_DATE ? 3 : mode == CM_TIME ? 4
+                 : (mode == CM_RAW || mode == CM_XML || mode == CM_NULL) ? 0 : 9;
       if (mode == CM_NULL) { raw[j] = "Unnamed: " + std::to_string(j); unnamed.push_back(j); }
-      else if ((mode == CM_RAW || mode == CM_XML || mode == CM_INT) && len != 0xFFFFFFFFu)
-        raw[j].assign((const char*)h_hdr + (size_t)g * 256, len);
-      else ok = false;  // float / boolean / oversized labels: pandas formats the Index as a whole
+      else if (lkind[j] != 9 && len != 0xFFFFFFFFu) raw[j].assign((const char*)h_hdr + (size_t)g * 256, len);
+      else ok = false;  // float / oversized labels
     }
+    if (ok && !sheet_labels_supported(lkind, raw)) ok = false;
     if (!ok) { T.active = 0; c->r_status[d] = RFQ_DOC_UNSUPPORTED; continue; }
     std::vector<std::string> before = raw;
     dedupe_names(raw, unnamed);

@@ -11,16 +11,28 @@ namespace rfq {
 // document-level problems (never guessed: the sheet is reported RFQ_DOC_UNSUPPORTED)
 enum {
   XU_BANG = 1u << 0,        // comment / CDATA / doctype inside the part
-  XU_NO_REF = 1u << 1,      // <row> or <c> without r=
+  XU_NO_REF = 1u << 1,      // malformed r= on a <row> or <c>
   XU_ORDER = 1u << 2,       // rows / columns not strictly increasing
-  XU_DATE = 1u << 3,        // date-styled number or t="d"
+  XU_DATE = 1u << 3,        // timedelta-styled number, negative date serial, or t="d" (ISO 8601 text)
   XU_RICH_INLINE = 1u << 4, // inline string with rich-text runs
   XU_BAD_NUMBER = 1u << 5,  // numeric literal we cannot type exactly (overflow, nan, malformed)
   XU_BAD_SST = 1u << 6,     // shared-string index out of range / no table
   XU_ENTITY = 1u << 7,      // unknown entity
   XU_TYPE = 1u << 8,        // unknown t=
-  XU_X005F = 1u << 9        // 'x005F_' escape inside a shared string
+  XU_X005F = 1u << 9,       // 'x005F_' escape inside a shared string
+  // not problems by themselves: which of its rows / cells carry r=.  openpyxl counts rows and
+  // columns from the previous element when r= is missing (worksheet/_reader.py parse_row /
+  // parse_cell); a part whose rows (cells) ALL lack r= is decoded by position, a mix is declined
+  XU_ROW_NOREF = 1u << 10, XU_ROW_HASREF = 1u << 11, XU_C_NOREF = 1u << 12, XU_C_HASREF = 1u << 13
 };
+#define RFQ_XU_INFO (XU_ROW_NOREF | XU_ROW_HASREF | XU_C_NOREF | XU_C_HASREF)
+RFQ_HD bool xu_rows_by_position(uint32_t f) { return (f & XU_ROW_NOREF) && !(f & XU_ROW_HASREF); }
+RFQ_HD bool xu_cells_by_position(uint32_t f) { return (f & XU_C_NOREF) && !(f & XU_C_HASREF); }
+RFQ_HD bool xu_problem(uint32_t f) {
+  if (f & ~(uint32_t)RFQ_XU_INFO) return true;
+  if ((f & XU_ROW_NOREF) && (f & XU_ROW_HASREF)) return true;
+  return (f & XU_C_NOREF) && (f & XU_C_HASREF);
+}
 
 struct XCell {
   uint32_t col;     // 1-based column
@@ -79,7 +91,9 @@ RFQ_HD uint32_t xlsx_row_number(const uint8_t* p, const uint8_t* e, uint32_t* fl
   const uint8_t* g = p;
   while (g < e && *g != '>') ++g;
   const uint8_t* vb; uint32_t vn;
-  if (!xml_attr(p, g, 'r', &vb, &vn) || vn == 0 || vn > 9) { *flags |= XU_NO_REF; return 0; }
+  if (!xml_attr(p, g, 'r', &vb, &vn) || vn == 0) { *flags |= XU_ROW_NOREF; return 0; }
+  *flags |= XU_ROW_HASREF;
+  if (vn > 9) { *flags |= XU_NO_REF; return 0; }
   uint32_t r = 0;
   for (uint32_t i = 0; i < vn; ++i) { uint32_t d = vb[i] - '0'; if (d > 9) { *flags |= XU_NO_REF; return 0; } r = r * 10 + d; }
   return r;
@@ -91,10 +105,21 @@ struct SstView {             // shared-string table of the workbook this sheet b
   uint32_t n;
 };
 
+// a date-styled number: from_excel; an out-of-range date is openpyxl's '#VALUE!' error cell -> NaN
+RFQ_HD XCell xlsx_date_cell(XCell x, double v, bool date1904, uint32_t* flags) {
+  if (v < 0.) { *flags |= XU_DATE; return x; }   // before the epoch: not produced by spreadsheets
+  ExcelDate ed = excel_to_datetime(v, date1904);
+  if (ed.kind == XD_ERROR) { x.mode = CM_FLOAT; x.bits = 0x7FF8000000000000ull; return x; }
+  x.mode = ed.kind == XD_TIME ? CM_TIME : CM_DATE;
+  x.bits = (uint64_t)ed.ms;
+  return x;
+}
+
 // ---- <c ...>...</c> -----------------------------------------------------------------------------
 // doc/len: the sheet part; cpos: offset of "<c". date_ids: sorted style ids that are dates.
 RFQ_HD XCell xlsx_parse_cell(const uint8_t* doc, uint32_t len, uint32_t cpos, const SstView& sst,
-                             const uint32_t* date_ids, uint32_t n_date, uint32_t* flags) {
+                             const uint32_t* date_ids, uint32_t n_date, bool date1904,
+                             uint32_t* flags) {
   XCell x; x.col = 0; x.mode = CM_NULL; x.bits = 0;
   const uint8_t* p = doc + cpos;
   const uint8_t* e = doc + len;
@@ -103,7 +128,9 @@ RFQ_HD XCell xlsx_parse_cell(const uint8_t* doc, uint32_t len, uint32_t cpos, co
   if (g >= e) return x;
   const uint8_t* vb; uint32_t vn;
   uint32_t row = 0;
-  if (!xml_attr(p, g, 'r', &vb, &vn) || !a1_parse(vb, vn, &x.col, &row)) { *flags |= XU_NO_REF; return x; }
+  if (!xml_attr(p, g, 'r', &vb, &vn) || vn == 0) *flags |= XU_C_NOREF;   // col stays 0: set by position
+  else if (!a1_parse(vb, vn, &x.col, &row)) { *flags |= XU_NO_REF; return x; }
+  else *flags |= XU_C_HASREF;
   // type
   int ty = 'n';
   if (xml_attr(p, g, 't', &vb, &vn)) {
@@ -147,17 +174,23 @@ RFQ_HD XCell xlsx_parse_cell(const uint8_t* doc, uint32_t len, uint32_t cpos, co
   if (!val_b || val_n == 0) return x;  // findtext(...) or None -> None -> ""
   switch (ty) {
     case 'n': {
-      for (uint32_t i = 0; i < n_date; ++i) if (date_ids[i] == style) { *flags |= XU_DATE; return x; }
+      // date_ids: cellXfs indices with a date number format; bit 31 marks a timedelta format
+      int dstyle = 0;
+      for (uint32_t i = 0; i < n_date; ++i)
+        if ((date_ids[i] & 0x7FFFFFFFu) == style) dstyle = (date_ids[i] >> 31) ? 2 : 1;
+      if (dstyle == 2) { *flags |= XU_DATE; return x; }
       bool is_float = false;
       for (uint32_t i = 0; i < val_n; ++i) if (val_b[i] == '.' || val_b[i] == 'e' || val_b[i] == 'E') is_float = true;
       if (!is_float) {
         int64_t iv;
         if (parse_int64(RawIter(val_b, val_n), &iv) != INT_OK) { *flags |= XU_BAD_NUMBER; return x; }
+        if (dstyle) return xlsx_date_cell(x, (double)iv, date1904, flags);
         x.mode = CM_INT; x.bits = (uint64_t)iv;
         return x;
       }
       double v;
       if (!strtod_exact(val_b, val_n, &v) || dbl_is_inf(v) || dbl_is_nan(v)) { *flags |= XU_BAD_NUMBER; return x; }
+      if (dstyle) return xlsx_date_cell(x, v, date1904, flags);
       // pandas _convert_cell: integral floats become ints
       if (v > -9.2e18 && v < 9.2e18) {
         int64_t iv = (int64_t)v;
@@ -203,13 +236,17 @@ enum {
   XF_FIRST_IS_INT = 1u << 8,  // first data row holds a Python int (or bool)
   XF_BAD_UTF8 = 1u << 9,
   XF_ENTITY = 1u << 10,
-  XF_BIG = 1u << 11           // int-looking string beyond int64
+  XF_BIG = 1u << 11,          // int-looking string beyond int64
+  XF_DATE = 1u << 12,         // datetime.datetime object
+  XF_TIME = 1u << 13          // datetime.time object
 };
 
 RFQ_HD uint32_t xclassify_cell(const CellSrc& s, bool first_row) {
   if (s.missing || s.mode == CM_NULL) return XF_NULL;
   if (s.mode == CM_INT) return XF_INT | XF_TYPED_NUM | XF_NON_STR | (first_row ? XF_FIRST_IS_INT : 0);
   if (s.mode == CM_BOOL) return XF_BOOL | XF_NON_STR | (first_row ? XF_FIRST_IS_INT : 0);
+  if (s.mode == CM_DATE) return XF_DATE | XF_NON_STR;
+  if (s.mode == CM_TIME) return XF_TIME | XF_NON_STR;
   if (s.mode == CM_FLOAT) {
     if (dbl_is_nan(bits_as_double(s.bits))) return XF_NULL;
     return XF_FLOAT | XF_TYPED_NUM | XF_NON_STR;
@@ -229,6 +266,13 @@ RFQ_HD uint32_t xclassify_cell(const CellSrc& s, bool first_row) {
 
 RFQ_HD int xdecide_column(uint32_t f) {
   if (f & XF_BIG) return CT_UNSUP;
+  // a datetime / time object makes maybe_convert_numeric raise TypeError and is no bool either;
+  // the DataFrame constructor then turns an all-datetime (+NaN) object column into datetime64
+  const bool dt = (f & (XF_DATE | XF_TIME)) != 0;
+  if (dt) {
+    if ((f & XF_DATE) && !(f & (XF_TIME | XF_FLOAT | XF_INT | XF_BOOL | XF_STR_NONNUM))) return CT_DATE;
+    return CT_XOBJ;
+  }
   if (!(f & XF_STR_NONNUM)) {            // lib.maybe_convert_numeric succeeds
     if (f & (XF_NULL | XF_FLOAT)) return CT_FLOAT;
     if (f & XF_INT) return CT_INT;

@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(256) xml_tags_kernel(XmlArgs a) {
   const uint8_t* doc = a.arena + a.doc_off[d];
   uint32_t base = tile * RFQ_TILE + lane * 16;
   uint32_t m = lt_mask(doc, len, base);
-  bool is_sst = a.kind[d] != 0;
+  bool is_sst = (a.kind[d] & 1) != 0;
   uint32_t nr = 0, nc = 0, ns = 0, bang = 0;
   uint32_t kinds = 0;  // 2 bits per byte: 1 row, 2 cell, 3 si
   for (uint32_t mm = m; mm; mm &= mm - 1) {
@@ -130,6 +130,14 @@ __global__ void __launch_bounds__(128) xrow_kernel(XmlArgs a) {
   if (flags) atomicOr(&a.shape[d].flags, flags);
 }
 
+// rows of a part that never writes r= are numbered by position (row_counter += 1)
+__global__ void __launch_bounds__(128) xrow_fix_kernel(XmlArgs a) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n_rows) return;
+  uint32_t d = x_find(a.row_base, a.n_docs + 1, i);
+  if (xu_rows_by_position(a.shape[d].flags)) a.rownum[i] = i - a.row_base[d] + 1;
+}
+
 // ---- cells ----------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) xcell_kernel(XmlArgs a) {
   uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -144,7 +152,7 @@ __global__ void __launch_bounds__(128) xcell_kernel(XmlArgs a) {
   }
   uint32_t flags = 0;
   XCell x = xlsx_parse_cell(doc, a.doc_len[d], a.cpos[k], sv, a.date_ids + a.date_off[d],
-                            a.date_off[d + 1] - a.date_off[d], &flags);
+                            a.date_off[d + 1] - a.date_off[d], (a.kind[d] & 2) != 0, &flags);
   if (x.mode == CM_RAW) x.bits += 0;  // offsets are already global into the string arena
   // row element of this cell, ordering checks
   uint32_t rb = a.row_base[d], nr = a.row_base[d + 1] - rb;
@@ -152,6 +160,7 @@ __global__ void __launch_bounds__(128) xcell_kernel(XmlArgs a) {
   if (nr == 0 || a.row_c0[e] > k) flags |= XU_ORDER;   // a <c> outside any <row>
   uint32_t r = a.rownum[e];
   if (e > rb && a.rownum[e - 1] >= r) flags |= XU_ORDER;
+  if ((flags & XU_C_NOREF) && nr) x.col = k - a.row_c0[e] + 1;   // col_counter += 1 from the row start
   ((XCell*)a.xcells)[k] = x;
   if (flags) atomicOr(&a.shape[d].flags, flags);
   if (!xcell_is_empty(x) && r >= 1 && r <= a.cap_rows[d]) {
@@ -187,7 +196,7 @@ __global__ void __launch_bounds__(128) xscatter_kernel(XmlArgs a, const uint32_t
   if (i >= a.n_rows) return;
   uint32_t d = x_find(a.row_base, a.n_docs + 1, i);
   uint32_t r = a.rownum[i];
-  if (a.shape[d].flags == 0 && r >= 1 && r <= a.shape[d].lastrow) r2elem[r2_base[d] + r] = i;
+  if (!xu_problem(a.shape[d].flags) && r >= 1 && r <= a.shape[d].lastrow) r2elem[r2_base[d] + r] = i;
 }
 
 // header cells (sheet row 1): decoded text, 256 bytes per column; meta = {mode, length}
@@ -216,6 +225,9 @@ __global__ void __launch_bounds__(128) xheader_kernel(TableArgs a, uint8_t* __re
     write_u64_rev(mag, o + n);
     if (iv < 0) o[0] = '-';
   }
+  else if (s.mode == CM_BOOL) { const char* w = (s.bits & 1) ? "True" : "False"; while (w[n]) { o[n] = (uint8_t)w[n]; ++n; } }
+  else if (s.mode == CM_DATE) n = pydatetime_write((int64_t)s.bits, o);   // str(label)
+  else if (s.mode == CM_TIME) n = pytime_write((int64_t)s.bits, o);
   hdr_meta[2 * j] = s.mode;
   hdr_meta[2 * j + 1] = n;
 }
@@ -303,6 +315,7 @@ void xml_decode(const XmlArgs& a, cudaStream_t s) {
   prof_mark("xrow_kernel", s);
   if (a.n_rows) {
     RFQ_LAUNCH(xrow_kernel, (a.n_rows + 127) / 128, 128, 0, s, a);
+    RFQ_LAUNCH(xrow_fix_kernel, (a.n_rows + 127) / 128, 128, 0, s, a);
     RFQ_LAUNCH(xrow_order_kernel, (a.n_rows + 127) / 128, 128, 0, s, a);
   }
   prof_mark("xcell_kernel", s);

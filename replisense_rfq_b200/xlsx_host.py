@@ -33,7 +33,17 @@ def _is_date_format(code) -> bool:
     return re.search(r"(?<![_\\])[dmhysDMHYS]", code) is not None
 
 
+_TIMEDELTA = re.compile(r"\[hh?\](:mm(:ss(\.0*)?)?)?|\[mm?\](:ss(\.0*)?)?|\[ss?\](\.0*)?", re.I)
+_TD_BIT = 0x80000000  # rfq_sheets_run: a date style whose format is a timedelta format
+
+
+def _is_timedelta_format(code) -> bool:
+    return code is not None and _TIMEDELTA.search(code.split(";")[0]) is not None
+
+
 def _date_style_ids(styles_xml) -> "set[int]":
+    """cellXfs indices with a date number format (openpyxl styles/stylesheet.py _normalise_numbers);
+    timedelta formats carry _TD_BIT."""
     if not styles_xml:
         return set()
     root = ET.fromstring(styles_xml)
@@ -47,16 +57,20 @@ def _date_style_ids(styles_xml) -> "set[int]":
     if xfs is not None:
         for idx, xf in enumerate(xfs.findall("{%s}xf" % _NS)):
             fid = int(xf.get("numFmtId", "0"))
-            if (fid in custom and _is_date_format(custom[fid])) or (fid not in custom and fid in _BUILTIN_DATE_IDS):
-                out.add(idx)
+            if fid in custom:
+                if _is_date_format(custom[fid]):
+                    out.add(idx | (_TD_BIT if _is_timedelta_format(custom[fid]) else 0))
+            elif fid in _BUILTIN_DATE_IDS:
+                out.add(idx | (_TD_BIT if fid == 46 else 0))  # 46 = "[h]:mm:ss"
     return out
 
 
 class Workbook:
-    __slots__ = ("sheet_names", "sheets", "sst", "date_styles")
+    __slots__ = ("sheet_names", "sheets", "sst", "date_styles", "date1904")
 
-    def __init__(self, sheet_names, sheets, sst, date_styles):
+    def __init__(self, sheet_names, sheets, sst, date_styles, date1904=False):
         self.sheet_names, self.sheets, self.sst, self.date_styles = sheet_names, sheets, sst, date_styles
+        self.date1904 = date1904
 
 
 def open_workbook(data: bytes) -> Workbook:
@@ -69,6 +83,8 @@ def open_workbook(data: bytes) -> Workbook:
             t = t[1:] if t.startswith("/") else posixpath.normpath(posixpath.join("xl", t))
             rels[r.get("Id")] = (r.get("Type"), t)
     root = ET.fromstring(z.read("xl/workbook.xml"))
+    pr = root.find("{%s}workbookPr" % _NS)
+    date1904 = pr is not None and pr.get("date1904") in ("1", "true")   # openpyxl WorkbookParser.epoch
     sheet_names, sheets = [], []
     for sh in root.find("{%s}sheets" % _NS).findall("{%s}sheet" % _NS):
         typ, target = rels[sh.get("{%s}id" % _NS_REL)]
@@ -83,7 +99,7 @@ def open_workbook(data: bytes) -> Workbook:
     if sst is None and "xl/sharedStrings.xml" in names:
         sst = z.read("xl/sharedStrings.xml")
     styles = z.read("xl/styles.xml") if "xl/styles.xml" in names else None
-    return Workbook(sheet_names, sheets, sst, _date_style_ids(styles))
+    return Workbook(sheet_names, sheets, sst, _date_style_ids(styles), date1904)
 
 
 def parse_workbooks(engine, books, max_rows: int = 1000) -> "list":
@@ -96,7 +112,7 @@ def parse_workbooks(engine, books, max_rows: int = 1000) -> "list":
             sst_idx = len(docs)
             docs.append(wb.sst); kind.append(1); sst_of.append(-1); dates.append(()); owner.append((b, None))
         for k, xml in enumerate(wb.sheets):
-            docs.append(xml); kind.append(0); sst_of.append(sst_idx); dates.append(wb.date_styles)
+            docs.append(xml); kind.append(2 if wb.date1904 else 0); sst_of.append(sst_idx); dates.append(wb.date_styles)
             owner.append((b, k))
     res = engine.sheets_batch(docs, kind, sst_of, max_rows, dates) if docs else None
     from .engine import EngineError

@@ -475,3 +475,115 @@ def sheet_xml_fuzz(seed: int):
             sst.append("<si><t>%s</t></si>" % xml_escape(s))
     sst.append("</sst>")
     return "".join(out).encode("utf-8"), "".join(sst).encode("utf-8")
+
+
+def sheet_xml_dates(seed: int):
+    """A worksheet with date-styled numbers (style 3 = a date format, style 4 = a timedelta format):
+    whole days, day fractions, serials below 1 (times) and below 60 (the 1900 leap-year bug),
+    out-of-range serials, date columns with blanks / error cells / strings / plain numbers.
+    Returns (sheet_xml, sst_xml, date_ids, td_ids, date1904)."""
+    r = random.Random(1000003 * seed + 17)
+    ncols = r.randint(2, 6)
+    nrows = r.randint(1, 30)
+    date1904 = r.random() < 0.15
+    strings, index = [], {}
+
+    def sid(s):
+        if s not in index:
+            index[s] = len(strings)
+            strings.append(s)
+        return index[s]
+
+    def serial(kind):
+        if kind == "day":
+            return "%d" % r.randint(20000, 60000)
+        if kind == "dayf":
+            return "%d.0" % r.randint(20000, 60000)
+        if kind == "sec":
+            return repr(r.randint(30000, 50000) + r.randint(0, 86399) / 86400)
+        if kind == "ms":
+            return repr(r.uniform(30000, 50000))
+        if kind == "time":
+            return repr(r.choice([0.5, 0.25, 0.75001, r.random(), 0.999999999, 0.0]))
+        if kind == "early":
+            return r.choice(["0", "1", "59", "60", "61", "1.5", "59.999", "31.25", "0.99999999999"])
+        if kind == "edge":
+            return r.choice(["2958465", "2958465.9999", "2958465.99999999", "2958466", "1e7", "3e6",
+                             "4000001", "99999999999", "2958464.5"])
+        raise ValueError(kind)
+
+    col_kinds = [r.choice(["day", "day", "dayf", "sec", "ms", "time", "early", "edge", "anydate",
+                           "date+blank", "date+str", "date+num", "int", "price", "sst"])
+                 for _ in range(ncols)]
+    use_td = r.random() < 0.04
+    out = [_XML_HEAD]
+    for i in range(nrows + 1):
+        rownum = i + 1
+        out.append('<row r="%d">' % rownum)
+        for c in range(ncols):
+            ref = "%s%d" % (col_letters(c), rownum)
+            if i == 0:
+                h = r.random()
+                if c and h < 0.06:      # a date / time / bool as a column label, next to string labels
+                    out.append('<c r="%s" s="3"><v>%s</v></c>' % (ref, r.choice(["45000", "45000", "45007.5", "0.25"])))
+                elif c and h < 0.08:
+                    out.append('<c r="%s" t="b"><v>%d</v></c>' % (ref, r.randint(0, 1)))
+                else:
+                    out.append('<c r="%s" t="s"><v>%d</v></c>' % (ref, sid(r.choice(["Date", "Delivery", "ETA", "Qty", "When"]))))
+                continue
+            k = col_kinds[c]
+            if k == "int":
+                out.append('<c r="%s"><v>%d</v></c>' % (ref, r.randint(1, 5000)))
+            elif k == "price":
+                out.append('<c r="%s" s="2"><v>%s</v></c>' % (ref, repr(r.randint(1, 10 ** 6) / 100)))
+            elif k == "sst":
+                out.append('<c r="%s" t="s"><v>%d</v></c>' % (ref, sid(r.choice(["RJF544", "tbd", "NA", "asap"]))))
+            else:
+                if k == "anydate":
+                    kk = r.choice(["day", "dayf", "sec", "ms", "time", "early", "edge"])
+                elif k == "date+blank":
+                    kk = r.choice(["day", "day", "blank", "err", "nastr"])
+                elif k == "date+str":
+                    kk = r.choice(["day", "sec", "str", "blank"])
+                elif k == "date+num":
+                    kk = r.choice(["day", "ms", "num", "bool"])
+                else:
+                    kk = k if r.random() > 0.06 else r.choice(["blank", "err"])
+                if kk == "blank":
+                    if r.random() < 0.5:
+                        out.append('<c r="%s" s="3"/>' % ref)
+                elif kk == "err":
+                    out.append('<c r="%s" s="3" t="e"><v>#N/A</v></c>' % ref)
+                elif kk == "nastr":
+                    out.append('<c r="%s" t="s"><v>%d</v></c>' % (ref, sid(r.choice(["NA", "", "null"]))))
+                elif kk == "str":
+                    out.append('<c r="%s" t="s"><v>%d</v></c>' % (ref, sid(r.choice(["tbd", "2024-01-05", "12"]))))
+                elif kk == "num":
+                    out.append('<c r="%s"><v>%s</v></c>' % (ref, r.choice(["5", "45000", "2.5"])))
+                elif kk == "bool":
+                    out.append('<c r="%s" t="b"><v>%d</v></c>' % (ref, r.randint(0, 1)))
+                else:
+                    style = 4 if use_td and r.random() < 0.3 else 3
+                    out.append('<c r="%s" s="%d"><v>%s</v></c>' % (ref, style, serial(kk)))
+        out.append("</row>")
+    out.append(_XML_TAIL)
+    sst = ['<?xml version="1.0" encoding="UTF-8" standalone="yes"?>\r\n'
+           '<sst xmlns="http://schemas.openxmlformats.org/spreadsheetml/2006/main" '
+           'count="%d" uniqueCount="%d">' % (len(strings), len(strings))]
+    for s in strings:
+        sst.append("<si><t>%s</t></si>" % xml_escape(s))
+    sst.append("</sst>")
+    return "".join(out).encode("utf-8"), "".join(sst).encode("utf-8"), {3, 4}, {4}, date1904
+
+
+def strip_refs(sheet_xml: bytes, rows: bool = True, cells: bool = True) -> bytes:
+    """The same worksheet as a writer that omits r= would emit it (rows and cells are then numbered
+    by position: openpyxl worksheet/_reader.py row_counter / col_counter).  Only meaningful for
+    dense sheets (no skipped rows or columns)."""
+    import re
+    s = sheet_xml
+    if rows:
+        s = re.sub(rb'<row r="\d+"', b"<row", s)
+    if cells:
+        s = re.sub(rb'<c r="[A-Z]+\d+"', b"<c", s)
+    return s

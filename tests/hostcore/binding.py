@@ -90,7 +90,7 @@ def csv_parse(data: bytes, nrows: int = 1000):
     raise RuntimeError("hostcore buffer too small")
 
 
-def sheet_parse(sheet_xml: bytes, sst_xml, date_ids=(), nrows: int = 1000):
+def sheet_parse(sheet_xml: bytes, sst_xml, date_ids=(), nrows: int = 1000, td_ids=(), date1904=False):
     """Sequential model of the GPU sheet pipeline: (status, text). status 0 ok, 2 unsupported,
     3 empty sheet."""
     import numpy as np
@@ -99,8 +99,8 @@ def sheet_parse(sheet_xml: bytes, sst_xml, date_ids=(), nrows: int = 1000):
     n = C.c_uint64()
     L = lib()
     L.hc_sheet_parse.argtypes = [C.c_char_p, C.c_uint32, C.c_char_p, C.c_uint32, C.c_void_p, C.c_uint32,
-                                 C.c_int64, C.c_char_p, C.c_uint64, C.POINTER(C.c_uint64)]
-    d = np.asarray(sorted(date_ids), dtype=np.uint32)
+                                 C.c_int, C.c_int64, C.c_char_p, C.c_uint64, C.POINTER(C.c_uint64)]
+    d = np.asarray(sorted(int(i) | (0x80000000 if i in td_ids else 0) for i in date_ids), dtype=np.uint32)
     st = L.hc_sheet_parse(sheet_xml, len(sheet_xml), sst_xml, len(sst_xml) if sst_xml else 0,
-                          d.ctypes.data if len(d) else None, len(d), nrows, buf, cap, C.byref(n))
+                          d.ctypes.data if len(d) else None, len(d), 1 if date1904 else 0, nrows, buf, cap, C.byref(n))
     return st, (buf.raw[:n.value].decode("utf-8") if st == 0 else None)

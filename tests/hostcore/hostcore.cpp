@@ -326,7 +326,7 @@ std::string py_repr_double(double v) {
 extern "C" {
 // status: 0 ok, 2 unsupported, 3 empty sheet (df.empty -> skipped by the reference)
 int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uint32_t sst_len,
-                   const uint32_t* date_ids, uint32_t n_date, int64_t nrows, uint8_t* out, uint64_t cap,
+                   const uint32_t* date_ids, uint32_t n_date, int date1904, int64_t nrows, uint8_t* out, uint64_t cap,
                    uint64_t* out_len) {
   *out_len = 0;
   uint32_t flags = 0;
@@ -358,10 +358,13 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
       if (!rows.empty()) rows.back().c1 = (uint32_t)cells.size();
       rows.push_back({xlsx_row_number(doc + i, e, &flags), (uint32_t)cells.size(), (uint32_t)cells.size()});
     } else if (tg == XT_C) {
-      cells.push_back(xlsx_parse_cell(doc, len, i, sv, date_ids, n_date, &flags));
+      cells.push_back(xlsx_parse_cell(doc, len, i, sv, date_ids, n_date, date1904 != 0, &flags));
     }
   }
   if (!rows.empty()) rows.back().c1 = (uint32_t)cells.size();
+  if (xu_rows_by_position(flags)) for (size_t k = 0; k < rows.size(); ++k) rows[k].r = (uint32_t)k + 1;
+  if (flags & XU_C_NOREF)
+    for (auto& R : rows) for (uint32_t k = R.c0; k < R.c1; ++k) if (cells[k].col == 0) cells[k].col = k - R.c0 + 1;
   uint32_t cap_rows = (uint32_t)std::min<int64_t>(nrows, 0x7FFFFFF0) + 1;  // file_rows_needed
   uint32_t W = 0, lastrow = 0, prev_r = 0;
   for (auto& R : rows) {
@@ -374,7 +377,7 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
       if (R.r <= cap_rows && !xcell_is_empty(cells[k])) { W = std::max(W, cells[k].col); lastrow = std::max(lastrow, R.r); }
     }
   }
-  if (flags) return 2;
+  if (xu_problem(flags)) return 2;
   if (lastrow <= 1) return 3;  // no data rows -> empty frame -> sheet skipped
   uint32_t ndata = lastrow - 1;
   std::vector<int> r2e(lastrow + 1, -1);
@@ -395,10 +398,18 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
   // header
   std::vector<std::string> raw(W); std::vector<size_t> unnamed;
   bool all_int = true;
+  std::vector<int> lkind(W, 0);
   for (uint32_t c = 0; c < W; ++c) {
     CellSrc s = cell(1, c);
     std::string nm;
-    if (s.mode == CM_BOOL || s.mode == CM_FLOAT) return 2;  // float / bool labels: pandas formats the Index as a whole
+    if (s.mode == CM_FLOAT) return 2;  // float labels
+    lkind[c] = s.mode == CM_INT ? 1 : s.mode == CM_BOOL ? 2 : s.mode == CM_DATE ? 3 : s.mode == CM_TIME ? 4 : 0;
+    if (s.mode == CM_BOOL) nm = (s.bits & 1) ? "True" : "False";
+    if (s.mode == CM_DATE || s.mode == CM_TIME) {
+      uint8_t b[32];
+      uint32_t n = s.mode == CM_DATE ? pydatetime_write((int64_t)s.bits, b) : pytime_write((int64_t)s.bits, b);
+      nm.assign((const char*)b, n);
+    }
     if (s.mode != CM_INT) all_int = false;
     if (s.mode == CM_INT) nm = std::to_string((long long)s.bits);
     else if (s.mode == CM_RAW) nm.assign((const char*)s.p, s.n);
@@ -406,6 +417,7 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
     if (s.mode == CM_NULL) { nm = "Unnamed: " + std::to_string(c); unnamed.push_back(c); }
     raw[c] = nm;
   }
+  if (!sheet_labels_supported(lkind, raw)) return 2;
   {
     std::vector<size_t> order; std::vector<bool> un(W, false);
     for (size_t k : unnamed) un[k] = true;

@@ -215,6 +215,59 @@ def test_sheet_model_fuzz_vs_oracle():
     assert unsup < 60
 
 
+def test_sheet_model_without_refs_vs_oracle():
+    """Worksheets whose <row> and/or <c> elements omit r= are numbered by position."""
+    bad, unsup = [], 0
+    for seed in range(300):
+        sx, ss = corpus.sheet_xml_fuzz(seed) if seed % 2 else corpus.sheet_xml_doc(seed)
+        sx = corpus.strip_refs(sx, rows=seed % 3 != 1, cells=seed % 3 != 2)
+        st, got = H.sheet_parse(sx, ss)
+        if st == 2:
+            unsup += 1
+            continue
+        if (None if st == 3 else got) != _sheet_oracle(sx, ss):
+            bad.append(seed)
+    assert not bad, bad
+    assert unsup < 40
+
+
+def test_sheet_model_dates_vs_oracle():
+    """Date-styled numbers: openpyxl from_excel (datetime / time / 1900 leap bug / 1904 epoch /
+    out of range -> NaN) and pandas' datetime64 / object printing; timedelta styles are declined."""
+    from oracle import xlsx_reader as X
+    bad, unsup, dates = [], 0, 0
+    for seed in range(400):
+        sx, ss, ids, tds, d1904 = corpus.sheet_xml_dates(seed)
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            df = X.table_to_frame(X.sheet_table(sx, X.read_string_table(ss), ids, tds, d1904, 1000), 1000)
+            want = None if df.empty else O.frame_to_text(df)
+        dates += any(str(t).startswith("datetime64") for t in df.dtypes)
+        st, got = H.sheet_parse(sx, ss, ids, 1000, tds, d1904)
+        if st == 2:
+            unsup += 1
+            continue
+        if (None if st == 3 else got) != want:
+            bad.append(seed)
+    assert not bad, bad
+    assert unsup < 40 and dates > 100
+
+
+def test_excel_serial_known_answers():
+    """Pins the oracle's from_excel on known answers (Excel's own calendar and the values
+    openpyxl's test-suite uses): serial 1 = 1900-01-01, 59 = 1900-02-28, 61 = 1900-03-01 (serial 60
+    is the non-existent 1900-02-29), a fraction below 1 is a time, 1904 epoch."""
+    from oracle.xlsx_reader import from_excel, MAC_EPOCH
+    import datetime as dt
+    assert from_excel(1) == dt.datetime(1900, 1, 1)
+    assert from_excel(59) == dt.datetime(1900, 2, 28)
+    assert from_excel(61) == dt.datetime(1900, 3, 1)
+    assert from_excel(45000) == dt.datetime(2023, 3, 15)
+    assert from_excel(0.5) == dt.time(12, 0)
+    assert from_excel(39448, MAC_EPOCH) == dt.datetime(2012, 1, 2)
+    assert from_excel(40372.27616898148) == dt.datetime(2010, 7, 13, 6, 37, 41)
+
+
 def test_strtod_exact_matches_python_float():
     import ctypes as C
     L = H.lib()

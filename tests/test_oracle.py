@@ -97,3 +97,22 @@ def test_live_reference_differential(tmp_path):
         p2.write_bytes(t)
         assert O.parse_txt_bytes(t) == asyncio.run(fp._parse_txt_async(p2)), seed
     logging.disable(logging.NOTSET)
+
+
+def test_host_date_styles_match_oracle():
+    """The product's host-side styles.xml reader (date / timedelta number formats, date1904) agrees
+    with the oracle's restatement of openpyxl's is_date_format / is_timedelta_format."""
+    from replisense_rfq_b200 import xlsx_host as Hh
+    from oracle import xlsx_reader as X
+    codes = ["General", "0.00", "yyyy\\-mm\\-dd", "dd/mm/yyyy;@", "[h]:mm:ss", "[mm]:ss.0", "[$-409]d\\-mmm\\-yy;@",
+             '#,##0.00\\ "days"', "[Red]0.00", "h:mm AM/PM", '"day" 0', "0.0E+00", "mmm\\ yy", "[ss].00",
+             "_-* #,##0.00\\ _d_-", "\\d0", "@", "[hh]:mm", "[Blue]yy"]
+    fmts = "".join('<numFmt numFmtId="%d" formatCode="%s"/>' % (170 + i, c.replace("&", "&amp;").replace('"', "&quot;"))
+                   for i, c in enumerate(codes))
+    xfs = "".join('<xf numFmtId="%d"/>' % k for k in list(range(0, 50)) + [170 + i for i in range(len(codes))])
+    styles = ('<styleSheet xmlns="http://schemas.openxmlformats.org/spreadsheetml/2006/main"><numFmts>%s</numFmts>'
+              '<cellXfs>%s</cellXfs></styleSheet>' % (fmts, xfs)).encode()
+    dates, tds = X.date_style_ids(styles)
+    got = Hh._date_style_ids(styles)
+    assert {i & 0x7FFFFFFF for i in got} == dates and len(dates) > 12
+    assert {i & 0x7FFFFFFF for i in got if i & 0x80000000} == tds and len(tds) >= 4

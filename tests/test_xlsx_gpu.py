@@ -126,3 +126,93 @@ def test_sheet_nrows_cap(eng):
     for cap in (1, 10, 57):
         (st, g), = _batch(eng, [(sx, ss)], cap)
         assert (None if st == 3 else g) == _oracle(sx, ss, cap), cap
+
+
+def _oracle_dates(sx, ss, ids, tds, d1904, nrows=1000):
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        df = X.table_to_frame(X.sheet_table(sx, X.read_string_table(ss), ids, tds, d1904, nrows), nrows)
+        return None if df.empty else O.frame_to_text(df)
+
+
+def test_sheet_dates(eng):
+    """Date-styled numbers: datetime64 columns (date only / seconds / milliseconds, NaT), datetimes
+    and times inside object columns, the 1900 leap-year shift, the 1904 epoch, out-of-range serials."""
+    cases = [corpus.sheet_xml_dates(s) for s in range(500)]
+    docs, kind, sst_of, ids = [], [], [], []
+    for sx, ss, dates, tds, d1904 in cases:
+        docs += [ss, sx]; kind += [1, 2 if d1904 else 0]; sst_of += [-1, len(docs) - 2]
+        ids += [(), [i | (0x80000000 if i in tds else 0) for i in dates]]
+    r = eng.sheets_batch(docs, kind, sst_of, 1000, ids)
+    bad, unsup = [], 0
+    for i, (sx, ss, dates, tds, d1904) in enumerate(cases):
+        st = int(r.status[2 * i + 1])
+        if st == 2:
+            unsup += 1
+            continue
+        got = None if st == 3 else r.doc_str(2 * i + 1)
+        if got != _oracle_dates(sx, ss, dates, tds, d1904):
+            bad.append(i)
+    assert not bad, bad[:10]
+    assert unsup < 0.1 * len(cases)
+
+
+_STYLES = ('<?xml version="1.0" encoding="UTF-8"?><styleSheet xmlns="http://schemas.openxmlformats.org/'
+           'spreadsheetml/2006/main"><numFmts count="2"><numFmt numFmtId="164" formatCode="yyyy\\-mm\\-dd"/>'
+           '<numFmt numFmtId="165" formatCode="#,##0.00\\ &quot;days&quot;"/></numFmts><cellXfs count="5">'
+           '<xf numFmtId="0"/><xf numFmtId="165"/><xf numFmtId="2"/><xf numFmtId="164"/><xf numFmtId="22"/>'
+           '</cellXfs></styleSheet>')
+
+
+def test_xlsx_with_dates_through_file_parser(eng, tmp_path):
+    """A workbook whose styles.xml declares a custom date format (cellXfs 3), a builtin one
+    (cellXfs 4 = numFmtId 22) and a non-date custom format with a quoted 'days' (cellXfs 1)."""
+    import asyncio
+    from replisense_rfq_b200 import FileParser
+    ss = ('<sst xmlns="http://schemas.openxmlformats.org/spreadsheetml/2006/main"><si><t>Part</t></si>'
+          '<si><t>Delivery</t></si><si><t>Stamp</t></si><si><t>Lead</t></si><si><t>RJF544</t></si></sst>')
+    rows = ['<row r="1"><c r="A1" t="s"><v>0</v></c><c r="B1" t="s"><v>1</v></c><c r="C1" t="s"><v>2</v></c>'
+            '<c r="D1" t="s"><v>3</v></c></row>']
+    for i in range(6):
+        r = i + 2
+        rows.append('<row r="%d"><c r="A%d" t="s"><v>4</v></c><c r="B%d" s="3"><v>%d</v></c>'
+                    '<c r="C%d" s="4"><v>%s</v></c><c r="D%d" s="1"><v>%d</v></c></row>'
+                    % (r, r, r, 45900 + 7 * i, r, repr(45900 + i / 7), r, 10 + i))
+    sx = ('<worksheet xmlns="http://schemas.openxmlformats.org/spreadsheetml/2006/main"><sheetData>'
+          + "".join(rows) + "</sheetData></worksheet>")
+    wb = ('<workbook xmlns="http://schemas.openxmlformats.org/spreadsheetml/2006/main" xmlns:r="http://'
+          'schemas.openxmlformats.org/officeDocument/2006/relationships"><sheets><sheet name="RFQ" '
+          'sheetId="1" r:id="rId1"/></sheets></workbook>')
+    rels = ('<Relationships xmlns="http://schemas.openxmlformats.org/package/2006/relationships">'
+            '<Relationship Id="rId1" Type="http://schemas.openxmlformats.org/officeDocument/2006/'
+            'relationships/worksheet" Target="worksheets/sheet1.xml"/></Relationships>')
+    path = tmp_path / "dates.xlsx"
+    with zipfile.ZipFile(path, "w", zipfile.ZIP_DEFLATED) as z:
+        z.writestr("xl/workbook.xml", wb)
+        z.writestr("xl/_rels/workbook.xml.rels", rels)
+        z.writestr("xl/styles.xml", _STYLES)
+        z.writestr("xl/sharedStrings.xml", ss)
+        z.writestr("xl/worksheets/sheet1.xml", sx)
+    want = O.parse_excel_path(path, 1000)
+    assert "2025-08-31" in want and "Lead" in want
+    res = asyncio.run(FileParser(engine=eng).parse_file_async(str(path)))
+    assert res["raw_text"] == want
+
+
+def test_sheet_without_refs(eng):
+    """Writers that omit r= on <row> and/or <c>: rows and columns are numbered by position
+    (openpyxl worksheet/_reader.py row_counter / col_counter)."""
+    pairs = []
+    for seed in range(300):
+        sx, ss = corpus.sheet_xml_fuzz(seed) if seed % 2 else corpus.sheet_xml_doc(seed, 5, 120)
+        pairs.append((corpus.strip_refs(sx, rows=seed % 3 != 1, cells=seed % 3 != 2), ss))
+    got = _batch(eng, pairs)
+    bad, unsup = [], 0
+    for i, ((st, g), (sx, ss)) in enumerate(zip(got, pairs)):
+        if st == 2:
+            unsup += 1
+            continue
+        if (None if st == 3 else g) != _oracle(sx, ss):
+            bad.append(i)
+    assert not bad, bad[:10]
+    assert unsup < 0.15 * len(pairs)
