@@ -41,6 +41,9 @@ extern "C" {
 #define RFQ_DOC_UNSUPPORTED 2
 /* sheet produced an empty frame (reference skips it: app/file_parser.py:228-229) */
 #define RFQ_DOC_EMPTY_SHEET 3
+/* prompt path: raw_text is empty or whitespace only → the reference answers "Empty or invalid
+ * input text" without building a prompt (app/rfq_agent.py:138-140) */
+#define RFQ_DOC_EMPTY_TEXT 4
 
 typedef struct rfq_ctx rfq_ctx;
 
@@ -90,10 +93,23 @@ int rfq_sheets_parse(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets
                      const int32_t* sst_of, const int64_t* max_rows, const uint32_t* date_off,
                      const uint32_t* date_ids);
 
+/* ---- prompt assembly (the step right after the parser): the text handling of
+ * RFQFieldGenerator._generate_sync (app/rfq_agent.py:138-151).  The staged batch holds raw_text
+ * documents (UTF-8).  Per document: whitespace-only (str.strip() empty) → RFQ_DOC_EMPTY_TEXT and
+ * no output; more than max_chars code points (the reference: 8000) → the first max_chars code
+ * points + mark ("... [truncated]"); output = head + text + tail, where the host passes
+ * head = EXTRACTION_PROMPT_TEMPLATE + '\n"""\n' and tail = '\n"""'. */
+int rfq_prompt_run(rfq_ctx* ctx, const uint8_t* head, uint32_t head_len, const uint8_t* tail,
+                   uint32_t tail_len, const uint8_t* mark, uint32_t mark_len, uint32_t max_chars);
+
 /* ---- device → host copy of the last run's output ---- */
 int rfq_fetch(rfq_ctx* ctx);
 
 /* convenience: stage + run + fetch */
+int rfq_prompt_build(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets,
+                     const uint64_t* lengths, uint32_t n_docs, const uint8_t* head,
+                     uint32_t head_len, const uint8_t* tail, uint32_t tail_len,
+                     const uint8_t* mark, uint32_t mark_len, uint32_t max_chars);
 int rfq_text_parse(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets,
                    const uint64_t* lengths, uint32_t n_docs);
 int rfq_csv_parse(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets,

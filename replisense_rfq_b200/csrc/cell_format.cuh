@@ -11,13 +11,19 @@ namespace rfq {
 
 RFQ_HD int ndigits_u64(uint64_t v) {
   int n = 1;
-  while (v >= 10) { v /= 10; ++n; }
-  return n;
+  if (v >= 10000000000000000ull) { v /= 10000000000000000ull; n += 16; }
+  uint32_t x;
+  if (v >= 100000000ull) { x = (uint32_t)(v / 100000000ull); n += 8; } else x = (uint32_t)v;
+  if (x >= 10000u) { x /= 10000u; n += 4; }
+  if (x >= 100u) { x /= 100u; n += 2; }
+  return n + (x >= 10u);
 }
 
 // writes decimal digits of v ending at end (exclusive); returns pointer to first digit
 RFQ_HD uint8_t* write_u64_rev(uint64_t v, uint8_t* end) {
-  do { *--end = (uint8_t)('0' + v % 10); v /= 10; } while (v);
+  while (v > 0xFFFFFFFFull) { *--end = (uint8_t)('0' + v % 10); v /= 10; }
+  uint32_t x = (uint32_t)v;   // 32-bit divisions from here on
+  do { *--end = (uint8_t)('0' + x % 10u); x /= 10u; } while (x);
   return end;
 }
 

@@ -88,9 +88,19 @@ RFQ_HD void csv_simplify(CellSrc& s) {
   if (!span_is_clean(s.p + 1, s.n - 2, 0xFF)) return;
   // clean ASCII with quotes inside: fine iff they all come as "" pairs
   uint32_t pairs = 0;
-  for (uint32_t i = 1; i + 1 < s.n; ++i) {
-    if (s.p[i] != '"') continue;
-    if (i + 2 < s.n && s.p[i + 1] == '"') { ++pairs; ++i; } else return;
+  const uint64_t ones = 0x0101010101010101ull, highs = 0x8080808080808080ull;
+  for (uint32_t i = 1; i + 1 < s.n;) {
+    uint32_t rem = s.n - 1 - i;
+    uint64_t y = load8_masked(s.p + i, rem) ^ (ones * '"');
+    uint64_t hit = (y - ones) & ~y & highs;                // exact for the first match
+    if (rem < 8) hit &= (1ull << (8 * rem)) - 1ull;
+    if (!hit) { i += 8; continue; }
+#ifdef __CUDA_ARCH__
+    i += (uint32_t)(__ffsll((long long)hit) - 1) >> 3;
+#else
+    i += (uint32_t)__builtin_ctzll(hit) >> 3;
+#endif
+    if (i + 2 < s.n && s.p[i + 1] == '"') { ++pairs; i += 2; } else return;
   }
   s.p += 1; s.n -= 2; s.mode = CM_CSVQ; s.bits = s.n - pairs;
 }
@@ -109,6 +119,52 @@ RFQ_HD double bits_as_double(uint64_t b) {
    : (src).mode == CM_CSVQ ? F(PairIter((src).p, (src).n), ##__VA_ARGS__)     \
                           : F(RawIter((src).p, (src).n), ##__VA_ARGS__))
 
+// The parsers are inlined only for plain spans (CM_RAW: clean CSV tokens, shared strings); the
+// three decoding iterators share ONE out-of-line copy of each parser per translation unit.
+// Arguments and results travel by value so that the caller's CellSrc stays in registers.
+#define RFQ_WITH_SLOW_ITER(mode, p, n, F, ...)                         \
+  ((mode) == CM_CSV ? F(CsvIter((p), (n)), ##__VA_ARGS__)              \
+   : (mode) == CM_XML ? F(XmlIter((p), (n)), ##__VA_ARGS__)            \
+                      : F(PairIter((p), (n)), ##__VA_ARGS__))
+struct I64Res { int64_t v; int st; };
+struct U64Res { UintTok u; int st; };
+struct F64Res { double v; int ok; };
+RFQ_HD_COLD TextInfo scan_text_slow(const uint8_t* p, uint32_t n, int mode) {
+  return RFQ_WITH_SLOW_ITER(mode, p, n, scan_text);
+}
+RFQ_HD_COLD I64Res parse_int64_slow(const uint8_t* p, uint32_t n, int mode) {
+  I64Res r; r.v = 0;
+  r.st = RFQ_WITH_SLOW_ITER(mode, p, n, parse_int64, &r.v);
+  return r;
+}
+RFQ_HD_COLD U64Res parse_uint64_slow(const uint8_t* p, uint32_t n, int mode) {
+  U64Res r;
+  r.st = RFQ_WITH_SLOW_ITER(mode, p, n, parse_uint64, &r.u);
+  return r;
+}
+RFQ_HD_COLD F64Res parse_double_slow(const uint8_t* p, uint32_t n, int mode) {   // 2 = an inf word
+  F64Res r; r.v = 0.;
+  r.ok = RFQ_WITH_SLOW_ITER(mode, p, n, parse_double, &r.v) ? 1 : 0;
+  if (!r.ok) {
+    int k = RFQ_WITH_SLOW_ITER(mode, p, n, inf_token);
+    if (k) { r.ok = 2; r.v = (double)k; }
+  }
+  return r;
+}
+RFQ_HD_COLD PyInt parse_pyint_any(const uint8_t* p, uint32_t n, int mode) {
+  return mode == CM_RAW ? parse_pyint(RawIter(p, n)) : RFQ_WITH_SLOW_ITER(mode, p, n, parse_pyint);
+}
+RFQ_HD_COLD uint32_t write_pyint_any(const uint8_t* p, uint32_t n, int mode, uint8_t* out) {
+  return mode == CM_RAW ? write_pyint(RawIter(p, n), out) : RFQ_WITH_SLOW_ITER(mode, p, n, write_pyint, out);
+}
+RFQ_HD double dbl_inf(int sign) {
+#ifdef __CUDA_ARCH__
+  return sign > 0 ? __longlong_as_double(0x7FF0000000000000LL) : __longlong_as_double(0xFFF0000000000000LL);
+#else
+  return sign > 0 ? __builtin_huge_val() : -__builtin_huge_val();
+#endif
+}
+
 RFQ_HD TextInfo cell_text(const CellSrc& s) {
   if (s.missing || !cell_is_text(s)) {
     TextInfo t; t.nbytes = t.ncp = t.nesc = 0; t.first8 = 0; t.utf8_ok = true; t.has_fchar = false;
@@ -123,21 +179,32 @@ RFQ_HD TextInfo cell_text(const CellSrc& s) {
   if (s.mode == CM_CSVQ) {
     TextInfo t; t.nbytes = (uint32_t)s.bits; t.ncp = t.nbytes; t.nesc = 0; t.utf8_ok = true; t.has_fchar = false;
     t.first8 = 0;
+    uint64_t raw = load8_masked(s.p, s.n);
+    const uint64_t ones = 0x0101010101010101ull, highs = 0x8080808080808080ull;
+    uint64_t y = raw ^ (ones * '"');
+    if (s.n >= 8 && !((y - ones) & ~y & highs)) { t.first8 = raw; return t; }   // no quote in the first 8
     PairIter it(s.p, s.n);
     for (int k = 0; k < 8; ++k) { int c = it.next(); if (c < 0) break; t.first8 |= (uint64_t)c << (8 * k); }
     return t;
   }
-  return RFQ_WITH_ITER(s, scan_text);
+  if (s.mode == CM_RAW) return scan_text(RawIter(s.p, s.n));
+  return scan_text_slow(s.p, s.n, s.mode);
 }
 RFQ_HD int cell_int64(const CellSrc& s, int64_t* v) {
   if (s.mode == CM_INT) { *v = (int64_t)s.bits; return INT_OK; }
   if (s.mode == CM_BOOL) { *v = (int64_t)(s.bits & 1); return INT_OK; }
   if (!cell_is_text(s)) return INT_INVALID;
-  return RFQ_WITH_ITER(s, parse_int64, v);
+  if (s.mode == CM_RAW) return parse_int64(RawIter(s.p, s.n), v);
+  I64Res r = parse_int64_slow(s.p, s.n, s.mode);
+  *v = r.v;
+  return r.st;
 }
 RFQ_HD int cell_uint64(const CellSrc& s, UintTok* v) {
   if (!cell_is_text(s)) { v->v = 0; v->neg = false; v->gt_i64 = false; return INT_INVALID; }
-  return RFQ_WITH_ITER(s, parse_uint64, v);
+  if (s.mode == CM_RAW) return parse_uint64(RawIter(s.p, s.n), v);
+  U64Res r = parse_uint64_slow(s.p, s.n, s.mode);
+  *v = r.u;
+  return r.st;
 }
 RFQ_HD bool cell_double(const CellSrc& s, double* v) {
   if (s.mode == CM_FLOAT) { *v = bits_as_double(s.bits); return true; }
@@ -151,14 +218,21 @@ RFQ_HD bool cell_double(const CellSrc& s, double* v) {
   }
   if (s.mode == CM_BOOL) { *v = (s.bits & 1) ? 1.0 : 0.0; return true; }
   if (!cell_is_text(s)) return false;
-  if (RFQ_WITH_ITER(s, parse_double, v)) return true;
-  int k = RFQ_WITH_ITER(s, inf_token);
+  if (s.mode != CM_RAW) {
+    F64Res r = parse_double_slow(s.p, s.n, s.mode);
+    if (!r.ok) return false;
+    *v = r.ok == 2 ? dbl_inf(r.v > 0. ? 1 : -1) : r.v;
+    return true;
+  }
+  if (parse_double(RawIter(s.p, s.n), v)) return true;
+  {   // the inf words start with [+-]?[iI]
+    uint64_t w = load8_masked(s.p, s.n);
+    uint32_t b0 = (uint32_t)(w & 0xFFu), b1 = (uint32_t)((w >> 8) & 0xFFu);
+    if ((((b0 == '+' || b0 == '-') ? b1 : b0) | 0x20u) != 'i') return false;
+  }
+  int k = inf_token(RawIter(s.p, s.n));
   if (k == 0) return false;
-#ifdef __CUDA_ARCH__
-  *v = k > 0 ? __longlong_as_double(0x7FF0000000000000LL) : __longlong_as_double(0xFFF0000000000000LL);
-#else
-  *v = k > 0 ? __builtin_huge_val() : -__builtin_huge_val();
-#endif
+  *v = dbl_inf(k);
   return true;
 }
 
@@ -193,6 +267,17 @@ RFQ_HD uint32_t classify_cell(const CellSrc& s, int* int_status) {
   if (is_na_token(t.nbytes, t.first8)) return SF_ANY_NA;
   uint32_t f = SF_ANY_NONNA;
   if (!t.utf8_ok) f |= SF_BAD_UTF8;
+  // Every numeric grammar here (str_to_int64 / str_to_uint64 / precise_xstrtod / the inf words /
+  // int()) starts with white space, a sign, a digit, '.' or 'i': any other first byte is a plain
+  // word, decided without running the parsers.
+  const uint32_t c0 = (uint32_t)(t.first8 & 0xFFu);
+  if (cell_is_text(s) && !(is_digit_ascii((int)c0) || c0 == '+' || c0 == '-' || c0 == '.' ||
+                           is_space_ascii((int)c0) || (c0 | 0x20u) == 'i')) {
+    *int_status = INT_INVALID;
+    f |= SF_UINT_INVALID | SF_FLOAT_BAD | SF_PYINT_BAD;
+    if (bool_token(t.nbytes, t.first8) < 0) f |= SF_BOOL_BAD;
+    return f;
+  }
   int64_t iv;
   int st = cell_int64(s, &iv);
   *int_status = st;
@@ -207,7 +292,13 @@ RFQ_HD uint32_t classify_cell(const CellSrc& s, int* int_status) {
     return f;
   }
   UintTok u;
-  int us = cell_uint64(s, &u);
+  int us;
+  if (st == INT_INVALID && cell_is_text(s) && (is_digit_ascii((int)c0) || c0 == '+' || c0 == '.')) {
+    // no minus sign and int64 stopped on a bad character before any overflow: uint64 stops there too
+    us = INT_INVALID; u.v = 0; u.neg = false; u.gt_i64 = false;
+  } else {
+    us = cell_uint64(s, &u);
+  }
   if (us == INT_INVALID) f |= SF_UINT_INVALID;
   else if (us == INT_OVERFLOW) f |= SF_UINT_OVF;
   else { if (u.neg) f |= SF_NEG; if (u.gt_i64) f |= SF_GT_I64; }
@@ -218,7 +309,7 @@ RFQ_HD uint32_t classify_cell(const CellSrc& s, int* int_status) {
   // uint64 token is int()-parsable; a token that cannot even start an integer is not
   if (!(us == INT_OK && !u.neg)) {
     int pp = pyint_prefix(t.first8, t.nbytes);   // dates, decimals, words: decided in registers
-    if (pp == 0 || (pp == 2 && !RFQ_WITH_ITER(s, parse_pyint).ok)) f |= SF_PYINT_BAD;
+    if (pp == 0 || (pp == 2 && !parse_pyint_any(s.p, s.n, s.mode).ok)) f |= SF_PYINT_BAD;
   }
   return f;
 }
@@ -287,7 +378,7 @@ RFQ_HD CellMeasure measure_cell(const CellSrc& s, int ctype) {
     return m;
   }
   if (ctype == CT_PYINT) {
-    PyInt pi = RFQ_WITH_ITER(s, parse_pyint);
+    PyInt pi = parse_pyint_any(s.p, s.n, s.mode);
     m.plain_len = pi.ndig + (pi.neg ? 1u : 0u);
     return m;
   }
@@ -352,7 +443,7 @@ RFQ_HD void printed_size(const CellSrc& s, int ctype, int kind, int dec, uint32_
     case PR_BOOL: n = cell_bool(s, t) == 1 ? 4 : 5; break;
     case PR_INT: { int64_t iv = 0; cell_int64(s, &iv); n = (uint32_t)int64_len(iv); break; }
     case PR_UINT: { UintTok u; cell_uint64(s, &u); n = (uint32_t)ndigits_u64(u.v); break; }
-    case PR_PYINT: { PyInt pi = RFQ_WITH_ITER(s, parse_pyint); n = pi.ndig + (pi.neg ? 1u : 0u); break; }
+    case PR_PYINT: { PyInt pi = parse_pyint_any(s.p, s.n, s.mode); n = pi.ndig + (pi.neg ? 1u : 0u); break; }
     case PR_FIXED: { Fixed6 f = fixed6(cell_as_double(s, ctype)); n = (uint32_t)fixed_len(f, dec); break; }
     case PR_OBJFLOAT: { Fixed6 f = fixed6(cell_as_double(s, ctype)); n = (uint32_t)objfloat_len(f); break; }
     case PR_SCI: n = (uint32_t)sci_len_of(cell_as_double(s, ctype)); break;
@@ -438,7 +529,7 @@ RFQ_HD uint32_t print_cell(const CellSrc& s, int ctype, int kind, int dec, uint8
       write_u64_rev(u.v, out + n);
       return n;
     }
-    case PR_PYINT: return RFQ_WITH_ITER(s, write_pyint, out);
+    case PR_PYINT: return write_pyint_any(s.p, s.n, s.mode, out);
     case PR_FIXED: {
       double v = cell_as_double(s, ctype);
       Fixed6 f = fixed6(v);

@@ -1,0 +1,170 @@
+// Sweep 2 of 3 (measure + layout + row offsets).  Cell typing + numeric parse, column decisions, and the fixed-width formatter / emitter
+// (SURVEY.md §7.1b K3, K4, K5): everything `pd.read_csv` does after tokenising plus
+// `dropna(how='all').fillna('')` and `to_string(index=False)` (app/file_parser.py:301-305).
+//
+// Work item = a block of `rb` consecutive data rows of one document that never crosses a
+// low_memory chunk boundary; a CTA takes items grid-stride, one thread per cell; a warp works on
+// consecutive rows of ONE column, so its lanes run the same parser on tokens of similar length
+// (mixing columns in a warp left 6 of 32 lanes active: profiles/r01_emit_v1_*); the item's bytes
+// are shared by its warps through L1.  Column statistics are reduced in
+// shared memory per item and merged into global memory with one atomic per column per item.
+// Three sweeps over the cells: classify -> (decide) -> measure -> (layout, row offsets) -> emit.
+// Tokens are re-parsed in each sweep instead of being materialised: the bytes stay in L2 and a
+// typed copy would cost more HBM traffic than the re-parse costs issue slots.
+#include "table_common.cuh"
+
+namespace rfq {
+
+// ---- decide chunk types (one thread per document; entries are few) ----------------------------
+__global__ void __launch_bounds__(128) csv_decide_kernel(TableArgs a) {
+  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= a.n_docs) return;
+  const TDoc D = a.docs[d];
+  if (!D.active) return;
+  const ChunkStat* stat = (const ChunkStat*)a.stat;
+  int flags = 0;
+  for (uint32_t k = 0; k < D.n_chunks; ++k) {
+    bool nf = false;
+    for (uint32_t c = 0; c < D.W; ++c) {
+      uint32_t e = D.stat_base + k * D.W + c;
+      ChunkStat S = stat[e];
+      if (S.flags & SF_BAD_UTF8) flags |= 1;
+      int t = decide_chunk_type(S);
+      a.ctype[e] = (uint8_t)t;
+      if (t == CT_STRNF && c >= D.lead) nf = true;
+    }
+    a.chunk_nf[D.stat_base + k * D.W] = nf ? 1 : 0;
+  }
+  if (flags) atomicOr(a.doc_flags + d, flags);
+}
+
+// ---- sweep 2: measure ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256, 3) csv_measure_kernel(TableArgs a) {
+  __shared__ uint32_t s_m[8][RFQ_MAX_W];  // plain, ip, tz(min), inf, obj, sci, fl(or), nan_left(or)
+  __shared__ uint32_t s_doc, s_keep;
+  ChunkMeasure* meas = (ChunkMeasure*)a.meas;
+  for (uint32_t item = blockIdx.x; item < a.n_items; item += gridDim.x) {
+    ItemCtx ic = item_ctx(a, item, &s_doc);
+    const TDoc D = a.docs[ic.d];
+    uint32_t W = D.W;
+    for (uint32_t c = threadIdx.x; c < W; c += blockDim.x) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) s_m[q][c] = q == 2 ? 6u : 0u;
+    }
+    if (threadIdx.x == 0) s_keep = 0;
+    __syncthreads();
+    if (!(a.doc_flags[ic.d] & 1)) {
+      uint32_t rbp = 32;
+      while (rbp < ic.nrows) rbp <<= 1;
+      const uint32_t ngrp = blockDim.x / rbp, rr = threadIdx.x % rbp, grp = threadIdx.x / rbp;
+      const uint32_t slot = D.r0 + 1 + ic.row0 + rr;
+      if (rr < ic.nrows && grp < ngrp && row_kept(a, D, slot, ic.chunk)) {
+        const RowCur rc = row_open(a, slot);
+        if (grp == 0) atomicAdd(&s_keep, 1u);
+        uint32_t extra = 0;
+        for (uint32_t c = D.lead + grp; c < W; c += ngrp) {
+          int ct = a.ctype[D.stat_base + ic.chunk * W + c];
+          CellMeasure m = measure_cell(row_cell(a, D, rc, c), ct);
+          if (m.is_nan) { if (!s_m[7][c]) s_m[7][c] = 1; continue; }
+          if (m.plain_len > s_m[0][c]) atomicMax(&s_m[0][c], m.plain_len);
+          if (m.ip_len > s_m[1][c]) atomicMax(&s_m[1][c], m.ip_len);
+          if (m.tz < s_m[2][c]) atomicMin(&s_m[2][c], m.tz);
+          if (m.inf_len > s_m[3][c]) atomicMax(&s_m[3][c], m.inf_len);
+          if (m.obj_len > s_m[4][c]) atomicMax(&s_m[4][c], m.obj_len);
+          if (m.sci_len > s_m[5][c]) atomicMax(&s_m[5][c], m.sci_len);
+          if ((s_m[6][c] & m.fl) != m.fl) atomicOr(&s_m[6][c], m.fl);
+          extra += m.extra_bytes;
+        }
+        if (extra) { if (ngrp == 1) a.row_extra[slot] = extra; else atomicAdd(a.row_extra + slot, extra); }
+      }
+    }
+    __syncthreads();
+    for (uint32_t c = threadIdx.x + D.lead; c < W; c += blockDim.x) {
+      ChunkMeasure* M = meas + D.stat_base + ic.chunk * W + c;
+      if (s_m[0][c]) atomicMax(&M->plain_len, s_m[0][c]);
+      if (s_m[1][c]) atomicMax(&M->ip_len, s_m[1][c]);
+      if (s_m[2][c] < 6) atomicMin(&M->min_tz, s_m[2][c]);
+      if (s_m[3][c]) atomicMax(&M->inf_len, s_m[3][c]);
+      if (s_m[4][c]) atomicMax(&M->obj_len, s_m[4][c]);
+      if (s_m[5][c]) atomicMax(&M->sci_len, s_m[5][c]);
+      if (s_m[6][c]) atomicOr(&M->fl, s_m[6][c]);
+      if (s_m[7][c]) atomicOr(&M->nan_left, 1u);
+    }
+    if (threadIdx.x == 0 && s_keep) atomicAdd(a.n_keep + ic.d, s_keep);
+    __syncthreads();
+  }
+}
+
+// ---- layout: class, width, decimals of every output column; line width -----------------------
+__global__ void __launch_bounds__(128) csv_layout_kernel(TableArgs a) {
+  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= a.n_docs) return;
+  const TDoc D = a.docs[d];
+  if (!D.active) return;
+  const ChunkMeasure* meas = (const ChunkMeasure*)a.meas;
+  ColOut* col = (ColOut*)a.col;
+  uint32_t off = 0;
+  int flags = 0;
+  for (uint32_t j = 0; j < D.h; ++j) {
+    uint32_t c = D.lead + j;
+    uint32_t e0 = D.stat_base + c;
+    bool nan_left = false;
+    for (uint32_t k = 0; k < D.n_chunks; ++k) nan_left |= meas[e0 + (size_t)k * D.W].nan_left != 0;
+    int cls = fold_column_class(a.ctype + e0, D.n_chunks, D.W, nan_left);
+    if (cls == CC_UNSUP) { flags |= 2; cls = CC_OBJ; }
+    ColumnLayout L = layout_column(cls, meas + e0, a.ctype + e0, D.n_chunks, D.W,
+                                   a.name_cp[D.col_base + j]);
+    ColOut o;
+    o.cls = L.cls; o.dec = L.dec; o.sci = L.sci ? 1 : 0; o.width = L.width; o.cp_off = off;
+    col[D.col_base + j] = o;
+    off += L.width + 1;
+  }
+  a.doc_linew[d] = off ? off - 1 : 0;
+  if (flags) atomicOr(a.doc_flags + d, flags);
+}
+
+// ---- bytes of every output line (indexed by record slot; slot r0 = banner + header line) ------
+__global__ void __launch_bounds__(256) csv_rowbytes_kernel(TableArgs a) {
+  uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot > a.n_slots) return;
+  unsigned long long b = 0;
+  if (slot < a.n_slots) {
+    uint32_t d = ub_search(a.slot_doc_r0, a.n_docs, slot);
+    const TDoc D = a.docs[d];
+    if (D.active && a.doc_flags[d] == 0) {
+      uint32_t L = slot - D.r0;
+      uint32_t keep = a.n_keep[d];
+      if (L == 0) b = D.banner_len + (keep ? a.doc_linew[d] + D.hdr_extra : D.empty_len);
+      else if (L <= D.n_data && keep) {
+        uint32_t chunk = (L - 1) / D.bl;
+        if (row_kept(a, D, slot, chunk)) b = 1ull + a.doc_linew[d] + a.row_extra[slot];
+      }
+    }
+  }
+  a.row_bytes[slot] = b;
+}
+
+__global__ void __launch_bounds__(128) csv_docout_kernel(TableArgs a) {
+  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= a.n_docs) return;
+  unsigned long long o0 = a.row_off[a.slot_doc_r0[d]], o1 = a.row_off[a.slot_doc_r0[d + 1]];
+  a.doc_out_off[d] = o0;
+  a.doc_out_len[d] = o1 - o0;
+}
+
+void csv_table_measure(const TableArgs& a, cudaStream_t s) {
+  if (a.n_docs == 0) return;
+  prof_mark("csv_decide_kernel", s);
+  if (!a.xcells) RFQ_LAUNCH(csv_decide_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
+  prof_mark("csv_measure_kernel", s);
+  if (a.n_items) RFQ_LAUNCH(csv_measure_kernel, table_grid(a.n_items), 256, 0, s, a);
+  prof_mark("csv_layout+rowbytes+scan", s);
+  RFQ_LAUNCH(csv_layout_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
+  RFQ_LAUNCH(csv_rowbytes_kernel, (a.n_slots + 1 + 255) / 256, 256, 0, s, a);
+  exclusive_scan<SumU64>(a.row_bytes, a.row_off, a.n_slots + 1, a.scan_tmp64, nullptr, s);
+  RFQ_LAUNCH(csv_docout_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
+  prof_mark("host+sync", s);
+}
+
+
+}  // namespace rfq

@@ -30,6 +30,28 @@ void txt_pipeline(const TxtArgs& a, cudaStream_t s);   // sizes: fills out_len/o
 void txt_emit(const TxtArgs& a, uint8_t* out, cudaStream_t s);
 
 // ------------------------------------------------------------------------------------------
+// prompt assembly (prompt_kernels.cu)
+struct PromptArgs {
+  const uint8_t* arena;       // device, packed raw_text documents (UTF-8)
+  const uint32_t* doc_off;
+  const uint32_t* doc_len;
+  uint32_t n_docs;
+  const uint8_t* head; uint32_t head_len;   // device copies of the host's template pieces
+  const uint8_t* tail; uint32_t tail_len;
+  const uint8_t* mark; uint32_t mark_len;   // appended when the text was cut
+  uint32_t max_chars;                       // code points kept
+  uint32_t* cut;              // [n_docs] bytes of the document kept
+  uint32_t* trunc;            // [n_docs]
+  int32_t* status;            // [n_docs]
+  unsigned long long* out_len;  // [n_docs]
+  unsigned long long* out_off;  // [n_docs]
+  unsigned long long* out_total;  // [1]
+  unsigned long long* scan_tmp64;
+};
+void prompt_measure(const PromptArgs& a, cudaStream_t s);
+void prompt_emit(const PromptArgs& a, uint8_t* out, cudaStream_t s);
+
+// ------------------------------------------------------------------------------------------
 // CSV / table pipeline
 
 // tokeniser (csv_scan.cu): one attempt = one separator over a set of documents

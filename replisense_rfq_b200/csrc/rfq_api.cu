@@ -225,6 +225,67 @@ int rfq_text_run(rfq_ctx* c) {
   return RFQ_OK;
 }
 
+int rfq_prompt_run(rfq_ctx* c, const uint8_t* head, uint32_t head_len, const uint8_t* tail,
+                   uint32_t tail_len, const uint8_t* mark, uint32_t mark_len, uint32_t max_chars) {
+  if (!c || (head_len && !head) || (tail_len && !tail) || (mark_len && !mark)) return RFQ_ERR_ARG;
+  if (!c->staged) { c->err = "rfq_prompt_run: nothing staged"; return RFQ_ERR_STATE; }
+  RFQ_CK(c, cudaSetDevice(c->device));
+  cudaStream_t s = c->stream;
+  uint32_t n = c->n_docs;
+  c->prof.begin();
+  g_prof = &c->prof;
+  struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
+  RFQ_CK(c, cudaEventRecord(c->ev0, s));
+  c->pool.reset();
+  // template pieces: one small pinned upload
+  const size_t o_tail = ((size_t)head_len + 15) & ~(size_t)15, o_mark = (o_tail + tail_len + 15) & ~(size_t)15;
+  const size_t pieces = o_mark + mark_len + 16;
+  RFQ_CK(c, c->h_up.reserve(pieces));
+  uint8_t* hp = (uint8_t*)c->h_up.p;
+  if (head_len) memcpy(hp, head, head_len);
+  if (tail_len) memcpy(hp + o_tail, tail, tail_len);
+  if (mark_len) memcpy(hp + o_mark, mark, mark_len);
+  uint8_t* d_pieces = c->pool.alloc<uint8_t>(pieces);
+  PromptArgs a{};
+  a.arena = (const uint8_t*)c->d_arena.p;
+  a.doc_off = c->d_doc_off; a.doc_len = c->d_doc_len; a.n_docs = n;
+  a.head = d_pieces; a.head_len = head_len;
+  a.tail = d_pieces + o_tail; a.tail_len = tail_len;
+  a.mark = d_pieces + o_mark; a.mark_len = mark_len;
+  a.max_chars = max_chars;
+  a.cut = c->pool.alloc<uint32_t>(n + 1);
+  a.trunc = c->pool.alloc<uint32_t>(n + 1);
+  a.status = c->pool.alloc<int32_t>(n + 1);
+  a.out_len = c->pool.alloc<unsigned long long>(n + 1);
+  a.out_off = c->pool.alloc<unsigned long long>(n + 1);
+  a.out_total = c->pool.alloc<unsigned long long>(1);
+  a.scan_tmp64 = c->pool.alloc<unsigned long long>(scan_partials_needed(n));
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  RFQ_CK(c, cudaMemcpyAsync(d_pieces, hp, pieces, cudaMemcpyHostToDevice, s));
+  prompt_measure(a, s);
+  unsigned long long total = 0;
+  if (n) {
+    RFQ_CK(c, cudaMemcpyAsync(c->h_scalar(), a.out_total, 8, cudaMemcpyDeviceToHost, s));
+    RFQ_CK(c, cudaStreamSynchronize(s));
+    total = *c->h_scalar();
+  }
+  uint8_t* d_text = c->pool.alloc<uint8_t>(total + 16);
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  prompt_emit(a, d_text, s);
+  c->segs.clear();
+  c->segs.push_back({d_text, total, 0});
+  c->host_tables = false;
+  prof_mark("end", s);
+  RFQ_CK(c, cudaEventRecord(c->ev1, s));
+  RFQ_CK(c, cudaGetLastError());
+  c->out_total = total;
+  c->d_out_off = a.out_off; c->d_out_len = a.out_len;
+  c->d_status = a.status; c->d_rows = nullptr; c->d_cols = nullptr; c->d_attempt = nullptr;
+  c->have_output = true;
+  c->timed = true;
+  return RFQ_OK;
+}
+
 int rfq_fetch(rfq_ctx* c) {
   if (!c) return RFQ_ERR_ARG;
   if (!c->have_output) { c->err = "rfq_fetch: no run to fetch"; return RFQ_ERR_STATE; }
@@ -296,6 +357,17 @@ int rfq_text_parse(rfq_ctx* c, const uint8_t* arena, const uint64_t* offsets,
   int r = rfq_stage(c, arena, offsets, lengths, n);
   if (r) return r;
   r = rfq_text_run(c);
+  if (r) return r;
+  return rfq_fetch(c);
+}
+
+int rfq_prompt_build(rfq_ctx* c, const uint8_t* arena, const uint64_t* offsets,
+                     const uint64_t* lengths, uint32_t n, const uint8_t* head, uint32_t head_len,
+                     const uint8_t* tail, uint32_t tail_len, const uint8_t* mark, uint32_t mark_len,
+                     uint32_t max_chars) {
+  int r = rfq_stage(c, arena, offsets, lengths, n);
+  if (r) return r;
+  r = rfq_prompt_run(c, head, head_len, tail, tail_len, mark, mark_len, max_chars);
   if (r) return r;
   return rfq_fetch(c);
 }

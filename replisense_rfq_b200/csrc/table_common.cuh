@@ -1,0 +1,96 @@
+// Shared by the three table sweeps (csv_classify.cu, csv_measure.cu, csv_emit.cu): work items,
+// per-row cursors and cell fetch for the CSV and sheet paths.
+#pragma once
+#include <cuda_runtime.h>
+#include "cell_ops.cuh"
+#include "launch.h"
+#include "pipeline.h"
+#include "scan.cuh"
+#include "xlsx_fetch.cuh"
+
+namespace rfq {
+
+#define RFQ_MAX_W 1024
+
+__device__ __forceinline__ uint32_t ub_search(const uint32_t* __restrict__ base, uint32_t n,
+                                              uint32_t x) {
+  // largest i in [0, n) with base[i] <= x
+  uint32_t lo = 0, hi = n;
+  while (hi - lo > 1) {
+    uint32_t mid = (lo + hi) >> 1;
+    if (__ldg(base + mid) <= x) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+__device__ __forceinline__ CellSrc fetch_cell(const TableArgs& a, const TDoc& D, uint32_t slot,
+                                              uint32_t c) {
+  if (a.xcells) return xfetch(a, D, slot - D.r0 + 1, c);  // sheet mode: slot r0+1+row <-> sheet row row+2
+  CellSrc s;
+  s.mode = 0; s.missing = false; s.clean = false; s.p = a.arena; s.n = 0; s.bits = 0;
+  uint32_t fbeg = __ldg(a.rec_fend + slot - 1);
+  uint32_t nf = __ldg(a.rec_fend + slot) - fbeg;
+  if (c >= nf) { s.missing = true; return s; }
+  uint32_t st = c == 0 ? __ldg(a.rec_start + slot) : __ldg(a.fend + fbeg + c - 1) + 1;
+  uint32_t en = __ldg(a.fend + fbeg + c);
+  s.p = a.arena + D.off + st;
+  s.n = en - st;
+  csv_simplify(s);
+  return s;
+}
+
+// per-row state hoisted out of the column loop (a thread walks the cells of ONE row)
+struct RowCur { uint32_t slot, fbeg, nf, start0; };
+__device__ __forceinline__ RowCur row_open(const TableArgs& a, uint32_t slot) {
+  RowCur r; r.slot = slot; r.fbeg = 0; r.nf = 0; r.start0 = 0;
+  if (!a.xcells) {
+    r.fbeg = __ldg(a.rec_fend + slot - 1);
+    r.nf = __ldg(a.rec_fend + slot) - r.fbeg;
+    r.start0 = __ldg(a.rec_start + slot);
+  }
+  return r;
+}
+__device__ __forceinline__ CellSrc row_cell(const TableArgs& a, const TDoc& D, const RowCur& r, uint32_t c) {
+  if (a.xcells) return xfetch(a, D, r.slot - D.r0 + 1, c);
+  CellSrc s;
+  s.mode = 0; s.missing = false; s.clean = false; s.p = a.arena; s.n = 0; s.bits = 0;
+  if (c >= r.nf) { s.missing = true; return s; }
+  uint32_t st = c == 0 ? r.start0 : __ldg(a.fend + r.fbeg + c - 1) + 1;
+  uint32_t en = __ldg(a.fend + r.fbeg + c);
+  s.p = a.arena + D.off + st;
+  s.n = en - st;
+  csv_simplify(s);
+  return s;
+}
+
+struct ItemCtx {
+  uint32_t d, row0, nrows, chunk;
+};
+__device__ __forceinline__ ItemCtx item_ctx(const TableArgs& a, uint32_t item, uint32_t* s_doc) {
+  if (threadIdx.x == 0) *s_doc = ub_search(a.item_doc_base, a.n_docs, item);
+  __syncthreads();
+  ItemCtx c;
+  c.d = *s_doc;
+  const TDoc& D = a.docs[c.d];
+  c.row0 = (item - D.item_base) * D.rb;
+  c.nrows = min(D.rb, D.n_data - c.row0);
+  c.chunk = c.row0 / D.bl;
+  return c;
+}
+
+__device__ __forceinline__ bool row_kept(const TableArgs& a, const TDoc& D, uint32_t slot,
+                                         uint32_t chunk) {
+  return !(__ldg(a.row_na + slot) == D.h && !a.chunk_nf[D.stat_base + chunk * D.W]);
+}
+
+
+// 8 resident CTAs of 256 threads per SM
+static inline int table_grid(uint32_t n_items) {
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  uint32_t g = (uint32_t)sms * 8u;
+  return (int)(n_items < g ? n_items : g);
+}
+
+}  // namespace rfq

@@ -148,6 +148,17 @@ class Engine:
             r = BatchResult(self)
             return [r.doc_str(d) for d in range(r.n)]
 
+    # -- prompt assembly (the step after the parser: app/rfq_agent.py:138-151)
+    def prompt_batch(self, docs: Sequence[bytes], head: bytes, tail: bytes, mark: bytes,
+                     max_chars: int = 8000) -> BatchResult:
+        """docs: raw_text documents (UTF-8).  status RFQ_DOC_EMPTY_TEXT where the text is blank."""
+        with self.lock:
+            a, off, ln = self._pack(docs)
+            self._check(self.lib.rfq_prompt_build(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data,
+                                                  len(docs), head, len(head), tail, len(tail), mark,
+                                                  len(mark), max_chars), "rfq_prompt_build")
+            return BatchResult(self)
+
     # -- csv
     def csv_batch(self, docs: Sequence[bytes], max_rows=1000) -> BatchResult:
         n = len(docs)
