@@ -44,6 +44,8 @@ extern "C" {
 /* prompt path: raw_text is empty or whitespace only → the reference answers "Empty or invalid
  * input text" without building a prompt (app/rfq_agent.py:138-140) */
 #define RFQ_DOC_EMPTY_TEXT 4
+/* numeric path: Python's int() / float() raises ValueError for this field */
+#define RFQ_DOC_VALUE_ERROR 5
 
 typedef struct rfq_ctx rfq_ctx;
 
@@ -92,6 +94,19 @@ int rfq_sheets_parse(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets
                      const uint64_t* lengths, uint32_t n_docs, const uint8_t* kind,
                      const int32_t* sst_of, const int64_t* max_rows, const uint32_t* date_off,
                      const uint32_t* date_ids);
+
+/* ---- batched file hash: FileParser._get_file_hash_async (app/file_parser.py:122-130) for every
+ * staged document at once — MD5 of the document bytes as 32 lowercase hex characters (the
+ * envelope's `file_hash`).  One thread per document (MD5 is sequential inside a document): meant
+ * for batches of many small files. */
+int rfq_md5_run(rfq_ctx* ctx);
+
+/* ---- quantity / price validators: LineItem.parse_quantity / parse_target_price
+ * (app/rfq_agent.py:27-39) over a batch of field strings: kind[d] 0 → int(v.replace(",", "")),
+ * 1 → float(v.replace(",", "")).  Output: 8 bytes per field (int64, or the bits of the double;
+ * rfq_out_text at 8*d) and rfq_out_status: RFQ_DOC_OK, RFQ_DOC_VALUE_ERROR (Python raises
+ * ValueError), RFQ_DOC_UNSUPPORTED (non-ASCII field, integer beyond int64, > 160 characters). */
+int rfq_numeric_run(rfq_ctx* ctx, const uint8_t* kind);
 
 /* ---- prompt assembly (the step right after the parser): the text handling of
  * RFQFieldGenerator._generate_sync (app/rfq_agent.py:138-151).  The staged batch holds raw_text

@@ -28,18 +28,21 @@ namespace rfq {
 // Python-int columns, the shift recomputation of split rows — goes through the general
 // formatters out of line.  Inlining all of it made cicc spend 8 minutes on this kernel and bought
 // nothing at run time.
-__device__ __noinline__ uint32_t print_cell_cold(const CellSrc& s, int ct, int kind, int dec, uint8_t* out) {
+__device__ __noinline__ uint32_t print_cell_cold(CellSrc s, int ct, int kind, int dec, uint8_t* out) {
   return print_cell(s, ct, kind, dec, out);
 }
-__device__ __noinline__ void printed_size_cold(const CellSrc& s, int ct, int kind, int dec,
-                                               uint32_t* ncp, uint32_t* nbytes) {
-  printed_size(s, ct, kind, dec, ncp, nbytes);
+struct SizeRes { uint32_t ncp, nbytes; };
+__device__ __noinline__ SizeRes printed_size_cold(CellSrc s, int ct, int kind, int dec) {
+  SizeRes r;
+  printed_size(s, ct, kind, dec, &r.ncp, &r.nbytes);
+  return r;
 }
 __device__ __forceinline__ void put_nat(int kind, uint32_t width, uint8_t* field) {
   if (kind == PR_DATE64) { field[width - 3] = 'N'; field[width - 2] = 'a'; field[width - 1] = 'T'; }
 }
 // any cell, any kind; returns printed bytes - printed code points
-__device__ __noinline__ uint32_t emit_cell_cold(const CellSrc& src, int ct, int kind, int dec,
+// (arguments by value: a reference would pin the caller's copy to local memory)
+__device__ __noinline__ uint32_t emit_cell_cold(CellSrc src, int ct, int kind, int dec,
                                                 uint32_t width, uint8_t* field, bool fill) {
   TextInfo t = cell_text(src);
   if (cell_is_nan(src, t, ct)) {
@@ -167,12 +170,11 @@ __device__ __forceinline__ uint32_t emit_cell(const CellSrc& src, int ct, int ki
   uint8_t buf[40];
   int n = (kind == PR_STR) ? -1 : format_number(src, ct, kind, dec, nbytes, first8, buf);
   if (n < 0) {  // rare: huge value in fixed notation, Python int, typed value printed as text
-    uint32_t ncp, nb;
-    printed_size_cold(src, ct, kind, dec, &ncp, &nb);
-    uint32_t pad = width - ncp;
+    SizeRes sz = printed_size_cold(src, ct, kind, dec);
+    uint32_t pad = width - sz.ncp;
     if (fill) for (uint32_t q = 0; q < pad; ++q) field[q] = ' ';
     print_cell_cold(src, ct, kind, dec, field + pad);
-    return nb - ncp;
+    return sz.nbytes - sz.ncp;
   }
   uint32_t pad = width - (uint32_t)n;
   if (fill) for (uint32_t q = 0; q < pad; ++q) field[q] = ' ';
@@ -182,8 +184,9 @@ __device__ __forceinline__ uint32_t emit_cell(const CellSrc& src, int ct, int ki
 
 // bytes - code points of the text cells left of column c in this row (rows with non-ASCII text
 // whose columns are split over thread groups)
-__device__ __noinline__ uint32_t row_shift_before(const TableArgs& a, const TDoc& D, const RowCur& rc,
+__device__ __noinline__ uint32_t row_shift_before(TableArgs a, uint32_t d, RowCur rc,
                                                   const uint8_t* ctrow, const ColOut* col, uint32_t c) {
+  const TDoc D = a.docs[d];
   uint32_t xb = 0;
   for (uint32_t c2 = D.lead; c2 < c; ++c2) {
     ColOut c2o = col[D.col_base + c2 - D.lead];
@@ -241,7 +244,7 @@ __global__ void __launch_bounds__(256) csv_emit_kernel(TableArgs a, uint8_t* __r
           if (ct == CT_XOBJ) ct = cell_own_ctype(src);
           int kind = print_kind(co.cls, ct, co.sci != 0);
           if (ngrp > 1 && j && extra)   // columns are split over groups: recompute the shift
-            xb = row_shift_before(a, D, rc, ctrow, col, c);
+            xb = row_shift_before(a, ic.d, rc, ctrow, col, c);
           uint8_t* p = rowp;
           if (j == 0) { *p = '\n'; p += 1; }
           else { p += co.cp_off + xb; if (!staged) *p = ' '; p += 1; }

@@ -30,6 +30,17 @@ void txt_pipeline(const TxtArgs& a, cudaStream_t s);   // sizes: fills out_len/o
 void txt_emit(const TxtArgs& a, uint8_t* out, cudaStream_t s);
 
 // ------------------------------------------------------------------------------------------
+// batched MD5 (md5_kernels.cu): 32 lowercase hex characters per document at out + 32 * d
+void md5_batch(const uint8_t* arena, const uint32_t* doc_off, const uint32_t* doc_len, uint32_t n_docs,
+               uint8_t* out, unsigned long long* out_off, unsigned long long* out_len, cudaStream_t s);
+
+// ------------------------------------------------------------------------------------------
+// quantity / price validators (numeric_kernels.cu): value[d] = int64 or double bits
+void numeric_batch(const uint8_t* arena, const uint32_t* doc_off, const uint32_t* doc_len,
+                   const uint8_t* kind, uint32_t n_docs, unsigned long long* value, int32_t* status,
+                   unsigned long long* out_off, unsigned long long* out_len, cudaStream_t s);
+
+// ------------------------------------------------------------------------------------------
 // prompt assembly (prompt_kernels.cu)
 struct PromptArgs {
   const uint8_t* arena;       // device, packed raw_text documents (UTF-8)

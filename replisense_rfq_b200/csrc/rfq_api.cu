@@ -225,6 +225,72 @@ int rfq_text_run(rfq_ctx* c) {
   return RFQ_OK;
 }
 
+int rfq_md5_run(rfq_ctx* c) {
+  if (!c) return RFQ_ERR_ARG;
+  if (!c->staged) { c->err = "rfq_md5_run: nothing staged"; return RFQ_ERR_STATE; }
+  RFQ_CK(c, cudaSetDevice(c->device));
+  cudaStream_t s = c->stream;
+  uint32_t n = c->n_docs;
+  c->prof.begin();
+  g_prof = &c->prof;
+  struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
+  RFQ_CK(c, cudaEventRecord(c->ev0, s));
+  c->pool.reset();
+  unsigned long long* out_off = c->pool.alloc<unsigned long long>(n + 1);
+  unsigned long long* out_len = c->pool.alloc<unsigned long long>(n + 1);
+  uint8_t* d_text = c->pool.alloc<uint8_t>(32ull * n + 16);
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  md5_batch((const uint8_t*)c->d_arena.p, c->d_doc_off, c->d_doc_len, n, d_text, out_off, out_len, s);
+  c->segs.clear();
+  c->segs.push_back({d_text, 32ull * n, 0});
+  c->host_tables = false;
+  prof_mark("end", s);
+  RFQ_CK(c, cudaEventRecord(c->ev1, s));
+  RFQ_CK(c, cudaGetLastError());
+  c->out_total = 32ull * n;
+  c->d_out_off = out_off; c->d_out_len = out_len;
+  c->d_status = nullptr; c->d_rows = nullptr; c->d_cols = nullptr; c->d_attempt = nullptr;
+  c->have_output = true;
+  c->timed = true;
+  return RFQ_OK;
+}
+
+int rfq_numeric_run(rfq_ctx* c, const uint8_t* kind) {
+  if (!c || (c->n_docs && !kind)) return RFQ_ERR_ARG;
+  if (!c->staged) { c->err = "rfq_numeric_run: nothing staged"; return RFQ_ERR_STATE; }
+  RFQ_CK(c, cudaSetDevice(c->device));
+  cudaStream_t s = c->stream;
+  uint32_t n = c->n_docs;
+  c->prof.begin();
+  g_prof = &c->prof;
+  struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
+  RFQ_CK(c, cudaEventRecord(c->ev0, s));
+  c->pool.reset();
+  RFQ_CK(c, c->h_up.reserve(n + 16));
+  if (n) memcpy(c->h_up.p, kind, n);
+  uint8_t* d_kind = c->pool.alloc<uint8_t>(n + 16);
+  unsigned long long* out_off = c->pool.alloc<unsigned long long>(n + 1);
+  unsigned long long* out_len = c->pool.alloc<unsigned long long>(n + 1);
+  unsigned long long* d_val = c->pool.alloc<unsigned long long>(n + 2);
+  int32_t* d_status = c->pool.alloc<int32_t>(n + 1);
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  if (n) RFQ_CK(c, cudaMemcpyAsync(d_kind, c->h_up.p, n, cudaMemcpyHostToDevice, s));
+  numeric_batch((const uint8_t*)c->d_arena.p, c->d_doc_off, c->d_doc_len, d_kind, n, d_val, d_status,
+                out_off, out_len, s);
+  c->segs.clear();
+  c->segs.push_back({(uint8_t*)d_val, 8ull * n, 0});
+  c->host_tables = false;
+  prof_mark("end", s);
+  RFQ_CK(c, cudaEventRecord(c->ev1, s));
+  RFQ_CK(c, cudaGetLastError());
+  c->out_total = 8ull * n;
+  c->d_out_off = out_off; c->d_out_len = out_len;
+  c->d_status = d_status; c->d_rows = nullptr; c->d_cols = nullptr; c->d_attempt = nullptr;
+  c->have_output = true;
+  c->timed = true;
+  return RFQ_OK;
+}
+
 int rfq_prompt_run(rfq_ctx* c, const uint8_t* head, uint32_t head_len, const uint8_t* tail,
                    uint32_t tail_len, const uint8_t* mark, uint32_t mark_len, uint32_t max_chars) {
   if (!c || (head_len && !head) || (tail_len && !tail) || (mark_len && !mark)) return RFQ_ERR_ARG;

@@ -148,6 +148,33 @@ class Engine:
             r = BatchResult(self)
             return [r.doc_str(d) for d in range(r.n)]
 
+    # -- file hashes (app/file_parser.py:122-130), one batch
+    def md5_many(self, docs: Sequence[bytes]) -> "list[str]":
+        with self.lock:
+            a, off, ln = self._pack(docs)
+            self._check(self.lib.rfq_stage(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data, len(docs)),
+                        "rfq_stage")
+            self._check(self.lib.rfq_md5_run(self.ctx), "rfq_md5_run")
+            self._check(self.lib.rfq_fetch(self.ctx), "rfq_fetch")
+            r = BatchResult(self)
+            return [r.doc_str(d) for d in range(r.n)]
+
+    # -- quantity / price validators (app/rfq_agent.py:27-39)
+    def numeric_batch(self, fields: Sequence[bytes], kinds) -> "tuple[np.ndarray, np.ndarray]":
+        """kinds[i]: 0 = int(v.replace(',', '')), 1 = float(v.replace(',', '')).  Returns (raw 8-byte
+        values as uint64, status)."""
+        kinds = np.ascontiguousarray(kinds, dtype=np.uint8)
+        with self.lock:
+            a, off, ln = self._pack(fields)
+            self._check(self.lib.rfq_stage(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data, len(fields)),
+                        "rfq_stage")
+            self._check(self.lib.rfq_numeric_run(self.ctx, kinds.ctypes.data), "rfq_numeric_run")
+            self._check(self.lib.rfq_fetch(self.ctx), "rfq_fetch")
+            r = BatchResult(self)
+            raw = (np.frombuffer(C.string_at(r.text_ptr, 8 * r.n), dtype=np.uint64).copy() if r.n
+                   else np.zeros(0, np.uint64))
+            return raw, np.asarray(r.status).copy()
+
     # -- prompt assembly (the step after the parser: app/rfq_agent.py:138-151)
     def prompt_batch(self, docs: Sequence[bytes], head: bytes, tail: bytes, mark: bytes,
                      max_chars: int = 8000) -> BatchResult:

@@ -185,6 +185,41 @@ class FileParser:
                 out[i] = r
         return out
 
+    _GPU_HASH_MAX = 1 << 20   # MD5 is sequential per document: bigger files keep hashlib
+
+    def parse_many_envelopes(self, docs: Sequence[bytes], names: Sequence[str]) -> "list[Any]":
+        """parse_file_async's result dict (app/file_parser.py:80-86) for many in-memory files:
+        raw_text from the batched parsers, file_hash from the batched MD5 kernel.  `names[i]` is the
+        file name (its suffix selects the parser).  Entries are dicts, or the exception
+        parse_file_async would have raised: un-wrapped size / type errors (:109,113), wrapped
+        FileParsingError(f"Failed to parse {name}: ...") for everything from the dispatch (:95)."""
+        n = len(docs)
+        out: "list[Any]" = [None] * n
+        kinds = [Path(nm).suffix.lower() for nm in names]
+        ok = []
+        for i, (b, k) in enumerate(zip(docs, kinds)):
+            if len(b) > self.max_file_size:
+                out[i] = FileParsingError(f"File too large: {len(b) / 1024 / 1024:.1f}MB "
+                                          f"(max: {self.max_file_size / 1024 / 1024}MB)")
+            elif k not in self.supported_extensions:
+                out[i] = FileParsingError(f"Unsupported file type: {k}")
+            else:
+                ok.append(i)
+        small = [i for i in ok if len(docs[i]) <= self._GPU_HASH_MAX]
+        hashes = dict(zip(small, self.engine.md5_many([docs[i] for i in small]))) if small else {}
+        for i in ok:
+            if i not in hashes:
+                hashes[i] = hashlib.md5(docs[i]).hexdigest()
+        texts = self.parse_many([docs[i] for i in ok], [kinds[i] for i in ok])
+        for i, t in zip(ok, texts):
+            name = Path(names[i]).name
+            if isinstance(t, Exception):
+                out[i] = FileParsingError(f"Failed to parse {name}: {t}")
+            else:
+                out[i] = {"raw_text": t, "source_file": name, "file_size": len(docs[i]),
+                          "file_hash": hashes[i], "parsing_method": f"async_{kinds[i][1:]}"}
+        return out
+
     def __del__(self):
         if hasattr(self, "thread_pool"):
             self.thread_pool.shutdown(wait=False)
