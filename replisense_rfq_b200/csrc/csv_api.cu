@@ -127,6 +127,7 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
     TDoc& T = td[i];
     memset(&T, 0, sizeof(T));
     T.off = a_off[i]; T.len = a_len[i]; T.r0 = sh.r0; T.f0 = sh.f0;
+    T.stat_base = (uint32_t)n_stat;   // non-decreasing over ALL documents: csv_decide_kernel searches it
     slot_r0[i] = sh.r0;
     item_base[i] = (uint32_t)n_items;
     uint32_t nrows = a_mr[i];

@@ -15,27 +15,27 @@
 
 namespace rfq {
 
-// ---- decide chunk types (one thread per document; entries are few) ----------------------------
+// ---- decide chunk types: one thread per (document, chunk, column) entry ------------------------
+// (chunk_nf is zeroed by the host before the run)
 __global__ void __launch_bounds__(128) csv_decide_kernel(TableArgs a) {
-  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
-  if (d >= a.n_docs) return;
-  const TDoc D = a.docs[d];
-  if (!D.active) return;
-  const ChunkStat* stat = (const ChunkStat*)a.stat;
-  int flags = 0;
-  for (uint32_t k = 0; k < D.n_chunks; ++k) {
-    bool nf = false;
-    for (uint32_t c = 0; c < D.W; ++c) {
-      uint32_t e = D.stat_base + k * D.W + c;
-      ChunkStat S = stat[e];
-      if (S.flags & SF_BAD_UTF8) flags |= 1;
-      int t = decide_chunk_type(S);
-      a.ctype[e] = (uint8_t)t;
-      if (t == CT_STRNF && c >= D.lead) nf = true;
-    }
-    a.chunk_nf[D.stat_base + k * D.W] = nf ? 1 : 0;
+  uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= a.n_stat) return;
+  // entries are laid out document by document: largest d with docs[d].stat_base <= e
+  uint32_t lo = 0, hi = a.n_docs;
+  while (hi - lo > 1) {
+    uint32_t mid = (lo + hi) >> 1;
+    if (a.docs[mid].stat_base <= e) lo = mid; else hi = mid;
   }
-  if (flags) atomicOr(a.doc_flags + d, flags);
+  const TDoc D = a.docs[lo];
+  if (!D.active || D.W == 0) return;
+  uint32_t rel = e - D.stat_base;
+  if (rel >= D.n_chunks * D.W) return;
+  uint32_t k = rel / D.W, c = rel - k * D.W;
+  ChunkStat S = ((const ChunkStat*)a.stat)[e];
+  if (S.flags & SF_BAD_UTF8) atomicOr(a.doc_flags + lo, 1);
+  int t = decide_chunk_type(S);
+  a.ctype[e] = (uint8_t)t;
+  if (t == CT_STRNF && c >= D.lead) a.chunk_nf[D.stat_base + k * D.W] = 1;
 }
 
 // ---- sweep 2: measure ---------------------------------------------------------------------------
@@ -155,7 +155,7 @@ __global__ void __launch_bounds__(128) csv_docout_kernel(TableArgs a) {
 void csv_table_measure(const TableArgs& a, cudaStream_t s) {
   if (a.n_docs == 0) return;
   prof_mark("csv_decide_kernel", s);
-  if (!a.xcells) RFQ_LAUNCH(csv_decide_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
+  if (!a.xcells && a.n_stat) RFQ_LAUNCH(csv_decide_kernel, (a.n_stat + 127) / 128, 128, 0, s, a);
   prof_mark("csv_measure_kernel", s);
   if (a.n_items) RFQ_LAUNCH(csv_measure_kernel, table_grid(a.n_items), 256, 0, s, a);
   prof_mark("csv_layout+rowbytes+scan", s);

@@ -18,8 +18,10 @@ namespace rfq {
 
 #define NUM_MAX_LITERAL 160
 
-// str.strip() white space within ASCII
-__device__ __forceinline__ bool py_space(uint32_t c) { return (c >= 0x09 && c <= 0x0D) || (c >= 0x1C && c <= 0x20); }
+// What int() / float() strip from an ASCII str: Py_ISSPACE (\t \n \v \f \r and the blank).  The
+// wider str.isspace() set (\x1c-\x1f, U+0085, ...) only applies to non-ASCII strings, which go
+// through _PyUnicode_TransformDecimalAndSpaceToASCII first — and are declined here.
+__device__ __forceinline__ bool py_space(uint32_t c) { return (c >= 0x09 && c <= 0x0D) || c == 0x20; }
 __device__ __forceinline__ bool dig(uint32_t c) { return c - '0' < 10u; }
 __device__ __forceinline__ uint32_t lower(uint32_t c) { return (c >= 'A' && c <= 'Z') ? c + 32 : c; }
 

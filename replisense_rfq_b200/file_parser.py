@@ -16,7 +16,7 @@ from pathlib import Path
 from typing import Any, Dict, Optional, Sequence
 
 from . import _lib
-from .engine import Engine, EngineError, default_engine
+from .engine import Engine, EngineError, default_pool
 
 logger = logging.getLogger(__name__)
 
@@ -46,9 +46,11 @@ class FileParser:
 
     @property
     def engine(self) -> Engine:
-        if self._engine is None:
-            self._engine = default_engine(self._device)  # raises without a CUDA device
-        return self._engine
+        if self._engine is not None:
+            return self._engine
+        # two streams per device: concurrent requests of the shared parser (app/main.py:47) overlap
+        # one call's copies with the other's kernels.  Raises without a CUDA device.
+        return default_pool(self._device).pick()
 
     # ------------------------------------------------------------------ envelope (:44-99)
     async def parse_file_async(self, file_path: str) -> Dict[str, Any]:
