@@ -112,7 +112,8 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
-        "data": "synthetic", "config": config_dict(args, sample_rows),
+        # same workload / config as our arm; each step is a bounded sample of it (see cpu_baseline.sample)
+        "data": "synthetic", "config": dict(config_dict(args, args.rows), sample_rows_per_process=sample_rows),
         "cells_per_s": sample_rows * 8 * cores * args.steps / dt,
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": f"{cores} processes x one {sample_rows}-row slice of the C2 CSV per step "
