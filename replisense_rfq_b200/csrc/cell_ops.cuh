@@ -400,6 +400,115 @@ RFQ_HD CellMeasure measure_cell(const CellSrc& s, int ctype) {
   return m;
 }
 
+// ---- 1 + 2 in one visit: the SF_* flags of a CSV cell AND what it would measure under every
+// chunk type it can end up in.  The column's type is only known after all its cells were seen, so
+// the candidates are reduced per (chunk, column) side by side and `finish_measure` picks the ones
+// the decided type uses.  Identical, value for value, to classify_cell + measure_cell (the
+// sequential model runs both ways in tests/test_hostcore.py); saves the second
+// tokenise-and-parse sweep.
+struct CellCand {
+  uint32_t flags;       // SF_*
+  int int_status;
+  bool na;              // an NA token (NA filter on)
+  bool has_float;       // float view valid: the cell is an int64 or parses as a double
+  bool need_exact;      // its float view depends on which parser the column ends up using
+  uint32_t str_len, extra;   // as text: printed code points, bytes - code points
+  uint32_t int_len, uint_len, bool_len;   // as int64 / uint64 / bool (0 = not such a token)
+  uint32_t ip_len, tz, inf_len, obj_len, sci_len, fl;   // as float64 (ChunkMeasure semantics)
+};
+
+RFQ_HD void cand_float_view(double v, CellCand* m) {
+  Fixed6 f = fixed6(v);
+  double a = v < 0 ? -v : v;
+  m->has_float = true;
+  if (f.inf) {
+    m->inf_len = 3 + f.neg; m->obj_len = 4; m->sci_len = m->inf_len; m->fl = MF_LARGE;
+  } else {
+    m->ip_len = f.neg + f.ip_digits; m->tz = f.tz; m->obj_len = objfloat_len(f);
+    m->fl = MF_FINITE | (a > 1e6 ? MF_LARGE : 0) | ((a < 1e-6 && a > 0.) ? MF_SMALL : 0);
+    m->sci_len = (uint32_t)sci_len_of(v);
+  }
+}
+
+RFQ_HD CellCand classify_measure_cell(const CellSrc& s) {
+  CellCand m;
+  m.flags = 0; m.int_status = INT_OK; m.na = false; m.has_float = false; m.need_exact = false;
+  m.str_len = 0; m.extra = 0; m.int_len = 0; m.uint_len = 0; m.bool_len = 0;
+  m.ip_len = 0; m.tz = 6; m.inf_len = 0; m.obj_len = 0; m.sci_len = 0; m.fl = 0;
+  TextInfo t = cell_text(s);
+  if (is_na_token(t.nbytes, t.first8)) { m.flags = SF_ANY_NA; m.na = true; return m; }
+  uint32_t f = SF_ANY_NONNA;
+  if (!t.utf8_ok) f |= SF_BAD_UTF8;
+  m.str_len = t.ncp + t.nesc;
+  m.extra = t.nbytes - t.ncp;
+  const int bt = bool_token(t.nbytes, t.first8);
+  if (bt >= 0) m.bool_len = bt == 1 ? 4u : 5u;
+  const uint32_t c0 = (uint32_t)(t.first8 & 0xFFu);
+  if (!(is_digit_ascii((int)c0) || c0 == '+' || c0 == '-' || c0 == '.' || is_space_ascii((int)c0) ||
+        (c0 | 0x20u) == 'i')) {          // a plain word (see classify_cell)
+    m.int_status = INT_INVALID;
+    f |= SF_UINT_INVALID | SF_FLOAT_BAD | SF_PYINT_BAD;
+    if (bt < 0) f |= SF_BOOL_BAD;
+    m.flags = f;
+    return m;
+  }
+  int64_t iv;
+  int st = cell_int64(s, &iv);
+  m.int_status = st;
+  if (st == INT_OK) {
+    if (iv < 0) f |= SF_NEG;
+    else if (iv == 0) {   // "-0": int 0, but -0.0 for xstrtod
+      UintTok u; cell_uint64(s, &u);
+      if (u.neg) { f |= SF_NEG; m.need_exact = true; }
+    }
+    f |= SF_BOOL_BAD;
+    m.flags = f;
+    m.int_len = (uint32_t)int64_len(iv);
+    if (iv >= 0) m.uint_len = m.int_len;     // a uint64 column prints its small members the same way
+    uint64_t mag = iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv;
+    if (mag > (1ull << 53)) {
+      m.need_exact = true;   // xstrtod(token) may differ from (double)int64
+#ifdef __CUDA_ARCH__
+      cand_float_view(__ll2double_rn(iv), &m);
+#else
+      cand_float_view((double)iv, &m);
+#endif
+      return m;
+    }
+    // an exactly representable integer seen as float64: "%.6f" is its digits + ".000000", the
+    // exponent of "%.6e" has two digits (what fixed6 / sci_len_of compute, without the 128-bit math)
+    m.has_float = true;
+    m.ip_len = m.int_len; m.tz = 6; m.obj_len = m.int_len - (iv < 0 ? 1u : 0u) + 3u;
+    m.sci_len = 12u + (iv < 0 ? 1u : 0u);
+    m.fl = MF_FINITE | (mag > 1000000ull ? MF_LARGE : 0);
+    return m;
+  }
+  UintTok u;
+  int us;
+  if (st == INT_INVALID && (is_digit_ascii((int)c0) || c0 == '+' || c0 == '.')) {
+    us = INT_INVALID; u.v = 0; u.neg = false; u.gt_i64 = false;
+  } else {
+    us = cell_uint64(s, &u);
+  }
+  if (us == INT_INVALID) f |= SF_UINT_INVALID;
+  else if (us == INT_OVERFLOW) f |= SF_UINT_OVF;
+  else {
+    if (u.neg) f |= SF_NEG;
+    if (u.gt_i64) f |= SF_GT_I64;
+    if (!u.neg) m.uint_len = (uint32_t)ndigits_u64(u.v);
+  }
+  double dv;
+  if (!cell_double(s, &dv)) f |= SF_FLOAT_BAD;
+  else cand_float_view(dv, &m);
+  if (bt < 0) f |= SF_BOOL_BAD;
+  if (!(us == INT_OK && !u.neg)) {
+    int pp = pyint_prefix(t.first8, t.nbytes);
+    if (pp == 0 || (pp == 2 && !parse_pyint_any(s.p, s.n, s.mode).ok)) f |= SF_PYINT_BAD;
+  }
+  m.flags = f;
+  return m;
+}
+
 // ---- 3. print -----------------------------------------------------------------------------------
 // How a cell prints given the class of its column and the type of its chunk.
 enum { PR_EMPTY = 0, PR_INT, PR_UINT, PR_FIXED, PR_SCI, PR_OBJFLOAT, PR_BOOL, PR_STR, PR_PYINT,

@@ -134,6 +134,42 @@ struct ChunkMeasure {
 };
 enum { MF_LARGE = 1, MF_SMALL = 2, MF_FINITE = 4, MF_DT_TIME = 8, MF_DT_MS = 16 };  // MF_DT_*: datetime cells
 
+// ---- one-sweep mode (cell_ops.cuh classify_measure_cell) ---------------------------------------
+// candidates of one (chunk, column), reduced over its cells
+struct ChunkCand {
+  uint32_t str_len, int_len, uint_len, bool_len;
+  uint32_t ip_len, min_tz, inf_len, obj_len, sci_len, fl;
+  uint32_t na_count;     // NA cells (all rows)
+  uint32_t need_exact;   // some cell's float view needs the exact sweep
+};
+
+// the ChunkMeasure the second sweep would have produced for a chunk of type `ctype`;
+// returns false when that type is not covered by the candidates (exact sweep needed)
+RFQ_HD bool finish_measure(const ChunkCand& c, int ctype, uint32_t dropped_rows, ChunkMeasure* out) {
+  ChunkMeasure m;
+  m.plain_len = 0; m.ip_len = 0; m.min_tz = 6; m.inf_len = 0; m.obj_len = 0; m.sci_len = 0; m.fl = 0;
+  m.nan_left = c.na_count > dropped_rows ? 1u : 0u;   // a dropped row is NA in every column
+  bool ok = true;
+  switch (ctype) {
+    case CT_STR: m.plain_len = c.str_len; break;
+    case CT_BOOL: case CT_BOOLNA: m.plain_len = c.bool_len; break;
+    case CT_UINT: m.plain_len = c.uint_len; break;
+    case CT_INT: case CT_INTNA:
+      m.plain_len = c.int_len;
+      m.ip_len = c.ip_len; m.min_tz = c.min_tz; m.inf_len = c.inf_len; m.obj_len = c.obj_len;
+      m.sci_len = c.sci_len; m.fl = c.fl;
+      break;
+    case CT_FLOAT:
+      if (c.need_exact) ok = false;
+      m.ip_len = c.ip_len; m.min_tz = c.min_tz; m.inf_len = c.inf_len; m.obj_len = c.obj_len;
+      m.sci_len = c.sci_len; m.fl = c.fl;
+      break;
+    default: ok = false; break;       // CT_STRNF (NA words print), CT_PYINT, CT_UNSUP
+  }
+  *out = m;
+  return ok;
+}
+
 struct ColumnLayout {
   int cls;
   int dec;        // decimals for CC_FLOAT fixed

@@ -3,6 +3,7 @@
 // O(documents + columns) bookkeeping (header names, table shapes, buffer carving); every pass
 // over document bytes or cells is a kernel.
 #include <cuda_runtime.h>
+#include <stdlib.h>
 #include <string.h>
 #include <algorithm>
 #include <string>
@@ -204,6 +205,17 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
   ta.scan_tmp64 = c->pool.alloc<unsigned long long>(scan_partials_needed((uint64_t)n_slots + 1));
   ta.doc_out_off = c->pool.alloc<unsigned long long>(m + 1);
   ta.doc_out_len = c->pool.alloc<unsigned long long>(m + 1);
+  // one sweep for typing AND measuring (cell_ops.cuh classify_measure_cell); RFQ_TWO_SWEEP=1 keeps
+  // the separate exact measure sweep for every document (debugging / cross-checking)
+  static const bool two_sweep = getenv("RFQ_TWO_SWEEP") && atoi(getenv("RFQ_TWO_SWEEP")) != 0;
+  if (!two_sweep) {
+    ta.cand = c->pool.alloc<ChunkCand>(n_stat + 1);
+    ta.chunk_dropped = c->pool.alloc<uint32_t>(n_stat + 1);
+    ta.doc_exact = c->pool.alloc<uint32_t>(m + 2);
+    uint32_t mw = 1;
+    for (uint32_t i = 0; i < m; ++i) mw = std::max(mw, td[i].W);
+    ta.max_w = mw;
+  }
   if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
   RFQ_CK(c, cudaMemcpyAsync(d_up2, c->h_up.p, up2.used, cudaMemcpyHostToDevice, s));
   ta.docs = (const TDoc*)(d_up2 + o_td);
@@ -216,6 +228,10 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
   RFQ_CK(c, cudaMemsetAsync(ta.row_na, 0, 4ull * (n_slots + 1), s));
   RFQ_CK(c, cudaMemsetAsync(ta.row_extra, 0, 4ull * (n_slots + 1), s));
   RFQ_CK(c, cudaMemsetAsync(ta.chunk_nf, 0, n_stat + 1, s));
+  if (ta.cand) {
+    RFQ_CK(c, cudaMemsetAsync(ta.chunk_dropped, 0, 4ull * (n_stat + 1), s));
+    RFQ_CK(c, cudaMemsetAsync(ta.doc_exact, 0, 4ull * (m + 2), s));
+  }
   RFQ_CK(c, cudaMemsetAsync(ta.n_keep, 0, 4ull * (m + 1), s));
   RFQ_CK(c, cudaMemsetAsync(ta.doc_flags, 0, 4ull * (m + 1), s));
   RFQ_CK(c, cudaMemsetAsync(ta.doc_linew, 0, 4ull * (m + 1), s));

@@ -36,6 +36,61 @@ __global__ void __launch_bounds__(128) csv_decide_kernel(TableArgs a) {
   int t = decide_chunk_type(S);
   a.ctype[e] = (uint8_t)t;
   if (t == CT_STRNF && c >= D.lead) a.chunk_nf[D.stat_base + k * D.W] = 1;
+  if (a.cand && c >= D.lead) {
+    // chunk types whose measurement the one-sweep candidates do not cover: the document goes
+    // through the exact second sweep (doc_exact[n_docs] counts them: 0 = that sweep exits at once)
+    bool exact = !(t == CT_STR || t == CT_BOOL || t == CT_BOOLNA || t == CT_UINT || t == CT_INT ||
+                   t == CT_INTNA || t == CT_FLOAT) ||
+                 (t == CT_FLOAT && ((const ChunkCand*)a.cand)[e].need_exact);
+    if (exact && atomicExch(a.doc_exact + lo, 1u) == 0u) atomicAdd(a.doc_exact + a.n_docs, 1u);
+  }
+}
+
+// ---- one-sweep mode: rows dropna removes, per chunk (the candidates cover all rows) ---------
+__global__ void __launch_bounds__(256) csv_rowstat_kernel(TableArgs a) {
+  uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+  bool dropped = false;
+  uint32_t key = 0;
+  if (slot < a.n_slots) {
+    uint32_t d = ub_search(a.slot_doc_r0, a.n_docs, slot);
+    const TDoc D = a.docs[d];
+    uint32_t L = slot - D.r0;
+    if (D.active && L >= 1 && L <= D.n_data) {
+      uint32_t chunk = (L - 1) / D.bl;
+      key = D.stat_base + chunk * D.W;
+      dropped = !row_kept(a, D, slot, chunk);
+    }
+  }
+  // neighbouring rows share their chunk: one atomic per warp in the common case
+  unsigned mask = __ballot_sync(0xffffffffu, dropped);
+  if (mask == 0) return;
+  uint32_t key0 = __shfl_sync(0xffffffffu, key, __ffs(mask) - 1);
+  bool same = !dropped || key == key0;
+  if (__all_sync(0xffffffffu, same)) {
+    if ((threadIdx.x & 31) == (uint32_t)(__ffs(mask) - 1)) atomicAdd(a.chunk_dropped + key0, (uint32_t)__popc(mask));
+  } else if (dropped) {
+    atomicAdd(a.chunk_dropped + key, 1u);
+  }
+}
+
+// ---- one-sweep mode: the ChunkMeasure of every entry from its candidates and decided type -----
+__global__ void __launch_bounds__(128) csv_finish_kernel(TableArgs a) {
+  uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= a.n_stat) return;
+  uint32_t lo = 0, hi = a.n_docs;
+  while (hi - lo > 1) {
+    uint32_t mid = (lo + hi) >> 1;
+    if (a.docs[mid].stat_base <= e) lo = mid; else hi = mid;
+  }
+  const TDoc D = a.docs[lo];
+  if (!D.active || D.W == 0 || a.doc_exact[lo]) return;   // exact documents keep the initial values
+  uint32_t rel = e - D.stat_base;
+  if (rel >= D.n_chunks * D.W) return;
+  uint32_t k = rel / D.W, c = rel - k * D.W;
+  if (c < D.lead) return;
+  ChunkMeasure M;
+  finish_measure(((const ChunkCand*)a.cand)[e], a.ctype[e], a.chunk_dropped[D.stat_base + k * D.W], &M);
+  ((ChunkMeasure*)a.meas)[e] = M;
 }
 
 // ---- sweep 2: measure ---------------------------------------------------------------------------
@@ -43,8 +98,11 @@ __global__ void __launch_bounds__(256, 3) csv_measure_kernel(TableArgs a) {
   __shared__ uint32_t s_m[8][RFQ_MAX_W];  // plain, ip, tz(min), inf, obj, sci, fl(or), nan_left(or)
   __shared__ uint32_t s_doc, s_keep;
   ChunkMeasure* meas = (ChunkMeasure*)a.meas;
+  const bool one_sweep = a.cand != nullptr;   // then only the documents marked exact are measured here
+  if (one_sweep && a.doc_exact[a.n_docs] == 0) return;
   for (uint32_t item = blockIdx.x; item < a.n_items; item += gridDim.x) {
     ItemCtx ic = item_ctx(a, item, &s_doc);
+    if (one_sweep && !a.doc_exact[ic.d]) { __syncthreads(); continue; }
     const TDoc D = a.docs[ic.d];
     uint32_t W = D.W;
     for (uint32_t c = threadIdx.x; c < W; c += blockDim.x) {
@@ -75,7 +133,7 @@ __global__ void __launch_bounds__(256, 3) csv_measure_kernel(TableArgs a) {
           if ((s_m[6][c] & m.fl) != m.fl) atomicOr(&s_m[6][c], m.fl);
           extra += m.extra_bytes;
         }
-        if (extra) { if (ngrp == 1) a.row_extra[slot] = extra; else atomicAdd(a.row_extra + slot, extra); }
+        if (extra && !one_sweep) { if (ngrp == 1) a.row_extra[slot] = extra; else atomicAdd(a.row_extra + slot, extra); }
       }
     }
     __syncthreads();
@@ -90,7 +148,7 @@ __global__ void __launch_bounds__(256, 3) csv_measure_kernel(TableArgs a) {
       if (s_m[6][c]) atomicOr(&M->fl, s_m[6][c]);
       if (s_m[7][c]) atomicOr(&M->nan_left, 1u);
     }
-    if (threadIdx.x == 0 && s_keep) atomicAdd(a.n_keep + ic.d, s_keep);
+    if (threadIdx.x == 0 && s_keep && !one_sweep) atomicAdd(a.n_keep + ic.d, s_keep);
     __syncthreads();
   }
 }
@@ -105,6 +163,11 @@ __global__ void __launch_bounds__(128) csv_layout_kernel(TableArgs a) {
   ColOut* col = (ColOut*)a.col;
   uint32_t off = 0;
   int flags = 0;
+  if (a.cand) {   // one-sweep mode: rows kept = data rows - rows dropna removed
+    uint32_t dr = 0;
+    for (uint32_t k = 0; k < D.n_chunks; ++k) dr += a.chunk_dropped[D.stat_base + k * D.W];
+    a.n_keep[d] = D.n_data - dr;
+  }
   for (uint32_t j = 0; j < D.h; ++j) {
     uint32_t c = D.lead + j;
     uint32_t e0 = D.stat_base + c;
@@ -156,6 +219,11 @@ void csv_table_measure(const TableArgs& a, cudaStream_t s) {
   if (a.n_docs == 0) return;
   prof_mark("csv_decide_kernel", s);
   if (!a.xcells && a.n_stat) RFQ_LAUNCH(csv_decide_kernel, (a.n_stat + 127) / 128, 128, 0, s, a);
+  if (a.cand) {
+    prof_mark("csv_rowstat+finish", s);
+    RFQ_LAUNCH(csv_rowstat_kernel, (a.n_slots + 255) / 256, 256, 0, s, a);
+    if (a.n_stat) RFQ_LAUNCH(csv_finish_kernel, (a.n_stat + 127) / 128, 128, 0, s, a);
+  }
   prof_mark("csv_measure_kernel", s);
   if (a.n_items) RFQ_LAUNCH(csv_measure_kernel, table_grid(a.n_items), 256, 0, s, a);
   prof_mark("csv_layout+rowbytes+scan", s);

@@ -154,6 +154,11 @@ struct TableArgs {
   const uint8_t* x_str_arena;     // decoded shared strings
   uint32_t* x_colflags;           // [n_cols] XF_* per output column
   uint32_t item_lo, item_hi;      // emit: work-item range of this launch (0, n_items = all)
+  // fused classify + measure (CSV path): candidates per (chunk, col), see cell_ops.cuh ChunkCand
+  void* cand;                     // ChunkCand[n_stat], nullptr = two-sweep mode
+  uint32_t* chunk_dropped;        // [n_stat] (entry of column 0 of each chunk): rows dropna removes
+  uint32_t* doc_exact;            // [n_docs] 1 = a chunk type the candidates do not cover: exact sweep
+  uint32_t max_w;                 // widest table of the batch (shared-memory size of the fused sweep)
 };
 
 struct ColOut { int32_t cls, dec, sci; uint32_t width, cp_off; };

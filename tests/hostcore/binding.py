@@ -104,3 +104,15 @@ def sheet_parse(sheet_xml: bytes, sst_xml, date_ids=(), nrows: int = 1000, td_id
     st = L.hc_sheet_parse(sheet_xml, len(sheet_xml), sst_xml, len(sst_xml) if sst_xml else 0,
                           d.ctypes.data if len(d) else None, len(d), 1 if date1904 else 0, nrows, buf, cap, C.byref(n))
     return st, (buf.raw[:n.value].decode("utf-8") if st == 0 else None)
+
+
+def set_fused(on: bool) -> None:
+    """Switch the sequential CSV model between the two-sweep form (classify, then measure under the
+    decided type) and the one-sweep candidates the GPU classify kernel reduces."""
+    lib().hc_set_fused(int(on))
+
+
+def fused_used() -> int:
+    L = lib()
+    L.hc_fused_used.restype = C.c_uint64
+    return int(L.hc_fused_used())

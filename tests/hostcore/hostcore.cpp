@@ -96,6 +96,8 @@ int64_t hc_txt(const uint8_t* p, int64_t len, uint8_t* out) {
 #include "../../replisense_rfq_b200/csrc/header_names.h"
 
 namespace {
+static bool g_fused = false;
+static uint64_t g_fused_used = 0;
 
 struct Rec { uint64_t start; uint32_t f0, f1; };
 
@@ -150,10 +152,29 @@ int csv_attempt(const uint8_t* doc, uint64_t len, uint32_t sep, int64_t nrows, s
   };
   std::vector<ChunkStat> stat((size_t)nch * W, ChunkStat{0, RFQ_NO_ROW, RFQ_NO_ROW, RFQ_NO_ROW, RFQ_NO_ROW, {0, 0, 0}});
   std::vector<uint32_t> row_na(ndata, 0);
+  std::vector<ChunkCand> cand((size_t)nch * W, ChunkCand{0, 0, 0, 0, 0, 6, 0, 0, 0, 0, 0, 0});
   for (uint32_t r = 0; r < ndata; ++r)
     for (uint32_t c = 0; c < W; ++c) {
       int is;
-      uint32_t f = classify_cell(cell(r, c), &is);
+      uint32_t f;
+      if (g_fused) {   // one visit: flags + measurement candidates (the fused GPU sweep)
+        CellCand m = classify_measure_cell(cell(r, c));
+        f = m.flags; is = m.int_status;
+        ChunkCand& C = cand[(size_t)(r / bl) * W + c];
+        if (m.na) C.na_count++;
+        else {
+          C.str_len = std::max(C.str_len, m.str_len); C.int_len = std::max(C.int_len, m.int_len);
+          C.uint_len = std::max(C.uint_len, m.uint_len); C.bool_len = std::max(C.bool_len, m.bool_len);
+          if (m.has_float) {
+            C.ip_len = std::max(C.ip_len, m.ip_len); C.min_tz = std::min(C.min_tz, m.tz);
+            C.inf_len = std::max(C.inf_len, m.inf_len); C.obj_len = std::max(C.obj_len, m.obj_len);
+            C.sci_len = std::max(C.sci_len, m.sci_len); C.fl |= m.fl;
+          }
+          if (m.need_exact) C.need_exact = 1;
+        }
+      } else {
+        f = classify_cell(cell(r, c), &is);
+      }
       ChunkStat& S = stat[(size_t)(r / bl) * W + c];
       S.flags |= f;
       if (is != INT_OK) {
@@ -178,7 +199,16 @@ int csv_attempt(const uint8_t* doc, uint64_t len, uint32_t sep, int64_t nrows, s
     nkeep += keep[r];
   }
   std::vector<ChunkMeasure> meas((size_t)nch * W, ChunkMeasure{0, 0, 6, 0, 0, 0, 0, 0});
-  for (uint32_t r = 0; r < ndata; ++r) {
+  bool exact = !g_fused;
+  if (g_fused) {
+    std::vector<uint32_t> dropped(nch, 0);
+    for (uint32_t r = 0; r < ndata; ++r) if (!keep[r]) dropped[r / bl]++;
+    for (size_t k = 0; k < meas.size(); ++k)
+      if ((k % W) >= lead && !finish_measure(cand[k], ctype[k], dropped[k / W], &meas[k])) exact = true;
+    if (exact) std::fill(meas.begin(), meas.end(), ChunkMeasure{0, 0, 6, 0, 0, 0, 0, 0});
+    else g_fused_used++;
+  }
+  for (uint32_t r = 0; r < ndata && exact; ++r) {
     if (!keep[r]) continue;
     for (uint32_t c = lead; c < W; ++c) {
       size_t k = (size_t)(r / bl) * W + c;
@@ -244,6 +274,9 @@ extern "C" {
 // Full reference trial loop restricted to what can differ structurally: utf-8 then latin-1, each
 // with ',', ';', TAB (cp1252 can never win where latin-1 failed: same bytes, same structure).
 // returns status (0 ok / 1 unparseable / 2 unsupported); *out_len bytes written to out (cap).
+void hc_set_fused(int on) { g_fused = on != 0; }
+uint64_t hc_fused_used() { return g_fused_used; }
+
 int hc_csv_parse(const uint8_t* doc, uint64_t len, int64_t nrows, uint8_t* out, uint64_t cap,
                  uint64_t* out_len) {
   static const uint32_t seps[3] = {',', ';', '\t'};

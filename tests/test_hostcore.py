@@ -290,3 +290,25 @@ def test_strtod_exact_matches_python_float():
         d = C.c_double()
         assert L.hc_strtod(t.encode(), len(t), C.byref(d)), t
         assert struct.pack("<d", d.value) == struct.pack("<d", float(t)), t
+
+
+def test_fused_measurement_equals_two_sweeps():
+    """The one-sweep measurement candidates (what the GPU classify kernel reduces) give the same text
+    as classifying first and measuring under the decided type, on the reference goldens and fuzz."""
+    import base64
+    import json
+    from pathlib import Path
+    docs = [corpus.fuzz_csv(s) for s in range(600)] + [corpus.rfq_csv(300, seed=s) for s in range(3)]
+    docs += [base64.b64decode(c["data"]) for c in json.loads((Path(__file__).parent / "golden" / "ref_csv.json").read_text())]
+    try:
+        H.set_fused(False)
+        two = [H.csv_parse(d, 1000) for d in docs]
+        H.set_fused(True)
+        u0 = H.fused_used()
+        one = [H.csv_parse(d, 1000) for d in docs]
+        used = H.fused_used() - u0
+    finally:
+        H.set_fused(False)
+    bad = [i for i, (a, b) in enumerate(zip(two, one)) if a != b]
+    assert not bad, bad[:10]
+    assert used > 400
