@@ -103,6 +103,12 @@ RFQ_HD uint64_t pack8(const char* s) {
    (uint64_t)(uint8_t)(g) << 48 | (uint64_t)(uint8_t)(h) << 56)
 
 RFQ_HD bool is_na_token(uint32_t n, uint64_t f) {
+  if (n == 0) return true;
+  if (n > 8) return false;
+  {   // every NA word starts with one of # - 1 < N n: most cells leave here
+    const uint32_t b = (uint32_t)(f & 0xFFu);
+    if (!(b == 'N' || b == 'n' || b == '#' || b == '-' || b == '1' || b == '<')) return false;
+  }
   switch (n) {
     case 0: return true;
     case 2: return f == RFQ_P8('N', 'A', 0, 0, 0, 0, 0, 0);
