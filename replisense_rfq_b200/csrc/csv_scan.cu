@@ -118,6 +118,7 @@ __global__ void __launch_bounds__(256) csv_tilefn_kernel(ScanArgs a) {
   bool bom = tile == 0 && doc_has_bom(doc, len);
   LaneBytes lb = load_lane_classes(doc, len, tile * RFQ_TILE + lane * 16, a.sep, bom);
   uint32_t f = lane_function(lb.cls, class_fn);
+  a.lane_fn[(size_t)t * 32 + lane] = f;   // pass 2 composes these instead of re-deriving them
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     uint32_t g = __shfl_down_sync(0xffffffffu, f, o);
@@ -155,7 +156,7 @@ __global__ void __launch_bounds__(256) csv_count_kernel(ScanArgs a) {
   bool bom = tile == 0 && doc_has_bom(doc, len);
   uint32_t base = tile * RFQ_TILE + lane * 16;
   LaneBytes lb = load_lane_classes(doc, len, base, a.sep, bom);
-  uint32_t f = lane_function(lb.cls, class_fn);
+  uint32_t f = a.lane_fn[(size_t)t * 32 + lane];
   // inclusive scan of lane functions, then shift to exclusive
   uint32_t incl = f;
 #pragma unroll
@@ -185,6 +186,7 @@ __global__ void __launch_bounds__(256) csv_count_kernel(ScanArgs a) {
     for (uint32_t k = 0; k < eof_k; ++k) s2 = (int)((class_fn[(lb.cls >> (4 * k)) & 0xFu] >> (4 * s2)) & 0xFu);
     final_state = s2;
   }
+  a.lane_cnt[(size_t)t * 32 + lane] = (uint16_t)(nf | (nl << 8));   // at most 16 of each per lane
 #pragma unroll
   for (int o = 16; o; o >>= 1) {
     nf += __shfl_xor_sync(0xffffffffu, nf, o);
@@ -210,12 +212,9 @@ __global__ void __launch_bounds__(256) csv_index_kernel(ScanArgs a) {
   LaneBytes lb = load_lane_classes(doc, len, base, a.sep, bom);
   uint32_t b0 = a.lane_state[3 * t], b1 = a.lane_state[3 * t + 1], b2 = a.lane_state[3 * t + 2];
   int st = (int)(((b0 >> lane) & 1u) | (((b1 >> lane) & 1u) << 1) | (((b2 >> lane) & 1u) << 2));
-  // this lane's counts, then exclusive prefix inside the warp
-  uint32_t nf = 0, nl = 0;
-  lane_walk(lb.cls, st, class_fn, class_ev, [&](int k, int e, int sb) {
-    nf += (e & EV_FIELD_END) ? 1u : 0u;
-    nl += (e & EV_LINE_END) ? 1u : 0u;
-  });
+  // this lane's counts (from pass 2), then exclusive prefix inside the warp
+  const uint32_t cnt = a.lane_cnt[(size_t)t * 32 + lane];
+  const uint32_t nf = cnt & 0xFFu, nl = cnt >> 8;
   uint32_t pf = nf, pl = nl;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
