@@ -76,13 +76,15 @@ __device__ __forceinline__ LaneBytes load_lane_classes(const uint8_t* __restrict
   return LaneBytes{cls};
 }
 
-// lane function by reverse composition: G <- G o t_k, running G kept as a byte table
+// lane function by reverse composition: G <- G o (t_2k then t_2k+1), running G kept as a byte
+// table; pair_fn[c0 | c1 << 4] is the function of two consecutive bytes of classes c0, c1, so the
+// 16 bytes cost 8 look-ups and 16 PRMTs
 __device__ __forceinline__ uint32_t lane_function(unsigned long long cls,
-                                                  const uint32_t* __restrict__ class_fn) {
+                                                  const uint32_t* __restrict__ pair_fn) {
   uint32_t glo = 0x03020100u, ghi = 0x07060504u;
 #pragma unroll
-  for (int k = 15; k >= 0; --k) {
-    uint32_t sel = class_fn[(cls >> (4 * k)) & 0xFu];
+  for (int k = 7; k >= 0; --k) {
+    uint32_t sel = pair_fn[(cls >> (8 * k)) & 0x7Fu];
     uint32_t nlo = __byte_perm(glo, ghi, sel & 0xFFFFu);
     uint32_t nhi = __byte_perm(glo, ghi, sel >> 16);
     glo = nlo; ghi = nhi;
@@ -108,6 +110,9 @@ __device__ __forceinline__ bool doc_has_bom(const uint8_t* __restrict__ doc, uin
 // ---- pass 1: transition function of every tile ------------------------------------------------
 __global__ void __launch_bounds__(256) csv_tilefn_kernel(ScanArgs a) {
   RFQ_INIT_CLASS_FN();
+  __shared__ uint32_t pair_fn[128];
+  if (threadIdx.x < 128) pair_fn[threadIdx.x] = fn_compose(class_fn[threadIdx.x & 7u], class_fn[(threadIdx.x >> 4) & 7u]);
+  __syncthreads();
   uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
   int lane = threadIdx.x & 31;
   if (t >= a.n_tiles) return;
@@ -117,7 +122,7 @@ __global__ void __launch_bounds__(256) csv_tilefn_kernel(ScanArgs a) {
   const uint8_t* doc = a.arena + a.doc_off[d];
   bool bom = tile == 0 && doc_has_bom(doc, len);
   LaneBytes lb = load_lane_classes(doc, len, tile * RFQ_TILE + lane * 16, a.sep, bom);
-  uint32_t f = lane_function(lb.cls, class_fn);
+  uint32_t f = lane_function(lb.cls, pair_fn);
   a.lane_fn[(size_t)t * 32 + lane] = f;   // pass 2 composes these instead of re-deriving them
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
