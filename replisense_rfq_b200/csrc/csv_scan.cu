@@ -101,9 +101,11 @@ __device__ __forceinline__ bool doc_has_bom(const uint8_t* __restrict__ doc, uin
 
 #define RFQ_INIT_CLASS_FN()                                         \
   __shared__ uint32_t class_fn[8], class_ev[8];                     \
+  __shared__ uint2 class_fe[8];   /* {next states, events} of a class in one 8-byte load */ \
   if (threadIdx.x < 8) {                                            \
     class_fn[threadIdx.x] = threadIdx.x < N_CLASSES ? csv_class_fn(threadIdx.x) : RFQ_FN_IDENTITY; \
     class_ev[threadIdx.x] = threadIdx.x < N_CLASSES ? csv_class_ev(threadIdx.x) : 0u;              \
+    class_fe[threadIdx.x] = make_uint2(class_fn[threadIdx.x], class_ev[threadIdx.x]);              \
   }                                                                 \
   __syncthreads();
 
@@ -136,14 +138,14 @@ __global__ void __launch_bounds__(256) csv_tilefn_kernel(ScanArgs a) {
 // (table driven: next state and events are nibble look-ups in shared memory, no branches)
 template <class F>
 __device__ __forceinline__ int lane_walk(unsigned long long cls, int st,
-                                         const uint32_t* __restrict__ class_fn,
-                                         const uint32_t* __restrict__ class_ev, F&& ev) {
+                                         const uint2* __restrict__ class_fe, F&& ev) {
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
     uint32_t c = (uint32_t)((cls >> (4 * k)) & 0xFu);
-    int e = (int)((class_ev[c] >> (4 * st)) & 0xFu);
+    const uint2 fe = class_fe[c];
+    int e = (int)((fe.y >> (4 * st)) & 0xFu);
     if (e) ev(k, e, st);
-    st = (int)((class_fn[c] >> (4 * st)) & 0xFu);
+    st = (int)((fe.x >> (4 * st)) & 0xFu);
   }
   return st;
 }
@@ -182,7 +184,7 @@ __global__ void __launch_bounds__(256) csv_count_kernel(ScanArgs a) {
   uint32_t nf = 0, nl = 0;
   uint32_t eof_k = (len >= base && len < base + 16) ? len - base : 0xFFu;
   int final_state = -1;
-  lane_walk(lb.cls, st, class_fn, class_ev, [&](int k, int e, int sb) {
+  lane_walk(lb.cls, st, class_fe, [&](int k, int e, int sb) {
     nf += (e & EV_FIELD_END) ? 1u : 0u;
     nl += (e & EV_LINE_END) ? 1u : 0u;
   });
@@ -230,7 +232,7 @@ __global__ void __launch_bounds__(256) csv_index_kernel(ScanArgs a) {
   uint32_t g = a.tile_nf_pre[t] + pf - nf;          // global index of this lane's first field end
   uint32_t r = a.tile_nl_pre[t] + pl - nl + d;      // record slot currently open at this lane
   uint32_t doc_begin = has_bom ? 3u : 0u;
-  lane_walk(lb.cls, st, class_fn, class_ev, [&](int k, int e, int sb) {
+  lane_walk(lb.cls, st, class_fe, [&](int k, int e, int sb) {
     uint32_t pos = base + k;
     if (e & EV_REC_START) a.rec_start[r] = pos;
     if (e & EV_REC_START_WS) {
