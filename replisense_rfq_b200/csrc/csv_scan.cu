@@ -153,6 +153,22 @@ __device__ __forceinline__ int lane_walk(unsigned long long cls, int st,
 // ---- pass 2: lane start states + per-tile counts ----------------------------------------------
 __global__ void __launch_bounds__(256) csv_count_kernel(ScanArgs a) {
   RFQ_INIT_CLASS_FN();
+  // two bytes per step: for classes (c0, c1) and every start state, one byte holding the state after
+  // both bytes (bits 0-2), their field ends (bits 3-4) and their line ends (bits 5-6)
+  __shared__ unsigned long long pair_walk[128];
+  if (threadIdx.x < 128) {
+    const uint32_t c0 = threadIdx.x & 7u, c1 = (threadIdx.x >> 4) & 7u;
+    unsigned long long w = 0;
+    for (int s0 = 0; s0 < 8; ++s0) {
+      int e0 = (int)((class_ev[c0] >> (4 * s0)) & 0xFu), s1 = (int)((class_fn[c0] >> (4 * s0)) & 0xFu);
+      int e1 = (int)((class_ev[c1] >> (4 * s1)) & 0xFu), s2 = (int)((class_fn[c1] >> (4 * s1)) & 0xFu);
+      uint32_t f2 = ((e0 & EV_FIELD_END) ? 1u : 0u) + ((e1 & EV_FIELD_END) ? 1u : 0u);
+      uint32_t l2 = ((e0 & EV_LINE_END) ? 1u : 0u) + ((e1 & EV_LINE_END) ? 1u : 0u);
+      w |= (unsigned long long)((uint32_t)s2 | (f2 << 3) | (l2 << 5)) << (8 * s0);
+    }
+    pair_walk[threadIdx.x] = w;
+  }
+  __syncthreads();
   uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
   int lane = threadIdx.x & 31;
   if (t >= a.n_tiles) return;
@@ -184,10 +200,16 @@ __global__ void __launch_bounds__(256) csv_count_kernel(ScanArgs a) {
   uint32_t nf = 0, nl = 0;
   uint32_t eof_k = (len >= base && len < base + 16) ? len - base : 0xFFu;
   int final_state = -1;
-  lane_walk(lb.cls, st, class_fe, [&](int k, int e, int sb) {
-    nf += (e & EV_FIELD_END) ? 1u : 0u;
-    nl += (e & EV_LINE_END) ? 1u : 0u;
-  });
+  {
+    int s1 = st;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      uint32_t x = (uint32_t)(pair_walk[(lb.cls >> (8 * k)) & 0x7Fu] >> (8 * s1)) & 0xFFu;
+      nf += (x >> 3) & 3u;
+      nl += (x >> 5) & 3u;
+      s1 = (int)(x & 7u);
+    }
+  }
   if (eof_k != 0xFFu) {  // state just before the virtual LF
     int s2 = st;
     for (uint32_t k = 0; k < eof_k; ++k) s2 = (int)((class_fn[(lb.cls >> (4 * k)) & 0xFu] >> (4 * s2)) & 0xFu);
