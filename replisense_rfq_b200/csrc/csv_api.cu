@@ -78,6 +78,7 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
   sa.tile_fn = c->pool.alloc<uint32_t>(nt + 1);
   sa.tile_fn_pre = c->pool.alloc<uint32_t>(nt + 1);
   sa.lane_state = c->pool.alloc<uint32_t>(3ull * nt + 1);
+  sa.lane_cls = c->pool.alloc<unsigned long long>(32ull * nt + 32);
   sa.lane_fn = c->pool.alloc<uint32_t>(32ull * nt + 32);
   sa.lane_cnt = c->pool.alloc<uint16_t>(32ull * nt + 32);
   sa.tile_nf = c->pool.alloc<uint32_t>(nt + 1);

@@ -126,6 +126,7 @@ __global__ void __launch_bounds__(256) csv_tilefn_kernel(ScanArgs a) {
   LaneBytes lb = load_lane_classes(doc, len, tile * RFQ_TILE + lane * 16, a.sep, bom);
   uint32_t f = lane_function(lb.cls, pair_fn);
   a.lane_fn[(size_t)t * 32 + lane] = f;   // pass 2 composes these instead of re-deriving them
+  a.lane_cls[(size_t)t * 32 + lane] = lb.cls;   // passes 2 and 3 read 8 bytes of classes instead of 16 of text
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     uint32_t g = __shfl_down_sync(0xffffffffu, f, o);
@@ -178,7 +179,7 @@ __global__ void __launch_bounds__(256) csv_count_kernel(ScanArgs a) {
   const uint8_t* doc = a.arena + a.doc_off[d];
   bool bom = tile == 0 && doc_has_bom(doc, len);
   uint32_t base = tile * RFQ_TILE + lane * 16;
-  LaneBytes lb = load_lane_classes(doc, len, base, a.sep, bom);
+  LaneBytes lb{a.lane_cls[(size_t)t * 32 + lane]};
   uint32_t f = a.lane_fn[(size_t)t * 32 + lane];
   // inclusive scan of lane functions, then shift to exclusive
   uint32_t incl = f;
@@ -238,7 +239,7 @@ __global__ void __launch_bounds__(256) csv_index_kernel(ScanArgs a) {
   bool has_bom = doc_has_bom(doc, len);
   bool bom = tile == 0 && has_bom;
   uint32_t base = tile * RFQ_TILE + lane * 16;
-  LaneBytes lb = load_lane_classes(doc, len, base, a.sep, bom);
+  LaneBytes lb{a.lane_cls[(size_t)t * 32 + lane]};
   uint32_t b0 = a.lane_state[3 * t], b1 = a.lane_state[3 * t + 1], b2 = a.lane_state[3 * t + 2];
   int st = (int)(((b0 >> lane) & 1u) | (((b1 >> lane) & 1u) << 1) | (((b2 >> lane) & 1u) << 2));
   // this lane's counts (from pass 2), then exclusive prefix inside the warp

@@ -75,6 +75,7 @@ struct ScanArgs {
   uint32_t* tile_fn;          // [n_tiles+1] transition function of each tile (nibble form)
   uint32_t* tile_fn_pre;      // [n_tiles+1] exclusive composition
   uint32_t* lane_state;       // [n_tiles*3] bit planes of the 32 lane start states
+  unsigned long long* lane_cls;  // [n_tiles*32] byte classes of each lane's 16 bytes, a nibble each (pass 1 -> 2, 3)
   uint32_t* lane_fn;          // [n_tiles*32] transition function of each lane's 16 bytes (pass 1 -> pass 2)
   uint16_t* lane_cnt;         // [n_tiles*32] field ends | line ends << 8 of each lane (pass 2 -> pass 3)
   uint32_t* tile_nf;          // [n_tiles+1] field ends per tile      (last = 0)
