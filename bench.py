@@ -257,13 +257,18 @@ def main():
     # of one step overlaps the kernels and the D2H copy of the other (PCIe is full duplex).  Every
     # step still uploads its input from pinned host memory and downloads its whole result.
     from replisense_rfq_b200.engine import EnginePool
-    depth = int(os.environ.get("RFQ_POOL_DEPTH", "3"))   # measured on B200: 2 -> 3.95 ms, 3 -> 3.51 ms, 4 -> 3.93 ms per step
+    # measured on B200 (C2, every engine warmed): depth 2 -> 3.98, 3 -> 3.54, 4 -> 3.25, 6 -> 3.09 ms per step;
+    # the PCIe floor for 86.8 MB up + 135.1 MB down at once is 2.71 ms (tools/pcie_probe.py)
+    depth = int(os.environ.get("RFQ_POOL_DEPTH", "4"))
     pool = EnginePool(local_rank, depth=depth)
 
     def one_step(e, _):
         r = e.csv_parse_arena(arena, offsets, lengths, mr)
         return int(r.lengths[0])
-    pool.map(one_step, range(4))
+    for e in pool.engines:   # every engine twice: its buffers are sized on the first call
+        for _ in range(2):
+            one_step(e, 0)
+    pool.map(one_step, range(2 * depth))
     barrier()
     t0 = time.perf_counter()
     outs = pool.map(one_step, range(args.steps))
