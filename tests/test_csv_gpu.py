@@ -98,6 +98,26 @@ def test_csv_crlf_and_wide(eng):
         assert eng.parse_csv_many([d], 10 ** 6)[0] == oracle(d, 10 ** 6)
 
 
+def test_csv_widest_tables(eng):
+    """1000 and 1024 columns (the one-sweep kernel needs its > 48 KB shared-memory opt-in there), mixed
+    column types, next to a narrow table in the same batch; 1025 columns are declined loudly."""
+    def table(w, nrows):
+        kinds = ["int", "float", "str", "bool", "na"]
+        def cell(r, c):
+            k = kinds[c % 5]
+            return {"int": str(r * c % 977), "float": "%.3f" % (r * 1.25 + c), "str": "p%d-%d" % (r, c),
+                    "bool": "True" if (r + c) % 3 else "False", "na": "" if (r + c) % 2 else "7"}[k]
+        return (",".join("c%d" % i for i in range(w)) + "\n" +
+                "\n".join(",".join(cell(r, c) for c in range(w)) for r in range(nrows)) + "\n").encode()
+    docs = [table(1000, 40), corpus.rfq_csv(50, seed=2), table(1024, 3)]
+    got = eng.parse_csv_many(docs, 1000)
+    for g, d in zip(got, docs):
+        assert g == oracle(d, 1000)
+    from replisense_rfq_b200 import EngineError
+    with pytest.raises(EngineError):
+        eng.parse_csv_many([table(1025, 2)], 1000)
+
+
 def test_csv_file_parser_api(eng, tmp_path):
     from replisense_rfq_b200 import FileParser, FileParsingError
     import asyncio
