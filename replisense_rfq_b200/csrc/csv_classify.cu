@@ -8,9 +8,10 @@
 // (mixing columns in a warp left 6 of 32 lanes active: profiles/r01_emit_v1_*); the item's bytes
 // are shared by its warps through L1.  Column statistics are reduced in
 // shared memory per item and merged into global memory with one atomic per column per item.
-// Three sweeps over the cells: classify -> (decide) -> measure -> (layout, row offsets) -> emit.
-// Tokens are re-parsed in each sweep instead of being materialised: the bytes stay in L2 and a
-// typed copy would cost more HBM traffic than the re-parse costs issue slots.
+// Two sweeps over the cells of a CSV document: typing + measuring in one (csv_classify_fused_kernel)
+// -> decide, rows dropped, layout, row offsets -> emit; sheets and the documents the one-sweep
+// candidates do not cover measure in a separate sweep under the decided type (csv_measure_kernel).
+// Tokens are re-parsed by emit instead of being materialised.
 #include <atomic>
 #include "table_common.cuh"
 
