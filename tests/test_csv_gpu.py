@@ -142,3 +142,31 @@ def test_csv_c2_full_size_bit_exact(eng):
     want = oracle(d, 10 ** 6)
     assert len(got) == len(want)
     assert got == want
+
+
+def test_engine_pool_concurrent_calls_keep_their_results():
+    """Several calls in flight on one GPU (EnginePool: one ctx + stream each): every call gets its
+    own document's text, whatever overlaps with it; the shared FileParser picks engines from a pool."""
+    import asyncio
+    from concurrent.futures import ThreadPoolExecutor
+    from replisense_rfq_b200 import FileParser, build
+    from replisense_rfq_b200.engine import EnginePool
+    build.build()
+    docs = [corpus.rfq_csv(200 + 37 * i, seed=i) for i in range(24)] + [corpus.fuzz_csv(s) for s in range(24)]
+    want = []
+    for d in docs:
+        try:
+            want.append(oracle(d, 1000))
+        except O.OracleParsingError:
+            want.append(None)
+    pool = EnginePool(0, depth=3)
+    try:
+        for _ in range(3):
+            got = pool.map(lambda e, d: e.parse_csv_many([d], 1000)[0], docs)
+            assert got == want
+    finally:
+        pool.close()
+    fp = FileParser()   # default: engines from the per-device pool
+    with ThreadPoolExecutor(8) as tp:
+        got = list(tp.map(lambda d: fp.parse_many([d], ["csv"])[0], docs))
+    assert [None if isinstance(g, Exception) else g for g in got] == want
