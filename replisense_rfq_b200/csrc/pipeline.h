@@ -200,6 +200,7 @@ struct XmlArgs {
   uint32_t n_rows, n_cells, n_si;
   uint32_t* rowpos; uint32_t* row_c0; uint32_t* rownum;  // [n_rows+1]
   uint32_t* cpos;                                        // [n_cells]
+  uint32_t* cell_doc; uint32_t* cell_row;                // [n_cells] document / <row> element of each <c> (~0u = none)
   void* xcells;                                          // XCell[n_cells]
   uint32_t* sipos; uint32_t* si_len; uint32_t* si_off;   // [n_si+1]
   uint8_t* str_arena;                                    // decoded shared strings

@@ -107,6 +107,8 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
   xa.row_c0 = c->pool.alloc<uint32_t>((size_t)xa.n_rows + 1);
   xa.rownum = c->pool.alloc<uint32_t>((size_t)xa.n_rows + 1);
   xa.cpos = c->pool.alloc<uint32_t>((size_t)xa.n_cells + 1);
+  xa.cell_doc = c->pool.alloc<uint32_t>((size_t)xa.n_cells + 1);
+  xa.cell_row = c->pool.alloc<uint32_t>((size_t)xa.n_cells + 1);
   xa.xcells = c->pool.alloc<XCell>((size_t)xa.n_cells + 1);
   xa.sipos = c->pool.alloc<uint32_t>((size_t)xa.n_si + 1);
   xa.si_len = c->pool.alloc<uint32_t>((size_t)xa.n_si + 1);

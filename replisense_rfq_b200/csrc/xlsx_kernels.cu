@@ -84,7 +84,11 @@ __global__ void __launch_bounds__(256) xml_tags_kernel(XmlArgs a) {
       int k = __ffs(mm) - 1;
       uint32_t kd = (kinds >> (2 * k)) & 3u;
       if (kd == 1) { a.rowpos[ir] = base + k; a.row_c0[ir] = ic; ++ir; }
-      else if (kd == 2) { a.cpos[ic++] = base + k; }
+      else if (kd == 2) {   // its document and the <row> element it follows are known right here
+        a.cpos[ic] = base + k; a.cell_doc[ic] = d;
+        a.cell_row[ic] = ir > a.tile_pre[0][a.tile_base[d]] ? ir - 1 : 0xFFFFFFFFu;
+        ++ic;
+      }
       else if (kd == 3) { a.sipos[is++] = base + k; }
     }
   }
@@ -142,7 +146,7 @@ __global__ void __launch_bounds__(128) xrow_fix_kernel(XmlArgs a) {
 __global__ void __launch_bounds__(128) xcell_kernel(XmlArgs a) {
   uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= a.n_cells) return;
-  uint32_t d = x_find(a.cell_base, a.n_docs + 1, k);
+  uint32_t d = a.cell_doc[k];
   const uint8_t* doc = a.arena + a.doc_off[d];
   SstView sv; sv.off = nullptr; sv.len = nullptr; sv.n = 0;
   int sd = a.sst_of[d];
@@ -156,9 +160,9 @@ __global__ void __launch_bounds__(128) xcell_kernel(XmlArgs a) {
   if (x.mode == CM_RAW) x.bits += 0;  // offsets are already global into the string arena
   // row element of this cell, ordering checks
   uint32_t rb = a.row_base[d], nr = a.row_base[d + 1] - rb;
-  uint32_t e = rb + x_find(a.row_c0 + rb, nr, k);
-  if (nr == 0 || a.row_c0[e] > k) flags |= XU_ORDER;   // a <c> outside any <row>
-  uint32_t r = a.rownum[e];
+  uint32_t e = a.cell_row[k];
+  if (e == 0xFFFFFFFFu) { flags |= XU_ORDER; e = rb; nr = 0; }   // a <c> before any <row> of its document
+  uint32_t r = nr ? a.rownum[e] : 0;
   if (e > rb && a.rownum[e - 1] >= r) flags |= XU_ORDER;
   if ((flags & XU_C_NOREF) && nr) x.col = k - a.row_c0[e] + 1;   // col_counter += 1 from the row start
   ((XCell*)a.xcells)[k] = x;
@@ -173,11 +177,10 @@ __global__ void __launch_bounds__(128) xcell_kernel(XmlArgs a) {
 __global__ void __launch_bounds__(128) xcell_order_kernel(XmlArgs a) {
   uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k + 1 >= a.n_cells) return;
-  uint32_t d = x_find(a.cell_base, a.n_docs + 1, k);
-  if (k + 1 >= a.cell_base[d + 1]) return;
-  uint32_t rb = a.row_base[d], nr = a.row_base[d + 1] - rb;
-  if (nr == 0) return;
-  uint32_t e0 = x_find(a.row_c0 + rb, nr, k), e1 = x_find(a.row_c0 + rb, nr, k + 1);
+  uint32_t d = a.cell_doc[k];
+  if (a.cell_doc[k + 1] != d) return;
+  uint32_t e0 = a.cell_row[k], e1 = a.cell_row[k + 1];
+  if (e0 == 0xFFFFFFFFu) return;
   const XCell* xc = (const XCell*)a.xcells;
   if (e0 == e1 && xc[k + 1].col <= xc[k].col) atomicOr(&a.shape[d].flags, XU_ORDER);
 }

@@ -79,13 +79,22 @@ def main():
         docs += [ss, sx]; kind += [1, 0]; sst_of += [-1, len(docs) - 2]
     nbytes = sum(map(len, docs))
     e2e = timed(lambda: eng.sheets_batch(docs, kind, sst_of, 1000), 3)
+    eng.set_profile(True)
+    t0 = time.perf_counter()
+    eng.sheets_batch(docs, kind, sst_of, 1000)
+    t_call = time.perf_counter() - t0
+    sheet_dev_ms = eng.last_run_ms()            # first kernel .. last kernel of rfq_sheets_run (host syncs inside)
+    sheet_prof = {k: round(v, 4) for k, v in eng.profile()}
+    eng.set_profile(False)
     t0 = time.perf_counter()
     for sx, ss in pairs[:20]:
         df = X.table_to_frame(X.sheet_table(sx, X.read_string_table(ss), nrows=1000), 1000)
         O.frame_to_text(df)
     cpu = (time.perf_counter() - t0) / sum(len(a) + len(b) for a, b in pairs[:20])
     out["C3_sheets"] = {"sheets": n_sheet, "MB": nbytes / 1e6, "e2e_MBps_incl_python_packing": nbytes / 1e6 / e2e,
-                        "sheets_per_s_e2e": n_sheet / e2e, "cpu_1core_MBps_restated_reader": 1e-6 / cpu}
+                        "sheets_per_s_e2e": n_sheet / e2e, "cpu_1core_MBps_restated_reader": 1e-6 / cpu,
+                        "run_ms_first_to_last_kernel": sheet_dev_ms, "call_ms": t_call * 1e3,
+                        "device_MBps": nbytes / 1e3 / sheet_dev_ms, "stage_ms": sheet_prof}
     (ROOT / "gpurun_out").mkdir(exist_ok=True)
     (ROOT / "gpurun_out" / "configs.json").write_text(json.dumps(out, indent=1))
     print(json.dumps(out, indent=1))
