@@ -49,6 +49,51 @@ RFQ_HD ExcelDate excel_to_datetime(double value, bool date1904) {
   return r;
 }
 
+// t="d" cells: ISO 8601 text as datetime.fromisoformat reads it.  Accepted here: YYYY-MM-DD, optionally
+// followed by 'T' or a blank and HH:MM[:SS[.f]] with 1-6 fraction digits that amount to whole
+// milliseconds, years 1000-9999, no zone.  Returns false for every other spelling (declined by the
+// caller, never guessed).  *ms = milliseconds since 0001-01-01T00:00.
+RFQ_HD bool parse_iso_datetime(const uint8_t* s, uint32_t n, int64_t* ms) {
+  auto dig = [&](uint32_t i) -> int { return (i < n && s[i] >= '0' && s[i] <= '9') ? s[i] - '0' : -1; };
+  auto num = [&](uint32_t i, int k) -> int { int v = 0; for (int q = 0; q < k; ++q) { int d = dig(i + q); if (d < 0) return -1; v = v * 10 + d; } return v; };
+  if (n < 10 || s[4] != '-' || s[7] != '-') return false;
+  int y = num(0, 4), mo = num(5, 2), da = num(8, 2);
+  if (y < 1000 || mo < 1 || mo > 12 || da < 1) return false;
+  const int mdays[12] = {31, 28, 31, 30, 31, 30, 31, 31, 30, 31, 30, 31};
+  bool leap = (y % 4 == 0 && y % 100 != 0) || y % 400 == 0;
+  if (da > mdays[mo - 1] + ((mo == 2 && leap) ? 1 : 0)) return false;
+  int h = 0, mi = 0, se = 0, frac_ms = 0;
+  if (n > 10) {
+    if (!(s[10] == 'T' || s[10] == ' ') || n < 16 || s[13] != ':') return false;
+    h = num(11, 2); mi = num(14, 2);
+    if (h < 0 || h > 23 || mi < 0 || mi > 59) return false;
+    uint32_t i = 16;
+    if (i < n) {
+      if (s[i] != ':' || n < 19) return false;
+      se = num(17, 2);
+      if (se < 0 || se > 59) return false;
+      i = 19;
+      if (i < n) {
+        if (s[i] != '.') return false;
+        uint32_t nd = n - (i + 1);
+        if (nd < 1 || nd > 6) return false;
+        int f = 0;
+        for (uint32_t q = 0; q < 6; ++q) { int d = q < nd ? dig(i + 1 + q) : 0; if (d < 0) return false; f = f * 10 + d; }
+        if (f % 1000) return false;            // microseconds: a finer column resolution than we carry
+        frac_ms = f / 1000;
+      }
+    }
+  }
+  // days since 0001-01-01 (proleptic Gregorian)
+  int64_t yy = y - (mo <= 2 ? 1 : 0);
+  int64_t era = yy / 400, yoe = yy - era * 400;
+  int64_t doy = (153 * (mo + (mo > 2 ? -3 : 9)) + 2) / 5 + da - 1;
+  int64_t doe = yoe * 365 + yoe / 4 - yoe / 100 + doy;
+  int64_t days = era * 146097 + doe - 306;
+  *ms = days * RFQ_MS_PER_DAY + ((int64_t)h * 3600 + mi * 60 + se) * 1000 + frac_ms;
+  return true;
+}
+
 struct Civil { int y, mo, d, h, mi, s, ms; };
 RFQ_HD Civil civil_from_ms(int64_t total) {
   Civil c;

@@ -13,7 +13,7 @@ enum {
   XU_BANG = 1u << 0,        // comment / CDATA / doctype inside the part
   XU_NO_REF = 1u << 1,      // malformed r= on a <row> or <c>
   XU_ORDER = 1u << 2,       // rows / columns not strictly increasing
-  XU_DATE = 1u << 3,        // timedelta-styled number, negative date serial, or t="d" (ISO 8601 text)
+  XU_DATE = 1u << 3,        // timedelta-styled number, negative date serial, t="d" text outside the accepted ISO forms
   XU_RICH_INLINE = 1u << 4, // inline string with rich-text runs
   XU_BAD_NUMBER = 1u << 5,  // numeric literal we cannot type exactly (overflow, nan, malformed)
   XU_BAD_SST = 1u << 6,     // shared-string index out of range / no table
@@ -215,7 +215,12 @@ RFQ_HD XCell xlsx_parse_cell(const uint8_t* doc, uint32_t len, uint32_t cpos, co
       return x;
     }
     case 'e': x.mode = CM_FLOAT; x.bits = 0x7FF8000000000000ull; return x;  // np.nan
-    case 'd': *flags |= XU_DATE; return x;
+    case 'd': {   // ISO 8601 text -> datetime.fromisoformat
+      int64_t ms;
+      if (!parse_iso_datetime(val_b, val_n, &ms)) { *flags |= XU_DATE; return x; }
+      x.mode = CM_DATE; x.bits = (uint64_t)ms;
+      return x;
+    }
     default: *flags |= XU_TYPE; return x;
   }
 }

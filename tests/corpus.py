@@ -512,7 +512,16 @@ def sheet_xml_dates(seed: int):
                              "4000001", "99999999999", "2958464.5"])
         raise ValueError(kind)
 
-    col_kinds = [r.choice(["day", "day", "dayf", "sec", "ms", "time", "early", "edge", "anydate",
+    def iso():
+        y, mo, da = r.randint(1990, 2040), r.randint(1, 12), r.randint(1, 28)
+        form = "bad" if r.random() < 0.004 else r.choice(["d", "d", "T", "T", " ", "hm", "ms", "us0"])
+        base = "%04d-%02d-%02d" % (y, mo, da)
+        hms = "%02d:%02d:%02d" % (r.randint(0, 23), r.randint(0, 59), r.randint(0, 59))
+        return {"d": base, "T": base + "T" + hms, " ": base + " " + hms, "hm": base + "T" + hms[:5],
+                "ms": base + "T" + hms + ".%03d" % r.randint(0, 999), "us0": base + "T" + hms + ".250000",
+                "bad": base + "T" + hms + "Z"}[form]
+
+    col_kinds = [r.choice(["day", "day", "dayf", "sec", "ms", "time", "early", "edge", "anydate", "iso",
                            "date+blank", "date+str", "date+num", "int", "price", "sst"])
                  for _ in range(ncols)]
     use_td = r.random() < 0.04
@@ -538,6 +547,8 @@ def sheet_xml_dates(seed: int):
                 out.append('<c r="%s" s="2"><v>%s</v></c>' % (ref, repr(r.randint(1, 10 ** 6) / 100)))
             elif k == "sst":
                 out.append('<c r="%s" t="s"><v>%d</v></c>' % (ref, sid(r.choice(["RJF544", "tbd", "NA", "asap"]))))
+            elif k == "iso":
+                out.append('<c r="%s" t="d"><v>%s</v></c>' % (ref, iso()))
             else:
                 if k == "anydate":
                     kk = r.choice(["day", "dayf", "sec", "ms", "time", "early", "edge"])
