@@ -182,6 +182,8 @@ class Engine:
 
     # -- file hashes (app/file_parser.py:122-130), one batch
     def md5_many(self, docs: Sequence[bytes]) -> "list[str]":
+        if not docs:
+            return []
         with self.lock:
             a, off, ln = self._pack(docs)
             self._check(self.lib.rfq_stage(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data, len(docs)),
@@ -196,6 +198,8 @@ class Engine:
         """kinds[i]: 0 = int(v.replace(',', '')), 1 = float(v.replace(',', '')).  Returns (raw 8-byte
         values as uint64, status)."""
         kinds = np.ascontiguousarray(kinds, dtype=np.uint8)
+        if not len(fields):
+            return np.zeros(0, np.uint64), np.zeros(0, np.int32)
         with self.lock:
             a, off, ln = self._pack(fields)
             self._check(self.lib.rfq_stage(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data, len(fields)),
