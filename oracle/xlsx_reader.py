@@ -20,7 +20,13 @@ and (installed pandas 3.0.2, read directly):
   pandas/io/excel/_openpyxl.py:596-646   _convert_cell, get_sheet_data
   pandas/io/excel/_base.py:636-697,700-937  _calc_rows, parse, _parse_sheet
 
-Pinned by the golden vectors of `.cache/42/cache.db` rows 12 and 14 (tests/golden/).
+Pinned by the golden vectors of `.cache/42/cache.db` rows 12 and 14 (tests/golden/): shared
+strings, numeric / string cells, row gaps, header inference, float formatting.  PARITY UNPINNED for
+what those two sheets do not contain: date-styled numbers and t="d" cells (from_excel /
+fromisoformat, checked only on Excel-calendar known answers in tests/test_hostcore.py), rows or
+cells without r=, inline strings, boolean / error cells — there the restatement of openpyxl's
+published code is the only reference available in this container.
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may import this module.
 """
 from __future__ import annotations
 
