@@ -252,25 +252,36 @@ class Engine:
 
     # -- sheets
     def sheets_batch(self, docs: Sequence[bytes], kind, sst_of, max_rows=1000, date_ids=None) -> BatchResult:
-        """docs: worksheet XML parts (kind 0) and sharedStrings parts (kind 1); sst_of[d] = index of
-        the sharedStrings part of sheet d or -1; date_ids[d] = iterable of date style ids."""
-        n = len(docs)
+        """docs: worksheet XML parts (kind 0, or 2 = workbook with the 1904 epoch) and sharedStrings
+        parts (kind 1); sst_of[d] = index of the sharedStrings part of sheet d or -1; date_ids[d] =
+        iterable of date style ids (bit 31 = a timedelta format)."""
+        with self.lock:
+            a, off, ln = self._pack(docs)
+            return self._sheets(a, off, ln, kind, sst_of, max_rows, date_ids)
+
+    def sheets_parse_arena(self, arena: PinnedArena, offsets, lengths, kind, sst_of, max_rows=1000,
+                           date_ids=None) -> BatchResult:
+        """sheets_batch over parts the caller already packed into a pinned arena (no host copy)."""
+        with self.lock:
+            return self._sheets(arena, offsets, lengths, kind, sst_of, max_rows, date_ids)
+
+    def _sheets(self, a, off, ln, kind, sst_of, max_rows, date_ids) -> BatchResult:
+        n = len(off)
         kind = np.ascontiguousarray(kind, dtype=np.uint8)
         sst_of = np.ascontiguousarray(sst_of, dtype=np.int32)
         mr = self._mr(n, max_rows)
         doff = np.zeros(n + 1, dtype=np.uint32)
         flat = []
-        for d in range(n):
-            ids = sorted(date_ids[d]) if date_ids is not None and date_ids[d] else []
-            flat.extend(ids)
-            doff[d + 1] = len(flat)
+        if date_ids is not None:
+            for d in range(n):
+                if date_ids[d]:
+                    flat.extend(sorted(date_ids[d]))
+                doff[d + 1] = len(flat)
         dids = np.asarray(flat if flat else [0], dtype=np.uint32)
-        with self.lock:
-            a, off, ln = self._pack(docs)
-            self._check(self.lib.rfq_sheets_parse(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data, n,
-                                                  kind.ctypes.data, sst_of.ctypes.data, mr.ctypes.data,
-                                                  doff.ctypes.data, dids.ctypes.data), "rfq_sheets_parse")
-            return BatchResult(self)
+        self._check(self.lib.rfq_sheets_parse(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data, n,
+                                              kind.ctypes.data, sst_of.ctypes.data, mr.ctypes.data,
+                                              doff.ctypes.data, dids.ctypes.data), "rfq_sheets_parse")
+        return BatchResult(self)
 
     # -- pre-packed pinned arena (no Python-side copies): what a high-throughput caller uses
     def _mr(self, n, max_rows):
