@@ -53,7 +53,8 @@ __device__ __noinline__ uint32_t emit_cell_cold(CellSrc src, int ct, int kind, i
     return 0;
   }
   uint32_t ncp, nb;
-  printed_size(src, ct, kind, dec, &ncp, &nb);
+  if (kind == PR_STR) { ncp = t.ncp + t.nesc; nb = t.nbytes + t.nesc; }   // the scan above already measured it
+  else printed_size(src, ct, kind, dec, &ncp, &nb);
   uint32_t pad = width - ncp;
   if (fill) for (uint32_t q = 0; q < pad; ++q) field[q] = ' ';
   print_cell(src, ct, kind, dec, field + pad);

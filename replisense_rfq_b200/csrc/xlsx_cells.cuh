@@ -128,19 +128,22 @@ RFQ_HD XCell xlsx_parse_cell(const uint8_t* doc, uint32_t len, uint32_t cpos, co
   if (g >= e) return x;
   const uint8_t* vb; uint32_t vn;
   uint32_t row = 0;
-  if (!xml_attr(p, g, 'r', &vb, &vn) || vn == 0) *flags |= XU_C_NOREF;   // col stays 0: set by position
-  else if (!a1_parse(vb, vn, &x.col, &row)) { *flags |= XU_NO_REF; return x; }
+  XAttrRTS at;
+  xml_attrs_rts(p, g, &at);
+  if (!(at.have & 1u) || at.vn[0] == 0) *flags |= XU_C_NOREF;   // col stays 0: set by position
+  else if (!a1_parse(at.vb[0], at.vn[0], &x.col, &row)) { *flags |= XU_NO_REF; return x; }
   else *flags |= XU_C_HASREF;
   // type
   int ty = 'n';
-  if (xml_attr(p, g, 't', &vb, &vn)) {
+  if (at.have & 2u) {
+    vb = at.vb[1]; vn = at.vn[1];
     if (vn == 1) ty = vb[0];                                   // n s b e d
     else if (vn == 3 && vb[0] == 's' && vb[1] == 't' && vb[2] == 'r') ty = 'S';
     else if (vn == 9 && vb[0] == 'i') ty = 'I';               // inlineStr
     else { *flags |= XU_TYPE; return x; }
   }
   uint32_t style = 0;
-  if (xml_attr(p, g, 's', &vb, &vn)) for (uint32_t i = 0; i < vn; ++i) style = style * 10 + (vb[i] - '0');
+  if (at.have & 4u) for (uint32_t i = 0; i < at.vn[2]; ++i) style = style * 10 + (at.vb[2][i] - '0');
   if (g[-1] == '/') return x;  // <c .../> : no value
   // children until </c>
   const uint8_t* q = g + 1;

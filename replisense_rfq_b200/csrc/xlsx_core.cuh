@@ -109,6 +109,35 @@ RFQ_HD bool xml_attr(const uint8_t* p, const uint8_t* e, char n0, const uint8_t*
   return false;
 }
 
+// the r=, t= and s= attributes of a <c ...> tag in ONE pass over its bytes (first occurrence of each,
+// quoted values skipped): what three xml_attr calls return
+struct XAttrRTS { const uint8_t* vb[3]; uint32_t vn[3]; uint32_t have; };   // index 0 r, 1 t, 2 s
+RFQ_HD void xml_attrs_rts(const uint8_t* p, const uint8_t* e, XAttrRTS* o) {
+  o->have = 0;
+  o->vb[0] = o->vb[1] = o->vb[2] = p; o->vn[0] = o->vn[1] = o->vn[2] = 0;
+  const uint8_t* q = p;
+  while (q + 3 < e) {
+    const uint8_t c = *q;
+    if (c == '"' || c == '\'') {            // a value whose name was not single-letter: skip it
+      ++q;
+      while (q < e && *q != c) ++q;
+      ++q;
+      continue;
+    }
+    if ((c == ' ' || c == '\t' || c == '\n' || c == '\r') && q[2] == '=' && (q[3] == '"' || q[3] == '\'')) {
+      const uint8_t n0 = q[1], quote = q[3];
+      const int k = n0 == 'r' ? 0 : n0 == 't' ? 1 : n0 == 's' ? 2 : -1;
+      const uint8_t* s = q + 4;
+      const uint8_t* t = s;
+      while (t < e && *t != quote) ++t;
+      if (k >= 0 && !((o->have >> k) & 1u)) { o->vb[k] = s; o->vn[k] = (uint32_t)(t - s); o->have |= 1u << k; }
+      q = t + 1;
+      continue;
+    }
+    ++q;
+  }
+}
+
 // "AB12" -> column 28 (1-based), row 12; false if malformed
 RFQ_HD bool a1_parse(const uint8_t* s, uint32_t n, uint32_t* col, uint32_t* row) {
   uint32_t i = 0, c = 0, r = 0;
@@ -166,6 +195,34 @@ RFQ_HD_COLD bool strtod_exact(const uint8_t* s, uint32_t n, double* out) {
   if (w < (1ull << 53) && !truncated && e10 >= -22 && e10 <= 22) {
     z = (double)w;
     z = e10 >= 0 ? RFQ_DMUL(z, RFQ_POW10(e10)) : RFQ_DDIV(z, RFQ_POW10(-e10));
+    *out = neg ? -z : z;
+    return true;
+  }
+  if (!truncated && e10 < 0 && e10 >= -19) {
+    // up to 19 digits over a power of ten that fits 64 bits (the 16-17 digit literals writers emit):
+    // correctly rounded quotient with one 128-bit division instead of the big-integer path
+    uint64_t D = 1;
+    for (long long q = 0; q < -e10; ++q) D *= 10ull;
+    int bw = 0, bd = 0;
+    for (uint64_t t = w; t; t >>= 1) ++bw;
+    for (uint64_t t = D; t; t >>= 1) ++bd;
+    int sft = 56 + bd - bw;                    // quotient gets 56..57 significant bits
+    if (sft < 0) sft = 0;
+    unsigned __int128 N = (unsigned __int128)w << sft;
+    uint64_t q = (uint64_t)(N / D);
+    bool sticky = (N % D) != 0;
+    int nb = 0;
+    for (uint64_t t = q; t; t >>= 1) ++nb;
+    int drop = nb - 53;                        // >= 3 whenever bits were shifted in
+    uint64_t mant = q;
+    if (drop > 0) {
+      uint64_t rem = q & ((1ull << drop) - 1ull), half = 1ull << (drop - 1);
+      mant = q >> drop;
+      if (rem > half || (rem == half && (sticky || (mant & 1ull)))) ++mant;
+    } else {
+      drop = 0;                                // short exact quotient (sticky implies nb >= 56, so not here)
+    }
+    z = ldexp((double)mant, drop - sft);       // mant <= 2^53: exact; exponent far inside the normal range
     *out = neg ? -z : z;
     return true;
   }

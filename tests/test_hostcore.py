@@ -284,6 +284,13 @@ def test_strtod_exact_matches_python_float():
             toks.append("%d.%d" % (r.randint(0, 10 ** r.randint(1, 18)), r.randint(0, 10 ** r.randint(1, 18))))
         else:
             toks.append("%.17g" % (r.uniform(-1, 1) * 10 ** r.randint(-30, 30)))
+    for _ in range(30000):   # 15-19 digit literals over 10^1..10^19: the single-division path
+        nd, k = r.randint(1, 19), r.randint(1, 19)
+        digits = str(r.randint(10 ** (nd - 1), 10 ** nd - 1)).rjust(k + 1, "0")
+        toks.append(digits[:-k] + "." + digits[-k:])
+    toks += ["0.5", "0.25", "1.0000000000000002", "1.00000000000000011102230246251565", "9007199254740992.5",
+             "9007199254740993.5", "0.0000000000000000001", "9999999999999999999.9"[:20], "4503599627370496.5",
+             "4503599627370497.5", "2251799813685248.25", "0.1000000000000000055511151231257827"]
     for t in toks:
         if "nan" in t or "inf" in t:
             continue
