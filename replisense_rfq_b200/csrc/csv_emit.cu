@@ -129,14 +129,32 @@ __device__ __forceinline__ uint32_t emit_cell(const CellSrc& src, int ct, int ki
                                               uint32_t width, uint8_t* field, bool fill) {
   const bool absent = src.missing || src.mode == CM_NULL;
   const bool text = cell_is_text(src);
-  if (!absent && text && !src.clean && !(src.mode == CM_CSVQ && kind == PR_STR))
+  // a plain span that is not clean ASCII (a shared string with accents, say) printed as text: count
+  // its continuation bytes and look for \t \n \r eight bytes at a time; without those three it is
+  // copied as it stands (UTF-8 validity was settled by the typing sweep)
+  uint32_t cont = 0;
+  bool raw_text = false;
+  if (!absent && src.mode == CM_RAW && !src.clean && kind == PR_STR) {
+    const uint64_t ones = 0x0101010101010101ull, highs = 0x8080808080808080ull;
+    uint64_t esc = 0;
+    for (uint32_t i = 0; i < src.n; i += 8) {
+      uint64_t x = load8_masked(src.p + i, src.n - i);
+      cont += (uint32_t)__popcll(x & ~(x << 1) & highs);              // 10xxxxxx
+      uint64_t a = x ^ (ones * 0x09), b = x ^ (ones * 0x0A), c = x ^ (ones * 0x0D);
+      uint64_t z = ((a - ones) & ~a) | ((b - ones) & ~b) | ((c - ones) & ~c);
+      if (src.n - i < 8) z &= (1ull << (8 * (src.n - i))) - 1ull;      // the zero padding is not a tab
+      esc |= z & highs;
+    }
+    raw_text = esc == 0;
+  }
+  if (!absent && text && !src.clean && !raw_text && !(src.mode == CM_CSVQ && kind == PR_STR))
     return emit_cell_cold(src, ct, kind, dec, width, field, fill);
-  // what is left: absent, typed value, clean token, ""-pair text printed as text
+  // what is left: absent, typed value, clean token, plain or ""-pair text printed as text
   uint32_t nbytes = 0;
   uint64_t first8 = 0;
   bool na = absent;
   if (!absent && text) {
-    if (src.clean) { nbytes = src.n; first8 = src.n ? load8_masked(src.p, src.n) : 0; }
+    if (src.clean || raw_text) { nbytes = src.n; first8 = src.n ? load8_masked(src.p, src.n) : 0; }
     else {
       nbytes = (uint32_t)src.bits;
       if (nbytes <= 8) {   // only short tokens can be NA words
@@ -153,11 +171,11 @@ __device__ __forceinline__ uint32_t emit_cell(const CellSrc& src, int ct, int ki
     put_nat(kind, width, field);
     return 0;
   }
-  if (kind == PR_STR && text) {   // clean ASCII: bytes == code points, nothing to escape
-    uint32_t pad = width - nbytes;
+  if (kind == PR_STR && text) {   // nothing to escape; code points = bytes - continuation bytes
+    uint32_t pad = width - (nbytes - cont);
     if (fill) for (uint32_t q = 0; q < pad; ++q) field[q] = ' ';
     uint8_t* o = field + pad;
-    if (src.clean) {
+    if (src.clean || raw_text) {
       for (uint32_t i = 0; i < src.n; i += 8) {
         uint64_t x = load8_masked(src.p + i, src.n - i);
         uint32_t m = src.n - i < 8 ? src.n - i : 8;
@@ -168,7 +186,7 @@ __device__ __forceinline__ uint32_t emit_cell(const CellSrc& src, int ct, int ki
       int c;
       while ((c = it.next()) >= 0) *o++ = (uint8_t)c;
     }
-    return 0;
+    return cont;
   }
   uint8_t buf[40];
   int n = (kind == PR_STR) ? -1 : format_number(src, ct, kind, dec, nbytes, first8, buf);
