@@ -215,6 +215,7 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
     ta.cand = c->pool.alloc<ChunkCand>(n_stat + 1);
     ta.chunk_dropped = c->pool.alloc<uint32_t>(n_stat + 1);
     ta.doc_exact = c->pool.alloc<uint32_t>(m + 2);
+    ta.cell_tag = c->pool.alloc<uint8_t>((size_t)NF + 16);
     uint32_t mw = 1;
     for (uint32_t i = 0; i < m; ++i) mw = std::max(mw, td[i].W);
     ta.max_w = mw;

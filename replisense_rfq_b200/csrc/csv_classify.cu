@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(256) csv_classify_fused_kernel(TableArgs a) {
       const RowCur rc = row_open(a, slot);
       uint32_t na = 0, extra = 0;
       for (uint32_t c = grp; c < W; c += ngrp) {
-        CellCand m = classify_measure_cell(row_cell(a, D, rc, c));
+        CellCand m = classify_measure_cell(row_cell_tag_write(a, D, rc, c));
         const uint32_t f = m.flags;
         if ((s_flags[c] & f) != f) atomicOr(&s_flags[c], f);
         if (m.int_status != INT_OK) {

@@ -261,7 +261,7 @@ __global__ void __launch_bounds__(256) csv_emit_kernel(TableArgs a, uint8_t* __r
           uint32_t j = c - D.lead;
           ColOut co = col[D.col_base + j];
           int ct = ctrow[c];
-          CellSrc src = row_cell(a, D, rc, c);
+          CellSrc src = row_cell_tag_read(a, D, rc, c);
           if (ct == CT_XOBJ) ct = cell_own_ctype(src);
           int kind = print_kind(co.cls, ct, co.sci != 0);
           if (ngrp > 1 && j && extra)   // columns are split over groups: recompute the shift

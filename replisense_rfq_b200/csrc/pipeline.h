@@ -162,6 +162,7 @@ struct TableArgs {
   uint32_t* chunk_dropped;        // [n_stat] (entry of column 0 of each chunk): rows dropna removes
   uint32_t* doc_exact;            // [n_docs] 1 = a chunk type the candidates do not cover: exact sweep
   uint32_t max_w;                 // widest table of the batch (shared-memory size of the fused sweep)
+  uint8_t* cell_tag;              // [n_fields] how the fused sweep found each field (table_common.cuh), nullptr = none
 };
 
 struct ColOut { int32_t cls, dec, sci; uint32_t width, cp_off; };

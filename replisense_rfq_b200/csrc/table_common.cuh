@@ -63,6 +63,42 @@ __device__ __forceinline__ CellSrc row_cell(const TableArgs& a, const TDoc& D, c
   return s;
 }
 
+// The fused sweep already ran csv_simplify on every field; it leaves the verdict in one byte per
+// field (index = position in `fend`) so that emit does not scan the bytes a second time:
+//   bits 0-1: 0 = needs the quote state machine (CM_CSV as found), 1 = clean unquoted span,
+//             2 = "..." around a clean span, 3 = "..." whose only quotes are "" pairs
+//   bits 2-7: number of "" pairs (kind 3; 63 or more pairs are filed under kind 0)
+__device__ __forceinline__ CellSrc row_cell_tag_write(const TableArgs& a, const TDoc& D, const RowCur& r, uint32_t c) {
+  CellSrc s = row_cell(a, D, r, c);
+  if (a.cell_tag && !a.xcells && !s.missing) {
+    uint32_t n0 = __ldg(a.fend + r.fbeg + c) - (c == 0 ? r.start0 : __ldg(a.fend + r.fbeg + c - 1) + 1);
+    uint32_t tag = 0;
+    if (s.mode == CM_RAW && s.clean) tag = s.n == n0 ? 1u : 2u;
+    else if (s.mode == CM_CSVQ) {
+      uint32_t pairs = s.n - (uint32_t)s.bits;
+      if (pairs < 63u) tag = 3u | (pairs << 2);
+      else { s.mode = CM_CSV; s.p -= 1; s.n += 2; s.bits = 0; }   // keep both sweeps on the same path
+    }
+    a.cell_tag[r.fbeg + c] = (uint8_t)tag;
+  }
+  return s;
+}
+__device__ __forceinline__ CellSrc row_cell_tag_read(const TableArgs& a, const TDoc& D, const RowCur& r, uint32_t c) {
+  if (!a.cell_tag || a.xcells) return row_cell(a, D, r, c);
+  CellSrc s;
+  s.mode = CM_CSV; s.missing = false; s.clean = false; s.p = a.arena; s.n = 0; s.bits = 0;
+  if (c >= r.nf) { s.missing = true; return s; }
+  uint32_t st = c == 0 ? r.start0 : __ldg(a.fend + r.fbeg + c - 1) + 1;
+  uint32_t en = __ldg(a.fend + r.fbeg + c);
+  const uint32_t tag = a.cell_tag[r.fbeg + c], kind = tag & 3u;
+  s.p = a.arena + D.off + st;
+  s.n = en - st;
+  if (kind == 1u) { s.mode = CM_RAW; s.clean = true; }
+  else if (kind == 2u) { s.p += 1; s.n -= 2; s.mode = CM_RAW; s.clean = true; }
+  else if (kind == 3u) { s.p += 1; s.n -= 2; s.mode = CM_CSVQ; s.bits = s.n - (tag >> 2); }
+  return s;
+}
+
 struct ItemCtx {
   uint32_t d, row0, nrows, chunk;
 };
