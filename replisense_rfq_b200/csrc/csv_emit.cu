@@ -176,9 +176,17 @@ __device__ __forceinline__ uint32_t emit_cell(const CellSrc& src, int ct, int ki
     if (fill) for (uint32_t q = 0; q < pad; ++q) field[q] = ' ';
     uint8_t* o = field + pad;
     if (src.clean || raw_text) {
-      for (uint32_t i = 0; i < src.n; i += 8) {
-        uint64_t x = load8_masked(src.p + i, src.n - i);
-        uint32_t m = src.n - i < 8 ? src.n - i : 8;
+      uint32_t i = 0;
+      for (; i + 8 <= src.n; i += 8) {          // whole windows: eight stores, no inner loop
+        const uint64_t x = load8_masked(src.p + i, 8);
+        const uint32_t lo = (uint32_t)x, hi = (uint32_t)(x >> 32);
+        uint8_t* d = o + i;
+        d[0] = (uint8_t)lo; d[1] = (uint8_t)(lo >> 8); d[2] = (uint8_t)(lo >> 16); d[3] = (uint8_t)(lo >> 24);
+        d[4] = (uint8_t)hi; d[5] = (uint8_t)(hi >> 8); d[6] = (uint8_t)(hi >> 16); d[7] = (uint8_t)(hi >> 24);
+      }
+      if (i < src.n) {
+        const uint64_t x = load8_masked(src.p + i, src.n - i);
+        const uint32_t m = src.n - i;
         for (uint32_t q = 0; q < m; ++q) o[i + q] = (uint8_t)(x >> (8 * q));
       }
     } else {
