@@ -8,6 +8,7 @@
 // and tiles never span documents; the end of each document is a virtual LF.
 // HBM-bound byte work (the input is read three times, from L2 when it fits): no tensor cores.
 #include <cuda_runtime.h>
+#include <algorithm>
 #include "csv_dfa.cuh"
 #include "launch.h"
 #include "pipeline.h"
@@ -115,9 +116,9 @@ __global__ void __launch_bounds__(256) csv_tilefn_kernel(ScanArgs a) {
   __shared__ uint32_t pair_fn[128];
   if (threadIdx.x < 128) pair_fn[threadIdx.x] = fn_compose(class_fn[threadIdx.x & 7u], class_fn[(threadIdx.x >> 4) & 7u]);
   __syncthreads();
-  uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
-  int lane = threadIdx.x & 31;
-  if (t >= a.n_tiles) return;
+  const int lane = threadIdx.x & 31;
+  // a CTA keeps its tables and walks tiles grid-stride (8 tiles per round, one per warp)
+  for (uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5); t < a.n_tiles; t += gridDim.x * 8) {
   uint32_t d = scan_find_doc(a.tile_base, a.n_docs, t);
   uint32_t tile = t - a.tile_base[d];
   uint32_t len = a.doc_len[d];
@@ -133,6 +134,7 @@ __global__ void __launch_bounds__(256) csv_tilefn_kernel(ScanArgs a) {
     if ((lane & (2 * o - 1)) == 0) f = fn_compose(f, g);
   }
   if (lane == 0) a.tile_fn[t] = tile == 0 ? fn_const(fn_apply(f, ST_R)) : f;
+  }
 }
 
 // walk 16 bytes from a known state; calls ev(k, events, state_before) for bytes with events
@@ -170,9 +172,9 @@ __global__ void __launch_bounds__(256) csv_count_kernel(ScanArgs a) {
     pair_walk[threadIdx.x] = w;
   }
   __syncthreads();
-  uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
-  int lane = threadIdx.x & 31;
-  if (t >= a.n_tiles) return;
+  const int lane = threadIdx.x & 31;
+  // a CTA keeps its tables and walks tiles grid-stride (8 tiles per round, one per warp)
+  for (uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5); t < a.n_tiles; t += gridDim.x * 8) {
   uint32_t d = scan_find_doc(a.tile_base, a.n_docs, t);
   uint32_t tile = t - a.tile_base[d];
   uint32_t len = a.doc_len[d];
@@ -224,14 +226,15 @@ __global__ void __launch_bounds__(256) csv_count_kernel(ScanArgs a) {
   }
   if (lane == 0) { a.tile_nf[t] = nf; a.tile_nl[t] = nl; }
   if (final_state >= 0) a.doc_final[d] = (uint32_t)final_state;
+  }
 }
 
 // ---- pass 3: write field ends / record ends / record starts -----------------------------------
 __global__ void __launch_bounds__(256) csv_index_kernel(ScanArgs a) {
   RFQ_INIT_CLASS_FN();
-  uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
-  int lane = threadIdx.x & 31;
-  if (t >= a.n_tiles) return;
+  const int lane = threadIdx.x & 31;
+  // a CTA keeps its tables and walks tiles grid-stride (8 tiles per round, one per warp)
+  for (uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5); t < a.n_tiles; t += gridDim.x * 8) {
   uint32_t d = scan_find_doc(a.tile_base, a.n_docs, t);
   uint32_t tile = t - a.tile_base[d];
   uint32_t len = a.doc_len[d];
@@ -270,6 +273,7 @@ __global__ void __launch_bounds__(256) csv_index_kernel(ScanArgs a) {
     if (e & EV_FIELD_END) a.fend[g++] = pos;
     if (e & EV_LINE_END) a.rec_fend[r++] = g;
   });
+  }
 }
 
 // ---- record shapes per document ---------------------------------------------------------------
@@ -308,9 +312,17 @@ __global__ void __launch_bounds__(256) csv_shape_kernel(ScanArgs a, const uint32
 }
 
 // ---------------------------------------------------------------------------------------------
+// resident CTAs of the scan kernels: 8 per SM
+static uint32_t scan_grid() {
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  return (uint32_t)sms * 8u;
+}
+
 void csv_scan_count(const ScanArgs& a, cudaStream_t s) {
   if (a.n_tiles == 0) return;
-  uint32_t nb = (a.n_tiles + 7) / 8;
+  uint32_t nb = std::min<uint32_t>((a.n_tiles + 7) / 8, scan_grid());
   prof_mark("csv_tilefn_kernel", s);
   RFQ_LAUNCH(csv_tilefn_kernel, nb, 256, 0, s, a);
   prof_mark("scan(tile_fn)", s);
@@ -328,7 +340,7 @@ void csv_scan_count(const ScanArgs& a, cudaStream_t s) {
 void csv_scan_index(const ScanArgs& a, cudaStream_t s) {
   if (a.n_tiles == 0) return;
   prof_mark("csv_index_kernel", s);
-  RFQ_LAUNCH(csv_index_kernel, (a.n_tiles + 7) / 8, 256, 0, s, a);
+  RFQ_LAUNCH(csv_index_kernel, (a.n_tiles + 7) / 8, 256, 0, s, a);   // no tables worth keeping: one round per CTA
 }
 
 void csv_doc_shape(const ScanArgs& a, const uint32_t* max_rows32, DocShape* shape, uint32_t n_slots,
