@@ -68,28 +68,53 @@ __device__ __forceinline__ void txt_lane_eval(const uint8_t* __restrict__ doc, u
   }
   win.w[0] = prev; win.w[1] = v.x; win.w[2] = v.y; win.w[3] = v.z; win.w[4] = v.w;
   win.w[5] = next;
-  emit = 0; nsp = 0;
+  // ASCII bytes are decided by 4-wide compares on the whole vector: a byte is emitted unless it is
+  // the LF of a CR LF, and it starts visible text unless it is one of str.isspace()'s ASCII members
+  // (\t-\r, \x1c-\x20).  Only non-ASCII CHARACTERS are walked, once each (their continuation bytes
+  // are settled with the lead byte; a continuation byte whose lead sits in the previous lane looks
+  // back through the halo).
+  const uint32_t ww[4] = {v.x, v.y, v.z, v.w};
+  uint32_t lf = 0, cr = 0, sp = 0, hi = 0;
 #pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    if (base + k >= len) break;
-    uint32_t b = win(k);
-    bool e;
-    if (b < 0x80u) {
-      e = true;
-      if (b == '\n') {
-        uint32_t pb = win(k - 1);
-        if (pb == '\r') e = false;
-        else if (pb >= 0x80u) {  // rare: dropped bytes between CR and LF
-          GlobalAcc g{doc, (int64_t)len};
-          e = !u8_lf_swallowed(g, base + k);
-        }
-      }
-      if (e && !u8_is_space_at(win, k)) nsp |= 1u << k;
-    } else {
-      e = u8_keep(win, k);
-      if (e && !u8_is_cont(b) && !u8_is_space_at(win, k)) nsp |= 1u << k;
+  for (int q = 0; q < 4; ++q) {
+    const uint32_t w = ww[q];
+    uint32_t mlf = __vcmpeq4(w, 0x0A0A0A0Au), mcr = __vcmpeq4(w, 0x0D0D0D0Du);
+    uint32_t msp = (__vcmpgeu4(w, 0x09090909u) & __vcmpleu4(w, 0x0D0D0D0Du)) |
+                   (__vcmpgeu4(w, 0x1C1C1C1Cu) & __vcmpleu4(w, 0x20202020u));
+    uint32_t mhi = __vcmpgeu4(w, 0x80808080u);
+    lf |= (((mlf & 0x08040201u) * 0x01010101u) >> 24) << (4 * q);
+    cr |= (((mcr & 0x08040201u) * 0x01010101u) >> 24) << (4 * q);
+    sp |= (((msp & 0x08040201u) * 0x01010101u) >> 24) << (4 * q);
+    hi |= (((mhi & 0x08040201u) * 0x01010101u) >> 24) << (4 * q);
+  }
+  const int64_t left = (int64_t)len - base;
+  const uint32_t valid = left >= 16 ? 0xFFFFu : left > 0 ? ((1u << left) - 1u) : 0u;
+  const uint32_t pb = prev >> 24;
+  const uint32_t after_cr = ((cr << 1) | (pb == '\r' ? 1u : 0u)) & 0xFFFFu;
+  const uint32_t after_hi = ((hi << 1) | (pb >= 0x80u ? 1u : 0u)) & 0xFFFFu;
+  uint32_t swallowed = lf & ~after_hi & after_cr;
+  for (uint32_t m = lf & after_hi & valid; m; m &= m - 1) {   // rare: dropped bytes may hide a CR
+    const int k = __ffs(m) - 1;
+    GlobalAcc g{doc, (int64_t)len};
+    if (u8_lf_swallowed(g, base + k)) swallowed |= 1u << k;
+  }
+  emit = valid & ~hi & ~swallowed;
+  nsp = emit & ~sp;
+  for (uint32_t m = hi & valid; m;) {
+    const int k = __ffs(m) - 1;
+    m &= m - 1;
+    const uint32_t b = win(k);
+    if (u8_is_cont(b)) {              // only reached when no valid lead in this lane covers it
+      if (k < 3 && u8_keep(win, k)) emit |= 1u << k;
+      continue;
     }
-    if (e) emit |= 1u << k;
+    const int n = u8_lead_len(b);
+    if (n && u8_seq_valid(win, k)) {
+      const uint32_t span = (((1u << n) - 1u) << k) & 0xFFFFu;
+      emit |= span;
+      m &= ~span;
+      if (!u8_is_space_at(win, k)) nsp |= 1u << k;
+    }
   }
 }
 
