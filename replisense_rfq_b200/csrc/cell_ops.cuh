@@ -57,14 +57,15 @@ RFQ_HD uint64_t load8_masked(const uint8_t* p, uint32_t rem) {
   return x;
 }
 
-// true iff every one of the n bytes at p is ASCII >= 0x0E and none equals `forbid`
-RFQ_HD bool span_is_clean(const uint8_t* p, uint32_t n, uint32_t forbid) {
+// true iff every one of the n bytes at p is >= 0x0E, none equals `forbid`, and (unless allow_high)
+// all are ASCII
+RFQ_HD bool span_is_clean(const uint8_t* p, uint32_t n, uint32_t forbid, bool allow_high = false) {
   const uint64_t ones = 0x0101010101010101ull, highs = 0x8080808080808080ull;
   for (uint32_t i = 0; i < n; i += 8) {
     uint32_t rem = n - i;
     uint64_t x = load8_masked(p + i, rem);
     if (rem < 8) x |= 0x2020202020202020ull & ~((1ull << (8 * rem)) - 1ull);  // padding = blanks
-    uint64_t bad = x & highs;                              // non-ASCII
+    uint64_t bad = allow_high ? 0ull : (x & highs);        // non-ASCII
     bad |= (x - ones * 0x0E) & ~x & highs;                 // a byte < 0x0E (NUL, \t, \n, \r, ...)
     uint64_t y = x ^ (ones * forbid);
     bad |= (y - ones) & ~y & highs;                        // a byte == forbid
@@ -81,11 +82,16 @@ RFQ_HD void csv_simplify(CellSrc& s) {
   if (s.n == 0) { s.mode = CM_RAW; s.clean = true; return; }
   if (s.p[0] != '"') {
     if (span_is_clean(s.p, s.n, 0xFF)) { s.mode = CM_RAW; s.clean = true; }
+    // accents, currency signs ...: still a plain span when no quote and no control byte is inside
+    else if (span_is_clean(s.p, s.n, '"', true)) s.mode = CM_RAW;
     return;
   }
   if (s.n < 2 || s.p[s.n - 1] != '"') return;
   if (span_is_clean(s.p + 1, s.n - 2, '"')) { s.p += 1; s.n -= 2; s.mode = CM_RAW; s.clean = true; return; }
-  if (!span_is_clean(s.p + 1, s.n - 2, 0xFF)) return;
+  if (!span_is_clean(s.p + 1, s.n - 2, 0xFF)) {
+    if (span_is_clean(s.p + 1, s.n - 2, '"', true)) { s.p += 1; s.n -= 2; s.mode = CM_RAW; }   // "..." around plain non-ASCII text
+    return;
+  }
   // clean ASCII with quotes inside: fine iff they all come as "" pairs
   uint32_t pairs = 0;
   const uint64_t ones = 0x0101010101010101ull, highs = 0x8080808080808080ull;

@@ -65,18 +65,19 @@ __device__ __forceinline__ CellSrc row_cell(const TableArgs& a, const TDoc& D, c
 
 // The fused sweep already ran csv_simplify on every field; it leaves the verdict in one byte per
 // field (index = position in `fend`) so that emit does not scan the bytes a second time:
-//   bits 0-1: 0 = needs the quote state machine (CM_CSV as found), 1 = clean unquoted span,
-//             2 = "..." around a clean span, 3 = "..." whose only quotes are "" pairs
-//   bits 2-7: number of "" pairs (kind 3; 63 or more pairs are filed under kind 0)
+//   bits 0-2: 0 = needs the quote state machine (CM_CSV as found), 1 = clean ASCII unquoted span,
+//             2 = "..." around a clean ASCII span, 3 = "..." whose only quotes are "" pairs,
+//             4 = plain unquoted span with non-ASCII bytes, 5 = "..." around such a span
+//   bits 3-7: number of "" pairs (kind 3; 31 or more pairs are filed under kind 0)
 __device__ __forceinline__ CellSrc row_cell_tag_write(const TableArgs& a, const TDoc& D, const RowCur& r, uint32_t c) {
   CellSrc s = row_cell(a, D, r, c);
   if (a.cell_tag && !a.xcells && !s.missing) {
     uint32_t n0 = __ldg(a.fend + r.fbeg + c) - (c == 0 ? r.start0 : __ldg(a.fend + r.fbeg + c - 1) + 1);
     uint32_t tag = 0;
-    if (s.mode == CM_RAW && s.clean) tag = s.n == n0 ? 1u : 2u;
+    if (s.mode == CM_RAW) tag = (s.clean ? 1u : 4u) + (s.n == n0 ? 0u : 1u);
     else if (s.mode == CM_CSVQ) {
       uint32_t pairs = s.n - (uint32_t)s.bits;
-      if (pairs < 63u) tag = 3u | (pairs << 2);
+      if (pairs < 31u) tag = 3u | (pairs << 3);
       else { s.mode = CM_CSV; s.p -= 1; s.n += 2; s.bits = 0; }   // keep both sweeps on the same path
     }
     a.cell_tag[r.fbeg + c] = (uint8_t)tag;
@@ -90,12 +91,13 @@ __device__ __forceinline__ CellSrc row_cell_tag_read(const TableArgs& a, const T
   if (c >= r.nf) { s.missing = true; return s; }
   uint32_t st = c == 0 ? r.start0 : __ldg(a.fend + r.fbeg + c - 1) + 1;
   uint32_t en = __ldg(a.fend + r.fbeg + c);
-  const uint32_t tag = a.cell_tag[r.fbeg + c], kind = tag & 3u;
+  const uint32_t tag = a.cell_tag[r.fbeg + c], kind = tag & 7u;
   s.p = a.arena + D.off + st;
   s.n = en - st;
-  if (kind == 1u) { s.mode = CM_RAW; s.clean = true; }
-  else if (kind == 2u) { s.p += 1; s.n -= 2; s.mode = CM_RAW; s.clean = true; }
-  else if (kind == 3u) { s.p += 1; s.n -= 2; s.mode = CM_CSVQ; s.bits = s.n - (tag >> 2); }
+  if (kind == 2u || kind == 3u || kind == 5u) { s.p += 1; s.n -= 2; }   // inside the quotes
+  if (kind == 1u || kind == 2u) { s.mode = CM_RAW; s.clean = true; }
+  else if (kind == 4u || kind == 5u) s.mode = CM_RAW;
+  else if (kind == 3u) { s.mode = CM_CSVQ; s.bits = s.n - (tag >> 3); }
   return s;
 }
 
