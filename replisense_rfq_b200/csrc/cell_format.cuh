@@ -186,6 +186,34 @@ RFQ_HD Fixed6 fixed6(double v) {
   return f;
 }
 
+// Short decimal literal  [+-] d{1,8} . d{1,6}  (a price): its "%.6f" digits are the literal's own
+// digits padded with zeros.  The double the parser makes of it is within a few ulp (< 5e-8 below
+// 1e8) of the literal, and the nearest rounding boundary of the sixth decimal is 5e-7 away, so the
+// correctly rounded "%.6f" of that double cannot print anything else: no 128-bit arithmetic and no
+// double needed.  Literals below 1e-5 are left to the general path (their |v| < 1e-6 test is made
+// on the parsed double).
+RFQ_HD bool decimal_literal(const uint8_t* p, uint32_t n, Fixed6* f) {
+  if (n < 3 || n > 16) return false;
+  uint32_t i = 0;
+  f->neg = false;
+  if (p[0] == '-' || p[0] == '+') { f->neg = p[0] == '-'; i = 1; }
+  uint64_t ip = 0; uint32_t nd = 0;
+  for (; i < n && (uint32_t)(p[i] - '0') < 10u; ++i) { ip = ip * 10u + (uint32_t)(p[i] - '0'); ++nd; }
+  if (nd == 0 || nd > 8 || i >= n || p[i] != '.') return false;
+  ++i;
+  uint32_t fr = 0, nf = 0;
+  for (; i < n && (uint32_t)(p[i] - '0') < 10u; ++i) { fr = fr * 10u + (uint32_t)(p[i] - '0'); ++nf; }
+  if (nf == 0 || nf > 6 || i != n) return false;
+  for (uint32_t q = nf; q < 6; ++q) fr *= 10u;
+  if (ip == 0 && fr < 10u) return false;
+  f->inf = false; f->big = false; f->ip = ip; f->frac = fr;
+  f->ip_digits = ndigits_u64(ip);
+  int tz = 0;
+  if (fr == 0) tz = 6; else { uint32_t t = fr; while (t % 10u == 0) { t /= 10u; ++tz; } }
+  f->tz = tz;
+  return true;
+}
+
 // length of "{:.6f}" cut to `dec` decimals (dec in 1..6); inf -> "inf"/"-inf"
 RFQ_HD int fixed_len(const Fixed6& f, int dec) {
   if (f.inf) return 3 + f.neg;

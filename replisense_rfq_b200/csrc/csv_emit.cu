@@ -109,6 +109,11 @@ __device__ __forceinline__ int format_number(const CellSrc& s, int ct, int kind,
       return n;
     }
     case PR_FIXED: case PR_OBJFLOAT: {
+      if (s.mode == CM_RAW && s.clean) {   // a short decimal literal prints its own digits (cell_format.cuh)
+        Fixed6 d6;
+        if (decimal_literal(s.p, s.n, &d6))
+          return fixed_write(d6, 0., kind == PR_FIXED ? dec : objfloat_dec(d6), kind == PR_OBJFLOAT, buf);
+      }
       double v = fast_f64(s, ct);
       Fixed6 f = fixed6(v);
       if (f.big) return -1;

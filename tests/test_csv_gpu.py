@@ -170,3 +170,27 @@ def test_engine_pool_concurrent_calls_keep_their_results():
     with ThreadPoolExecutor(8) as tp:
         got = list(tp.map(lambda d: fp.parse_many([d], ["csv"])[0], docs))
     assert [None if isinstance(g, Exception) else g for g in got] == want
+
+
+def test_csv_decimal_literals(eng):
+    """Short decimal literals (prices) take a digits-only path in the typing sweep and in emit: every
+    shape around its limits (8 / 9 integer digits, 6 / 7 decimals, 1e6, 1e-5, signs, zeros) against
+    pandas, in fixed, object-float and mixed columns."""
+    import random
+    r = random.Random(17)
+    docs = []
+    for t in range(120):
+        rows = []
+        for i in range(r.randint(2, 40)):
+            ip = r.choice([0, 0, 1, 9, 12, 999, 123456, 999999, 1000000, 1000001, 99999999, 123456789])
+            nd = r.randint(1, 7)
+            fr = "".join(r.choice("0123456789") for _ in range(nd))
+            if r.random() < 0.2:
+                fr = "0" * nd
+            tok = "%s%d.%s" % (r.choice(["", "", "-", "+"]), ip, fr)
+            other = r.choice(["1.5", "", "2", "NA", "0.000001", "0.00001", "1e3", "7.25", "x"])
+            rows.append("%s,%s,%s" % (tok, other, r.choice(["a", "b", ""])))
+        docs.append(("p,q,s\n" + "\n".join(rows) + "\n").encode())
+    got = eng.parse_csv_many(docs, 1000)
+    bad = [i for i, (g, d) in enumerate(zip(got, docs)) if g != oracle(d, 1000)]
+    assert not bad, bad[:10]
