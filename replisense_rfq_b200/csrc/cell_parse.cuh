@@ -166,6 +166,12 @@ RFQ_HD int parse_int64(It it, int64_t* out) {
   if (!is_digit_ascii(c)) return INT_INVALID;
   uint64_t mag = 0;
   const uint64_t lim = neg ? 9223372036854775808ull : 9223372036854775807ull;
+  int nd = 0;
+  while (is_digit_ascii(c) && nd < 18) {      // 18 digits cannot overflow: no check per digit
+    mag = mag * 10 + (uint32_t)(c - '0');
+    ++nd;
+    c = it.next();
+  }
   while (is_digit_ascii(c)) {
     uint32_t d = (uint32_t)(c - '0');
     if (mag > (lim - d) / 10) return INT_OVERFLOW;

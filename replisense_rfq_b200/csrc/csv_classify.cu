@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(256) csv_classify_kernel(TableArgs a) {
 // Shared memory: 16 reduction arrays of max_w words (dynamic), so narrow tables keep occupancy.
 enum { FA_FLAGS = 0, FA_BAD, FA_OVF, FA_UINV, FA_UOVF, FA_STR, FA_INT, FA_UINT, FA_BOOL, FA_IP, FA_TZ,
        FA_INF, FA_OBJ, FA_SCI, FA_FL, FA_NA, FA_COUNT };
-#define RFQ_SMAX(arr, v) do { uint32_t v_ = (v); if (v_ > (arr)[c]) atomicMax(&(arr)[c], v_); } while (0)
+#define RFQ_SMAX(arr, v) do { uint32_t v_ = (v); if (v_ && v_ > (arr)[c]) atomicMax(&(arr)[c], v_); } while (0)
 
 __global__ void __launch_bounds__(256) csv_classify_fused_kernel(TableArgs a) {
   extern __shared__ uint32_t s_arr[];
