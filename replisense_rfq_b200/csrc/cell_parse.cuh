@@ -195,6 +195,12 @@ RFQ_HD int parse_uint64(It it, UintTok* out) {
   if (c == '+') c = it.next();
   if (!is_digit_ascii(c)) return INT_INVALID;
   uint64_t v = 0;
+  int nd = 0;
+  while (is_digit_ascii(c) && nd < 19) {      // 19 digits cannot overflow
+    v = v * 10 + (uint32_t)(c - '0');
+    ++nd;
+    c = it.next();
+  }
   while (is_digit_ascii(c)) {
     uint32_t d = (uint32_t)(c - '0');
     if (v > (18446744073709551615ull - d) / 10) return INT_OVERFLOW;

@@ -70,9 +70,16 @@ __device__ __forceinline__ CellSrc row_cell(const TableArgs& a, const TDoc& D, c
 //             4 = plain unquoted span with non-ASCII bytes, 5 = "..." around such a span
 //   bits 3-7: number of "" pairs (kind 3; 31 or more pairs are filed under kind 0)
 __device__ __forceinline__ CellSrc row_cell_tag_write(const TableArgs& a, const TDoc& D, const RowCur& r, uint32_t c) {
-  CellSrc s = row_cell(a, D, r, c);
-  if (a.cell_tag && !a.xcells && !s.missing) {
-    uint32_t n0 = __ldg(a.fend + r.fbeg + c) - (c == 0 ? r.start0 : __ldg(a.fend + r.fbeg + c - 1) + 1);
+  if (!a.cell_tag || a.xcells) return row_cell(a, D, r, c);
+  CellSrc s;
+  s.mode = CM_CSV; s.missing = false; s.clean = false; s.p = a.arena; s.n = 0; s.bits = 0;
+  if (c >= r.nf) { s.missing = true; return s; }
+  const uint32_t st = c == 0 ? r.start0 : __ldg(a.fend + r.fbeg + c - 1) + 1;
+  const uint32_t n0 = __ldg(a.fend + r.fbeg + c) - st;
+  s.p = a.arena + D.off + st;
+  s.n = n0;
+  csv_simplify(s);
+  {
     uint32_t tag = 0;
     if (s.mode == CM_RAW) tag = (s.clean ? 1u : 4u) + (s.n == n0 ? 0u : 1u);
     else if (s.mode == CM_CSVQ) {
