@@ -155,36 +155,54 @@ __global__ void __launch_bounds__(256, 3) csv_measure_kernel(TableArgs a) {
 }
 
 // ---- layout: class, width, decimals of every output column; line width -----------------------
-__global__ void __launch_bounds__(128) csv_layout_kernel(TableArgs a) {
-  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(256) csv_layout_kernel(TableArgs a) {   // one warp per document
+  const uint32_t d = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const uint32_t lane = threadIdx.x & 31u;
   if (d >= a.n_docs) return;
   const TDoc D = a.docs[d];
   if (!D.active) return;
   const ChunkMeasure* meas = (const ChunkMeasure*)a.meas;
   ColOut* col = (ColOut*)a.col;
-  uint32_t off = 0;
-  int flags = 0;
   if (a.cand) {   // one-sweep mode: rows kept = data rows - rows dropna removed
     uint32_t dr = 0;
-    for (uint32_t k = 0; k < D.n_chunks; ++k) dr += a.chunk_dropped[D.stat_base + k * D.W];
-    a.n_keep[d] = D.n_data - dr;
+    for (uint32_t k = lane; k < D.n_chunks; k += 32) dr += a.chunk_dropped[D.stat_base + k * D.W];
+#pragma unroll
+    for (int o = 16; o; o >>= 1) dr += __shfl_xor_sync(0xffffffffu, dr, o);
+    if (lane == 0) a.n_keep[d] = D.n_data - dr;
   }
-  for (uint32_t j = 0; j < D.h; ++j) {
-    uint32_t c = D.lead + j;
-    uint32_t e0 = D.stat_base + c;
-    bool nan_left = false;
-    for (uint32_t k = 0; k < D.n_chunks; ++k) nan_left |= meas[e0 + (size_t)k * D.W].nan_left != 0;
-    int cls = fold_column_class(a.ctype + e0, D.n_chunks, D.W, nan_left);
-    if (cls == CC_UNSUP) { flags |= 2; cls = CC_OBJ; }
-    ColumnLayout L = layout_column(cls, meas + e0, a.ctype + e0, D.n_chunks, D.W,
-                                   a.name_cp[D.col_base + j]);
+  uint32_t carry = 0;   // code points of the columns to the left, separators included
+  bool unsup = false;
+  for (uint32_t j0 = 0; j0 < D.h; j0 += 32) {   // lanes take columns; a warp scan gives their offsets
+    const uint32_t j = j0 + lane;
+    uint32_t w1 = 0;
     ColOut o;
-    o.cls = L.cls; o.dec = L.dec; o.sci = L.sci ? 1 : 0; o.width = L.width; o.cp_off = off;
-    col[D.col_base + j] = o;
-    off += L.width + 1;
+    o.cls = 0; o.dec = 0; o.sci = 0; o.width = 0; o.cp_off = 0;
+    if (j < D.h) {
+      uint32_t c = D.lead + j;
+      uint32_t e0 = D.stat_base + c;
+      bool nan_left = false;
+      for (uint32_t k = 0; k < D.n_chunks; ++k) nan_left |= meas[e0 + (size_t)k * D.W].nan_left != 0;
+      int cls = fold_column_class(a.ctype + e0, D.n_chunks, D.W, nan_left);
+      if (cls == CC_UNSUP) { unsup = true; cls = CC_OBJ; }
+      ColumnLayout L = layout_column(cls, meas + e0, a.ctype + e0, D.n_chunks, D.W,
+                                     a.name_cp[D.col_base + j]);
+      o.cls = L.cls; o.dec = L.dec; o.sci = L.sci ? 1 : 0; o.width = L.width;
+      w1 = L.width + 1;
+    }
+    uint32_t incl = w1;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) {
+      uint32_t x = __shfl_up_sync(0xffffffffu, incl, s);
+      if (lane >= (uint32_t)s) incl += x;
+    }
+    if (j < D.h) { o.cp_off = carry + incl - w1; col[D.col_base + j] = o; }
+    carry += __shfl_sync(0xffffffffu, incl, 31);
   }
-  a.doc_linew[d] = off ? off - 1 : 0;
-  if (flags) atomicOr(a.doc_flags + d, flags);
+  const bool any_unsup = __any_sync(0xffffffffu, unsup);
+  if (lane == 0) {
+    a.doc_linew[d] = carry ? carry - 1 : 0;
+    if (any_unsup) atomicOr(a.doc_flags + d, 2);
+  }
 }
 
 // ---- bytes of every output line (indexed by record slot; slot r0 = banner + header line) ------
@@ -228,7 +246,7 @@ void csv_table_measure(const TableArgs& a, cudaStream_t s) {
   prof_mark("csv_measure_kernel", s);
   if (a.n_items) RFQ_LAUNCH(csv_measure_kernel, table_grid(a.n_items), 256, 0, s, a);
   prof_mark("csv_layout+rowbytes+scan", s);
-  RFQ_LAUNCH(csv_layout_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
+  RFQ_LAUNCH(csv_layout_kernel, (a.n_docs + 7) / 8, 256, 0, s, a);
   RFQ_LAUNCH(csv_rowbytes_kernel, (a.n_slots + 1 + 255) / 256, 256, 0, s, a);
   exclusive_scan<SumU64>(a.row_bytes, a.row_off, a.n_slots + 1, a.scan_tmp64, nullptr, s);
   RFQ_LAUNCH(csv_docout_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
