@@ -171,6 +171,58 @@ RFQ_HD double dbl_inf(int sign) {
 #endif
 }
 
+// scan_text for a plain span: lengths and escape counts eight bytes at a time; only windows that
+// hold non-ASCII bytes are walked byte by byte for the UTF-8 validation
+RFQ_HD uint64_t zero_bytes(uint64_t y) {   // 0x80 in every byte of y that is zero (exact)
+  const uint64_t lo7 = 0x7F7F7F7F7F7F7F7Full;
+  return ~(((y & lo7) + lo7) | y | lo7);
+}
+RFQ_HD TextInfo scan_text_raw(const uint8_t* p, uint32_t n) {
+  TextInfo t;
+  t.nbytes = n; t.ncp = 0; t.nesc = 0; t.first8 = n ? load8_masked(p, n) : 0; t.utf8_ok = true; t.has_fchar = false;
+  const uint64_t ones = 0x0101010101010101ull, highs = 0x8080808080808080ull;
+  uint32_t cont = 0;
+  int need = 0;
+  uint32_t lo = 0x80, hi = 0xBF;
+  for (uint32_t i = 0; i < n; i += 8) {
+    const uint32_t rem = n - i, m = rem < 8 ? rem : 8;
+    const uint64_t x = i == 0 ? t.first8 : load8_masked(p + i, rem);
+    const uint64_t esc = zero_bytes(x ^ (ones * 0x09)) | zero_bytes(x ^ (ones * 0x0A)) | zero_bytes(x ^ (ones * 0x0D));
+#ifdef __CUDA_ARCH__
+    t.nesc += (uint32_t)__popcll(esc);
+#else
+    t.nesc += (uint32_t)__builtin_popcountll(esc);
+#endif
+    if (!(x & highs)) {
+      if (need) { t.utf8_ok = false; need = 0; }
+      continue;
+    }
+    const uint64_t cb = x & ~(x << 1) & highs;   // 10xxxxxx
+#ifdef __CUDA_ARCH__
+    cont += (uint32_t)__popcll(cb);
+#else
+    cont += (uint32_t)__builtin_popcountll(cb);
+#endif
+    for (uint32_t q = 0; q < m; ++q) {
+      const uint32_t c = (uint32_t)(x >> (8 * q)) & 0xFFu;
+      if (need) {
+        if (c < lo || c > hi) { t.utf8_ok = false; need = 0; }
+        else { --need; lo = 0x80; hi = 0xBF; }
+        continue;
+      }
+      if (c < 0x80u) continue;
+      lo = 0x80; hi = 0xBF;
+      if (c >= 0xC2u && c <= 0xDFu) need = 1;
+      else if (c >= 0xE0u && c <= 0xEFu) { need = 2; if (c == 0xE0u) lo = 0xA0; if (c == 0xEDu) hi = 0x9F; }
+      else if (c >= 0xF0u && c <= 0xF4u) { need = 3; if (c == 0xF0u) lo = 0x90; if (c == 0xF4u) hi = 0x8F; }
+      else t.utf8_ok = false;
+    }
+  }
+  if (need) t.utf8_ok = false;
+  t.ncp = n - cont;
+  return t;
+}
+
 RFQ_HD TextInfo cell_text(const CellSrc& s) {
   if (s.missing || !cell_is_text(s)) {
     TextInfo t; t.nbytes = t.ncp = t.nesc = 0; t.first8 = 0; t.utf8_ok = true; t.has_fchar = false;
@@ -193,7 +245,7 @@ RFQ_HD TextInfo cell_text(const CellSrc& s) {
     for (int k = 0; k < 8; ++k) { int c = it.next(); if (c < 0) break; t.first8 |= (uint64_t)c << (8 * k); }
     return t;
   }
-  if (s.mode == CM_RAW) return scan_text(RawIter(s.p, s.n));
+  if (s.mode == CM_RAW) return scan_text_raw(s.p, s.n);
   return scan_text_slow(s.p, s.n, s.mode);
 }
 RFQ_HD int cell_int64(const CellSrc& s, int64_t* v) {

@@ -274,6 +274,14 @@ extern "C" {
 // Full reference trial loop restricted to what can differ structurally: utf-8 then latin-1, each
 // with ',', ';', TAB (cp1252 can never win where latin-1 failed: same bytes, same structure).
 // returns status (0 ok / 1 unparseable / 2 unsupported); *out_len bytes written to out (cap).
+// 1 when the windowed scan of a plain span agrees with the byte-by-byte scan_text
+int hc_scan_text_cmp(const uint8_t* p, uint32_t n) {
+  TextInfo a = scan_text(RawIter(p, n)), b = scan_text_raw(p, n);
+  if (a.nbytes != b.nbytes || a.first8 != b.first8 || a.utf8_ok != b.utf8_ok) return 0;
+  if (a.utf8_ok && (a.ncp != b.ncp || a.nesc != b.nesc)) return 0;   // counts only mean something for valid text
+  return 1;
+}
+
 void hc_set_fused(int on) { g_fused = on != 0; }
 uint64_t hc_fused_used() { return g_fused_used; }
 

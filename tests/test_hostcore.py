@@ -319,3 +319,15 @@ def test_fused_measurement_equals_two_sweeps():
     bad = [i for i, (a, b) in enumerate(zip(two, one)) if a != b]
     assert not bad, bad[:10]
     assert used > 400
+
+
+def test_windowed_text_scan_equals_bytewise():
+    """scan_text_raw (8 bytes at a time, only non-ASCII windows walked) against scan_text on valid
+    and broken UTF-8, escapes and every length around the window size."""
+    L = H.lib()
+    r = random.Random(9)
+    pieces = [b"a", b" ", b"\t", b"\n", b"\r", "é".encode(), "₹".encode(), "日".encode(), "😀".encode(),
+              b"\x80", b"\xc3", b"\xe2\x82", b"\xf0\x9f", b"\xc0\xaf", b"\xed\xa0\x80", b"\xf4\x90\x80\x80", b"\xff", b"."]
+    for _ in range(30000):
+        b = b"".join(r.choice(pieces) for _ in range(r.randint(0, 14)))
+        assert L.hc_scan_text_cmp(b, len(b)) == 1, b
