@@ -66,7 +66,20 @@ RFQ_HD bool xml_name_end(uint32_t c) { return c == ' ' || c == '>' || c == '/' |
 // classify the tag that starts at p[0] == '<' (p may be read up to 7 bytes ahead, bounded by e)
 RFQ_HD int xml_classify(const uint8_t* p, const uint8_t* e) {
   uint32_t b[8];
+#ifdef __CUDA_ARCH__
+  {   // the 8 bytes in two aligned loads (the arena carries slack past the last document)
+    const unsigned long long* q = (const unsigned long long*)((uintptr_t)p & ~(uintptr_t)7);
+    const uint32_t sh = (uint32_t)((uintptr_t)p & 7u) * 8u;
+    unsigned long long x = __ldg(q);
+    if (sh) x = (x >> sh) | (__ldg(q + 1) << (64u - sh));
+    const size_t rem = (size_t)(e - p);
+    if (rem < 8) x &= (1ull << (8 * rem)) - 1ull;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) b[i] = (uint32_t)(x >> (8 * i)) & 0xFFu;
+  }
+#else
   for (int i = 0; i < 8; ++i) b[i] = (p + i < e) ? p[i] : 0u;
+#endif
   if (b[1] == '!') return XT_BANG;
   if (b[1] == '/') {
     if (b[2] == 'c' && b[3] == '>') return XT_C_END;
