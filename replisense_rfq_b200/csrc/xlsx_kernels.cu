@@ -30,12 +30,13 @@ __device__ __forceinline__ uint32_t x_find(const uint32_t* __restrict__ base, ui
 __device__ __forceinline__ uint32_t lt_mask(const uint8_t* __restrict__ doc, uint32_t len, uint32_t base) {
   if (base >= len) return 0u;
   uint4 v = __ldg(reinterpret_cast<const uint4*>(doc + base));
-  uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
   uint32_t m = 0;
 #pragma unroll
-  for (int k = 0; k < 16; ++k)
-    if (base + k < len && ((w[k >> 2] >> ((k & 3) * 8)) & 0xFFu) == '<') m |= 1u << k;
-  return m;
+  for (int q = 0; q < 4; ++q)   // 0xFF per matching byte -> one bit per byte
+    m |= (((__vcmpeq4(w[q], 0x3C3C3C3Cu) & 0x08040201u) * 0x01010101u) >> 24) << (4 * q);
+  const uint32_t left = len - base;   // base < len here
+  return left >= 16 ? m : m & ((1u << left) - 1u);
 }
 
 template <bool WRITE>
