@@ -63,7 +63,7 @@ RFQ_HD uint32_t sst_decode_si(const uint8_t* p, const uint8_t* e, uint8_t* out, 
     if (tg == XT_RPH_END) { in_rph = 0; ++q; continue; }
     if (tg == XT_T && !in_rph) {
       const uint8_t* g = q;
-      while (g < e && *g != '>') ++g;
+      g = find_byte(g, e, '>');
       if (g >= e) break;
       if (g[-1] == '/') { q = g; continue; }  // <t/>
       const uint8_t* tb = g + 1;
@@ -89,7 +89,7 @@ RFQ_HD uint32_t sst_decode_si(const uint8_t* p, const uint8_t* e, uint8_t* out, 
 // ---- <row ...>: its r= number ------------------------------------------------------------------
 RFQ_HD uint32_t xlsx_row_number(const uint8_t* p, const uint8_t* e, uint32_t* flags) {
   const uint8_t* g = p;
-  while (g < e && *g != '>') ++g;
+  g = find_byte(g, e, '>');
   const uint8_t* vb; uint32_t vn;
   if (!xml_attr(p, g, 'r', &vb, &vn) || vn == 0) { *flags |= XU_ROW_NOREF; return 0; }
   *flags |= XU_ROW_HASREF;
@@ -124,7 +124,7 @@ RFQ_HD XCell xlsx_parse_cell(const uint8_t* doc, uint32_t len, uint32_t cpos, co
   const uint8_t* p = doc + cpos;
   const uint8_t* e = doc + len;
   const uint8_t* g = p;
-  while (g < e && *g != '>') ++g;
+  g = find_byte(g, e, '>');
   if (g >= e) return x;
   const uint8_t* vb; uint32_t vn;
   uint32_t row = 0;
@@ -155,15 +155,15 @@ RFQ_HD XCell xlsx_parse_cell(const uint8_t* doc, uint32_t len, uint32_t cpos, co
     if (tg == XT_C_END || tg == XT_C || tg == XT_ROW_END) break;
     if (tg == XT_BANG) *flags |= XU_BANG;
     const uint8_t* h = q;
-    while (h < e && *h != '>') ++h;
+    h = find_byte(h, e, '>');
     if (h >= e) break;
     if (tg == XT_V && !have_v) {
       have_v = true;
-      if (h[-1] != '/') { val_b = h + 1; const uint8_t* t2 = val_b; while (t2 < e && *t2 != '<') ++t2; val_n = (uint32_t)(t2 - val_b); }
+      if (h[-1] != '/') { val_b = h + 1; const uint8_t* t2 = find_byte(val_b, e, '<'); val_n = (uint32_t)(t2 - val_b); }
     } else if (tg == XT_IS) { in_is = h[-1] != '/'; }
     else if (tg == XT_R && in_is) { *flags |= XU_RICH_INLINE; }
     else if (tg == XT_T && in_is) {
-      if (h[-1] != '/' && n_t == 0) { is_b = h + 1; const uint8_t* t2 = is_b; while (t2 < e && *t2 != '<') ++t2; is_n = (uint32_t)(t2 - is_b); }
+      if (h[-1] != '/' && n_t == 0) { is_b = h + 1; const uint8_t* t2 = find_byte(is_b, e, '<'); is_n = (uint32_t)(t2 - is_b); }
       ++n_t;
     }
     q = h + 1;

@@ -100,6 +100,30 @@ RFQ_HD int xml_classify(const uint8_t* p, const uint8_t* e) {
   return XT_OTHER;
 }
 
+// first position in [p, e) holding byte c, or e: eight bytes per step on the device (two aligned
+// loads; the arena carries slack past its last document)
+RFQ_HD const uint8_t* find_byte(const uint8_t* p, const uint8_t* e, uint8_t c) {
+#ifdef __CUDA_ARCH__
+  const unsigned long long ones = 0x0101010101010101ull, lo7 = 0x7F7F7F7F7F7F7F7Full;
+  while (p < e) {
+    const unsigned long long* q = (const unsigned long long*)((uintptr_t)p & ~(uintptr_t)7);
+    const uint32_t sh = (uint32_t)((uintptr_t)p & 7u) * 8u;
+    unsigned long long x = __ldg(q);
+    if (sh) x = (x >> sh) | (__ldg(q + 1) << (64u - sh));
+    const unsigned long long y = x ^ (ones * c);
+    unsigned long long hit = ~(((y & lo7) + lo7) | y | lo7);   // 0x80 in every byte equal to c
+    const size_t rem = (size_t)(e - p);
+    if (rem < 8) hit &= (1ull << (8 * rem)) - 1ull;
+    if (hit) return p + ((__ffsll((long long)hit) - 1) >> 3);
+    p += 8;
+  }
+  return e;
+#else
+  while (p < e && *p != c) ++p;
+  return p;
+#endif
+}
+
 // find attribute ` name="value"` inside the tag [p, e) (e = position of the closing '>').
 // name is 1 or 2 chars (r, t, s, ht ...). Returns value span; false if absent.
 RFQ_HD bool xml_attr(const uint8_t* p, const uint8_t* e, char n0, const uint8_t** vb, uint32_t* vn) {
