@@ -258,7 +258,7 @@ __global__ void __launch_bounds__(256) csv_index_kernel(ScanArgs a) {
   uint32_t g = a.tile_nf_pre[t] + pf - nf;          // global index of this lane's first field end
   uint32_t r = a.tile_nl_pre[t] + pl - nl + d;      // record slot currently open at this lane
   uint32_t doc_begin = has_bom ? 3u : 0u;
-  lane_walk(lb.cls, st, class_fe, [&](int k, int e, int sb) {
+  auto on_event = [&](int k, int e, int sb) {
     uint32_t pos = base + k;
     if (e & EV_REC_START) a.rec_start[r] = pos;
     if (e & EV_REC_START_WS) {
@@ -272,7 +272,26 @@ __global__ void __launch_bounds__(256) csv_index_kernel(ScanArgs a) {
     }
     if (e & EV_FIELD_END) a.fend[g++] = pos;
     if (e & EV_LINE_END) a.rec_fend[r++] = g;
-  });
+  };
+  {
+    // An ordinary byte right after an ordinary byte changes nothing (the state is already U or Q and
+    // neither raises an event on class O): only bytes of another class, and the first ordinary byte
+    // after one (or at the start of the lane), are visited.
+    unsigned long long t = lb.cls;
+    t = (t | (t >> 1) | (t >> 2) | (t >> 3)) & 0x1111111111111111ull;   // bit 4k = nibble k is not CL_O
+    t = (t | (t >> 3)) & 0x0303030303030303ull;
+    t = (t | (t >> 6)) & 0x000F000F000F000Full;
+    t = (t | (t >> 12)) & 0x000000FF000000FFull;
+    const uint32_t nz = (uint32_t)(t | (t >> 24)) & 0xFFFFu;
+    int s1 = st;
+    for (uint32_t m = (nz | (nz << 1) | 1u) & 0xFFFFu; m; m &= m - 1) {
+      const int kk = __ffs(m) - 1;
+      const uint2 fe = class_fe[(uint32_t)(lb.cls >> (4 * kk)) & 0xFu];
+      const int e = (int)((fe.y >> (4 * s1)) & 0xFu);
+      if (e) on_event(kk, e, s1);
+      s1 = (int)((fe.x >> (4 * s1)) & 0xFu);
+    }
+  }
   }
 }
 
