@@ -156,7 +156,9 @@ RFQ_HD int inf_token(It it) {
 // ---- integers ---------------------------------------------------------------------------------
 enum { INT_OK = 0, INT_INVALID = 1, INT_OVERFLOW = 2 };
 
-// str_to_int64: [space]* [+-] digits [space]* ; the first failure scanning left to right wins.
+// str_to_int64: [space]* [+-] digits [space]* ; the first failure scanning left to right wins,
+// except that an overflow followed by anything but digits is an invalid token (probed on pandas
+// 3.0.2: "9223372036854775808 " and "111111111111111111111.5" send the column to the float pass).
 template <class It>
 RFQ_HD int parse_int64(It it, int64_t* out) {
   int c = it.next();
@@ -174,7 +176,13 @@ RFQ_HD int parse_int64(It it, int64_t* out) {
   }
   while (is_digit_ascii(c)) {
     uint32_t d = (uint32_t)(c - '0');
-    if (mag > (lim - d) / 10) return INT_OVERFLOW;
+    if (mag > (lim - d) / 10) {
+      // reported as an overflow only when nothing but digits follows ("1e20 digits" + ".5", a
+      // trailing blank, a letter: ERROR_INVALID_CHARS — the column goes on to the float pass)
+      c = it.next();
+      while (is_digit_ascii(c)) c = it.next();
+      return c >= 0 ? INT_INVALID : INT_OVERFLOW;
+    }
     mag = mag * 10 + d;
     c = it.next();
   }
@@ -203,7 +211,11 @@ RFQ_HD int parse_uint64(It it, UintTok* out) {
   }
   while (is_digit_ascii(c)) {
     uint32_t d = (uint32_t)(c - '0');
-    if (v > (18446744073709551615ull - d) / 10) return INT_OVERFLOW;
+    if (v > (18446744073709551615ull - d) / 10) {
+      c = it.next();                      // same rule as str_to_int64: digits only after the overflow
+      while (is_digit_ascii(c)) c = it.next();
+      return c >= 0 ? INT_INVALID : INT_OVERFLOW;
+    }
     v = v * 10 + d;
     c = it.next();
   }

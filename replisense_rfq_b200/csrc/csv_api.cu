@@ -86,6 +86,7 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
   sa.tile_nf_pre = c->pool.alloc<uint32_t>(nt + 1);
   sa.tile_nl_pre = c->pool.alloc<uint32_t>(nt + 1);
   sa.doc_final = c->pool.alloc<uint32_t>(m + 1);
+  sa.doc_unsup = c->pool.alloc<uint32_t>(m + 1);
   sa.scan_tmp = c->pool.alloc<uint32_t>(scan_partials_needed(nt + 1));
   DocShape* d_shape = c->pool.alloc<DocShape>(m + 1);
   if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
@@ -94,7 +95,9 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
   sa.doc_len = (const uint32_t*)(d_up + o_len);
   sa.tile_base = (const uint32_t*)(d_up + o_tb);
   const uint32_t* d_mr = (const uint32_t*)(d_up + o_mr);
+  sa.max_rows = d_mr;
   RFQ_CK(c, cudaMemsetAsync(sa.doc_final, 0, 4ull * (m + 1), s));
+  RFQ_CK(c, cudaMemsetAsync(sa.doc_unsup, 0, 4ull * (m + 1), s));
   csv_scan_count(sa, s);
   RFQ_CK(c, c->h_down.reserve(sizeof(DocShape) * (m + 1) + 32ull * (m + 1) + 4096));
   uint32_t* h_tot = (uint32_t*)c->h_down.p;
@@ -136,7 +139,8 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
     item_base[i] = (uint32_t)n_items;
     uint32_t nrows = a_mr[i];
     uint32_t h = (uint32_t)A.hdr.names.size();
-    if (sh.n_rec == 0 || !A.hdr.found || !A.hdr.utf8_ok) A.fail = 1;                  // EmptyDataError / decode
+    if (sh.pad) A.fail = 2;                                                            // bare CR + blank-first record
+    else if (sh.n_rec == 0 || !A.hdr.found || !A.hdr.utf8_ok) A.fail = 1;             // EmptyDataError / decode
     else if (sh.final_state == ST_Q && (uint64_t)sh.n_rec < (uint64_t)nrows + 1) A.fail = 1;  // EOF inside string
     else if (h != sh.hdr_nf) A.fail = 2;                                                // internal mismatch: never guess
     else {
@@ -163,10 +167,10 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
         names += empty;
         for (uint32_t j = 0; j < h; ++j) {
           name_off.push_back((uint32_t)names.size());
-          name_len.push_back((uint32_t)A.hdr.names[j].size());
+          name_len.push_back((uint32_t)A.hdr.disp[j].size());   // display label (escapes, trim_front)
           name_cp.push_back(A.hdr.ncp[j]);
-          T.hdr_extra += (uint32_t)A.hdr.names[j].size() - A.hdr.ncp[j];
-          names += A.hdr.names[j];
+          T.hdr_extra += (uint32_t)A.hdr.disp[j].size() - A.hdr.ncp[j];
+          names += A.hdr.disp[j];
         }
         T.active = 1; A.active = true;
       }

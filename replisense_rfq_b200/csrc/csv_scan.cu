@@ -269,6 +269,13 @@ __global__ void __launch_bounds__(256) csv_index_kernel(ScanArgs a) {
         if ((c == ' ' || c == '\t') && c != a.sep) --p; else break;
       }
       a.rec_start[r] = p;
+      // pandas finds the start of such a line by walking back to the previous '\n' (tokenizer.c,
+      // WHITESPACE_LINE: `while (i + 1 > datapos && !IS_TERMINATOR(*buf))`, and only LF is a
+      // terminator there).  After a bare CR, or after the delimiter a skipped blank line swallowed,
+      // it runs into the earlier rows and what comes out depends on its read-buffer positions: not
+      // reproduced, the document is reported unsupported instead.
+      if (p > doc_begin && doc[p - 1] != '\n' &&
+          r - (a.tile_nl_pre[a.tile_base[d]] + d) <= a.max_rows[d]) a.doc_unsup[d] = 1u;
     }
     if (e & EV_FIELD_END) a.fend[g++] = pos;
     if (e & EV_LINE_END) a.rec_fend[r++] = g;
@@ -306,7 +313,7 @@ __global__ void __launch_bounds__(256) csv_shape_init_kernel(ScanArgs a, DocShap
   s.final_state = a.doc_final[d];
   s.r0 = a.tile_nl_pre[t0] + d;
   s.f0 = a.tile_nf_pre[t0];
-  s.pad = 0;
+  s.pad = a.doc_unsup[d];   // filled by the index pass, which runs first
   shape[d] = s;
 }
 

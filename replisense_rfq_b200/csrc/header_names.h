@@ -17,14 +17,72 @@ namespace rfq {
 struct HeaderInfo {
   bool found = false;                 // a header record exists
   bool utf8_ok = true;
-  std::vector<std::string> names;     // final (mangled) column names
-  std::vector<uint32_t> ncp;          // code points of each name
+  std::vector<std::string> names;     // final (mangled) column names ("Empty DataFrame" prints these)
+  std::vector<std::string> disp;      // labels as to_string prints them (display_labels)
+  std::vector<uint32_t> ncp;          // code points of each display label
 };
 
 inline bool utf8_valid_count(const std::string& s, uint32_t* ncp) {
   TextInfo t = scan_text(RawIter((const uint8_t*)s.data(), (uint32_t)s.size()));
   *ncp = t.ncp;
   return t.utf8_ok;
+}
+
+// Python's str.isspace() for one code point (the set str.lstrip() removes)
+inline bool py_isspace_cp(uint32_t cp) {
+  return (cp >= 0x09 && cp <= 0x0D) || (cp >= 0x1C && cp <= 0x20) || cp == 0x85 || cp == 0xA0 || cp == 0x1680 ||
+         (cp >= 0x2000 && cp <= 0x200A) || cp == 0x2028 || cp == 0x2029 || cp == 0x202F || cp == 0x205F ||
+         cp == 0x3000;
+}
+
+// Column labels as `to_string` prints them: pandas formats the columns Index through
+// `Index._format_flat` -> `format_array(values, None, justify='all')` (every label becomes
+// " " + pprint_thing(label, escape_chars=('\t', '\r', '\n'))) followed by `trim_front`, which cuts
+// the smallest common run of leading whitespace (str.lstrip() semantics) from ALL labels
+// (pandas/core/indexes/base.py `_format_with_header`, pandas/io/formats/format.py
+// `_GenericArrayFormatter._format_strings`, pandas/io/formats/printing.py `trim_front`).  So TAB / CR /
+// LF inside a label print as the two characters \t \r \n, and a header row whose names all start
+// with blanks loses the common part.  The "Empty DataFrame" text prints the raw names instead.
+// Labels must be valid UTF-8 (the caller checks); returns the code points of each display label.
+inline void display_labels(const std::vector<std::string>& names, std::vector<std::string>& disp,
+                           std::vector<uint32_t>& ncp) {
+  const size_t n = names.size();
+  disp.assign(n, std::string());
+  ncp.assign(n, 0);
+  std::vector<uint32_t> lead_cp(n, 0), lead_bytes(n, 0);
+  uint32_t cut = 0xFFFFFFFFu;
+  for (size_t k = 0; k < n; ++k) {
+    std::string& d = disp[k];
+    for (char ch : names[k]) {
+      if (ch == '\t') d += "\\t"; else if (ch == '\r') d += "\\r"; else if (ch == '\n') d += "\\n"; else d.push_back(ch);
+    }
+    // leading whitespace of the escaped label, in code points (+1 for the blank format_array adds)
+    size_t i = 0; uint32_t cps = 0, tot = 0;
+    bool in_lead = true;
+    while (i < d.size()) {
+      uint8_t b = (uint8_t)d[i];
+      uint32_t cp = b; size_t l = 1;
+      if (b >= 0xF0 && i + 3 < d.size()) { cp = ((b & 7u) << 18) | (((uint8_t)d[i + 1] & 0x3Fu) << 12) | (((uint8_t)d[i + 2] & 0x3Fu) << 6) | ((uint8_t)d[i + 3] & 0x3Fu); l = 4; }
+      else if (b >= 0xE0 && i + 2 < d.size()) { cp = ((b & 0xFu) << 12) | (((uint8_t)d[i + 1] & 0x3Fu) << 6) | ((uint8_t)d[i + 2] & 0x3Fu); l = 3; }
+      else if (b >= 0xC0 && i + 1 < d.size()) { cp = ((b & 0x1Fu) << 6) | ((uint8_t)d[i + 1] & 0x3Fu); l = 2; }
+      if (in_lead && py_isspace_cp(cp)) { ++cps; lead_bytes[k] = (uint32_t)(i + l); } else in_lead = false;
+      ++tot; i += l;
+    }
+    lead_cp[k] = cps; ncp[k] = tot;
+    if (cps + 1 < cut) cut = cps + 1;
+  }
+  if (n == 0 || cut <= 1) return;     // only the blank format_array added is common
+  cut -= 1;                           // code points to drop from every label
+  for (size_t k = 0; k < n; ++k) {
+    std::string& d = disp[k];
+    size_t i = 0;
+    for (uint32_t q = 0; q < cut && i < d.size(); ++q) {
+      uint8_t b = (uint8_t)d[i];
+      i += b >= 0xF0 ? 4 : b >= 0xE0 ? 3 : b >= 0xC0 ? 2 : 1;
+    }
+    d.erase(0, i);
+    ncp[k] -= cut;
+  }
 }
 
 // pandas' duplicate-name mangling (`a`, `a.1`, ...): named columns first, then the unnamed ones
@@ -99,6 +157,8 @@ inline HeaderInfo parse_header(const uint8_t* doc, uint64_t len, uint32_t sep, b
   h.ncp.resize(raw.size());
   for (size_t k = 0; k < raw.size(); ++k)
     if (!utf8_valid_count(raw[k], &h.ncp[k])) h.utf8_ok = false;
+  if (h.utf8_ok) display_labels(h.names, h.disp, h.ncp);
+  else h.disp = h.names;
   return h;
 }
 

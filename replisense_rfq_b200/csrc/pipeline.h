@@ -83,6 +83,8 @@ struct ScanArgs {
   uint32_t* tile_nf_pre;      // [n_tiles+1] exclusive prefix, last = total
   uint32_t* tile_nl_pre;      // [n_tiles+1]
   uint32_t* doc_final;        // [n_docs] DFA state before the virtual LF (ST_Q = EOF in string)
+  const uint32_t* max_rows;   // [n_docs] nrows of each document (records beyond 1 + nrows are never used)
+  uint32_t* doc_unsup;        // [n_docs] set when the document holds a construct pandas tokenises by accident (see csv_index_kernel)
   uint32_t* scan_tmp;         // scan partials
   // outputs of the index pass (allocated after the totals are known)
   uint32_t* fend;             // [n_fields] doc-relative position of each field-end byte
@@ -101,7 +103,7 @@ struct DocShape {
   uint32_t final_state;
   uint32_t r0;         // global record slot of record 0
   uint32_t f0;         // global field index of the document's first field
-  uint32_t pad;
+  uint32_t pad;        // != 0: a record pandas tokenises by accident (bare CR + blank-first line): unsupported
 };
 void csv_doc_shape(const ScanArgs& a, const uint32_t* max_rows32, DocShape* shape, uint32_t n_slots,
                    cudaStream_t s);

@@ -215,12 +215,19 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
     T.empty_off = (uint32_t)names.size(); T.empty_len = (uint32_t)empty.size();
     names += empty;
     T.banner_off = 0; T.banner_len = 0;
+    std::vector<uint32_t> ncp(T.W, 0);
+    bool valid = true;
+    for (uint32_t j = 0; j < T.W; ++j)
+      if (!utf8_valid_count(raw[j], &ncp[j])) valid = false;
+    if (!valid) { T.active = 0; c->r_status[d] = RFQ_DOC_UNSUPPORTED; }
+    // labels as to_string prints them: escapes + trim_front (header_names.h display_labels)
+    std::vector<std::string> disp = raw;
+    if (valid && !(all_int && before == raw)) display_labels(raw, disp, ncp);
     for (uint32_t j = 0; j < T.W; ++j) {
-      uint32_t g = T.col_base + j, cp = 0;
-      if (!utf8_valid_count(raw[j], &cp)) { T.active = 0; c->r_status[d] = RFQ_DOC_UNSUPPORTED; }
-      name_off[g] = (uint32_t)names.size(); name_len[g] = (uint32_t)raw[j].size(); name_cp[g] = cp;
-      T.hdr_extra += (uint32_t)raw[j].size() - cp;
-      names += raw[j];
+      uint32_t g = T.col_base + j;
+      name_off[g] = (uint32_t)names.size(); name_len[g] = (uint32_t)disp[j].size(); name_cp[g] = ncp[j];
+      T.hdr_extra += (uint32_t)disp[j].size() - ncp[j];
+      names += disp[j];
     }
   }
   // a document that turned unsupported keeps its slots and columns but gets no work items

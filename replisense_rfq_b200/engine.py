@@ -89,7 +89,9 @@ class PinnedArena:
 
 
 class BatchResult:
-    """Views over the library-owned pinned output of the last run (valid until the next run)."""
+    """Views over the library-owned pinned output of the last run.  The text stays valid only until
+    the engine's next call: read it while holding `engine.lock` (the `parse_*_many` methods and
+    `Engine.locked()` do), or from the one thread that owns the engine."""
 
     def __init__(self, eng: "Engine"):
         lib, ctx = eng.lib, eng.ctx
@@ -136,7 +138,8 @@ class Engine:
                 f"rfq_create(device={device}) failed: no CUDA device — there is no CPU fallback")
         self.ctx = h
         self.device = device
-        self.lock = threading.Lock()
+        # re-entrant: a caller that has to read a BatchResult takes it around the *_batch call
+        self.lock = threading.RLock()
         self._arena = None
 
     # -- helpers
@@ -235,20 +238,28 @@ class Engine:
                                                n, mr.ctypes.data), "rfq_csv_parse")
             return BatchResult(self)
 
-    def parse_csv_many(self, docs: Sequence[bytes], max_rows=1000) -> "list[str | None]":
+    def parse_csv_many(self, docs: Sequence[bytes], max_rows=1000,
+                       on_unsupported: str = "raise") -> "list[str | None | EngineError]":
         """raw_text per document; None where every (encoding, separator) attempt failed (the
-        caller raises the reference's FileParsingError)."""
-        r = self.csv_batch(docs, max_rows)
-        out = []
-        for d in range(r.n):
-            st = int(r.status[d])
-            if st == _lib.DOC_OK:
-                out.append(r.doc_str(d))
-            elif st == _lib.DOC_CSV_UNPARSEABLE:
-                out.append(None)
-            else:
-                raise EngineError(f"document {d}: unsupported construct on the GPU path (status {st})")
-        return out
+        caller raises the reference's FileParsingError).  A document that uses a construct the GPU
+        path does not decode raises EngineError, or — with on_unsupported="return" — gets an
+        EngineError instance in its slot so the rest of the batch survives.  The texts are built
+        while the engine lock is held: the pinned output belongs to this call until then."""
+        with self.lock:
+            r = self.csv_batch(docs, max_rows)
+            out = []
+            for d in range(r.n):
+                st = int(r.status[d])
+                if st == _lib.DOC_OK:
+                    out.append(r.doc_str(d))
+                elif st == _lib.DOC_CSV_UNPARSEABLE:
+                    out.append(None)
+                else:
+                    err = EngineError(f"document {d}: unsupported construct on the GPU path (status {st})")
+                    if on_unsupported == "raise":
+                        raise err
+                    out.append(err)
+            return out
 
     # -- sheets
     def sheets_batch(self, docs: Sequence[bytes], kind, sst_of, max_rows=1000, date_ids=None) -> BatchResult:
@@ -375,6 +386,7 @@ class EnginePool:
         for e in self.engines:
             self._free.put(e)
         self._pool = ThreadPoolExecutor(max_workers=depth)
+        self._rr, self._rr_lock = 0, threading.Lock()
 
     def _run(self, fn, args):
         e = self._free.get()
@@ -393,14 +405,17 @@ class EnginePool:
         return [f.result() for f in [self.submit(fn, it) for it in items]]
 
     def pick(self) -> Engine:
-        """An engine that is idle right now (else the next one in turn): concurrent callers of one
-        shared FileParser land on different streams."""
+        """An engine that is idle right now, else the next one in turn (its caller then waits on that
+        engine's lock): concurrent callers of one shared FileParser land on different streams.  Every
+        parse_*_many call holds its engine's lock until its result has been turned into Python
+        objects, so a busy engine handed out here is never rerun under a reader."""
         for e in self.engines:
             if e.lock.acquire(blocking=False):
                 e.lock.release()
                 return e
-        self._rr = (getattr(self, "_rr", 0) + 1) % len(self.engines)
-        return self.engines[self._rr]
+        with self._rr_lock:
+            self._rr = (self._rr + 1) % len(self.engines)
+            return self.engines[self._rr]
 
     def close(self):
         self._pool.shutdown(wait=True)

@@ -165,8 +165,9 @@ class FileParser:
             if k == "txt":
                 res = self.engine.parse_text_many(batch)
             elif k == "csv":
-                res = [r if r is not None else FileParsingError(f"CSV parsing failed: {_CSV_FAIL}")
-                       for r in self.engine.parse_csv_many(batch, self.max_excel_rows)]
+                res = [FileParsingError(f"CSV parsing failed: {_CSV_FAIL}") if r is None
+                       else FileParsingError(f"CSV parsing failed: {r}") if isinstance(r, EngineError) else r
+                       for r in self.engine.parse_csv_many(batch, self.max_excel_rows, on_unsupported="return")]
             elif k == "xlsx":
                 from . import xlsx_host
                 res = []

@@ -60,7 +60,8 @@ def build_prompts(engine, texts: Sequence[str], template: str = EXTRACTION_PROMP
     docs = [t.encode("utf-8") for t in texts]
     if not docs:
         return []
-    r = engine.prompt_batch(docs, (template + '\n"""\n').encode("utf-8"), PROMPT_TAIL.encode("utf-8"),
-                            TRUNCATION_MARK.encode("utf-8"), max_chars)
-    st = np.asarray(r.status)
-    return [None if int(st[d]) else r.doc_str(d) for d in range(r.n)]
+    with engine.lock:   # the pinned output is ours until the strings have been built
+        r = engine.prompt_batch(docs, (template + '\n"""\n').encode("utf-8"), PROMPT_TAIL.encode("utf-8"),
+                                TRUNCATION_MARK.encode("utf-8"), max_chars)
+        st = np.asarray(r.status)
+        return [None if int(st[d]) else r.doc_str(d) for d in range(r.n)]

@@ -114,18 +114,19 @@ def parse_workbooks(engine, books, max_rows: int = 1000) -> "list":
         for k, xml in enumerate(wb.sheets):
             docs.append(xml); kind.append(2 if wb.date1904 else 0); sst_of.append(sst_idx); dates.append(wb.date_styles)
             owner.append((b, k))
-    res = engine.sheets_batch(docs, kind, sst_of, max_rows, dates) if docs else None
     from .engine import EngineError
     parts = [[] for _ in books]
     failed = {}
-    for d, (b, k) in enumerate(owner):
-        if k is None:
-            continue
-        st = int(res.status[d])
-        if st == _lib.DOC_EMPTY_SHEET:
-            continue  # `if df.empty: continue` (app/file_parser.py:228-229)
-        if st != _lib.DOC_OK:
-            failed[b] = EngineError(f"sheet {books[b].sheet_names[k]!r}: construct not decoded on the GPU path")
-            continue
-        parts[b].append(f"=== Sheet: {books[b].sheet_names[k]} ===\n" + res.doc_str(d))
+    with engine.lock:   # the pinned output is ours until the texts have been built
+        res = engine.sheets_batch(docs, kind, sst_of, max_rows, dates) if docs else None
+        for d, (b, k) in enumerate(owner):
+            if k is None:
+                continue
+            st = int(res.status[d])
+            if st == _lib.DOC_EMPTY_SHEET:
+                continue  # `if df.empty: continue` (app/file_parser.py:228-229)
+            if st != _lib.DOC_OK:
+                failed[b] = EngineError(f"sheet {books[b].sheet_names[k]!r}: construct not decoded on the GPU path")
+                continue
+            parts[b].append(f"=== Sheet: {books[b].sheet_names[k]} ===\n" + res.doc_str(d))
     return [failed[b] if b in failed else ("\n\n".join(p) if p else _EMPTY) for b, p in enumerate(parts)]

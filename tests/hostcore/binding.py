@@ -21,7 +21,7 @@ def lib():
     global _lib
     if _lib is None:
         so = HERE / "libhostcore.so"
-        srcs = [HERE / "hostcore.cpp"] + sorted((HERE.parent.parent / "replisense_rfq_b200/csrc").glob("*.cuh"))
+        srcs = [HERE / "hostcore.cpp"] + sorted((HERE.parent.parent / "replisense_rfq_b200/csrc").glob("*.cuh")) + sorted((HERE.parent.parent / "replisense_rfq_b200/csrc").glob("*.h"))
         if not so.exists() or any(s.stat().st_mtime > so.stat().st_mtime for s in srcs):
             subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-ffp-contract=off",
                                    "-o", str(so), str(HERE / "hostcore.cpp")])

@@ -107,6 +107,7 @@ int csv_attempt(const uint8_t* doc, uint64_t len, uint32_t sep, int64_t nrows, s
   std::vector<Rec> recs;
   uint64_t i = 0;
   if (len >= 3 && doc[0] == 0xEF && doc[1] == 0xBB && doc[2] == 0xBF) i = 3;
+  const uint64_t doc_begin = i;
   int st = ST_R;
   uint64_t ws_start = 0, cur_start = 0;
   uint32_t cur_f0 = 0;
@@ -117,7 +118,11 @@ int csv_attempt(const uint8_t* doc, uint64_t len, uint32_t sep, int64_t nrows, s
     int ns = csv_next(st, cl);
     if (st != ST_W && ns == ST_W) ws_start = i;
     if (ev & EV_REC_START) { cur_start = i; cur_f0 = (uint32_t)fend.size(); }
-    if (ev & EV_REC_START_WS) { cur_start = ws_start; cur_f0 = (uint32_t)fend.size(); }
+    if (ev & EV_REC_START_WS) {
+      cur_start = ws_start; cur_f0 = (uint32_t)fend.size();
+      // pandas walks back to the previous LF here: after a bare CR the outcome is an accident (unsupported)
+      if (ws_start > doc_begin && doc[ws_start - 1] != '\n') return 2;
+    }
     if (ev & EV_FIELD_END) fend.push_back(i);
     if (ev & EV_LINE_END) {
       recs.push_back({cur_start, cur_f0, (uint32_t)fend.size()});
@@ -243,7 +248,7 @@ int csv_attempt(const uint8_t* doc, uint64_t len, uint32_t sep, int64_t nrows, s
     if (j) out += ' ';
     out.append(lay[j].width - cp, ' ');
     if (numeric) out += ' ';
-    out += hdr.names[j];
+    out += hdr.disp[j];
   }
   std::vector<uint8_t> buf;
   for (uint32_t r = 0; r < ndata; ++r) {
@@ -477,19 +482,24 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
       raw[i2] = col; counts[col] = cur + 1;
     }
   }
+  bool int_index = false;
   if (all_int) {  // Int64 Index: labels left-justified to one width (only if dedupe changed nothing)
     bool distinct = true;
     for (uint32_t a = 0; a < W; ++a) for (uint32_t b = a + 1; b < W; ++b) if (raw[a] == raw[b]) distinct = false;
     bool digits_only = true;
     for (auto& x : raw) for (char ch : x) if (!((ch >= '0' && ch <= '9') || ch == '-')) digits_only = false;
     if (distinct && digits_only) {
+      int_index = true;
       size_t mx = 0;
       for (auto& x : raw) mx = std::max(mx, x.size());
       for (auto& x : raw) x.append(mx - x.size(), ' ');
     }
   }
   std::vector<uint32_t> ncp(W);
-  for (uint32_t c = 0; c < W; ++c) utf8_valid_count(raw[c], &ncp[c]);
+  bool names_valid = true;
+  for (uint32_t c = 0; c < W; ++c) if (!utf8_valid_count(raw[c], &ncp[c])) names_valid = false;
+  std::vector<std::string> disp = raw;
+  if (names_valid && !int_index) display_labels(raw, disp, ncp);
   // inference
   std::vector<uint32_t> xf(W, 0); std::vector<uint32_t> row_na(ndata, 0);
   for (uint32_t r = 0; r < ndata; ++r)
@@ -528,7 +538,7 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
       if (c) text += ' ';
       text.append(lay[c].width - cp, ' ');
       if (numeric) text += ' ';
-      text += raw[c];
+      text += disp[c];
     }
     std::vector<uint8_t> buf;
     for (uint32_t r = 0; r < ndata; ++r) {
