@@ -47,8 +47,8 @@ RFQ_HD uint64_t load8_masked(const uint8_t* p, uint32_t rem) {
 #ifdef __CUDA_ARCH__
   const unsigned long long* q = (const unsigned long long*)((uintptr_t)p & ~(uintptr_t)7);
   uint32_t sh = (uint32_t)((uintptr_t)p & 7u) * 8u;
-  x = __ldg(q);
-  if (sh) x = (x >> sh) | ((uint64_t)__ldg(q + 1) << (64u - sh));
+  x = *q;                                   // generic loads: p may point into a shared-memory stage
+  if (sh) x = (x >> sh) | ((uint64_t)q[1] << (64u - sh));
 #else
   x = 0;
   for (uint32_t i = 0; i < 8 && i < rem; ++i) x |= (uint64_t)p[i] << (8 * i);

@@ -1,0 +1,395 @@
+// Row walker of the CSV path: a thread that knows where a record starts finds its fields itself,
+// eight bytes at a time, instead of reading a field index from memory.
+//
+// Inside one record pandas' tokenizer (csv_dfa.cuh; tokenizer.c `tokenize_bytes`, reached from
+// app/file_parser.py:301) only moves between START_FIELD / IN_FIELD / IN_QUOTED_FIELD /
+// QUOTE_IN_QUOTED_FIELD: a field that starts with '"' runs to the quote that is not followed by another
+// quote, whatever follows that quote up to the next delimiter / LF / CR is literal; any other field runs
+// to the next delimiter / LF / CR and its quotes are literal.  The record start itself (blank lines,
+// CR LF pairs, the blanks that open a line) comes from the parallel DFA scan (csv2_scan.cu), so the two
+// always agree on where a record ends.
+//
+// While it looks for the end of a field the walker also learns what downstream code needs to know
+// about its bytes: control bytes (NUL cuts a token, TAB / LF / CR print as escapes), non-ASCII bytes,
+// "" pairs.  The result is the same CellSrc shapes csv_simplify() makes out of an indexed field
+// (CM_RAW clean / plain, CM_CSVQ, CM_CSV), so every per-cell function of cell_ops.cuh applies.
+#pragma once
+#include "cell_ops.cuh"
+
+namespace rfq {
+
+// 8 bytes at p + i, little endian, for a record that ends at `limit` (exclusive): bytes at or
+// beyond the limit read as LF (the virtual record terminator).  Reads up to 15 bytes past p + i:
+// every buffer this runs on (arena, shared-memory stage) carries 16 bytes of slack.
+RFQ_HD uint64_t row_window(const uint8_t* p, uint32_t i, uint32_t limit) {
+  const uint32_t rem = limit > i ? limit - i : 0u;
+  uint64_t x = load8_masked(p + i, rem);
+  if (rem < 8) x |= 0x0A0A0A0A0A0A0A0Aull & ~(rem ? ((1ull << (8 * rem)) - 1ull) : 0ull);
+  return x;
+}
+
+RFQ_HD uint32_t first_flag_byte(uint64_t flags) {   // index of the lowest byte whose 0x80 bit is set
+#ifdef __CUDA_ARCH__
+  return (uint32_t)(__ffsll((long long)flags) - 1) >> 3;
+#else
+  return (uint32_t)__builtin_ctzll(flags) >> 3;
+#endif
+}
+
+// bytes of x below index k kept, the others replaced by blanks (so they are neither control nor high)
+RFQ_HD uint64_t keep_below(uint64_t x, uint32_t k) {
+  const uint64_t m = k >= 8 ? ~0ull : ((1ull << (8 * k)) - 1ull);
+  return (x & m) | (0x2020202020202020ull & ~m);
+}
+
+struct FieldScan {
+  CellSrc src;
+  uint32_t next;   // position of the byte after the field's terminator
+  bool eol;        // the terminator ended the record (LF, CR or the limit)
+};
+
+// Field that starts at p[pos]; the record cannot extend beyond `limit`.  pos == limit is an empty
+// last field.
+RFQ_HD FieldScan scan_field(const uint8_t* p, uint32_t pos, uint32_t limit, uint32_t sep) {
+  const uint64_t ones = 0x0101010101010101ull, highs = 0x8080808080808080ull;
+  const uint64_t sep8 = ones * sep;
+  FieldScan r;
+  r.src.mode = CM_RAW; r.src.missing = false; r.src.clean = true; r.src.bits = 0;
+  r.src.p = p + pos; r.src.n = 0;
+  uint64_t acc = 0;        // 0x80 bits: some byte is non-ASCII; bit 0: some byte is a control byte
+  uint32_t i = pos;
+  uint32_t body = pos;     // where the unquoted scan starts (after a closed quote section: the junk)
+  bool quoted = false, junk = false;
+  uint32_t pairs = 0, close = 0;
+  if (pos < limit && p[pos] == '"') {
+    quoted = true;
+    i = pos + 1;
+    bool closed = false;
+    while (!closed) {
+      if (i >= limit) break;                               // unterminated: the record ends inside the quotes
+      const uint64_t x = load8_masked(p + i, limit - i);   // bytes beyond the limit read as zero (never a quote)
+      const uint64_t q = zero_bytes(x ^ (ones * '"'));
+      const uint32_t rem = limit - i;
+      if (!q) {
+        const uint64_t xm = rem < 8 ? keep_below(x, rem) : x;
+        acc |= (xm & highs) | (((xm - ones * 0x0E) & ~xm & highs) ? 1ull : 0ull);
+        i += 8;
+        continue;
+      }
+      const uint32_t k = first_flag_byte(q);
+      const uint64_t xm = keep_below(x, k);
+      acc |= (xm & highs) | (((xm - ones * 0x0E) & ~xm & highs) ? 1ull : 0ull);
+      const uint32_t j = i + k;                            // a quote inside the quoted section
+      const uint32_t c1 = j + 1 < limit ? p[j + 1] : '\n';
+      if (c1 == '"') { ++pairs; i = j + 2; continue; }
+      closed = true; close = j;
+      if (c1 == sep || c1 == '\n' || c1 == '\r') {         // the usual end: quote, then the terminator
+        const uint32_t inner = j - (pos + 1);
+        r.next = j + 2;
+        r.eol = c1 != sep;
+        if (acc & 1ull) { r.src.mode = CM_CSV; r.src.clean = false; r.src.n = j + 1 - pos; return r; }
+        r.src.p = p + pos + 1; r.src.n = inner;
+        if (pairs == 0) { r.src.clean = !(acc & highs); return r; }
+        if (!(acc & highs)) { r.src.mode = CM_CSVQ; r.src.clean = false; r.src.bits = inner - pairs; return r; }
+        r.src.mode = CM_CSV; r.src.clean = false; r.src.p = p + pos; r.src.n = j + 1 - pos;
+        return r;
+      }
+      junk = true; body = j + 1;                           // "x"y : literal bytes up to the terminator
+    }
+    if (!closed) {   // EOF inside string / record limit inside the quotes
+      r.src.mode = CM_CSV; r.src.clean = false; r.src.n = limit - pos;
+      r.next = limit + 1; r.eol = true;
+      return r;
+    }
+    i = body;
+  }
+  // unquoted bytes up to the delimiter / LF / CR / limit
+  for (;;) {
+    const uint64_t x = row_window(p, i, limit);
+    const uint64_t t = zero_bytes(x ^ sep8) | zero_bytes(x ^ (ones * 0x0A)) | zero_bytes(x ^ (ones * 0x0D));
+    if (!t) {
+      acc |= (x & highs) | (((x - ones * 0x0E) & ~x & highs) ? 1ull : 0ull);
+      i += 8;
+      continue;
+    }
+    const uint32_t k = first_flag_byte(t);
+    const uint64_t xm = keep_below(x, k);
+    acc |= (xm & highs) | (((xm - ones * 0x0E) & ~xm & highs) ? 1ull : 0ull);
+    const uint32_t e = i + k;
+    const uint32_t tb = (uint32_t)(x >> (8 * k)) & 0xFFu;
+    r.next = e + 1;
+    r.eol = tb != sep;
+    r.src.n = e - pos;
+    if (quoted || junk || (acc & 1ull)) { r.src.mode = CM_CSV; r.src.clean = false; }
+    else r.src.clean = !(acc & highs);
+    (void)close;
+    return r;
+  }
+}
+
+// The same field as the index-based fetch (fetch_cell + csv_simplify) would describe it: used by the
+// cold kernels, which re-find a cell from the start of its row.
+struct RowWalk {
+  const uint8_t* p;     // base pointer: p[pos] are document bytes
+  uint32_t pos, limit, sep;
+  bool eol;             // the record's terminator has been consumed
+  RFQ_HD RowWalk(const uint8_t* base, uint32_t start, uint32_t lim, uint32_t s) : p(base), pos(start), limit(lim), sep(s), eol(false) {}
+  RFQ_HD CellSrc next() {
+    if (eol) {            // short row: pandas pads with empty tokens
+      CellSrc s; s.mode = CM_CSV; s.missing = true; s.clean = false; s.p = p; s.n = 0; s.bits = 0;
+      return s;
+    }
+    FieldScan f = scan_field(p, pos, limit, sep);
+    pos = f.next; eol = f.eol;
+    return f.src;
+  }
+};
+
+// ---- the cells the hot kernels finish themselves ------------------------------------------------
+// Everything else (numbers that are not short decimal literals or small integers, text that needs the
+// quote state machine, non-ASCII numeric-looking tokens) goes to the fix-up kernels, which run the
+// general functions of cell_ops.cuh.  Keeping those out of the hot kernels is what lets them compile
+// to a small register count.
+// Does precise_xstrtod accept this token (cell_parse.cuh parse_double, without computing the value)?
+// 0 = no, 1 = yes, 2 = left to the general parser (an inf word, an exponent longer than 17 digits)
+RFQ_HD int float_shape(const uint8_t* p, uint32_t n) {
+  uint32_t i = 0;
+  while (i < n && is_space_ascii(p[i])) ++i;
+  if (i < n && (p[i] == '-' || p[i] == '+')) ++i;
+  if (i < n && (p[i] | 0x20u) == 'i') return 2;
+  uint32_t nd = 0;
+  while (i < n && is_digit_ascii(p[i])) { ++i; ++nd; }
+  if (i < n && p[i] == '.') {
+    ++i;
+    while (i < n && is_digit_ascii(p[i])) { ++i; ++nd; }
+  }
+  if (nd == 0) return 0;
+  if (i < n && (p[i] | 0x20u) == 'e') {
+    ++i;
+    if (i < n && (p[i] == '-' || p[i] == '+')) ++i;
+    uint32_t ne = 0;
+    while (i < n && is_digit_ascii(p[i])) { ++i; ++ne; }
+    if (ne == 0) return 0;
+    if (ne > 17) return 2;
+  }
+  while (i < n && is_space_ascii(p[i])) ++i;
+  return i < n ? 0 : 1;
+}
+
+// the inf words _try_double accepts after xstrtod fails: [+-]?(inf|infinity), any case, nothing around
+RFQ_HD bool inf_word(const uint8_t* p, uint32_t n) {
+  uint32_t i = (n && (p[0] == '+' || p[0] == '-')) ? 1u : 0u;
+  const uint32_t l = n - i;
+  if (l != 3 && l != 8) return false;
+  const char* w = "infinity";
+  for (uint32_t k = 0; k < l; ++k) if ((p[i + k] | 0x20u) != (uint32_t)w[k]) return false;
+  return true;
+}
+
+struct HotCand {
+  bool cold;            // not decided here
+  CellCand m;
+};
+
+RFQ_HD HotCand classify_measure_hot(const CellSrc& s) {
+  HotCand h;
+  h.cold = false;
+  CellCand& m = h.m;
+  m.flags = 0; m.int_status = INT_OK; m.na = false; m.has_float = false; m.need_exact = false;
+  m.str_len = 0; m.extra = 0; m.int_len = 0; m.uint_len = 0; m.bool_len = 0;
+  m.ip_len = 0; m.tz = 6; m.inf_len = 0; m.obj_len = 0; m.sci_len = 0; m.fl = 0;
+  if (s.missing) { m.flags = SF_ANY_NA; m.na = true; return h; }
+  if (s.mode == CM_CSV) { h.cold = true; return h; }
+  uint32_t nbytes, ncp;
+  uint64_t first8;
+  if (s.clean) { nbytes = s.n; ncp = s.n; first8 = s.n ? load8_masked(s.p, s.n) : 0; }
+  else if (s.mode == CM_CSVQ) {
+    nbytes = (uint32_t)s.bits; ncp = nbytes;
+    first8 = 0;
+    PairIter it(s.p, s.n);
+    for (int k = 0; k < 8; ++k) { int c = it.next(); if (c < 0) break; first8 |= (uint64_t)c << (8 * k); }
+  } else {   // plain span with non-ASCII bytes
+    TextInfo t = scan_text_raw(s.p, s.n);
+    if (!t.utf8_ok) m.flags |= SF_BAD_UTF8;
+    if (t.nesc) { h.cold = true; return h; }   // cannot happen (no control bytes), kept for safety
+    nbytes = t.nbytes; ncp = t.ncp; first8 = t.first8;
+  }
+  if (is_na_token(nbytes, first8)) { m.flags = SF_ANY_NA; m.na = true; return h; }
+  uint32_t f = m.flags | SF_ANY_NONNA;
+  m.str_len = ncp;
+  m.extra = nbytes - ncp;
+  const int bt = bool_token(nbytes, first8);
+  if (bt >= 0) m.bool_len = bt == 1 ? 4u : 5u;
+  const uint32_t c0 = (uint32_t)(first8 & 0xFFu);
+  if (!(is_digit_ascii((int)c0) || c0 == '+' || c0 == '-' || c0 == '.' || is_space_ascii((int)c0) ||
+        (c0 | 0x20u) == 'i')) {          // a plain word: no numeric grammar starts like this
+    m.int_status = INT_INVALID;
+    f |= SF_UINT_INVALID | SF_FLOAT_BAD | SF_PYINT_BAD;
+    if (bt < 0) f |= SF_BOOL_BAD;
+    m.flags = f;
+    return h;
+  }
+  if (!s.clean || s.mode != CM_RAW) { h.cold = true; return h; }   // numeric-looking but quoted-with-pairs / non-ASCII
+  int64_t iv;
+  const int st = parse_int64(RawIter(s.p, s.n), &iv);
+  m.int_status = st;
+  if (st == INT_OK) {
+    const uint64_t mag = iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv;
+    if (mag > (1ull << 53) || (iv == 0 && c0 != '0')) { h.cold = true; return h; }   // float view needs the exact parser; "-0", " 0", "+0"
+    if (iv < 0) f |= SF_NEG;
+    f |= SF_BOOL_BAD;
+    m.flags = f;
+    m.int_len = (uint32_t)int64_len(iv);
+    if (iv >= 0) m.uint_len = m.int_len;
+    m.has_float = true;
+    m.ip_len = m.int_len; m.tz = 6; m.obj_len = m.int_len - (iv < 0 ? 1u : 0u) + 3u;
+    m.sci_len = 12u + (iv < 0 ? 1u : 0u);
+    m.fl = MF_FINITE | (mag > 1000000ull ? MF_LARGE : 0);
+    return h;
+  }
+  if (st == INT_OVERFLOW) { h.cold = true; return h; }
+  Fixed6 d6;
+  if (!decimal_literal(s.p, s.n, &d6)) {
+    // not an integer: a date, a part number that starts with a digit, ... decided here when no
+    // grammar takes it; real floats beyond the literal shape go to the fix-up kernel
+    const uint32_t c1 = (c0 == '+' || c0 == '-') ? (uint32_t)((first8 >> 8) & 0xFFu) : c0;
+    if ((c1 | 0x20u) == 'i') {                 // INR, item, -inf: only the inf words are numbers
+      if (inf_word(s.p, s.n)) { h.cold = true; return h; }
+    } else if (float_shape(s.p, s.n) != 0) { h.cold = true; return h; }
+    uint32_t i = 0;
+    while (i < s.n && is_space_ascii(s.p[i])) ++i;
+    if (i < s.n && s.p[i] == '-') f |= SF_NEG; else f |= SF_UINT_INVALID;   // str_to_uint64: a leading '-' is "negative", not an error
+    f |= SF_FLOAT_BAD;
+    if (bt < 0) f |= SF_BOOL_BAD;
+    const int pp = pyint_prefix(first8, nbytes);
+    if (pp == 2) { h.cold = true; return h; }
+    if (pp == 0) f |= SF_PYINT_BAD;
+    m.flags = f;
+    return h;
+  }
+  // [+-]d{1,8}.d{1,6}: not an int64, not a uint64 (invalid, or "negative" for a leading '-'), never
+  // int()-parsable, not a bool; as float64 its "%.6f" digits are its own (cell_format.cuh)
+  if (c0 == '-') f |= SF_NEG; else f |= SF_UINT_INVALID;
+  f |= SF_PYINT_BAD | SF_BOOL_BAD;
+  m.flags = f;
+  m.has_float = true;
+  m.ip_len = (d6.neg ? 1u : 0u) + (uint32_t)d6.ip_digits; m.tz = (uint32_t)d6.tz;
+  m.obj_len = (uint32_t)objfloat_len(d6);
+  m.sci_len = 12u + (d6.neg ? 1u : 0u);
+  m.fl = MF_FINITE | ((d6.ip > 1000000ull || (d6.ip == 1000000ull && d6.frac)) ? MF_LARGE : 0);
+  return h;
+}
+
+// ---- the cells the hot emit sweep prints itself -------------------------------------------------
+// n bytes from src (any address space, any alignment) to dst (byte stores)
+RFQ_HD void copy_span(uint8_t* dst, const uint8_t* src, uint32_t n) {
+  uint32_t i = 0;
+  for (; i + 8 <= n; i += 8) {
+    const uint64_t x = load8_masked(src + i, 8);
+    const uint32_t lo = (uint32_t)x, hi = (uint32_t)(x >> 32);
+    uint8_t* d = dst + i;
+    d[0] = (uint8_t)lo; d[1] = (uint8_t)(lo >> 8); d[2] = (uint8_t)(lo >> 16); d[3] = (uint8_t)(lo >> 24);
+    d[4] = (uint8_t)hi; d[5] = (uint8_t)(hi >> 8); d[6] = (uint8_t)(hi >> 16); d[7] = (uint8_t)(hi >> 24);
+  }
+  if (i < n) {
+    const uint64_t x = load8_masked(src + i, n - i);
+    for (uint32_t q = 0; i + q < n; ++q) dst[i + q] = (uint8_t)(x >> (8 * q));
+  }
+}
+
+// One cell printed right-justified into its (blank-filled) field.  Returns 0 = done, 1 = the row
+// goes to the fix-up kernel.  *extra receives printed bytes - printed code points.
+RFQ_HD int emit_hot(const CellSrc& s, int ct, int kind, int dec, uint32_t width,
+                                        uint8_t* field, uint32_t* extra) {
+  *extra = 0;
+  if (s.missing) return 0;
+  if (s.mode == CM_CSV) return 1;
+  uint32_t nbytes;
+  uint64_t first8;
+  if (s.clean) { nbytes = s.n; first8 = s.n ? load8_masked(s.p, s.n) : 0; }
+  else if (s.mode == CM_CSVQ) {
+    nbytes = (uint32_t)s.bits; first8 = 0x2020202020202020ull;
+    if (nbytes <= 8) {   // only short tokens can be NA words
+      first8 = 0;
+      PairIter it(s.p, s.n);
+      for (int k = 0; k < 8; ++k) { int c = it.next(); if (c < 0) break; first8 |= (uint64_t)c << (8 * k); }
+    }
+  } else { nbytes = s.n; first8 = s.n ? load8_masked(s.p, s.n) : 0; }
+  if (ct != CT_STRNF && is_na_token(nbytes, first8)) return 0;   // NaN -> '' after fillna: the blanks are there already
+  switch (kind) {
+    case PR_STR: {
+      if (s.mode == CM_CSVQ) {
+        uint8_t* o = field + (width - nbytes);
+        PairIter it(s.p, s.n);
+        int c;
+        while ((c = it.next()) >= 0) *o++ = (uint8_t)c;
+        return 0;
+      }
+      uint32_t cont = 0;
+      if (!s.clean) {   // plain span with non-ASCII bytes (valid UTF-8: the typing sweep checked): count continuation bytes
+        const uint64_t highs = 0x8080808080808080ull;
+        for (uint32_t i = 0; i < s.n; i += 8) {
+          const uint64_t x = load8_masked(s.p + i, s.n - i);
+#ifdef __CUDA_ARCH__
+          cont += (uint32_t)__popcll(x & ~(x << 1) & highs);
+#else
+          cont += (uint32_t)__builtin_popcountll(x & ~(x << 1) & highs);
+#endif
+        }
+      }
+      copy_span(field + (width - (s.n - cont)), s.p, s.n);
+      *extra = cont;
+      return 0;
+    }
+    case PR_BOOL: {
+      const int bv = bool_token(nbytes, first8);
+      if (bv < 0 || !s.clean) return 1;
+      const uint32_t w4 = bv == 1 ? 0x65757254u /* True */ : 0x736C6146u /* Fals */;
+      uint8_t* o = field + (width - (bv == 1 ? 4u : 5u));
+      o[0] = (uint8_t)w4; o[1] = (uint8_t)(w4 >> 8); o[2] = (uint8_t)(w4 >> 16); o[3] = (uint8_t)(w4 >> 24);
+      if (bv == 0) o[4] = 'e';
+      return 0;
+    }
+    case PR_INT: {
+      if (!s.clean || s.mode != CM_RAW) return 1;
+      const uint32_t b0 = (uint32_t)(first8 & 0xFFu), b1 = (uint32_t)((first8 >> 8) & 0xFFu);
+      const uint32_t last = s.p[s.n - 1];
+      const bool canon = (uint32_t)(last - '0') < 10u &&
+                         ((uint32_t)(b0 - '1') < 9u || (b0 == '-' && (uint32_t)(b1 - '1') < 9u) || (s.n == 1 && b0 == '0'));
+      if (canon) { copy_span(field + (width - s.n), s.p, s.n); return 0; }   // an int64 token in canonical form prints as itself
+      int64_t iv = 0;
+      if (parse_int64(RawIter(s.p, s.n), &iv) != INT_OK) return 1;
+      const uint32_t n = (uint32_t)int64_len(iv);
+      uint8_t* o = field + (width - n);
+      write_u64_rev(iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv, o + n);
+      if (iv < 0) o[0] = '-';
+      return 0;
+    }
+    case PR_FIXED: case PR_OBJFLOAT: {
+      if (!s.clean || s.mode != CM_RAW) return 1;
+      Fixed6 d6;
+      if (ct == CT_INT || ct == CT_INTNA) {   // integer tokens of a float column: digits + ".000000"
+        int64_t iv = 0;
+        if (parse_int64(RawIter(s.p, s.n), &iv) != INT_OK) return 1;
+        const uint64_t mag = iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv;
+        if (mag > (1ull << 53)) return 1;
+        d6.neg = iv < 0; d6.inf = false; d6.big = false; d6.ip = mag; d6.frac = 0; d6.ip_digits = ndigits_u64(mag); d6.tz = 6;
+      } else if (!decimal_literal(s.p, s.n, &d6)) {   // a short decimal literal prints its own digits (cell_format.cuh)
+        int64_t iv = 0;                               // "100" next to "99.5": xstrtod makes the same value of it
+        if (parse_int64(RawIter(s.p, s.n), &iv) != INT_OK) return 1;
+        const uint64_t mag = iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv;
+        if (mag > (1ull << 53) || (iv == 0 && s.p[0] != '0')) return 1;   // beyond exact doubles; "-0"
+        d6.neg = iv < 0; d6.inf = false; d6.big = false; d6.ip = mag; d6.frac = 0; d6.ip_digits = ndigits_u64(mag); d6.tz = 6;
+      }
+      uint8_t buf[24];
+      const int dd = kind == PR_FIXED ? dec : objfloat_dec(d6);
+      const int n = fixed_write(d6, 0., dd, kind == PR_OBJFLOAT, buf);
+      uint8_t* o = field + (width - (uint32_t)n);
+      for (int q = 0; q < n; ++q) o[q] = buf[q];
+      return 0;
+    }
+    default: return 1;   // uint64, "%.6e", Python ints
+  }
+}
+
+}  // namespace rfq

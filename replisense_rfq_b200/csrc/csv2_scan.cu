@@ -1,0 +1,275 @@
+// One-pass row scan (SURVEY.md §7.1b K1 + K2): pandas' tokenizer state machine (csv_dfa.cuh; tokenizer.c
+// `tokenize_bytes`, reached from app/file_parser.py:301) run over all documents of an attempt in ONE
+// sweep of their bytes.  The only thing it leaves behind is where every record starts — fields are found
+// again by the row kernels while they read the bytes anyway (csv2_rows.cuh).
+//
+// A CTA takes 16 KB chunks in ticket order.  Per chunk: every lane turns its 16 bytes into a
+// state -> state transition function (8 states as nibbles, composed with PRMT), functions are
+// composed per tile, per warp, per chunk; the chunk's function is published and the state the chunk
+// starts in comes from a decoupled look-back over the chunks before it.  Then the lanes replay their
+// bytes from the now-known states (only bytes that can change the state are visited), record starts
+// and record ends are kept as bit masks in registers, the number of records since the start of the
+// document is carried across chunks by a second (segmented) look-back, and every record start is
+// written to its slot.  Documents begin on 16-byte boundaries and tiles never span documents; the end
+// of a document is a virtual LF.  The bytes are read from HBM exactly once: no tensor cores, by design.
+#include <cuda_runtime.h>
+#include <algorithm>
+#include "csv2.h"
+#include "csv_scan_core.cuh"
+#include "launch.h"
+
+namespace rfq {
+
+// look-back descriptor: bits 63..62 status, low bits payload
+#define RFQ2_AGG 1ull
+#define RFQ2_INC 2ull
+#define RFQ2_SEG_FLAG (1ull << 40)            // segmented count: a document starts inside
+#define RFQ2_SEG_MASK ((1ull << 40) - 1ull)
+
+__device__ __forceinline__ unsigned long long ld_desc(const unsigned long long* p) {
+  return *(const volatile unsigned long long*)p;
+}
+__device__ __forceinline__ void st_desc(unsigned long long* p, unsigned long long v) {
+  *(volatile unsigned long long*)p = v;
+}
+// records since the last document start: a happens before b
+__device__ __forceinline__ unsigned long long seg_op(unsigned long long a, unsigned long long b) {
+  if (b & RFQ2_SEG_FLAG) return b;
+  return (a & RFQ2_SEG_FLAG) | (((a & RFQ2_SEG_MASK) + (b & RFQ2_SEG_MASK)) & RFQ2_SEG_MASK);
+}
+
+// exclusive prefix of the transition functions of chunks [0, chunk); publishes this chunk's
+// aggregate, then its inclusive prefix.  Called by all 32 lanes of one warp.
+__device__ uint32_t lookback_fn(unsigned long long* desc, uint32_t chunk, uint32_t agg, int lane) {
+  if (lane == 0) st_desc(desc + chunk, ((chunk == 0 ? RFQ2_INC : RFQ2_AGG) << 62) | agg);
+  if (chunk == 0) return RFQ_FN_IDENTITY;
+  uint32_t acc = RFQ_FN_IDENTITY;
+  int base = (int)chunk - 1;
+  for (;;) {
+    const int idx = base - lane;
+    unsigned long long v = (RFQ2_INC << 62) | RFQ_FN_IDENTITY;   // before chunk 0: nothing happened
+    if (idx >= 0) { do { v = ld_desc(desc + idx); } while ((v >> 62) == 0ull); }
+    const unsigned inc = __ballot_sync(0xffffffffu, (v >> 62) == RFQ2_INC);
+    const int nl = inc ? __ffs(inc) : 32;                        // lanes [0, nl) take part
+    uint32_t f = lane < nl ? (uint32_t)v : RFQ_FN_IDENTITY;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {                           // lane l + o is the earlier chunk
+      const uint32_t g = __shfl_down_sync(0xffffffffu, f, o);
+      if (lane + o < 32) f = fn_compose(g, f);
+    }
+    f = __shfl_sync(0xffffffffu, f, 0);
+    acc = fn_compose(f, acc);
+    if (inc) break;
+    base -= 32;
+  }
+  if (lane == 0) st_desc(desc + chunk, (RFQ2_INC << 62) | fn_compose(acc, agg));
+  return acc;
+}
+
+// the same for the segmented record counts (a chunk in which a document starts ends the walk)
+__device__ unsigned long long lookback_seg(unsigned long long* desc, uint32_t chunk, unsigned long long agg, int lane) {
+  if (lane == 0) st_desc(desc + chunk, ((chunk == 0 ? RFQ2_INC : RFQ2_AGG) << 62) | agg);
+  if (chunk == 0) return 0ull;
+  unsigned long long acc = 0ull;
+  int base = (int)chunk - 1;
+  for (;;) {
+    const int idx = base - lane;
+    unsigned long long v = (RFQ2_INC << 62);
+    if (idx >= 0) { do { v = ld_desc(desc + idx); } while ((v >> 62) == 0ull); }
+    const unsigned stop = __ballot_sync(0xffffffffu, (v >> 62) == RFQ2_INC || (v & RFQ2_SEG_FLAG));
+    const int nl = stop ? __ffs(stop) : 32;
+    unsigned long long f = lane < nl ? (v & (RFQ2_SEG_FLAG | RFQ2_SEG_MASK)) : 0ull;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned long long g = __shfl_down_sync(0xffffffffu, f, o);
+      if (lane + o < 32) f = seg_op(g, f);
+    }
+    f = __shfl_sync(0xffffffffu, f, 0);
+    acc = seg_op(f, acc);
+    if (stop) break;
+    base -= 32;
+  }
+  if (lane == 0) st_desc(desc + chunk, (RFQ2_INC << 62) | seg_op(acc, agg));
+  return acc;
+}
+
+__global__ void __launch_bounds__(256) csv2_scan_kernel(Csv2Args a) {
+  RFQ_INIT_CLASS_FN();
+  __shared__ uint32_t pair_fn[128];
+  if (threadIdx.x < 128) pair_fn[threadIdx.x] = fn_compose(class_fn[threadIdx.x & 7u], class_fn[(threadIdx.x >> 4) & 7u]);
+  __shared__ uint32_t s_chunk, s_wfn[8], s_start_state;
+  __shared__ unsigned long long s_wseg[8], s_seg_in;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  (void)class_ev;
+  for (;;) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_chunk = atomicAdd(a.ticket, 1u);
+    __syncthreads();
+    const uint32_t chunk = s_chunk;
+    if (chunk >= a.n_chunks) break;
+    const uint32_t t0 = chunk * RFQ2_SCAN_TILES + (uint32_t)w * 4u;
+    // ---- 1. byte classes, lane / tile / warp transition functions
+    unsigned long long cls[4];
+    uint32_t lfn[4], tfn[4];
+    uint32_t wf = RFQ_FN_IDENTITY;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t t = t0 + q;
+      cls[q] = 0ull; lfn[q] = RFQ_FN_IDENTITY; tfn[q] = RFQ_FN_IDENTITY;
+      if (t < a.n_tiles) {
+        const uint32_t d = scan_find_doc(a.tile_base, a.n_docs, t);
+        const uint32_t tile = t - __ldg(a.tile_base + d);
+        const uint32_t len = a.docs[d].len;
+        const uint8_t* doc = a.arena + a.docs[d].off;
+        const bool bom = tile == 0 && doc_has_bom(doc, len);
+        const LaneBytes lb = load_lane_classes(doc, len, tile * RFQ_TILE + lane * 16, a.docs[d].sep, bom);
+        uint32_t f = lane_function(lb.cls, pair_fn);
+        cls[q] = lb.cls; lfn[q] = f;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t g = __shfl_down_sync(0xffffffffu, f, o);
+          if ((lane & (2 * o - 1)) == 0) f = fn_compose(f, g);
+        }
+        f = __shfl_sync(0xffffffffu, f, 0);
+        if (tile == 0) f = fn_const(fn_apply(f, ST_R));   // a document starts in ST_R whatever came before
+        tfn[q] = f;
+        wf = fn_compose(wf, f);
+      }
+    }
+    if (lane == 0) s_wfn[w] = wf;
+    __syncthreads();
+    // ---- 2. the state this chunk starts in
+    if (w == 0) {
+      uint32_t cf = RFQ_FN_IDENTITY;
+#pragma unroll
+      for (int v = 0; v < 8; ++v) cf = fn_compose(cf, s_wfn[v]);
+      const uint32_t pre = lookback_fn(a.fn_desc, chunk, cf, lane);
+      if (lane == 0) s_start_state = (uint32_t)fn_apply(pre, ST_R);
+    }
+    __syncthreads();
+    int st = (int)s_start_state;
+    for (int v = 0; v < w; ++v) st = fn_apply(s_wfn[v], st);
+    // ---- 3. replay: record starts / ends of every lane as bit masks, counts
+    uint32_t ev[4];      // bits 0-15 record starts, 16-31 starts after leading blanks
+    uint32_t le[4];      // bits 0-15 record ends, 16-25 records of the lanes before this one in the tile
+    uint32_t tot[4];     // records of the tile
+    unsigned long long wseg = 0ull;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t t = t0 + q;
+      ev[q] = 0; le[q] = 0; tot[q] = 0;
+      if (t < a.n_tiles) {
+        const uint32_t d = scan_find_doc(a.tile_base, a.n_docs, t);
+        const uint32_t tile = t - __ldg(a.tile_base + d);
+        const uint32_t len = a.docs[d].len;
+        const uint32_t base = tile * RFQ_TILE + lane * 16;
+        uint32_t incl = lfn[q];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t g = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl = fn_compose(g, incl);
+        }
+        uint32_t excl = __shfl_up_sync(0xffffffffu, incl, 1);
+        if (lane == 0) excl = RFQ_FN_IDENTITY;
+        int s1 = fn_apply(excl, tile == 0 ? ST_R : st);
+        const uint32_t eof_k = (len >= base && len < base + 16) ? len - base : 0xFFu;
+        // an ordinary byte after an ordinary byte changes nothing: visit the others, and the first
+        // ordinary byte after one of them (or at the start of the lane)
+        unsigned long long tt = cls[q];
+        tt = (tt | (tt >> 1) | (tt >> 2) | (tt >> 3)) & 0x1111111111111111ull;
+        tt = (tt | (tt >> 3)) & 0x0303030303030303ull;
+        tt = (tt | (tt >> 6)) & 0x000F000F000F000Full;
+        tt = (tt | (tt >> 12)) & 0x000000FF000000FFull;
+        const uint32_t nz = (uint32_t)(tt | (tt >> 24)) & 0xFFFFu;
+        uint32_t sm = 0, wm = 0, lm = 0;
+        for (uint32_t m = (nz | (nz << 1) | 1u) & 0xFFFFu; m; m &= m - 1) {
+          const int kk = __ffs(m) - 1;
+          const uint2 fe = class_fe[(uint32_t)(cls[q] >> (4 * kk)) & 0xFu];
+          const uint32_t e = (fe.y >> (4 * s1)) & 0xFu;
+          if ((uint32_t)kk == eof_k) a.run[d].final_state = (uint32_t)s1;   // state before the virtual LF
+          if (e) {
+            if (e & EV_REC_START) sm |= 1u << kk;
+            if (e & EV_REC_START_WS) wm |= 1u << kk;
+            if (e & EV_LINE_END) lm |= 1u << kk;
+          }
+          s1 = (int)((fe.x >> (4 * s1)) & 0xFu);
+        }
+        const uint32_t nl = (uint32_t)__popc(lm);
+        uint32_t pl = nl;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t x = __shfl_up_sync(0xffffffffu, pl, o);
+          if (lane >= o) pl += x;
+        }
+        ev[q] = sm | (wm << 16);
+        le[q] = lm | ((pl - nl) << 16);
+        tot[q] = __shfl_sync(0xffffffffu, pl, 31);
+        wseg = seg_op(wseg, (unsigned long long)tot[q] | (tile == 0 ? RFQ2_SEG_FLAG : 0ull));
+        st = fn_apply(tfn[q], st);
+      }
+    }
+    if (lane == 0) s_wseg[w] = wseg;
+    __syncthreads();
+    // ---- 4. records since the start of the document, before this chunk
+    if (w == 0) {
+      unsigned long long cs = 0ull;
+#pragma unroll
+      for (int v = 0; v < 8; ++v) cs = seg_op(cs, s_wseg[v]);
+      const unsigned long long pre = lookback_seg(a.cnt_desc, chunk, cs, lane);
+      if (lane == 0) s_seg_in = pre;
+    }
+    __syncthreads();
+    unsigned long long seg = s_seg_in;
+    for (int v = 0; v < w; ++v) seg = seg_op(seg, s_wseg[v]);
+    // ---- 5. write the record starts
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t t = t0 + q;
+      if (t < a.n_tiles) {
+        const uint32_t d = scan_find_doc(a.tile_base, a.n_docs, t);
+        const uint32_t tile = t - __ldg(a.tile_base + d);
+        const Doc2& D = a.docs[d];
+        const uint32_t len = D.len;
+        const uint32_t base = tile * RFQ_TILE + lane * 16;
+        const uint32_t rec0 = (tile == 0 ? 0u : (uint32_t)(seg & RFQ2_SEG_MASK)) + (le[q] >> 16);
+        const uint32_t lm = le[q] & 0xFFFFu;
+        uint32_t* out = a.rec_start + D.slot_base;
+        for (uint32_t m = (ev[q] | (ev[q] >> 16)) & 0xFFFFu; m; m &= m - 1) {
+          const uint32_t kk = (uint32_t)__ffs(m) - 1u;
+          const uint32_t idx = rec0 + (uint32_t)__popc(lm & ((1u << kk) - 1u));
+          if (idx > D.max_rows + 1u) continue;      // records beyond 1 + nrows are never read
+          uint32_t pos = base + kk;
+          if ((ev[q] >> 16) & (1u << kk)) {
+            // the blanks that opened this line belong to its first field: walk back over them
+            const uint8_t* doc = a.arena + D.off;
+            const uint32_t doc_begin = doc_has_bom(doc, len) ? 3u : 0u;
+            while (pos > doc_begin) {
+              const uint32_t c = doc[pos - 1];
+              if ((c == ' ' || c == '\t') && c != D.sep) --pos; else break;
+            }
+            // pandas finds the start of such a line by walking back to the previous '\n' (tokenizer.c,
+            // WHITESPACE_LINE: only LF stops it).  After a bare CR, or after the delimiter a skipped
+            // blank line swallowed, it runs into earlier rows and the outcome depends on its read-buffer
+            // positions: not reproduced, the document is declined.
+            if (pos > doc_begin && doc[pos - 1] != '\n') atomicOr(&a.run[d].flags, (uint32_t)RUN_UNSUP);
+          }
+          out[idx] = pos;
+        }
+        if (len >= base && len < base + 16) a.run[d].n_rec = rec0 + (uint32_t)__popc(lm);
+        seg = seg_op(seg, (unsigned long long)tot[q] | (tile == 0 ? RFQ2_SEG_FLAG : 0ull));
+      }
+    }
+  }
+}
+
+void csv2_scan(const Csv2Args& a, cudaStream_t s) {
+  if (a.n_chunks == 0) return;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const uint32_t grid = std::min<uint32_t>(a.n_chunks, (uint32_t)sms * 6u);
+  prof_mark("csv2_scan_kernel", s);
+  RFQ_LAUNCH(csv2_scan_kernel, grid, 256, 0, s, a);
+}
+
+}  // namespace rfq

@@ -1,0 +1,393 @@
+// Typing sweep of the row pipeline (SURVEY.md §7.1b K3 + K4): what `pd.read_csv` does after
+// tokenising — NA set, int64 / uint64 / float64 / bool / str inference per low_memory chunk — fused with
+// the measurements `to_string` needs (printed width of every cell under every type its column can still
+// become), app/file_parser.py:301-305.
+//
+// Work item = RFQ2_ROWS consecutive data rows of one document (never across a low_memory chunk
+// boundary).  The item's bytes are one contiguous span of the arena: one thread brings it into shared
+// memory with a bulk asynchronous copy (cp.async.bulk + mbarrier), then every thread walks ONE row out
+// of the stage (csv2_rows.cuh), so the lanes of a warp sit on the same column at the same time and
+// their unaligned 8-byte windows are shared-memory reads, not 32 different L1 lines.  Cells the hot
+// classifier does not decide (exact float parsing, integers beyond 2^53, text that needs the quote
+// state machine) are appended to a list and finished by csv2_type_cold_kernel with the general
+// functions of cell_ops.cuh; keeping those out of this kernel keeps its register count small.
+// HBM-bound byte work: no tensor cores, by design.
+#include <algorithm>
+#include <atomic>
+#include "csv2.h"
+#include "csv2_rows.cuh"
+#include "csv2_stage.cuh"
+#include "csv_dfa.cuh"
+#include "launch.h"
+#include "scan.cuh"
+#include "table_common.cuh"
+
+namespace rfq {
+
+// ---- per document, right after the scan: rows used, attempt-level failures ---------------------
+__global__ void __launch_bounds__(128) csv2_docprep_kernel(Csv2Args a) {
+  const uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= a.n_docs) return;
+  const Doc2& D = a.docs[d];
+  DocRun R = a.run[d];
+  uint32_t fl = R.flags;
+  if (R.n_rec == 0) fl |= RUN_FAIL;                                                    // EmptyDataError
+  if (R.final_state == ST_Q && (unsigned long long)R.n_rec < (unsigned long long)D.max_rows + 1ull) fl |= RUN_FAIL;   // EOF inside string
+  R.n_data = R.n_rec ? min(R.n_rec - 1u, D.max_rows) : 0u;
+  R.flags = fl;
+  a.run[d] = R;
+}
+
+enum { S_FLAGS = 0, S_BAD, S_OVF, S_UINV, S_UOVF, S_STR, S_INT, S_UINT, S_BOOL, S_IP, S_TZ, S_OBJ, S_SCI, S_FL,
+       S_NA, S_COUNT };
+#define RFQ2_TYPE_STAGE (24u << 10)
+
+#define SMAXC(arr, v) do { const uint32_t v_ = (v); if (v_ > (arr)[c]) atomicMax(&(arr)[c], v_); } while (0)
+
+__global__ void __launch_bounds__(RFQ2_ROWS) csv2_type_kernel(Csv2Args a, uint32_t max_w) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  uint8_t* s_stage = smem;
+  uint32_t* s_arr = reinterpret_cast<uint32_t*>(smem + RFQ2_TYPE_STAGE + 32);
+  __shared__ __align__(8) unsigned long long s_bar;
+  __shared__ uint32_t s_doc, s_red[2];
+  if (threadIdx.x == 0) mbar_init(&s_bar, 1);
+  mbar_init_fence();
+  __syncthreads();
+  uint32_t phase = 0;
+  for (uint32_t item = blockIdx.x; item < a.n_items; item += gridDim.x) {
+    if (threadIdx.x == 0) { s_doc = ub_search(a.item_base, a.n_docs, item); s_red[0] = 0; s_red[1] = 0; }
+    __syncthreads();
+    const uint32_t d = s_doc;
+    const Doc2 D = a.docs[d];
+    const DocRun R = a.run[d];
+    const uint32_t row0 = (item - D.item_base) * RFQ2_ROWS;
+    if ((R.flags & (RUN_FAIL | RUN_UNSUP)) || row0 >= R.n_data) { __syncthreads(); continue; }
+    const uint32_t nrows = min(RFQ2_ROWS, R.n_data - row0);
+    const uint32_t chunk = row0 / D.bl;
+    const uint32_t W = D.W;
+    const uint32_t slot0 = D.slot_base + 1u + row0;
+    // ---- stage the item's bytes
+    const uint32_t start = __ldg(a.rec_start + slot0);
+    const uint32_t e_idx = 1u + row0 + nrows;
+    const uint32_t end = e_idx < R.n_rec ? __ldg(a.rec_start + D.slot_base + e_idx) : D.len;
+    const uint32_t g_lo = (D.off + start) & ~15u;
+    const uint32_t g_hi = (D.off + end + 31u) & ~15u;       // 16 bytes of slack for the window loads
+    const bool staged = g_hi - g_lo <= RFQ2_TYPE_STAGE;
+    if (threadIdx.x == 0) {
+      if (staged) bulk_load(s_stage, a.arena + g_lo, g_hi - g_lo, &s_bar);
+      if (g_hi - g_lo > a.counters[3]) atomicMax(a.counters + 3, g_hi - g_lo);   // sizes the next run's emit stage
+    }
+    for (uint32_t c = threadIdx.x; c < W * S_COUNT; c += blockDim.x) s_arr[c] = 0;
+    const uint8_t* base = staged ? s_stage - (size_t)(g_lo - D.off) : a.arena + D.off;   // base[pos] = document byte pos
+    if (staged) mbar_wait(&s_bar, phase), phase ^= 1u;
+    __syncthreads();
+    uint32_t* s_flags = s_arr + S_FLAGS * W; uint32_t* s_bad = s_arr + S_BAD * W; uint32_t* s_ovf = s_arr + S_OVF * W;
+    uint32_t* s_uinv = s_arr + S_UINV * W; uint32_t* s_uovf = s_arr + S_UOVF * W; uint32_t* s_str = s_arr + S_STR * W;
+    uint32_t* s_int = s_arr + S_INT * W; uint32_t* s_uint = s_arr + S_UINT * W; uint32_t* s_bool = s_arr + S_BOOL * W;
+    uint32_t* s_ip = s_arr + S_IP * W; uint32_t* s_tz = s_arr + S_TZ * W; uint32_t* s_obj = s_arr + S_OBJ * W;
+    uint32_t* s_sci = s_arr + S_SCI * W; uint32_t* s_fl = s_arr + S_FL * W; uint32_t* s_na = s_arr + S_NA * W;
+    uint32_t allna = 0, extra = 0;
+    if (threadIdx.x < nrows) {
+      const uint32_t slot = slot0 + threadIdx.x, row = row0 + threadIdx.x;
+      const uint32_t rs = threadIdx.x == 0 ? start : __ldg(a.rec_start + slot);
+      const uint32_t limit = (2u + row < R.n_rec) ? __ldg(a.rec_start + slot + 1) : D.len;
+      RowWalk w(base, rs, limit, D.sep);
+      uint32_t na = 0;
+      const uint32_t inv_row = ~row;
+      for (uint32_t c = 0; c < W; ++c) {
+        const CellSrc src = w.next();
+        const HotCand hc = classify_measure_hot(src);
+        if (hc.cold) {
+          const uint32_t k = atomicAdd(a.counters + 0, 1u);
+          if (k < a.cold_cells_cap) a.cold_cells[k] = ColdCell{d, slot, c};
+          else atomicOr(&a.run[d].flags, (uint32_t)RUN_GENERAL);
+          continue;
+        }
+        const CellCand& m = hc.m;
+        const uint32_t f = m.flags;
+        if ((s_flags[c] & f) != f) atomicOr(&s_flags[c], f);
+        // the lanes of a warp sit on the same column: one shared-memory add per warp for its NA cells
+        const unsigned am = __activemask();
+        const unsigned nm = __ballot_sync(am, m.na);
+        if (m.na) {
+          if ((threadIdx.x & 31u) == (uint32_t)(__ffs(nm) - 1)) atomicAdd(&s_na[c], (uint32_t)__popc(nm));
+          if (c >= D.lead) ++na;
+          continue;
+        }
+        if (m.int_status != INT_OK) {
+          SMAXC(s_bad, inv_row);
+          if (m.int_status == INT_OVERFLOW) SMAXC(s_ovf, inv_row);
+          if (f & SF_UINT_INVALID) SMAXC(s_uinv, inv_row);
+          if (f & SF_UINT_OVF) SMAXC(s_uovf, inv_row);
+        }
+        SMAXC(s_str, m.str_len); SMAXC(s_int, m.int_len); SMAXC(s_uint, m.uint_len); SMAXC(s_bool, m.bool_len);
+        if (m.has_float) {
+          SMAXC(s_ip, m.ip_len); SMAXC(s_tz, 6u - m.tz); SMAXC(s_obj, m.obj_len); SMAXC(s_sci, m.sci_len);
+          if ((s_fl[c] & m.fl) != m.fl) atomicOr(&s_fl[c], m.fl);
+        }
+        if (c >= D.lead) extra += m.extra;
+      }
+      if (!w.eol) atomicOr(&a.run[d].flags, (uint32_t)RUN_FAIL);   // "Expected N fields in line K, saw M"
+      a.row_na[slot] = na;
+      a.row_extra[slot] = extra;
+      allna = na == D.h ? 1u : 0u;
+    }
+    // item totals: rows whose output cells are all NA, extra bytes
+    {
+      const unsigned bm = __ballot_sync(0xffffffffu, allna != 0);
+      uint32_t ex = extra;
+#pragma unroll
+      for (int o = 16; o; o >>= 1) ex += __shfl_xor_sync(0xffffffffu, ex, o);
+      if ((threadIdx.x & 31u) == 0) { if (bm) atomicAdd(&s_red[0], (uint32_t)__popc(bm)); if (ex) atomicAdd(&s_red[1], ex); }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      a.item_allna[item] = s_red[0];
+      a.item_extra[item] = s_red[1];
+      if (s_red[0]) atomicAdd(a.chunk_allna + D.stat_base + chunk * W, s_red[0]);
+    }
+    for (uint32_t c = threadIdx.x; c < W; c += blockDim.x) {
+      StatV2* S = a.stat + D.stat_base + chunk * W + c;
+      if (s_flags[c]) atomicOr(&S->flags, s_flags[c]);
+      if (s_bad[c]) atomicMax(&S->inv_bad, s_bad[c]);
+      if (s_ovf[c]) atomicMax(&S->inv_ovf, s_ovf[c]);
+      if (s_uinv[c]) atomicMax(&S->inv_uinv, s_uinv[c]);
+      if (s_uovf[c]) atomicMax(&S->inv_uovf, s_uovf[c]);
+      if (s_str[c]) atomicMax(&S->str_len, s_str[c]);
+      if (s_int[c]) atomicMax(&S->int_len, s_int[c]);
+      if (s_uint[c]) atomicMax(&S->uint_len, s_uint[c]);
+      if (s_bool[c]) atomicMax(&S->bool_len, s_bool[c]);
+      if (s_ip[c]) atomicMax(&S->ip_len, s_ip[c]);
+      if (s_tz[c]) atomicMax(&S->inv_tz, s_tz[c]);
+      if (s_obj[c]) atomicMax(&S->obj_len, s_obj[c]);
+      if (s_sci[c]) atomicMax(&S->sci_len, s_sci[c]);
+      if (s_fl[c]) atomicOr(&S->fl, s_fl[c]);
+      if (s_na[c]) atomicAdd(&S->na_count, s_na[c]);
+    }
+    __syncthreads();
+  }
+}
+
+// ---- fix-up: the cells the hot sweep left, one thread each, general functions --------------------
+__global__ void __launch_bounds__(128) csv2_type_cold_kernel(Csv2Args a) {
+  const uint32_t n = min(a.counters[0], a.cold_cells_cap);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const ColdCell cc = a.cold_cells[i];
+    const Doc2& D = a.docs[cc.doc];
+    const DocRun& R = a.run[cc.doc];
+    const uint32_t k_idx = cc.slot - D.slot_base;          // record index (1 = first data row)
+    const uint32_t row = k_idx - 1u;
+    const uint32_t rs = a.rec_start[cc.slot];
+    const uint32_t limit = (k_idx + 1u < R.n_rec) ? a.rec_start[cc.slot + 1] : D.len;
+    RowWalk w(a.arena + D.off, rs, limit, D.sep);
+    CellSrc src = w.next();
+    for (uint32_t c = 0; c < cc.col; ++c) src = w.next();
+    const CellCand m = classify_measure_cell(src);
+    const uint32_t chunk = row / D.bl;
+    StatV2* S = a.stat + D.stat_base + chunk * D.W + cc.col;
+    if (m.flags) atomicOr(&S->flags, m.flags);
+    const uint32_t item = D.item_base + row / RFQ2_ROWS;
+    if (m.na) {
+      atomicAdd(&S->na_count, 1u);
+      if (cc.col >= D.lead && atomicAdd(a.row_na + cc.slot, 1u) + 1u == D.h) {   // the row turned out all NA
+        atomicAdd(a.item_allna + item, 1u);
+        atomicAdd(a.chunk_allna + D.stat_base + chunk * D.W, 1u);
+      }
+      continue;
+    }
+    const uint32_t inv_row = ~row;
+    if (m.int_status != INT_OK) {
+      atomicMax(&S->inv_bad, inv_row);
+      if (m.int_status == INT_OVERFLOW) atomicMax(&S->inv_ovf, inv_row);
+      if (m.flags & SF_UINT_INVALID) atomicMax(&S->inv_uinv, inv_row);
+      if (m.flags & SF_UINT_OVF) atomicMax(&S->inv_uovf, inv_row);
+    }
+    if (m.str_len) atomicMax(&S->str_len, m.str_len);
+    if (m.int_len) atomicMax(&S->int_len, m.int_len);
+    if (m.uint_len) atomicMax(&S->uint_len, m.uint_len);
+    if (m.bool_len) atomicMax(&S->bool_len, m.bool_len);
+    if (m.has_float) {
+      if (m.ip_len) atomicMax(&S->ip_len, m.ip_len);
+      if (m.tz < 6) atomicMax(&S->inv_tz, 6u - m.tz);
+      if (m.inf_len) atomicMax(&S->inf_len, m.inf_len);
+      if (m.obj_len) atomicMax(&S->obj_len, m.obj_len);
+      if (m.sci_len) atomicMax(&S->sci_len, m.sci_len);
+      if (m.fl) atomicOr(&S->fl, m.fl);
+    }
+    if (m.need_exact) S->need_exact = 1u;
+    if (cc.col >= D.lead && m.extra) {
+      atomicAdd(a.row_extra + cc.slot, m.extra);
+      atomicAdd(a.item_extra + item, m.extra);
+    }
+  }
+}
+
+// ---- per document: chunk types, rows dropped, measures, column layout ---------------------------
+__device__ __forceinline__ ChunkStat stat_of(const StatV2& s) {
+  ChunkStat c;
+  c.flags = s.flags;
+  c.int_bad_min = s.inv_bad ? ~s.inv_bad : RFQ_NO_ROW;
+  c.int_ovf_min = s.inv_ovf ? ~s.inv_ovf : RFQ_NO_ROW;
+  c.uint_inv_min = s.inv_uinv ? ~s.inv_uinv : RFQ_NO_ROW;
+  c.uint_ovf_min = s.inv_uovf ? ~s.inv_uovf : RFQ_NO_ROW;
+  c.pad[0] = c.pad[1] = c.pad[2] = 0;
+  return c;
+}
+__device__ __forceinline__ ChunkCand cand_of(const StatV2& s) {
+  ChunkCand c;
+  c.str_len = s.str_len; c.int_len = s.int_len; c.uint_len = s.uint_len; c.bool_len = s.bool_len;
+  c.ip_len = s.ip_len; c.min_tz = 6u - s.inv_tz; c.inf_len = s.inf_len; c.obj_len = s.obj_len;
+  c.sci_len = s.sci_len; c.fl = s.fl; c.na_count = s.na_count; c.need_exact = s.need_exact;
+  return c;
+}
+
+__global__ void __launch_bounds__(256) csv2_plan_kernel(Csv2Args a) {
+  const uint32_t d = blockIdx.x;
+  const Doc2 D = a.docs[d];
+  DocRun R = a.run[d];
+  __shared__ uint32_t s_flags, s_dropped, s_carry;
+  if (threadIdx.x == 0) { s_flags = 0; s_dropped = 0; s_carry = 0; }
+  __syncthreads();
+  const bool dead = (R.flags & (RUN_FAIL | RUN_UNSUP)) != 0;
+  const uint32_t W = D.W;
+  const uint32_t n_chunks = dead ? 0u : (R.n_data + D.bl - 1) / D.bl;
+  const uint32_t n_ent = n_chunks * W;
+  ChunkMeasure* meas = (ChunkMeasure*)a.meas;
+  // 1. chunk types
+  for (uint32_t e = threadIdx.x; e < n_ent; e += blockDim.x) {
+    const uint32_t k = e / W, c = e - k * W;
+    const StatV2 S = a.stat[D.stat_base + e];
+    uint32_t fl = 0;
+    if (S.flags & SF_BAD_UTF8) fl |= RUN_FAIL;               // UnicodeDecodeError in a cell
+    const int t = decide_chunk_type(stat_of(S));
+    a.ctype[D.stat_base + e] = (uint8_t)t;
+    if (c >= D.lead) {
+      if (t == CT_STRNF) a.chunk_nf[D.stat_base + k * W] = 1;
+      const bool exact = !(t == CT_STR || t == CT_BOOL || t == CT_BOOLNA || t == CT_UINT || t == CT_INT ||
+                           t == CT_INTNA || t == CT_FLOAT) || (t == CT_FLOAT && S.need_exact);
+      if (exact) fl |= RUN_GENERAL;                           // measured by the three-sweep path instead
+    }
+    if (fl) atomicOr(&s_flags, fl);
+  }
+  __syncthreads();
+  // 2. measures under the decided types, rows dropna removes
+  for (uint32_t e = threadIdx.x; e < n_ent; e += blockDim.x) {
+    const uint32_t k = e / W, c = e - k * W;
+    const uint32_t e0 = D.stat_base + k * W;
+    const uint32_t dropped = a.chunk_nf[e0] ? 0u : a.chunk_allna[e0];
+    if (c == 0 && dropped) atomicAdd(&s_dropped, dropped);
+    ChunkMeasure M;
+    finish_measure(cand_of(a.stat[D.stat_base + e]), a.ctype[D.stat_base + e], dropped, &M);
+    meas[D.stat_base + e] = M;
+  }
+  __syncthreads();
+  const uint32_t n_keep = dead ? 0u : R.n_data - s_dropped;
+  // 3. columns: class, width, decimals, offsets (block-wide running offset, 256 columns per round)
+  bool unsup = false;
+  for (uint32_t j0 = 0; j0 < D.h; j0 += blockDim.x) {
+    const uint32_t j = j0 + threadIdx.x;
+    uint32_t w1 = 0;
+    ColOut2 o; o.cls = 0; o.dec = 0; o.sci = 0; o.width = 0; o.cp_off = 0;
+    if (j < D.h && !dead) {
+      const uint32_t e0 = D.stat_base + D.lead + j;
+      bool nan_left = false;
+      for (uint32_t k = 0; k < n_chunks; ++k) nan_left |= meas[e0 + (size_t)k * W].nan_left != 0;
+      int cls = fold_column_class(a.ctype + e0, n_chunks, W, nan_left);
+      if (cls == CC_UNSUP) { unsup = true; cls = CC_OBJ; }
+      const ColumnLayout L = layout_column(cls, meas + e0, a.ctype + e0, n_chunks, W, a.name_cp[D.col_base + j]);
+      o.cls = L.cls; o.dec = L.dec; o.sci = L.sci ? 1 : 0; o.width = L.width;
+      w1 = L.width + 1;
+    }
+    uint32_t tot;
+    const uint32_t ex = block_excl_scan<SumU32>(w1, &tot);
+    if (j < D.h) { o.cp_off = s_carry + ex; a.col[D.col_base + j] = o; }
+    __syncthreads();
+    if (threadIdx.x == 0) s_carry += tot;
+    __syncthreads();
+  }
+  if (unsup) atomicOr(&s_flags, (uint32_t)RUN_UNSUP);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    R.flags |= s_flags;
+    R.n_keep = n_keep;
+    R.linew = s_carry ? s_carry - 1 : 0;
+    R.hdr_bytes = (R.flags & (RUN_FAIL | RUN_UNSUP | RUN_GENERAL)) ? 0u
+                  : D.banner_len + (n_keep ? R.linew + D.hdr_extra : D.empty_len);
+    a.run[d] = R;
+  }
+}
+
+// bytes of every work item's output range (the document's first item carries banner + header line)
+__global__ void __launch_bounds__(256) csv2_item_bytes_kernel(Csv2Args a) {
+  const uint32_t item = blockIdx.x * blockDim.x + threadIdx.x;
+  if (item > a.n_items) return;
+  unsigned long long b = 0;
+  if (item < a.n_items) {
+    const uint32_t d = ub_search(a.item_base, a.n_docs, item);
+    const Doc2& D = a.docs[d];
+    const DocRun& R = a.run[d];
+    if (!(R.flags & (RUN_FAIL | RUN_UNSUP | RUN_GENERAL))) {
+      const uint32_t row0 = (item - D.item_base) * RFQ2_ROWS;
+      if (item == D.item_base) b += R.hdr_bytes;
+      if (row0 < R.n_data && R.n_keep) {
+        const uint32_t nrows = min(RFQ2_ROWS, R.n_data - row0);
+        const uint32_t e0 = D.stat_base + (row0 / D.bl) * D.W;
+        const uint32_t dropped = a.chunk_nf[e0] ? 0u : a.item_allna[item];
+        const unsigned long long rb = (unsigned long long)(nrows - dropped) * (1ull + R.linew) + a.item_extra[item];
+        b += rb;
+        if (rb < 0xFFFFFFFFull && (uint32_t)rb > a.counters[4]) atomicMax(a.counters + 4, (uint32_t)rb);
+      }
+    }
+  }
+  a.item_bytes[item] = b;
+}
+
+__global__ void __launch_bounds__(128) csv2_docout_kernel(Csv2Args a) {
+  const uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= a.n_docs) return;
+  const unsigned long long o0 = a.item_off[a.item_base[d]], o1 = a.item_off[a.item_base[d + 1]];
+  a.doc_out_off[d] = o0;
+  a.doc_out_len[d] = o1 - o0;
+}
+
+static int sm_count() {
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  return sms;
+}
+
+void csv2_type(const Csv2Args& a, cudaStream_t s) {
+  if (a.n_docs == 0) return;
+  prof_mark("csv2_docprep_kernel", s);
+  RFQ_LAUNCH(csv2_docprep_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
+  if (a.n_items == 0) return;
+  const uint32_t smem = RFQ2_TYPE_STAGE + 32u + (uint32_t)S_COUNT * a.max_w * 4u;
+  static std::atomic<unsigned long long> attr_done{0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!(attr_done.load() >> (dev & 63) & 1ull)) {   // per-device opt-in above 48 KB (wide tables)
+    cudaFuncSetAttribute(csv2_type_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         RFQ2_TYPE_STAGE + 32 + S_COUNT * RFQ_MAX_W * 4);
+    attr_done.fetch_or(1ull << (dev & 63));
+  }
+  int per_sm = 1;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, csv2_type_kernel, RFQ2_ROWS, smem);
+  const uint32_t grid = std::min<uint32_t>(a.n_items, (uint32_t)(sm_count() * std::max(per_sm, 1)));
+  prof_mark("csv2_type_kernel", s);
+  RFQ_LAUNCH(csv2_type_kernel, grid, RFQ2_ROWS, smem, s, a, a.max_w);
+  prof_mark("csv2_type_cold_kernel", s);
+  RFQ_LAUNCH(csv2_type_cold_kernel, sm_count() * 4, 128, 0, s, a);
+}
+
+void csv2_plan(const Csv2Args& a, cudaStream_t s) {
+  if (a.n_docs == 0) return;
+  prof_mark("csv2_plan_kernel", s);
+  RFQ_LAUNCH(csv2_plan_kernel, a.n_docs, 256, 0, s, a);
+  prof_mark("csv2_item_bytes+scan", s);
+  RFQ_LAUNCH(csv2_item_bytes_kernel, (a.n_items + 1 + 255) / 256, 256, 0, s, a);
+  exclusive_scan<SumU64>(a.item_bytes, a.item_off, a.n_items + 1, a.scan_tmp64, nullptr, s);
+  RFQ_LAUNCH(csv2_docout_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
+}
+
+}  // namespace rfq

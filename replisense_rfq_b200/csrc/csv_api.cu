@@ -12,6 +12,7 @@
 #include "../../include/rfq_parse.h"
 #include "col_decide.cuh"
 #include "csv_dfa.cuh"
+#include "csv2.h"
 #include "ctx.h"
 #include "header_names.h"
 
@@ -319,6 +320,194 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
   return RFQ_OK;
 }
 
+// One (encoding, separator) attempt through the row pipeline (csv2.h).  The host looks at the first
+// two records of every document (header names, table width), carves every array from bounds, enqueues
+// the whole attempt and synchronises ONCE, when it reads the results.  Documents whose header already
+// decides the attempt (no header, one column) never reach the device.  Documents whose chunk types the
+// one-sweep candidates do not cover come back in `general` and go through csv_attempt above.
+static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8_t* d_arena,
+                        const std::vector<uint32_t>& off, const std::vector<uint32_t>& len,
+                        int enc, int sep_i, const std::vector<int64_t>& max_rows,
+                        std::vector<uint8_t>& resolved, std::vector<uint32_t>& general) {
+  cudaStream_t s = c->stream;
+  const uint32_t sep = kSeps[sep_i];
+  // ---- 1. headers on the host; documents the header already decides
+  std::vector<uint32_t> act;            // indices into sel
+  std::vector<HeaderInfo> hdrs;
+  for (uint32_t i = 0; i < sel.size(); ++i) {
+    const uint32_t d = sel[i];
+    HeaderInfo h = parse_header(c->h_arena + c->h_doc_off[d], c->h_doc_len[d], sep, enc == 1);
+    if (!h.found || !h.utf8_ok || h.names.size() <= 1) continue;       // EmptyDataError / decode error / len(df.columns) <= 1
+    const uint32_t W = std::max<uint32_t>((uint32_t)h.names.size(), h.first_nf);
+    if (W > 1024) { resolved[d] = 1; c->r_status[d] = RFQ_DOC_UNSUPPORTED; continue; }
+    act.push_back(i);
+    hdrs.push_back(std::move(h));
+  }
+  const uint32_t m = (uint32_t)act.size();
+  if (m == 0) return RFQ_OK;
+  // ---- 2. carve
+  std::vector<Doc2> docs(m);
+  std::vector<uint32_t> tile_base(m + 1), item_base(m + 1), name_off, name_len, name_cp;
+  std::string names;
+  uint64_t tiles = 0, n_slots = 0, n_items = 0, n_stat = 0, n_cols = 0, in_bytes = 0, cells = 0;
+  uint32_t max_w = 1;
+  for (uint32_t k = 0; k < m; ++k) {
+    const uint32_t d = sel[act[k]];
+    const HeaderInfo& H = hdrs[k];
+    Doc2& D = docs[k];
+    memset(&D, 0, sizeof(D));
+    D.off = off[d]; D.len = len[d]; D.sep = sep;
+    D.max_rows = (uint32_t)std::min<int64_t>(std::max<int64_t>(max_rows[d], 0), 0x7FFFFFF0);
+    D.h = (uint32_t)H.names.size();
+    D.W = std::max<uint32_t>(D.h, H.first_nf);
+    D.lead = D.W - D.h;
+    D.bl = chunk_rows_for_width(D.W);
+    D.latin1 = enc == 1;
+    const uint64_t rows_bound = std::min<uint64_t>(D.max_rows, (uint64_t)D.len / 2 + 2);   // a record takes two bytes at least
+    D.slot_base = (uint32_t)n_slots; n_slots += rows_bound + 2;
+    D.item_base = (uint32_t)n_items; D.n_items = (uint32_t)std::max<uint64_t>(1, (rows_bound + RFQ2_ROWS - 1) / RFQ2_ROWS);
+    n_items += D.n_items;
+    D.stat_base = (uint32_t)n_stat; D.n_chunks = (uint32_t)std::max<uint64_t>(1, (rows_bound + D.bl - 1) / D.bl);
+    n_stat += (uint64_t)D.n_chunks * D.W;
+    D.col_base = (uint32_t)n_cols; n_cols += D.h;
+    cells += rows_bound * D.W;
+    max_w = std::max(max_w, D.W);
+    tile_base[k] = (uint32_t)tiles; item_base[k] = D.item_base;
+    tiles += ((uint64_t)D.len + 1 + RFQ_TILE - 1) / RFQ_TILE;
+    in_bytes += D.len;
+    std::string banner = std::string("=== CSV Data (using ") + kEncNames[enc] + ", separator '" + (char)sep + "') ===\n";
+    D.banner_off = (uint32_t)names.size(); D.banner_len = (uint32_t)banner.size();
+    names += banner;
+    std::string empty = empty_frame_text(H.names);
+    D.empty_off = (uint32_t)names.size(); D.empty_len = (uint32_t)empty.size();
+    names += empty;
+    for (uint32_t j = 0; j < D.h; ++j) {
+      name_off.push_back((uint32_t)names.size());
+      name_len.push_back((uint32_t)H.disp[j].size());
+      name_cp.push_back(H.ncp[j]);
+      D.hdr_extra += (uint32_t)H.disp[j].size() - H.ncp[j];
+      names += H.disp[j];
+    }
+  }
+  tile_base[m] = (uint32_t)tiles; item_base[m] = (uint32_t)n_items;
+  if (n_slots >= (1ull << 31) || n_items >= (1ull << 31) || n_stat >= (1ull << 31) || tiles >= (1ull << 31)) {
+    c->err = "batch too large"; return RFQ_ERR_ARG;
+  }
+  Csv2Args a{};
+  a.arena = d_arena; a.n_docs = m;
+  a.n_tiles = (uint32_t)tiles; a.n_chunks = (uint32_t)((tiles + RFQ2_SCAN_TILES - 1) / RFQ2_SCAN_TILES);
+  a.n_items = (uint32_t)n_items; a.n_slots = (uint32_t)n_slots; a.n_stat = (uint32_t)n_stat; a.n_cols = (uint32_t)n_cols;
+  a.max_w = max_w;
+  // ---- 3. upload the description
+  RFQ_CK(c, c->h_up.reserve(sizeof(Doc2) * (m + 1) + 8ull * (m + 2) + 12ull * (n_cols + 1) + names.size() + 8192));
+  Uploader up((uint8_t*)c->h_up.p);
+  const size_t o_docs = up.put(docs.data(), m), o_tb = up.put(tile_base.data(), m + 1), o_ib = up.put(item_base.data(), m + 1);
+  const size_t o_no = up.put(name_off.data(), name_off.size()), o_nl = up.put(name_len.data(), name_len.size());
+  const size_t o_nc = up.put(name_cp.data(), name_cp.size()), o_nm = up.put(names.data(), names.size());
+  uint8_t* d_up = c->pool.alloc<uint8_t>(up.used + 256);
+  // ---- 4. scratch: one zeroed region, then arrays that are written before they are read
+  const size_t z_fn = 0, z_cnt = z_fn + 8ull * a.n_chunks, z_tick = z_cnt + 8ull * a.n_chunks, z_cntr = z_tick + 16;
+  const size_t z_run = (z_cntr + 32 + 255) & ~(size_t)255, z_stat = (z_run + sizeof(DocRun) * m + 255) & ~(size_t)255;
+  const size_t z_ctype = (z_stat + sizeof(StatV2) * n_stat + 255) & ~(size_t)255, z_allna = (z_ctype + n_stat + 255) & ~(size_t)255;
+  const size_t z_nf = (z_allna + 4ull * n_stat + 255) & ~(size_t)255, z_end = (z_nf + n_stat + 255) & ~(size_t)255;
+  uint8_t* z = c->pool.alloc<uint8_t>(z_end + 256);
+  a.rec_start = c->pool.alloc<uint32_t>(n_slots + 2);
+  a.row_na = c->pool.alloc<uint32_t>(n_slots + 2);
+  a.row_extra = c->pool.alloc<uint32_t>(n_slots + 2);
+  a.meas = c->pool.alloc<ChunkMeasure>(n_stat + 1);
+  a.item_allna = c->pool.alloc<uint32_t>(n_items + 1);
+  a.item_extra = c->pool.alloc<uint32_t>(n_items + 1);
+  a.item_bytes = c->pool.alloc<unsigned long long>(n_items + 2);
+  a.item_off = c->pool.alloc<unsigned long long>(n_items + 2);
+  a.scan_tmp64 = c->pool.alloc<unsigned long long>(scan_partials_needed(n_items + 1));
+  a.col = c->pool.alloc<ColOut2>(n_cols + 1);
+  a.doc_out_off = c->pool.alloc<unsigned long long>(m + 1);
+  a.doc_out_len = c->pool.alloc<unsigned long long>(m + 1);
+  a.cold_cells_cap = (uint32_t)std::min<uint64_t>(cells + 1, 4u << 20);
+  a.cold_cells = c->pool.alloc<ColdCell>(a.cold_cells_cap);
+  a.cold_rows_cap = (uint32_t)n_slots;
+  a.cold_rows = c->pool.alloc<ColdRow>(a.cold_rows_cap + 1);
+  // output: sized from what the last run produced, else twice the input; a sweep that does not fit
+  // reports it and is run again in a larger buffer
+  unsigned long long cap = std::max<unsigned long long>(2ull * in_bytes, c->csv2_out_hint + c->csv2_out_hint / 16) + (64u << 10);
+  uint8_t* d_text = c->pool.alloc<uint8_t>(cap + 64);
+  if (c->pool.failed || !z || !d_up) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  a.fn_desc = (unsigned long long*)(z + z_fn); a.cnt_desc = (unsigned long long*)(z + z_cnt);
+  a.ticket = (uint32_t*)(z + z_tick); a.counters = (uint32_t*)(z + z_cntr);
+  a.run = (DocRun*)(z + z_run); a.stat = (StatV2*)(z + z_stat); a.ctype = z + z_ctype;
+  a.chunk_allna = (uint32_t*)(z + z_allna); a.chunk_nf = z + z_nf;
+  RFQ_CK(c, cudaMemcpyAsync(d_up, c->h_up.p, up.used, cudaMemcpyHostToDevice, s));
+  RFQ_CK(c, cudaMemsetAsync(z, 0, z_end, s));
+  a.docs = (const Doc2*)(d_up + o_docs); a.tile_base = (const uint32_t*)(d_up + o_tb);
+  a.item_base = (const uint32_t*)(d_up + o_ib);
+  a.name_off = (const uint32_t*)(d_up + o_no); a.name_len = (const uint32_t*)(d_up + o_nl);
+  a.name_cp = (const uint32_t*)(d_up + o_nc); a.names = d_up + o_nm;
+  a.out = d_text; a.out_cap = cap;
+  // shared-memory stages of the emit sweep: input span of an item from the average row, output from the
+  // last run's largest item (rows that do not fit are written by the fix-up kernel)
+  {
+    const uint64_t avg_item = n_items ? (in_bytes + n_items - 1) / n_items : 0;
+    uint64_t in_st = std::max<uint64_t>(avg_item + avg_item / 4 + 512, c->csv2_in_hint + c->csv2_in_hint / 8 + 64);
+    in_st = std::min<uint64_t>(std::max<uint64_t>(in_st, 4096), 48u << 10);
+    uint64_t out_st = c->csv2_item_out_hint ? c->csv2_item_out_hint + c->csv2_item_out_hint / 8 + 64 : 2 * in_st;
+    out_st = std::min<uint64_t>(std::max<uint64_t>(out_st, 8192), 96u << 10);
+    a.in_stage = (uint32_t)((in_st + 15) & ~15ull); a.out_stage = (uint32_t)((out_st + 15) & ~15ull);
+  }
+  // ---- 5. the whole attempt, one synchronisation
+  csv2_scan(a, s);
+  csv2_type(a, s);
+  csv2_plan(a, s);
+  csv2_emit(a, s);
+  RFQ_CK(c, c->h_down.reserve(sizeof(DocRun) * (m + 1) + 16ull * (m + 1) + 4096));
+  uint8_t* hd = (uint8_t*)c->h_down.p;
+  unsigned long long* h_total = (unsigned long long*)hd;
+  uint32_t* h_cntr = (uint32_t*)(hd + 64);
+  DocRun* h_run = (DocRun*)(hd + 256);
+  unsigned long long* h_ooff = (unsigned long long*)(hd + 256 + sizeof(DocRun) * (m + 1));
+  unsigned long long* h_olen = h_ooff + (m + 1);
+  RFQ_CK(c, cudaMemcpyAsync(h_total, a.item_off + a.n_items, 8, cudaMemcpyDeviceToHost, s));
+  RFQ_CK(c, cudaMemcpyAsync(h_cntr, a.counters, 32, cudaMemcpyDeviceToHost, s));
+  RFQ_CK(c, cudaMemcpyAsync(h_run, a.run, sizeof(DocRun) * m, cudaMemcpyDeviceToHost, s));
+  RFQ_CK(c, cudaMemcpyAsync(h_ooff, a.doc_out_off, 8ull * m, cudaMemcpyDeviceToHost, s));
+  RFQ_CK(c, cudaMemcpyAsync(h_olen, a.doc_out_len, 8ull * m, cudaMemcpyDeviceToHost, s));
+  c->prof.mark("host+sync", s);
+  RFQ_CK(c, cudaStreamSynchronize(s));
+  unsigned long long total = *h_total;
+  if (total > cap) {   // the output did not fit: larger buffer, emit again
+    cap = total + total / 16 + (64u << 10);
+    d_text = c->pool.alloc<uint8_t>(cap + 64);
+    if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+    a.out = d_text; a.out_cap = cap;
+    RFQ_CK(c, cudaMemsetAsync(a.counters + 1, 0, 8, s));
+    csv2_emit(a, s);
+    RFQ_CK(c, cudaMemcpyAsync(h_cntr, a.counters, 32, cudaMemcpyDeviceToHost, s));
+    RFQ_CK(c, cudaStreamSynchronize(s));
+  }
+  RFQ_CK(c, cudaGetLastError());
+  if (h_cntr[2]) { c->err = "csv2: fix-up list overflow"; return RFQ_ERR_STATE; }
+  c->csv2_out_hint = total;
+  c->csv2_in_hint = h_cntr[3];
+  c->csv2_item_out_hint = h_cntr[4];
+  const uint64_t host_base = c->out_total;
+  c->segs.push_back({d_text, total, host_base});
+  c->out_total += total;
+  for (uint32_t k = 0; k < m; ++k) {
+    const uint32_t d = sel[act[k]];
+    const uint32_t fl = h_run[k].flags;
+    if (fl & RUN_UNSUP) { resolved[d] = 1; c->r_status[d] = RFQ_DOC_UNSUPPORTED; continue; }
+    if (fl & RUN_FAIL) continue;                  // next (encoding, separator)
+    if (fl & RUN_GENERAL) { general.push_back(d); continue; }
+    resolved[d] = 1;
+    c->r_status[d] = RFQ_DOC_OK;
+    c->r_off[d] = host_base + h_ooff[k];
+    c->r_len[d] = h_olen[k];
+    c->r_rows[d] = h_run[k].n_keep;
+    c->r_cols[d] = docs[k].h;
+    c->r_attempt[d] = (uint8_t)(enc * 3 + sep_i);
+  }
+  return RFQ_OK;
+}
+
 extern "C" int rfq_csv_run(rfq_ctx* c, const int64_t* max_rows_in) {
   if (!c) return RFQ_ERR_ARG;
   if (!c->staged) { c->err = "rfq_csv_run: nothing staged"; return RFQ_ERR_STATE; }
@@ -388,8 +577,16 @@ extern "C" int rfq_csv_run(rfq_ctx* c, const int64_t* max_rows_in) {
       d_latin = (const uint8_t*)c->d_arena2.p;
       arena = d_latin; off = &l_off; len = &l_len;
     }
+    // RFQ_CSV_V1=1 keeps every document on the three-sweep path (cross-checking, sheets use it anyway)
+    static const bool v1 = getenv("RFQ_CSV_V1") && atoi(getenv("RFQ_CSV_V1")) != 0;
     for (int sep_i = 0; sep_i < 3 && !pending.empty(); ++sep_i) {
-      int rc = csv_attempt(c, pending, arena, *off, *len, enc, sep_i, max_rows, resolved);
+      int rc;
+      if (v1) rc = csv_attempt(c, pending, arena, *off, *len, enc, sep_i, max_rows, resolved);
+      else {
+        std::vector<uint32_t> general;
+        rc = csv2_attempt(c, pending, arena, *off, *len, enc, sep_i, max_rows, resolved, general);
+        if (!rc && !general.empty()) rc = csv_attempt(c, general, arena, *off, *len, enc, sep_i, max_rows, resolved);
+      }
       if (rc) return rc;
       std::vector<uint32_t> next;
       for (uint32_t d : pending) if (!resolved[d]) next.push_back(d);

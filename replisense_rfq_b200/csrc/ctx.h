@@ -131,6 +131,9 @@ struct rfq_ctx {
   std::vector<uint32_t> r_rows, r_cols;
   std::vector<uint8_t> r_attempt;
   rfq::HostBuf h_up, h_down;   // per-attempt upload / download staging
+  // row pipeline: sizes seen by the last CSV run, used to size the next run's buffers without a sync
+  unsigned long long csv2_out_hint = 0;      // output bytes of an attempt
+  uint32_t csv2_in_hint = 0, csv2_item_out_hint = 0;   // largest input span / output range of a work item
   float last_ms = 0.f;
   uint64_t h2d_bytes = 0, d2h_bytes = 0;
 

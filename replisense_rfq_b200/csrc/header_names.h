@@ -20,6 +20,7 @@ struct HeaderInfo {
   std::vector<std::string> names;     // final (mangled) column names ("Empty DataFrame" prints these)
   std::vector<std::string> disp;      // labels as to_string prints them (display_labels)
   std::vector<uint32_t> ncp;          // code points of each display label
+  uint32_t first_nf = 0;              // fields of the second record (0 = there is none): with the header it fixes the table width
 };
 
 inline bool utf8_valid_count(const std::string& s, uint32_t* ncp) {
@@ -138,6 +139,18 @@ inline HeaderInfo parse_header(const uint8_t* doc, uint64_t len, uint32_t sep, b
     st = csv_next(st, cl);
   }
   if (!done || !open) return h;
+  {   // the second record's field count (pandas sizes the table from the header and the first data row)
+    bool done2 = false;
+    uint32_t nf2 = 0;
+    for (; i <= len && !done2; ++i) {
+      int cl = (i == len) ? CL_LF : csv_class(doc[i], sep);
+      int ev = csv_events(st, cl);
+      if (ev & EV_FIELD_END) ++nf2;
+      if (ev & EV_LINE_END) done2 = true;
+      st = csv_next(st, cl);
+    }
+    h.first_nf = done2 ? nf2 : 0;
+  }
   h.found = true;
   std::vector<std::string> raw;
   std::vector<size_t> unnamed;

@@ -116,3 +116,18 @@ def fused_used() -> int:
     L = lib()
     L.hc_fused_used.restype = C.c_uint64
     return int(L.hc_fused_used())
+
+
+def set_walk(on: bool) -> None:
+    """Cells found by the row walker (csv2_rows.cuh scan_field) instead of the field index; the hot
+    kernels' per-cell shortcut is cross-checked against the general functions while it runs."""
+    lib().hc_set_walk(int(on))
+
+
+def walk_stats():
+    """(walker/index disagreements, hot/general typing disagreements, cells typed hot, cells left cold,
+    hot/general printing disagreements, cells printed hot, cells left to the general formatters)"""
+    import numpy as np
+    o = np.zeros(7, dtype=np.uint64)
+    lib().hc_walk_stats(C.c_void_p(o.ctypes.data))
+    return tuple(int(x) for x in o)

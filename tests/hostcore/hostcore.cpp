@@ -95,9 +95,35 @@ int64_t hc_txt(const uint8_t* p, int64_t len, uint8_t* out) {
 #include "../../replisense_rfq_b200/csrc/cell_ops.cuh"
 #include "../../replisense_rfq_b200/csrc/header_names.h"
 
+#include "../../replisense_rfq_b200/csrc/csv2_rows.cuh"
 namespace {
 static bool g_fused = false;
 static uint64_t g_fused_used = 0;
+// row-walker mode: cells are found by scan_field from the record start (what the v2 kernels do)
+// instead of through the field index; hot-path results are compared with the general functions
+static bool g_walk = false;
+static uint64_t g_walk_mismatch = 0, g_hot_mismatch = 0, g_hot_cells = 0, g_cold_cells = 0;
+static uint64_t g_emit_hot = 0, g_emit_cold = 0, g_emit_mismatch = 0;
+
+static bool same_src(const CellSrc& a, const CellSrc& b) {
+  if (a.missing != b.missing) return false;
+  if (a.missing) return true;
+  // the walker may call a span CM_RAW where csv_simplify keeps CM_CSV (same decoded bytes): compare decoded text
+  auto dec = [](const CellSrc& s) {
+    std::string o; int c;
+    if (s.mode == CM_CSV) { CsvIter it(s.p, s.n); while ((c = it.next()) >= 0) o.push_back((char)c); }
+    else if (s.mode == CM_CSVQ) { PairIter it(s.p, s.n); while ((c = it.next()) >= 0) o.push_back((char)c); }
+    else o.assign((const char*)s.p, s.n);
+    return o;
+  };
+  return dec(a) == dec(b);
+}
+static bool same_cand(const CellCand& a, const CellCand& b) {
+  return a.flags == b.flags && a.int_status == b.int_status && a.na == b.na && a.has_float == b.has_float &&
+         a.need_exact == b.need_exact && a.str_len == b.str_len && a.extra == b.extra && a.int_len == b.int_len &&
+         a.uint_len == b.uint_len && a.bool_len == b.bool_len && a.ip_len == b.ip_len && a.tz == b.tz &&
+         a.inf_len == b.inf_len && a.obj_len == b.obj_len && a.sci_len == b.sci_len && a.fl == b.fl;
+}
 
 struct Rec { uint64_t start; uint32_t f0, f1; };
 
@@ -144,7 +170,7 @@ int csv_attempt(const uint8_t* doc, uint64_t len, uint32_t sep, int64_t nrows, s
   uint32_t ndata = (uint32_t)recs.size() - 1;
   uint32_t bl = chunk_rows_for_width(W);
   uint32_t nch = (ndata + bl - 1) / bl;
-  auto cell = [&](uint32_t row, uint32_t c) {
+  auto cell_idx = [&](uint32_t row, uint32_t c) {
     const Rec& R = recs[row + 1];
     CellSrc s; s.mode = 0; s.missing = false; s.clean = false; s.bits = 0; s.p = doc; s.n = 0;
     uint32_t nf = R.f1 - R.f0;
@@ -155,6 +181,28 @@ int csv_attempt(const uint8_t* doc, uint64_t len, uint32_t sep, int64_t nrows, s
     csv_simplify(s);
     return s;
   };
+  // padded copy: the walker's window loads may read a few bytes past the document
+  std::vector<uint8_t> padded;
+  if (g_walk) { padded.assign(doc, doc + len); padded.resize(len + 32, 0); }
+  auto cell_walk = [&](uint32_t row, uint32_t c) {
+    const Rec& R = recs[row + 1];
+    uint32_t limit = (row + 2 < recs.size()) ? (uint32_t)recs[row + 2].start : (uint32_t)len;
+    RowWalk w(padded.data(), (uint32_t)R.start, limit, sep);
+    CellSrc s = w.next();
+    for (uint32_t k = 0; k < c; ++k) s = w.next();
+    if (c + 1 == W) {   // after the last column the record must be over (rows longer than W were rejected above)
+      if (!w.eol) ++g_walk_mismatch;
+    }
+    // map back onto the caller's buffer so pointers stay valid after `padded` is gone (same offsets)
+    if (!s.missing) s.p = doc + (s.p - padded.data());
+    return s;
+  };
+  auto cell = [&](uint32_t row, uint32_t c) {
+    if (!g_walk) return cell_idx(row, c);
+    CellSrc a = cell_walk(row, c), b = cell_idx(row, c);
+    if (!same_src(a, b)) ++g_walk_mismatch;
+    return a;
+  };
   std::vector<ChunkStat> stat((size_t)nch * W, ChunkStat{0, RFQ_NO_ROW, RFQ_NO_ROW, RFQ_NO_ROW, RFQ_NO_ROW, {0, 0, 0}});
   std::vector<uint32_t> row_na(ndata, 0);
   std::vector<ChunkCand> cand((size_t)nch * W, ChunkCand{0, 0, 0, 0, 0, 6, 0, 0, 0, 0, 0, 0});
@@ -163,7 +211,13 @@ int csv_attempt(const uint8_t* doc, uint64_t len, uint32_t sep, int64_t nrows, s
       int is;
       uint32_t f;
       if (g_fused) {   // one visit: flags + measurement candidates (the fused GPU sweep)
-        CellCand m = classify_measure_cell(cell(r, c));
+        CellSrc cs = cell(r, c);
+        CellCand m = classify_measure_cell(cs);
+        if (g_walk) {  // the hot kernels' shortcut must agree with the general function wherever it decides
+          HotCand hc = classify_measure_hot(cs);
+          if (hc.cold) ++g_cold_cells;
+          else { ++g_hot_cells; if (!same_cand(hc.m, m)) ++g_hot_mismatch; }
+        }
         f = m.flags; is = m.int_status;
         ChunkCand& C = cand[(size_t)(r / bl) * W + c];
         if (m.na) C.na_count++;
@@ -267,6 +321,20 @@ int csv_attempt(const uint8_t* doc, uint64_t len, uint32_t sep, int64_t nrows, s
       uint32_t wrote = print_cell(s, ct, kind, lay[j].dec, buf.data());
       if (wrote != nb) { out += "<<SIZE MISMATCH>>"; }
       out.append((const char*)buf.data(), wrote);
+      if (g_walk) {   // the hot emit sweep's shortcut must print the same field wherever it prints at all
+        const uint32_t width = lay[j].width;
+        std::vector<uint8_t> field(width + nb + 64, ' ');
+        std::vector<uint8_t> pad(s.missing ? 0 : s.n + 32, 0);   // window loads read a few bytes past the token
+        CellSrc s2 = s;
+        if (!s.missing) { memcpy(pad.data(), s.p, s.n); s2.p = pad.data(); }
+        uint32_t ex = 0;
+        if (emit_hot(s2, ct, kind, lay[j].dec, width, field.data(), &ex) == 0) {
+          ++g_emit_hot;
+          std::string want(width - ncp, ' ');
+          want.append((const char*)buf.data(), wrote);
+          if (ex != nb - ncp || std::string((const char*)field.data(), width + ex) != want) ++g_emit_mismatch;
+        } else ++g_emit_cold;
+      }
     }
   }
   return 0;
@@ -287,6 +355,16 @@ int hc_scan_text_cmp(const uint8_t* p, uint32_t n) {
   return 1;
 }
 
+// 1 when the hot classifier leaves this row's field `col` to the fix-up kernel (debugging aid)
+int hc_hot_is_cold(const uint8_t* row, uint32_t n, uint32_t sep, uint32_t col) {
+  std::vector<uint8_t> b(row, row + n); b.resize(n + 32, 0);
+  RowWalk w(b.data(), 0, n, sep);
+  CellSrc s = w.next();
+  for (uint32_t k = 0; k < col; ++k) s = w.next();
+  return classify_measure_hot(s).cold ? 1 : 0;
+}
+void hc_set_walk(int on) { g_walk = on != 0; }
+void hc_walk_stats(uint64_t* o) { o[0] = g_walk_mismatch; o[1] = g_hot_mismatch; o[2] = g_hot_cells; o[3] = g_cold_cells; o[4] = g_emit_mismatch; o[5] = g_emit_hot; o[6] = g_emit_cold; }
 void hc_set_fused(int on) { g_fused = on != 0; }
 uint64_t hc_fused_used() { return g_fused_used; }
 

@@ -367,3 +367,40 @@ def test_windowed_text_scan_equals_bytewise():
     for _ in range(30000):
         b = b"".join(r.choice(pieces) for _ in range(r.randint(0, 14)))
         assert L.hc_scan_text_cmp(b, len(b)) == 1, b
+
+
+def test_row_walker_and_hot_paths_agree_with_general():
+    """The row pipeline's building blocks against the general functions on the CPU: cells found by
+    scan_field from the record start equal the cells of the field index (decoded bytes), the hot typing
+    shortcut gives the same candidates as classify_measure_cell wherever it decides, the hot printing
+    shortcut prints the same field wherever it prints (csv2_rows.cuh)."""
+    import base64
+    import json
+    from pathlib import Path
+    docs = [corpus.fuzz_csv(s) for s in range(50000, 51200)] + [corpus.rfq_csv(400, seed=s) for s in range(3)]
+    docs += [base64.b64decode(c["data"]) for c in json.loads((Path(__file__).parent / "golden" / "ref_csv.json").read_text())]
+    try:
+        H.set_fused(True)
+        plain = [H.csv_parse(d, 1000) for d in docs]
+        H.set_walk(True)
+        s0 = H.walk_stats()
+        walked = [H.csv_parse(d, 1000) for d in docs]
+        s1 = H.walk_stats()
+    finally:
+        H.set_walk(False)
+        H.set_fused(False)
+    assert plain == walked
+    d = [b - a for a, b in zip(s0, s1)]
+    assert d[0] == 0 and d[1] == 0 and d[4] == 0, d
+    assert d[2] > 10 * 1000 and d[5] > 10 * 1000, d      # the shortcuts are actually taken
+    # C2-shaped rows never leave the hot paths
+    try:
+        H.set_fused(True)
+        H.set_walk(True)
+        s0 = H.walk_stats()
+        H.csv_parse(corpus.rfq_csv(2000, seed=9), 10 ** 6)
+        s1 = H.walk_stats()
+    finally:
+        H.set_walk(False)
+        H.set_fused(False)
+    assert s1[3] == s0[3] and s1[6] == s0[6]
