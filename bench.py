@@ -91,41 +91,47 @@ def make_doc(rows: int, seed: int) -> bytes:
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference's own CPU path (oracle port of _parse_csv_sync over the
-    same pandas) on all host cores, a bounded sample of the same workload per step."""
+    """--impl reference: the reference's own CPU path on all host cores, a bounded sample of the same
+    workload per step: FileParser._parse_csv_sync of the reference's unmodified app/file_parser.py when
+    oracle/_ref holds it (oracle/build_ref.py puts it there), else the oracle port of the same lines."""
     if rank != 0:
         return
     import multiprocessing as mp
+    from oracle import ref_runner
+    kind = "reference" if ref_runner.available() else "port"
     cores = os.cpu_count() or 1
     sample_rows = max(1000, min(args.rows, args.ref_sample_rows))
     doc = make_doc(sample_rows, 0)
     with mp.get_context("fork").Pool(cores) as pool:
         for _ in range(args.warmup):
-            pool.map(_ref_one, [(doc, sample_rows)] * cores)
+            pool.map(_ref_one, [(doc, sample_rows, kind)] * cores)
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            pool.map(_ref_one, [(doc, sample_rows)] * cores)
+            pool.map(_ref_one, [(doc, sample_rows, kind)] * cores)
         dt = time.perf_counter() - t0
     mb = len(doc) * cores * args.steps / 1e6
     val = mb / dt
+    what = ("the reference's own FileParser._parse_csv_sync (oracle/_ref/app/file_parser.py, unmodified)"
+            if kind == "reference" else "oracle port of FileParser._parse_csv_sync over pandas")
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
-        # same workload / config as our arm; each step is a bounded sample of it (see cpu_baseline.sample)
-        "data": "synthetic", "config": dict(config_dict(args, args.rows), sample_rows_per_process=sample_rows),
+        "data": "synthetic", "config": config_dict(args, args.rows),
         "cells_per_s": sample_rows * 8 * cores * args.steps / dt,
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{cores} processes x one {sample_rows}-row slice of the C2 CSV per step "
-                                   "(oracle port of FileParser._parse_csv_sync over pandas)"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": f"{cores} processes x one {sample_rows}-row slice of the C2 CSV per step ({what})"},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
 
 
 def _ref_one(a):
+    doc, rows, kind = a
+    if kind == "reference":
+        from oracle import ref_runner
+        return len(ref_runner.parse_csv_bytes(doc, rows))
     from oracle import file_parser_oracle as O
-    doc, rows = a
     return len(O.parse_csv_bytes(doc, rows))
 
 
@@ -135,6 +141,8 @@ def config_dict(args, rows):
                         "notes[80% empty]), one document per GPU, FileParser(max_file_size_mb=4096, "
                         f"max_excel_rows={rows})",
             "rows": rows, "cols": 8, "l2": "flushed between timed steps (256 MiB device write)",
+            "reference_arm": f"--impl reference runs {args.ref_sample_rows}-row slices of the same CSV, one per host "
+                             "core per step (pandas' to_string is super-linear in rows: the slice favours the CPU)",
             "parallelism": f"documents sharded across {args.gpus} GPU(s), no collective"}
 
 
@@ -199,11 +207,24 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
-    # ---- parity gate on a slice before any timing counts
+    # ---- parity gate, EVERY rank, before any timing counts: the SHA-256 of this rank's full output
+    # against the hash the oracle produced for its document (tests/golden/c2_sha256.json, generator
+    # tests/golden/make_c2_hashes.py); other sizes: the whole text against the oracle on a capped size
+    import hashlib
     from oracle import file_parser_oracle as O
-    if rank == 0:
-        small = make_doc(2000, seed=rank)
-        assert eng.parse_csv_many([small], 2000)[0] == O.parse_csv_bytes(small, 2000), "parity gate"
+    gold = json.loads((ROOT / "tests" / "golden" / "c2_sha256.json").read_text())
+    if args.rows == gold["rows"] and str(rank) in gold["seeds"]:
+        g = gold["seeds"][str(rank)]
+        assert hashlib.sha256(doc).hexdigest() == g["input_sha256"], "bench input differs from the hashed corpus"
+        r0 = eng.csv_parse_arena(arena, offsets, lengths, mr)
+        assert int(r0.status[0]) == 0, "parity gate: document not parsed"
+        assert hashlib.sha256(r0.doc_bytes(0)).hexdigest() == g["output_sha256"], f"parity gate: rank {rank} output differs from the oracle's"
+        parity = f"sha256 of the full {g['output_bytes']}-byte output == oracle's (seed {rank})"
+    else:
+        nsmall = min(args.rows, 20000)
+        small = make_doc(nsmall, seed=rank)
+        assert eng.parse_csv_many([small], nsmall)[0] == O.parse_csv_bytes(small, nsmall), "parity gate"
+        parity = f"text of a {nsmall}-row document == oracle's (no committed hash for {args.rows} rows / seed {rank})"
 
     # ---- device-resident: stage once, time K runs with CUDA events, L2 flushed between steps
     eng.stage(arena, offsets, lengths)
@@ -286,7 +307,27 @@ def main():
     t0 = time.perf_counter()
     txt = eng.csv_parse_arena(arena, offsets, lengths, mr).doc_str(0)
     t_str = time.perf_counter() - t0
-    assert len(txt.encode("utf-8")) == out_bytes
+    assert txt.isascii() == (len(txt) == out_bytes)
+    del txt
+    # e2e_python: file bytes -> str through the reference-facing method FileParser._parse_csv_sync
+    # (file read, pack into pinned memory, H2D, kernels, D2H, str)
+    from replisense_rfq_b200 import FileParser
+    import tempfile
+    tdir = "/dev/shm" if os.path.isdir("/dev/shm") else None
+    fd, fpath = tempfile.mkstemp(suffix=".csv", dir=tdir)
+    with os.fdopen(fd, "wb") as f:
+        f.write(doc)
+    fp = FileParser(max_file_size_mb=4096, max_excel_rows=args.rows, engine=eng)
+    fp._parse_csv_sync(Path(fpath))
+    t_py = []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        out_txt = fp._parse_csv_sync(Path(fpath))
+        t_py.append(time.perf_counter() - t0)
+        n_txt = len(out_txt)
+        del out_txt
+    os.unlink(fpath)
+    t_py = min(t_py)
 
     if rank != 0:
         if world > 1:
@@ -299,12 +340,13 @@ def main():
     # dominant kernel (live CUDA-event timing on the launching stream, averaged per launch)
     kern = {k: v / args.steps for k, v in prof_acc.items() if k.endswith("_kernel")}
     dom = max(kern, key=kern.get)
-    alg = {"csv_emit_kernel": nbytes + out_bytes, "csv_measure_kernel": nbytes,
+    alg = {"csv2_emit_kernel": nbytes + out_bytes, "csv2_type_kernel": nbytes, "csv2_scan_kernel": nbytes,
+           "csv_emit_kernel": nbytes + out_bytes, "csv_measure_kernel": nbytes,
            "csv_classify_kernel": nbytes, "csv_tilefn_kernel": nbytes, "csv_count_kernel": nbytes,
            "csv_index_kernel": nbytes}.get(dom, nbytes)
     achieved = alg / (kern[dom] / 1e3) / 1e9
     traffic = None
-    tf = ROOT / "profiles" / "traffic_r01.json"
+    tf = ROOT / "profiles" / "traffic_r02.json"
     if tf.exists() and args.rows == 1_000_000:
         traffic = json.loads(tf.read_text()).get(dom)
     line = {
@@ -322,6 +364,10 @@ def main():
                 "d2h_bytes_per_step": out_bytes + 64, "ms_per_step": t_pipe / args.steps * 1e3,
                 "in_flight": depth, "serial_value": total_mb / t_e2e,
                 "serial_ms_per_step": t_e2e / args.steps * 1e3, "to_python_str_ms": t_str * 1e3},
+        # the same document through the Python method the reference's callers use (file -> str), this rank
+        "e2e_python": {"value": nbytes / 1e6 / t_py, "unit": UNIT, "ms_per_call": t_py * 1e3, "chars": n_txt,
+                       "call": "FileParser(max_file_size_mb=4096, max_excel_rows=rows)._parse_csv_sync(path)"},
+        "parity_gate": parity,
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "unit": "GB/s",
                      "frac": achieved / hbm, "traffic": traffic, "peak_source": hbm_src,

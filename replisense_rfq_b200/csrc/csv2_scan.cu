@@ -110,12 +110,12 @@ __global__ void __launch_bounds__(256) csv2_scan_kernel(Csv2Args a) {
     const uint32_t t0 = chunk * RFQ2_SCAN_TILES + (uint32_t)w * 4u;
     // ---- 1. byte classes, lane / tile / warp transition functions
     unsigned long long cls[4];
-    uint32_t lfn[4], tfn[4];
+    uint32_t efn[4], tfn[4], dq[4];    // per tile: the lane's exclusive function, the tile's function, its document
     uint32_t wf = RFQ_FN_IDENTITY;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const uint32_t t = t0 + q;
-      cls[q] = 0ull; lfn[q] = RFQ_FN_IDENTITY; tfn[q] = RFQ_FN_IDENTITY;
+      cls[q] = 0ull; efn[q] = RFQ_FN_IDENTITY; tfn[q] = RFQ_FN_IDENTITY; dq[q] = 0;
       if (t < a.n_tiles) {
         const uint32_t d = scan_find_doc(a.tile_base, a.n_docs, t);
         const uint32_t tile = t - __ldg(a.tile_base + d);
@@ -123,14 +123,19 @@ __global__ void __launch_bounds__(256) csv2_scan_kernel(Csv2Args a) {
         const uint8_t* doc = a.arena + a.docs[d].off;
         const bool bom = tile == 0 && doc_has_bom(doc, len);
         const LaneBytes lb = load_lane_classes(doc, len, tile * RFQ_TILE + lane * 16, a.docs[d].sep, bom);
-        uint32_t f = lane_function(lb.cls, pair_fn);
-        cls[q] = lb.cls; lfn[q] = f;
+        uint32_t incl = lane_function(lb.cls, pair_fn);
+        cls[q] = lb.cls; dq[q] = d;
+        // one inclusive scan: lane 31 ends up with the tile's function, every lane with what happens before it
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-          const uint32_t g = __shfl_down_sync(0xffffffffu, f, o);
-          if ((lane & (2 * o - 1)) == 0) f = fn_compose(f, g);
+          const uint32_t g = __shfl_up_sync(0xffffffffu, incl, o);
+          const uint32_t c2 = fn_compose(g, incl);
+          if (lane >= o) incl = c2;
         }
-        f = __shfl_sync(0xffffffffu, f, 0);
+        uint32_t ex = __shfl_up_sync(0xffffffffu, incl, 1);
+        if (lane == 0) ex = RFQ_FN_IDENTITY;
+        efn[q] = ex;
+        uint32_t f = __shfl_sync(0xffffffffu, incl, 31);
         if (tile == 0) f = fn_const(fn_apply(f, ST_R));   // a document starts in ST_R whatever came before
         tfn[q] = f;
         wf = fn_compose(wf, f);
@@ -159,30 +164,15 @@ __global__ void __launch_bounds__(256) csv2_scan_kernel(Csv2Args a) {
       const uint32_t t = t0 + q;
       ev[q] = 0; le[q] = 0; tot[q] = 0;
       if (t < a.n_tiles) {
-        const uint32_t d = scan_find_doc(a.tile_base, a.n_docs, t);
+        const uint32_t d = dq[q];
         const uint32_t tile = t - __ldg(a.tile_base + d);
         const uint32_t len = a.docs[d].len;
         const uint32_t base = tile * RFQ_TILE + lane * 16;
-        uint32_t incl = lfn[q];
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const uint32_t g = __shfl_up_sync(0xffffffffu, incl, o);
-          if (lane >= o) incl = fn_compose(g, incl);
-        }
-        uint32_t excl = __shfl_up_sync(0xffffffffu, incl, 1);
-        if (lane == 0) excl = RFQ_FN_IDENTITY;
-        int s1 = fn_apply(excl, tile == 0 ? ST_R : st);
+        int s1 = fn_apply(efn[q], tile == 0 ? ST_R : st);
         const uint32_t eof_k = (len >= base && len < base + 16) ? len - base : 0xFFu;
-        // an ordinary byte after an ordinary byte changes nothing: visit the others, and the first
-        // ordinary byte after one of them (or at the start of the lane)
-        unsigned long long tt = cls[q];
-        tt = (tt | (tt >> 1) | (tt >> 2) | (tt >> 3)) & 0x1111111111111111ull;
-        tt = (tt | (tt >> 3)) & 0x0303030303030303ull;
-        tt = (tt | (tt >> 6)) & 0x000F000F000F000Full;
-        tt = (tt | (tt >> 12)) & 0x000000FF000000FFull;
-        const uint32_t nz = (uint32_t)(tt | (tt >> 24)) & 0xFFFFu;
+        const uint32_t vm = visit_mask16(cls[q]);
         uint32_t sm = 0, wm = 0, lm = 0;
-        for (uint32_t m = (nz | (nz << 1) | 1u) & 0xFFFFu; m; m &= m - 1) {
+        for (uint32_t m = vm; m; m &= m - 1) {
           const int kk = __ffs(m) - 1;
           const uint2 fe = class_fe[(uint32_t)(cls[q] >> (4 * kk)) & 0xFu];
           const uint32_t e = (fe.y >> (4 * s1)) & 0xFu;
@@ -226,7 +216,7 @@ __global__ void __launch_bounds__(256) csv2_scan_kernel(Csv2Args a) {
     for (int q = 0; q < 4; ++q) {
       const uint32_t t = t0 + q;
       if (t < a.n_tiles) {
-        const uint32_t d = scan_find_doc(a.tile_base, a.n_docs, t);
+        const uint32_t d = dq[q];
         const uint32_t tile = t - __ldg(a.tile_base + d);
         const Doc2& D = a.docs[d];
         const uint32_t len = D.len;

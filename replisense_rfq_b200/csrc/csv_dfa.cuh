@@ -117,17 +117,15 @@ RFQ_HD uint32_t csv_class_ev(int cl) {
 // (a then b)(s) = b(a(s))
 RFQ_HD uint32_t fn_compose(uint32_t a, uint32_t b) {
 #if defined(__CUDA_ARCH__)
-  // expand b to a byte table, look up with a's nibbles via PRMT
-  uint32_t blo = (b & 0xFu) | ((b & 0xF0u) << 4) | ((b & 0xF00u) << 8) | ((b & 0xF000u) << 12);
-  uint32_t bh = b >> 16;
-  uint32_t bhi = (bh & 0xFu) | ((bh & 0xF0u) << 4) | ((bh & 0xF00u) << 8) | ((bh & 0xF000u) << 12);
-  uint32_t r0 = __byte_perm(blo, bhi, a & 0xFFFFu);   // bytes b(a(0..3))
-  uint32_t r1 = __byte_perm(blo, bhi, a >> 16);       // bytes b(a(4..7))
-  uint32_t p0 = (r0 | (r0 >> 4));                     // byte0 = n0|n1<<4, byte2 = n2|n3<<4
-  uint32_t p1 = (r1 | (r1 >> 4));
-  uint32_t lo = (p0 & 0xFFu) | ((p0 >> 8) & 0xFF00u);
-  uint32_t hi = (p1 & 0xFFu) | ((p1 >> 8) & 0xFF00u);
-  return lo | (hi << 16);
+  // b as a byte table (two PRMTs interleave its even and odd nibbles), looked up with a's nibbles
+  // (PRMT again: a selector nibble below 8 picks a byte), bytes squeezed back into nibbles
+  const uint32_t ev = b & 0x0F0F0F0Fu, od = (b >> 4) & 0x0F0F0F0Fu;
+  const uint32_t blo = __byte_perm(ev, od, 0x5140u);   // b(0), b(1), b(2), b(3)
+  const uint32_t bhi = __byte_perm(ev, od, 0x7362u);   // b(4) .. b(7)
+  const uint32_t r0 = __byte_perm(blo, bhi, a);         // b(a(0..3))
+  const uint32_t r1 = __byte_perm(blo, bhi, a >> 16);   // b(a(4..7))
+  const uint32_t p0 = r0 | (r0 >> 4), p1 = r1 | (r1 >> 4);   // byte 0 = n0 | n1 << 4, byte 2 = n2 | n3 << 4
+  return __byte_perm(p0, p1, 0x6420u);
 #else
   uint32_t r = 0;
   for (int s = 0; s < 8; ++s) {
@@ -137,6 +135,29 @@ RFQ_HD uint32_t fn_compose(uint32_t a, uint32_t b) {
   return r;
 #endif
 }
+// Which of a lane's 16 bytes (classes as nibbles, byte k in bits 4k..4k+3) a replay has to visit to
+// see every record event and every state change a LATER visited byte can tell apart.  With bit 4k
+// standing for byte k: A = quote / LF / CR, N = anything but an ordinary byte, D = delimiter.  Visited:
+// A; a non-ordinary byte whose predecessor is non-ordinary (a delimiter or blank right after an ordinary
+// byte leaves the machine where an ordinary byte leaves it, as far as any later visited byte can
+// tell: U / F / QQ all go to the same place on LF, CR, blank and delimiter, and a quote right after that
+// delimiter makes the delimiter visited); a delimiter right before a quote or at the end of the lane;
+// the byte after any of these; byte 0.  Returns bit k = byte k is visited.
+RFQ_HD uint32_t visit_mask16(unsigned long long n) {
+  const unsigned long long M1 = 0x1111111111111111ull;
+  const unsigned long long b0 = n & M1, b1 = (n >> 1) & M1, b2 = (n >> 2) & M1;
+  const unsigned long long N = b0 | b1 | b2;
+  const unsigned long long QTm = b1 & ~b0 & ~b2;
+  const unsigned long long A = (b1 & ~b2) | (b2 & ~b0 & ~b1);
+  const unsigned long long Dm = b0 & ~b1 & ~b2;
+  const unsigned long long V1 = A | (N & ((N << 4) | 1ull)) | (Dm & ((QTm >> 4) | (1ull << 60)));
+  unsigned long long tt = V1 | (V1 << 4) | 1ull;
+  tt = (tt | (tt >> 3)) & 0x0303030303030303ull;
+  tt = (tt | (tt >> 6)) & 0x000F000F000F000Full;
+  tt = (tt | (tt >> 12)) & 0x000000FF000000FFull;
+  return (uint32_t)(tt | (tt >> 24)) & 0xFFFFu;
+}
+
 RFQ_HD int fn_apply(uint32_t f, int s) { return (int)((f >> (4 * s)) & 0xFu); }
 RFQ_HD uint32_t fn_const(int s) { return 0x11111111u * (uint32_t)s; }
 

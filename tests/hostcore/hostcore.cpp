@@ -363,6 +363,42 @@ int hc_hot_is_cold(const uint8_t* row, uint32_t n, uint32_t sep, uint32_t col) {
   for (uint32_t k = 0; k < col; ++k) s = w.next();
   return classify_measure_hot(s).cold ? 1 : 0;
 }
+// Reduced replay of the row scan (csv_dfa.cuh visit_mask16) against the full DFA walk, lane by lane
+// (16 bytes, exact start state): record starts / ends must come out the same.  Returns mismatching lanes.
+uint64_t hc_visit_check(const uint8_t* doc, uint64_t len, uint32_t sep) {
+  uint64_t bad = 0;
+  int st = ST_R;
+  for (uint64_t base = 0; base <= len; base += 16) {
+    unsigned long long cls = 0;
+    for (int k = 0; k < 16; ++k) {
+      uint64_t pos = base + k;
+      int c = pos < len ? csv_class(doc[pos], sep) : (pos == len ? CL_LF : CL_PAD);
+      cls |= (unsigned long long)c << (4 * k);
+    }
+    uint32_t sm = 0, wm = 0, lm = 0, sm2 = 0, wm2 = 0, lm2 = 0;
+    int s1 = st, s2 = st;
+    for (int k = 0; k < 16; ++k) {
+      int c = (int)((cls >> (4 * k)) & 0xF);
+      int e = csv_events(s1, c);
+      if (e & EV_REC_START) sm |= 1u << k;
+      if (e & EV_REC_START_WS) wm |= 1u << k;
+      if (e & EV_LINE_END) lm |= 1u << k;
+      s1 = csv_next(s1, c);
+    }
+    for (uint32_t m = visit_mask16(cls); m; m &= m - 1) {
+      int k = __builtin_ctz(m);
+      int c = (int)((cls >> (4 * k)) & 0xF);
+      int e = csv_events(s2, c);
+      if (e & EV_REC_START) sm2 |= 1u << k;
+      if (e & EV_REC_START_WS) wm2 |= 1u << k;
+      if (e & EV_LINE_END) lm2 |= 1u << k;
+      s2 = csv_next(s2, c);
+    }
+    if (sm != sm2 || wm != wm2 || lm != lm2) ++bad;
+    st = s1;
+  }
+  return bad;
+}
 void hc_set_walk(int on) { g_walk = on != 0; }
 void hc_walk_stats(uint64_t* o) { o[0] = g_walk_mismatch; o[1] = g_hot_mismatch; o[2] = g_hot_cells; o[3] = g_cold_cells; o[4] = g_emit_mismatch; o[5] = g_emit_hot; o[6] = g_emit_cold; }
 void hc_set_fused(int on) { g_fused = on != 0; }

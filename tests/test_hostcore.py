@@ -404,3 +404,19 @@ def test_row_walker_and_hot_paths_agree_with_general():
         H.set_walk(False)
         H.set_fused(False)
     assert s1[3] == s0[3] and s1[6] == s0[6]
+
+
+def test_scan_visits_only_what_matters():
+    """The row scan replays a lane's 16 bytes visiting only the bytes visit_mask16 (csv_dfa.cuh) selects:
+    record starts and record ends must be exactly those of the full state-machine walk."""
+    import ctypes as C
+    L = H.lib()
+    L.hc_visit_check.restype = C.c_uint64
+    L.hc_visit_check.argtypes = [C.c_char_p, C.c_uint64, C.c_uint32]
+    r = random.Random(5)
+    alphabet = [b",", b'"', b"\n", b"\r", b" ", b"\t", b"a", b"1", b";"]
+    docs = [corpus.fuzz_csv(s) for s in range(60000, 60800)] + [corpus.rfq_csv(300, seed=1)]
+    docs += [b"".join(r.choice(alphabet) for _ in range(r.randint(0, 70))) for _ in range(8000)]
+    for d in docs:
+        for sep in (44, 59, 9):
+            assert L.hc_visit_check(d, len(d), sep) == 0, (d, sep)
