@@ -21,10 +21,13 @@
 namespace rfq {
 
 #define RFQ2_ROWS 128u            // data rows per work item = threads per CTA of the row kernels
-#define RFQ2_SCAN_TILES 32u       // 512-byte tiles per scan chunk (16 KB per CTA round)
+#define RFQ2_SCAN_TILES 32u
+// 16-byte units of cell_meta per row: 8 cells each
+#define RFQ2_META_VECS(W) (((W) + 7u) / 8u)       // 512-byte tiles per scan chunk (16 KB per CTA round)
 
 struct Doc2 {
   uint32_t off, len;              // document bytes in the arena
+  uint32_t meta_base;             // cell_meta of record slot k at meta_base + (k - 1) * meta_stride(W), in 16-byte units
   uint32_t sep, max_rows;         // separator of this attempt, nrows
   uint32_t W, lead, h, bl;        // table width, implicit-index columns, output columns, low_memory chunk rows
   uint32_t slot_base;             // rec_start[slot_base + k] = start of record k (k <= max_rows + 1)
@@ -80,6 +83,7 @@ struct Csv2Args {
   // rows
   uint32_t* row_na;               // [n_slots] NA cells among the output columns
   uint32_t* row_extra;            // [n_slots] printed bytes - printed code points
+  uint16_t* cell_meta;            // [n_slots * meta_stride(W)] what the typing sweep found per cell (csv2_rows.cuh)
   StatV2* stat;                   // [n_stat]
   uint8_t* ctype;                 // [n_stat]
   uint32_t* chunk_allna;          // [n_stat] (entry of column 0 of each chunk) rows whose output cells are all NA

@@ -175,18 +175,37 @@ __global__ void __launch_bounds__(RFQ2_ROWS) csv2_emit_kernel(Csv2Args a, uint32
         uint8_t* rowp = s_out + mis + roff;
         const uint32_t rs = threadIdx.x == 0 ? start : __ldg(a.rec_start + slot);
         const uint32_t limit = (2u + row0 + threadIdx.x < R.n_rec) ? __ldg(a.rec_start + slot + 1) : D.len;
-        RowWalk w(base, rs, limit, D.sep);
-        for (uint32_t c = 0; c < D.lead; ++c) w.next();
         const uint8_t* ctrow = a.ctype + e0 + D.lead;
+        const uint4* mrow = reinterpret_cast<const uint4*>(a.cell_meta) + D.meta_base +
+                            (size_t)(row0 + threadIdx.x) * RFQ2_META_VECS(W);
         rowp[0] = '\n';
-        uint32_t xb = 0;
-        for (uint32_t j = 0; j < D.h; ++j) {
+        uint32_t xb = 0, pos = rs;
+        uint4 mv = make_uint4(0u, 0u, 0u, 0u);
+        for (uint32_t c = 0; c < W; ++c) {
+          if ((c & 7u) == 0) mv = __ldg(mrow + (c >> 3));
+          const uint32_t k = c & 7u;
+          const uint32_t word = k < 2 ? mv.x : k < 4 ? mv.y : k < 6 ? mv.z : mv.w;
+          const uint32_t me = (word >> (16u * (k & 1u))) & 0xFFFFu;
+          const uint32_t mode = (me >> CMETA_MODE_SHIFT) & 3u;
+          CellSrc src;
+          src.mode = CM_RAW; src.missing = false; src.clean = mode == 0; src.bits = 0; src.p = base; src.n = 0;
+          if (me & CMETA_MISSING) src.missing = true;
+          else if (mode == 3u) { cold = true; break; }
+          else if (mode == 2u) {                       // ""-pair text: its two lengths come from a fresh scan
+            const FieldScan f = scan_field(base, pos, limit, D.sep);
+            src = f.src; pos = f.next;
+          } else {
+            const uint32_t q = (me >> 11) & 1u, len = me & 0x7FFu;
+            src.p = base + pos + q; src.n = len;
+            pos += len + 1u + 2u * q;
+          }
+          if (c < D.lead) continue;
+          const uint32_t j = c - D.lead;
           const ColOut2 co = small ? s_col[j] : a.col[D.col_base + j];
           const int ct = small ? s_ct[j] : ctrow[j];
-          const CellSrc src = w.next();
           const int kind = print_kind(co.cls, ct, co.sci != 0);
           uint32_t ex;
-          if (emit_hot(src, ct, kind, co.dec, co.width, rowp + 1 + co.cp_off + xb, &ex)) { cold = true; break; }
+          if (emit_hot(src, ct, kind, co.dec, co.width, rowp + 1 + co.cp_off + xb, &ex, (int)(me >> 15))) { cold = true; break; }
           xb += ex;
         }
       }

@@ -133,12 +133,14 @@ struct RowWalk {
   const uint8_t* p;     // base pointer: p[pos] are document bytes
   uint32_t pos, limit, sep;
   bool eol;             // the record's terminator has been consumed
-  RFQ_HD RowWalk(const uint8_t* base, uint32_t start, uint32_t lim, uint32_t s) : p(base), pos(start), limit(lim), sep(s), eol(false) {}
+  RFQ_HD RowWalk(const uint8_t* base, uint32_t start, uint32_t lim, uint32_t s) : p(base), pos(start), limit(lim), sep(s), eol(false), field_pos(start) {}
+  uint32_t field_pos;   // where the field returned last started
   RFQ_HD CellSrc next() {
     if (eol) {            // short row: pandas pads with empty tokens
       CellSrc s; s.mode = CM_CSV; s.missing = true; s.clean = false; s.p = p; s.n = 0; s.bits = 0;
       return s;
     }
+    field_pos = pos;
     FieldScan f = scan_field(p, pos, limit, sep);
     pos = f.next; eol = f.eol;
     return f.src;
@@ -191,93 +193,138 @@ struct HotCand {
   CellCand m;
 };
 
-RFQ_HD HotCand classify_measure_hot(const CellSrc& s) {
-  HotCand h;
-  h.cold = false;
-  CellCand& m = h.m;
-  m.flags = 0; m.int_status = INT_OK; m.na = false; m.has_float = false; m.need_exact = false;
-  m.str_len = 0; m.extra = 0; m.int_len = 0; m.uint_len = 0; m.bool_len = 0;
-  m.ip_len = 0; m.tz = 6; m.inf_len = 0; m.obj_len = 0; m.sci_len = 0; m.fl = 0;
-  if (s.missing) { m.flags = SF_ANY_NA; m.na = true; return h; }
-  if (s.mode == CM_CSV) { h.cold = true; return h; }
-  uint32_t nbytes, ncp;
+// The hot classifier reports what it found through a sink, so that the typing sweep can fold each
+// outcome straight into its statistics (no struct of seventeen candidates travelling through
+// registers) while the CPU cross-check collects the same calls into a CellCand:
+//   cold()                                       left to the fix-up kernel
+//   na()                                         missing cell or NA token
+//   word(flags, str_len, extra, bool_len)        not a number (int64 status: invalid)
+//   integer(flags, str_len, int_len, neg, large) an int64 of magnitude <= 2^53 (float view: digits + ".000000")
+//   decimal(flags, str_len, ip_len, tz, obj_len, neg, large)   [+-]d{1,8}.d{1,6}
+template <class Sink>
+RFQ_HD void classify_hot(const CellSrc& s, Sink& k) {
+  if (s.missing) { k.na(); return; }
+  if (s.mode == CM_CSV) { k.cold(); return; }
+  uint32_t nbytes, ncp, f = SF_ANY_NONNA;
   uint64_t first8;
   if (s.clean) { nbytes = s.n; ncp = s.n; first8 = s.n ? load8_masked(s.p, s.n) : 0; }
   else if (s.mode == CM_CSVQ) {
     nbytes = (uint32_t)s.bits; ncp = nbytes;
     first8 = 0;
     PairIter it(s.p, s.n);
-    for (int k = 0; k < 8; ++k) { int c = it.next(); if (c < 0) break; first8 |= (uint64_t)c << (8 * k); }
+    for (int q = 0; q < 8; ++q) { int c = it.next(); if (c < 0) break; first8 |= (uint64_t)c << (8 * q); }
   } else {   // plain span with non-ASCII bytes
     TextInfo t = scan_text_raw(s.p, s.n);
-    if (!t.utf8_ok) m.flags |= SF_BAD_UTF8;
-    if (t.nesc) { h.cold = true; return h; }   // cannot happen (no control bytes), kept for safety
+    if (!t.utf8_ok) f |= SF_BAD_UTF8;
+    if (t.nesc) { k.cold(); return; }   // cannot happen (no control bytes), kept for safety
     nbytes = t.nbytes; ncp = t.ncp; first8 = t.first8;
   }
-  if (is_na_token(nbytes, first8)) { m.flags = SF_ANY_NA; m.na = true; return h; }
-  uint32_t f = m.flags | SF_ANY_NONNA;
-  m.str_len = ncp;
-  m.extra = nbytes - ncp;
+  if (is_na_token(nbytes, first8)) { k.na(); return; }
   const int bt = bool_token(nbytes, first8);
-  if (bt >= 0) m.bool_len = bt == 1 ? 4u : 5u;
+  const uint32_t bool_len = bt < 0 ? 0u : bt == 1 ? 4u : 5u;
   const uint32_t c0 = (uint32_t)(first8 & 0xFFu);
   if (!(is_digit_ascii((int)c0) || c0 == '+' || c0 == '-' || c0 == '.' || is_space_ascii((int)c0) ||
         (c0 | 0x20u) == 'i')) {          // a plain word: no numeric grammar starts like this
-    m.int_status = INT_INVALID;
     f |= SF_UINT_INVALID | SF_FLOAT_BAD | SF_PYINT_BAD;
     if (bt < 0) f |= SF_BOOL_BAD;
-    m.flags = f;
-    return h;
+    k.word(f, ncp, nbytes - ncp, bool_len);
+    return;
   }
-  if (!s.clean || s.mode != CM_RAW) { h.cold = true; return h; }   // numeric-looking but quoted-with-pairs / non-ASCII
+  if (!s.clean || s.mode != CM_RAW) { k.cold(); return; }   // numeric-looking but quoted-with-pairs / non-ASCII
   int64_t iv;
   const int st = parse_int64(RawIter(s.p, s.n), &iv);
-  m.int_status = st;
   if (st == INT_OK) {
     const uint64_t mag = iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv;
-    if (mag > (1ull << 53) || (iv == 0 && c0 != '0')) { h.cold = true; return h; }   // float view needs the exact parser; "-0", " 0", "+0"
+    if (mag > (1ull << 53) || (iv == 0 && c0 != '0')) { k.cold(); return; }   // float view needs the exact parser; "-0", " 0", "+0"
     if (iv < 0) f |= SF_NEG;
     f |= SF_BOOL_BAD;
-    m.flags = f;
-    m.int_len = (uint32_t)int64_len(iv);
-    if (iv >= 0) m.uint_len = m.int_len;
-    m.has_float = true;
-    m.ip_len = m.int_len; m.tz = 6; m.obj_len = m.int_len - (iv < 0 ? 1u : 0u) + 3u;
-    m.sci_len = 12u + (iv < 0 ? 1u : 0u);
-    m.fl = MF_FINITE | (mag > 1000000ull ? MF_LARGE : 0);
-    return h;
+    k.integer(f, ncp, (uint32_t)int64_len(iv), iv < 0, mag > 1000000ull);
+    return;
   }
-  if (st == INT_OVERFLOW) { h.cold = true; return h; }
+  if (st == INT_OVERFLOW) { k.cold(); return; }
   Fixed6 d6;
   if (!decimal_literal(s.p, s.n, &d6)) {
     // not an integer: a date, a part number that starts with a digit, ... decided here when no
     // grammar takes it; real floats beyond the literal shape go to the fix-up kernel
     const uint32_t c1 = (c0 == '+' || c0 == '-') ? (uint32_t)((first8 >> 8) & 0xFFu) : c0;
     if ((c1 | 0x20u) == 'i') {                 // INR, item, -inf: only the inf words are numbers
-      if (inf_word(s.p, s.n)) { h.cold = true; return h; }
-    } else if (float_shape(s.p, s.n) != 0) { h.cold = true; return h; }
+      if (inf_word(s.p, s.n)) { k.cold(); return; }
+    } else if (float_shape(s.p, s.n) != 0) { k.cold(); return; }
     uint32_t i = 0;
     while (i < s.n && is_space_ascii(s.p[i])) ++i;
     if (i < s.n && s.p[i] == '-') f |= SF_NEG; else f |= SF_UINT_INVALID;   // str_to_uint64: a leading '-' is "negative", not an error
     f |= SF_FLOAT_BAD;
     if (bt < 0) f |= SF_BOOL_BAD;
     const int pp = pyint_prefix(first8, nbytes);
-    if (pp == 2) { h.cold = true; return h; }
+    if (pp == 2) { k.cold(); return; }
     if (pp == 0) f |= SF_PYINT_BAD;
-    m.flags = f;
-    return h;
+    k.word(f, ncp, nbytes - ncp, bool_len);
+    return;
   }
   // [+-]d{1,8}.d{1,6}: not an int64, not a uint64 (invalid, or "negative" for a leading '-'), never
   // int()-parsable, not a bool; as float64 its "%.6f" digits are its own (cell_format.cuh)
   if (c0 == '-') f |= SF_NEG; else f |= SF_UINT_INVALID;
   f |= SF_PYINT_BAD | SF_BOOL_BAD;
-  m.flags = f;
-  m.has_float = true;
-  m.ip_len = (d6.neg ? 1u : 0u) + (uint32_t)d6.ip_digits; m.tz = (uint32_t)d6.tz;
-  m.obj_len = (uint32_t)objfloat_len(d6);
-  m.sci_len = 12u + (d6.neg ? 1u : 0u);
-  m.fl = MF_FINITE | ((d6.ip > 1000000ull || (d6.ip == 1000000ull && d6.frac)) ? MF_LARGE : 0);
-  return h;
+  k.decimal(f, ncp, (d6.neg ? 1u : 0u) + (uint32_t)d6.ip_digits, (uint32_t)d6.tz, (uint32_t)objfloat_len(d6), d6.neg,
+            d6.ip > 1000000ull || (d6.ip == 1000000ull && d6.frac));
+}
+
+// the calls collected into the candidates classify_measure_cell() reports (CPU cross-check, fix-ups)
+struct CandSink {
+  HotCand h;
+  RFQ_HD CandSink() {
+    h.cold = false;
+    CellCand& m = h.m;
+    m.flags = 0; m.int_status = INT_OK; m.na = false; m.has_float = false; m.need_exact = false;
+    m.str_len = 0; m.extra = 0; m.int_len = 0; m.uint_len = 0; m.bool_len = 0;
+    m.ip_len = 0; m.tz = 6; m.inf_len = 0; m.obj_len = 0; m.sci_len = 0; m.fl = 0;
+  }
+  RFQ_HD void cold() { h.cold = true; }
+  RFQ_HD void na() { h.m.flags = SF_ANY_NA; h.m.na = true; }
+  RFQ_HD void word(uint32_t f, uint32_t str_len, uint32_t extra, uint32_t bool_len) {
+    h.m.flags = f; h.m.int_status = INT_INVALID; h.m.str_len = str_len; h.m.extra = extra; h.m.bool_len = bool_len;
+  }
+  RFQ_HD void integer(uint32_t f, uint32_t str_len, uint32_t int_len, bool neg, bool large) {
+    CellCand& m = h.m;
+    m.flags = f; m.str_len = str_len; m.int_len = int_len;
+    if (!neg) m.uint_len = int_len;
+    m.has_float = true;
+    m.ip_len = int_len; m.tz = 6; m.obj_len = int_len - (neg ? 1u : 0u) + 3u;
+    m.sci_len = 12u + (neg ? 1u : 0u);
+    m.fl = MF_FINITE | (large ? MF_LARGE : 0);
+  }
+  RFQ_HD void decimal(uint32_t f, uint32_t str_len, uint32_t ip_len, uint32_t tz, uint32_t obj_len, bool neg, bool large) {
+    CellCand& m = h.m;
+    m.flags = f; m.int_status = INT_INVALID; m.str_len = str_len;
+    m.has_float = true;
+    m.ip_len = ip_len; m.tz = tz; m.obj_len = obj_len; m.sci_len = 12u + (neg ? 1u : 0u);
+    m.fl = MF_FINITE | (large ? MF_LARGE : 0);
+  }
+};
+RFQ_HD HotCand classify_measure_hot(const CellSrc& s) {
+  CandSink k;
+  classify_hot(s, k);
+  return k.h;
+}
+
+// -?(0|[1-9]d{0,7}).d{dec}: the shape decimal_literal() accepts (at most 8 integer digits, dec <= 6
+// decimals, not below 1e-5) written the way "%.{dec}f" writes it — no '+', no leading zeros, exactly
+// `dec` decimals — so the printed field is the token itself.
+RFQ_HD bool canonical_decimal(const uint8_t* p, uint32_t n, int dec) {
+  if (n < (uint32_t)dec + 2u || n > 17u) return false;
+  uint32_t i = p[0] == '-' ? 1u : 0u;
+  const uint32_t dot = n - 1u - (uint32_t)dec;
+  if (dot <= i || dot - i > 8u || p[dot] != '.') return false;
+  if (p[i] == '0' && dot - i != 1u) return false;                 // leading zero
+  uint32_t nz = 0;
+  for (uint32_t k = i; k < n; ++k) {
+    if (k == dot) continue;
+    const uint32_t dgt = (uint32_t)p[k] - '0';
+    if (dgt > 9u) return false;
+    if (k < dot || k + 1u < n) nz |= dgt;                          // any non-zero digit above the last decimal
+  }
+  if (p[i] == '0' && nz == 0) return false;                        // below 1e-5 (or zero): left to the general path
+  return true;
 }
 
 // ---- the cells the hot emit sweep prints itself -------------------------------------------------
@@ -297,13 +344,29 @@ RFQ_HD void copy_span(uint8_t* dst, const uint8_t* src, uint32_t n) {
   }
 }
 
+// What the typing sweep found out about a cell, 16 bits, so that the emit sweep neither looks for
+// the end of the field again nor repeats the NA test:
+//   bits 0-10 length of the span (2047 and more: filed under mode 3), bit 11 the span sits inside quotes
+//   (starts one byte later, the field is two bytes longer), bits 12-13 mode: 0 plain clean ASCII span,
+//   1 plain span with non-ASCII bytes, 2 scan the field again (""-pair text), 3 the row goes to the
+//   fix-up kernel; bit 14 missing (short row), bit 15 an NA token.
+enum { CMETA_QUOTED = 1u << 11, CMETA_MODE_SHIFT = 12, CMETA_MISSING = 1u << 14, CMETA_NA = 1u << 15 };
+RFQ_HD uint32_t cell_meta(const CellSrc& s, bool quoted, bool cold, bool na) {
+  if (s.missing) return CMETA_MISSING | CMETA_NA;
+  if (cold || s.mode == CM_CSV || s.n > 2046u) return 3u << CMETA_MODE_SHIFT;
+  if (s.mode == CM_CSVQ) return (2u << CMETA_MODE_SHIFT) | (na ? CMETA_NA : 0u);
+  return s.n | (quoted ? CMETA_QUOTED : 0u) | ((s.clean ? 0u : 1u) << CMETA_MODE_SHIFT) | (na ? CMETA_NA : 0u);
+}
+
 // One cell printed right-justified into its (blank-filled) field.  Returns 0 = done, 1 = the row
 // goes to the fix-up kernel.  *extra receives printed bytes - printed code points.
+// na_known: -1 = find out here, 0 / 1 = what the typing sweep found (is_na_token of the token).
 RFQ_HD int emit_hot(const CellSrc& s, int ct, int kind, int dec, uint32_t width,
-                                        uint8_t* field, uint32_t* extra) {
+                                        uint8_t* field, uint32_t* extra, int na_known = -1) {
   *extra = 0;
   if (s.missing) return 0;
   if (s.mode == CM_CSV) return 1;
+  if (na_known == 1 && ct != CT_STRNF) return 0;
   uint32_t nbytes;
   uint64_t first8;
   if (s.clean) { nbytes = s.n; first8 = s.n ? load8_masked(s.p, s.n) : 0; }
@@ -315,7 +378,7 @@ RFQ_HD int emit_hot(const CellSrc& s, int ct, int kind, int dec, uint32_t width,
       for (int k = 0; k < 8; ++k) { int c = it.next(); if (c < 0) break; first8 |= (uint64_t)c << (8 * k); }
     }
   } else { nbytes = s.n; first8 = s.n ? load8_masked(s.p, s.n) : 0; }
-  if (ct != CT_STRNF && is_na_token(nbytes, first8)) return 0;   // NaN -> '' after fillna: the blanks are there already
+  if (na_known < 0 && ct != CT_STRNF && is_na_token(nbytes, first8)) return 0;   // NaN -> '' after fillna: the blanks are there already
   switch (kind) {
     case PR_STR: {
       if (s.mode == CM_CSVQ) {
@@ -374,6 +437,9 @@ RFQ_HD int emit_hot(const CellSrc& s, int ct, int kind, int dec, uint32_t width,
         const uint64_t mag = iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv;
         if (mag > (1ull << 53)) return 1;
         d6.neg = iv < 0; d6.inf = false; d6.big = false; d6.ip = mag; d6.frac = 0; d6.ip_digits = ndigits_u64(mag); d6.tz = 6;
+      } else if (kind == PR_FIXED && canonical_decimal(s.p, s.n, dec)) {
+        copy_span(field + (width - s.n), s.p, s.n);   // "959.40" in a two-decimal column is its own "%.2f"
+        return 0;
       } else if (!decimal_literal(s.p, s.n, &d6)) {   // a short decimal literal prints its own digits (cell_format.cuh)
         int64_t iv = 0;                               // "100" next to "99.5": xstrtod makes the same value of it
         if (parse_int64(RawIter(s.p, s.n), &iv) != INT_OK) return 1;

@@ -14,6 +14,7 @@
 // of a document is a virtual LF.  The bytes are read from HBM exactly once: no tensor cores, by design.
 #include <cuda_runtime.h>
 #include <algorithm>
+#include <stdlib.h>
 #include "csv2.h"
 #include "csv_scan_core.cuh"
 #include "launch.h"
@@ -257,7 +258,8 @@ void csv2_scan(const Csv2Args& a, cudaStream_t s) {
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const uint32_t grid = std::min<uint32_t>(a.n_chunks, (uint32_t)sms * 6u);
+  static const int per_sm = getenv("RFQ2_SCAN_CTAS") ? atoi(getenv("RFQ2_SCAN_CTAS")) : 6;
+  const uint32_t grid = std::min<uint32_t>(a.n_chunks, (uint32_t)sms * (uint32_t)per_sm);
   prof_mark("csv2_scan_kernel", s);
   RFQ_LAUNCH(csv2_scan_kernel, grid, 256, 0, s, a);
 }

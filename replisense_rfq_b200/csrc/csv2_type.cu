@@ -38,11 +38,47 @@ __global__ void __launch_bounds__(128) csv2_docprep_kernel(Csv2Args a) {
   a.run[d] = R;
 }
 
-enum { S_FLAGS = 0, S_BAD, S_OVF, S_UINV, S_UOVF, S_STR, S_INT, S_UINT, S_BOOL, S_IP, S_TZ, S_OBJ, S_SCI, S_FL,
-       S_NA, S_COUNT };
+enum { S_FLAGS = 0, S_BAD, S_UINV, S_STR, S_INT, S_UINT, S_BOOL, S_IP, S_TZ, S_OBJ, S_SCI, S_FL, S_NA, S_COUNT };
 #define RFQ2_TYPE_STAGE (24u << 10)
 
-#define SMAXC(arr, v) do { const uint32_t v_ = (v); if (v_ > (arr)[c]) atomicMax(&(arr)[c], v_); } while (0)
+
+// What classify_hot (csv2_rows.cuh) finds goes straight into the item's shared-memory statistics:
+// each outcome touches only the entries it can change (a word: flags, text width, first-bad-row marks).
+struct TypeSink {
+  uint32_t* s_arr; uint32_t W, c, inv_row, extra;
+  bool is_cold, is_na;
+  __device__ __forceinline__ uint32_t& at(int k) { return s_arr[k * W + c]; }
+  __device__ __forceinline__ void smax(int k, uint32_t v) { if (v > at(k)) atomicMax(&at(k), v); }
+  __device__ __forceinline__ void flags(uint32_t f) { if ((at(S_FLAGS) & f) != f) atomicOr(&at(S_FLAGS), f); }
+  __device__ __forceinline__ void cold() { is_cold = true; }
+  __device__ __forceinline__ void na() { is_na = true; }
+  __device__ __forceinline__ void word(uint32_t f, uint32_t str_len, uint32_t ex, uint32_t bool_len) {
+    flags(f);
+    smax(S_BAD, inv_row);
+    if (f & SF_UINT_INVALID) smax(S_UINV, inv_row);
+    smax(S_STR, str_len);
+    if (bool_len) smax(S_BOOL, bool_len);
+    extra = ex;
+  }
+  __device__ __forceinline__ void integer(uint32_t f, uint32_t str_len, uint32_t int_len, bool neg, bool large) {
+    flags(f);
+    smax(S_STR, str_len); smax(S_INT, int_len);
+    if (!neg) smax(S_UINT, int_len);
+    smax(S_IP, int_len); smax(S_OBJ, int_len - (neg ? 1u : 0u) + 3u); smax(S_SCI, 12u + (neg ? 1u : 0u));
+    const uint32_t fl = MF_FINITE | (large ? MF_LARGE : 0);
+    if ((at(S_FL) & fl) != fl) atomicOr(&at(S_FL), fl);
+  }
+  __device__ __forceinline__ void decimal(uint32_t f, uint32_t str_len, uint32_t ip_len, uint32_t tz, uint32_t obj_len,
+                                          bool neg, bool large) {
+    flags(f);
+    smax(S_BAD, inv_row);
+    if (f & SF_UINT_INVALID) smax(S_UINV, inv_row);
+    smax(S_STR, str_len);
+    smax(S_IP, ip_len); smax(S_TZ, 6u - tz); smax(S_OBJ, obj_len); smax(S_SCI, 12u + (neg ? 1u : 0u));
+    const uint32_t fl = MF_FINITE | (large ? MF_LARGE : 0);
+    if ((at(S_FL) & fl) != fl) atomicOr(&at(S_FL), fl);
+  }
+};
 
 __global__ void __launch_bounds__(RFQ2_ROWS) csv2_type_kernel(Csv2Args a, uint32_t max_w) {
   extern __shared__ __align__(16) uint8_t smem[];
@@ -81,11 +117,6 @@ __global__ void __launch_bounds__(RFQ2_ROWS) csv2_type_kernel(Csv2Args a, uint32
     const uint8_t* base = staged ? s_stage - (size_t)(g_lo - D.off) : a.arena + D.off;   // base[pos] = document byte pos
     if (staged) mbar_wait(&s_bar, phase), phase ^= 1u;
     __syncthreads();
-    uint32_t* s_flags = s_arr + S_FLAGS * W; uint32_t* s_bad = s_arr + S_BAD * W; uint32_t* s_ovf = s_arr + S_OVF * W;
-    uint32_t* s_uinv = s_arr + S_UINV * W; uint32_t* s_uovf = s_arr + S_UOVF * W; uint32_t* s_str = s_arr + S_STR * W;
-    uint32_t* s_int = s_arr + S_INT * W; uint32_t* s_uint = s_arr + S_UINT * W; uint32_t* s_bool = s_arr + S_BOOL * W;
-    uint32_t* s_ip = s_arr + S_IP * W; uint32_t* s_tz = s_arr + S_TZ * W; uint32_t* s_obj = s_arr + S_OBJ * W;
-    uint32_t* s_sci = s_arr + S_SCI * W; uint32_t* s_fl = s_arr + S_FL * W; uint32_t* s_na = s_arr + S_NA * W;
     uint32_t allna = 0, extra = 0;
     if (threadIdx.x < nrows) {
       const uint32_t slot = slot0 + threadIdx.x, row = row0 + threadIdx.x;
@@ -94,38 +125,41 @@ __global__ void __launch_bounds__(RFQ2_ROWS) csv2_type_kernel(Csv2Args a, uint32
       RowWalk w(base, rs, limit, D.sep);
       uint32_t na = 0;
       const uint32_t inv_row = ~row;
+      uint4* mrow = reinterpret_cast<uint4*>(a.cell_meta) + D.meta_base + (size_t)row * RFQ2_META_VECS(W);
+      unsigned long long mlo = 0ull, mhi = 0ull;
+      TypeSink k;
+      k.s_arr = s_arr; k.W = W; k.inv_row = inv_row;
       for (uint32_t c = 0; c < W; ++c) {
         const CellSrc src = w.next();
-        const HotCand hc = classify_measure_hot(src);
-        if (hc.cold) {
-          const uint32_t k = atomicAdd(a.counters + 0, 1u);
-          if (k < a.cold_cells_cap) a.cold_cells[k] = ColdCell{d, slot, c};
+        k.c = c; k.is_cold = false; k.is_na = false; k.extra = 0;
+        classify_hot(src, k);
+        {   // 16 bits per cell for the emit sweep, eight cells per 16-byte store
+          const bool quoted = !src.missing && src.p != base + w.field_pos;
+          const uint32_t me = cell_meta(src, quoted, k.is_cold, k.is_na);
+          const uint32_t q = c & 7u;
+          if (q < 4u) mlo |= (unsigned long long)me << (16u * q);
+          else mhi |= (unsigned long long)me << (16u * (q - 4u));
+          if (q == 7u || c + 1 == W) {
+            mrow[c >> 3] = make_uint4((uint32_t)mlo, (uint32_t)(mlo >> 32), (uint32_t)mhi, (uint32_t)(mhi >> 32));
+            mlo = 0ull; mhi = 0ull;
+          }
+        }
+        if (k.is_cold) {
+          const uint32_t i = atomicAdd(a.counters + 0, 1u);
+          if (i < a.cold_cells_cap) a.cold_cells[i] = ColdCell{d, slot, c};
           else atomicOr(&a.run[d].flags, (uint32_t)RUN_GENERAL);
           continue;
         }
-        const CellCand& m = hc.m;
-        const uint32_t f = m.flags;
-        if ((s_flags[c] & f) != f) atomicOr(&s_flags[c], f);
         // the lanes of a warp sit on the same column: one shared-memory add per warp for its NA cells
         const unsigned am = __activemask();
-        const unsigned nm = __ballot_sync(am, m.na);
-        if (m.na) {
-          if ((threadIdx.x & 31u) == (uint32_t)(__ffs(nm) - 1)) atomicAdd(&s_na[c], (uint32_t)__popc(nm));
+        const unsigned nm = __ballot_sync(am, k.is_na);
+        if (k.is_na) {
+          if ((threadIdx.x & 31u) == (uint32_t)(__ffs(nm) - 1)) atomicAdd(&s_arr[S_NA * W + c], (uint32_t)__popc(nm));
+          if (!(s_arr[S_FLAGS * W + c] & SF_ANY_NA)) atomicOr(&s_arr[S_FLAGS * W + c], (uint32_t)SF_ANY_NA);
           if (c >= D.lead) ++na;
           continue;
         }
-        if (m.int_status != INT_OK) {
-          SMAXC(s_bad, inv_row);
-          if (m.int_status == INT_OVERFLOW) SMAXC(s_ovf, inv_row);
-          if (f & SF_UINT_INVALID) SMAXC(s_uinv, inv_row);
-          if (f & SF_UINT_OVF) SMAXC(s_uovf, inv_row);
-        }
-        SMAXC(s_str, m.str_len); SMAXC(s_int, m.int_len); SMAXC(s_uint, m.uint_len); SMAXC(s_bool, m.bool_len);
-        if (m.has_float) {
-          SMAXC(s_ip, m.ip_len); SMAXC(s_tz, 6u - m.tz); SMAXC(s_obj, m.obj_len); SMAXC(s_sci, m.sci_len);
-          if ((s_fl[c] & m.fl) != m.fl) atomicOr(&s_fl[c], m.fl);
-        }
-        if (c >= D.lead) extra += m.extra;
+        if (c >= D.lead) extra += k.extra;
       }
       if (!w.eol) atomicOr(&a.run[d].flags, (uint32_t)RUN_FAIL);   // "Expected N fields in line K, saw M"
       a.row_na[slot] = na;
@@ -148,21 +182,21 @@ __global__ void __launch_bounds__(RFQ2_ROWS) csv2_type_kernel(Csv2Args a, uint32
     }
     for (uint32_t c = threadIdx.x; c < W; c += blockDim.x) {
       StatV2* S = a.stat + D.stat_base + chunk * W + c;
-      if (s_flags[c]) atomicOr(&S->flags, s_flags[c]);
-      if (s_bad[c]) atomicMax(&S->inv_bad, s_bad[c]);
-      if (s_ovf[c]) atomicMax(&S->inv_ovf, s_ovf[c]);
-      if (s_uinv[c]) atomicMax(&S->inv_uinv, s_uinv[c]);
-      if (s_uovf[c]) atomicMax(&S->inv_uovf, s_uovf[c]);
-      if (s_str[c]) atomicMax(&S->str_len, s_str[c]);
-      if (s_int[c]) atomicMax(&S->int_len, s_int[c]);
-      if (s_uint[c]) atomicMax(&S->uint_len, s_uint[c]);
-      if (s_bool[c]) atomicMax(&S->bool_len, s_bool[c]);
-      if (s_ip[c]) atomicMax(&S->ip_len, s_ip[c]);
-      if (s_tz[c]) atomicMax(&S->inv_tz, s_tz[c]);
-      if (s_obj[c]) atomicMax(&S->obj_len, s_obj[c]);
-      if (s_sci[c]) atomicMax(&S->sci_len, s_sci[c]);
-      if (s_fl[c]) atomicOr(&S->fl, s_fl[c]);
-      if (s_na[c]) atomicAdd(&S->na_count, s_na[c]);
+#define RFQ2_SV(k) s_arr[(k) * W + c]
+      if (RFQ2_SV(S_FLAGS)) atomicOr(&S->flags, RFQ2_SV(S_FLAGS));
+      if (RFQ2_SV(S_BAD)) atomicMax(&S->inv_bad, RFQ2_SV(S_BAD));
+      if (RFQ2_SV(S_UINV)) atomicMax(&S->inv_uinv, RFQ2_SV(S_UINV));
+      if (RFQ2_SV(S_STR)) atomicMax(&S->str_len, RFQ2_SV(S_STR));
+      if (RFQ2_SV(S_INT)) atomicMax(&S->int_len, RFQ2_SV(S_INT));
+      if (RFQ2_SV(S_UINT)) atomicMax(&S->uint_len, RFQ2_SV(S_UINT));
+      if (RFQ2_SV(S_BOOL)) atomicMax(&S->bool_len, RFQ2_SV(S_BOOL));
+      if (RFQ2_SV(S_IP)) atomicMax(&S->ip_len, RFQ2_SV(S_IP));
+      if (RFQ2_SV(S_TZ)) atomicMax(&S->inv_tz, RFQ2_SV(S_TZ));
+      if (RFQ2_SV(S_OBJ)) atomicMax(&S->obj_len, RFQ2_SV(S_OBJ));
+      if (RFQ2_SV(S_SCI)) atomicMax(&S->sci_len, RFQ2_SV(S_SCI));
+      if (RFQ2_SV(S_FL)) atomicOr(&S->fl, RFQ2_SV(S_FL));
+      if (RFQ2_SV(S_NA)) atomicAdd(&S->na_count, RFQ2_SV(S_NA));
+#undef RFQ2_SV
     }
     __syncthreads();
   }

@@ -349,7 +349,7 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
   std::vector<Doc2> docs(m);
   std::vector<uint32_t> tile_base(m + 1), item_base(m + 1), name_off, name_len, name_cp;
   std::string names;
-  uint64_t tiles = 0, n_slots = 0, n_items = 0, n_stat = 0, n_cols = 0, in_bytes = 0, cells = 0;
+  uint64_t tiles = 0, n_slots = 0, n_items = 0, n_stat = 0, n_cols = 0, in_bytes = 0, cells = 0, meta_vecs = 0;
   uint32_t max_w = 1;
   for (uint32_t k = 0; k < m; ++k) {
     const uint32_t d = sel[act[k]];
@@ -370,6 +370,7 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
     D.stat_base = (uint32_t)n_stat; D.n_chunks = (uint32_t)std::max<uint64_t>(1, (rows_bound + D.bl - 1) / D.bl);
     n_stat += (uint64_t)D.n_chunks * D.W;
     D.col_base = (uint32_t)n_cols; n_cols += D.h;
+    D.meta_base = (uint32_t)meta_vecs; meta_vecs += rows_bound * RFQ2_META_VECS(D.W);
     cells += rows_bound * D.W;
     max_w = std::max(max_w, D.W);
     tile_base[k] = (uint32_t)tiles; item_base[k] = D.item_base;
@@ -390,7 +391,8 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
     }
   }
   tile_base[m] = (uint32_t)tiles; item_base[m] = (uint32_t)n_items;
-  if (n_slots >= (1ull << 31) || n_items >= (1ull << 31) || n_stat >= (1ull << 31) || tiles >= (1ull << 31)) {
+  if (n_slots >= (1ull << 31) || n_items >= (1ull << 31) || n_stat >= (1ull << 31) || tiles >= (1ull << 31) ||
+      meta_vecs >= (1ull << 31)) {
     c->err = "batch too large"; return RFQ_ERR_ARG;
   }
   Csv2Args a{};
@@ -414,6 +416,7 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
   a.rec_start = c->pool.alloc<uint32_t>(n_slots + 2);
   a.row_na = c->pool.alloc<uint32_t>(n_slots + 2);
   a.row_extra = c->pool.alloc<uint32_t>(n_slots + 2);
+  a.cell_meta = (uint16_t*)c->pool.alloc<uint4>(meta_vecs + 1);
   a.meas = c->pool.alloc<ChunkMeasure>(n_stat + 1);
   a.item_allna = c->pool.alloc<uint32_t>(n_items + 1);
   a.item_extra = c->pool.alloc<uint32_t>(n_items + 1);
