@@ -300,6 +300,28 @@ def main():
     if world > 1:
         dist.all_reduce(tp, op=dist.ReduceOp.MAX)
     t_pipe = float(tp.item())
+    # ---- e2e_prompt: what /upload/ consumes (app/main.py:243-273): the prompt and text_length; raw_text is
+    # parsed and wrapped on the device and never crosses PCIe (D2H drops from the whole text to the prompt)
+    from replisense_rfq_b200 import prompt as Pm
+    p_head = (Pm.EXTRACTION_PROMPT_TEMPLATE + '\n"""\n').encode()
+    p_tail, p_mark = Pm.PROMPT_TAIL.encode(), Pm.TRUNCATION_MARK.encode()
+
+    def prompt_step(e, _):
+        r = e.csv_prompt_arena(arena, offsets, lengths, mr, p_head, p_tail, p_mark, Pm.MAX_PROMPT_CHARS)
+        return int(r.lengths[0]), int(r.raw_chars[0])
+    for e in pool.engines:
+        for _ in range(2):
+            prompt_step(e, 0)
+    barrier()
+    t0 = time.perf_counter()
+    pouts = pool.map(prompt_step, range(args.steps))
+    torch.cuda.synchronize()
+    t_prompt = time.perf_counter() - t0
+    tq = torch.tensor([t_prompt], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tq, op=dist.ReduceOp.MAX)
+    t_prompt = float(tq.item())
+    prompt_bytes, raw_chars = pouts[0]
     pool.close()
     sampler.stop_flag = True
     sampler.join()
@@ -367,6 +389,10 @@ def main():
         # the same document through the Python method the reference's callers use (file -> str), this rank
         "e2e_python": {"value": nbytes / 1e6 / t_py, "unit": UNIT, "ms_per_call": t_py * 1e3, "chars": n_txt,
                        "call": "FileParser(max_file_size_mb=4096, max_excel_rows=rows)._parse_csv_sync(path)"},
+        # parse + prompt assembly fused on the device (rfq_csv_prompt_parse): H2D of the file, D2H of the prompt only
+        "e2e_prompt": {"value": total_mb / t_prompt, "unit": UNIT, "ms_per_step": t_prompt / args.steps * 1e3,
+                       "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": prompt_bytes + 64, "in_flight": depth,
+                       "text_length": raw_chars, "call": "rfq_csv_prompt_parse (C ABI), host buffers"},
         "parity_gate": parity,
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "unit": "GB/s",

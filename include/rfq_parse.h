@@ -117,6 +117,27 @@ int rfq_numeric_run(rfq_ctx* ctx, const uint8_t* kind);
 int rfq_prompt_run(rfq_ctx* ctx, const uint8_t* head, uint32_t head_len, const uint8_t* tail,
                    uint32_t tail_len, const uint8_t* mark, uint32_t mark_len, uint32_t max_chars);
 
+/* ---- CSV parse fused with prompt assembly: the /upload/ flow of the reference (app/main.py:243-273) parses
+ * the file, builds the prompt from raw_text (app/rfq_agent.py:138-151) and returns the LLM's fields plus
+ * `text_length`; raw_text itself never leaves the service.  This entry runs rfq_csv_run and
+ * rfq_prompt_run back to back on the device: the parsed text stays in HBM, the output of the run (what
+ * rfq_fetch downloads) is the prompts.  Per-document status: RFQ_DOC_OK, RFQ_DOC_CSV_UNPARSEABLE /
+ * RFQ_DOC_UNSUPPORTED from the parse stage, RFQ_DOC_EMPTY_TEXT from the prompt stage.
+ * rfq_out_raw_bytes / rfq_out_raw_chars give the size of each raw_text in bytes and in code points
+ * (the reference's `text_length`; ~0 where the parse stage took the three-sweep path and did not count). */
+int rfq_csv_prompt_run(rfq_ctx* ctx, const int64_t* max_rows, const uint8_t* head, uint32_t head_len,
+                       const uint8_t* tail, uint32_t tail_len, const uint8_t* mark, uint32_t mark_len,
+                       uint32_t max_chars);
+int rfq_csv_prompt_parse(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets, const uint64_t* lengths,
+                         uint32_t n_docs, const int64_t* max_rows, const uint8_t* head, uint32_t head_len,
+                         const uint8_t* tail, uint32_t tail_len, const uint8_t* mark, uint32_t mark_len,
+                         uint32_t max_chars);
+const uint64_t* rfq_out_raw_bytes(const rfq_ctx* ctx);
+const uint64_t* rfq_out_raw_chars(const rfq_ctx* ctx);
+/* code points of every text of the last CSV run (NULL after other runs; ~0 = not counted): lets a
+ * binding build its string object without scanning the bytes when chars == bytes (ASCII) */
+const uint64_t* rfq_out_chars(const rfq_ctx* ctx);
+
 /* ---- device → host copy of the last run's output ---- */
 int rfq_fetch(rfq_ctx* ctx);
 

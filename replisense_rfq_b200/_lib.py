@@ -42,6 +42,14 @@ SIGNATURES = {
     "rfq_text_parse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),
     "rfq_csv_parse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32,
                                 C.c_void_p]),
+    "rfq_csv_prompt_run": (C.c_int, [C.c_void_p, C.c_void_p, C.c_char_p, C.c_uint32, C.c_char_p, C.c_uint32,
+                                     C.c_char_p, C.c_uint32, C.c_uint32]),
+    "rfq_csv_prompt_parse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
+                                       C.c_char_p, C.c_uint32, C.c_char_p, C.c_uint32, C.c_char_p, C.c_uint32,
+                                       C.c_uint32]),
+    "rfq_out_raw_bytes": (C.c_void_p, [C.c_void_p]),
+    "rfq_out_raw_chars": (C.c_void_p, [C.c_void_p]),
+    "rfq_out_chars": (C.c_void_p, [C.c_void_p]),
     "rfq_out_count": (C.c_uint32, [C.c_void_p]),
     "rfq_out_text": (C.c_void_p, [C.c_void_p]),
     "rfq_out_offsets": (C.c_void_p, [C.c_void_p]),

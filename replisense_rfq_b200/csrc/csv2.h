@@ -46,7 +46,7 @@ struct DocRun {
   uint32_t n_data, n_keep;        // data rows used, rows left after dropna
   uint32_t linew;                 // code points of one output line
   uint32_t hdr_bytes;             // banner + header line (or the empty-frame text)
-  uint32_t pad;
+  uint32_t extra;                 // printed bytes - printed code points of the data rows (0 = they are ASCII)
 };
 enum { RUN_FAIL = 1,              // this (encoding, separator) attempt fails the way pandas fails it
        RUN_UNSUP = 2,             // a construct that is declined (RFQ_DOC_UNSUPPORTED)

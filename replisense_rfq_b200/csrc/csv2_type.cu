@@ -369,6 +369,7 @@ __global__ void __launch_bounds__(256) csv2_item_bytes_kernel(Csv2Args a) {
         const uint32_t dropped = a.chunk_nf[e0] ? 0u : a.item_allna[item];
         const unsigned long long rb = (unsigned long long)(nrows - dropped) * (1ull + R.linew) + a.item_extra[item];
         b += rb;
+        if (a.item_extra[item]) atomicAdd(&a.run[d].extra, a.item_extra[item]);
         if (rb < 0xFFFFFFFFull && (uint32_t)rb > a.counters[4]) atomicMax(a.counters + 4, (uint32_t)rb);
       }
     }

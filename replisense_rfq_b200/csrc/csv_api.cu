@@ -506,6 +506,12 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
     c->r_len[d] = h_olen[k];
     c->r_rows[d] = h_run[k].n_keep;
     c->r_cols[d] = docs[k].h;
+    {   // code points of the text: bytes minus the continuation bytes of the header line and of the rows
+      uint64_t ex = h_run[k].extra;
+      if (h_run[k].n_keep) ex += docs[k].hdr_extra;
+      else { uint32_t cp = 0; std::string e = empty_frame_text(hdrs[k].names); utf8_valid_count(e, &cp); ex += e.size() - cp; }
+      c->r_chars[d] = h_olen[k] - ex;
+    }
     c->r_attempt[d] = (uint8_t)(enc * 3 + sep_i);
   }
   return RFQ_OK;
@@ -522,12 +528,14 @@ extern "C" int rfq_csv_run(rfq_ctx* c, const int64_t* max_rows_in) {
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
   RFQ_CK(c, cudaEventRecord(c->ev0, s));
   c->pool.reset();
+  c->status_override.clear();
   c->segs.clear();
   c->out_total = 0;
   c->host_tables = true;
   c->r_off.assign(n, 0); c->r_len.assign(n, 0);
   c->r_status.assign(n, RFQ_DOC_CSV_UNPARSEABLE);
   c->r_rows.assign(n, 0); c->r_cols.assign(n, 0); c->r_attempt.assign(n, 0xFF);
+  c->r_chars.assign(n, ~0ull);   // unknown unless the row pipeline produced the document
   std::vector<int64_t> max_rows(n, 1000);
   if (max_rows_in) for (uint32_t d = 0; d < n; ++d) max_rows[d] = max_rows_in[d];
   std::vector<uint8_t> resolved(n, 0);
@@ -603,3 +611,110 @@ extern "C" int rfq_csv_run(rfq_ctx* c, const int64_t* max_rows_in) {
   c->timed = true;
   return RFQ_OK;
 }
+
+
+// ---- CSV parse fused with prompt assembly (the /upload/ flow: app/main.py:243-273 never returns raw_text,
+// only the prompt built from it and its length) ----------------------------------------------------------
+extern "C" int rfq_csv_prompt_run(rfq_ctx* c, const int64_t* max_rows, const uint8_t* head, uint32_t head_len,
+                                  const uint8_t* tail, uint32_t tail_len, const uint8_t* mark, uint32_t mark_len,
+                                  uint32_t max_chars) {
+  if (!c || (head_len && !head) || (tail_len && !tail) || (mark_len && !mark)) return RFQ_ERR_ARG;
+  int rc = rfq_csv_run(c, max_rows);
+  if (rc) return rc;
+  cudaStream_t s = c->stream;
+  const uint32_t n = c->n_docs;
+  g_prof = &c->prof;
+  struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
+  // what the parse stage produced; where every parsed text lies on the device
+  c->raw_bytes.assign(c->r_len.begin(), c->r_len.end());
+  c->raw_chars.assign(c->r_chars.begin(), c->r_chars.end());
+  c->status_override.assign(n, -1);
+  const uint64_t cap_bytes = 4ull * max_chars + 4;     // max_chars + 1 code points never take more
+  std::vector<unsigned long long> src(n, 0);
+  std::vector<uint32_t> take(n, 0), dst_off(n, 0);
+  uint64_t total_g = 0;
+  for (uint32_t d = 0; d < n; ++d) {
+    if (c->r_status[d] != RFQ_DOC_OK) { c->status_override[d] = c->r_status[d]; c->raw_bytes[d] = 0; c->raw_chars[d] = 0; }
+    else {
+      const uint64_t off = c->r_off[d];
+      for (const auto& sg : c->segs)
+        if (off >= sg.host_base && off < sg.host_base + std::max<uint64_t>(sg.bytes, 1)) { src[d] = (unsigned long long)(uintptr_t)(sg.d + (off - sg.host_base)); break; }
+      take[d] = (uint32_t)std::min<uint64_t>(c->r_len[d], cap_bytes);
+    }
+    dst_off[d] = (uint32_t)total_g;
+    total_g += ((uint64_t)take[d] + 15) & ~15ull;
+  }
+  if (total_g + 64 >= (1ull << 32)) { c->err = "prompt arena must be < 4 GiB"; return RFQ_ERR_ARG; }
+  const size_t o_tail = ((size_t)head_len + 15) & ~(size_t)15, o_mark = (o_tail + tail_len + 15) & ~(size_t)15;
+  const size_t pieces = o_mark + mark_len + 16;
+  RFQ_CK(c, c->h_up.reserve(pieces + 16ull * (n + 2) + 4096));
+  Uploader up((uint8_t*)c->h_up.p);
+  const size_t o_src = up.put(src.data(), n), o_take = up.put(take.data(), n), o_dst = up.put(dst_off.data(), n);
+  up.used = (up.used + 255) & ~(size_t)255;
+  const size_t o_pieces = up.used;
+  uint8_t* hp = (uint8_t*)c->h_up.p + o_pieces;
+  if (head_len) memcpy(hp, head, head_len);
+  if (tail_len) memcpy(hp + o_tail, tail, tail_len);
+  if (mark_len) memcpy(hp + o_mark, mark, mark_len);
+  up.used += pieces;
+  uint8_t* d_up = c->pool.alloc<uint8_t>(up.used + 256);
+  uint8_t* d_gather = c->pool.alloc<uint8_t>(total_g + 64);
+  PromptArgs a{};
+  a.n_docs = n;
+  a.max_chars = max_chars;
+  a.cut = c->pool.alloc<uint32_t>(n + 1);
+  a.trunc = c->pool.alloc<uint32_t>(n + 1);
+  a.status = c->pool.alloc<int32_t>(n + 1);
+  a.out_len = c->pool.alloc<unsigned long long>(n + 1);
+  a.out_off = c->pool.alloc<unsigned long long>(n + 1);
+  a.out_total = c->pool.alloc<unsigned long long>(1);
+  a.scan_tmp64 = c->pool.alloc<unsigned long long>(scan_partials_needed(n));
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  RFQ_CK(c, cudaMemcpyAsync(d_up, c->h_up.p, up.used, cudaMemcpyHostToDevice, s));
+  RFQ_CK(c, cudaMemsetAsync(d_gather + total_g, 0, 64, s));
+  prompt_gather((const unsigned long long*)(d_up + o_src), (const uint32_t*)(d_up + o_take),
+                (const uint32_t*)(d_up + o_dst), d_gather, n, s);
+  a.arena = d_gather;
+  a.doc_off = (const uint32_t*)(d_up + o_dst); a.doc_len = (const uint32_t*)(d_up + o_take);
+  a.head = d_up + o_pieces; a.head_len = head_len;
+  a.tail = d_up + o_pieces + o_tail; a.tail_len = tail_len;
+  a.mark = d_up + o_pieces + o_mark; a.mark_len = mark_len;
+  prompt_measure(a, s);
+  unsigned long long total = 0;
+  if (n) {
+    RFQ_CK(c, cudaMemcpyAsync(c->h_scalar(), a.out_total, 8, cudaMemcpyDeviceToHost, s));
+    RFQ_CK(c, cudaStreamSynchronize(s));
+    total = *c->h_scalar();
+  }
+  uint8_t* d_text = c->pool.alloc<uint8_t>(total + 16);
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  prompt_emit(a, d_text, s);
+  // the prompts are this run's output; the parsed texts stay where they are until the next run
+  c->segs.clear();
+  c->segs.push_back({d_text, total, 0});
+  c->host_tables = false;
+  prof_mark("end", s);
+  RFQ_CK(c, cudaEventRecord(c->ev1, s));
+  RFQ_CK(c, cudaGetLastError());
+  c->out_total = total;
+  c->d_out_off = a.out_off; c->d_out_len = a.out_len;
+  c->d_status = a.status; c->d_rows = nullptr; c->d_cols = nullptr; c->d_attempt = nullptr;
+  c->have_output = true;
+  c->timed = true;
+  return RFQ_OK;
+}
+
+extern "C" int rfq_csv_prompt_parse(rfq_ctx* c, const uint8_t* arena, const uint64_t* offsets, const uint64_t* lengths,
+                                    uint32_t n, const int64_t* max_rows, const uint8_t* head, uint32_t head_len,
+                                    const uint8_t* tail, uint32_t tail_len, const uint8_t* mark, uint32_t mark_len,
+                                    uint32_t max_chars) {
+  int r = rfq_stage(c, arena, offsets, lengths, n);
+  if (r) return r;
+  r = rfq_csv_prompt_run(c, max_rows, head, head_len, tail, tail_len, mark, mark_len, max_chars);
+  if (r) return r;
+  return rfq_fetch(c);
+}
+
+extern "C" const uint64_t* rfq_out_raw_bytes(const rfq_ctx* c) { return c && !c->raw_bytes.empty() ? c->raw_bytes.data() : nullptr; }
+extern "C" const uint64_t* rfq_out_raw_chars(const rfq_ctx* c) { return c && !c->raw_chars.empty() ? c->raw_chars.data() : nullptr; }
+extern "C" const uint64_t* rfq_out_chars(const rfq_ctx* c) { return c && c->host_tables && !c->r_chars.empty() ? c->r_chars.data() : nullptr; }

@@ -126,11 +126,14 @@ struct rfq_ctx {
   bool overlap_fetch = false;
   std::vector<OutSeg> segs;
   bool host_tables = false;
-  std::vector<uint64_t> r_off, r_len;
+  std::vector<uint64_t> r_off, r_len, r_chars;   // r_chars: code points of the text (~0 = not known)
   std::vector<int32_t> r_status;
   std::vector<uint32_t> r_rows, r_cols;
   std::vector<uint8_t> r_attempt;
   rfq::HostBuf h_up, h_down;   // per-attempt upload / download staging
+  // fused parse -> prompt runs: what the parse stage produced per document (the text itself stays on the device)
+  std::vector<uint64_t> raw_bytes, raw_chars;
+  std::vector<int32_t> status_override;   // applied to the fetched status table (parse failures of a fused run)
   // row pipeline: sizes seen by the last CSV run, used to size the next run's buffers without a sync
   unsigned long long csv2_out_hint = 0;      // output bytes of an attempt
   uint32_t csv2_in_hint = 0, csv2_item_out_hint = 0;   // largest input span / output range of a work item

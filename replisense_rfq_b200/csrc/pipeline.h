@@ -59,6 +59,9 @@ struct PromptArgs {
   unsigned long long* out_total;  // [1]
   unsigned long long* scan_tmp64;
 };
+// the first take[d] bytes of every document, wherever it lies on the device, into one 16-byte aligned arena
+void prompt_gather(const unsigned long long* src_ptr, const uint32_t* take, const uint32_t* dst_off, uint8_t* dst,
+                   uint32_t n_docs, cudaStream_t s);
 void prompt_measure(const PromptArgs& a, cudaStream_t s);
 void prompt_emit(const PromptArgs& a, uint8_t* out, cudaStream_t s);
 

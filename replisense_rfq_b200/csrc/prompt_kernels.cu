@@ -107,6 +107,25 @@ __global__ void __launch_bounds__(256) prompt_emit_kernel(PromptArgs a, uint8_t*
   }
 }
 
+// Fused parse -> prompt runs (rfq_csv_prompt_run): the parsed text stays on the device; only the part
+// a prompt can use (max_chars code points are at most 4 * max_chars bytes) is gathered next to the
+// other documents' so that the prompt kernels see one arena.
+__global__ void __launch_bounds__(256) prompt_gather_kernel(const unsigned long long* __restrict__ src_ptr,
+                                                            const uint32_t* __restrict__ take,
+                                                            const uint32_t* __restrict__ dst_off, uint8_t* __restrict__ dst) {
+  const uint32_t d = blockIdx.x;
+  const uint8_t* src = reinterpret_cast<const uint8_t*>(src_ptr[d]);
+  const uint32_t n = take[d], padded = (n + 15u) & ~15u;
+  uint8_t* o = dst + dst_off[d];
+  for (uint32_t i = threadIdx.x; i < padded; i += blockDim.x) o[i] = i < n ? src[i] : (uint8_t)0;
+}
+void prompt_gather(const unsigned long long* src_ptr, const uint32_t* take, const uint32_t* dst_off, uint8_t* dst,
+                   uint32_t n_docs, cudaStream_t s) {
+  if (n_docs == 0) return;
+  prof_mark("prompt_gather_kernel", s);
+  RFQ_LAUNCH(prompt_gather_kernel, n_docs, 256, 0, s, src_ptr, take, dst_off, dst);
+}
+
 void prompt_measure(const PromptArgs& a, cudaStream_t s) {
   if (a.n_docs == 0) return;
   prof_mark("prompt_measure_kernel", s);

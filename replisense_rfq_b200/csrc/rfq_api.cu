@@ -99,6 +99,7 @@ int rfq_stage(rfq_ctx* c, const uint8_t* arena, const uint64_t* offsets, const u
   c->n_docs = n;
   c->staged = false;
   c->have_output = false;
+  c->status_override.clear(); c->raw_bytes.clear(); c->raw_chars.clear();
   bool aligned = true;
   uint64_t span = 0;
   for (uint32_t d = 0; d < n; ++d) {
@@ -184,6 +185,7 @@ int rfq_text_run(rfq_ctx* c) {
   c->prof.begin();
   RFQ_CK(c, cudaEventRecord(c->ev0, s));
   c->pool.reset();
+  c->status_override.clear();
   TxtArgs a{};
   a.arena = (const uint8_t*)c->d_arena.p;
   a.doc_off = c->d_doc_off; a.doc_len = c->d_doc_len; a.tile_base = c->d_tile_base;
@@ -236,6 +238,7 @@ int rfq_md5_run(rfq_ctx* c) {
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
   RFQ_CK(c, cudaEventRecord(c->ev0, s));
   c->pool.reset();
+  c->status_override.clear();
   unsigned long long* out_off = c->pool.alloc<unsigned long long>(n + 1);
   unsigned long long* out_len = c->pool.alloc<unsigned long long>(n + 1);
   uint8_t* d_text = c->pool.alloc<uint8_t>(32ull * n + 16);
@@ -266,6 +269,7 @@ int rfq_numeric_run(rfq_ctx* c, const uint8_t* kind) {
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
   RFQ_CK(c, cudaEventRecord(c->ev0, s));
   c->pool.reset();
+  c->status_override.clear();
   RFQ_CK(c, c->h_up.reserve(n + 16));
   if (n) memcpy(c->h_up.p, kind, n);
   uint8_t* d_kind = c->pool.alloc<uint8_t>(n + 16);
@@ -303,6 +307,7 @@ int rfq_prompt_run(rfq_ctx* c, const uint8_t* head, uint32_t head_len, const uin
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
   RFQ_CK(c, cudaEventRecord(c->ev0, s));
   c->pool.reset();
+  c->status_override.clear();
   // template pieces: one small pinned upload
   const size_t o_tail = ((size_t)head_len + 15) & ~(size_t)15, o_mark = (o_tail + tail_len + 15) & ~(size_t)15;
   const size_t pieces = o_mark + mark_len + 16;
@@ -409,6 +414,9 @@ int rfq_fetch(rfq_ctx* c) {
   }
   RFQ_CK(c, cudaStreamSynchronize(s));
   if (pre) RFQ_CK(c, cudaStreamSynchronize(c->copy_stream));
+  if (!c->host_tables && c->status_override.size() == n)   // fused parse -> prompt run: parse failures win
+    for (uint32_t d = 0; d < n; ++d)
+      if (c->status_override[d] >= 0) c->h_status[d] = c->status_override[d];
   if (c->timed) {
     cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
     c->prof.finish();

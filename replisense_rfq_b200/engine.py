@@ -261,6 +261,33 @@ class Engine:
                     out.append(err)
             return out
 
+    # -- csv parse fused with prompt assembly: raw_text never leaves the device
+    def csv_prompt_arena(self, arena: PinnedArena, offsets, lengths, max_rows, head: bytes, tail: bytes,
+                         mark: bytes, max_chars: int = 8000) -> BatchResult:
+        """rfq_csv_prompt_parse over a packed pinned arena.  The BatchResult holds the prompts;
+        `.raw_bytes` / `.raw_chars` give the size of each raw_text (text_length of the reference)."""
+        mr = self._mr(len(offsets), max_rows)
+        with self.lock:
+            self._check(self.lib.rfq_csv_prompt_parse(self.ctx, arena.ptr, offsets.ctypes.data, lengths.ctypes.data,
+                                                      len(offsets), mr.ctypes.data, head, len(head), tail, len(tail),
+                                                      mark, len(mark), max_chars), "rfq_csv_prompt_parse")
+            r = BatchResult(self)
+            n = r.n
+            for name, fn in (("raw_bytes", self.lib.rfq_out_raw_bytes), ("raw_chars", self.lib.rfq_out_raw_chars)):
+                ptr = fn(self.ctx)
+                setattr(r, name, np.ctypeslib.as_array((C.c_uint64 * n).from_address(ptr)).copy() if n and ptr
+                        else np.zeros(0, np.uint64))
+            return r
+
+    def csv_prompts_many(self, docs: Sequence[bytes], max_rows, head: bytes, tail: bytes, mark: bytes,
+                         max_chars: int = 8000) -> "list[tuple[str | None, int, int]]":
+        """(prompt or None, text_length in code points, status) per CSV document, one fused GPU call."""
+        with self.lock:
+            a, off, ln = self._pack(docs)
+            r = self.csv_prompt_arena(a, off, ln, max_rows, head, tail, mark, max_chars)
+            return [(r.doc_str(d) if int(r.status[d]) == _lib.DOC_OK else None, int(r.raw_chars[d]), int(r.status[d]))
+                    for d in range(r.n)]
+
     # -- sheets
     def sheets_batch(self, docs: Sequence[bytes], kind, sst_of, max_rows=1000, date_ids=None) -> BatchResult:
         """docs: worksheet XML parts (kind 0, or 2 = workbook with the 1904 epoch) and sharedStrings

@@ -65,3 +65,12 @@ def build_prompts(engine, texts: Sequence[str], template: str = EXTRACTION_PROMP
                                 TRUNCATION_MARK.encode("utf-8"), max_chars)
         st = np.asarray(r.status)
         return [None if int(st[d]) else r.doc_str(d) for d in range(r.n)]
+
+
+def csv_to_prompts(engine, docs: Sequence[bytes], max_rows: int = 1000, template: str = EXTRACTION_PROMPT_TEMPLATE,
+                   max_chars: int = MAX_PROMPT_CHARS) -> "list[tuple[Optional[str], int, int]]":
+    """What /upload/ needs of a CSV file (app/main.py:243-273): the prompt the reference would send and
+    `text_length`, in ONE fused GPU call — raw_text is parsed and wrapped on the device and never
+    downloaded.  Returns (prompt | None, len(raw_text) in code points, RFQ_DOC_* status) per document."""
+    return engine.csv_prompts_many(docs, max_rows, (template + '\n"""\n').encode("utf-8"), PROMPT_TAIL.encode("utf-8"),
+                                   TRUNCATION_MARK.encode("utf-8"), max_chars)

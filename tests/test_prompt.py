@@ -80,3 +80,35 @@ def test_prompts_after_parser_on_gpu(tmp_path):
     got = P.build_prompts(eng, raw)
     assert got == [build_prompt(t, P.EXTRACTION_PROMPT_TEMPLATE) for t in raw]
     assert got[2].endswith('... [truncated]\n"""')
+
+
+@pytest.mark.gpu
+def test_fused_csv_to_prompt_on_gpu():
+    """rfq_csv_prompt_parse: parse and prompt assembly back to back on the device (raw_text is never
+    downloaded) give the reference's prompt and text_length for every document, and the parse stage's
+    verdict where it fails."""
+    from oracle import file_parser_oracle as O
+    from replisense_rfq_b200 import Engine, build, _lib
+    from tests import corpus
+    build.build()
+    eng = Engine(0)
+    docs = [corpus.rfq_csv(n, seed=n) for n in (3, 40, 400, 30000)] + [corpus.fuzz_csv(s) for s in range(70000, 70300)]
+    docs += [b"a\n1\n", b"", "näme,₹\n日本語,₹500\nWürth,1\n".encode()]
+    got = P.csv_to_prompts(eng, docs, 1000)
+    n_ok = 0
+    for d, (prompt, chars, status) in zip(docs, got):
+        try:
+            raw = O.parse_csv_bytes(d, 1000)
+        except O.OracleParsingError:
+            raw = None
+        if status == _lib.DOC_UNSUPPORTED:
+            assert corpus.bare_cr_blank_first(d)
+            continue
+        if raw is None:
+            assert status == _lib.DOC_CSV_UNPARSEABLE and prompt is None
+            continue
+        assert status == _lib.DOC_OK
+        assert prompt == build_prompt(raw, P.EXTRACTION_PROMPT_TEMPLATE)
+        assert chars == len(raw) or chars == 2 ** 64 - 1   # ~0: the three-sweep path does not count
+        n_ok += chars == len(raw)
+    assert n_ok > 200
