@@ -138,6 +138,23 @@ const uint64_t* rfq_out_raw_chars(const rfq_ctx* ctx);
  * binding build its string object without scanning the bytes when chars == bytes (ASCII) */
 const uint64_t* rfq_out_chars(const rfq_ctx* ctx);
 
+/* ---- mixed batch: text, CSV and sheet documents in ONE arena, one upload.  The
+ * reference dispatches on the file suffix (app/file_parser.py:62-77); kind[d] carries that decision:
+ * RFQ_KIND_TEXT → the text path, RFQ_KIND_CSV → the CSV path (max_rows[d] = max_excel_rows),
+ * RFQ_KIND_SHEET / RFQ_KIND_SHEET_1904 / RFQ_KIND_SST → the sheet path (sst_of, date_off, date_ids as in
+ * rfq_sheets_run, indices into THIS batch; date_off has n_docs + 1 entries).  Results come back in input
+ * order with the statuses of the respective paths; a sharedStrings part has no output of its own. */
+#define RFQ_KIND_TEXT 0
+#define RFQ_KIND_CSV 1
+#define RFQ_KIND_SHEET 2
+#define RFQ_KIND_SHEET_1904 3
+#define RFQ_KIND_SST 4
+int rfq_mixed_run(rfq_ctx* ctx, const uint8_t* kind, const int64_t* max_rows, const int32_t* sst_of,
+                  const uint32_t* date_off, const uint32_t* date_ids);
+int rfq_mixed_parse(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets, const uint64_t* lengths,
+                    uint32_t n_docs, const uint8_t* kind, const int64_t* max_rows, const int32_t* sst_of,
+                    const uint32_t* date_off, const uint32_t* date_ids);
+
 /* ---- device → host copy of the last run's output ---- */
 int rfq_fetch(rfq_ctx* ctx);
 

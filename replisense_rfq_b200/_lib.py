@@ -50,6 +50,8 @@ SIGNATURES = {
     "rfq_out_raw_bytes": (C.c_void_p, [C.c_void_p]),
     "rfq_out_raw_chars": (C.c_void_p, [C.c_void_p]),
     "rfq_out_chars": (C.c_void_p, [C.c_void_p]),
+    "rfq_mixed_run": (C.c_int, [C.c_void_p] * 6),
+    "rfq_mixed_parse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32] + [C.c_void_p] * 5),
     "rfq_out_count": (C.c_uint32, [C.c_void_p]),
     "rfq_out_text": (C.c_void_p, [C.c_void_p]),
     "rfq_out_offsets": (C.c_void_p, [C.c_void_p]),
@@ -68,6 +70,7 @@ SIGNATURES = {
     "rfq_text_normalise_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                              C.c_void_p]),
 }
+KIND_TEXT, KIND_CSV, KIND_SHEET, KIND_SHEET_1904, KIND_SST = 0, 1, 2, 3, 4
 NOALLOC_MAX_BYTES = 4 << 20
 ERR_TOO_LARGE = -4
 

@@ -137,6 +137,11 @@ struct rfq_ctx {
   // row pipeline: sizes seen by the last CSV run, used to size the next run's buffers without a sync
   unsigned long long csv2_out_hint = 0;      // output bytes of an attempt
   uint32_t csv2_in_hint = 0, csv2_item_out_hint = 0;   // largest input span / output range of a work item
+  // rfq_mixed_run drives the text / CSV / sheet runs over subsets of one staged batch: a nested run
+  // keeps the scratch pool and the timing events of the outer call
+  bool nested = false;
+  rfq::DevBuf d_viewtab;
+  rfq::HostBuf h_viewtab;
   float last_ms = 0.f;
   uint64_t h2d_bytes = 0, d2h_bytes = 0;
 
@@ -146,7 +151,7 @@ struct rfq_ctx {
   }
   void release_all() {
     pool.release();
-    d_arena.release(); d_doctab.release(); d_out.release(); d_arena2.release();
+    d_arena.release(); d_doctab.release(); d_out.release(); d_arena2.release(); d_viewtab.release(); h_viewtab.release();
     h_stage.release(); h_doctab.release(); h_out.release(); h_tabs.release(); h_small.release(); h_up.release(); h_down.release();
   }
 };

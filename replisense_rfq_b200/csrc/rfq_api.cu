@@ -182,9 +182,8 @@ int rfq_text_run(rfq_ctx* c) {
   RFQ_CK(c, cudaSetDevice(c->device));
   cudaStream_t s = c->stream;
   uint32_t n = c->n_docs, nt = c->n_tiles;
-  c->prof.begin();
-  RFQ_CK(c, cudaEventRecord(c->ev0, s));
-  c->pool.reset();
+  if (!c->nested) c->prof.begin();
+  if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
   c->status_override.clear();
   TxtArgs a{};
   a.arena = (const uint8_t*)c->d_arena.p;
@@ -233,11 +232,10 @@ int rfq_md5_run(rfq_ctx* c) {
   RFQ_CK(c, cudaSetDevice(c->device));
   cudaStream_t s = c->stream;
   uint32_t n = c->n_docs;
-  c->prof.begin();
+  if (!c->nested) c->prof.begin();
   g_prof = &c->prof;
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
-  RFQ_CK(c, cudaEventRecord(c->ev0, s));
-  c->pool.reset();
+  if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
   c->status_override.clear();
   unsigned long long* out_off = c->pool.alloc<unsigned long long>(n + 1);
   unsigned long long* out_len = c->pool.alloc<unsigned long long>(n + 1);
@@ -264,11 +262,10 @@ int rfq_numeric_run(rfq_ctx* c, const uint8_t* kind) {
   RFQ_CK(c, cudaSetDevice(c->device));
   cudaStream_t s = c->stream;
   uint32_t n = c->n_docs;
-  c->prof.begin();
+  if (!c->nested) c->prof.begin();
   g_prof = &c->prof;
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
-  RFQ_CK(c, cudaEventRecord(c->ev0, s));
-  c->pool.reset();
+  if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
   c->status_override.clear();
   RFQ_CK(c, c->h_up.reserve(n + 16));
   if (n) memcpy(c->h_up.p, kind, n);
@@ -302,11 +299,10 @@ int rfq_prompt_run(rfq_ctx* c, const uint8_t* head, uint32_t head_len, const uin
   RFQ_CK(c, cudaSetDevice(c->device));
   cudaStream_t s = c->stream;
   uint32_t n = c->n_docs;
-  c->prof.begin();
+  if (!c->nested) c->prof.begin();
   g_prof = &c->prof;
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
-  RFQ_CK(c, cudaEventRecord(c->ev0, s));
-  c->pool.reset();
+  if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
   c->status_override.clear();
   // template pieces: one small pinned upload
   const size_t o_tail = ((size_t)head_len + 15) & ~(size_t)15, o_mark = (o_tail + tail_len + 15) & ~(size_t)15;

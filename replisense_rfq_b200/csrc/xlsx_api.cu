@@ -40,11 +40,10 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
   RFQ_CK(c, cudaSetDevice(c->device));
   cudaStream_t s = c->stream;
   const uint32_t n = c->n_docs;
-  c->prof.begin();
+  if (!c->nested) c->prof.begin();
   g_prof = &c->prof;
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
-  RFQ_CK(c, cudaEventRecord(c->ev0, s));
-  c->pool.reset();
+  if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
   c->status_override.clear();
   c->segs.clear();
   c->out_total = 0;

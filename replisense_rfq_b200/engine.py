@@ -321,6 +321,33 @@ class Engine:
                                               doff.ctypes.data, dids.ctypes.data), "rfq_sheets_parse")
         return BatchResult(self)
 
+    # -- mixed batch: text, CSV and sheet parts in one arena, one upload (rfq_mixed_parse)
+    def mixed_parse_arena(self, arena: PinnedArena, offsets, lengths, kind, max_rows=1000, sst_of=None,
+                          date_ids=None) -> BatchResult:
+        n = len(offsets)
+        kind = np.ascontiguousarray(kind, dtype=np.uint8)
+        mr = self._mr(n, max_rows)
+        so = np.full(n, -1, dtype=np.int32) if sst_of is None else np.ascontiguousarray(sst_of, dtype=np.int32)
+        doff = np.zeros(n + 1, dtype=np.uint32)
+        flat = []
+        if date_ids is not None:
+            for d in range(n):
+                if date_ids[d]:
+                    flat.extend(sorted(date_ids[d]))
+                doff[d + 1] = len(flat)
+        dids = np.asarray(flat if flat else [0], dtype=np.uint32)
+        with self.lock:
+            self._check(self.lib.rfq_mixed_parse(self.ctx, arena.ptr, offsets.ctypes.data, lengths.ctypes.data, n,
+                                                 kind.ctypes.data, mr.ctypes.data, so.ctypes.data,
+                                                 doff.ctypes.data, dids.ctypes.data), "rfq_mixed_parse")
+            return BatchResult(self)
+
+    def mixed_batch(self, docs: Sequence[bytes], kind, max_rows=1000, sst_of=None, date_ids=None) -> BatchResult:
+        """docs[i] of kind[i] (_lib.KIND_*): one pack, one upload, the three pipelines over their subsets."""
+        with self.lock:
+            a, off, ln = self._pack(docs)
+            return self.mixed_parse_arena(a, off, ln, kind, max_rows, sst_of, date_ids)
+
     # -- pre-packed pinned arena (no Python-side copies): what a high-throughput caller uses
     def _mr(self, n, max_rows):
         if np.isscalar(max_rows):

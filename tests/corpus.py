@@ -634,3 +634,48 @@ def strip_refs(sheet_xml: bytes, rows: bool = True, cells: bool = True) -> bytes
     if cells:
         s = re.sub(rb'<c r="[A-Z]+\d+"', b"<c", s)
     return s
+
+
+# ------------------------------------------------------------------ .xlsx containers
+_WB_XML = ('<?xml version="1.0" encoding="UTF-8" standalone="yes"?>\n'
+           '<workbook xmlns="http://schemas.openxmlformats.org/spreadsheetml/2006/main" '
+           'xmlns:r="http://schemas.openxmlformats.org/officeDocument/2006/relationships"><sheets>%s</sheets></workbook>')
+_RELS_XML = ('<?xml version="1.0" encoding="UTF-8" standalone="yes"?>\n'
+             '<Relationships xmlns="http://schemas.openxmlformats.org/package/2006/relationships">%s</Relationships>')
+_REL_WS = "http://schemas.openxmlformats.org/officeDocument/2006/relationships/worksheet"
+_REL_SST = "http://schemas.openxmlformats.org/officeDocument/2006/relationships/sharedStrings"
+
+
+def make_xlsx(sheets, sst_xml, names=None, level: int = 6) -> bytes:
+    """An .xlsx container (zip, DEFLATE) around worksheet parts + one sharedStrings part."""
+    import io
+    import zipfile
+    names = names or ["Sheet%d" % (i + 1) for i in range(len(sheets))]
+    sh = "".join('<sheet name="%s" sheetId="%d" r:id="rId%d"/>' % (xml_escape(nm), i + 1, i + 1) for i, nm in enumerate(names))
+    rel = "".join('<Relationship Id="rId%d" Type="%s" Target="worksheets/sheet%d.xml"/>' % (i + 1, _REL_WS, i + 1)
+                  for i in range(len(sheets)))
+    rel += '<Relationship Id="rId%d" Type="%s" Target="sharedStrings.xml"/>' % (len(sheets) + 1, _REL_SST)
+    buf = io.BytesIO()
+    with zipfile.ZipFile(buf, "w", zipfile.ZIP_DEFLATED if level else zipfile.ZIP_STORED, compresslevel=level or None) as z:
+        z.writestr("xl/workbook.xml", _WB_XML % sh)
+        z.writestr("xl/_rels/workbook.xml.rels", _RELS_XML % rel)
+        z.writestr("xl/sharedStrings.xml", sst_xml)
+        for i, x in enumerate(sheets):
+            z.writestr("xl/worksheets/sheet%d.xml" % (i + 1), x)
+    return buf.getvalue()
+
+
+def mixed_batch(n: int, seed: int = 0):
+    """Config C5 in miniature: (documents, kinds) — 40 % CSV (10-2000 rows), 30 % .xlsx, 30 % text bodies."""
+    r = random.Random(seed)
+    docs, kinds = [], []
+    for i in range(n):
+        x = r.random()
+        if x < 0.4:
+            docs.append(rfq_csv(r.choice([10, 25, 60, 150, 400, 2000]), seed=seed * 100003 + i)); kinds.append("csv")
+        elif x < 0.7:
+            sx, ss = sheet_xml_doc(seed * 100003 + i)
+            docs.append(make_xlsx([sx], ss)); kinds.append("xlsx")
+        else:
+            docs.append(text_body(seed * 100003 + i)); kinds.append("txt")
+    return docs, kinds
