@@ -156,6 +156,8 @@ def main():
     ap.add_argument("--ref-sample-rows", type=int, default=20_000)
     ap.add_argument("--cpu-sample-rows", type=int, default=100_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--config-scale", type=float, default=1.0,
+                    help="document counts of the C3 / C4 / C5 entries relative to BASELINE.json (0 = skip them)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -351,6 +353,15 @@ def main():
     os.unlink(fpath)
     t_py = min(t_py)
 
+    # ---- BASELINE configs C3 / C4 / C5 at their stated sizes (extra keys; strong scaling over the ranks)
+    configs = None
+    if args.config_scale > 0:
+        arena.free()
+        del flush
+        torch.cuda.empty_cache()
+        from tools import bench_configs
+        hbm_peak, _ = peaks()
+        configs = bench_configs.run_all(eng, torch, dist if world > 1 else None, rank, world, hbm_peak, args.config_scale)
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -401,6 +412,8 @@ def main():
         "kernel_ms_per_step": {k: round(v / args.steps, 4) for k, v in sorted(prof_acc.items(), key=lambda x: -x[1])},
         "clocks": sampler.summary(),
     }
+    if configs is not None:
+        line["configs"] = configs
     if not args.no_cpu_baseline:
         rows = min(args.cpu_sample_rows, args.rows)
         sample = make_doc(rows, seed=0)

@@ -33,7 +33,8 @@ struct Doc2 {
   uint32_t slot_base;             // rec_start[slot_base + k] = start of record k (k <= max_rows + 1)
   uint32_t item_base, n_items;    // work items (RFQ2_ROWS data rows each), at least one
   uint32_t stat_base, n_chunks;   // (chunk, col) entries at stat_base + chunk * W + col; chunks carved
-  uint32_t col_base;              // output columns at col_base + j
+  uint32_t col_base;              // layout of output column j at col_base + j
+  uint32_t name_base;             // its label at name_base + j (shared by documents with the same header record)
   uint32_t banner_off, banner_len, empty_off, empty_len, hdr_extra;   // texts in the names arena
   uint32_t latin1;                // the bytes are latin-1 (every high byte is one character, two bytes of output)
 };

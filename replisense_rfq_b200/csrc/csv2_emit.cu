@@ -109,17 +109,17 @@ __global__ void __launch_bounds__(RFQ2_ROWS) csv2_emit_kernel(Csv2Args a, uint32
           for (uint32_t j = lane; j < D.h; j += 32) {
             const ColOut2 co = a.col[D.col_base + j];
             uint32_t xb = 0;
-            for (uint32_t j2 = 0; j2 < j; ++j2) xb += a.name_len[D.col_base + j2] - a.name_cp[D.col_base + j2];
+            for (uint32_t j2 = 0; j2 < j; ++j2) xb += a.name_len[D.name_base + j2] - a.name_cp[D.name_base + j2];
             const bool numeric = co.cls == CC_INT || co.cls == CC_UINT || co.cls == CC_FLOAT || co.cls == CC_BOOL;
-            const uint32_t cp = a.name_cp[D.col_base + j] + (numeric ? 1u : 0u);
+            const uint32_t cp = a.name_cp[D.name_base + j] + (numeric ? 1u : 0u);
             uint8_t* q = p + co.cp_off + xb;
             if (j) q[-1] = ' ';
             const uint32_t pad = co.width - cp;
             for (uint32_t i = 0; i < pad; ++i) q[i] = ' ';
             q += pad;
             if (numeric) *q++ = ' ';
-            const uint8_t* nm = a.names + a.name_off[D.col_base + j];
-            const uint32_t nl = a.name_len[D.col_base + j];
+            const uint8_t* nm = a.names + a.name_off[D.name_base + j];
+            const uint32_t nl = a.name_len[D.name_base + j];
             for (uint32_t i = 0; i < nl; ++i) q[i] = nm[i];
           }
         }

@@ -328,7 +328,7 @@ __global__ void __launch_bounds__(256) csv2_plan_kernel(Csv2Args a) {
       for (uint32_t k = 0; k < n_chunks; ++k) nan_left |= meas[e0 + (size_t)k * W].nan_left != 0;
       int cls = fold_column_class(a.ctype + e0, n_chunks, W, nan_left);
       if (cls == CC_UNSUP) { unsup = true; cls = CC_OBJ; }
-      const ColumnLayout L = layout_column(cls, meas + e0, a.ctype + e0, n_chunks, W, a.name_cp[D.col_base + j]);
+      const ColumnLayout L = layout_column(cls, meas + e0, a.ctype + e0, n_chunks, W, a.name_cp[D.name_base + j]);
       o.cls = L.cls; o.dec = L.dec; o.sci = L.sci ? 1 : 0; o.width = L.width;
       w1 = L.width + 1;
     }

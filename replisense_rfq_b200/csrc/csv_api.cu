@@ -7,6 +7,7 @@
 #include <string.h>
 #include <algorithm>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/rfq_parse.h"
@@ -331,35 +332,79 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
                         std::vector<uint8_t>& resolved, std::vector<uint32_t>& general) {
   cudaStream_t s = c->stream;
   const uint32_t sep = kSeps[sep_i];
-  // ---- 1. headers on the host; documents the header already decides
-  std::vector<uint32_t> act;            // indices into sel
-  std::vector<HeaderInfo> hdrs;
+  // ---- 1. headers on the host; documents the header already decides.  The scan of the first two
+  // records allocates nothing; names are built once per DISTINCT header record (batches of files made
+  // from one template share it), and their texts are stored once in the names arena.
+  struct HeaderTexts { HeaderInfo info; uint32_t banner_off, banner_len, empty_off, empty_len, hdr_extra, name_base; };
+  std::unordered_map<std::string, uint32_t> seen;   // header record bytes -> index into hts
+  std::vector<HeaderTexts> hts;
+  std::vector<uint32_t> act, act_ht, act_first_nf;  // indices into sel / hts, second-record fields
+  std::vector<uint32_t> name_off, name_len, name_cp;
+  std::string names, key;
+  std::vector<HeaderScan> scans(sel.size());
+  {
+    const DfaTables dfa(sep);
+    parallel_for((uint32_t)sel.size(), [&](uint32_t i) {
+      const uint32_t d = sel[i];
+      scans[i] = scan_header(c->h_arena + c->h_doc_off[d], c->h_doc_len[d], dfa, enc == 1);
+    });
+  }
   for (uint32_t i = 0; i < sel.size(); ++i) {
     const uint32_t d = sel[i];
-    HeaderInfo h = parse_header(c->h_arena + c->h_doc_off[d], c->h_doc_len[d], sep, enc == 1);
-    if (!h.found || !h.utf8_ok || h.names.size() <= 1) continue;       // EmptyDataError / decode error / len(df.columns) <= 1
-    const uint32_t W = std::max<uint32_t>((uint32_t)h.names.size(), h.first_nf);
+    const uint8_t* hdoc = c->h_arena + c->h_doc_off[d];
+    const HeaderScan& hs = scans[i];
+    if (!hs.found || hs.h <= 1) continue;                       // EmptyDataError / len(df.columns) <= 1
+    key.assign((const char*)hdoc + hs.begin, (size_t)(hs.end - hs.begin));
+    auto it = seen.find(key);
+    uint32_t hi;
+    if (it != seen.end()) hi = it->second;
+    else {
+      HeaderTexts T;
+      T.info = parse_header(hdoc, c->h_doc_len[d], sep, enc == 1);
+      T.banner_off = T.banner_len = T.empty_off = T.empty_len = T.hdr_extra = T.name_base = 0;
+      if (T.info.found && T.info.utf8_ok) {
+        const HeaderInfo& H = T.info;
+        std::string banner = std::string("=== CSV Data (using ") + kEncNames[enc] + ", separator '" + (char)sep + "') ===\n";
+        T.banner_off = (uint32_t)names.size(); T.banner_len = (uint32_t)banner.size();
+        names += banner;
+        std::string empty = empty_frame_text(H.names);
+        T.empty_off = (uint32_t)names.size(); T.empty_len = (uint32_t)empty.size();
+        names += empty;
+        T.name_base = (uint32_t)name_off.size();
+        for (size_t j = 0; j < H.names.size(); ++j) {
+          name_off.push_back((uint32_t)names.size());
+          name_len.push_back((uint32_t)H.disp[j].size());
+          name_cp.push_back(H.ncp[j]);
+          T.hdr_extra += (uint32_t)H.disp[j].size() - H.ncp[j];
+          names += H.disp[j];
+        }
+      }
+      hi = (uint32_t)hts.size();
+      hts.push_back(std::move(T));
+      seen.emplace(key, hi);
+    }
+    const HeaderInfo& H = hts[hi].info;
+    if (!H.found || !H.utf8_ok || H.names.size() <= 1) continue;   // decode error in a label
+    const uint32_t W = std::max<uint32_t>((uint32_t)H.names.size(), hs.first_nf);
     if (W > 1024) { resolved[d] = 1; c->r_status[d] = RFQ_DOC_UNSUPPORTED; continue; }
-    act.push_back(i);
-    hdrs.push_back(std::move(h));
+    act.push_back(i); act_ht.push_back(hi); act_first_nf.push_back(hs.first_nf);
   }
   const uint32_t m = (uint32_t)act.size();
   if (m == 0) return RFQ_OK;
   // ---- 2. carve
   std::vector<Doc2> docs(m);
-  std::vector<uint32_t> tile_base(m + 1), item_base(m + 1), name_off, name_len, name_cp;
-  std::string names;
+  std::vector<uint32_t> tile_base(m + 1), item_base(m + 1);
   uint64_t tiles = 0, n_slots = 0, n_items = 0, n_stat = 0, n_cols = 0, in_bytes = 0, cells = 0, meta_vecs = 0;
   uint32_t max_w = 1;
   for (uint32_t k = 0; k < m; ++k) {
     const uint32_t d = sel[act[k]];
-    const HeaderInfo& H = hdrs[k];
+    const HeaderTexts& T = hts[act_ht[k]];
     Doc2& D = docs[k];
     memset(&D, 0, sizeof(D));
     D.off = off[d]; D.len = len[d]; D.sep = sep;
     D.max_rows = (uint32_t)std::min<int64_t>(std::max<int64_t>(max_rows[d], 0), 0x7FFFFFF0);
-    D.h = (uint32_t)H.names.size();
-    D.W = std::max<uint32_t>(D.h, H.first_nf);
+    D.h = (uint32_t)T.info.names.size();
+    D.W = std::max<uint32_t>(D.h, act_first_nf[k]);
     D.lead = D.W - D.h;
     D.bl = chunk_rows_for_width(D.W);
     D.latin1 = enc == 1;
@@ -369,26 +414,16 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
     n_items += D.n_items;
     D.stat_base = (uint32_t)n_stat; D.n_chunks = (uint32_t)std::max<uint64_t>(1, (rows_bound + D.bl - 1) / D.bl);
     n_stat += (uint64_t)D.n_chunks * D.W;
-    D.col_base = (uint32_t)n_cols; n_cols += D.h;
+    D.col_base = (uint32_t)n_cols; n_cols += D.h;      // layout of this document's columns
+    D.name_base = T.name_base;                          // labels: shared by every document with this header record
     D.meta_base = (uint32_t)meta_vecs; meta_vecs += rows_bound * RFQ2_META_VECS(D.W);
     cells += rows_bound * D.W;
     max_w = std::max(max_w, D.W);
     tile_base[k] = (uint32_t)tiles; item_base[k] = D.item_base;
     tiles += ((uint64_t)D.len + 1 + RFQ_TILE - 1) / RFQ_TILE;
     in_bytes += D.len;
-    std::string banner = std::string("=== CSV Data (using ") + kEncNames[enc] + ", separator '" + (char)sep + "') ===\n";
-    D.banner_off = (uint32_t)names.size(); D.banner_len = (uint32_t)banner.size();
-    names += banner;
-    std::string empty = empty_frame_text(H.names);
-    D.empty_off = (uint32_t)names.size(); D.empty_len = (uint32_t)empty.size();
-    names += empty;
-    for (uint32_t j = 0; j < D.h; ++j) {
-      name_off.push_back((uint32_t)names.size());
-      name_len.push_back((uint32_t)H.disp[j].size());
-      name_cp.push_back(H.ncp[j]);
-      D.hdr_extra += (uint32_t)H.disp[j].size() - H.ncp[j];
-      names += H.disp[j];
-    }
+    D.banner_off = T.banner_off; D.banner_len = T.banner_len;
+    D.empty_off = T.empty_off; D.empty_len = T.empty_len; D.hdr_extra = T.hdr_extra;
   }
   tile_base[m] = (uint32_t)tiles; item_base[m] = (uint32_t)n_items;
   if (n_slots >= (1ull << 31) || n_items >= (1ull << 31) || n_stat >= (1ull << 31) || tiles >= (1ull << 31) ||
@@ -401,7 +436,7 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
   a.n_items = (uint32_t)n_items; a.n_slots = (uint32_t)n_slots; a.n_stat = (uint32_t)n_stat; a.n_cols = (uint32_t)n_cols;
   a.max_w = max_w;
   // ---- 3. upload the description
-  RFQ_CK(c, c->h_up.reserve(sizeof(Doc2) * (m + 1) + 8ull * (m + 2) + 12ull * (n_cols + 1) + names.size() + 8192));
+  RFQ_CK(c, c->h_up.reserve(sizeof(Doc2) * (m + 1) + 8ull * (m + 2) + 12ull * (name_off.size() + 1) + names.size() + 8192));
   Uploader up((uint8_t*)c->h_up.p);
   const size_t o_docs = up.put(docs.data(), m), o_tb = up.put(tile_base.data(), m + 1), o_ib = up.put(item_base.data(), m + 1);
   const size_t o_no = up.put(name_off.data(), name_off.size()), o_nl = up.put(name_len.data(), name_len.size());
@@ -509,7 +544,7 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
     {   // code points of the text: bytes minus the continuation bytes of the header line and of the rows
       uint64_t ex = h_run[k].extra;
       if (h_run[k].n_keep) ex += docs[k].hdr_extra;
-      else { uint32_t cp = 0; std::string e = empty_frame_text(hdrs[k].names); utf8_valid_count(e, &cp); ex += e.size() - cp; }
+      else { uint32_t cp = 0; std::string e = empty_frame_text(hts[act_ht[k]].info.names); utf8_valid_count(e, &cp); ex += e.size() - cp; }
       c->r_chars[d] = h_olen[k] - ex;
     }
     c->r_attempt[d] = (uint8_t)(enc * 3 + sep_i);

@@ -5,7 +5,9 @@
 // data rows never pass through here.
 #pragma once
 #include <stdint.h>
+#include <algorithm>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -115,6 +117,79 @@ inline void dedupe_names(std::vector<std::string>& raw, const std::vector<size_t
     raw[i2] = col;
     counts[col] = cur + 1;
   }
+}
+
+// The first two records of a document without building anything: where the header record lies, how
+// many fields it and the record after it have.  O(bytes of two records), no allocation — what decides
+// whether an (encoding, separator) attempt is worth sending to the device at all.
+struct HeaderScan {
+  bool found = false;          // a header record exists
+  uint64_t begin = 0, end = 0; // bytes of the header record: [begin, end), end = its terminator (or len)
+  uint32_t h = 0;              // its fields
+  uint32_t first_nf = 0;       // fields of the second record (0 = none)
+};
+// the DFA as tables: byte -> class for one separator, (state, class) -> next state / events
+struct DfaTables {
+  uint8_t cls[256];
+  uint8_t next[8][8], ev[8][8];
+  explicit DfaTables(uint32_t sep) {
+    for (int b = 0; b < 256; ++b) cls[b] = (uint8_t)csv_class((uint32_t)b, sep);
+    for (int st = 0; st < 8; ++st)
+      for (int c = 0; c < 8; ++c) {
+        next[st][c] = c < N_CLASSES ? (uint8_t)csv_next(st, c) : (uint8_t)st;
+        ev[st][c] = c < N_CLASSES ? (uint8_t)csv_events(st, c) : 0;
+      }
+  }
+};
+inline HeaderScan scan_header(const uint8_t* doc, uint64_t len, const DfaTables& T, bool latin1 = false) {
+  HeaderScan r;
+  uint64_t i = 0;
+  if (!latin1 && len >= 3 && doc[0] == 0xEF && doc[1] == 0xBB && doc[2] == 0xBF) i = 3;
+  int st = ST_R;
+  uint64_t ws_start = 0;
+  bool open = false, done = false;
+  for (; i <= len && !done; ++i) {
+    const int cl = (i == len) ? CL_LF : T.cls[doc[i]];
+    const int ev = T.ev[st][cl];
+    const int ns = T.next[st][cl];
+    if (st != ST_W && ns == ST_W) ws_start = i;
+    if (ev) {
+      if (ev & EV_REC_START) { open = true; r.begin = i; }
+      if (ev & EV_REC_START_WS) { open = true; r.begin = ws_start; }
+      if (ev & EV_FIELD_END) ++r.h;
+      if (ev & EV_LINE_END) { done = true; r.end = i; }
+    }
+    st = ns;
+  }
+  if (!done || !open) return r;
+  r.found = true;
+  bool done2 = false;
+  uint32_t nf2 = 0;
+  for (; i <= len && !done2; ++i) {
+    const int cl = (i == len) ? CL_LF : T.cls[doc[i]];
+    const int ev = T.ev[st][cl];
+    if (ev & EV_FIELD_END) ++nf2;
+    if (ev & EV_LINE_END) done2 = true;
+    st = T.next[st][cl];
+  }
+  r.first_nf = done2 ? nf2 : 0;
+  return r;
+}
+inline HeaderScan scan_header(const uint8_t* doc, uint64_t len, uint32_t sep, bool latin1 = false) {
+  return scan_header(doc, len, DfaTables(sep), latin1);
+}
+
+// fn(i) for i in [0, n) on a few host threads (the per-document host work of big batches)
+template <class F>
+inline void parallel_for(uint32_t n, F&& fn) {
+  unsigned hw = std::thread::hardware_concurrency();
+  const uint32_t nt = n < 8192 ? 1u : std::min<uint32_t>(hw ? hw : 4u, 16u);
+  if (nt <= 1) { for (uint32_t i = 0; i < n; ++i) fn(i); return; }
+  std::vector<std::thread> th;
+  const uint32_t per = (n + nt - 1) / nt;
+  for (uint32_t t = 0; t < nt; ++t)
+    th.emplace_back([=, &fn] { for (uint32_t i = t * per; i < std::min<uint32_t>(n, (t + 1) * per); ++i) fn(i); });
+  for (auto& x : th) x.join();
 }
 
 // Tokenise the first record of `doc` with the same DFA the kernels run.

@@ -6,6 +6,7 @@
 #include <string.h>
 #include <algorithm>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/rfq_parse.h"
@@ -185,49 +186,65 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
   // ---- 5. column names (python engine: blank -> "Unnamed: k", duplicates mangled)
   std::vector<uint32_t> name_off(n_cols), name_len(n_cols), name_cp(n_cols);
   std::string names;
+  // sheets cut from one template share their header row: labels are built once per distinct row
+  struct HdrTexts { bool ok = true; std::vector<std::string> disp; std::vector<uint32_t> ncp; std::string empty; };
+  std::unordered_map<std::string, HdrTexts> hdr_cache;
+  std::string hkey;
   for (uint32_t d = 0; d < n; ++d) {
     TDoc& T = td[d];
     if (!T.active) continue;
-    std::vector<std::string> raw(T.W);
-    std::vector<size_t> unnamed;
-    bool ok = true, all_int = true;
-    std::vector<int> lkind(T.W, 0);
+    hkey.clear();
     for (uint32_t j = 0; j < T.W; ++j) {
-      uint32_t g = T.col_base + j, mode = h_hmeta[2 * g], len = h_hmeta[2 * g + 1];
-      if (mode != CM_INT) all_int = false;
-      lkind[j] = mode == CM_INT ? 1 : mode == CM_BOOL ? 2 : mode == CM_DATE ? 3 : mode == CM_TIME ? 4
-                 : (mode == CM_RAW || mode == CM_XML || mode == CM_NULL) ? 0 : 9;
-      if (mode == CM_NULL) { raw[j] = "Unnamed: " + std::to_string(j); unnamed.push_back(j); }
-      else if (lkind[j] != 9 && len != 0xFFFFFFFFu) raw[j].assign((const char*)h_hdr + (size_t)g * 256, len);
-      else ok = false;  // float / oversized labels
+      const uint32_t g = T.col_base + j, len = h_hmeta[2 * g + 1];
+      hkey.append((const char*)&h_hmeta[2 * g], 8);
+      if (len != 0xFFFFFFFFu) hkey.append((const char*)h_hdr + (size_t)g * 256, std::min<uint32_t>(len, 256));
     }
-    if (ok && !sheet_labels_supported(lkind, raw)) ok = false;
-    if (!ok) { T.active = 0; c->r_status[d] = RFQ_DOC_UNSUPPORTED; continue; }
-    std::vector<std::string> before = raw;
-    dedupe_names(raw, unnamed);
-    if (all_int && before == raw) {
-      // an all-integer header is an Int64 Index: pandas left-justifies its labels to one width
-      size_t mx = 0;
-      for (auto& x : raw) mx = std::max(mx, x.size());
-      for (auto& x : raw) x.append(mx - x.size(), ' ');
+    auto hit = hdr_cache.find(hkey);
+    if (hit == hdr_cache.end()) {
+      HdrTexts H;
+      std::vector<std::string> raw(T.W);
+      std::vector<size_t> unnamed;
+      bool all_int = true;
+      std::vector<int> lkind(T.W, 0);
+      for (uint32_t j = 0; j < T.W; ++j) {
+        uint32_t g = T.col_base + j, mode = h_hmeta[2 * g], len = h_hmeta[2 * g + 1];
+        if (mode != CM_INT) all_int = false;
+        lkind[j] = mode == CM_INT ? 1 : mode == CM_BOOL ? 2 : mode == CM_DATE ? 3 : mode == CM_TIME ? 4
+                   : (mode == CM_RAW || mode == CM_XML || mode == CM_NULL) ? 0 : 9;
+        if (mode == CM_NULL) { raw[j] = "Unnamed: " + std::to_string(j); unnamed.push_back(j); }
+        else if (lkind[j] != 9 && len != 0xFFFFFFFFu) raw[j].assign((const char*)h_hdr + (size_t)g * 256, len);
+        else H.ok = false;  // float / oversized labels
+      }
+      if (H.ok && !sheet_labels_supported(lkind, raw)) H.ok = false;
+      if (H.ok) {
+        std::vector<std::string> before = raw;
+        dedupe_names(raw, unnamed);
+        if (all_int && before == raw) {
+          // an all-integer header is an Int64 Index: pandas left-justifies its labels to one width
+          size_t mx = 0;
+          for (auto& x : raw) mx = std::max(mx, x.size());
+          for (auto& x : raw) x.append(mx - x.size(), ' ');
+        }
+        H.empty = empty_frame_text(raw);
+        H.ncp.assign(T.W, 0);
+        for (uint32_t j = 0; j < T.W; ++j)
+          if (!utf8_valid_count(raw[j], &H.ncp[j])) H.ok = false;
+        // labels as to_string prints them: escapes + trim_front (header_names.h display_labels)
+        H.disp = raw;
+        if (H.ok && !(all_int && before == raw)) display_labels(raw, H.disp, H.ncp);
+      }
+      hit = hdr_cache.emplace(hkey, std::move(H)).first;
     }
-    std::string empty = empty_frame_text(raw);
-    T.empty_off = (uint32_t)names.size(); T.empty_len = (uint32_t)empty.size();
-    names += empty;
+    const HdrTexts& H = hit->second;
+    if (!H.ok) { T.active = 0; c->r_status[d] = RFQ_DOC_UNSUPPORTED; continue; }
+    T.empty_off = (uint32_t)names.size(); T.empty_len = (uint32_t)H.empty.size();
+    names += H.empty;
     T.banner_off = 0; T.banner_len = 0;
-    std::vector<uint32_t> ncp(T.W, 0);
-    bool valid = true;
-    for (uint32_t j = 0; j < T.W; ++j)
-      if (!utf8_valid_count(raw[j], &ncp[j])) valid = false;
-    if (!valid) { T.active = 0; c->r_status[d] = RFQ_DOC_UNSUPPORTED; }
-    // labels as to_string prints them: escapes + trim_front (header_names.h display_labels)
-    std::vector<std::string> disp = raw;
-    if (valid && !(all_int && before == raw)) display_labels(raw, disp, ncp);
     for (uint32_t j = 0; j < T.W; ++j) {
       uint32_t g = T.col_base + j;
-      name_off[g] = (uint32_t)names.size(); name_len[g] = (uint32_t)disp[j].size(); name_cp[g] = ncp[j];
-      T.hdr_extra += (uint32_t)disp[j].size() - ncp[j];
-      names += disp[j];
+      name_off[g] = (uint32_t)names.size(); name_len[g] = (uint32_t)H.disp[j].size(); name_cp[g] = H.ncp[j];
+      T.hdr_extra += (uint32_t)H.disp[j].size() - H.ncp[j];
+      names += H.disp[j];
     }
   }
   // a document that turned unsupported keeps its slots and columns but gets no work items
