@@ -108,6 +108,14 @@ int rfq_md5_run(rfq_ctx* ctx);
  * ValueError), RFQ_DOC_UNSUPPORTED (non-ASCII field, integer beyond int64, > 160 characters). */
 int rfq_numeric_run(rfq_ctx* ctx, const uint8_t* kind);
 
+/* ---- where the JSON sits in an LLM reply: the byte work of
+ * RFQFieldGenerator._extract_json_from_string (app/rfq_agent.py:208-236) over a batch of staged replies.
+ * Output: 16 bytes per reply (rfq_out_text at 16*d), four little-endian u32: position of the first '{',
+ * of the last '}' (strategy 2: re.search(r'\{.*\}', s, re.DOTALL); 0xFFFFFFFF = none), and [begin, end) of
+ * strategy 3's cleaned text (strip, drop a leading ```json and a trailing ```, strip).  json.loads of
+ * those spans stays with the caller, as it is CPython's parser in the reference. */
+int rfq_json_spans_run(rfq_ctx* ctx);
+
 /* ---- prompt assembly (the step right after the parser): the text handling of
  * RFQFieldGenerator._generate_sync (app/rfq_agent.py:138-151).  The staged batch holds raw_text
  * documents (UTF-8).  Per document: whitespace-only (str.strip() empty) → RFQ_DOC_EMPTY_TEXT and

@@ -33,6 +33,7 @@ SIGNATURES = {
     "rfq_fetch": (C.c_int, [C.c_void_p]),
     "rfq_md5_run": (C.c_int, [C.c_void_p]),
     "rfq_numeric_run": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "rfq_json_spans_run": (C.c_int, [C.c_void_p]),
     "rfq_prompt_run": (C.c_int, [C.c_void_p, C.c_char_p, C.c_uint32, C.c_char_p, C.c_uint32, C.c_char_p,
                                  C.c_uint32, C.c_uint32]),
     "rfq_prompt_build": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_char_p,

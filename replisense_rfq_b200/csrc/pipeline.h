@@ -41,6 +41,11 @@ void numeric_batch(const uint8_t* arena, const uint32_t* doc_off, const uint32_t
                    unsigned long long* out_off, unsigned long long* out_len, cudaStream_t s);
 
 // ------------------------------------------------------------------------------------------
+// where the JSON sits in an LLM reply (json_kernels.cu): out[4*d..] = first '{', last '}', cleaned [begin, end)
+void json_spans_batch(const uint8_t* arena, const uint32_t* doc_off, const uint32_t* doc_len, uint32_t n_docs,
+                      uint32_t* out, unsigned long long* out_off, unsigned long long* out_len, cudaStream_t s);
+
+// ------------------------------------------------------------------------------------------
 // prompt assembly (prompt_kernels.cu)
 struct PromptArgs {
   const uint8_t* arena;       // device, packed raw_text documents (UTF-8)

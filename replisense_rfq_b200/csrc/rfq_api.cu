@@ -256,6 +256,36 @@ int rfq_md5_run(rfq_ctx* c) {
   return RFQ_OK;
 }
 
+int rfq_json_spans_run(rfq_ctx* c) {
+  if (!c) return RFQ_ERR_ARG;
+  if (!c->staged) { c->err = "rfq_json_spans_run: nothing staged"; return RFQ_ERR_STATE; }
+  RFQ_CK(c, cudaSetDevice(c->device));
+  cudaStream_t s = c->stream;
+  uint32_t n = c->n_docs;
+  if (!c->nested) c->prof.begin();
+  g_prof = &c->prof;
+  struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
+  if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
+  c->status_override.clear();
+  unsigned long long* out_off = c->pool.alloc<unsigned long long>(n + 1);
+  unsigned long long* out_len = c->pool.alloc<unsigned long long>(n + 1);
+  uint32_t* d_val = c->pool.alloc<uint32_t>(4ull * n + 4);
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  json_spans_batch((const uint8_t*)c->d_arena.p, c->d_doc_off, c->d_doc_len, n, d_val, out_off, out_len, s);
+  c->segs.clear();
+  c->segs.push_back({(uint8_t*)d_val, 16ull * n, 0});
+  c->host_tables = false;
+  prof_mark("end", s);
+  RFQ_CK(c, cudaEventRecord(c->ev1, s));
+  RFQ_CK(c, cudaGetLastError());
+  c->out_total = 16ull * n;
+  c->d_out_off = out_off; c->d_out_len = out_len;
+  c->d_status = nullptr; c->d_rows = nullptr; c->d_cols = nullptr; c->d_attempt = nullptr;
+  c->have_output = true;
+  c->timed = true;
+  return RFQ_OK;
+}
+
 int rfq_numeric_run(rfq_ctx* c, const uint8_t* kind) {
   if (!c || (c->n_docs && !kind)) return RFQ_ERR_ARG;
   if (!c->staged) { c->err = "rfq_numeric_run: nothing staged"; return RFQ_ERR_STATE; }

@@ -214,6 +214,19 @@ class Engine:
                    else np.zeros(0, np.uint64))
             return raw, np.asarray(r.status).copy()
 
+    # -- where the JSON sits in LLM replies (app/rfq_agent.py:208-236)
+    def json_spans(self, replies: Sequence[bytes]) -> np.ndarray:
+        """[n, 4] u32: first '{', last '}' (0xFFFFFFFF = none), cleaned [begin, end) of every reply."""
+        if not len(replies):
+            return np.zeros((0, 4), np.uint32)
+        with self.lock:
+            a, off, ln = self._pack(replies)
+            self._check(self.lib.rfq_stage(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data, len(replies)), "rfq_stage")
+            self._check(self.lib.rfq_json_spans_run(self.ctx), "rfq_json_spans_run")
+            self._check(self.lib.rfq_fetch(self.ctx), "rfq_fetch")
+            r = BatchResult(self)
+            return np.frombuffer(C.string_at(r.text_ptr, 16 * r.n), dtype=np.uint32).reshape(r.n, 4).copy()
+
     # -- prompt assembly (the step after the parser: app/rfq_agent.py:138-151)
     def prompt_batch(self, docs: Sequence[bytes], head: bytes, tail: bytes, mark: bytes,
                      max_chars: int = 8000) -> BatchResult:

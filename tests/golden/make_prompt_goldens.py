@@ -28,6 +28,12 @@ def main():
         if prompt.startswith(template):
             out["prompts"][str(rid)] = prompt
     (HERE / "cache_prompts.json").write_text(json.dumps(out, ensure_ascii=False, indent=0))
+    # the values of the same table are the LLM's replies to those requests: what
+    # RFQFieldGenerator._parse_and_validate_response received (app/rfq_agent.py:185-190)
+    replies = {}
+    for rid, val in con.execute("select rowid, value from Cache order by rowid"):
+        replies[str(rid)] = max((a for _, a, _ in pickletools.genops(bytes(val)) if isinstance(a, str)), key=len)
+    (HERE / "cache_replies.json").write_text(json.dumps(replies, ensure_ascii=False, indent=0))
     print({k: len(v) for k, v in out["prompts"].items()})
 
 
