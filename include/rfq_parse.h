@@ -46,6 +46,9 @@ extern "C" {
 #define RFQ_DOC_EMPTY_TEXT 4
 /* numeric path: Python's int() / float() raises ValueError for this field */
 #define RFQ_DOC_VALUE_ERROR 5
+/* inflate path: bad DEFLATE stream, size or CRC-32 differs from the zip directory's, unknown method
+ * (zipfile raises BadZipFile / zlib.error there) */
+#define RFQ_DOC_CORRUPT 6
 
 typedef struct rfq_ctx rfq_ctx;
 
@@ -162,6 +165,20 @@ int rfq_mixed_run(rfq_ctx* ctx, const uint8_t* kind, const int64_t* max_rows, co
 int rfq_mixed_parse(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets, const uint64_t* lengths,
                     uint32_t n_docs, const uint8_t* kind, const int64_t* max_rows, const int32_t* sst_of,
                     const uint32_t* date_off, const uint32_t* date_ids);
+
+/* ---- device-side DEFLATE: the zip members of .xlsx containers inflated on the GPU —
+ * the step pd.read_excel does with zipfile + zlib inside app/file_parser.py:225.  The staged batch holds
+ * the members' RAW data as it lies in the container (the host walks the zip directory: O(members));
+ * method[d] is the zip compression method (0 stored, 8 deflate), out_len[d] the uncompressed size and
+ * crc32[d] the CRC-32 from the directory.  Output = the inflated members (rfq_out_text etc.), status
+ * RFQ_DOC_OK or RFQ_DOC_CORRUPT.
+ * rfq_restage_output makes the inflated members the staged batch without leaving the device (each starts
+ * on a 16-byte boundary; corrupt members become empty documents), so rfq_sheets_run / rfq_text_run /
+ * rfq_mixed_run (text and sheet kinds) follow directly; rfq_fetch_tables downloads only the per-document
+ * tables of the last run (statuses, lengths), not its text. */
+int rfq_inflate_run(rfq_ctx* ctx, const uint8_t* method, const uint64_t* out_len, const uint32_t* crc32);
+int rfq_restage_output(rfq_ctx* ctx);
+int rfq_fetch_tables(rfq_ctx* ctx);
 
 /* ---- device → host copy of the last run's output ---- */
 int rfq_fetch(rfq_ctx* ctx);

@@ -12,7 +12,7 @@ HERE = Path(__file__).resolve().parent
 LIB_PATH = HERE / "librfqparse.so"
 
 RFQ_OK = 0
-DOC_OK, DOC_CSV_UNPARSEABLE, DOC_UNSUPPORTED, DOC_EMPTY_SHEET, DOC_EMPTY_TEXT, DOC_VALUE_ERROR = 0, 1, 2, 3, 4, 5
+DOC_OK, DOC_CSV_UNPARSEABLE, DOC_UNSUPPORTED, DOC_EMPTY_SHEET, DOC_EMPTY_TEXT, DOC_VALUE_ERROR, DOC_CORRUPT = 0, 1, 2, 3, 4, 5, 6
 
 _lib = None
 
@@ -34,6 +34,9 @@ SIGNATURES = {
     "rfq_md5_run": (C.c_int, [C.c_void_p]),
     "rfq_numeric_run": (C.c_int, [C.c_void_p, C.c_void_p]),
     "rfq_json_spans_run": (C.c_int, [C.c_void_p]),
+    "rfq_inflate_run": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "rfq_restage_output": (C.c_int, [C.c_void_p]),
+    "rfq_fetch_tables": (C.c_int, [C.c_void_p]),
     "rfq_prompt_run": (C.c_int, [C.c_void_p, C.c_char_p, C.c_uint32, C.c_char_p, C.c_uint32, C.c_char_p,
                                  C.c_uint32, C.c_uint32]),
     "rfq_prompt_build": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_char_p,

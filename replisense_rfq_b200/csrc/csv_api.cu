@@ -555,6 +555,7 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
 extern "C" int rfq_csv_run(rfq_ctx* c, const int64_t* max_rows_in) {
   if (!c) return RFQ_ERR_ARG;
   if (!c->staged) { c->err = "rfq_csv_run: nothing staged"; return RFQ_ERR_STATE; }
+  if (!c->h_arena) { c->err = "rfq_csv_run: the staged batch exists on the device only (rfq_restage_output); the CSV path reads header records on the host"; return RFQ_ERR_STATE; }
   RFQ_CK(c, cudaSetDevice(c->device));
   cudaStream_t s = c->stream;
   const uint32_t n = c->n_docs;

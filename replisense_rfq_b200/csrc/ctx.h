@@ -139,6 +139,11 @@ struct rfq_ctx {
   uint32_t csv2_in_hint = 0, csv2_item_out_hint = 0;   // largest input span / output range of a work item
   // rfq_mixed_run drives the text / CSV / sheet runs over subsets of one staged batch: a nested run
   // keeps the scratch pool and the timing events of the outer call
+  // device-side inflate: its output lives outside the per-run pool so that it can become the staged batch
+  rfq::DevBuf d_inflated;
+  std::vector<uint64_t> inf_off, inf_len;
+  uint64_t inf_total = 0;
+  bool inflated_valid = false;
   bool nested = false;
   rfq::DevBuf d_viewtab;
   rfq::HostBuf h_viewtab;
@@ -151,7 +156,7 @@ struct rfq_ctx {
   }
   void release_all() {
     pool.release();
-    d_arena.release(); d_doctab.release(); d_out.release(); d_arena2.release(); d_viewtab.release(); h_viewtab.release();
+    d_arena.release(); d_doctab.release(); d_out.release(); d_arena2.release(); d_viewtab.release(); h_viewtab.release(); d_inflated.release();
     h_stage.release(); h_doctab.release(); h_out.release(); h_tabs.release(); h_small.release(); h_up.release(); h_down.release();
   }
 };

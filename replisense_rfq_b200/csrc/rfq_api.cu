@@ -256,6 +256,99 @@ int rfq_md5_run(rfq_ctx* c) {
   return RFQ_OK;
 }
 
+int rfq_inflate_run(rfq_ctx* c, const uint8_t* method, const uint64_t* out_len, const uint32_t* crc32) {
+  if (!c || (c->n_docs && (!method || !out_len || !crc32))) return RFQ_ERR_ARG;
+  if (!c->staged) { c->err = "rfq_inflate_run: nothing staged"; return RFQ_ERR_STATE; }
+  RFQ_CK(c, cudaSetDevice(c->device));
+  cudaStream_t s = c->stream;
+  const uint32_t n = c->n_docs;
+  if (!c->nested) c->prof.begin();
+  g_prof = &c->prof;
+  struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
+  if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
+  c->status_override.clear();
+  c->inflated_valid = false;
+  c->inf_off.assign(n, 0); c->inf_len.assign(out_len, out_len + n);
+  uint64_t total = 0;
+  for (uint32_t d = 0; d < n; ++d) { c->inf_off[d] = total; total += (out_len[d] + RFQ_ALIGN - 1) / RFQ_ALIGN * RFQ_ALIGN; }
+  if (total + 64 >= (1ull << 32)) { c->err = "inflated batch must be < 4 GiB (split the batch)"; return RFQ_ERR_ARG; }
+  c->inf_total = total;
+  RFQ_CK(c, c->d_inflated.reserve(total + 64));
+  RFQ_CK(c, cudaMemsetAsync(c->d_inflated.p, 0, total + 64, s));
+  RFQ_CK(c, c->h_up.reserve(21ull * (n + 2) + 4096));
+  uint8_t* hu = (uint8_t*)c->h_up.p;
+  const size_t o_off = 0, o_len = (8ull * n + 255) & ~255ull, o_crc = (o_len + 8ull * n + 255) & ~255ull,
+               o_m = (o_crc + 4ull * n + 255) & ~255ull, used = o_m + n;
+  RFQ_CK(c, c->h_up.reserve(used + 256));
+  hu = (uint8_t*)c->h_up.p;
+  if (n) {
+    memcpy(hu + o_off, c->inf_off.data(), 8ull * n);
+    memcpy(hu + o_len, out_len, 8ull * n);
+    memcpy(hu + o_crc, crc32, 4ull * n);
+    memcpy(hu + o_m, method, n);
+  }
+  uint8_t* d_up = c->pool.alloc<uint8_t>(used + 256);
+  int32_t* d_status = c->pool.alloc<int32_t>(n + 1);
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  RFQ_CK(c, cudaMemcpyAsync(d_up, hu, used, cudaMemcpyHostToDevice, s));
+  inflate_batch((const uint8_t*)c->d_arena.p, c->d_doc_off, c->d_doc_len, d_up + o_m,
+                (const unsigned long long*)(d_up + o_off), (const unsigned long long*)(d_up + o_len),
+                (const uint32_t*)(d_up + o_crc), n, (uint8_t*)c->d_inflated.p, d_status, s);
+  c->segs.clear();
+  c->segs.push_back({(const uint8_t*)c->d_inflated.p, total, 0});
+  c->host_tables = false;
+  prof_mark("end", s);
+  RFQ_CK(c, cudaEventRecord(c->ev1, s));
+  RFQ_CK(c, cudaGetLastError());
+  c->out_total = total;
+  c->d_out_off = (unsigned long long*)(d_up + o_off); c->d_out_len = (unsigned long long*)(d_up + o_len);
+  c->d_status = d_status; c->d_rows = nullptr; c->d_cols = nullptr; c->d_attempt = nullptr;
+  c->have_output = true;
+  c->timed = true;
+  c->inflated_valid = true;
+  return RFQ_OK;
+}
+
+int rfq_restage_output(rfq_ctx* c) {
+  if (!c) return RFQ_ERR_ARG;
+  if (!c->inflated_valid || !c->have_output) { c->err = "rfq_restage_output: the last run was not rfq_inflate_run"; return RFQ_ERR_STATE; }
+  RFQ_CK(c, cudaSetDevice(c->device));
+  cudaStream_t s = c->stream;
+  const uint32_t n = c->n_docs;
+  // statuses decide which members carry text; the inflate itself must be finished before the buffers swap roles
+  RFQ_CK(c, c->h_down.reserve(4ull * (n + 1) + 256));
+  int32_t* hs = (int32_t*)c->h_down.p;
+  if (n) RFQ_CK(c, cudaMemcpyAsync(hs, c->d_status, 4ull * n, cudaMemcpyDeviceToHost, s));
+  RFQ_CK(c, cudaStreamSynchronize(s));
+  std::swap(c->d_arena, c->d_inflated);
+  uint64_t tiles = 0;
+  c->h_doc_off.resize(n); c->h_doc_len.resize(n); c->h_tile_base.resize(n + 1);
+  for (uint32_t d = 0; d < n; ++d) {
+    c->h_doc_off[d] = (uint32_t)c->inf_off[d];
+    c->h_doc_len[d] = hs[d] == RFQ_DOC_OK ? (uint32_t)c->inf_len[d] : 0u;
+    c->h_tile_base[d] = (uint32_t)tiles;
+    tiles += ((uint64_t)c->h_doc_len[d] + RFQ_TILE - 1) / RFQ_TILE;
+  }
+  c->h_tile_base[n] = (uint32_t)tiles;
+  c->n_tiles = (uint32_t)tiles;
+  c->arena_bytes = c->inf_total;
+  c->h_arena = nullptr;            // the bytes exist on the device only
+  size_t tab = sizeof(uint32_t) * (3ull * n + 1);
+  RFQ_CK(c, c->d_doctab.reserve(tab));
+  RFQ_CK(c, c->h_doctab.reserve(tab));
+  uint32_t* ht = (uint32_t*)c->h_doctab.p;
+  if (n) { memcpy(ht, c->h_doc_off.data(), 4ull * n); memcpy(ht + n, c->h_doc_len.data(), 4ull * n); }
+  memcpy(ht + 2ull * n, c->h_tile_base.data(), 4ull * (n + 1));
+  RFQ_CK(c, cudaMemcpyAsync(c->d_doctab.p, ht, tab, cudaMemcpyHostToDevice, s));
+  c->d_doc_off = (uint32_t*)c->d_doctab.p;
+  c->d_doc_len = c->d_doc_off + n;
+  c->d_tile_base = c->d_doc_len + n;
+  c->inflated_valid = false;
+  c->have_output = false;
+  c->staged = true;
+  return RFQ_OK;
+}
+
 int rfq_json_spans_run(rfq_ctx* c) {
   if (!c) return RFQ_ERR_ARG;
   if (!c->staged) { c->err = "rfq_json_spans_run: nothing staged"; return RFQ_ERR_STATE; }
@@ -383,7 +476,10 @@ int rfq_prompt_run(rfq_ctx* c, const uint8_t* head, uint32_t head_len, const uin
   return RFQ_OK;
 }
 
-int rfq_fetch(rfq_ctx* c) {
+static int fetch_impl(rfq_ctx* c, bool with_text);
+int rfq_fetch(rfq_ctx* c) { return fetch_impl(c, true); }
+int rfq_fetch_tables(rfq_ctx* c) { return fetch_impl(c, false); }
+static int fetch_impl(rfq_ctx* c, bool with_text) {
   if (!c) return RFQ_ERR_ARG;
   if (!c->have_output) { c->err = "rfq_fetch: no run to fetch"; return RFQ_ERR_STATE; }
   RFQ_CK(c, cudaSetDevice(c->device));
@@ -396,7 +492,7 @@ int rfq_fetch(rfq_ctx* c) {
     for (auto& sg : c->segs) sg.copied = false;
     pre = false;
   }
-  RFQ_CK(c, c->h_out.reserve(c->out_total + 16));
+  if (with_text) RFQ_CK(c, c->h_out.reserve(c->out_total + 16));
   RFQ_CK(c, c->h_tabs.reserve((8ull + 8 + 4 + 4 + 4 + 1) * (n + 1) + 64));
   uint8_t* base = (uint8_t*)c->h_tabs.p;
   c->h_out_off = (uint64_t*)base;
@@ -407,10 +503,10 @@ int rfq_fetch(rfq_ctx* c) {
   c->h_attempt = (uint8_t*)(base + 28ull * (n + 1));
   memset(c->h_status, 0, 4ull * (n + 1) * 3 + (n + 1));
   for (auto& sg : c->segs)
-    if (sg.bytes && !sg.copied)
+    if (with_text && sg.bytes && !sg.copied)
       RFQ_CK(c, cudaMemcpyAsync((uint8_t*)c->h_out.p + sg.host_base, sg.d, sg.bytes,
                                 cudaMemcpyDeviceToHost, s));
-  c->d2h_bytes = c->out_total;
+  c->d2h_bytes = with_text ? c->out_total : 0;
   if (c->host_tables) {
     if (n) {
       memcpy(c->h_out_off, c->r_off.data(), 8ull * n);

@@ -310,6 +310,55 @@ class Engine:
             a, off, ln = self._pack(docs)
             return self._sheets(a, off, ln, kind, sst_of, max_rows, date_ids)
 
+    def sheets_batch_deflated(self, members, kind, sst_of, max_rows=1000, date_ids=None):
+        """sheets_batch over zip members that are still compressed (xlsx_host.Member): upload the raw
+        data, inflate on the device (rfq_inflate_run), make the result the staged batch
+        (rfq_restage_output), run the sheet path.  Returns (BatchResult, inflate status per member)."""
+        n = len(members)
+        method = np.fromiter((m.method for m in members), dtype=np.uint8, count=n)
+        size = np.fromiter((m.size for m in members), dtype=np.uint64, count=n)
+        crc = np.fromiter((m.crc for m in members), dtype=np.uint32, count=n)
+        with self.lock:
+            a, off, ln = self._pack([m.raw for m in members])
+            self._check(self.lib.rfq_stage(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data, n), "rfq_stage")
+            self._check(self.lib.rfq_inflate_run(self.ctx, method.ctypes.data, size.ctypes.data, crc.ctypes.data),
+                        "rfq_inflate_run")
+            self._check(self.lib.rfq_fetch_tables(self.ctx), "rfq_fetch_tables")
+            inflate_status = BatchResult(self).status.copy()
+            self._check(self.lib.rfq_restage_output(self.ctx), "rfq_restage_output")
+            kind = np.ascontiguousarray(kind, dtype=np.uint8)
+            so = np.ascontiguousarray(sst_of, dtype=np.int32)
+            mr = self._mr(n, max_rows)
+            doff = np.zeros(n + 1, dtype=np.uint32)
+            flat = []
+            if date_ids is not None:
+                for d in range(n):
+                    if date_ids[d]:
+                        flat.extend(sorted(date_ids[d]))
+                    doff[d + 1] = len(flat)
+            dids = np.asarray(flat if flat else [0], dtype=np.uint32)
+            self._check(self.lib.rfq_sheets_run(self.ctx, kind.ctypes.data, so.ctypes.data, mr.ctypes.data,
+                                                doff.ctypes.data, dids.ctypes.data), "rfq_sheets_run")
+            self._check(self.lib.rfq_fetch(self.ctx), "rfq_fetch")
+            return BatchResult(self), inflate_status
+
+    def inflate_many(self, members) -> "list[bytes | None]":
+        """The inflated bytes of every member (None where the stream, its size or its CRC-32 is bad)."""
+        n = len(members)
+        if n == 0:
+            return []
+        method = np.fromiter((m.method for m in members), dtype=np.uint8, count=n)
+        size = np.fromiter((m.size for m in members), dtype=np.uint64, count=n)
+        crc = np.fromiter((m.crc for m in members), dtype=np.uint32, count=n)
+        with self.lock:
+            a, off, ln = self._pack([m.raw for m in members])
+            self._check(self.lib.rfq_stage(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data, n), "rfq_stage")
+            self._check(self.lib.rfq_inflate_run(self.ctx, method.ctypes.data, size.ctypes.data, crc.ctypes.data),
+                        "rfq_inflate_run")
+            self._check(self.lib.rfq_fetch(self.ctx), "rfq_fetch")
+            r = BatchResult(self)
+            return [r.doc_bytes(d) if int(r.status[d]) == _lib.DOC_OK else None for d in range(n)]
+
     def sheets_parse_arena(self, arena: PinnedArena, offsets, lengths, kind, sst_of, max_rows=1000,
                            date_ids=None) -> BatchResult:
         """sheets_batch over parts the caller already packed into a pinned arena (no host copy)."""

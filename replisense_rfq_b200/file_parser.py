@@ -144,7 +144,7 @@ class FileParser:
     def _parse_excel_sync(self, file_path: Path) -> str:
         try:
             from . import xlsx_host
-            parts = xlsx_host.open_workbook(Path(file_path).read_bytes())
+            parts = xlsx_host.scan_workbook(Path(file_path).read_bytes())   # big parts stay compressed: inflated on the GPU
             text = xlsx_host.parse_workbooks(self.engine, [parts], self.max_excel_rows)[0]
             if isinstance(text, Exception):
                 raise text
@@ -155,62 +155,45 @@ class FileParser:
     # ------------------------------------------------------------------ batched entry point
     def parse_many(self, docs: Sequence[bytes], kinds: Sequence[str]) -> "list[str | FileParsingError]":
         """Many documents in one go. `kinds[i]` in {'txt', 'csv', 'xlsx'}; returns raw_text or the
-        FileParsingError the reference would have raised for that document, in input order.  All kinds
-        travel in ONE packed arena and one upload (rfq_mixed_parse): text bodies, CSV files, and the
-        worksheet / sharedStrings parts the host took out of every .xlsx container."""
+        FileParsingError the reference would have raised for that document, in input order.  Text bodies
+        and CSV files travel in ONE packed arena and one upload (rfq_mixed_parse).  The worksheet /
+        sharedStrings parts of all .xlsx containers travel as they lie in the zip — still compressed — and
+        are inflated on the device (rfq_inflate_run) before the sheet path runs over them."""
         from . import xlsx_host
         n = len(docs)
         out: "list[Any]" = [None] * n
-        flat, fkind, sst_of, dates, owner = [], [], [], [], []   # owner: (input index, sheet index | None)
-        books: "dict[int, Any]" = {}
+        flat, fkind, owner = [], [], []
+        books, book_idx = [], []
         for i, (doc, k) in enumerate(zip(docs, kinds)):
             k = k.lower().lstrip(".")
             if k == "txt":
-                flat.append(doc); fkind.append(_lib.KIND_TEXT); sst_of.append(-1); dates.append(()); owner.append((i, None))
+                flat.append(doc); fkind.append(_lib.KIND_TEXT); owner.append(i)
             elif k == "csv":
-                flat.append(doc); fkind.append(_lib.KIND_CSV); sst_of.append(-1); dates.append(()); owner.append((i, None))
+                flat.append(doc); fkind.append(_lib.KIND_CSV); owner.append(i)
             elif k == "xlsx":
                 try:
-                    wb = xlsx_host.open_workbook(doc)
+                    books.append(xlsx_host.scan_workbook(doc))
+                    book_idx.append(i)
                 except Exception as e:  # noqa: BLE001
                     out[i] = FileParsingError(f"Excel parsing failed: {e}")
-                    continue
-                books[i] = wb
-                sst_idx = -1
-                if wb.sst is not None:
-                    sst_idx = len(flat)
-                    flat.append(wb.sst); fkind.append(_lib.KIND_SST); sst_of.append(-1); dates.append(()); owner.append((i, -1))
-                for sh, xml in enumerate(wb.sheets):
-                    flat.append(xml); fkind.append(_lib.KIND_SHEET_1904 if wb.date1904 else _lib.KIND_SHEET)
-                    sst_of.append(sst_idx); dates.append(wb.date_styles); owner.append((i, sh))
             else:
                 out[i] = FileParsingError(f"Unsupported file type: .{k}")
-        if not flat:
-            return out
         eng = self.engine
-        with eng.lock:   # the pinned output is ours until every text has been built
-            r = eng.mixed_batch(flat, fkind, self.max_excel_rows, sst_of, dates)
-            parts: "dict[int, list[str]]" = {i: [] for i in books}
-            failed: "dict[int, Exception]" = {}
-            for d, (i, sh) in enumerate(owner):
-                st = int(r.status[d])
-                if fkind[d] == _lib.KIND_TEXT:
-                    out[i] = r.doc_str(d)
-                elif fkind[d] == _lib.KIND_CSV:
-                    out[i] = (r.doc_str(d) if st == _lib.DOC_OK
-                              else FileParsingError(f"CSV parsing failed: {_CSV_FAIL}") if st == _lib.DOC_CSV_UNPARSEABLE
-                              else FileParsingError("CSV parsing failed: unsupported construct on the GPU path "
-                                                    f"(status {st})"))
-                elif sh is not None and sh >= 0:
-                    if st == _lib.DOC_EMPTY_SHEET:
-                        continue   # `if df.empty: continue` (app/file_parser.py:228-229)
-                    if st != _lib.DOC_OK:
-                        failed[i] = FileParsingError(f"Excel parsing failed: sheet {books[i].sheet_names[sh]!r}: "
-                                                     "construct not decoded on the GPU path")
-                        continue
-                    parts[i].append(f"=== Sheet: {books[i].sheet_names[sh]} ===\n" + r.doc_str(d))
-        for i in books:
-            out[i] = failed[i] if i in failed else ("\n\n".join(parts[i]) if parts[i] else _EXCEL_EMPTY)
+        if flat:
+            with eng.lock:   # the pinned output is ours until every text has been built
+                r = eng.mixed_batch(flat, fkind, self.max_excel_rows)
+                for d, i in enumerate(owner):
+                    st = int(r.status[d])
+                    if fkind[d] == _lib.KIND_TEXT:
+                        out[i] = r.doc_str(d)
+                    else:
+                        out[i] = (r.doc_str(d) if st == _lib.DOC_OK
+                                  else FileParsingError(f"CSV parsing failed: {_CSV_FAIL}") if st == _lib.DOC_CSV_UNPARSEABLE
+                                  else FileParsingError("CSV parsing failed: unsupported construct on the GPU path "
+                                                        f"(status {st})"))
+        if books:
+            for i, t in zip(book_idx, xlsx_host.parse_workbooks(eng, books, self.max_excel_rows)):
+                out[i] = FileParsingError(f"Excel parsing failed: {t}") if isinstance(t, Exception) else t
         return out
 
     _GPU_HASH_MAX = 1 << 20   # MD5 is sequential per document: bigger files keep hashlib

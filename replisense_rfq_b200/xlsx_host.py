@@ -73,6 +73,60 @@ class Workbook:
         self.date1904 = date1904
 
 
+class Member:
+    """One zip member as it lies in the container: raw (still compressed) bytes + what the zip directory
+    says about it.  The GPU inflates it (rfq_inflate_run)."""
+    __slots__ = ("raw", "method", "size", "crc")
+
+    def __init__(self, raw, method, size, crc):
+        self.raw, self.method, self.size, self.crc = raw, method, size, crc
+
+
+def _member(z: zipfile.ZipFile, data: bytes, name: str) -> Member:
+    zi = z.getinfo(name)
+    if zi.flag_bits & 0x1:
+        raise zipfile.BadZipFile("encrypted member %r" % name)
+    ho = zi.header_offset
+    if data[ho:ho + 4] != b"PK\x03\x04":
+        raise zipfile.BadZipFile("bad local header of %r" % name)
+    fnlen = int.from_bytes(data[ho + 26:ho + 28], "little")
+    exlen = int.from_bytes(data[ho + 28:ho + 30], "little")
+    start = ho + 30 + fnlen + exlen
+    return Member(memoryview(data)[start:start + zi.compress_size], zi.compress_type, zi.file_size, zi.CRC)
+
+
+def scan_workbook(data: bytes) -> Workbook:
+    """open_workbook without inflating the big parts: worksheet and sharedStrings parts come back as
+    `Member`s (raw zip data for the GPU); only workbook.xml, its rels and styles.xml — a few KB that
+    decide names, order and date styles — are inflated here."""
+    z = zipfile.ZipFile(io.BytesIO(data))
+    names = set(z.namelist())
+    rels = {}
+    if "xl/_rels/workbook.xml.rels" in names:
+        for r in ET.fromstring(z.read("xl/_rels/workbook.xml.rels")).findall("{%s}Relationship" % _NS_PKG):
+            t = r.get("Target")
+            t = t[1:] if t.startswith("/") else posixpath.normpath(posixpath.join("xl", t))
+            rels[r.get("Id")] = (r.get("Type"), t)
+    root = ET.fromstring(z.read("xl/workbook.xml"))
+    pr = root.find("{%s}workbookPr" % _NS)
+    date1904 = pr is not None and pr.get("date1904") in ("1", "true")
+    sheet_names, sheets = [], []
+    for sh in root.find("{%s}sheets" % _NS).findall("{%s}sheet" % _NS):
+        typ, target = rels[sh.get("{%s}id" % _NS_REL)]
+        if not typ.endswith("/worksheet"):
+            continue
+        sheet_names.append(sh.get("name"))
+        sheets.append(_member(z, data, target))
+    sst = None
+    for typ, target in rels.values():
+        if typ.endswith("/sharedStrings") and target in names:
+            sst = _member(z, data, target)
+    if sst is None and "xl/sharedStrings.xml" in names:
+        sst = _member(z, data, "xl/sharedStrings.xml")
+    styles = z.read("xl/styles.xml") if "xl/styles.xml" in names else None
+    return Workbook(sheet_names, sheets, sst, _date_style_ids(styles), date1904)
+
+
 def open_workbook(data: bytes) -> Workbook:
     z = zipfile.ZipFile(io.BytesIO(data))
     names = set(z.namelist())
@@ -104,8 +158,10 @@ def open_workbook(data: bytes) -> Workbook:
 
 def parse_workbooks(engine, books, max_rows: int = 1000) -> "list":
     """raw_text of every workbook (one GPU batch for all their parts); an EngineError instance in
-    place of the text where a sheet uses a construct that is not decoded on the GPU path."""
+    place of the text where a sheet uses a construct that is not decoded on the GPU path.  Workbooks
+    from scan_workbook carry their parts still compressed: the batch is inflated on the device."""
     docs, kind, sst_of, dates, owner = [], [], [], [], []
+    deflated = any(isinstance(wb.sst, Member) or any(isinstance(x, Member) for x in wb.sheets) for wb in books)
     for b, wb in enumerate(books):
         sst_idx = -1
         if wb.sst is not None:
@@ -118,9 +174,15 @@ def parse_workbooks(engine, books, max_rows: int = 1000) -> "list":
     parts = [[] for _ in books]
     failed = {}
     with engine.lock:   # the pinned output is ours until the texts have been built
-        res = engine.sheets_batch(docs, kind, sst_of, max_rows, dates) if docs else None
+        if docs and deflated:
+            res, inflate_status = engine.sheets_batch_deflated(docs, kind, sst_of, max_rows, dates)
+            for d, (b, k) in enumerate(owner):
+                if int(inflate_status[d]) != _lib.DOC_OK:
+                    failed[b] = EngineError("zip member is corrupt (bad DEFLATE stream, size or CRC-32)")
+        else:
+            res = engine.sheets_batch(docs, kind, sst_of, max_rows, dates) if docs else None
         for d, (b, k) in enumerate(owner):
-            if k is None:
+            if k is None or b in failed:
                 continue
             st = int(res.status[d])
             if st == _lib.DOC_EMPTY_SHEET:
