@@ -65,7 +65,11 @@ void* rfq_get_stream(rfq_ctx* ctx);
 void* rfq_host_alloc(rfq_ctx* ctx, uint64_t bytes);
 void rfq_host_free(rfq_ctx* ctx, void* p);
 
-/* ---- staging: host → device copy of one batch (kept resident until the next rfq_stage) ---- */
+/* ---- staging: host → device copy of one batch (kept resident until the next rfq_stage) ----
+ * When every offset is a multiple of 16 the library copies straight out of `arena` (asynchronously if
+ * it is pinned) and keeps the pointer: rfq_csv_run / rfq_mixed_run read the first records of every
+ * document from it on the host.  The caller must keep `arena` alive and unchanged until the runs over
+ * this batch have returned; other offsets are repacked into a library-owned buffer at once. */
 int rfq_stage(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets,
               const uint64_t* lengths, uint32_t n_docs);
 

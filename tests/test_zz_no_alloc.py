@@ -49,6 +49,9 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row():
     want = [eng.text_batch([d]).doc_bytes(0) for d in docs]   # existing entry point, C ABI
     got = [_noalloc(lib, torch, d) for d in docs]
     assert got == want
+    # and against the oracle directly, so this test stands on its own
+    from oracle import file_parser_oracle as O
+    assert [g.decode("utf-8") for g in got] == [O.parse_txt_bytes(d) for d in docs]
     # a second full round: identical again
     assert [_noalloc(lib, torch, d) for d in docs[:4]] == want[:4]
     # on an explicit stream too
