@@ -44,7 +44,7 @@ void numeric_batch(const uint8_t* arena, const uint32_t* doc_off, const uint32_t
 // device-side DEFLATE (inflate_kernels.cu): member d of the arena -> out + out_off[d] (out_len[d] bytes expected)
 void inflate_batch(const uint8_t* arena, const uint32_t* doc_off, const uint32_t* doc_len, const uint8_t* method,
                    const unsigned long long* out_off, const unsigned long long* out_len, const uint32_t* crc,
-                   uint32_t n_docs, uint8_t* out, int32_t* status, cudaStream_t s);
+                   uint32_t n_docs, uint8_t* out, int32_t* status, uint32_t* ticket, cudaStream_t s);
 
 // ------------------------------------------------------------------------------------------
 // where the JSON sits in an LLM reply (json_kernels.cu): out[4*d..] = first '{', last '}', cleaned [begin, end)

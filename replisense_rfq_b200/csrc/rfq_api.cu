@@ -289,11 +289,12 @@ int rfq_inflate_run(rfq_ctx* c, const uint8_t* method, const uint64_t* out_len, 
   }
   uint8_t* d_up = c->pool.alloc<uint8_t>(used + 256);
   int32_t* d_status = c->pool.alloc<int32_t>(n + 1);
+  uint32_t* d_ticket = c->pool.alloc<uint32_t>(4);
   if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
   RFQ_CK(c, cudaMemcpyAsync(d_up, hu, used, cudaMemcpyHostToDevice, s));
   inflate_batch((const uint8_t*)c->d_arena.p, c->d_doc_off, c->d_doc_len, d_up + o_m,
                 (const unsigned long long*)(d_up + o_off), (const unsigned long long*)(d_up + o_len),
-                (const uint32_t*)(d_up + o_crc), n, (uint8_t*)c->d_inflated.p, d_status, s);
+                (const uint32_t*)(d_up + o_crc), n, (uint8_t*)c->d_inflated.p, d_status, d_ticket, s);
   c->segs.clear();
   c->segs.push_back({(const uint8_t*)c->d_inflated.p, total, 0});
   c->host_tables = false;
