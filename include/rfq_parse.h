@@ -170,6 +170,23 @@ int rfq_mixed_parse(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets,
                     uint32_t n_docs, const uint8_t* kind, const int64_t* max_rows, const int32_t* sst_of,
                     const uint32_t* date_off, const uint32_t* date_ids);
 
+/* ---- text framing: documents assembled on the device from pieces, the way
+ * FileParser._parse_pdf_sync frames what the PDF engine extracted (app/file_parser.py:166-212; the
+ * extraction itself — MuPDF — is out of scope): per page "=== Page N ===\n" + page_text.strip() when that
+ * is not empty, table blocks, image notes, parts joined by "\n\n", a fixed text when nothing is left.
+ * The staged batch holds the PIECES (page texts, table blocks, literal headers) in output order;
+ * piece_strip[i] = 1 applies str.strip() (Unicode whitespace) to piece i.  Pieces form parts
+ * (part_first_piece, n_parts + 1 entries), parts form output documents (doc_first_part, n_out + 1 entries):
+ *   RFQ_PART_ALWAYS    printed as it is
+ *   RFQ_PART_IF_TEXT   printed only if its LAST piece is not empty after stripping (a page header + its text)
+ *   RFQ_PART_FALLBACK  printed only if no other part of the document is
+ * Printed parts of a document are joined by "\n\n".  Output: n_out texts. */
+#define RFQ_PART_ALWAYS 0
+#define RFQ_PART_IF_TEXT 1
+#define RFQ_PART_FALLBACK 2
+int rfq_frame_run(rfq_ctx* ctx, uint32_t n_out, const uint32_t* doc_first_part, uint32_t n_parts,
+                  const uint8_t* part_kind, const uint32_t* part_first_piece, const uint8_t* piece_strip);
+
 /* ---- device-side DEFLATE: the zip members of .xlsx containers inflated on the GPU —
  * the step pd.read_excel does with zipfile + zlib inside app/file_parser.py:225.  The staged batch holds
  * the members' RAW data as it lies in the container (the host walks the zip directory: O(members));

@@ -34,6 +34,7 @@ SIGNATURES = {
     "rfq_md5_run": (C.c_int, [C.c_void_p]),
     "rfq_numeric_run": (C.c_int, [C.c_void_p, C.c_void_p]),
     "rfq_json_spans_run": (C.c_int, [C.c_void_p]),
+    "rfq_frame_run": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "rfq_inflate_run": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "rfq_restage_output": (C.c_int, [C.c_void_p]),
     "rfq_fetch_tables": (C.c_int, [C.c_void_p]),
@@ -74,6 +75,7 @@ SIGNATURES = {
     "rfq_text_normalise_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                              C.c_void_p]),
 }
+PART_ALWAYS, PART_IF_TEXT, PART_FALLBACK = 0, 1, 2
 KIND_TEXT, KIND_CSV, KIND_SHEET, KIND_SHEET_1904, KIND_SST = 0, 1, 2, 3, 4
 NOALLOC_MAX_BYTES = 4 << 20
 ERR_TOO_LARGE = -4

@@ -144,6 +144,7 @@ struct rfq_ctx {
   std::vector<uint64_t> inf_off, inf_len;
   uint64_t inf_total = 0;
   bool inflated_valid = false;
+  uint32_t out_n = 0;   // documents of the last run's output when it differs from the staged count (0 = n_docs)
   bool nested = false;
   rfq::DevBuf d_viewtab;
   rfq::HostBuf h_viewtab;

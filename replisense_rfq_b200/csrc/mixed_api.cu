@@ -31,7 +31,7 @@ extern "C" int rfq_mixed_run(rfq_ctx* c, const uint8_t* kind, const int64_t* max
   c->prof.begin();
   RFQ_CK(c, cudaEventRecord(c->ev0, s));
   c->pool.reset();
-  c->status_override.clear();
+  c->status_override.clear(); c->out_n = 0;
   // ---- the three subsets, in input order
   std::vector<uint32_t> idx[3];          // 0 text, 1 csv, 2 sheets + sharedStrings
   std::vector<int32_t> pos_in_sheets(n, -1);

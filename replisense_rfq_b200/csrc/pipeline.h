@@ -41,6 +41,23 @@ void numeric_batch(const uint8_t* arena, const uint32_t* doc_off, const uint32_t
                    unsigned long long* out_off, unsigned long long* out_len, cudaStream_t s);
 
 // ------------------------------------------------------------------------------------------
+// text framing (frame_kernels.cu): documents assembled from pieces (page texts, table rows, literal headers)
+struct FrameArgs {
+  const uint8_t* arena; const uint32_t* doc_off; const uint32_t* doc_len;   // the staged pieces
+  uint32_t n_pieces, n_parts, n_out;
+  const uint32_t* doc_first_part;     // [n_out+1]
+  const uint8_t* part_kind;           // [n_parts] RFQ_PART_*
+  const uint32_t* part_first_piece;   // [n_parts+1]
+  const uint8_t* piece_strip;         // [n_pieces] 1 = str.strip() the piece
+  uint32_t* piece_a; uint32_t* piece_n;          // [n_pieces] kept span of every piece
+  unsigned long long* piece_dst;      // [n_pieces] where it goes in the output, ~0 = nowhere
+  unsigned long long* out_len; unsigned long long* out_off; unsigned long long* out_total;   // [n_out]
+  unsigned long long* scan_tmp64;
+};
+void frame_measure(const FrameArgs& a, cudaStream_t s);
+void frame_emit(const FrameArgs& a, uint8_t* out, cudaStream_t s);
+
+// ------------------------------------------------------------------------------------------
 // device-side DEFLATE (inflate_kernels.cu): member d of the arena -> out + out_off[d] (out_len[d] bytes expected)
 void inflate_batch(const uint8_t* arena, const uint32_t* doc_off, const uint32_t* doc_len, const uint8_t* method,
                    const unsigned long long* out_off, const unsigned long long* out_len, const uint32_t* crc,

@@ -99,7 +99,7 @@ int rfq_stage(rfq_ctx* c, const uint8_t* arena, const uint64_t* offsets, const u
   c->n_docs = n;
   c->staged = false;
   c->have_output = false;
-  c->status_override.clear(); c->raw_bytes.clear(); c->raw_chars.clear();
+  c->status_override.clear(); c->out_n = 0; c->raw_bytes.clear(); c->raw_chars.clear();
   bool aligned = true;
   uint64_t span = 0;
   for (uint32_t d = 0; d < n; ++d) {
@@ -184,7 +184,7 @@ int rfq_text_run(rfq_ctx* c) {
   uint32_t n = c->n_docs, nt = c->n_tiles;
   if (!c->nested) c->prof.begin();
   if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
-  c->status_override.clear();
+  c->status_override.clear(); c->out_n = 0;
   TxtArgs a{};
   a.arena = (const uint8_t*)c->d_arena.p;
   a.doc_off = c->d_doc_off; a.doc_len = c->d_doc_len; a.tile_base = c->d_tile_base;
@@ -236,7 +236,7 @@ int rfq_md5_run(rfq_ctx* c) {
   g_prof = &c->prof;
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
   if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
-  c->status_override.clear();
+  c->status_override.clear(); c->out_n = 0;
   unsigned long long* out_off = c->pool.alloc<unsigned long long>(n + 1);
   unsigned long long* out_len = c->pool.alloc<unsigned long long>(n + 1);
   uint8_t* d_text = c->pool.alloc<uint8_t>(32ull * n + 16);
@@ -266,7 +266,7 @@ int rfq_inflate_run(rfq_ctx* c, const uint8_t* method, const uint64_t* out_len, 
   g_prof = &c->prof;
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
   if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
-  c->status_override.clear();
+  c->status_override.clear(); c->out_n = 0;
   c->inflated_valid = false;
   c->inf_off.assign(n, 0); c->inf_len.assign(out_len, out_len + n);
   uint64_t total = 0;
@@ -350,6 +350,64 @@ int rfq_restage_output(rfq_ctx* c) {
   return RFQ_OK;
 }
 
+int rfq_frame_run(rfq_ctx* c, uint32_t n_out, const uint32_t* doc_first_part, uint32_t n_parts, const uint8_t* part_kind,
+                  const uint32_t* part_first_piece, const uint8_t* piece_strip) {
+  if (!c || !doc_first_part || (n_parts && (!part_kind || !part_first_piece)) || (c->n_docs && !piece_strip)) return RFQ_ERR_ARG;
+  if (!c->staged) { c->err = "rfq_frame_run: nothing staged"; return RFQ_ERR_STATE; }
+  const uint32_t n = c->n_docs;
+  if (doc_first_part[n_out] != n_parts || (n_parts && part_first_piece[n_parts] != n)) { c->err = "rfq_frame_run: tables do not cover the staged pieces"; return RFQ_ERR_ARG; }
+  RFQ_CK(c, cudaSetDevice(c->device));
+  cudaStream_t s = c->stream;
+  if (!c->nested) c->prof.begin();
+  g_prof = &c->prof;
+  struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
+  if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
+  c->status_override.clear(); c->out_n = 0;
+  const size_t o_dfp = 0, o_pk = (4ull * (n_out + 1) + 255) & ~255ull, o_pfp = (o_pk + n_parts + 255) & ~255ull,
+               o_ps = (o_pfp + 4ull * (n_parts + 1) + 255) & ~255ull, used = o_ps + n;
+  RFQ_CK(c, c->h_up.reserve(used + 256));
+  uint8_t* hu = (uint8_t*)c->h_up.p;
+  memcpy(hu + o_dfp, doc_first_part, 4ull * (n_out + 1));
+  if (n_parts) { memcpy(hu + o_pk, part_kind, n_parts); memcpy(hu + o_pfp, part_first_piece, 4ull * (n_parts + 1)); }
+  if (n) memcpy(hu + o_ps, piece_strip, n);
+  uint8_t* d_up = c->pool.alloc<uint8_t>(used + 256);
+  FrameArgs a{};
+  a.arena = (const uint8_t*)c->d_arena.p; a.doc_off = c->d_doc_off; a.doc_len = c->d_doc_len;
+  a.n_pieces = n; a.n_parts = n_parts; a.n_out = n_out;
+  a.piece_a = c->pool.alloc<uint32_t>(n + 1); a.piece_n = c->pool.alloc<uint32_t>(n + 1);
+  a.piece_dst = c->pool.alloc<unsigned long long>(n + 1);
+  a.out_len = c->pool.alloc<unsigned long long>(n_out + 1); a.out_off = c->pool.alloc<unsigned long long>(n_out + 1);
+  a.out_total = c->pool.alloc<unsigned long long>(1);
+  a.scan_tmp64 = c->pool.alloc<unsigned long long>(scan_partials_needed(n_out));
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  RFQ_CK(c, cudaMemcpyAsync(d_up, hu, used, cudaMemcpyHostToDevice, s));
+  a.doc_first_part = (const uint32_t*)(d_up + o_dfp); a.part_kind = d_up + o_pk;
+  a.part_first_piece = (const uint32_t*)(d_up + o_pfp); a.piece_strip = d_up + o_ps;
+  frame_measure(a, s);
+  unsigned long long total = 0;
+  if (n_out) {
+    RFQ_CK(c, cudaMemcpyAsync(c->h_scalar(), a.out_total, 8, cudaMemcpyDeviceToHost, s));
+    RFQ_CK(c, cudaStreamSynchronize(s));
+    total = *c->h_scalar();
+  }
+  uint8_t* d_text = c->pool.alloc<uint8_t>(total + 16);
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  frame_emit(a, d_text, s);
+  c->segs.clear();
+  c->segs.push_back({d_text, total, 0});
+  c->host_tables = false;
+  prof_mark("end", s);
+  RFQ_CK(c, cudaEventRecord(c->ev1, s));
+  RFQ_CK(c, cudaGetLastError());
+  c->out_total = total;
+  c->out_n = n_out;
+  c->d_out_off = a.out_off; c->d_out_len = a.out_len;
+  c->d_status = nullptr; c->d_rows = nullptr; c->d_cols = nullptr; c->d_attempt = nullptr;
+  c->have_output = true;
+  c->timed = true;
+  return RFQ_OK;
+}
+
 int rfq_json_spans_run(rfq_ctx* c) {
   if (!c) return RFQ_ERR_ARG;
   if (!c->staged) { c->err = "rfq_json_spans_run: nothing staged"; return RFQ_ERR_STATE; }
@@ -360,7 +418,7 @@ int rfq_json_spans_run(rfq_ctx* c) {
   g_prof = &c->prof;
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
   if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
-  c->status_override.clear();
+  c->status_override.clear(); c->out_n = 0;
   unsigned long long* out_off = c->pool.alloc<unsigned long long>(n + 1);
   unsigned long long* out_len = c->pool.alloc<unsigned long long>(n + 1);
   uint32_t* d_val = c->pool.alloc<uint32_t>(4ull * n + 4);
@@ -390,7 +448,7 @@ int rfq_numeric_run(rfq_ctx* c, const uint8_t* kind) {
   g_prof = &c->prof;
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
   if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
-  c->status_override.clear();
+  c->status_override.clear(); c->out_n = 0;
   RFQ_CK(c, c->h_up.reserve(n + 16));
   if (n) memcpy(c->h_up.p, kind, n);
   uint8_t* d_kind = c->pool.alloc<uint8_t>(n + 16);
@@ -427,7 +485,7 @@ int rfq_prompt_run(rfq_ctx* c, const uint8_t* head, uint32_t head_len, const uin
   g_prof = &c->prof;
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
   if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
-  c->status_override.clear();
+  c->status_override.clear(); c->out_n = 0;
   // template pieces: one small pinned upload
   const size_t o_tail = ((size_t)head_len + 15) & ~(size_t)15, o_mark = (o_tail + tail_len + 15) & ~(size_t)15;
   const size_t pieces = o_mark + mark_len + 16;
@@ -485,7 +543,7 @@ static int fetch_impl(rfq_ctx* c, bool with_text) {
   if (!c->have_output) { c->err = "rfq_fetch: no run to fetch"; return RFQ_ERR_STATE; }
   RFQ_CK(c, cudaSetDevice(c->device));
   cudaStream_t s = c->stream;
-  uint32_t n = c->n_docs;
+  uint32_t n = c->out_n ? c->out_n : c->n_docs;
   bool pre = false;
   for (auto& sg : c->segs) pre |= sg.copied;
   if (pre && c->h_out.cap < c->out_total + 16) {   // must grow: the early copies are void
@@ -580,7 +638,7 @@ int rfq_csv_parse(rfq_ctx* c, const uint8_t* arena, const uint64_t* offsets,
   return rfq_fetch(c);
 }
 
-uint32_t rfq_out_count(const rfq_ctx* c) { return c ? c->n_docs : 0; }
+uint32_t rfq_out_count(const rfq_ctx* c) { return c ? (c->out_n ? c->out_n : c->n_docs) : 0; }
 const uint8_t* rfq_out_text(const rfq_ctx* c) { return c ? (const uint8_t*)c->h_out.p : nullptr; }
 const uint64_t* rfq_out_offsets(const rfq_ctx* c) { return c ? c->h_out_off : nullptr; }
 const uint64_t* rfq_out_lengths(const rfq_ctx* c) { return c ? c->h_out_len : nullptr; }

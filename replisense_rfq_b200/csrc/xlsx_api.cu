@@ -45,7 +45,7 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
   g_prof = &c->prof;
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
   if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
-  c->status_override.clear();
+  c->status_override.clear(); c->out_n = 0;
   c->segs.clear();
   c->out_total = 0;
   c->host_tables = true;

@@ -214,6 +214,24 @@ class Engine:
                    else np.zeros(0, np.uint64))
             return raw, np.asarray(r.status).copy()
 
+    # -- text framing (app/file_parser.py:166-212): documents assembled from pieces on the device
+    def frame_many(self, pieces: Sequence[bytes], strip, part_kind, part_first_piece, doc_first_part) -> "list[str]":
+        n_out = len(doc_first_part) - 1
+        if n_out <= 0:
+            return []
+        strip = np.ascontiguousarray(strip, dtype=np.uint8)
+        pk = np.ascontiguousarray(part_kind, dtype=np.uint8)
+        pfp = np.ascontiguousarray(part_first_piece, dtype=np.uint32)
+        dfp = np.ascontiguousarray(doc_first_part, dtype=np.uint32)
+        with self.lock:
+            a, off, ln = self._pack(pieces)
+            self._check(self.lib.rfq_stage(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data, len(pieces)), "rfq_stage")
+            self._check(self.lib.rfq_frame_run(self.ctx, n_out, dfp.ctypes.data, len(pk), pk.ctypes.data, pfp.ctypes.data,
+                                               strip.ctypes.data), "rfq_frame_run")
+            self._check(self.lib.rfq_fetch(self.ctx), "rfq_fetch")
+            r = BatchResult(self)
+            return [r.doc_str(d) for d in range(r.n)]
+
     # -- where the JSON sits in LLM replies (app/rfq_agent.py:208-236)
     def json_spans(self, replies: Sequence[bytes]) -> np.ndarray:
         """[n, 4] u32: first '{', last '}' (0xFFFFFFFF = none), cleaned [begin, end) of every reply."""
