@@ -227,6 +227,14 @@ const uint32_t* rfq_out_cols(const rfq_ctx* ctx);
 /* CSV: winning attempt, encoding index (0 utf-8, 1 latin-1, 2 cp1252) * 3 + separator index */
 const uint8_t* rfq_out_attempt(const rfq_ctx* ctx);
 
+/* ---- a fetched text as fixed-width code units, for bindings whose string type stores text that way
+ * (CPython: 1, 2 or 4 bytes per code point).  rfq_out_maxchar: an upper bound of the largest code point
+ * of document d (0x7F, 0xFF, 0xFFFF or 0x10FFFF).  rfq_out_widen: its n_chars code points written to dst
+ * as 1-, 2- or 4-byte units (n_chars must be the document's code-point count: rfq_out_chars).  Host code,
+ * a few threads: the conversion at the language boundary, not part of the parse. */
+int rfq_out_maxchar(const rfq_ctx* ctx, uint32_t d, uint32_t* maxchar);
+int rfq_out_widen(const rfq_ctx* ctx, uint32_t d, int unit, void* dst, uint64_t n_chars);
+
 /* ---- measurement helpers (bench.py): device time of the last *_run, and launch counters ---- */
 float rfq_last_run_ms(const rfq_ctx* ctx);
 uint64_t rfq_launch_count(const rfq_ctx* ctx);

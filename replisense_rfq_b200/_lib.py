@@ -55,6 +55,8 @@ SIGNATURES = {
     "rfq_out_raw_bytes": (C.c_void_p, [C.c_void_p]),
     "rfq_out_raw_chars": (C.c_void_p, [C.c_void_p]),
     "rfq_out_chars": (C.c_void_p, [C.c_void_p]),
+    "rfq_out_maxchar": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32)]),
+    "rfq_out_widen": (C.c_int, [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_uint64]),
     "rfq_mixed_run": (C.c_int, [C.c_void_p] * 6),
     "rfq_mixed_parse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32] + [C.c_void_p] * 5),
     "rfq_out_count": (C.c_uint32, [C.c_void_p]),

@@ -5,6 +5,7 @@
 #include <string.h>
 #include <algorithm>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/rfq_parse.h"
@@ -647,6 +648,82 @@ uint64_t rfq_out_total_bytes(const rfq_ctx* c) { return c ? c->out_total : 0; }
 const uint32_t* rfq_out_rows(const rfq_ctx* c) { return c ? c->h_rows : nullptr; }
 const uint32_t* rfq_out_cols(const rfq_ctx* c) { return c ? c->h_cols : nullptr; }
 const uint8_t* rfq_out_attempt(const rfq_ctx* c) { return c ? c->h_attempt : nullptr; }
+
+// ---- fixed-width code units of a fetched text, for bindings whose string type stores them that way
+// (CPython: 1, 2 or 4 bytes per code point).  Host-side, a few threads: a language-boundary conversion,
+// not part of the parse.
+}  // extern "C"
+namespace {
+template <class F> void host_parallel(uint64_t n, uint64_t min_chunk, F&& fn) {
+  unsigned hw = std::thread::hardware_concurrency();
+  uint64_t nt = std::min<uint64_t>(std::min<uint64_t>(hw ? hw : 4u, 16u), std::max<uint64_t>(1, n / min_chunk));
+  if (nt <= 1) { fn(0, n, 0u); return; }
+  std::vector<std::thread> th;
+  const uint64_t per = (n + nt - 1) / nt;
+  for (uint64_t t = 0; t < nt; ++t) th.emplace_back([=, &fn] { fn(std::min(n, t * per), std::min(n, (t + 1) * per), (unsigned)t); });
+  for (auto& x : th) x.join();
+}
+}  // namespace
+extern "C" {
+
+int rfq_out_maxchar(const rfq_ctx* c, uint32_t d, uint32_t* maxchar) {
+  const uint32_t n = c ? (c->out_n ? c->out_n : c->n_docs) : 0;
+  if (!c || !c->fetched || d >= n || !maxchar) return RFQ_ERR_ARG;
+  const uint8_t* p = (const uint8_t*)c->h_out.p + c->h_out_off[d];
+  const uint64_t len = c->h_out_len[d];
+  uint8_t part[16] = {0};
+  host_parallel(len, 4u << 20, [&](uint64_t a, uint64_t b, unsigned t) {
+    uint8_t m = 0;
+    for (uint64_t i = a; i < b; ++i) m = std::max(m, p[i]);
+    part[t] = m;
+  });
+  uint8_t m = 0;
+  for (uint8_t x : part) m = std::max(m, x);
+  // the largest byte of valid UTF-8 is a lead byte (or ASCII): it bounds the largest code point
+  *maxchar = m < 0x80 ? 0x7Fu : m < 0xC4 ? 0xFFu : m < 0xF0 ? 0xFFFFu : 0x10FFFFu;
+  return RFQ_OK;
+}
+
+int rfq_out_widen(const rfq_ctx* c, uint32_t d, int unit, void* dst, uint64_t n_chars) {
+  const uint32_t n = c ? (c->out_n ? c->out_n : c->n_docs) : 0;
+  if (!c || !c->fetched || d >= n || !dst || (unit != 1 && unit != 2 && unit != 4)) return RFQ_ERR_ARG;
+  const uint8_t* p = (const uint8_t*)c->h_out.p + c->h_out_off[d];
+  const uint64_t len = c->h_out_len[d];
+  // chunk boundaries on character starts; characters before every chunk
+  uint64_t cut[17], before[17];
+  unsigned nt = 0;
+  {
+    unsigned hw = std::thread::hardware_concurrency();
+    nt = (unsigned)std::min<uint64_t>(std::min<uint64_t>(hw ? hw : 4u, 16u), std::max<uint64_t>(1, len / (4u << 20)));
+    for (unsigned t = 0; t <= nt; ++t) {
+      uint64_t x = len * t / nt;
+      while (x < len && (p[x] & 0xC0) == 0x80) ++x;
+      cut[t] = x;
+    }
+  }
+  std::vector<std::thread> th;
+  uint64_t cnt[16] = {0};
+  auto count = [&](unsigned t) { uint64_t k = 0; for (uint64_t i = cut[t]; i < cut[t + 1]; ++i) k += (p[i] & 0xC0) != 0x80; cnt[t] = k; };
+  if (nt == 1) count(0); else { for (unsigned t = 0; t < nt; ++t) th.emplace_back(count, t); for (auto& x : th) x.join(); th.clear(); }
+  before[0] = 0;
+  for (unsigned t = 0; t < nt; ++t) before[t + 1] = before[t] + cnt[t];
+  if (before[nt] != n_chars) return RFQ_ERR_ARG;
+  auto widen = [&](unsigned t) {
+    uint64_t o = before[t];
+    uint8_t* d1 = (uint8_t*)dst; uint16_t* d2 = (uint16_t*)dst; uint32_t* d4 = (uint32_t*)dst;
+    for (uint64_t i = cut[t]; i < cut[t + 1];) {
+      uint32_t b = p[i], cp; int l;
+      if (b < 0x80) { cp = b; l = 1; }
+      else if (b < 0xE0) { cp = ((b & 0x1Fu) << 6) | (p[i + 1] & 0x3Fu); l = 2; }
+      else if (b < 0xF0) { cp = ((b & 0x0Fu) << 12) | ((p[i + 1] & 0x3Fu) << 6) | (p[i + 2] & 0x3Fu); l = 3; }
+      else { cp = ((b & 0x07u) << 18) | ((p[i + 1] & 0x3Fu) << 12) | ((p[i + 2] & 0x3Fu) << 6) | (p[i + 3] & 0x3Fu); l = 4; }
+      if (unit == 1) d1[o] = (uint8_t)cp; else if (unit == 2) d2[o] = (uint16_t)cp; else d4[o] = cp;
+      ++o; i += l;
+    }
+  };
+  if (nt == 1) widen(0); else { for (unsigned t = 0; t < nt; ++t) th.emplace_back(widen, t); for (auto& x : th) x.join(); }
+  return RFQ_OK;
+}
 
 float rfq_last_run_ms(const rfq_ctx* c) { return c ? c->last_ms : 0.f; }
 uint64_t rfq_launch_count(const rfq_ctx*) { return g_launch_count.load(); }

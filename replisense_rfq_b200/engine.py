@@ -22,6 +22,37 @@ _decode_utf8.restype = C.py_object
 _decode_utf8.argtypes = [C.c_void_p, C.c_ssize_t, C.c_char_p]
 
 
+# Big texts: CPython's UTF-8 decoder is one thread writing into freshly mapped pages (60 ms for 135 MB).
+# When the code-point count is known (the device counted it), the string object is allocated at its final
+# width and the library fills its buffer with several threads (rfq_out_widen).  The offsets of a compact
+# string's data are checked on a small string at import; on any surprise the plain decoder is used.
+_py_new = C.pythonapi.PyUnicode_New
+_py_new.restype = C.py_object
+_py_new.argtypes = [C.c_ssize_t, C.c_uint32]
+
+
+def _str_data_offsets():
+    import sys
+    try:
+        # header sizes of CPython's compact strings, from objects whose size is header + units + terminator
+        off_ascii, off_compact = sys.getsizeof("") - 1, sys.getsizeof("a\xe9") - 3
+        if sys.implementation.name != "cpython" or (off_ascii, off_compact) != (40, 56):
+            return None
+        for text, maxchar, off, unit in (("abc", 127, off_ascii, 1), ("a\xe9c", 255, off_compact, 1),
+                                         ("a\u20b9c", 0xFFFF, off_compact, 2), ("a\U0001f600c", 0x10FFFF, off_compact, 4)):
+            o = _py_new(len(text), maxchar)
+            raw = text.encode({1: "latin-1", 2: "utf-16-le", 4: "utf-32-le"}[unit])
+            C.memmove(id(o) + off, raw, len(raw))
+            if o != text or len(o) != len(text):
+                return None
+        return off_ascii, off_compact
+    except Exception:  # noqa: BLE001
+        return None
+
+
+_STR_OFFSETS = _str_data_offsets()
+_FAST_STR_MIN = 1 << 20
+
 _PACK_THREADS = 8
 _pack_executor = None
 
@@ -111,6 +142,9 @@ class BatchResult:
         self.rows = arr(lib.rfq_out_rows(ctx), C.c_uint32, np.uint32)
         self.cols = arr(lib.rfq_out_cols(ctx), C.c_uint32, np.uint32)
         self.attempt = arr(lib.rfq_out_attempt(ctx), C.c_uint8, np.uint8)
+        self._lib, self._ctx = lib, ctx
+        cp = lib.rfq_out_chars(ctx)
+        self.chars = np.ctypeslib.as_array((C.c_uint64 * n).from_address(cp)).copy() if n and cp else None
 
     def doc_bytes(self, d: int) -> bytes:
         ln = int(self.lengths[d])
@@ -122,6 +156,16 @@ class BatchResult:
         ln = int(self.lengths[d])
         if ln == 0:
             return ""
+        if ln >= _FAST_STR_MIN and _STR_OFFSETS is not None and self.chars is not None:
+            nch = int(self.chars[d])
+            if nch != 0xFFFFFFFFFFFFFFFF and 0 < nch <= ln:
+                mc = C.c_uint32()
+                if self._lib.rfq_out_maxchar(self._ctx, d, C.byref(mc)) == 0:
+                    unit = 1 if mc.value <= 0xFF else 2 if mc.value <= 0xFFFF else 4
+                    o = _py_new(nch, mc.value)
+                    off = _STR_OFFSETS[0] if mc.value <= 0x7F else _STR_OFFSETS[1]
+                    if self._lib.rfq_out_widen(self._ctx, d, unit, id(o) + off, nch) == 0:
+                        return o
         # decode straight out of the pinned buffer (no intermediate bytes object)
         return _decode_utf8(self.text_ptr + int(self.offsets[d]), ln, None)
 

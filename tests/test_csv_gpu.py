@@ -218,3 +218,15 @@ def test_csv_decimal_literals(eng):
     got = eng.parse_csv_many(docs, 1000)
     bad = [i for i, (g, d) in enumerate(zip(got, docs)) if g != oracle(d, 1000)]
     assert not bad, bad[:10]
+
+
+def test_big_texts_become_python_strings_at_every_width(eng):
+    """Texts above 1 MB are built as str objects of their final width (1, 2 or 4 bytes per code point)
+    and filled by the library's threads instead of CPython's one-thread UTF-8 decoder: ASCII, Latin-1
+    range, BMP and astral documents must come out equal to the oracle's strings."""
+    for word in ("plain", "Würth é", "₹ 日本語", "ok 😀"):
+        rows = "\n".join('P-%06d,"%s %d",%d.%02d' % (i, word, i % 97, i % 5000, i % 100) for i in range(60000))
+        d = ("part,desc,price\n" + rows + "\n").encode("utf-8")
+        got = eng.parse_csv_many([d], 10 ** 6)[0]
+        want = oracle(d, 10 ** 6)
+        assert len(got) == len(want) > (1 << 20) and got == want, word
