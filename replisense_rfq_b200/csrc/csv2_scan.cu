@@ -94,12 +94,13 @@ __device__ unsigned long long lookback_seg(unsigned long long* desc, uint32_t ch
   return acc;
 }
 
-__global__ void __launch_bounds__(256) csv2_scan_kernel(Csv2Args a) {
+#define RFQ2_SCAN_WARPS (RFQ2_SCAN_TILES / 4u)
+__global__ void __launch_bounds__(RFQ2_SCAN_WARPS * 32) csv2_scan_kernel(Csv2Args a) {
   RFQ_INIT_CLASS_FN();
   __shared__ uint32_t pair_fn[128];
-  if (threadIdx.x < 128) pair_fn[threadIdx.x] = fn_compose(class_fn[threadIdx.x & 7u], class_fn[(threadIdx.x >> 4) & 7u]);
-  __shared__ uint32_t s_chunk, s_wfn[8], s_start_state;
-  __shared__ unsigned long long s_wseg[8], s_seg_in;
+  for (uint32_t i = threadIdx.x; i < 128; i += blockDim.x) pair_fn[i] = fn_compose(class_fn[i & 7u], class_fn[(i >> 4) & 7u]);
+  __shared__ uint32_t s_chunk, s_wfn[RFQ2_SCAN_WARPS], s_start_state;
+  __shared__ unsigned long long s_wseg[RFQ2_SCAN_WARPS], s_seg_in;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   (void)class_ev;
   for (;;) {
@@ -148,7 +149,7 @@ __global__ void __launch_bounds__(256) csv2_scan_kernel(Csv2Args a) {
     if (w == 0) {
       uint32_t cf = RFQ_FN_IDENTITY;
 #pragma unroll
-      for (int v = 0; v < 8; ++v) cf = fn_compose(cf, s_wfn[v]);
+      for (int v = 0; v < (int)RFQ2_SCAN_WARPS; ++v) cf = fn_compose(cf, s_wfn[v]);
       const uint32_t pre = lookback_fn(a.fn_desc, chunk, cf, lane);
       if (lane == 0) s_start_state = (uint32_t)fn_apply(pre, ST_R);
     }
@@ -205,7 +206,7 @@ __global__ void __launch_bounds__(256) csv2_scan_kernel(Csv2Args a) {
     if (w == 0) {
       unsigned long long cs = 0ull;
 #pragma unroll
-      for (int v = 0; v < 8; ++v) cs = seg_op(cs, s_wseg[v]);
+      for (int v = 0; v < (int)RFQ2_SCAN_WARPS; ++v) cs = seg_op(cs, s_wseg[v]);
       const unsigned long long pre = lookback_seg(a.cnt_desc, chunk, cs, lane);
       if (lane == 0) s_seg_in = pre;
     }
@@ -258,10 +259,10 @@ void csv2_scan(const Csv2Args& a, cudaStream_t s) {
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  static const int per_sm = getenv("RFQ2_SCAN_CTAS") ? atoi(getenv("RFQ2_SCAN_CTAS")) : 6;
+  static const int per_sm = getenv("RFQ2_SCAN_CTAS") ? atoi(getenv("RFQ2_SCAN_CTAS")) : (int)(32u / RFQ2_SCAN_WARPS);
   const uint32_t grid = std::min<uint32_t>(a.n_chunks, (uint32_t)sms * (uint32_t)per_sm);
   prof_mark("csv2_scan_kernel", s);
-  RFQ_LAUNCH(csv2_scan_kernel, grid, 256, 0, s, a);
+  RFQ_LAUNCH(csv2_scan_kernel, grid, RFQ2_SCAN_WARPS * 32, 0, s, a);
 }
 
 }  // namespace rfq
