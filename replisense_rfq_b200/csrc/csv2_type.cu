@@ -24,18 +24,13 @@
 
 namespace rfq {
 
-// ---- per document, right after the scan: rows used, attempt-level failures ---------------------
-__global__ void __launch_bounds__(128) csv2_docprep_kernel(Csv2Args a) {
-  const uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
-  if (d >= a.n_docs) return;
-  const Doc2& D = a.docs[d];
-  DocRun R = a.run[d];
-  uint32_t fl = R.flags;
-  if (R.n_rec == 0) fl |= RUN_FAIL;                                                    // EmptyDataError
-  if (R.final_state == ST_Q && (unsigned long long)R.n_rec < (unsigned long long)D.max_rows + 1ull) fl |= RUN_FAIL;   // EOF inside string
+// What the scan left about a document, completed: data rows used and the failures that show without
+// looking at a cell.  Every kernel that needs them before csv2_plan_kernel stores them derives them itself.
+__device__ __forceinline__ DocRun doc_view(const Doc2& D, DocRun R) {
+  if (R.n_rec == 0) R.flags |= RUN_FAIL;                                                    // EmptyDataError
+  if (R.final_state == ST_Q && (unsigned long long)R.n_rec < (unsigned long long)D.max_rows + 1ull) R.flags |= RUN_FAIL;   // EOF inside string
   R.n_data = R.n_rec ? min(R.n_rec - 1u, D.max_rows) : 0u;
-  R.flags = fl;
-  a.run[d] = R;
+  return R;
 }
 
 enum { S_FLAGS = 0, S_BAD, S_UINV, S_STR, S_INT, S_UINT, S_BOOL, S_IP, S_TZ, S_OBJ, S_SCI, S_FL, S_NA, S_COUNT };
@@ -95,7 +90,7 @@ __global__ void __launch_bounds__(RFQ2_ROWS) csv2_type_kernel(Csv2Args a, uint32
     __syncthreads();
     const uint32_t d = s_doc;
     const Doc2 D = a.docs[d];
-    const DocRun R = a.run[d];
+    const DocRun R = doc_view(D, a.run[d]);
     const uint32_t row0 = (item - D.item_base) * RFQ2_ROWS;
     if ((R.flags & (RUN_FAIL | RUN_UNSUP)) || row0 >= R.n_data) { __syncthreads(); continue; }
     const uint32_t nrows = min(RFQ2_ROWS, R.n_data - row0);
@@ -278,7 +273,7 @@ __device__ __forceinline__ ChunkCand cand_of(const StatV2& s) {
 __global__ void __launch_bounds__(256) csv2_plan_kernel(Csv2Args a) {
   const uint32_t d = blockIdx.x;
   const Doc2 D = a.docs[d];
-  DocRun R = a.run[d];
+  DocRun R = doc_view(D, a.run[d]);
   __shared__ uint32_t s_flags, s_dropped, s_carry;
   if (threadIdx.x == 0) { s_flags = 0; s_dropped = 0; s_carry = 0; }
   __syncthreads();
@@ -394,8 +389,6 @@ static int sm_count() {
 
 void csv2_type(const Csv2Args& a, cudaStream_t s) {
   if (a.n_docs == 0) return;
-  prof_mark("csv2_docprep_kernel", s);
-  RFQ_LAUNCH(csv2_docprep_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
   if (a.n_items == 0) return;
   const uint32_t smem = RFQ2_TYPE_STAGE + 32u + (uint32_t)S_COUNT * a.max_w * 4u;
   static std::atomic<unsigned long long> attr_done{0};
@@ -415,11 +408,62 @@ void csv2_type(const Csv2Args& a, cudaStream_t s) {
   RFQ_LAUNCH(csv2_type_cold_kernel, sm_count() * 4, 128, 0, s, a);
 }
 
+// item bytes -> offsets -> document offsets in ONE launch when the batch has few enough items for one CTA
+// to walk them (1024 items per round): five launches less on the critical path of a single big document
+__global__ void __launch_bounds__(1024) csv2_offsets_kernel(Csv2Args a) {
+  __shared__ unsigned long long s_warp[32], s_carry;
+  if (threadIdx.x == 0) s_carry = 0ull;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (uint32_t base = 0; base <= a.n_items; base += 1024) {
+    const uint32_t item = base + threadIdx.x;
+    unsigned long long b = 0;
+    if (item < a.n_items) {
+      const uint32_t d = ub_search(a.item_base, a.n_docs, item);
+      const Doc2& D = a.docs[d];
+      const DocRun& R = a.run[d];
+      if (!(R.flags & (RUN_FAIL | RUN_UNSUP | RUN_GENERAL))) {
+        const uint32_t row0 = (item - D.item_base) * RFQ2_ROWS;
+        if (item == D.item_base) b += R.hdr_bytes;
+        if (row0 < R.n_data && R.n_keep) {
+          const uint32_t nrows = min(RFQ2_ROWS, R.n_data - row0);
+          const uint32_t e0 = D.stat_base + (row0 / D.bl) * D.W;
+          const uint32_t dropped = a.chunk_nf[e0] ? 0u : a.item_allna[item];
+          const unsigned long long rb = (unsigned long long)(nrows - dropped) * (1ull + R.linew) + a.item_extra[item];
+          b += rb;
+          if (a.item_extra[item]) atomicAdd(&a.run[d].extra, a.item_extra[item]);
+          if (rb < 0xFFFFFFFFull && (uint32_t)rb > a.counters[4]) atomicMax(a.counters + 4, (uint32_t)rb);
+        }
+      }
+    }
+    unsigned long long incl = warp_incl_scan<SumU64>(b, lane);
+    if (lane == 31) s_warp[w] = incl;
+    __syncthreads();
+    if (w == 0) {
+      unsigned long long x = s_warp[lane];
+      x = warp_incl_scan<SumU64>(x, lane);
+      s_warp[lane] = x;
+    }
+    __syncthreads();
+    const unsigned long long excl = s_carry + (w ? s_warp[w - 1] : 0ull) + incl - b;
+    if (item <= a.n_items) a.item_off[item] = excl;
+    __syncthreads();
+    if (threadIdx.x == 0) s_carry += s_warp[31];
+    __syncthreads();
+  }
+  for (uint32_t d = threadIdx.x; d < a.n_docs; d += blockDim.x) {
+    const unsigned long long o0 = a.item_off[a.item_base[d]], o1 = a.item_off[a.item_base[d + 1]];
+    a.doc_out_off[d] = o0;
+    a.doc_out_len[d] = o1 - o0;
+  }
+}
+
 void csv2_plan(const Csv2Args& a, cudaStream_t s) {
   if (a.n_docs == 0) return;
   prof_mark("csv2_plan_kernel", s);
   RFQ_LAUNCH(csv2_plan_kernel, a.n_docs, 256, 0, s, a);
   prof_mark("csv2_item_bytes+scan", s);
+  if (a.n_items <= (1u << 16)) { RFQ_LAUNCH(csv2_offsets_kernel, 1, 1024, 0, s, a); return; }
   RFQ_LAUNCH(csv2_item_bytes_kernel, (a.n_items + 1 + 255) / 256, 256, 0, s, a);
   exclusive_scan<SumU64>(a.item_bytes, a.item_off, a.n_items + 1, a.scan_tmp64, nullptr, s);
   RFQ_LAUNCH(csv2_docout_kernel, (a.n_docs + 127) / 128, 128, 0, s, a);
