@@ -339,7 +339,11 @@ RFQ_HD void copy_span(uint8_t* dst, const uint8_t* src, uint32_t n) {
     d[4] = (uint8_t)hi; d[5] = (uint8_t)(hi >> 8); d[6] = (uint8_t)(hi >> 16); d[7] = (uint8_t)(hi >> 24);
   }
   if (i < n) {
+#ifdef __CUDA_ARCH__
+    const uint64_t x = load8_masked(src + i, 8);      // only the n - i low bytes are stored
+#else
     const uint64_t x = load8_masked(src + i, n - i);
+#endif
     for (uint32_t q = 0; i + q < n; ++q) dst[i + q] = (uint8_t)(x >> (8 * q));
   }
 }
@@ -367,17 +371,18 @@ RFQ_HD int emit_hot(const CellSrc& s, int ct, int kind, int dec, uint32_t width,
   if (s.missing) return 0;
   if (s.mode == CM_CSV) return 1;
   if (na_known == 1 && ct != CT_STRNF) return 0;
-  uint32_t nbytes;
-  uint64_t first8;
-  if (s.clean) { nbytes = s.n; first8 = s.n ? load8_masked(s.p, s.n) : 0; }
-  else if (s.mode == CM_CSVQ) {
-    nbytes = (uint32_t)s.bits; first8 = 0x2020202020202020ull;
-    if (nbytes <= 8) {   // only short tokens can be NA words
-      first8 = 0;
-      PairIter it(s.p, s.n);
-      for (int k = 0; k < 8; ++k) { int c = it.next(); if (c < 0) break; first8 |= (uint64_t)c << (8 * k); }
-    }
-  } else { nbytes = s.n; first8 = s.n ? load8_masked(s.p, s.n) : 0; }
+  const uint32_t nbytes = s.mode == CM_CSVQ ? (uint32_t)s.bits : s.n;
+  uint64_t first8 = 0;
+  if (na_known < 0 || kind == PR_BOOL || kind == PR_INT) {   // text whose NA test is done is copied without a look at its head
+    if (s.mode == CM_CSVQ) {
+      first8 = 0x2020202020202020ull;
+      if (nbytes <= 8) {   // only short tokens can be NA words
+        first8 = 0;
+        PairIter it(s.p, s.n);
+        for (int k = 0; k < 8; ++k) { int c = it.next(); if (c < 0) break; first8 |= (uint64_t)c << (8 * k); }
+      }
+    } else if (s.n) first8 = load8_masked(s.p, s.n);
+  }
   if (na_known < 0 && ct != CT_STRNF && is_na_token(nbytes, first8)) return 0;   // NaN -> '' after fillna: the blanks are there already
   switch (kind) {
     case PR_STR: {

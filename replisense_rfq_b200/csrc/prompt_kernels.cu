@@ -117,13 +117,14 @@ __global__ void __launch_bounds__(256) prompt_gather_kernel(const unsigned long 
   const uint8_t* src = reinterpret_cast<const uint8_t*>(src_ptr[d]);
   const uint32_t n = take[d], padded = (n + 15u) & ~15u;
   uint8_t* o = dst + dst_off[d];
-  for (uint32_t i = threadIdx.x; i < padded; i += blockDim.x) o[i] = i < n ? src[i] : (uint8_t)0;
+  // blockIdx.y slices the document: a 32 KB head is sixteen CTAs, not one
+  for (uint32_t i = blockIdx.y * blockDim.x + threadIdx.x; i < padded; i += gridDim.y * blockDim.x) o[i] = i < n ? src[i] : (uint8_t)0;
 }
 void prompt_gather(const unsigned long long* src_ptr, const uint32_t* take, const uint32_t* dst_off, uint8_t* dst,
                    uint32_t n_docs, cudaStream_t s) {
   if (n_docs == 0) return;
   prof_mark("prompt_gather_kernel", s);
-  RFQ_LAUNCH(prompt_gather_kernel, n_docs, 256, 0, s, src_ptr, take, dst_off, dst);
+  RFQ_LAUNCH(prompt_gather_kernel, dim3(n_docs, n_docs < 4096 ? 16 : 1), 256, 0, s, src_ptr, take, dst_off, dst);
 }
 
 void prompt_measure(const PromptArgs& a, cudaStream_t s) {

@@ -18,10 +18,10 @@ out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv", "--metrics", m
 rows = list(csv.reader(io.StringIO(out)))
 h, u = rows[0], rows[1]
 cols = [i for i, a in enumerate(h) if a in mets.split(",")]
-lines = ["ncu --set full --import-source on --clock-control none, one launch of each CSV kernel of the FINAL round-1 pipeline",
+lines = ["ncu --set full --import-source on --clock-control none, one launch of each hot kernel of the CSV row pipeline (round 2)",
          "workload: bench.py C2 (1 M rows x 8 cols, 86.8 MB in -> 135.1 MB out), B200; report %s (not tracked)" % rep,
          "times under ncu are cold-cache / serialised; bench.py's CUDA-event times are the measured ones", ""]
-traffic = {"source": "%s (ncu --set full, C2 1M rows, final round-1 kernels): dram__bytes_read.sum + "
+traffic = {"source": "%s (ncu --set full, C2 1M rows, round-2 kernels): dram__bytes_read.sum + "
                      "dram__bytes_write.sum per launch" % out_txt}
 mult = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1}
 seen = set()
