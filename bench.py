@@ -325,6 +325,33 @@ def main():
     t_prompt = float(tq.item())
     prompt_bytes, raw_chars = pouts[0]
     pool.close()
+    # ---- what the host side of this box can move: every rank copies a step's input up and a step's output
+    # down at the same time (two streams, pinned memory), all ranks at once; max over ranks.  e2e cannot be
+    # faster than `both_ms`, e2e_prompt not faster than `h2d_ms`.
+    def _copy_probe(h2d, d2h, reps=8):
+        barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            if h2d:
+                with torch.cuda.stream(ps1):
+                    p_di.copy_(p_hi, non_blocking=True)
+            if d2h:
+                with torch.cuda.stream(ps2):
+                    p_ho.copy_(p_do, non_blocking=True)
+        torch.cuda.synchronize()
+        tt = torch.tensor([(time.perf_counter() - t0) / reps], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt.item())
+    p_hi = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    p_ho = torch.empty(out_bytes, dtype=torch.uint8).pin_memory()
+    p_di = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    p_do = torch.empty(out_bytes, dtype=torch.uint8, device="cuda")
+    ps1, ps2 = torch.cuda.Stream(), torch.cuda.Stream()
+    _copy_probe(True, True, 2)
+    pc_h2d, pc_d2h, pc_both = _copy_probe(True, False), _copy_probe(False, True), _copy_probe(True, True)
+    del p_hi, p_ho, p_di, p_do
     sampler.stop_flag = True
     sampler.join()
     # and once more all the way to a Python str (what FileParser._parse_csv_sync returns)
@@ -396,14 +423,22 @@ def main():
         "e2e": {"value": total_mb / t_pipe, "unit": UNIT, "h2d_bytes_per_step": nbytes,
                 "d2h_bytes_per_step": out_bytes + 64, "ms_per_step": t_pipe / args.steps * 1e3,
                 "in_flight": depth, "serial_value": total_mb / t_e2e,
-                "serial_ms_per_step": t_e2e / args.steps * 1e3, "to_python_str_ms": t_str * 1e3},
+                "serial_ms_per_step": t_e2e / args.steps * 1e3, "to_python_str_ms": t_str * 1e3,
+                "frac_of_copy_ceiling": pc_both / (t_pipe / args.steps)},
+        # the copies alone on this box, all ranks at once (max over ranks): what e2e / e2e_prompt are bounded by
+        "copy_ceiling": {"h2d_ms": pc_h2d * 1e3, "d2h_ms": pc_d2h * 1e3, "both_ms": pc_both * 1e3,
+                         "h2d_GBps_per_gpu": nbytes / pc_h2d / 1e9, "d2h_GBps_per_gpu": out_bytes / pc_d2h / 1e9,
+                         "both_GBps_all_gpus": (nbytes + out_bytes) * world / pc_both / 1e9,
+                         "what": "pinned H2D of one step's input and D2H of one step's output on two streams, "
+                                 "every rank at the same time"},
         # the same document through the Python method the reference's callers use (file -> str), this rank
         "e2e_python": {"value": nbytes / 1e6 / t_py, "unit": UNIT, "ms_per_call": t_py * 1e3, "chars": n_txt,
                        "call": "FileParser(max_file_size_mb=4096, max_excel_rows=rows)._parse_csv_sync(path)"},
         # parse + prompt assembly fused on the device (rfq_csv_prompt_parse): H2D of the file, D2H of the prompt only
         "e2e_prompt": {"value": total_mb / t_prompt, "unit": UNIT, "ms_per_step": t_prompt / args.steps * 1e3,
                        "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": prompt_bytes + 64, "in_flight": depth,
-                       "text_length": raw_chars, "call": "rfq_csv_prompt_parse (C ABI), host buffers"},
+                       "text_length": raw_chars, "call": "rfq_csv_prompt_parse (C ABI), host buffers",
+                       "frac_of_copy_ceiling": pc_h2d / (t_prompt / args.steps)},
         "parity_gate": parity,
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "unit": "GB/s",

@@ -259,7 +259,7 @@ void csv2_scan(const Csv2Args& a, cudaStream_t s) {
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  static const int per_sm = getenv("RFQ2_SCAN_CTAS") ? atoi(getenv("RFQ2_SCAN_CTAS")) : (int)(32u / RFQ2_SCAN_WARPS);
+  static const int per_sm = getenv("RFQ2_SCAN_CTAS") ? atoi(getenv("RFQ2_SCAN_CTAS")) : 6;   // 48 of 64 warps: the look-back waits of one CTA are another's issue slots
   const uint32_t grid = std::min<uint32_t>(a.n_chunks, (uint32_t)sms * (uint32_t)per_sm);
   prof_mark("csv2_scan_kernel", s);
   RFQ_LAUNCH(csv2_scan_kernel, grid, RFQ2_SCAN_WARPS * 32, 0, s, a);

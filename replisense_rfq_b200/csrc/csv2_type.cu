@@ -346,30 +346,50 @@ __global__ void __launch_bounds__(256) csv2_plan_kernel(Csv2Args a) {
   }
 }
 
-// bytes of every work item's output range (the document's first item carries banner + header line)
-__global__ void __launch_bounds__(256) csv2_item_bytes_kernel(Csv2Args a) {
-  const uint32_t item = blockIdx.x * blockDim.x + threadIdx.x;
-  if (item > a.n_items) return;
-  unsigned long long b = 0;
-  if (item < a.n_items) {
-    const uint32_t d = ub_search(a.item_base, a.n_docs, item);
-    const Doc2& D = a.docs[d];
-    const DocRun& R = a.run[d];
-    if (!(R.flags & (RUN_FAIL | RUN_UNSUP | RUN_GENERAL))) {
-      const uint32_t row0 = (item - D.item_base) * RFQ2_ROWS;
-      if (item == D.item_base) b += R.hdr_bytes;
-      if (row0 < R.n_data && R.n_keep) {
-        const uint32_t nrows = min(RFQ2_ROWS, R.n_data - row0);
-        const uint32_t e0 = D.stat_base + (row0 / D.bl) * D.W;
-        const uint32_t dropped = a.chunk_nf[e0] ? 0u : a.item_allna[item];
-        const unsigned long long rb = (unsigned long long)(nrows - dropped) * (1ull + R.linew) + a.item_extra[item];
-        b += rb;
-        if (a.item_extra[item]) atomicAdd(&a.run[d].extra, a.item_extra[item]);
-        if (rb < 0xFFFFFFFFull && (uint32_t)rb > a.counters[4]) atomicMax(a.counters + 4, (uint32_t)rb);
-      }
-    }
+// bytes of a work item's output range (the document's first item carries banner + header line): loads
+// only, so that a caller with several items in flight overlaps their latencies
+struct ItemBytes { unsigned long long b; uint32_t d, ex, big; };
+__device__ __forceinline__ ItemBytes item_bytes_of(const Csv2Args& a, uint32_t item) {
+  ItemBytes r{0ull, 0xFFFFFFFFu, 0u, 0u};
+  if (item >= a.n_items) return r;
+  r.d = ub_search(a.item_base, a.n_docs, item);
+  const Doc2& D = a.docs[r.d];
+  const DocRun& R = a.run[r.d];
+  if (R.flags & (RUN_FAIL | RUN_UNSUP | RUN_GENERAL)) return r;
+  const uint32_t row0 = (item - D.item_base) * RFQ2_ROWS;
+  if (item == D.item_base) r.b += R.hdr_bytes;
+  if (row0 < R.n_data && R.n_keep) {
+    const uint32_t nrows = min(RFQ2_ROWS, R.n_data - row0);
+    const uint32_t e0 = D.stat_base + (row0 / D.bl) * D.W;
+    const uint32_t dropped = a.chunk_nf[e0] ? 0u : a.item_allna[item];
+    r.ex = a.item_extra[item];
+    const unsigned long long rb = (unsigned long long)(nrows - dropped) * (1ull + R.linew) + r.ex;
+    r.b += rb;
+    if (rb < 0xFFFFFFFFull) r.big = (uint32_t)rb;
   }
-  a.item_bytes[item] = b;
+  return r;
+}
+// The two per-document side results (non-ASCII extra bytes, largest item), reduced over the warp before they
+// touch global memory: neighbouring items belong to the same document nearly always.  All 32 lanes call it.
+__device__ __forceinline__ void item_bytes_commit(const Csv2Args& a, const ItemBytes& r) {
+  const uint32_t d0 = __shfl_sync(0xffffffffu, r.d, 0);
+  if (__all_sync(0xffffffffu, r.d == d0 || (r.ex == 0 && r.big == 0))) {
+    const uint32_t sum = __reduce_add_sync(0xffffffffu, r.ex), mx = __reduce_max_sync(0xffffffffu, r.big);
+    if ((threadIdx.x & 31u) == 0 && d0 != 0xFFFFFFFFu) {
+      if (sum) atomicAdd(&a.run[d0].extra, sum);
+      if (mx > a.counters[4]) atomicMax(a.counters + 4, mx);
+    }
+  } else {
+    if (r.ex) atomicAdd(&a.run[r.d].extra, r.ex);
+    if (r.big > a.counters[4]) atomicMax(a.counters + 4, r.big);
+  }
+}
+
+__global__ void __launch_bounds__(256) csv2_item_bytes_kernel(Csv2Args a) {
+  const uint32_t item = blockIdx.x * blockDim.x + threadIdx.x;   // whole warps: the grid covers n_items + 1 rounded up
+  const ItemBytes r = item_bytes_of(a, item);
+  item_bytes_commit(a, r);
+  if (item <= a.n_items) a.item_bytes[item] = r.b;
 }
 
 __global__ void __launch_bounds__(128) csv2_docout_kernel(Csv2Args a) {
@@ -378,6 +398,7 @@ __global__ void __launch_bounds__(128) csv2_docout_kernel(Csv2Args a) {
   const unsigned long long o0 = a.item_off[a.item_base[d]], o1 = a.item_off[a.item_base[d + 1]];
   a.doc_out_off[d] = o0;
   a.doc_out_len[d] = o1 - o0;
+  if (d == 0) *reinterpret_cast<unsigned long long*>(a.counters + 6) = a.item_off[a.n_items];   // total bytes of the attempt
 }
 
 static int sm_count() {
@@ -408,49 +429,41 @@ void csv2_type(const Csv2Args& a, cudaStream_t s) {
   RFQ_LAUNCH(csv2_type_cold_kernel, sm_count() * 4, 128, 0, s, a);
 }
 
-// item bytes -> offsets -> document offsets in ONE launch when the batch has few enough items for one CTA
-// to walk them (1024 items per round): five launches less on the critical path of a single big document
+// item bytes -> offsets -> document offsets in ONE launch when the batch has few enough items for one CTA:
+// five launches less on the critical path of a single big document.  The bytes of all items are
+// computed first (independent loads, no barrier between rounds), then every thread scans its own
+// consecutive items around ONE block scan.
 __global__ void __launch_bounds__(1024) csv2_offsets_kernel(Csv2Args a) {
-  __shared__ unsigned long long s_warp[32], s_carry;
-  if (threadIdx.x == 0) s_carry = 0ull;
-  __syncthreads();
+  __shared__ unsigned long long s_warp[32];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  for (uint32_t base = 0; base <= a.n_items; base += 1024) {
-    const uint32_t item = base + threadIdx.x;
-    unsigned long long b = 0;
-    if (item < a.n_items) {
-      const uint32_t d = ub_search(a.item_base, a.n_docs, item);
-      const Doc2& D = a.docs[d];
-      const DocRun& R = a.run[d];
-      if (!(R.flags & (RUN_FAIL | RUN_UNSUP | RUN_GENERAL))) {
-        const uint32_t row0 = (item - D.item_base) * RFQ2_ROWS;
-        if (item == D.item_base) b += R.hdr_bytes;
-        if (row0 < R.n_data && R.n_keep) {
-          const uint32_t nrows = min(RFQ2_ROWS, R.n_data - row0);
-          const uint32_t e0 = D.stat_base + (row0 / D.bl) * D.W;
-          const uint32_t dropped = a.chunk_nf[e0] ? 0u : a.item_allna[item];
-          const unsigned long long rb = (unsigned long long)(nrows - dropped) * (1ull + R.linew) + a.item_extra[item];
-          b += rb;
-          if (a.item_extra[item]) atomicAdd(&a.run[d].extra, a.item_extra[item]);
-          if (rb < 0xFFFFFFFFull && (uint32_t)rb > a.counters[4]) atomicMax(a.counters + 4, (uint32_t)rb);
-        }
-      }
+  for (uint32_t base = 0; base <= a.n_items; base += 8192) {   // eight items per thread in flight
+    ItemBytes r[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) r[k] = item_bytes_of(a, base + k * 1024 + threadIdx.x);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t item = base + k * 1024 + threadIdx.x;
+      item_bytes_commit(a, r[k]);
+      if (item <= a.n_items) a.item_bytes[item] = r[k].b;
     }
-    unsigned long long incl = warp_incl_scan<SumU64>(b, lane);
-    if (lane == 31) s_warp[w] = incl;
-    __syncthreads();
-    if (w == 0) {
-      unsigned long long x = s_warp[lane];
-      x = warp_incl_scan<SumU64>(x, lane);
-      s_warp[lane] = x;
-    }
-    __syncthreads();
-    const unsigned long long excl = s_carry + (w ? s_warp[w - 1] : 0ull) + incl - b;
-    if (item <= a.n_items) a.item_off[item] = excl;
-    __syncthreads();
-    if (threadIdx.x == 0) s_carry += s_warp[31];
-    __syncthreads();
   }
+  __syncthreads();
+  const uint32_t per = (a.n_items + 1u + 1023u) / 1024u;
+  const uint32_t lo = min(threadIdx.x * per, a.n_items + 1u), hi = min(lo + per, a.n_items + 1u);
+  unsigned long long sum = 0;
+  for (uint32_t i = lo; i < hi; ++i) sum += a.item_bytes[i];
+  const unsigned long long incl = warp_incl_scan<SumU64>(sum, lane);
+  if (lane == 31) s_warp[w] = incl;
+  __syncthreads();
+  if (w == 0) s_warp[lane] = warp_incl_scan<SumU64>(s_warp[lane], lane);
+  __syncthreads();
+  unsigned long long run = (w ? s_warp[w - 1] : 0ull) + incl - sum;
+  for (uint32_t i = lo; i < hi; ++i) {
+    a.item_off[i] = run;
+    if (i == a.n_items) *reinterpret_cast<unsigned long long*>(a.counters + 6) = run;   // total bytes of the attempt
+    run += a.item_bytes[i];
+  }
+  __syncthreads();
   for (uint32_t d = threadIdx.x; d < a.n_docs; d += blockDim.x) {
     const unsigned long long o0 = a.item_off[a.item_base[d]], o1 = a.item_off[a.item_base[d + 1]];
     a.doc_out_off[d] = o0;

@@ -444,7 +444,9 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
   uint8_t* d_up = c->pool.alloc<uint8_t>(up.used + 256);
   // ---- 4. scratch: one zeroed region, then arrays that are written before they are read
   const size_t z_fn = 0, z_cnt = z_fn + 8ull * a.n_chunks, z_tick = z_cnt + 8ull * a.n_chunks, z_cntr = z_tick + 16;
-  const size_t z_run = (z_cntr + 32 + 255) & ~(size_t)255, z_stat = (z_run + sizeof(DocRun) * m + 255) & ~(size_t)255;
+  // counters | run | doc_out_off | doc_out_len are what the host reads back: contiguous, one copy
+  const size_t z_run = z_cntr + 32, z_ooff = z_run + sizeof(DocRun) * m, z_olen = z_ooff + 8ull * (m + 1), z_down_end = z_olen + 8ull * (m + 1);
+  const size_t z_stat = (z_down_end + 255) & ~(size_t)255;
   const size_t z_ctype = (z_stat + sizeof(StatV2) * n_stat + 255) & ~(size_t)255, z_allna = (z_ctype + n_stat + 255) & ~(size_t)255;
   const size_t z_nf = (z_allna + 4ull * n_stat + 255) & ~(size_t)255, z_end = (z_nf + n_stat + 255) & ~(size_t)255;
   uint8_t* z = c->pool.alloc<uint8_t>(z_end + 256);
@@ -459,8 +461,6 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
   a.item_off = c->pool.alloc<unsigned long long>(n_items + 2);
   a.scan_tmp64 = c->pool.alloc<unsigned long long>(scan_partials_needed(n_items + 1));
   a.col = c->pool.alloc<ColOut2>(n_cols + 1);
-  a.doc_out_off = c->pool.alloc<unsigned long long>(m + 1);
-  a.doc_out_len = c->pool.alloc<unsigned long long>(m + 1);
   a.cold_cells_cap = (uint32_t)std::min<uint64_t>(cells + 1, 4u << 20);
   a.cold_cells = c->pool.alloc<ColdCell>(a.cold_cells_cap);
   a.cold_rows_cap = (uint32_t)n_slots;
@@ -473,6 +473,7 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
   a.fn_desc = (unsigned long long*)(z + z_fn); a.cnt_desc = (unsigned long long*)(z + z_cnt);
   a.ticket = (uint32_t*)(z + z_tick); a.counters = (uint32_t*)(z + z_cntr);
   a.run = (DocRun*)(z + z_run); a.stat = (StatV2*)(z + z_stat); a.ctype = z + z_ctype;
+  a.doc_out_off = (unsigned long long*)(z + z_ooff); a.doc_out_len = (unsigned long long*)(z + z_olen);
   a.chunk_allna = (uint32_t*)(z + z_allna); a.chunk_nf = z + z_nf;
   RFQ_CK(c, cudaMemcpyAsync(d_up, c->h_up.p, up.used, cudaMemcpyHostToDevice, s));
   RFQ_CK(c, cudaMemsetAsync(z, 0, z_end, s));
@@ -496,18 +497,14 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
   csv2_type(a, s);
   csv2_plan(a, s);
   csv2_emit(a, s);
-  RFQ_CK(c, c->h_down.reserve(sizeof(DocRun) * (m + 1) + 16ull * (m + 1) + 4096));
+  RFQ_CK(c, c->h_down.reserve(z_down_end - z_cntr + 64));
   uint8_t* hd = (uint8_t*)c->h_down.p;
-  unsigned long long* h_total = (unsigned long long*)hd;
-  uint32_t* h_cntr = (uint32_t*)(hd + 64);
-  DocRun* h_run = (DocRun*)(hd + 256);
-  unsigned long long* h_ooff = (unsigned long long*)(hd + 256 + sizeof(DocRun) * (m + 1));
-  unsigned long long* h_olen = h_ooff + (m + 1);
-  RFQ_CK(c, cudaMemcpyAsync(h_total, a.item_off + a.n_items, 8, cudaMemcpyDeviceToHost, s));
-  RFQ_CK(c, cudaMemcpyAsync(h_cntr, a.counters, 32, cudaMemcpyDeviceToHost, s));
-  RFQ_CK(c, cudaMemcpyAsync(h_run, a.run, sizeof(DocRun) * m, cudaMemcpyDeviceToHost, s));
-  RFQ_CK(c, cudaMemcpyAsync(h_ooff, a.doc_out_off, 8ull * m, cudaMemcpyDeviceToHost, s));
-  RFQ_CK(c, cudaMemcpyAsync(h_olen, a.doc_out_len, 8ull * m, cudaMemcpyDeviceToHost, s));
+  uint32_t* h_cntr = (uint32_t*)hd;                                    // [6..7] = total bytes (64 bits)
+  const unsigned long long* h_total = (const unsigned long long*)(hd + 24);
+  const DocRun* h_run = (const DocRun*)(hd + (z_run - z_cntr));
+  const unsigned long long* h_ooff = (const unsigned long long*)(hd + (z_ooff - z_cntr));
+  const unsigned long long* h_olen = (const unsigned long long*)(hd + (z_olen - z_cntr));
+  RFQ_CK(c, cudaMemcpyAsync(hd, z + z_cntr, z_down_end - z_cntr, cudaMemcpyDeviceToHost, s));
   c->prof.mark("host+sync", s);
   RFQ_CK(c, cudaStreamSynchronize(s));
   unsigned long long total = *h_total;

@@ -5,7 +5,10 @@
 // data rows never pass through here.
 #pragma once
 #include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
 #include <algorithm>
+#include <charconv>
 #include <string>
 #include <thread>
 #include <unordered_map>
@@ -47,8 +50,11 @@ inline bool py_isspace_cp(uint32_t cp) {
 // LF inside a label print as the two characters \t \r \n, and a header row whose names all start
 // with blanks loses the common part.  The "Empty DataFrame" text prints the raw names instead.
 // Labels must be valid UTF-8 (the caller checks); returns the code points of each display label.
+// no_blank (optional): labels that format_array prints WITHOUT the blank (a negative float label of an
+// object Index, "-4.5": the sign takes the place of the blank) — trim_front then finds nothing common and
+// every other label keeps its blank.
 inline void display_labels(const std::vector<std::string>& names, std::vector<std::string>& disp,
-                           std::vector<uint32_t>& ncp) {
+                           std::vector<uint32_t>& ncp, const std::vector<uint8_t>* no_blank = nullptr) {
   const size_t n = names.size();
   disp.assign(n, std::string());
   ncp.assign(n, 0);
@@ -72,19 +78,26 @@ inline void display_labels(const std::vector<std::string>& names, std::vector<st
       ++tot; i += l;
     }
     lead_cp[k] = cps; ncp[k] = tot;
-    if (cps + 1 < cut) cut = cps + 1;
+    const uint32_t own = (no_blank && (*no_blank)[k]) ? cps : cps + 1;
+    if (own < cut) cut = own;
+  }
+  if (n && cut == 0) {                // some label starts at once: the others keep the blank format_array added
+    for (size_t k = 0; k < n; ++k)
+      if (!(no_blank && (*no_blank)[k])) { disp[k].insert(disp[k].begin(), ' '); ncp[k] += 1; }
+    return;
   }
   if (n == 0 || cut <= 1) return;     // only the blank format_array added is common
   cut -= 1;                           // code points to drop from every label
   for (size_t k = 0; k < n; ++k) {
     std::string& d = disp[k];
     size_t i = 0;
-    for (uint32_t q = 0; q < cut && i < d.size(); ++q) {
+    const uint32_t drop = (no_blank && (*no_blank)[k]) ? cut + 1 : cut;
+    for (uint32_t q = 0; q < drop && i < d.size(); ++q) {
       uint8_t b = (uint8_t)d[i];
       i += b >= 0xF0 ? 4 : b >= 0xE0 ? 3 : b >= 0xC0 ? 2 : 1;
     }
     d.erase(0, i);
-    ncp[k] -= cut;
+    ncp[k] -= drop;
   }
 }
 
@@ -252,23 +265,76 @@ inline HeaderInfo parse_header(const uint8_t* doc, uint64_t len, uint32_t sep, b
 
 // Header row of a sheet: labels keep their Python type (pandas/io/parsers/python_parser.py
 // _infer_columns).  kind per label: 0 str (or blank -> "Unnamed: k"), 1 int, 2 bool, 3 datetime,
-// 4 time, anything else = a type whose Index formatting is not restated (float, NaN).
-// Supported: all labels int (an Int64 Index), or at least one str label next to int / bool /
-// datetime / time labels (an object Index: every label prints as str(label)).  Declined: Index
-// dtypes pandas formats as a whole (all bool, all datetime, ...), bool next to int (True == 1 is one
-// dict key for the de-duplication), and equal text under different types (2024 vs "2024").
-inline bool sheet_labels_supported(const std::vector<int>& kind, const std::vector<std::string>& text) {
-  bool has_str = false, has_int = false, has_bool = false, has_other = false;
-  for (int k : kind) {
-    if (k == 0) has_str = true; else if (k == 1) has_int = true; else if (k == 2) has_bool = true;
-    else if (k == 3 || k == 4) has_other = true; else return false;
+// 4 time, 5 float (text = repr(label)), anything else = a type whose Index formatting is not restated
+// (NaN).  `value` = the number behind an int / bool / float label.
+// Supported: all labels int (an Int64 Index), or an object Index — labels of two type families or more,
+// any str, any time: every label prints as str(label), a float as f"{x: .6f}" with its zeros trimmed
+// (format.py _GenericArrayFormatter).  Declined: Index dtypes pandas formats as a whole (all bool, all
+// datetime, int + float = a Float64 Index), labels that are ONE dict key for the de-duplication under
+// different types (True == 1 == 1.0), and equal text under different types (2024 vs "2024").
+inline bool sheet_labels_supported(const std::vector<int>& kind, const std::vector<std::string>& text,
+                                   const std::vector<double>* value = nullptr) {
+  // type families: an Index of ONE family other than str / time has its own dtype and formatter
+  // (bool, int64, float64 = int + float, datetime64); two families or more, any str, any time -> object
+  uint32_t fam = 0;
+  bool has_float = false;
+  for (size_t i = 0; i < kind.size(); ++i) {
+    const int k = kind[i];
+    if (k == 0) fam |= 1u; else if (k == 1) fam |= 2u; else if (k == 5) { fam |= 2u; has_float = true; }
+    else if (k == 2) fam |= 4u; else if (k == 3) fam |= 8u; else if (k == 4) fam |= 16u; else return false;
   }
-  if ((has_bool || has_other) && !has_str) return false;
-  if (has_bool && has_int) return false;
+  const bool all_int = fam == 2u && !has_float;
+  const bool object_index = (fam & 1u) || (fam & 16u) || (fam & (fam - 1u)) != 0;
+  if (!all_int && !object_index) return false;
   for (size_t i = 0; i < kind.size(); ++i)
-    for (size_t j = i + 1; j < kind.size(); ++j)
-      if (kind[i] != kind[j] && text[i] == text[j]) return false;
+    for (size_t j = i + 1; j < kind.size(); ++j) {
+      if (kind[i] == kind[j]) continue;
+      if (text[i] == text[j]) return false;
+      // True == 1 == 1.0 is ONE dict key for the de-duplication
+      const bool ni = kind[i] == 1 || kind[i] == 2 || kind[i] == 5, nj = kind[j] == 1 || kind[j] == 2 || kind[j] == 5;
+      if (ni && nj && (!value || (*value)[i] == (*value)[j])) return false;
+    }
   return true;
+}
+
+// repr(float) of CPython (float_repr_style 'short': the shortest digits that round-trip, Objects/floatobject.c
+// float_repr -> PyOS_double_to_string(x, 'r', 0, Py_DTSF_ADD_DOT_0)): fixed notation for 1e-4 <= |x| < 1e16,
+// else d[.ddd]e+XX with at least two exponent digits.  std::to_chars gives the same shortest digits.
+inline std::string py_float_repr(double v) {
+  if (v != v) return "nan";
+  if (v == 1.0 / 0.0) return "inf";
+  if (v == -1.0 / 0.0) return "-inf";
+  char buf[64];
+  auto r = std::to_chars(buf, buf + sizeof(buf), v, std::chars_format::scientific);
+  std::string t(buf, r.ptr);                       // [-]d[.ddd]e[+-]XX
+  std::string out;
+  size_t i = 0;
+  if (t[i] == '-') { out = "-"; ++i; }
+  std::string digits;
+  size_t e = t.find('e');
+  for (size_t k = i; k < e; ++k) if (t[k] != '.') digits.push_back(t[k]);
+  const int exp10 = atoi(t.c_str() + e + 1);
+  if (exp10 < -4 || exp10 >= 16) {
+    out.push_back(digits[0]);
+    if (digits.size() > 1) { out.push_back('.'); out.append(digits, 1, std::string::npos); }
+    char eb[16];
+    snprintf(eb, sizeof(eb), "e%c%02d", exp10 < 0 ? '-' : '+', exp10 < 0 ? -exp10 : exp10);
+    return out + eb;
+  }
+  if (exp10 < 0) {
+    out += "0.";
+    out.append((size_t)(-exp10 - 1), '0');
+    return out + digits;
+  }
+  if (digits.size() <= (size_t)exp10 + 1) {
+    out += digits;
+    out.append((size_t)exp10 + 1 - digits.size(), '0');
+    return out + ".0";
+  }
+  out.append(digits, 0, (size_t)exp10 + 1);
+  out.push_back('.');
+  out.append(digits, (size_t)exp10 + 1, std::string::npos);
+  return out;
 }
 
 // "Empty DataFrame\nColumns: [a, b]\nIndex: []" (display.max_seq_items = 100)

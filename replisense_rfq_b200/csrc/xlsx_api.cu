@@ -3,6 +3,8 @@
 // (the host inflated the zip and read workbook.xml / rels / styles.xml);
 // every pass over XML bytes or cells is a kernel, the host does O(documents + columns) work.
 #include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <algorithm>
 #include <string>
@@ -41,6 +43,7 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
   RFQ_CK(c, cudaSetDevice(c->device));
   cudaStream_t s = c->stream;
   const uint32_t n = c->n_docs;
+  static const bool why = getenv("RFQ_SHEET_WHY") != nullptr;   // say on stderr why a sheet is declined
   if (!c->nested) c->prof.begin();
   g_prof = &c->prof;
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
@@ -138,7 +141,10 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
                                                             // kernel writes it for all unflagged sheets)
     uint32_t fl = sh.flags;
     if (sst_of[d] >= 0) fl |= h_shape[sst_of[d]].flags;
-    if (xu_problem(fl) || sh.W > 1024) { c->r_status[d] = RFQ_DOC_UNSUPPORTED; n_slots += 1; continue; }
+    if (xu_problem(fl) || sh.W > 1024) {
+      if (why) fprintf(stderr, "rfq sheet %u declined: part flags 0x%x width %u\n", d, fl, sh.W);
+      c->r_status[d] = RFQ_DOC_UNSUPPORTED; n_slots += 1; continue;
+    }
     if (sh.lastrow <= 1) { c->r_status[d] = RFQ_DOC_EMPTY_SHEET; n_slots += 1; continue; }
     T.W = sh.W; T.h = sh.W; T.lead = 0;
     T.n_data = sh.lastrow - 1;
@@ -198,6 +204,7 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
       const uint32_t g = T.col_base + j, len = h_hmeta[2 * g + 1];
       hkey.append((const char*)&h_hmeta[2 * g], 8);
       if (len != 0xFFFFFFFFu) hkey.append((const char*)h_hdr + (size_t)g * 256, std::min<uint32_t>(len, 256));
+      if (h_hmeta[2 * g] == CM_FLOAT) hkey.append((const char*)h_hdr + (size_t)g * 256 + 240, 8);   // the value itself
     }
     auto hit = hdr_cache.find(hkey);
     if (hit == hdr_cache.end()) {
@@ -206,16 +213,30 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
       std::vector<size_t> unnamed;
       bool all_int = true;
       std::vector<int> lkind(T.W, 0);
+      std::vector<std::string> ftext(T.W);          // float labels as an object Index prints them
+      std::vector<uint8_t> no_blank(T.W, 0);
+      std::vector<double> lval(T.W, 0.0);
       for (uint32_t j = 0; j < T.W; ++j) {
         uint32_t g = T.col_base + j, mode = h_hmeta[2 * g], len = h_hmeta[2 * g + 1];
         if (mode != CM_INT) all_int = false;
         lkind[j] = mode == CM_INT ? 1 : mode == CM_BOOL ? 2 : mode == CM_DATE ? 3 : mode == CM_TIME ? 4
-                   : (mode == CM_RAW || mode == CM_XML || mode == CM_NULL) ? 0 : 9;
+                   : mode == CM_FLOAT ? 5 : (mode == CM_RAW || mode == CM_XML || mode == CM_NULL) ? 0 : 9;
         if (mode == CM_NULL) { raw[j] = "Unnamed: " + std::to_string(j); unnamed.push_back(j); }
-        else if (lkind[j] != 9 && len != 0xFFFFFFFFu) raw[j].assign((const char*)h_hdr + (size_t)g * 256, len);
-        else H.ok = false;  // float / oversized labels
+        else if (lkind[j] == 5 && len != 0xFFFFFFFFu && len <= 200) {
+          double v;
+          memcpy(&v, h_hdr + (size_t)g * 256 + 240, 8);
+          ftext[j].assign((const char*)h_hdr + (size_t)g * 256, len);
+          raw[j] = py_float_repr(v);                // the label as a name (de-duplication, "Empty DataFrame")
+          lval[j] = v;
+        }
+        else if (lkind[j] != 9 && lkind[j] != 5 && len != 0xFFFFFFFFu) {
+          raw[j].assign((const char*)h_hdr + (size_t)g * 256, len);
+          if (lkind[j] == 1) lval[j] = strtod(raw[j].c_str(), nullptr);
+          if (lkind[j] == 2) lval[j] = raw[j] == "True" ? 1.0 : 0.0;
+        }
+        else H.ok = false;  // NaN / oversized labels
       }
-      if (H.ok && !sheet_labels_supported(lkind, raw)) H.ok = false;
+      if (H.ok && !sheet_labels_supported(lkind, raw, &lval)) H.ok = false;
       if (H.ok) {
         std::vector<std::string> before = raw;
         dedupe_names(raw, unnamed);
@@ -231,12 +252,21 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
           if (!utf8_valid_count(raw[j], &H.ncp[j])) H.ok = false;
         // labels as to_string prints them: escapes + trim_front (header_names.h display_labels)
         H.disp = raw;
-        if (H.ok && !(all_int && before == raw)) display_labels(raw, H.disp, H.ncp);
+        if (H.ok && !(all_int && before == raw)) {
+          // a float label that kept its name prints through the float formatter (a renamed one is a str now)
+          std::vector<std::string> shown = raw;
+          for (uint32_t j = 0; j < T.W; ++j)
+            if (lkind[j] == 5 && raw[j] == before[j]) { shown[j] = ftext[j]; no_blank[j] = ftext[j][0] == '-'; }
+          display_labels(shown, H.disp, H.ncp, &no_blank);
+        }
       }
       hit = hdr_cache.emplace(hkey, std::move(H)).first;
     }
     const HdrTexts& H = hit->second;
-    if (!H.ok) { T.active = 0; c->r_status[d] = RFQ_DOC_UNSUPPORTED; continue; }
+    if (!H.ok) {
+      if (why) fprintf(stderr, "rfq sheet %u declined: header labels\n", d);
+      T.active = 0; c->r_status[d] = RFQ_DOC_UNSUPPORTED; continue;
+    }
     T.empty_off = (uint32_t)names.size(); T.empty_len = (uint32_t)H.empty.size();
     names += H.empty;
     T.banner_off = 0; T.banner_len = 0;
@@ -324,7 +354,10 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
   c->out_total = total;
   for (uint32_t d = 0; d < n; ++d) {
     if (!td[d].active) continue;
-    if (h_flags[d]) { c->r_status[d] = RFQ_DOC_UNSUPPORTED; continue; }
+    if (h_flags[d]) {
+      if (why) fprintf(stderr, "rfq sheet %u declined: column flags 0x%x\n", d, h_flags[d]);
+      c->r_status[d] = RFQ_DOC_UNSUPPORTED; continue;
+    }
     c->r_off[d] = h_ooff[d]; c->r_len[d] = h_olen[d];
     c->r_rows[d] = h_keep[d]; c->r_cols[d] = td[d].W;
   }

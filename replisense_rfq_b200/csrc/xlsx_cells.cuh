@@ -22,17 +22,14 @@ enum {
   XU_X005F = 1u << 9,       // 'x005F_' escape inside a shared string
   // not problems by themselves: which of its rows / cells carry r=.  openpyxl counts rows and
   // columns from the previous element when r= is missing (worksheet/_reader.py parse_row /
-  // parse_cell); a part whose rows (cells) ALL lack r= is decoded by position, a mix is declined
+  // parse_cell); a part whose rows (cells) ALL lack r= is decoded by position, in a mix an element
+  // without r= continues from the nearest one before it that has it
   XU_ROW_NOREF = 1u << 10, XU_ROW_HASREF = 1u << 11, XU_C_NOREF = 1u << 12, XU_C_HASREF = 1u << 13
 };
 #define RFQ_XU_INFO (XU_ROW_NOREF | XU_ROW_HASREF | XU_C_NOREF | XU_C_HASREF)
 RFQ_HD bool xu_rows_by_position(uint32_t f) { return (f & XU_ROW_NOREF) && !(f & XU_ROW_HASREF); }
 RFQ_HD bool xu_cells_by_position(uint32_t f) { return (f & XU_C_NOREF) && !(f & XU_C_HASREF); }
-RFQ_HD bool xu_problem(uint32_t f) {
-  if (f & ~(uint32_t)RFQ_XU_INFO) return true;
-  if ((f & XU_ROW_NOREF) && (f & XU_ROW_HASREF)) return true;
-  return (f & XU_C_NOREF) && (f & XU_C_HASREF);
-}
+RFQ_HD bool xu_problem(uint32_t f) { return (f & ~(uint32_t)RFQ_XU_INFO) != 0; }
 
 struct XCell {
   uint32_t col;     // 1-based column
@@ -96,6 +93,7 @@ RFQ_HD uint32_t xlsx_row_number(const uint8_t* p, const uint8_t* e, uint32_t* fl
   if (vn > 9) { *flags |= XU_NO_REF; return 0; }
   uint32_t r = 0;
   for (uint32_t i = 0; i < vn; ++i) { uint32_t d = vb[i] - '0'; if (d > 9) { *flags |= XU_NO_REF; return 0; } r = r * 10 + d; }
+  if (r == 0) *flags |= XU_NO_REF;   // 0 is "no number yet" here
   return r;
 }
 

@@ -135,12 +135,25 @@ __global__ void __launch_bounds__(128) xrow_kernel(XmlArgs a) {
   if (flags) atomicOr(&a.shape[d].flags, flags);
 }
 
-// rows of a part that never writes r= are numbered by position (row_counter += 1)
+// rows without r= continue the count of the row before them (openpyxl worksheet/_reader.py parse_row:
+// row_counter = int(r) when r= is there, else row_counter += 1).  A part that never writes r= is numbered
+// by position; in a part that writes it on SOME rows a row walks back to the nearest row that has one
+// (a number other than 0 is final: either it was read from r= or another thread of this kernel derived it).
+#define RFQ_XROW_WALK 4096u
 __global__ void __launch_bounds__(128) xrow_fix_kernel(XmlArgs a) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= a.n_rows) return;
   uint32_t d = x_find(a.row_base, a.n_docs + 1, i);
-  if (xu_rows_by_position(a.shape[d].flags)) a.rownum[i] = i - a.row_base[d] + 1;
+  const uint32_t fl = a.shape[d].flags, rb = a.row_base[d];
+  if (xu_rows_by_position(fl)) { a.rownum[i] = i - rb + 1; return; }
+  if (!(fl & XU_ROW_NOREF)) return;
+  volatile uint32_t* rn = a.rownum;
+  if (rn[i] != 0) return;
+  uint32_t j = i, steps = 0;
+  while (j > rb && rn[j - 1] == 0 && steps < RFQ_XROW_WALK) { --j; ++steps; }
+  if (steps >= RFQ_XROW_WALK) { atomicOr(&a.shape[d].flags, XU_ORDER); return; }   // a run this long: declined, not crawled
+  const uint32_t before = j > rb ? rn[j - 1] : 0u;     // the counter starts at 0
+  rn[i] = before + (i - j) + 1;
 }
 
 // ---- cells ----------------------------------------------------------------------------------------
@@ -165,12 +178,48 @@ __global__ void __launch_bounds__(128) xcell_kernel(XmlArgs a) {
   if (e == 0xFFFFFFFFu) { flags |= XU_ORDER; e = rb; nr = 0; }   // a <c> before any <row> of its document
   uint32_t r = nr ? a.rownum[e] : 0;
   if (e > rb && a.rownum[e - 1] >= r) flags |= XU_ORDER;
-  if ((flags & XU_C_NOREF) && nr) x.col = k - a.row_c0[e] + 1;   // col_counter += 1 from the row start
+  if ((flags & XU_C_NOREF) && nr) x.col = k - a.row_c0[e] + 1;   // col_counter += 1 from the row start (xcell_fix_kernel
+                                                                 // corrects it when an earlier cell of the row has r=)
   ((XCell*)a.xcells)[k] = x;
   if (flags) atomicOr(&a.shape[d].flags, flags);
   if (!xcell_is_empty(x) && r >= 1 && r <= a.cap_rows[d]) {
     if (x.col > a.shape[d].W) atomicMax(&a.shape[d].W, x.col);
     if (r > a.shape[d].lastrow) atomicMax(&a.shape[d].lastrow, r);
+  }
+}
+
+// cells without r= in a part that writes r= on SOME cells: col_counter += 1 from the nearest earlier cell of
+// the row that has one (openpyxl worksheet/_reader.py parse_cell).  Columns taken from r= are final.
+__device__ __forceinline__ bool xcell_has_ref(const uint8_t* doc, uint32_t len, uint32_t cpos) {
+  const uint8_t* p = doc + cpos;
+  const uint8_t* e = doc + len;
+  const uint8_t* g = find_byte(p, e, '>');
+  if (g >= e) return false;
+  XAttrRTS at;
+  xml_attrs_rts(p, g, &at);
+  return (at.have & 1u) && at.vn[0] != 0;
+}
+__global__ void __launch_bounds__(128) xcell_fix_kernel(XmlArgs a) {
+  uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= a.n_cells) return;
+  const uint32_t d = a.cell_doc[k];
+  const uint32_t fl = a.shape[d].flags;
+  if (!((fl & XU_C_NOREF) && (fl & XU_C_HASREF)) || (fl & ~(uint32_t)RFQ_XU_INFO)) return;
+  const uint32_t e = a.cell_row[k];
+  if (e == 0xFFFFFFFFu) return;
+  const uint8_t* doc = a.arena + a.doc_off[d];
+  const uint32_t len = a.doc_len[d];
+  if (xcell_has_ref(doc, len, a.cpos[k])) return;
+  XCell* xc = (XCell*)a.xcells;
+  const uint32_t c0 = a.row_c0[e];
+  for (uint32_t j = k; j > c0; --j) {
+    if (xcell_has_ref(doc, len, a.cpos[j - 1])) {
+      const uint32_t col = xc[j - 1].col + (k - (j - 1));
+      xc[k].col = col;
+      const uint32_t r = a.rownum[e];
+      if (!xcell_is_empty(xc[k]) && r >= 1 && r <= a.cap_rows[d] && col > a.shape[d].W) atomicMax(&a.shape[d].W, col);
+      return;
+    }
   }
 }
 
@@ -230,6 +279,13 @@ __global__ void __launch_bounds__(128) xheader_kernel(TableArgs a, uint8_t* __re
     if (iv < 0) o[0] = '-';
   }
   else if (s.mode == CM_BOOL) { const char* w = (s.bits & 1) ? "True" : "False"; while (w[n]) { o[n] = (uint8_t)w[n]; ++n; } }
+  else if (s.mode == CM_FLOAT) {   // a float label of an object Index prints as f"{x: .6f}" with its zeros trimmed; the
+    const double v = bits_as_double(s.bits);   // host also needs repr(x): the bits travel behind the text
+    const Fixed6 f = fixed6(v);
+    if (f.big || f.inf || dbl_is_nan(v)) n = 0xFFFFFFFFu;
+    else n = (uint32_t)fixed_write(f, v, objfloat_dec(f), false, o);
+    for (int q = 0; q < 8; ++q) o[240 + q] = (uint8_t)(s.bits >> (8 * q));
+  }
   else if (s.mode == CM_DATE) n = pydatetime_write((int64_t)s.bits, o);   // str(label)
   else if (s.mode == CM_TIME) n = pytime_write((int64_t)s.bits, o);
   hdr_meta[2 * j] = s.mode;
@@ -325,6 +381,7 @@ void xml_decode(const XmlArgs& a, cudaStream_t s) {
   prof_mark("xcell_kernel", s);
   if (a.n_cells) {
     RFQ_LAUNCH(xcell_kernel, (a.n_cells + 127) / 128, 128, 0, s, a);
+    RFQ_LAUNCH(xcell_fix_kernel, (a.n_cells + 127) / 128, 128, 0, s, a);
     RFQ_LAUNCH(xcell_order_kernel, (a.n_cells + 127) / 128, 128, 0, s, a);
   }
   prof_mark("host+sync", s);

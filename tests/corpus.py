@@ -636,6 +636,16 @@ def strip_refs(sheet_xml: bytes, rows: bool = True, cells: bool = True) -> bytes
     return s
 
 
+def strip_refs_partial(sheet_xml: bytes, seed: int, p_row: float = 0.4, p_cell: float = 0.4) -> bytes:
+    """The same worksheet with r= removed from a random subset of its rows and cells (a writer that
+    only states a reference where the position jumps): an element without r= continues the count of
+    the element before it (openpyxl worksheet/_reader.py parse_row / parse_cell)."""
+    import re
+    r = random.Random(seed)
+    s = re.sub(rb'<row r="\d+"', lambda m: b"<row" if r.random() < p_row else m.group(0), sheet_xml)
+    return re.sub(rb'<c r="[A-Z]+\d+"', lambda m: b"<c" if r.random() < p_cell else m.group(0), s)
+
+
 # ------------------------------------------------------------------ .xlsx containers
 _WB_XML = ('<?xml version="1.0" encoding="UTF-8" standalone="yes"?>\n'
            '<workbook xmlns="http://schemas.openxmlformats.org/spreadsheetml/2006/main" '

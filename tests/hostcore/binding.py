@@ -131,3 +131,12 @@ def walk_stats():
     o = np.zeros(7, dtype=np.uint64)
     lib().hc_walk_stats(C.c_void_p(o.ctypes.data))
     return tuple(int(x) for x in o)
+
+
+def float_repr(v: float) -> str:
+    """py_float_repr of header_names.h (labels of sheet columns)."""
+    L = lib()
+    L.hc_float_repr.argtypes = [C.c_double, C.c_char_p]
+    buf = C.create_string_buffer(64)
+    n = L.hc_float_repr(v, buf)
+    return buf.raw[:n].decode()

@@ -442,6 +442,7 @@ int hc_csv_parse(const uint8_t* doc, uint64_t len, int64_t nrows, uint8_t* out, 
 #include "../../replisense_rfq_b200/csrc/xlsx_core.cuh"
 extern "C" {
 int hc_strtod(const uint8_t* s, uint32_t n, double* out) { return rfq::strtod_exact(s, n, out) ? 1 : 0; }
+int hc_float_repr(double v, char* out) { std::string t = rfq::py_float_repr(v); memcpy(out, t.data(), t.size()); return (int)t.size(); }
 int hc_xml_decode(const uint8_t* p, uint32_t n, uint8_t* out) {
   rfq::XmlIter it(p, n); int c, k = 0;
   while ((c = it.next()) >= 0) out[k++] = (uint8_t)c;
@@ -522,9 +523,16 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
     }
   }
   if (!rows.empty()) rows.back().c1 = (uint32_t)cells.size();
-  if (xu_rows_by_position(flags)) for (size_t k = 0; k < rows.size(); ++k) rows[k].r = (uint32_t)k + 1;
+  // elements without r= continue the count of the element before them (row_counter / col_counter)
+  if (flags & XU_ROW_NOREF) {
+    uint32_t counter = 0;
+    for (auto& R : rows) { if (R.r == 0) R.r = counter + 1; counter = R.r; }
+  }
   if (flags & XU_C_NOREF)
-    for (auto& R : rows) for (uint32_t k = R.c0; k < R.c1; ++k) if (cells[k].col == 0) cells[k].col = k - R.c0 + 1;
+    for (auto& R : rows) {
+      uint32_t counter = 0;
+      for (uint32_t k = R.c0; k < R.c1; ++k) { if (cells[k].col == 0) cells[k].col = counter + 1; counter = cells[k].col; }
+    }
   uint32_t cap_rows = (uint32_t)std::min<int64_t>(nrows, 0x7FFFFFF0) + 1;  // file_rows_needed
   uint32_t W = 0, lastrow = 0, prev_r = 0;
   for (auto& R : rows) {
@@ -559,11 +567,26 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
   std::vector<std::string> raw(W); std::vector<size_t> unnamed;
   bool all_int = true;
   std::vector<int> lkind(W, 0);
+  std::vector<std::string> ftext(W);
+  std::vector<uint8_t> no_blank(W, 0);
+  std::vector<double> lval(W, 0.0);
   for (uint32_t c = 0; c < W; ++c) {
     CellSrc s = cell(1, c);
     std::string nm;
-    if (s.mode == CM_FLOAT) return 2;  // float labels
-    lkind[c] = s.mode == CM_INT ? 1 : s.mode == CM_BOOL ? 2 : s.mode == CM_DATE ? 3 : s.mode == CM_TIME ? 4 : 0;
+    lkind[c] = s.mode == CM_INT ? 1 : s.mode == CM_BOOL ? 2 : s.mode == CM_DATE ? 3 : s.mode == CM_TIME ? 4
+               : s.mode == CM_FLOAT ? 5 : 0;
+    if (s.mode == CM_FLOAT) {   // float label: repr() as a name, f"{x: .6f}" trimmed when printed
+      const double v = bits_as_double(s.bits);
+      const Fixed6 f = fixed6(v);
+      if (f.big || f.inf || dbl_is_nan(v)) return 2;
+      uint8_t b[64];
+      const int n = fixed_write(f, v, objfloat_dec(f), false, b);
+      ftext[c].assign((const char*)b, n);
+      nm = py_float_repr(v);
+      lval[c] = v;
+    }
+    if (s.mode == CM_INT) lval[c] = (double)(long long)s.bits;
+    if (s.mode == CM_BOOL) lval[c] = (s.bits & 1) ? 1.0 : 0.0;
     if (s.mode == CM_BOOL) nm = (s.bits & 1) ? "True" : "False";
     if (s.mode == CM_DATE || s.mode == CM_TIME) {
       uint8_t b[32];
@@ -577,7 +600,8 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
     if (s.mode == CM_NULL) { nm = "Unnamed: " + std::to_string(c); unnamed.push_back(c); }
     raw[c] = nm;
   }
-  if (!sheet_labels_supported(lkind, raw)) return 2;
+  if (!sheet_labels_supported(lkind, raw, &lval)) return 2;
+  const std::vector<std::string> before = raw;
   {
     std::vector<size_t> order; std::vector<bool> un(W, false);
     for (size_t k : unnamed) un[k] = true;
@@ -613,7 +637,12 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
   bool names_valid = true;
   for (uint32_t c = 0; c < W; ++c) if (!utf8_valid_count(raw[c], &ncp[c])) names_valid = false;
   std::vector<std::string> disp = raw;
-  if (names_valid && !int_index) display_labels(raw, disp, ncp);
+  if (names_valid && !int_index) {
+    std::vector<std::string> shown = raw;
+    for (uint32_t c = 0; c < W; ++c)
+      if (lkind[c] == 5 && raw[c] == before[c]) { shown[c] = ftext[c]; no_blank[c] = ftext[c][0] == '-'; }
+    display_labels(shown, disp, ncp, &no_blank);
+  }
   // inference
   std::vector<uint32_t> xf(W, 0); std::vector<uint32_t> row_na(ndata, 0);
   for (uint32_t r = 0; r < ndata; ++r)

@@ -420,3 +420,77 @@ def test_scan_visits_only_what_matters():
     for d in docs:
         for sep in (44, 59, 9):
             assert L.hc_visit_check(d, len(d), sep) == 0, (d, sep)
+
+
+def test_float_repr_matches_python():
+    """Float column labels keep repr(label) as their name (header_names.h py_float_repr)."""
+    import random
+    import struct
+    r = random.Random(11)
+    vals = [0.0, -0.0, 1.0, 4.5, -4.5, 2024.0, 0.1, 1e15, 1e16, 123456789012345678.0, 1e-4, 9.999e-5, 1e-5, 5e-324,
+            1.7976931348623157e308, 0.30000000000000004, 1234567.891, 1e22, 1.5e300, -2.5e-7, 1 / 3]
+    vals += [r.uniform(-1, 1) * 10 ** r.randint(-20, 20) for _ in range(3000)]
+    vals += [round(r.uniform(0, 1e6), r.randint(0, 6)) for _ in range(3000)]
+    vals += [struct.unpack("<d", struct.pack("<Q", r.getrandbits(64)))[0] for _ in range(3000)]
+    for v in vals:
+        if v != v or v in (float("inf"), float("-inf")):
+            continue
+        assert H.float_repr(v) == repr(v), (v, H.float_repr(v))
+
+
+def _label_sheet(labels, rows=2):
+    """A small sheet whose first row holds the given label cells (already XML), then numeric rows."""
+    out = [corpus._XML_HEAD, '<row r="1">']
+    for c, cell in enumerate(labels):
+        out.append(cell.replace("REF", "%s1" % corpus.col_letters(c)))
+    out.append("</row>")
+    for i in range(rows):
+        out.append('<row r="%d">' % (i + 2))
+        for c in range(len(labels)):
+            out.append('<c r="%s%d"><v>%d</v></c>' % (corpus.col_letters(c), i + 2, 10 * i + c))
+        out.append("</row>")
+    out.append(corpus._XML_TAIL)
+    sst = ('<sst xmlns="http://schemas.openxmlformats.org/spreadsheetml/2006/main"><si><t>Part</t></si>'
+           '<si><t>  lead</t></si><si><t>4.5</t></si></sst>')
+    return "".join(out).encode(), sst.encode()
+
+
+def test_sheet_model_float_labels():
+    """Float labels next to string labels (an object Index): printed through the float formatter, named by
+    repr(); a negative one keeps every other label's blank; all-numeric headers stay declined."""
+    S = lambda i: '<c r="REF" t="s"><v>%d</v></c>' % i
+    F = lambda v: '<c r="REF"><v>%s</v></c>' % v
+    cases = [[S(0), F("4.5")], [S(0), F("4.5"), F("4.5")], [S(0), F("-4.5"), F("0.1234567")], [S(1), F("2024.0")],
+             [S(0), F("1e-7"), F("123456.7890123")], [S(0), F("4.5"), S(2)], [S(0), F("7.25"), '<c r="REF"><v>7</v></c>'],
+             [S(0), F("1e5"), '<c r="REF" t="b"><v>1</v></c>']]
+    for labels in cases:
+        sx, ss = _label_sheet(labels)
+        st, got = H.sheet_parse(sx, ss)
+        want = _sheet_oracle(sx, ss)
+        if st == 2:
+            continue
+        assert got == want, (labels, got, want)
+    # the common ones must be decoded, not declined
+    for labels in cases[:5]:
+        sx, ss = _label_sheet(labels)
+        assert H.sheet_parse(sx, ss)[0] == 0, labels
+    sx, ss = _label_sheet([F("4.5"), '<c r="REF"><v>7</v></c>'])
+    assert H.sheet_parse(sx, ss)[0] == 2      # int + float labels: a Float64 Index, formatted as a whole
+
+
+def test_sheet_model_partial_refs_vs_oracle():
+    """Worksheets that write r= on SOME rows / cells: the others continue the count (row_counter /
+    col_counter of openpyxl's reader).  Dense sheets keep their shape; sparse ones shift, and whatever
+    results is what the oracle reads too.  Non-increasing numbers stay declined."""
+    bad, unsup = [], 0
+    for seed in range(300):
+        sx, ss = corpus.sheet_xml_fuzz(seed) if seed % 3 == 0 else corpus.sheet_xml_doc(seed, 5, 60)
+        sx = corpus.strip_refs_partial(sx, seed, 0.0 if seed % 5 == 1 else 0.4, 0.0 if seed % 5 == 2 else 0.4)
+        st, got = H.sheet_parse(sx, ss)
+        if st == 2:
+            unsup += 1
+            continue
+        if (None if st == 3 else got) != _sheet_oracle(sx, ss):
+            bad.append(seed)
+    assert not bad, bad
+    assert unsup < 30

@@ -118,7 +118,7 @@ def test_sheet_fuzz(eng):
         if (None if st == 3 else g) != _oracle(sx, ss):
             bad.append(i)
     assert not bad, bad[:10]
-    assert unsup < 0.2 * len(pairs)
+    assert unsup <= 0.02 * len(pairs)
 
 
 def test_sheet_nrows_cap(eng):
@@ -215,4 +215,56 @@ def test_sheet_without_refs(eng):
         if (None if st == 3 else g) != _oracle(sx, ss):
             bad.append(i)
     assert not bad, bad[:10]
-    assert unsup < 0.15 * len(pairs)
+    assert unsup <= 0.02 * len(pairs)
+
+
+def test_sheet_with_partial_refs(eng):
+    """Writers that state r= only on SOME rows / cells: an element without it continues the count of the
+    element before it (openpyxl worksheet/_reader.py parse_row / parse_cell: row_counter, col_counter)."""
+    pairs = []
+    for seed in range(300):
+        sx, ss = corpus.sheet_xml_fuzz(seed) if seed % 3 == 0 else corpus.sheet_xml_doc(seed, 5, 60)
+        pairs.append((corpus.strip_refs_partial(sx, seed, 0.0 if seed % 5 == 1 else 0.4, 0.0 if seed % 5 == 2 else 0.4), ss))
+    got = _batch(eng, pairs)
+    bad, unsup = [], 0
+    for i, ((st, g), (sx, ss)) in enumerate(zip(got, pairs)):
+        if st == 2:
+            unsup += 1
+            continue
+        if (None if st == 3 else g) != _oracle(sx, ss):
+            bad.append(i)
+    assert not bad, bad[:10]
+    assert unsup <= 0.02 * len(pairs)
+
+
+def test_sheet_float_labels(eng):
+    """Float column labels next to string labels (an object Index): named by repr(label), printed as
+    f"{x: .6f}" with the zeros trimmed (pandas format.py _GenericArrayFormatter), a negative one keeps the
+    other labels' blank; int + float labels (a Float64 Index) stay declined."""
+    S = lambda i: '<c r="REF" t="s"><v>%d</v></c>' % i
+    F = lambda v: '<c r="REF"><v>%s</v></c>' % v
+    sst = ('<sst xmlns="http://schemas.openxmlformats.org/spreadsheetml/2006/main"><si><t>Part</t></si>'
+           '<si><t>  lead</t></si><si><t>4.5</t></si></sst>').encode()
+
+    def sheet(labels):
+        out = [corpus._XML_HEAD, '<row r="1">']
+        out += [c.replace("REF", "%s1" % corpus.col_letters(k)) for k, c in enumerate(labels)]
+        out.append("</row>")
+        for i in range(3):
+            out.append('<row r="%d">' % (i + 2))
+            out += ['<c r="%s%d"><v>%d</v></c>' % (corpus.col_letters(k), i + 2, 10 * i + k) for k in range(len(labels))]
+            out.append("</row>")
+        out.append(corpus._XML_TAIL)
+        return "".join(out).encode()
+    cases = [[S(0), F("4.5")], [S(0), F("4.5"), F("4.5")], [S(0), F("-4.5"), F("0.1234567")], [S(1), F("2024.0")],
+             [S(0), F("1e-7"), F("123456.7890123")], [S(0), F("4.5"), S(2)], [S(0), F("7.25"), '<c r="REF"><v>7</v></c>'],
+             [S(0), F("1e5"), '<c r="REF" t="b"><v>1</v></c>'], [F("4.5"), '<c r="REF"><v>7</v></c>']]
+    pairs = [(sheet(c), sst) for c in cases]
+    got = _batch(eng, pairs)
+    for i, ((st, g), (sx, ss)) in enumerate(zip(got, pairs)):
+        if i < 5:
+            assert st == 0, i
+        if i == len(cases) - 1:
+            assert st == 2
+        if st != 2:
+            assert g == _oracle(sx, ss), i

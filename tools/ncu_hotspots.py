@@ -34,5 +34,5 @@ ti = sum(a[0] for a in agg.values()) or 1
 ts = sum(a[1] for a in agg.values()) or 1
 tt = sum(a[2] for a in agg.values())
 print("tot warp inst", ti, "avg active %.1f" % (tt / ti), "samples", ts)
-for k, a in sorted(agg.items(), key=lambda x: -x[1][0])[:int(sys.argv[3]) if len(sys.argv) > 3 else 30]:
+for k, a in sorted(agg.items(), key=lambda x: -x[1][1 if "--by-samples" in sys.argv else 0])[:int(sys.argv[3]) if len(sys.argv) > 3 else 30]:
     print("%5.1f%% inst %5.1f%% smp act %4.1f %-16s:%4d  %s" % (100 * a[0] / ti, 100 * a[1] / ts, a[2] / max(a[0], 1), k[0], k[1], k[2]))
