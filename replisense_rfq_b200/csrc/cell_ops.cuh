@@ -16,7 +16,8 @@ namespace rfq {
 // CM_CSVQ: inside of a quoted CSV field that is clean ASCII and whose only quotes are "" pairs
 // (span = between the outer quotes, bits = decoded length)
 enum { CM_CSV = 0, CM_RAW = 1, CM_INT = 2, CM_FLOAT = 3, CM_BOOL = 4, CM_XML = 5, CM_NULL = 6, CM_CSVQ = 7,
-       CM_DATE = 8, CM_TIME = 9 };   // sheet cells: ms since 0001-01-01 / ms of the day (datetime_fmt.cuh)
+       CM_DATE = 8, CM_TIME = 9,     // sheet cells: ms since 0001-01-01 / ms of the day (datetime_fmt.cuh)
+       CM_TDELTA = 10 };             // a timedelta-styled number: signed microseconds
 
 // decoded bytes of a CM_CSVQ span: every "" is one "
 struct PairIter {
@@ -314,6 +315,7 @@ RFQ_HD int cell_own_ctype(const CellSrc& s) {
     case CM_BOOL: return CT_BOOL;
     case CM_DATE: return CT_DATE;
     case CM_TIME: return CT_TIME;
+    case CM_TDELTA: return CT_TDELTA;
     default: return CT_STR;
   }
 }
@@ -421,6 +423,13 @@ RFQ_HD CellMeasure measure_cell(const CellSrc& s, int ctype) {
   }
   if (ctype == CT_BOOL || ctype == CT_BOOLNA) {
     m.plain_len = cell_bool(s, t) == 1 ? 4 : 5;
+    return m;
+  }
+  if (ctype == CT_TDELTA) {   // ip_len / obj_len of a float are free here: the two timedelta64 forms
+    const int64_t us = (int64_t)s.bits;
+    m.plain_len = pytd_len(us);
+    if (!xobj) { m.ip_len = td64_len(us, 0); m.obj_len = td64_len(us, 1); }   // (a mixed object column prints str(td))
+    m.fl = MF_FINITE | ((us % RFQ_US_PER_DAY) ? MF_DT_TIME : 0);
     return m;
   }
   if (ctype == CT_DATE || ctype == CT_TIME) {
@@ -570,7 +579,9 @@ RFQ_HD CellCand classify_measure_cell(const CellSrc& s) {
 // ---- 3. print -----------------------------------------------------------------------------------
 // How a cell prints given the class of its column and the type of its chunk.
 enum { PR_EMPTY = 0, PR_INT, PR_UINT, PR_FIXED, PR_SCI, PR_OBJFLOAT, PR_BOOL, PR_STR, PR_PYINT,
-       PR_DATE64, PR_DATETIME, PR_TIME };   // datetime64 column (dec = resolution) / str(datetime) / str(time)
+       PR_DATE64, PR_DATETIME, PR_TIME,     // datetime64 column (dec = resolution) / str(datetime) / str(time)
+       PR_TD64, PR_PYTD };                  // timedelta64 column (dec = 0 whole days, 1 long form) / str(timedelta)
+RFQ_HD bool pr_prints_nat(int kind) { return kind == PR_DATE64 || kind == PR_TD64; }
 
 RFQ_HD int print_kind(int cls, int ctype, bool sci) {
   switch (cls) {
@@ -581,6 +592,7 @@ RFQ_HD int print_kind(int cls, int ctype, bool sci) {
     case CC_STR: return PR_STR;
     case CC_OBJF: return PR_OBJFLOAT;
     case CC_DATE: return PR_DATE64;
+    case CC_TDELTA: return PR_TD64;
     default:
       switch (ctype) {
         case CT_INT: return PR_INT;
@@ -590,6 +602,7 @@ RFQ_HD int print_kind(int cls, int ctype, bool sci) {
         case CT_PYINT: return PR_PYINT;
         case CT_DATE: return PR_DATETIME;
         case CT_TIME: return PR_TIME;
+        case CT_TDELTA: return PR_PYTD;
         default: return PR_STR;
       }
   }
@@ -600,12 +613,14 @@ RFQ_HD void printed_size(const CellSrc& s, int ctype, int kind, int dec, uint32_
                          uint32_t* nbytes) {
   *ncp = 0; *nbytes = 0;
   TextInfo t = cell_text(s);
-  if (cell_is_nan(s, t, ctype)) { if (kind == PR_DATE64) { *ncp = 3; *nbytes = 3; } return; }   // NaT
+  if (cell_is_nan(s, t, ctype)) { if (pr_prints_nat(kind)) { *ncp = 3; *nbytes = 3; } return; }   // NaT
   uint32_t n = 0;
   switch (kind) {
     case PR_DATE64: n = date64_len(dec); break;
     case PR_DATETIME: n = pydatetime_len((int64_t)s.bits); break;
     case PR_TIME: n = pytime_len((int64_t)s.bits); break;
+    case PR_TD64: n = td64_len((int64_t)s.bits, dec); break;
+    case PR_PYTD: n = pytd_len((int64_t)s.bits); break;
     case PR_STR: *ncp = t.ncp + t.nesc; *nbytes = t.nbytes + t.nesc; return;
     case PR_BOOL: n = cell_bool(s, t) == 1 ? 4 : 5; break;
     case PR_INT: { int64_t iv = 0; cell_int64(s, &iv); n = (uint32_t)int64_len(iv); break; }
@@ -668,7 +683,7 @@ RFQ_HD uint32_t print_cell(const CellSrc& s, int ctype, int kind, int dec, uint8
   }
   TextInfo t = cell_text(s);
   if (cell_is_nan(s, t, ctype)) {
-    if (kind != PR_DATE64) return 0;
+    if (!pr_prints_nat(kind)) return 0;
     out[0] = 'N'; out[1] = 'a'; out[2] = 'T';
     return 3;
   }
@@ -676,6 +691,8 @@ RFQ_HD uint32_t print_cell(const CellSrc& s, int ctype, int kind, int dec, uint8
     case PR_DATE64: return date64_write((int64_t)s.bits, dec, out);
     case PR_DATETIME: return pydatetime_write((int64_t)s.bits, out);
     case PR_TIME: return pytime_write((int64_t)s.bits, out);
+    case PR_TD64: return td64_write((int64_t)s.bits, dec, out);
+    case PR_PYTD: return pytd_write((int64_t)s.bits, out);
     case PR_BOOL: {
       const char* w = cell_bool(s, t) == 1 ? "True" : "False";
       uint32_t k = 0;

@@ -27,13 +27,14 @@ enum {
   CT_XOBJ = 9,    // sheet column of mixed Python objects: every cell prints as its own type
   CT_DATE = 11,   // sheet column whose non-blank cells are all datetimes: datetime64, blanks NaT
   CT_TIME = 12,   // (cell level only) a datetime.time inside a mixed object column
+  CT_TDELTA = 13, // sheet column whose non-blank cells are all timedeltas: timedelta64, blanks NaT
   CT_PYINT = 10   // object column of Python ints (a value beyond uint64 / a negative next to an overflow):
                   // every token is int()-parsable and prints as str(int(token)); NA -> NaN
 };
 
 // printing class of a whole column
 // CC_OBJF: float64 column with holes after fillna('') -> object column whose cells are all floats
-enum { CC_INT = 0, CC_UINT = 1, CC_FLOAT = 2, CC_BOOL = 3, CC_STR = 4, CC_OBJ = 5, CC_OBJF = 6, CC_UNSUP = 7, CC_DATE = 8 };
+enum { CC_INT = 0, CC_UINT = 1, CC_FLOAT = 2, CC_BOOL = 3, CC_STR = 4, CC_OBJ = 5, CC_OBJF = 6, CC_UNSUP = 7, CC_DATE = 8, CC_TDELTA = 9 };
 
 // per (chunk, column) classification flags, OR-reduced over the cells
 enum {
@@ -97,7 +98,7 @@ RFQ_HD uint32_t chunk_rows_for_width(uint32_t width) {
 RFQ_HD int fold_column_class(const uint8_t* ctypes, uint32_t n_chunks, uint32_t stride,
                              bool any_nan_left) {
   bool all_int = true, all_uint = true, all_num = true, all_bool = true, all_str = true;
-  bool unsup = false, any_uint = false, all_date = true;
+  bool unsup = false, any_uint = false, all_date = true, all_td = true;
   for (uint32_t k = 0; k < n_chunks; ++k) {
     int t = ctypes[(size_t)k * stride];
     if (t == CT_UNSUP) unsup = true;
@@ -108,6 +109,7 @@ RFQ_HD int fold_column_class(const uint8_t* ctypes, uint32_t n_chunks, uint32_t 
     if (t != CT_BOOL) all_bool = false;
     if (t != CT_STR) all_str = false;
     if (t != CT_DATE) all_date = false;
+    if (t != CT_TDELTA) all_td = false;
   }
   if (unsup) return CC_UNSUP;
   if (n_chunks == 0) return CC_OBJ;  // no data rows: dtype object, prints nothing
@@ -118,6 +120,7 @@ RFQ_HD int fold_column_class(const uint8_t* ctypes, uint32_t n_chunks, uint32_t 
   if (all_bool) return CC_BOOL;
   if (all_str) return CC_STR;
   if (all_date) return CC_DATE;
+  if (all_td) return CC_TDELTA;
   return CC_OBJ;
 }
 
@@ -213,6 +216,17 @@ RFQ_HD ColumnLayout layout_column(int cls, const ChunkMeasure* m, const uint8_t*
     for (uint32_t k = 0; k < n_chunks; ++k) { fl |= m[(size_t)k * stride].fl; nat |= m[(size_t)k * stride].nan_left; }
     L.dec = (fl & MF_DT_MS) ? 2 : (fl & MF_DT_TIME) ? 1 : 0;
     w = (fl & MF_FINITE) ? (L.dec == 0 ? 10u : L.dec == 1 ? 19u : 23u) : (nat ? 3u : 0u);
+  } else if (cls == CC_TDELTA) {
+    // "{days} days" when every value is whole days, else the long form per value (NaT never sets the width)
+    uint32_t fl = 0, nat = 0;
+    for (uint32_t k = 0; k < n_chunks; ++k) { fl |= m[(size_t)k * stride].fl; nat |= m[(size_t)k * stride].nan_left; }
+    L.dec = (fl & MF_DT_TIME) ? 1 : 0;
+    for (uint32_t k = 0; k < n_chunks; ++k) {
+      const uint32_t l = L.dec ? m[(size_t)k * stride].obj_len : m[(size_t)k * stride].ip_len;
+      if (l > w) w = l;
+    }
+    if (!(fl & MF_FINITE)) w = nat ? 3u : 0u;
+    else if (nat && w < 3u) w = 3u;
   } else if (cls == CC_STR) {
     for (uint32_t k = 0; k < n_chunks; ++k)
       if (m[(size_t)k * stride].plain_len > w) w = m[(size_t)k * stride].plain_len;

@@ -40,7 +40,7 @@ __device__ __noinline__ SizeRes printed_size_cold(CellSrc s, int ct, int kind, i
   return r;
 }
 __device__ __forceinline__ void put_nat(int kind, uint32_t width, uint8_t* field) {
-  if (kind == PR_DATE64) { field[width - 3] = 'N'; field[width - 2] = 'a'; field[width - 1] = 'T'; }
+  if (pr_prints_nat(kind)) { field[width - 3] = 'N'; field[width - 2] = 'a'; field[width - 1] = 'T'; }
 }
 // any cell, any kind; returns printed bytes - printed code points
 // (arguments by value: a reference would pin the caller's copy to local memory)
@@ -123,6 +123,8 @@ __device__ __forceinline__ int format_number(const CellSrc& s, int ct, int kind,
     case PR_DATE64: return (int)date64_write((int64_t)s.bits, dec, buf);
     case PR_DATETIME: return (int)pydatetime_write((int64_t)s.bits, buf);
     case PR_TIME: return (int)pytime_write((int64_t)s.bits, buf);
+    case PR_TD64: return (int)td64_write((int64_t)s.bits, dec, buf);
+    case PR_PYTD: return (int)pytd_write((int64_t)s.bits, buf);
     default: return -1;   // PR_PYINT: arbitrary length, measured and written in place
   }
 }

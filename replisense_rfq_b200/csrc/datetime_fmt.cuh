@@ -155,4 +155,87 @@ RFQ_HD uint32_t pytime_write(int64_t ms, uint8_t* o) {
   return k;
 }
 
+// ---- timedelta-styled numbers ([h]:mm:ss and friends) ----------------------------------------------
+// from_excel(value, timedelta=True) of openpyxl 3.1 (utils/datetime.py):
+//     td = datetime.timedelta(days=value)
+//     if td.microseconds: td = timedelta(seconds=td.total_seconds() // 1, microseconds=round(td.microseconds, -3))
+// over CPython's timedelta arithmetic (Modules/_datetimemodule.c accum(): the whole days are exact, the
+// fraction is ONE double product frac * 86400e6 rounded half-even to a whole microsecond).  Accepted:
+// |value| < 150 000 days: total_seconds() is the correctly rounded double of an exact quotient whose
+// fraction is at most 0.999999, and below 2^34 seconds that rounding cannot reach the next whole second,
+// so its floor is the exact integer floor taken here; anything longer is declined by the caller.
+#define RFQ_US_PER_DAY 86400000000ll
+RFQ_HD bool excel_to_timedelta(double value, int64_t* us_out) {
+  if (!(value > -150000.0 && value < 150000.0)) return false;
+  double ip;
+  const double fr = modf(value, &ip);
+  int64_t total = (int64_t)ip * RFQ_US_PER_DAY + rfq_rint_ll(RFQ_DMUL(fr, 86400000000.0));
+  int64_t us = total % 1000000ll;
+  if (us < 0) us += 1000000ll;
+  if (us) {
+    const int64_t w = (total - us) / 1000000ll;                    // total_seconds() // 1 (floor: us >= 0)
+    const int64_t r = us % 1000ll;
+    int64_t base = us - r;                                         // round(us, -3): half to even
+    if (r > 500 || (r == 500 && ((base / 1000ll) & 1ll))) base += 1000ll;
+    total = w * 1000000ll + base;
+  }
+  *us_out = total;
+  return true;
+}
+// (days, seconds of the day, microseconds) with 0 <= seconds < 86400, 0 <= us < 1e6 (floor division)
+struct TdParts { int64_t days; int h, mi, s; int us; };
+RFQ_HD TdParts td_parts(int64_t total) {
+  TdParts p;
+  int64_t d = total / RFQ_US_PER_DAY, rem = total % RFQ_US_PER_DAY;
+  if (rem < 0) { rem += RFQ_US_PER_DAY; d -= 1; }
+  p.days = d;
+  p.us = (int)(rem % 1000000ll);
+  const int sec = (int)(rem / 1000000ll);
+  p.h = sec / 3600; p.mi = (sec / 60) % 60; p.s = sec % 60;
+  return p;
+}
+RFQ_HD uint32_t put_i64(uint8_t* o, int64_t v) {   // decimal digits with a '-' for negatives; returns the length
+  uint8_t tmp[24];
+  uint32_t n = 0;
+  uint64_t m = v < 0 ? 0ull - (uint64_t)v : (uint64_t)v;
+  do { tmp[n++] = (uint8_t)('0' + m % 10); m /= 10; } while (m);
+  uint32_t k = 0;
+  if (v < 0) o[k++] = '-';
+  while (n) o[k++] = tmp[--n];
+  return k;
+}
+RFQ_HD uint32_t put_us6(uint8_t* o, int us) { for (int q = 5; q >= 0; --q) { o[q] = (uint8_t)('0' + us % 10); us /= 10; } return 6; }
+// A timedelta64 column as to_string prints it (pandas/io/formats/format.py get_format_timedelta64 ->
+// Timedelta._repr_base): res 0 = every value of the column is whole days -> "{days} days"; res 1 =
+// "{days} days HH:MM:SS" (" +" before the hours of a negative one), ".ffffff" where THIS value has a
+// fraction of a second.
+RFQ_HD uint32_t td64_write(int64_t total, int res, uint8_t* o) {
+  const TdParts p = td_parts(total);
+  uint32_t k = put_i64(o, p.days);
+  o[k++] = ' '; o[k++] = 'd'; o[k++] = 'a'; o[k++] = 'y'; o[k++] = 's';
+  if (res == 0) return k;
+  o[k++] = ' ';
+  if (p.days < 0) o[k++] = '+';
+  put2(o + k, p.h); o[k + 2] = ':'; put2(o + k + 3, p.mi); o[k + 5] = ':'; put2(o + k + 6, p.s); k += 8;
+  if (p.us) { o[k++] = '.'; k += put_us6(o + k, p.us); }
+  return k;
+}
+RFQ_HD uint32_t td64_len(int64_t total, int res) { uint8_t b[48]; return td64_write(total, res, b); }
+// str(datetime.timedelta): "[D day[s], ]H:MM:SS[.ffffff]" — what an object column or a label prints
+RFQ_HD uint32_t pytd_write(int64_t total, uint8_t* o) {
+  const TdParts p = td_parts(total);
+  uint32_t k = 0;
+  if (p.days) {
+    k = put_i64(o, p.days);
+    o[k++] = ' '; o[k++] = 'd'; o[k++] = 'a'; o[k++] = 'y';
+    if (p.days != 1 && p.days != -1) o[k++] = 's';
+    o[k++] = ','; o[k++] = ' ';
+  }
+  k += put_i64(o + k, p.h);
+  o[k++] = ':'; put2(o + k, p.mi); k += 2; o[k++] = ':'; put2(o + k, p.s); k += 2;
+  if (p.us) { o[k++] = '.'; k += put_us6(o + k, p.us); }
+  return k;
+}
+RFQ_HD uint32_t pytd_len(int64_t total) { uint8_t b[48]; return pytd_write(total, b); }
+
 }  // namespace rfq

@@ -265,7 +265,7 @@ inline HeaderInfo parse_header(const uint8_t* doc, uint64_t len, uint32_t sep, b
 
 // Header row of a sheet: labels keep their Python type (pandas/io/parsers/python_parser.py
 // _infer_columns).  kind per label: 0 str (or blank -> "Unnamed: k"), 1 int, 2 bool, 3 datetime,
-// 4 time, 5 float (text = repr(label)), anything else = a type whose Index formatting is not restated
+// 4 time, 5 float (text = repr(label)), 6 timedelta (alone: a TimedeltaIndex), anything else = a type whose Index formatting is not restated
 // (NaN).  `value` = the number behind an int / bool / float label.
 // Supported: all labels int (an Int64 Index), or an object Index — labels of two type families or more,
 // any str, any time: every label prints as str(label), a float as f"{x: .6f}" with its zeros trimmed
@@ -281,7 +281,8 @@ inline bool sheet_labels_supported(const std::vector<int>& kind, const std::vect
   for (size_t i = 0; i < kind.size(); ++i) {
     const int k = kind[i];
     if (k == 0) fam |= 1u; else if (k == 1) fam |= 2u; else if (k == 5) { fam |= 2u; has_float = true; }
-    else if (k == 2) fam |= 4u; else if (k == 3) fam |= 8u; else if (k == 4) fam |= 16u; else return false;
+    else if (k == 2) fam |= 4u; else if (k == 3) fam |= 8u; else if (k == 4) fam |= 16u; else if (k == 6) fam |= 32u;
+    else return false;
   }
   const bool all_int = fam == 2u && !has_float;
   const bool object_index = (fam & 1u) || (fam & 16u) || (fam & (fam - 1u)) != 0;

@@ -220,7 +220,7 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
         uint32_t g = T.col_base + j, mode = h_hmeta[2 * g], len = h_hmeta[2 * g + 1];
         if (mode != CM_INT) all_int = false;
         lkind[j] = mode == CM_INT ? 1 : mode == CM_BOOL ? 2 : mode == CM_DATE ? 3 : mode == CM_TIME ? 4
-                   : mode == CM_FLOAT ? 5 : (mode == CM_RAW || mode == CM_XML || mode == CM_NULL) ? 0 : 9;
+                   : mode == CM_FLOAT ? 5 : mode == CM_TDELTA ? 6 : (mode == CM_RAW || mode == CM_XML || mode == CM_NULL) ? 0 : 9;
         if (mode == CM_NULL) { raw[j] = "Unnamed: " + std::to_string(j); unnamed.push_back(j); }
         else if (lkind[j] == 5 && len != 0xFFFFFFFFu && len <= 200) {
           double v;

@@ -113,6 +113,17 @@ RFQ_HD XCell xlsx_date_cell(XCell x, double v, bool date1904, uint32_t* flags) {
   return x;
 }
 
+// a timedelta-styled number: from_excel(value, timedelta=True); beyond the range the conversion is exact
+// for (datetime_fmt.cuh excel_to_timedelta) the sheet is declined
+RFQ_HD XCell xlsx_timedelta_cell(XCell x, double v, bool exact, uint32_t* flags) {
+  int64_t us;
+  // timedelta(days=v) beyond 999 999 999 days: OverflowError -> openpyxl's '#VALUE!' error cell -> NaN
+  if (v >= 1.0e9 || v <= -1.0e9) { x.mode = CM_FLOAT; x.bits = 0x7FF8000000000000ull; return x; }
+  if (!exact || !excel_to_timedelta(v, &us)) { *flags |= XU_DATE; return x; }
+  x.mode = CM_TDELTA; x.bits = (uint64_t)us;
+  return x;
+}
+
 // ---- <c ...>...</c> -----------------------------------------------------------------------------
 // doc/len: the sheet part; cpos: offset of "<c". date_ids: sorted style ids that are dates.
 RFQ_HD XCell xlsx_parse_cell(const uint8_t* doc, uint32_t len, uint32_t cpos, const SstView& sst,
@@ -179,18 +190,19 @@ RFQ_HD XCell xlsx_parse_cell(const uint8_t* doc, uint32_t len, uint32_t cpos, co
       int dstyle = 0;
       for (uint32_t i = 0; i < n_date; ++i)
         if ((date_ids[i] & 0x7FFFFFFFu) == style) dstyle = (date_ids[i] >> 31) ? 2 : 1;
-      if (dstyle == 2) { *flags |= XU_DATE; return x; }
       bool is_float = false;
       for (uint32_t i = 0; i < val_n; ++i) if (val_b[i] == '.' || val_b[i] == 'e' || val_b[i] == 'E') is_float = true;
       if (!is_float) {
         int64_t iv;
         if (parse_int64(RawIter(val_b, val_n), &iv) != INT_OK) { *flags |= XU_BAD_NUMBER; return x; }
+        if (dstyle == 2) return xlsx_timedelta_cell(x, (double)iv, iv > -(1ll << 53) && iv < (1ll << 53), flags);
         if (dstyle) return xlsx_date_cell(x, (double)iv, date1904, flags);
         x.mode = CM_INT; x.bits = (uint64_t)iv;
         return x;
       }
       double v;
       if (!strtod_exact(val_b, val_n, &v) || dbl_is_inf(v) || dbl_is_nan(v)) { *flags |= XU_BAD_NUMBER; return x; }
+      if (dstyle == 2) return xlsx_timedelta_cell(x, v, true, flags);
       if (dstyle) return xlsx_date_cell(x, v, date1904, flags);
       // pandas _convert_cell: integral floats become ints
       if (v > -9.2e18 && v < 9.2e18) {
@@ -244,7 +256,8 @@ enum {
   XF_ENTITY = 1u << 10,
   XF_BIG = 1u << 11,          // int-looking string beyond int64
   XF_DATE = 1u << 12,         // datetime.datetime object
-  XF_TIME = 1u << 13          // datetime.time object
+  XF_TIME = 1u << 13,         // datetime.time object
+  XF_TDELTA = 1u << 14        // datetime.timedelta object
 };
 
 RFQ_HD uint32_t xclassify_cell(const CellSrc& s, bool first_row) {
@@ -253,6 +266,7 @@ RFQ_HD uint32_t xclassify_cell(const CellSrc& s, bool first_row) {
   if (s.mode == CM_BOOL) return XF_BOOL | XF_NON_STR | (first_row ? XF_FIRST_IS_INT : 0);
   if (s.mode == CM_DATE) return XF_DATE | XF_NON_STR;
   if (s.mode == CM_TIME) return XF_TIME | XF_NON_STR;
+  if (s.mode == CM_TDELTA) return XF_TDELTA | XF_NON_STR;
   if (s.mode == CM_FLOAT) {
     if (dbl_is_nan(bits_as_double(s.bits))) return XF_NULL;
     return XF_FLOAT | XF_TYPED_NUM | XF_NON_STR;
@@ -274,9 +288,11 @@ RFQ_HD int xdecide_column(uint32_t f) {
   if (f & XF_BIG) return CT_UNSUP;
   // a datetime / time object makes maybe_convert_numeric raise TypeError and is no bool either;
   // the DataFrame constructor then turns an all-datetime (+NaN) object column into datetime64
-  const bool dt = (f & (XF_DATE | XF_TIME)) != 0;
+  // (maybe_infer_to_datetimelike); the same for timedeltas -> timedelta64
+  const bool dt = (f & (XF_DATE | XF_TIME | XF_TDELTA)) != 0;
   if (dt) {
-    if ((f & XF_DATE) && !(f & (XF_TIME | XF_FLOAT | XF_INT | XF_BOOL | XF_STR_NONNUM))) return CT_DATE;
+    if ((f & XF_DATE) && !(f & (XF_TIME | XF_TDELTA | XF_FLOAT | XF_INT | XF_BOOL | XF_STR_NONNUM))) return CT_DATE;
+    if ((f & XF_TDELTA) && !(f & (XF_DATE | XF_TIME | XF_FLOAT | XF_INT | XF_BOOL | XF_STR_NONNUM))) return CT_TDELTA;
     return CT_XOBJ;
   }
   if (!(f & XF_STR_NONNUM)) {            // lib.maybe_convert_numeric succeeds

@@ -288,6 +288,7 @@ __global__ void __launch_bounds__(128) xheader_kernel(TableArgs a, uint8_t* __re
   }
   else if (s.mode == CM_DATE) n = pydatetime_write((int64_t)s.bits, o);   // str(label)
   else if (s.mode == CM_TIME) n = pytime_write((int64_t)s.bits, o);
+  else if (s.mode == CM_TDELTA) n = pytd_write((int64_t)s.bits, o);
   hdr_meta[2 * j] = s.mode;
   hdr_meta[2 * j + 1] = n;
 }

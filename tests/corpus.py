@@ -513,7 +513,7 @@ def sheet_xml_fuzz(seed: int):
     return "".join(out).encode("utf-8"), "".join(sst).encode("utf-8")
 
 
-def sheet_xml_dates(seed: int):
+def sheet_xml_dates(seed: int, p_td: float = 0.04):
     """A worksheet with date-styled numbers (style 3 = a date format, style 4 = a timedelta format):
     whole days, day fractions, serials below 1 (times) and below 60 (the 1900 leap-year bug),
     out-of-range serials, date columns with blanks / error cells / strings / plain numbers.
@@ -560,7 +560,7 @@ def sheet_xml_dates(seed: int):
     col_kinds = [r.choice(["day", "day", "dayf", "sec", "ms", "time", "early", "edge", "anydate", "iso",
                            "date+blank", "date+str", "date+num", "int", "price", "sst"])
                  for _ in range(ncols)]
-    use_td = r.random() < 0.04
+    use_td = r.random() < p_td
     out = [_XML_HEAD]
     for i in range(nrows + 1):
         rownum = i + 1
@@ -611,7 +611,11 @@ def sheet_xml_dates(seed: int):
                     out.append('<c r="%s" t="b"><v>%d</v></c>' % (ref, r.randint(0, 1)))
                 else:
                     style = 4 if use_td and r.random() < 0.3 else 3
-                    out.append('<c r="%s" s="%d"><v>%s</v></c>' % (ref, style, serial(kk)))
+                    v = serial(kk)
+                    if style == 4 and kk == "edge":      # the edges of a duration, not of a calendar date
+                        v = r.choice(["0", "0.000001", "149999.5", "-3.25", "1e9", "1e10", "-0.0000005", "0.99999999999",
+                                      "1.0000000001", "-149999.999", "0.5000005"])
+                    out.append('<c r="%s" s="%d"><v>%s</v></c>' % (ref, style, v))
         out.append("</row>")
     out.append(_XML_TAIL)
     sst = ['<?xml version="1.0" encoding="UTF-8" standalone="yes"?>\r\n'

@@ -140,3 +140,18 @@ def float_repr(v: float) -> str:
     buf = C.create_string_buffer(64)
     n = L.hc_float_repr(v, buf)
     return buf.raw[:n].decode()
+
+
+def timedelta_us(v: float) -> int:
+    L = lib()
+    L.hc_timedelta_us.argtypes = [C.c_double]
+    L.hc_timedelta_us.restype = C.c_longlong
+    return L.hc_timedelta_us(v)
+
+
+def timedelta_str(us: int) -> str:
+    L = lib()
+    L.hc_timedelta_str.argtypes = [C.c_longlong, C.c_char_p]
+    buf = C.create_string_buffer(64)
+    n = L.hc_timedelta_str(us, buf)
+    return buf.raw[:n].decode()

@@ -442,6 +442,8 @@ int hc_csv_parse(const uint8_t* doc, uint64_t len, int64_t nrows, uint8_t* out, 
 #include "../../replisense_rfq_b200/csrc/xlsx_core.cuh"
 extern "C" {
 int hc_strtod(const uint8_t* s, uint32_t n, double* out) { return rfq::strtod_exact(s, n, out) ? 1 : 0; }
+long long hc_timedelta_us(double v) { int64_t us = 0; return rfq::excel_to_timedelta(v, &us) ? (long long)us : (long long)0x7FFFFFFFFFFFFFFFll; }
+int hc_timedelta_str(long long us, char* out) { return (int)rfq::pytd_write((int64_t)us, (uint8_t*)out); }
 int hc_float_repr(double v, char* out) { std::string t = rfq::py_float_repr(v); memcpy(out, t.data(), t.size()); return (int)t.size(); }
 int hc_xml_decode(const uint8_t* p, uint32_t n, uint8_t* out) {
   rfq::XmlIter it(p, n); int c, k = 0;
@@ -574,7 +576,7 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
     CellSrc s = cell(1, c);
     std::string nm;
     lkind[c] = s.mode == CM_INT ? 1 : s.mode == CM_BOOL ? 2 : s.mode == CM_DATE ? 3 : s.mode == CM_TIME ? 4
-               : s.mode == CM_FLOAT ? 5 : 0;
+               : s.mode == CM_FLOAT ? 5 : s.mode == CM_TDELTA ? 6 : 0;
     if (s.mode == CM_FLOAT) {   // float label: repr() as a name, f"{x: .6f}" trimmed when printed
       const double v = bits_as_double(s.bits);
       const Fixed6 f = fixed6(v);
@@ -588,9 +590,10 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
     if (s.mode == CM_INT) lval[c] = (double)(long long)s.bits;
     if (s.mode == CM_BOOL) lval[c] = (s.bits & 1) ? 1.0 : 0.0;
     if (s.mode == CM_BOOL) nm = (s.bits & 1) ? "True" : "False";
-    if (s.mode == CM_DATE || s.mode == CM_TIME) {
-      uint8_t b[32];
-      uint32_t n = s.mode == CM_DATE ? pydatetime_write((int64_t)s.bits, b) : pytime_write((int64_t)s.bits, b);
+    if (s.mode == CM_DATE || s.mode == CM_TIME || s.mode == CM_TDELTA) {
+      uint8_t b[48];
+      uint32_t n = s.mode == CM_DATE ? pydatetime_write((int64_t)s.bits, b)
+                   : s.mode == CM_TIME ? pytime_write((int64_t)s.bits, b) : pytd_write((int64_t)s.bits, b);
       nm.assign((const char*)b, n);
     }
     if (s.mode != CM_INT) all_int = false;

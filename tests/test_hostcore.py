@@ -269,7 +269,7 @@ def test_sheet_model_without_refs_vs_oracle():
 
 def test_sheet_model_dates_vs_oracle():
     """Date-styled numbers: openpyxl from_excel (datetime / time / 1900 leap bug / 1904 epoch /
-    out of range -> NaN) and pandas' datetime64 / object printing; timedelta styles are declined."""
+    out of range -> NaN) and pandas' datetime64 / object printing."""
     from oracle import xlsx_reader as X
     bad, unsup, dates = [], 0, 0
     for seed in range(400):
@@ -494,3 +494,43 @@ def test_sheet_model_partial_refs_vs_oracle():
             bad.append(seed)
     assert not bad, bad
     assert unsup < 30
+
+
+def test_timedelta_conversion_matches_python():
+    """excel_to_timedelta (datetime_fmt.cuh) = openpyxl's from_excel(value, timedelta=True) over CPython's
+    timedelta arithmetic, microsecond for microsecond."""
+    import random
+    from oracle.xlsx_reader import from_excel
+    r = random.Random(5)
+    vals = [0, 1, 1.5, 0.25, -0.5, 100.000011574, 1.123456789, 1e-6, 0.0000005, 0.5000005, 49999.999999, -49999.5, 149999.99999999, -149999.000001,
+            2.0000000001, 0.999999999, 1 / 3, 2 / 3, 1e-9, 12345.678901234567]
+    vals += [r.uniform(-5, 5) for _ in range(3000)] + [r.uniform(-149000, 149000) for _ in range(6000)]
+    vals += [r.randint(0, 86400 * 1000) / 86400000 for _ in range(3000)] + [float(r.randint(-500, 500)) for _ in range(200)]
+    sx_rows = []
+    for v in vals:
+        td = from_excel(v, timedelta=True)
+        want = (td.days * 86400 + td.seconds) * 10 ** 6 + td.microseconds
+        assert H.timedelta_us(float(v)) == want, (v, H.timedelta_us(float(v)), want)
+        assert H.timedelta_str(want) == str(td), (v, H.timedelta_str(want), str(td))
+
+
+def test_sheet_model_timedelta_vs_oracle():
+    """Timedelta-styled numbers: a timedelta64 column ("N days" / "N days HH:MM:SS[.ffffff]", NaT), str(td) inside
+    object columns and as a label."""
+    bad, unsup, tds = [], 0, 0
+    from oracle import xlsx_reader as X
+    for seed in range(300):
+        sx, ss, ids, td_ids, d1904 = corpus.sheet_xml_dates(seed, p_td=0.6)
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            df = X.table_to_frame(X.sheet_table(sx, X.read_string_table(ss), ids, td_ids, d1904, 1000), 1000)
+            want = None if df.empty else O.frame_to_text(df)
+        tds += any(str(t).startswith("timedelta64") for t in df.dtypes)
+        st, got = H.sheet_parse(sx, ss, ids, 1000, td_ids, d1904)
+        if st == 2:
+            unsup += 1
+            continue
+        if (None if st == 3 else got) != want:
+            bad.append(seed)
+    assert not bad, bad
+    assert unsup <= 6 and tds > 10
