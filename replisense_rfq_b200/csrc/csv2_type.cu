@@ -436,32 +436,57 @@ void csv2_type(const Csv2Args& a, cudaStream_t s) {
 __global__ void __launch_bounds__(1024) csv2_offsets_kernel(Csv2Args a) {
   __shared__ unsigned long long s_warp[32];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  for (uint32_t base = 0; base <= a.n_items; base += 8192) {   // eight items per thread in flight
-    ItemBytes r[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) r[k] = item_bytes_of(a, base + k * 1024 + threadIdx.x);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const uint32_t item = base + k * 1024 + threadIdx.x;
-      item_bytes_commit(a, r[k]);
-      if (item <= a.n_items) a.item_bytes[item] = r[k].b;
-    }
-  }
-  __syncthreads();
   const uint32_t per = (a.n_items + 1u + 1023u) / 1024u;
   const uint32_t lo = min(threadIdx.x * per, a.n_items + 1u), hi = min(lo + per, a.n_items + 1u);
   unsigned long long sum = 0;
-  for (uint32_t i = lo; i < hi; ++i) sum += a.item_bytes[i];
+  unsigned long long b8[8];
+  const bool in_regs = per <= 8u;                 // up to 8191 items: a thread's items never leave its registers
+  {
+    // bytes of this thread's consecutive items, eight loads in flight; their side results are folded per
+    // thread (consecutive items share a document nearly always) and committed once per warp
+    ItemBytes acc{0ull, 0xFFFFFFFFu, 0u, 0u};
+    for (uint32_t base = lo; base < hi; base += 8) {
+      ItemBytes r[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) r[k] = item_bytes_of(a, base + k < hi ? base + k : 0xFFFFFFFFu);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (base + k >= hi) continue;
+        sum += r[k].b;
+        if (in_regs) b8[k] = r[k].b; else a.item_bytes[base + k] = r[k].b;
+        if (r[k].d == 0xFFFFFFFFu || (r[k].ex == 0 && r[k].big == 0)) continue;
+        if (acc.d == 0xFFFFFFFFu) acc.d = r[k].d;
+        if (acc.d == r[k].d) { acc.ex += r[k].ex; acc.big = max(acc.big, r[k].big); }
+        else {   // a second document inside one thread's items: straight to memory
+          if (r[k].ex) atomicAdd(&a.run[r[k].d].extra, r[k].ex);
+          if (r[k].big > a.counters[4]) atomicMax(a.counters + 4, r[k].big);
+        }
+      }
+    }
+    item_bytes_commit(a, acc);
+  }
   const unsigned long long incl = warp_incl_scan<SumU64>(sum, lane);
   if (lane == 31) s_warp[w] = incl;
   __syncthreads();
   if (w == 0) s_warp[lane] = warp_incl_scan<SumU64>(s_warp[lane], lane);
   __syncthreads();
   unsigned long long run = (w ? s_warp[w - 1] : 0ull) + incl - sum;
-  for (uint32_t i = lo; i < hi; ++i) {
-    a.item_off[i] = run;
-    if (i == a.n_items) *reinterpret_cast<unsigned long long*>(a.counters + 6) = run;   // total bytes of the attempt
-    run += a.item_bytes[i];
+  if (in_regs) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t i = lo + k;
+      if (i >= hi) continue;
+      a.item_off[i] = run;
+      if (i == a.n_items) *reinterpret_cast<unsigned long long*>(a.counters + 6) = run;   // total bytes of the attempt
+      run += b8[k];
+    }
+  } else {
+    for (uint32_t i = lo; i < hi; ++i) {
+      const unsigned long long b = a.item_bytes[i];
+      a.item_off[i] = run;
+      if (i == a.n_items) *reinterpret_cast<unsigned long long*>(a.counters + 6) = run;
+      run += b;
+    }
   }
   __syncthreads();
   for (uint32_t d = threadIdx.x; d < a.n_docs; d += blockDim.x) {
