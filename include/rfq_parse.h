@@ -49,6 +49,20 @@ extern "C" {
 /* inflate path: bad DEFLATE stream, size or CRC-32 differs from the zip directory's, unknown method
  * (zipfile raises BadZipFile / zlib.error there) */
 #define RFQ_DOC_CORRUPT 6
+/* .json path: json.loads raises json.JSONDecodeError.  Which message and where, as Python reports them:
+ * rfq_out_attempt[d] = RFQ_JSON_E_* (the message), rfq_out_rows[d] = lineno, rfq_out_cols[d] = colno,
+ * rfq_out_chars[d] = the character index ("<message>: line L column C (char P)") */
+#define RFQ_DOC_JSON_INVALID 7
+#define RFQ_JSON_E_VALUE 1          /* Expecting value */
+#define RFQ_JSON_E_PROPNAME 2       /* Expecting property name enclosed in double quotes */
+#define RFQ_JSON_E_COLON 3          /* Expecting ':' delimiter */
+#define RFQ_JSON_E_COMMA 4          /* Expecting ',' delimiter */
+#define RFQ_JSON_E_EXTRA 5          /* Extra data */
+#define RFQ_JSON_E_UNTERMINATED 6   /* Unterminated string starting at */
+#define RFQ_JSON_E_CTRL 7           /* Invalid control character at */
+#define RFQ_JSON_E_ESCAPE 8         /* Invalid \escape */
+#define RFQ_JSON_E_UESCAPE 9        /* Invalid \uXXXX escape */
+#define RFQ_JSON_E_BOM 10           /* Unexpected UTF-8 BOM (decode using utf-8-sig) */
 
 typedef struct rfq_ctx rfq_ctx;
 
@@ -122,6 +136,14 @@ int rfq_numeric_run(rfq_ctx* ctx, const uint8_t* kind);
  * strategy 3's cleaned text (strip, drop a leading ```json and a trailing ```, strip).  json.loads of
  * those spans stays with the caller, as it is CPython's parser in the reference. */
 int rfq_json_spans_run(rfq_ctx* ctx);
+
+/* The .json file type of FileParser (replaces _parse_json_async, app/file_parser.py:315-331): the staged
+ * documents are read as strict UTF-8 with universal newlines, parsed like json.loads and printed like
+ * json.dumps(data, indent=2, ensure_ascii=False) behind "=== JSON Data ===\n".  Status per document:
+ * RFQ_DOC_OK, RFQ_DOC_JSON_INVALID (with the reference's message and position, see above), or
+ * RFQ_DOC_UNSUPPORTED for what is declined (bytes that are not UTF-8, an object with two equal keys, a
+ * lone surrogate escape, an integer of more than 4300 digits, nesting beyond 96). */
+int rfq_json_run(rfq_ctx* ctx);
 
 /* ---- prompt assembly (the step right after the parser): the text handling of
  * RFQFieldGenerator._generate_sync (app/rfq_agent.py:138-151).  The staged batch holds raw_text

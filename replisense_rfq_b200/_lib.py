@@ -13,6 +13,12 @@ LIB_PATH = HERE / "librfqparse.so"
 
 RFQ_OK = 0
 DOC_OK, DOC_CSV_UNPARSEABLE, DOC_UNSUPPORTED, DOC_EMPTY_SHEET, DOC_EMPTY_TEXT, DOC_VALUE_ERROR, DOC_CORRUPT = 0, 1, 2, 3, 4, 5, 6
+DOC_JSON_INVALID = 7
+# RFQ_JSON_E_*: the messages of json.JSONDecodeError (Lib/json/decoder.py, Modules/_json.c)
+JSON_ERRORS = {1: "Expecting value", 2: "Expecting property name enclosed in double quotes", 3: "Expecting ':' delimiter",
+               4: "Expecting ',' delimiter", 5: "Extra data", 6: "Unterminated string starting at",
+               7: "Invalid control character at", 8: "Invalid \\escape", 9: "Invalid \\uXXXX escape",
+               10: "Unexpected UTF-8 BOM (decode using utf-8-sig)"}
 
 _lib = None
 
@@ -34,6 +40,7 @@ SIGNATURES = {
     "rfq_md5_run": (C.c_int, [C.c_void_p]),
     "rfq_numeric_run": (C.c_int, [C.c_void_p, C.c_void_p]),
     "rfq_json_spans_run": (C.c_int, [C.c_void_p]),
+    "rfq_json_run": (C.c_int, [C.c_void_p]),
     "rfq_frame_run": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "rfq_inflate_run": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "rfq_restage_output": (C.c_int, [C.c_void_p]),

@@ -1,0 +1,118 @@
+// The .json path on the device (app/file_parser.py:315-331): json.loads + json.dumps(indent=2,
+// ensure_ascii=False) of every staged document, restated in json_pretty.cuh.  One thread walks one
+// document (the grammar is sequential); documents are claimed through a ticket so that a few large ones do
+// not pin a warp's other lanes to the slowest.  Two launches: measure (validation, error position, output
+// size), then write at the offsets the host derived.  Byte work, no tensor cores.
+#include <algorithm>
+#include <atomic>
+#include "json_pretty.cuh"
+#include "launch.h"
+#include "pipeline.h"
+
+namespace rfq {
+
+static_assert(sizeof(JsonResult) == sizeof(JsonDocRes), "JsonDocRes mirrors JsonResult");
+
+// scratch of document d for the duplicate-key test: 2 * (len / 4 + 2) words, carved from the arena offsets
+__device__ __forceinline__ uint32_t* json_keys_of(uint32_t* keys, const uint32_t* doc_off, uint32_t d) {
+  return keys + (size_t)doc_off[d] / 2 + 4ull * d;
+}
+
+// A CTA claims 64 consecutive documents and first brings those that fit (RFQ_JSON_STAGE bytes each) into
+// shared memory with coalesced 16-byte loads: the walk reads its document a byte at a time, and from global
+// memory every such read is a dependent round trip.
+#define RFQ_JSON_STAGE 1024u
+__device__ __forceinline__ const uint8_t* json_stage(const uint8_t* __restrict__ arena, const uint32_t* __restrict__ doc_off,
+                                                     const uint32_t* __restrict__ doc_len, uint32_t n_docs, uint32_t base,
+                                                     uint8_t* smem) {
+  for (uint32_t k = 0; k < 64; ++k) {
+    const uint32_t d = base + k;
+    if (d >= n_docs) break;
+    const uint32_t len = doc_len[d];
+    if (len > RFQ_JSON_STAGE) continue;
+    const uint8_t* src = arena + doc_off[d];                 // documents start on 16-byte boundaries, padded to 16
+    for (uint32_t j = threadIdx.x * 16u; j < len; j += 64u * 16u)
+      *reinterpret_cast<uint4*>(smem + k * RFQ_JSON_STAGE + j) = __ldg(reinterpret_cast<const uint4*>(src + j));
+  }
+  __syncthreads();
+  const uint32_t d = base + threadIdx.x;
+  if (d >= n_docs) return nullptr;
+  return doc_len[d] <= RFQ_JSON_STAGE ? smem + threadIdx.x * RFQ_JSON_STAGE : arena + doc_off[d];
+}
+
+__global__ void __launch_bounds__(64) json_measure_kernel(const uint8_t* __restrict__ arena, const uint32_t* __restrict__ doc_off,
+                                                          const uint32_t* __restrict__ doc_len, uint32_t n_docs, uint32_t* keys,
+                                                          JsonResult* res, uint32_t* ticket) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  __shared__ uint32_t s_base;
+  for (;;) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_base = atomicAdd(ticket, 64u);
+    __syncthreads();
+    const uint32_t base = s_base;
+    if (base >= n_docs) return;
+    const uint8_t* p = json_stage(arena, doc_off, doc_len, n_docs, base, smem);
+    if (!p) continue;
+    const uint32_t d = base + threadIdx.x;
+    JsonResult r;
+    json_pretty(p, doc_len[d], nullptr, json_keys_of(keys, doc_off, d), &r);
+    res[d] = r;
+  }
+}
+
+__global__ void __launch_bounds__(64) json_emit_kernel(const uint8_t* __restrict__ arena, const uint32_t* __restrict__ doc_off,
+                                                       const uint32_t* __restrict__ doc_len, uint32_t n_docs, uint32_t* keys,
+                                                       const JsonResult* __restrict__ res, const unsigned long long* __restrict__ out_off,
+                                                       uint8_t* out, uint32_t* ticket) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  __shared__ uint32_t s_base;
+  for (;;) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_base = atomicAdd(ticket, 64u);
+    __syncthreads();
+    const uint32_t base = s_base;
+    if (base >= n_docs) return;
+    const uint8_t* p = json_stage(arena, doc_off, doc_len, n_docs, base, smem);
+    if (!p) continue;
+    const uint32_t d = base + threadIdx.x;
+    if (res[d].status != JS_OK) continue;
+    uint8_t* o = out + out_off[d];
+    const char* banner = "=== JSON Data ===\n";
+    uint32_t k = 0;
+    for (; banner[k]; ++k) o[k] = (uint8_t)banner[k];
+    JsonResult r;
+    json_pretty(p, doc_len[d], o + k, json_keys_of(keys, doc_off, d), &r);
+  }
+}
+
+static void json_smem_optin() {
+  static std::atomic<unsigned long long> done{0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (done.load() >> (dev & 63) & 1ull) return;
+  cudaFuncSetAttribute(json_measure_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * RFQ_JSON_STAGE);
+  cudaFuncSetAttribute(json_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * RFQ_JSON_STAGE);
+  done.fetch_or(1ull << (dev & 63));
+}
+
+void json_pretty_measure(const uint8_t* arena, const uint32_t* doc_off, const uint32_t* doc_len, uint32_t n_docs, uint32_t* keys,
+                         JsonDocRes* res, uint32_t* ticket, cudaStream_t s) {
+  if (n_docs == 0) return;
+  json_smem_optin();
+  prof_mark("json_measure_kernel", s);
+  const uint32_t grid = std::min<uint32_t>((n_docs + 63) / 64, 148u * 3u);
+  RFQ_LAUNCH(json_measure_kernel, grid, 64, 64 * RFQ_JSON_STAGE, s, arena, doc_off, doc_len, n_docs, keys,
+             reinterpret_cast<JsonResult*>(res), ticket);
+}
+
+void json_pretty_emit(const uint8_t* arena, const uint32_t* doc_off, const uint32_t* doc_len, uint32_t n_docs, uint32_t* keys,
+                      const JsonDocRes* res, const unsigned long long* out_off, uint8_t* out, uint32_t* ticket, cudaStream_t s) {
+  if (n_docs == 0) return;
+  json_smem_optin();
+  prof_mark("json_emit_kernel", s);
+  const uint32_t grid = std::min<uint32_t>((n_docs + 63) / 64, 148u * 3u);
+  RFQ_LAUNCH(json_emit_kernel, grid, 64, 64 * RFQ_JSON_STAGE, s, arena, doc_off, doc_len, n_docs, keys,
+             reinterpret_cast<const JsonResult*>(res), out_off, out, ticket);
+}
+
+}  // namespace rfq

@@ -69,6 +69,14 @@ void json_spans_batch(const uint8_t* arena, const uint32_t* doc_off, const uint3
                       uint32_t* out, unsigned long long* out_off, unsigned long long* out_len, cudaStream_t s);
 
 // ------------------------------------------------------------------------------------------
+// the .json path (json_pretty.cu): measure = validate + error position + output size, emit = write
+struct JsonDocRes { uint32_t status, err, pos, line, col; unsigned long long out_bytes; };   // = JsonResult (json_pretty.cuh)
+void json_pretty_measure(const uint8_t* arena, const uint32_t* doc_off, const uint32_t* doc_len, uint32_t n_docs, uint32_t* keys,
+                         JsonDocRes* res, uint32_t* ticket, cudaStream_t s);
+void json_pretty_emit(const uint8_t* arena, const uint32_t* doc_off, const uint32_t* doc_len, uint32_t n_docs, uint32_t* keys,
+                      const JsonDocRes* res, const unsigned long long* out_off, uint8_t* out, uint32_t* ticket, cudaStream_t s);
+
+// ------------------------------------------------------------------------------------------
 // prompt assembly (prompt_kernels.cu)
 struct PromptArgs {
   const uint8_t* arena;       // device, packed raw_text documents (UTF-8)

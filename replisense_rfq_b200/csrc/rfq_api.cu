@@ -439,6 +439,70 @@ int rfq_json_spans_run(rfq_ctx* c) {
   return RFQ_OK;
 }
 
+// The .json path (app/file_parser.py:315-331): strict UTF-8, json.loads, json.dumps(indent=2, ensure_ascii=False)
+// behind the "=== JSON Data ===" banner.  Two launches around one host synchronisation (output sizes).
+int rfq_json_run(rfq_ctx* c) {
+  if (!c) return RFQ_ERR_ARG;
+  if (!c->staged) { c->err = "rfq_json_run: nothing staged"; return RFQ_ERR_STATE; }
+  RFQ_CK(c, cudaSetDevice(c->device));
+  cudaStream_t s = c->stream;
+  const uint32_t n = c->n_docs;
+  if (!c->nested) c->prof.begin();
+  g_prof = &c->prof;
+  struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
+  if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
+  c->status_override.clear(); c->out_n = 0;
+  c->segs.clear();
+  c->out_total = 0;
+  c->host_tables = true;
+  c->r_off.assign(n, 0); c->r_len.assign(n, 0); c->r_chars.assign(n, ~0ull);
+  c->r_status.assign(n, RFQ_DOC_OK);
+  c->r_rows.assign(n, 0); c->r_cols.assign(n, 0); c->r_attempt.assign(n, 0);
+  uint32_t* d_keys = c->pool.alloc<uint32_t>(c->arena_bytes / 2 + 4ull * n + 64);
+  JsonDocRes* d_res = c->pool.alloc<JsonDocRes>(n + 1);
+  unsigned long long* d_off = c->pool.alloc<unsigned long long>(n + 1);
+  uint32_t* d_ticket = c->pool.alloc<uint32_t>(4);
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  RFQ_CK(c, cudaMemsetAsync(d_ticket, 0, 16, s));
+  json_pretty_measure((const uint8_t*)c->d_arena.p, c->d_doc_off, c->d_doc_len, n, d_keys, d_res, d_ticket, s);
+  RFQ_CK(c, c->h_down.reserve(sizeof(JsonDocRes) * (n + 1) + 64));
+  JsonDocRes* h_res = (JsonDocRes*)c->h_down.p;
+  if (n) RFQ_CK(c, cudaMemcpyAsync(h_res, d_res, sizeof(JsonDocRes) * n, cudaMemcpyDeviceToHost, s));
+  prof_mark("host+sync", s);
+  RFQ_CK(c, cudaStreamSynchronize(s));
+  RFQ_CK(c, c->h_up.reserve(8ull * (n + 1) + 64));
+  unsigned long long* h_off = (unsigned long long*)c->h_up.p;
+  unsigned long long total = 0;
+  for (uint32_t d = 0; d < n; ++d) {
+    const JsonDocRes& r = h_res[d];
+    h_off[d] = total;
+    if (r.status == 0) {
+      c->r_off[d] = total; c->r_len[d] = 18 + r.out_bytes;      // "=== JSON Data ===\n" + the text
+      total += (c->r_len[d] + 15) & ~15ull;
+    } else if (r.status == 1) {
+      // json.JSONDecodeError: which message, and the position it reports (include/rfq_parse.h)
+      c->r_status[d] = RFQ_DOC_JSON_INVALID;
+      c->r_attempt[d] = (uint8_t)r.err; c->r_rows[d] = r.line; c->r_cols[d] = r.col; c->r_chars[d] = r.pos;
+    } else c->r_status[d] = RFQ_DOC_UNSUPPORTED;
+  }
+  uint8_t* d_text = c->pool.alloc<uint8_t>(total + 64);
+  if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+  if (total) {
+    RFQ_CK(c, cudaMemcpyAsync(d_off, h_off, 8ull * n, cudaMemcpyHostToDevice, s));
+    RFQ_CK(c, cudaMemsetAsync(d_ticket + 1, 0, 4, s));
+    json_pretty_emit((const uint8_t*)c->d_arena.p, c->d_doc_off, c->d_doc_len, n, d_keys, d_res, d_off, d_text, d_ticket + 1, s);
+  }
+  c->segs.push_back({d_text, total, 0});
+  c->out_total = total;
+  prof_mark("end", s);
+  RFQ_CK(c, cudaEventRecord(c->ev1, s));
+  RFQ_CK(c, cudaGetLastError());
+  c->d_out_off = nullptr; c->d_out_len = nullptr;
+  c->have_output = true;
+  c->timed = true;
+  return RFQ_OK;
+}
+
 int rfq_numeric_run(rfq_ctx* c, const uint8_t* kind) {
   if (!c || (c->n_docs && !kind)) return RFQ_ERR_ARG;
   if (!c->staged) { c->err = "rfq_numeric_run: nothing staged"; return RFQ_ERR_STATE; }

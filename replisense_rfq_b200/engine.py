@@ -289,6 +289,37 @@ class Engine:
             r = BatchResult(self)
             return np.frombuffer(C.string_at(r.text_ptr, 16 * r.n), dtype=np.uint32).reshape(r.n, 4).copy()
 
+    # -- the .json file type (app/file_parser.py:315-331)
+    def parse_json_many(self, docs: Sequence[bytes]) -> "list[str | EngineError]":
+        """raw_text of every .json document ("=== JSON Data ===" + json.dumps(json.loads(text), indent=2,
+        ensure_ascii=False)), or an EngineError in its slot: `.json_error` holds the text of the
+        json.JSONDecodeError the reference would see ("Expecting value: line 1 column 1 (char 0)"); a
+        document the GPU path declines has `.json_error` None."""
+        if not len(docs):
+            return []
+        with self.lock:
+            a, off, ln = self._pack(docs)
+            self._check(self.lib.rfq_stage(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data, len(docs)), "rfq_stage")
+            self._check(self.lib.rfq_json_run(self.ctx), "rfq_json_run")
+            self._check(self.lib.rfq_fetch(self.ctx), "rfq_fetch")
+            r = BatchResult(self)
+            out: "list[Any]" = []
+            for d in range(r.n):
+                st = int(r.status[d])
+                if st == _lib.DOC_OK:
+                    out.append(r.doc_str(d))
+                elif st == _lib.DOC_JSON_INVALID:
+                    e = EngineError("invalid JSON")
+                    e.json_error = "%s: line %d column %d (char %d)" % (_lib.JSON_ERRORS[int(r.attempt[d])], int(r.rows[d]),
+                                                                       int(r.cols[d]), int(r.chars[d]))
+                    out.append(e)
+                else:
+                    e = EngineError("JSON document not decoded on the GPU path (status %d): not UTF-8, duplicate keys, a lone "
+                                    "surrogate escape, an integer beyond 4300 digits or nesting beyond 96" % st)
+                    e.json_error = None
+                    out.append(e)
+            return out
+
     # -- prompt assembly (the step after the parser: app/rfq_agent.py:138-151)
     def prompt_batch(self, docs: Sequence[bytes], head: bytes, tail: bytes, mark: bytes,
                      max_chars: int = 8000) -> BatchResult:

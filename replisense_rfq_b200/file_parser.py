@@ -1,9 +1,9 @@
 """Host-side mirror of the reference's `FileParser` (app/file_parser.py:25-375) for the formats
-on the north-star path — .txt, .csv, .xlsx — with every byte of parsing done by the CUDA
+on the north-star path — .txt, .csv, .xlsx, .json — with every byte of parsing done by the CUDA
 library behind include/rfq_parse.h.  Same constructor arguments, method names, result envelope
 and error behaviour as the reference, plus the batched `parse_many` entry point.
 
-Out of scope here: .pdf, .docx, .xls, .json — they are reported as unsupported
+Out of scope here: .pdf, .docx, .xls — they are reported as unsupported
 file types rather than routed to a CPU implementation.
 """
 from __future__ import annotations
@@ -22,7 +22,7 @@ logger = logging.getLogger(__name__)
 
 HAS_PYMUPDF = False  # PDF extraction (MuPDF layout engine) is not part of this build
 
-_SUPPORTED = {".txt", ".xlsx", ".csv"}
+_SUPPORTED = {".txt", ".xlsx", ".csv", ".json"}
 
 _CSV_FAIL = "Unable to parse CSV with any supported encoding/separator combination"
 _EXCEL_EMPTY = "Excel file appears to be empty or unreadable"
@@ -68,6 +68,8 @@ class FileParser:
                 text = await self._parse_excel_async(file_path)
             elif suffix == ".csv":
                 text = await self._parse_csv_async(file_path)
+            elif suffix == ".json":
+                text = await self._parse_json_async(file_path)
             else:
                 raise FileParsingError(f"Unsupported file format: {file_path.suffix}")
             result = {
@@ -136,6 +138,22 @@ class FileParser:
         except Exception as e:
             raise FileParsingError(f"CSV parsing failed: {str(e)}")
 
+    # ------------------------------------------------------------------ json (:315-331)
+    @staticmethod
+    def _json_result(t):
+        """A slot of Engine.parse_json_many as the reference's result: the text, or its FileParsingError."""
+        if isinstance(t, EngineError):
+            if getattr(t, "json_error", None) is not None:
+                return FileParsingError(f"Invalid JSON format: {t.json_error}")
+            return FileParsingError(f"JSON parsing failed: {t}")
+        return t
+
+    async def _parse_json_async(self, file_path: Path) -> str:
+        t = self._json_result(self.engine.parse_json_many([Path(file_path).read_bytes()])[0])
+        if isinstance(t, Exception):
+            raise t
+        return t
+
     # ------------------------------------------------------------------ excel (:214-252)
     async def _parse_excel_async(self, file_path: Path) -> str:
         return await asyncio.get_event_loop().run_in_executor(
@@ -154,7 +172,7 @@ class FileParser:
 
     # ------------------------------------------------------------------ batched entry point
     def parse_many(self, docs: Sequence[bytes], kinds: Sequence[str]) -> "list[str | FileParsingError]":
-        """Many documents in one go. `kinds[i]` in {'txt', 'csv', 'xlsx'}; returns raw_text or the
+        """Many documents in one go. `kinds[i]` in {'txt', 'csv', 'xlsx', 'json'}; returns raw_text or the
         FileParsingError the reference would have raised for that document, in input order.  Text bodies
         and CSV files travel in ONE packed arena and one upload (rfq_mixed_parse).  The worksheet /
         sharedStrings parts of all .xlsx containers travel as they lie in the zip — still compressed — and
@@ -164,12 +182,15 @@ class FileParser:
         out: "list[Any]" = [None] * n
         flat, fkind, owner = [], [], []
         books, book_idx = [], []
+        jdocs, jidx = [], []
         for i, (doc, k) in enumerate(zip(docs, kinds)):
             k = k.lower().lstrip(".")
             if k == "txt":
                 flat.append(doc); fkind.append(_lib.KIND_TEXT); owner.append(i)
             elif k == "csv":
                 flat.append(doc); fkind.append(_lib.KIND_CSV); owner.append(i)
+            elif k == "json":
+                jdocs.append(doc); jidx.append(i)
             elif k == "xlsx":
                 try:
                     books.append(xlsx_host.scan_workbook(doc))
@@ -191,6 +212,9 @@ class FileParser:
                                   else FileParsingError(f"CSV parsing failed: {_CSV_FAIL}") if st == _lib.DOC_CSV_UNPARSEABLE
                                   else FileParsingError("CSV parsing failed: unsupported construct on the GPU path "
                                                         f"(status {st})"))
+        if jdocs:
+            for i, t in zip(jidx, eng.parse_json_many(jdocs)):
+                out[i] = self._json_result(t)
         if books:
             for i, t in zip(book_idx, xlsx_host.parse_workbooks(eng, books, self.max_excel_rows)):
                 out[i] = FileParsingError(f"Excel parsing failed: {t}") if isinstance(t, Exception) else t

@@ -693,3 +693,72 @@ def mixed_batch(n: int, seed: int = 0):
         else:
             docs.append(text_body(seed * 100003 + i)); kinds.append("txt")
     return docs, kinds
+
+
+# ------------------------------------------------------------------ .json documents
+def _json_value(r, depth=0):
+    k = r.random()
+    if depth > 5 or k < 0.45:
+        c = r.random()
+        if c < 0.25:
+            return r.choice([0, 1, -1, 7, 1200, -45, 10 ** 12, 2 ** 63, -2 ** 70, 12345678901234567890123])
+        if c < 0.5:
+            return r.choice([0.0, -0.0, 1.5, 4.25, 1250.75, 1e15, 1e16, 1e-4, 9.5e-5, 1e22, 2.5e-7, 0.1, 1 / 3, 1e300,
+                             r.uniform(-1e6, 1e6), round(r.uniform(0, 1e5), 2), r.uniform(0, 1) * 10 ** r.randint(-30, 30)])
+        if c < 0.6:
+            return r.choice([True, False, None])
+        return r.choice(["", "RJF544", "a & b", "Würth", "日本語", "₹500", "line1\nline2", "tab\there", "q\"uote", "back\\slash",
+                         "\u0001ctl", "emoji 😀", "/slash", "x" * r.randint(0, 40), " lead", "null", "1e5", "\x7f"])
+    if k < 0.75:
+        return {r.choice(["part", "qty", "price", "desc", "ünit", "a b", "", "k%d" % r.randint(0, 50), "n\"q", "items"]) + str(i):
+                _json_value(r, depth + 1) for i in range(r.randint(0, 5))}
+    return [_json_value(r, depth + 1) for _ in range(r.randint(0, 5))]
+
+
+def json_doc(seed: int) -> bytes:
+    """A valid .json document: nested objects / arrays, every scalar type, escapes written both raw and as
+    \\uXXXX, assorted whitespace and newline conventions, NaN / Infinity, numbers in odd spellings."""
+    import json
+    r = random.Random(seed * 7919 + 5)
+    obj = _json_value(r)
+    style = r.randint(0, 4)
+    if style == 0:
+        t = json.dumps(obj)                                   # ensure_ascii: non-ASCII as \uXXXX (surrogate pairs too)
+    elif style == 1:
+        t = json.dumps(obj, ensure_ascii=False, separators=(",", ":"))
+    elif style == 2:
+        t = json.dumps(obj, indent=r.choice([1, 2, 4, "\t"]), ensure_ascii=False)
+    elif style == 3:
+        t = json.dumps(obj, indent=2).replace("\n", "\r\n")
+    else:
+        t = "  " + json.dumps(obj, ensure_ascii=False, indent=3).replace("\n", "\r") + " \n"
+    if r.random() < 0.2:   # spellings json.dumps never writes
+        t = t.replace("1.5", r.choice(["1.50", "15e-1", "0.15E+1", "1.5000000000000000", "1.4999999999999999999"]))
+        t = t.replace("1200", r.choice(["1200", "1.2e3", "12E2", "1200.0"]))
+    if r.random() < 0.1:
+        t = t.replace("null", r.choice(["NaN", "Infinity", "-Infinity", "null"]))
+    return t.encode("utf-8")
+
+
+def json_doc_broken(seed: int) -> bytes:
+    """A .json document with one defect: a truncation, a swapped / dropped / inserted character."""
+    r = random.Random(seed * 104729 + 11)
+    d = bytearray(json_doc(seed))
+    if not d:
+        return b""
+    k = r.randint(0, 5)
+    pos = r.randrange(len(d))
+    if k == 0:
+        del d[pos:]
+    elif k == 1:
+        del d[pos]
+    elif k == 2:
+        d[pos] = r.choice(b'{}[],:"\\ xe.-0\n\t\x01')
+    elif k == 3:
+        d.insert(pos, r.choice(b'{}[],:"\\ x.-0\n'))
+    elif k == 4:
+        d += r.choice([b" x", b",", b"]", b"}", b" 1", b"\xef\xbb\xbf"])
+    else:
+        d = bytearray(r.choice([b"\xef\xbb\xbf", b"", b" "])) + d
+    return bytes(d)
+

@@ -155,3 +155,25 @@ def timedelta_str(us: int) -> str:
     buf = C.create_string_buffer(64)
     n = L.hc_timedelta_str(us, buf)
     return buf.raw[:n].decode()
+
+
+JSON_ERRORS = {1: "Expecting value", 2: "Expecting property name enclosed in double quotes", 3: "Expecting ':' delimiter",
+               4: "Expecting ',' delimiter", 5: "Extra data", 6: "Unterminated string starting at",
+               7: "Invalid control character at", 8: "Invalid \\escape", 9: "Invalid \\uXXXX escape",
+               10: "Unexpected UTF-8 BOM (decode using utf-8-sig)"}
+
+
+def json_pretty(doc: bytes):
+    """(status, text or error message): json_pretty of json_pretty.cuh, measure pass + write pass."""
+    L = lib()
+    L.hc_json_pretty.argtypes = [C.c_char_p, C.c_uint32, C.c_char_p, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]
+    cap = 6 * len(doc) + 64
+    buf = C.create_string_buffer(cap)
+    n = C.c_uint64(0)
+    info = (C.c_uint32 * 4)()
+    st = L.hc_json_pretty(doc, len(doc), buf, cap, C.byref(n), info)
+    if st == 0:
+        return 0, buf.raw[:n.value].decode("utf-8")
+    if st == 1:
+        return 1, "%s: line %d column %d (char %d)" % (JSON_ERRORS[info[0]], info[2], info[3], info[1])
+    return st, None

@@ -58,5 +58,5 @@ def test_error_behaviour_matches_reference(tmp_path):
 
 def test_supported_extensions():
     from replisense_rfq_b200 import FileParser, get_supported_extensions
-    assert get_supported_extensions() == {".txt", ".csv", ".xlsx"}
-    assert FileParser().supported_extensions == {".txt", ".csv", ".xlsx"}
+    assert get_supported_extensions() == {".txt", ".csv", ".xlsx", ".json"}
+    assert FileParser().supported_extensions == {".txt", ".csv", ".xlsx", ".json"}
