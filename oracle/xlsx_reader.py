@@ -21,11 +21,21 @@ and (installed pandas 3.0.2, read directly):
   pandas/io/excel/_base.py:636-697,700-937  _calc_rows, parse, _parse_sheet
 
 Pinned by the golden vectors of `.cache/42/cache.db` rows 12 and 14 (tests/golden/): shared
-strings, numeric / string cells, row gaps, header inference, float formatting.  PARITY UNPINNED for
-what those two sheets do not contain: date-styled numbers and t="d" cells (from_excel /
-fromisoformat, checked only on Excel-calendar known answers in tests/test_hostcore.py), rows or
-cells without r=, inline strings, boolean / error cells — there the restatement of openpyxl's
-published code is the only reference available in this container.
+strings, numeric / string cells, row gaps, header inference, float formatting.  Beyond those two
+sheets the READER is a restatement of openpyxl 3.1.5's published code (openpyxl is not installed
+here and cannot be), while everything downstream of it — TextParser, dtype inference, to_string —
+is the real pandas.  What the restatement is checked against:
+  * date serials: ECMA-376 part 1 §18.17.4 (serial 1 = 1900-01-01, the 1900 leap-year gap at 60, the
+    1904 date system) and the values openpyxl's own tests use (openpyxl/utils/tests/test_datetime.py,
+    3.1.5: from_excel(39385) = 2007-10-30, 0.5 -> 12:00, 40372.27616898148 -> 2010-07-13 06:37:41) in
+    tests/test_hostcore.py::test_excel_serial_known_answers;
+  * timedelta-styled numbers: CPython's own datetime.timedelta does the arithmetic here, and the device
+    restatement is compared with it microsecond for microsecond on 12 000 values
+    (tests/test_hostcore.py::test_timedelta_conversion_matches_python);
+  * t="d" cells: datetime.fromisoformat of the running CPython.
+PARITY UNPINNED only for what has no external answer in this container: the order in which
+openpyxl's reader numbers rows and cells without r= (row_counter / col_counter, restated from
+worksheet/_reader.py) and its treatment of inline strings, boolean and error cells.
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may import this module.
 """
 from __future__ import annotations

@@ -302,6 +302,10 @@ def test_excel_serial_known_answers():
     assert from_excel(0.5) == dt.time(12, 0)
     assert from_excel(39448, MAC_EPOCH) == dt.datetime(2012, 1, 2)
     assert from_excel(40372.27616898148) == dt.datetime(2010, 7, 13, 6, 37, 41)
+    assert from_excel(39385) == dt.datetime(2007, 10, 30)
+    # timedelta-styled numbers: whole days stay whole, fractions are rounded to the millisecond
+    assert from_excel(1.5, timedelta=True) == dt.timedelta(days=1, hours=12)
+    assert from_excel(0.000011574, timedelta=True) == dt.timedelta(seconds=1)
 
 
 def test_strtod_exact_matches_python_float():
