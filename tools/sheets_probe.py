@@ -19,7 +19,11 @@ def main():
         docs += [ss, sx]; kind += [1, 0]; sst_of += [-1, len(docs) - 2]
     for _ in range(3):
         r = eng.sheets_batch(docs, kind, sst_of, 1000)
-    print("sheets", n, "out bytes", int(r.total), "run ms", eng.last_run_ms())
+    print("sheets", n, "in MB", sum(len(d) for d in docs) / 1e6, "out bytes", int(r.total), "run ms", eng.last_run_ms())
+    eng.set_profile(True)
+    r = eng.sheets_batch(docs, kind, sst_of, 1000)
+    for name, ms in eng.profile():
+        print("   %-28s %8.3f ms" % (name, ms))
 
 
 if __name__ == "__main__":
