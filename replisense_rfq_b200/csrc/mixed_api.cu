@@ -3,7 +3,10 @@
 // text, CSV and sheet pipelines then run over their own subsets of it (views of the document tables, no
 // second copy of any byte), and their results are merged into one per-document table in input order.
 #include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
+#include <chrono>
 #include <algorithm>
 #include <vector>
 
@@ -32,6 +35,14 @@ extern "C" int rfq_mixed_run(rfq_ctx* c, const uint8_t* kind, const int64_t* max
   RFQ_CK(c, cudaEventRecord(c->ev0, s));
   c->pool.reset();
   c->status_override.clear(); c->out_n = 0;
+  static const bool host_prof = getenv("RFQ_HOST_PROFILE") != nullptr;   // host time of every stage on stderr
+  auto t_prev = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what) {
+    if (!host_prof) return;
+    const auto t = std::chrono::steady_clock::now();
+    fprintf(stderr, "rfq_mixed_run host %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t - t_prev).count());
+    t_prev = t;
+  };
   // ---- the three subsets, in input order
   std::vector<uint32_t> idx[3];          // 0 text, 1 csv, 2 sheets + sharedStrings
   std::vector<int32_t> pos_in_sheets(n, -1);
@@ -82,6 +93,7 @@ extern "C" int rfq_mixed_run(rfq_ctx* c, const uint8_t* kind, const int64_t* max
   uint64_t m_total = 0;
   int rc = RFQ_OK;
   c->nested = true;
+  lap("views");
   for (int k = 0; k < 3 && rc == RFQ_OK; ++k) {
     const uint32_t m = (uint32_t)idx[k].size();
     if (m == 0) continue;
@@ -141,6 +153,7 @@ extern "C" int rfq_mixed_run(rfq_ctx* c, const uint8_t* kind, const int64_t* max
       for (auto sg : c->segs) { sg.host_base += m_total; sg.copied = false; m_segs.push_back(sg); }
       m_total += c->out_total;
     }
+    lap(k == 0 ? "text run + merge" : k == 1 ? "csv run + merge" : "sheets run + merge");
   }
   c->nested = false;
   // ---- back to the full batch
@@ -158,6 +171,7 @@ extern "C" int rfq_mixed_run(rfq_ctx* c, const uint8_t* kind, const int64_t* max
   RFQ_CK(c, cudaEventRecord(c->ev1, s));
   c->have_output = true;
   c->timed = true;
+  lap("restore + tables");
   return RFQ_OK;
 }
 

@@ -4,6 +4,7 @@
 // every pass over XML bytes or cells is a kernel, the host does O(documents + columns) work.
 #include <cuda_runtime.h>
 #include <stdio.h>
+#include <chrono>
 #include <stdlib.h>
 #include <string.h>
 #include <algorithm>
@@ -44,6 +45,14 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
   cudaStream_t s = c->stream;
   const uint32_t n = c->n_docs;
   static const bool why = getenv("RFQ_SHEET_WHY") != nullptr;   // say on stderr why a sheet is declined
+  static const bool host_prof = getenv("RFQ_HOST_PROFILE") != nullptr;   // host time of every stage on stderr
+  auto t_prev = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what) {
+    if (!host_prof) return;
+    const auto t = std::chrono::steady_clock::now();
+    fprintf(stderr, "rfq_sheets_run host %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t - t_prev).count());
+    t_prev = t;
+  };
   if (!c->nested) c->prof.begin();
   g_prof = &c->prof;
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
@@ -103,7 +112,9 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
   RFQ_CK(c, cudaMemcpyAsync(h_tot + 1, xa.cell_base + n, 4, cudaMemcpyDeviceToHost, s));
   RFQ_CK(c, cudaMemcpyAsync(h_tot + 2, xa.si_base + n, 4, cudaMemcpyDeviceToHost, s));
   RFQ_CK(c, cudaStreamSynchronize(s));
+  lap("sync");
   xa.n_rows = h_tot[0]; xa.n_cells = h_tot[1]; xa.n_si = h_tot[2];
+  lap("before 2");
   // ---- 2. positions, shared strings, rows, cells
   uint64_t sst_bytes = 0;
   for (uint32_t d = 0; d < n; ++d) if (kind[d] & 1) sst_bytes += c->h_doc_len[d];
@@ -123,6 +134,8 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
   XDocShape* h_shape = (XDocShape*)((uint8_t*)c->h_down.p + 256);
   RFQ_CK(c, cudaMemcpyAsync(h_shape, xa.shape, sizeof(XDocShape) * n, cudaMemcpyDeviceToHost, s));
   RFQ_CK(c, cudaStreamSynchronize(s));
+  lap("sync");
+  lap("before 3");
   // ---- 3. table shapes
   std::vector<TDoc> td(n);
   std::vector<uint32_t> item_base(n + 1), slot_r0(n + 1), r2_base(n + 1);
@@ -157,6 +170,7 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
   }
   item_base[n] = (uint32_t)n_items; slot_r0[n] = (uint32_t)n_slots; r2_base[n] = (uint32_t)n_r2;
   if (n_slots >= (1ull << 31) || n_items >= (1ull << 31)) { c->err = "batch too large"; return RFQ_ERR_ARG; }
+  lap("before 4");
   // ---- 4. sheet-row -> <row> element map, header cells
   RFQ_CK(c, c->h_up.reserve(sizeof(TDoc) * (n + 1) + 16ull * (n + 2) + 8192));
   Up up2((uint8_t*)c->h_up.p);
@@ -189,23 +203,35 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
     RFQ_CK(c, cudaMemcpyAsync(h_hmeta, d_hmeta, 8ull * n_cols, cudaMemcpyDeviceToHost, s));
   }
   RFQ_CK(c, cudaStreamSynchronize(s));
+  lap("sync");
+  lap("before 5");
   // ---- 5. column names (python engine: blank -> "Unnamed: k", duplicates mangled)
   std::vector<uint32_t> name_off(n_cols), name_len(n_cols), name_cp(n_cols);
   std::string names;
-  // sheets cut from one template share their header row: labels are built once per distinct row
-  struct HdrTexts { bool ok = true; std::vector<std::string> disp; std::vector<uint32_t> ncp; std::string empty; };
+  // sheets cut from one template share their header row: labels are built once per distinct row and stored
+  // once; a batch of many small sheets spends its host time here, so the per-sheet parts run on host threads
+  struct HdrTexts {
+    bool ok = true; std::vector<std::string> disp; std::vector<uint32_t> ncp; std::string empty;
+    uint32_t empty_off = 0, hdr_extra = 0; std::vector<uint32_t> off;   // where the texts sit in `names`
+  };
   std::unordered_map<std::string, HdrTexts> hdr_cache;
-  std::string hkey;
-  for (uint32_t d = 0; d < n; ++d) {
-    TDoc& T = td[d];
-    if (!T.active) continue;
-    hkey.clear();
+  std::vector<std::string> hkeys(n);
+  parallel_for(n, [&](uint32_t d) {
+    const TDoc& T = td[d];
+    if (!T.active) return;
+    std::string& hkey = hkeys[d];
     for (uint32_t j = 0; j < T.W; ++j) {
       const uint32_t g = T.col_base + j, len = h_hmeta[2 * g + 1];
       hkey.append((const char*)&h_hmeta[2 * g], 8);
       if (len != 0xFFFFFFFFu) hkey.append((const char*)h_hdr + (size_t)g * 256, std::min<uint32_t>(len, 256));
       if (h_hmeta[2 * g] == CM_FLOAT) hkey.append((const char*)h_hdr + (size_t)g * 256 + 240, 8);   // the value itself
     }
+  });
+  std::vector<const HdrTexts*> hdr_of(n, nullptr);
+  for (uint32_t d = 0; d < n; ++d) {
+    TDoc& T = td[d];
+    if (!T.active) continue;
+    const std::string& hkey = hkeys[d];
     auto hit = hdr_cache.find(hkey);
     if (hit == hdr_cache.end()) {
       HdrTexts H;
@@ -260,23 +286,36 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
           display_labels(shown, H.disp, H.ncp, &no_blank);
         }
       }
+      if (H.ok) {
+        H.empty_off = (uint32_t)names.size();
+        names += H.empty;
+        H.off.resize(T.W);
+        for (uint32_t j = 0; j < T.W; ++j) {
+          H.off[j] = (uint32_t)names.size();
+          H.hdr_extra += (uint32_t)H.disp[j].size() - H.ncp[j];
+          names += H.disp[j];
+        }
+      }
       hit = hdr_cache.emplace(hkey, std::move(H)).first;
     }
-    const HdrTexts& H = hit->second;
+    hdr_of[d] = &hit->second;       // (node addresses of an unordered_map are stable)
+  }
+  parallel_for(n, [&](uint32_t d) {
+    TDoc& T = td[d];
+    if (!T.active) return;
+    const HdrTexts& H = *hdr_of[d];
     if (!H.ok) {
       if (why) fprintf(stderr, "rfq sheet %u declined: header labels\n", d);
-      T.active = 0; c->r_status[d] = RFQ_DOC_UNSUPPORTED; continue;
+      T.active = 0; c->r_status[d] = RFQ_DOC_UNSUPPORTED; return;
     }
-    T.empty_off = (uint32_t)names.size(); T.empty_len = (uint32_t)H.empty.size();
-    names += H.empty;
+    T.empty_off = H.empty_off; T.empty_len = (uint32_t)H.empty.size();
     T.banner_off = 0; T.banner_len = 0;
+    T.hdr_extra += H.hdr_extra;
     for (uint32_t j = 0; j < T.W; ++j) {
-      uint32_t g = T.col_base + j;
-      name_off[g] = (uint32_t)names.size(); name_len[g] = (uint32_t)H.disp[j].size(); name_cp[g] = H.ncp[j];
-      T.hdr_extra += (uint32_t)H.disp[j].size() - H.ncp[j];
-      names += H.disp[j];
+      const uint32_t g = T.col_base + j;
+      name_off[g] = H.off[j]; name_len[g] = (uint32_t)H.disp[j].size(); name_cp[g] = H.ncp[j];
     }
-  }
+  });
   // a document that turned unsupported keeps its slots and columns but gets no work items
   {
     uint64_t it = 0;
@@ -323,6 +362,7 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
   RFQ_CK(c, cudaMemsetAsync(ta.doc_flags, 0, 4ull * (n + 1), s));
   RFQ_CK(c, cudaMemsetAsync(ta.doc_linew, 0, 4ull * (n + 1), s));
   RFQ_CK(c, cudaMemsetAsync(ta.x_colflags, 0, 4ull * (n_cols + 1), s));
+  lap("before 6");
   // ---- 6. infer, measure, lay out, emit (shared with the CSV path)
   table_stat_init(ta, s);
   xlsx_table_classify(ta, s);
@@ -343,6 +383,7 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
     RFQ_CK(c, cudaMemcpyAsync(h_flags, ta.doc_flags, 4ull * n, cudaMemcpyDeviceToHost, s));
   }
   RFQ_CK(c, cudaStreamSynchronize(s));
+  lap("sync");
   const uint64_t total = *h_total;
   uint8_t* d_text = c->pool.alloc<uint8_t>(total + 64);
   if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
