@@ -52,11 +52,11 @@ __global__ void __launch_bounds__(64) json_measure_kernel(const uint8_t* __restr
     const uint32_t base = s_base;
     if (base >= n_docs) return;
     const uint8_t* p = json_stage(arena, doc_off, doc_len, n_docs, base, smem);
-    if (!p) continue;
     const uint32_t d = base + threadIdx.x;
     JsonResult r;
-    json_pretty(p, doc_len[d], nullptr, json_keys_of(keys, doc_off, d), &r);
-    res[d] = r;
+    // every lane walks (a lane without a document walks an empty one): the walk votes once per byte
+    json_pretty(p ? p : arena, p ? doc_len[d] : 0u, nullptr, p ? json_keys_of(keys, doc_off, d) : nullptr, &r);
+    if (p) res[d] = r;
   }
 }
 
@@ -73,15 +73,17 @@ __global__ void __launch_bounds__(64) json_emit_kernel(const uint8_t* __restrict
     const uint32_t base = s_base;
     if (base >= n_docs) return;
     const uint8_t* p = json_stage(arena, doc_off, doc_len, n_docs, base, smem);
-    if (!p) continue;
     const uint32_t d = base + threadIdx.x;
-    if (res[d].status != JS_OK) continue;
-    uint8_t* o = out + out_off[d];
-    const char* banner = "=== JSON Data ===\n";
-    uint32_t k = 0;
-    for (; banner[k]; ++k) o[k] = (uint8_t)banner[k];
+    const bool mine = p && res[d].status == JS_OK;
+    uint8_t* o = mine ? out + out_off[d] : nullptr;
+    if (mine) {
+      const char* banner = "=== JSON Data ===\n";
+      uint32_t k = 0;
+      for (; banner[k]; ++k) o[k] = (uint8_t)banner[k];
+      o += k;
+    }
     JsonResult r;
-    json_pretty(p, doc_len[d], o + k, json_keys_of(keys, doc_off, d), &r);
+    json_pretty(mine ? p : arena, mine ? doc_len[d] : 0u, o, mine ? json_keys_of(keys, doc_off, d) : nullptr, &r);
   }
 }
 

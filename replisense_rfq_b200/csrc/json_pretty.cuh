@@ -29,6 +29,11 @@
 namespace rfq {
 
 #define RFQ_JSON_MAX_DEPTH 96
+#ifdef __CUDA_ARCH__
+#define RFQ_JSON_ANY(x) __any_sync(0xffffffffu, (x))
+#else
+#define RFQ_JSON_ANY(x) (x)
+#endif
 enum { JS_OK = 0, JS_INVALID = 1, JS_UNSUPPORTED = 2 };
 // json.JSONDecodeError messages
 enum { JE_NONE = 0, JE_VALUE, JE_PROPNAME, JE_COLON, JE_COMMA, JE_EXTRA, JE_UNTERMINATED, JE_CTRL, JE_ESCAPE,
@@ -434,7 +439,9 @@ struct JsonFrame { uint32_t key0; };
 // Parses p[0, len) and pretty-prints it into out (or only measures when out == nullptr).
 // keys: scratch of 2 * (len / 4 + 2) uint32 for the duplicate-key test (may be nullptr: then every document
 // with an object of two keys or more is declined).
-RFQ_HD void json_pretty(const uint8_t* p, uint32_t len, uint8_t* out, uint32_t* keys, JsonResult* res) {
+// (first formulation: nested loops per token.  Kept for the host tests, which run it beside the flat machine
+// below; a GPU thread runs the flat one, whose lanes meet again after every byte.)
+RFQ_HD void json_pretty_nested(const uint8_t* p, uint32_t len, uint8_t* out, uint32_t* keys, JsonResult* res) {
   res->status = JS_OK; res->err = JE_NONE; res->pos = 0; res->line = 1; res->col = 1; res->out_bytes = 0;
   JsonSink sink{out, 0};
   uint32_t err = 0, at = 0;
@@ -573,6 +580,222 @@ RFQ_HD void json_pretty(const uint8_t* p, uint32_t len, uint8_t* out, uint32_t* 
     return;
   }
 fail:
+  res->status = JS_INVALID; res->err = err;
+  json_locate(p, len, at, res);
+}
+
+// ---- the same walk as ONE loop over the bytes -----------------------------------------------------------
+// Every iteration takes one byte (an escape sequence, a literal or the end of a number take a bounded few
+// more) and switches on the state, so the 32 documents of a warp, each somewhere else in the grammar, run
+// the iteration together and part only inside it.  Same results as json_pretty_nested, byte for byte and
+// error for error (tests/test_json.py runs both).
+RFQ_HD void json_pretty(const uint8_t* p, uint32_t len, uint8_t* out, uint32_t* keys, JsonResult* res) {
+  res->status = JS_OK; res->err = JE_NONE; res->pos = 0; res->line = 1; res->col = 1; res->out_bytes = 0;
+  JsonSink sink{out, 0};
+  uint32_t err = 0, at = 0;
+  bool unsup = false;
+  {
+    struct Acc { const uint8_t* p; uint32_t n; RFQ_HD uint32_t operator()(int64_t k) const { return (k >= 0 && k < (int64_t)n) ? p[k] : 0u; } };
+    const Acc B{p, len};
+    for (uint32_t k = 0; k < len;) {
+      const uint32_t c = p[k];
+      if (c < 0x80) { ++k; continue; }
+      const int l = u8_lead_len(c);
+      if (l == 0 || !u8_seq_valid(B, (int64_t)k)) { unsup = true; break; }
+      k += (uint32_t)l;
+    }
+  }
+  {
+    enum { S_VALUE, S_AFTER, S_OBJ_OPEN, S_ARR_OPEN, S_KEY_EXPECT, S_COLON, S_STR, S_NUM_MINUS, S_NUM_ZERO, S_NUM_INT,
+           S_NUM_FRAC, S_NUM_EXP, S_DONE, S_FAIL };
+    const uint32_t END = 0x100u;                       // the byte after the last one
+    uint64_t is_obj[(RFQ_JSON_MAX_DEPTH + 63) / 64] = {0};
+    uint32_t key0[RFQ_JSON_MAX_DEPTH];
+    uint32_t depth = 0, n_keys = 0, i = 0, st = S_VALUE;
+    if (unsup) st = S_FAIL;
+    else if (len >= 3 && p[0] == 0xEF && p[1] == 0xBB && p[2] == 0xBF) { err = JE_BOM; at = 0; st = S_FAIL; }
+    uint32_t str_begin = 0, num_begin = 0;
+    bool lone = false, is_key = false, key_esc = false, num_float = false;
+    // On the GPU the loop is left by the whole warp at once: the vote brings the 32 documents back together
+    // after every byte (without it the compiler threads each state straight into the next and the lanes never
+    // meet again).  All 32 lanes of a warp must therefore call this function together.
+    while (RFQ_JSON_ANY(st < S_DONE)) {
+      if (st < S_DONE) {
+      const uint32_t c = i < len ? p[i] : END;
+      switch (st) {
+        case S_VALUE: {
+          if (json_ws(c)) { ++i; break; }
+          if (c == '"') { str_begin = i; is_key = false; sink.put('"'); ++i; st = S_STR; break; }
+          if (c == '{') { ++i; st = S_OBJ_OPEN; break; }
+          if (c == '[') { ++i; st = S_ARR_OPEN; break; }
+          if (c == '-') {
+            if (i + 9 <= len && p[i + 1] == 'I' && p[i + 2] == 'n' && p[i + 3] == 'f' && p[i + 4] == 'i' && p[i + 5] == 'n' &&
+                p[i + 6] == 'i' && p[i + 7] == 't' && p[i + 8] == 'y') { sink.puts("-Infinity"); i += 9; st = S_AFTER; break; }
+            num_begin = i; num_float = false; ++i; st = S_NUM_MINUS; break;
+          }
+          if (c >= '0' && c <= '9') { num_begin = i; num_float = false; ++i; st = c == '0' ? S_NUM_ZERO : S_NUM_INT; break; }
+          {
+            const char* w = c == 'n' ? "null" : c == 't' ? "true" : c == 'f' ? "false" : c == 'N' ? "NaN" : c == 'I' ? "Infinity" : nullptr;
+            uint32_t k = 0;
+            if (w) while (w[k] && i + k < len && p[i + k] == (uint8_t)w[k]) ++k;
+            if (!w || w[k]) { err = JE_VALUE; at = i; st = S_FAIL; goto next; }
+            sink.puts(w); i += k; st = S_AFTER;
+          }
+          break;
+        }
+        case S_OBJ_OPEN: case S_ARR_OPEN: {
+          if (json_ws(c)) { ++i; break; }
+          const bool obj = st == S_OBJ_OPEN;
+          if (c == (obj ? (uint32_t)'}' : (uint32_t)']')) { sink.put(obj ? '{' : '['); sink.put(c); ++i; st = S_AFTER; break; }
+          if (depth >= RFQ_JSON_MAX_DEPTH) { unsup = true; st = S_FAIL; goto next; }
+          if (obj) is_obj[depth >> 6] |= 1ull << (depth & 63); else is_obj[depth >> 6] &= ~(1ull << (depth & 63));
+          key0[depth] = n_keys;
+          ++depth;
+          sink.put(obj ? '{' : '['); sink.newline_indent(depth);
+          if (!obj) { st = S_VALUE; break; }                       // the same byte again, as a value
+          if (c != '"') { err = JE_PROPNAME; at = i; st = S_FAIL; goto next; }
+          str_begin = i; is_key = true; key_esc = false; sink.put('"'); ++i; st = S_STR;
+          break;
+        }
+        case S_KEY_EXPECT: {
+          if (json_ws(c)) { ++i; break; }
+          if (c != '"') { err = JE_PROPNAME; at = i; st = S_FAIL; goto next; }
+          str_begin = i; is_key = true; key_esc = false; sink.put('"'); ++i; st = S_STR;
+          break;
+        }
+        case S_COLON: {
+          if (json_ws(c)) { ++i; break; }
+          if (c != ':') { err = JE_COLON; at = i; st = S_FAIL; goto next; }
+          ++i; sink.put(':'); sink.put(' '); st = S_VALUE;
+          break;
+        }
+        case S_STR: {
+          if (c == END) { err = JE_UNTERMINATED; at = str_begin; st = S_FAIL; goto next; }
+          if (c == '"') {
+            sink.put('"'); ++i;
+            if (!is_key) { st = S_AFTER; break; }
+            // a key ends: equal keys inside one object are declined (dict semantics are not a streaming transformation)
+            const uint32_t k_begin = str_begin + 1, k_end = i - 1, first = key0[depth - 1];
+            if (n_keys > first) {
+              if (!keys) { unsup = true; st = S_FAIL; goto next; }
+              for (uint32_t q = first; q < n_keys; ++q) {
+                const uint32_t b0 = keys[2 * q] & 0x7FFFFFFFu, b1 = keys[2 * q + 1];
+                if (json_keys_equal(p, b0, b1, k_begin, k_end, key_esc || (keys[2 * q] >> 31))) { unsup = true; st = S_FAIL; goto next; }
+              }
+            }
+            if (keys) { keys[2 * n_keys] = k_begin | (key_esc ? 0x80000000u : 0u); keys[2 * n_keys + 1] = k_end; }
+            ++n_keys;
+            st = S_COLON;
+            break;
+          }
+          if (c < 0x20) { err = JE_CTRL; at = i; st = S_FAIL; goto next; }
+          if (c != '\\') { sink.put(c); ++i; break; }
+          // an escape: two bytes, six for \uXXXX, twelve for a surrogate pair
+          key_esc = true;
+          if (i + 1 >= len) { err = JE_UNTERMINATED; at = str_begin; st = S_FAIL; goto next; }
+          const uint32_t e = p[i + 1];
+          uint32_t cp;
+          if (e != 'u') {
+            switch (e) {
+              case '"': cp = '"'; break;
+              case '\\': cp = '\\'; break;
+              case '/': cp = '/'; break;
+              case 'b': cp = 8; break;
+              case 'f': cp = 12; break;
+              case 'n': cp = 10; break;
+              case 'r': cp = 13; break;
+              case 't': cp = 9; break;
+              default: err = JE_ESCAPE; at = i; st = S_FAIL; goto next;
+            }
+            i += 2;
+          } else {
+            if (i + 6 >= len) { err = JE_UESCAPE; at = i + 1; st = S_FAIL; goto next; }   // (_json.c wants a character after the four digits)
+            cp = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const int h = json_hex(p[i + 2 + k]);
+              if (h < 0) { err = JE_UESCAPE; at = i + 1; st = S_FAIL; goto next; }
+              cp = cp * 16 + (uint32_t)h;
+            }
+            i += 6;
+            if (cp >= 0xD800 && cp <= 0xDBFF && i + 6 < len && p[i] == '\\' && p[i + 1] == 'u') {
+              uint32_t c2 = 0;
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const int h = json_hex(p[i + 2 + k]);
+                if (h < 0) { err = JE_UESCAPE; at = i + 1; st = S_FAIL; goto next; }
+                c2 = c2 * 16 + (uint32_t)h;
+              }
+              if (c2 >= 0xDC00 && c2 <= 0xDFFF) { cp = 0x10000 + (((cp - 0xD800) << 10) | (c2 - 0xDC00)); i += 6; }
+            }
+            if (cp >= 0xD800 && cp <= 0xDFFF) lone = true;
+          }
+          // encode_basestring
+          if (cp == '"' || cp == '\\') { sink.put('\\'); sink.put(cp); }
+          else if (cp == 10) { sink.put('\\'); sink.put('n'); }
+          else if (cp == 13) { sink.put('\\'); sink.put('r'); }
+          else if (cp == 9) { sink.put('\\'); sink.put('t'); }
+          else if (cp == 8) { sink.put('\\'); sink.put('b'); }
+          else if (cp == 12) { sink.put('\\'); sink.put('f'); }
+          else if (cp < 0x20) {
+            sink.put('\\'); sink.put('u'); sink.put('0'); sink.put('0');
+            sink.put("0123456789abcdef"[cp >> 4]); sink.put("0123456789abcdef"[cp & 15]);
+          }
+          else if (cp < 0x80) sink.put(cp);
+          else if (cp < 0x800) { sink.put(0xC0 | (cp >> 6)); sink.put(0x80 | (cp & 0x3F)); }
+          else if (cp < 0x10000) { sink.put(0xE0 | (cp >> 12)); sink.put(0x80 | ((cp >> 6) & 0x3F)); sink.put(0x80 | (cp & 0x3F)); }
+          else { sink.put(0xF0 | (cp >> 18)); sink.put(0x80 | ((cp >> 12) & 0x3F)); sink.put(0x80 | ((cp >> 6) & 0x3F)); sink.put(0x80 | (cp & 0x3F)); }
+          break;
+        }
+        case S_NUM_MINUS: {
+          if (c >= '0' && c <= '9') { ++i; st = c == '0' ? S_NUM_ZERO : S_NUM_INT; break; }
+          err = JE_VALUE; at = num_begin; st = S_FAIL; goto next;
+        }
+        case S_NUM_ZERO: case S_NUM_INT: case S_NUM_FRAC: case S_NUM_EXP: {
+          if (c >= '0' && c <= '9' && st != S_NUM_ZERO) { ++i; break; }
+          if (c == '.' && (st == S_NUM_ZERO || st == S_NUM_INT) && i + 1 < len && p[i + 1] >= '0' && p[i + 1] <= '9') {
+            i += 2; num_float = true; st = S_NUM_FRAC; break;
+          }
+          if ((c == 'e' || c == 'E') && st != S_NUM_EXP) {
+            uint32_t k = i + 1;
+            if (k < len && (p[k] == '+' || p[k] == '-')) ++k;
+            if (k < len && p[k] >= '0' && p[k] <= '9') { i = k + 1; num_float = true; st = S_NUM_EXP; break; }
+          }
+          // the number ends before this byte
+          if (!num_float) {
+            const bool neg = p[num_begin] == '-';
+            const uint32_t nd = i - num_begin - (neg ? 1u : 0u);
+            if (nd > 4300) { unsup = true; st = S_FAIL; goto next; }     // int() refuses: ValueError, another message
+            if (neg && nd == 1 && p[num_begin + 1] == '0') sink.put('0');  // int("-0") is 0
+            else sink.copy(p + num_begin, i - num_begin);
+          } else if (!json_float(p + num_begin, i - num_begin, &sink)) { unsup = true; st = S_FAIL; goto next; }
+          st = S_AFTER;
+          break;                                                          // the same byte again, after a value
+        }
+        case S_AFTER: {
+          if (json_ws(c)) { ++i; break; }
+          if (depth == 0) {
+            if (c != END) { err = JE_EXTRA; at = i; st = S_FAIL; goto next; }
+            st = S_DONE;
+            break;
+          }
+          const bool obj = (is_obj[(depth - 1) >> 6] >> ((depth - 1) & 63)) & 1ull;
+          if (c == ',') { ++i; sink.put(','); sink.newline_indent(depth); st = obj ? S_KEY_EXPECT : S_VALUE; break; }
+          if (c == (obj ? (uint32_t)'}' : (uint32_t)']')) {
+            ++i; --depth; n_keys = key0[depth];
+            sink.newline_indent(depth); sink.put(c);
+            break;
+          }
+          err = JE_COMMA; at = i; st = S_FAIL; goto next;
+        }
+        default: st = S_DONE; break;
+      }
+      next:;
+      }
+    }
+    if (unsup || (st == S_DONE && lone)) { res->status = JS_UNSUPPORTED; return; }
+    if (st == S_DONE) { res->out_bytes = sink.n; return; }
+  }
   res->status = JS_INVALID; res->err = err;
   json_locate(p, len, at, res);
 }

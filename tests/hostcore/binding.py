@@ -177,3 +177,10 @@ def json_pretty(doc: bytes):
     if st == 1:
         return 1, "%s: line %d column %d (char %d)" % (JSON_ERRORS[info[0]], info[2], info[3], info[1])
     return st, None
+
+
+def json_nested(on: bool) -> None:
+    """Select the nested-loop formulation of json_pretty.cuh (default: the flat state machine the GPU runs)."""
+    L = lib()
+    L.hc_json_nested.argtypes = [C.c_int]
+    L.hc_json_nested(1 if on else 0)

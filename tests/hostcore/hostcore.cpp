@@ -717,16 +717,21 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
 #include "../../replisense_rfq_b200/csrc/json_pretty.cuh"
 extern "C" {
 // returns status (0 ok, 1 invalid, 2 unsupported); info = {err, pos, line, col}; text written to out (cap bytes)
+static int g_json_nested = 0;
+void hc_json_nested(int on) { g_json_nested = on; }
 int hc_json_pretty(const uint8_t* doc, uint32_t len, uint8_t* out, uint64_t cap, uint64_t* out_len, uint32_t* info) {
   std::vector<uint32_t> keys(2 * ((size_t)len / 4 + 2));
   rfq::JsonResult r;
-  rfq::json_pretty(doc, len, nullptr, keys.data(), &r);
+  auto run = [&](uint8_t* o, rfq::JsonResult* rr) {
+    if (g_json_nested) rfq::json_pretty_nested(doc, len, o, keys.data(), rr); else rfq::json_pretty(doc, len, o, keys.data(), rr);
+  };
+  run(nullptr, &r);
   info[0] = r.err; info[1] = r.pos; info[2] = r.line; info[3] = r.col;
   *out_len = r.out_bytes;
   if (r.status != rfq::JS_OK) return (int)r.status;
   if (r.out_bytes > cap) return -1;
   rfq::JsonResult r2;
-  rfq::json_pretty(doc, len, out, keys.data(), &r2);
+  run(out, &r2);
   if (r2.status != rfq::JS_OK || r2.out_bytes != r.out_bytes) return -2;
   return 0;
 }

@@ -37,9 +37,20 @@ def _model(data: bytes):
     return None, "declined"
 
 
-def test_host_model_matches_goldens_and_fuzz():
-    """json_pretty.cuh compiled for the host: every golden, 3000 valid and 3000 broken documents; declines
-    only what DESIGN.md §4 lists (not UTF-8, duplicate keys, lone surrogates)."""
+@pytest.mark.parametrize("nested", [False, True])
+def test_host_model_matches_goldens_and_fuzz(nested):
+    """json_pretty.cuh compiled for the host — the flat state machine the GPU runs, and the nested-loop
+    formulation beside it: every golden, 3000 valid and 3000 broken documents; declines only what DESIGN.md
+    §4 lists (not UTF-8, duplicate keys, lone surrogates)."""
+    from tests.hostcore import binding as H
+    H.json_nested(nested)
+    try:
+        _check_model()
+    finally:
+        H.json_nested(False)
+
+
+def _check_model():
     docs = [base64.b64decode(c["in"]) for c in GOLD]
     docs += [corpus.json_doc(s) for s in range(1000, 4000)] + [corpus.json_doc_broken(s) for s in range(1000, 4000)]
     declined = 0
