@@ -356,8 +356,11 @@ def main():
     sampler.join()
     # and once more all the way to a Python str (what FileParser._parse_csv_sync returns)
     t0 = time.perf_counter()
-    txt = eng.csv_parse_arena(arena, offsets, lengths, mr).doc_str(0)
+    res_ = eng.csv_parse_arena(arena, offsets, lengths, mr)
+    t1 = time.perf_counter()
+    txt = res_.doc_str(0)
     t_str = time.perf_counter() - t0
+    t_str_only = time.perf_counter() - t1
     assert txt.isascii() == (len(txt) == out_bytes)
     del txt
     # e2e_python: file bytes -> str through the reference-facing method FileParser._parse_csv_sync
@@ -423,7 +426,7 @@ def main():
         "e2e": {"value": total_mb / t_pipe, "unit": UNIT, "h2d_bytes_per_step": nbytes,
                 "d2h_bytes_per_step": out_bytes + 64, "ms_per_step": t_pipe / args.steps * 1e3,
                 "in_flight": depth, "serial_value": total_mb / t_e2e,
-                "serial_ms_per_step": t_e2e / args.steps * 1e3, "to_python_str_ms": t_str * 1e3,
+                "serial_ms_per_step": t_e2e / args.steps * 1e3, "to_python_str_ms": t_str * 1e3, "str_build_only_ms": t_str_only * 1e3,
                 "frac_of_copy_ceiling": pc_both / (t_pipe / args.steps)},
         # the copies alone on this box, all ranks at once (max over ranks): what e2e / e2e_prompt are bounded by
         "copy_ceiling": {"h2d_ms": pc_h2d * 1e3, "d2h_ms": pc_d2h * 1e3, "both_ms": pc_both * 1e3,

@@ -1,6 +1,7 @@
 // C-ABI layer (include/rfq_parse.h): context, device/pinned memory pools, staging, fetch.
 // Host-side orchestration only; every byte of parsing happens in the kernels.
 #include <cuda_runtime.h>
+#include <sys/mman.h>
 #include <stdio.h>
 #include <string.h>
 #include <algorithm>
@@ -766,8 +767,29 @@ int rfq_out_widen(const rfq_ctx* c, uint32_t d, int unit, void* dst, uint64_t n_
     }
   }
   std::vector<std::thread> th;
+  // the pages of a fresh str have never been touched: ask for huge ones where the kernel hands them out on request
+  {
+    const uintptr_t a0 = ((uintptr_t)dst + (2u << 20) - 1) & ~(uintptr_t)((2u << 20) - 1);
+    const uintptr_t a1 = ((uintptr_t)dst + n_chars * (uint64_t)unit) & ~(uintptr_t)((2u << 20) - 1);
+    if (a1 > a0) madvise((void*)a0, a1 - a0, MADV_HUGEPAGE);
+  }
+  if (unit == 1 && n_chars == len) {
+    // every byte starts a character: the text is ASCII and the str is a copy of it
+    auto copy = [&](unsigned t) { memcpy((uint8_t*)dst + cut[t], p + cut[t], cut[t + 1] - cut[t]); };
+    if (nt == 1) copy(0); else { for (unsigned t = 0; t < nt; ++t) th.emplace_back(copy, t); for (auto& x : th) x.join(); }
+    return RFQ_OK;
+  }
   uint64_t cnt[16] = {0};
-  auto count = [&](unsigned t) { uint64_t k = 0; for (uint64_t i = cut[t]; i < cut[t + 1]; ++i) k += (p[i] & 0xC0) != 0x80; cnt[t] = k; };
+  auto count = [&](unsigned t) {
+    uint64_t k = 0, i = cut[t];
+    const uint64_t e = cut[t + 1];
+    for (; i + 8 <= e; i += 8) {     // eight bytes at a time: continuation bytes are 10xxxxxx
+      uint64_t x; memcpy(&x, p + i, 8);
+      k += 8 - (uint64_t)__builtin_popcountll((x >> 7) & ~(x >> 6) & 0x0101010101010101ull);
+    }
+    for (; i < e; ++i) k += (p[i] & 0xC0) != 0x80;
+    cnt[t] = k;
+  };
   if (nt == 1) count(0); else { for (unsigned t = 0; t < nt; ++t) th.emplace_back(count, t); for (auto& x : th) x.join(); th.clear(); }
   before[0] = 0;
   for (unsigned t = 0; t < nt; ++t) before[t + 1] = before[t] + cnt[t];
@@ -776,6 +798,16 @@ int rfq_out_widen(const rfq_ctx* c, uint32_t d, int unit, void* dst, uint64_t n_
     uint64_t o = before[t];
     uint8_t* d1 = (uint8_t*)dst; uint16_t* d2 = (uint16_t*)dst; uint32_t* d4 = (uint32_t*)dst;
     for (uint64_t i = cut[t]; i < cut[t + 1];) {
+      if (i + 8 <= cut[t + 1]) {       // a run of ASCII is widened eight characters at a time
+        uint64_t x; memcpy(&x, p + i, 8);
+        if (!(x & 0x8080808080808080ull)) {
+          if (unit == 1) memcpy(d1 + o, &x, 8);
+          else if (unit == 2) for (int q = 0; q < 8; ++q) d2[o + q] = (uint16_t)((x >> (8 * q)) & 0xFF);
+          else for (int q = 0; q < 8; ++q) d4[o + q] = (uint32_t)((x >> (8 * q)) & 0xFF);
+          o += 8; i += 8;
+          continue;
+        }
+      }
       uint32_t b = p[i], cp; int l;
       if (b < 0x80) { cp = b; l = 1; }
       else if (b < 0xE0) { cp = ((b & 0x1Fu) << 6) | (p[i + 1] & 0x3Fu); l = 2; }
