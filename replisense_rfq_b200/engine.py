@@ -204,6 +204,37 @@ class Engine:
         offsets, lengths, total = a.pack(docs)
         return a, offsets, lengths
 
+    def read_file(self, path) -> "tuple[PinnedArena, np.ndarray, np.ndarray]":
+        """The bytes of one file read straight into this engine's pinned arena (no bytes object, no second
+        copy): what a file-level parser stages.  Call with the engine lock held, like _pack."""
+        import os
+        with open(path, "rb", buffering=0) as f:
+            n = os.fstat(f.fileno()).st_size
+            a = self.arena(((n + 15) & ~15) + 64)
+            got, mv = 0, memoryview(a.view)
+            while got < n:
+                k = f.readinto(mv[got:n])
+                if not k:
+                    break
+                got += k
+        return a, np.zeros(1, dtype=np.uint64), np.array([got], dtype=np.uint64)
+
+    def parse_csv_file(self, path, max_rows=1000) -> "str | None":
+        """raw_text of one .csv file (None = every (encoding, separator) attempt failed); raises EngineError for a
+        construct the GPU path declines."""
+        with self.lock:
+            a, off, ln = self.read_file(path)
+            mr = self._mr(1, max_rows)
+            self._check(self.lib.rfq_csv_parse(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data, 1, mr.ctypes.data),
+                        "rfq_csv_parse")
+            r = BatchResult(self)
+            st = int(r.status[0])
+            if st == _lib.DOC_OK:
+                return r.doc_str(0)
+            if st == _lib.DOC_CSV_UNPARSEABLE:
+                return None
+            raise EngineError(f"document 0: unsupported construct on the GPU path (status {st})")
+
     def stage(self, arena: PinnedArena, offsets: np.ndarray, lengths: np.ndarray):
         self._check(self.lib.rfq_stage(self.ctx, arena.ptr, offsets.ctypes.data,
                                        lengths.ctypes.data, len(offsets)), "rfq_stage")
@@ -226,6 +257,13 @@ class Engine:
                                                 len(docs)), "rfq_text_parse")
             r = BatchResult(self)
             return [r.doc_str(d) for d in range(r.n)]
+
+    def parse_text_file(self, path) -> str:
+        """raw_text of one .txt file, read straight into pinned memory."""
+        with self.lock:
+            a, off, ln = self.read_file(path)
+            self._check(self.lib.rfq_text_parse(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data, 1), "rfq_text_parse")
+            return BatchResult(self).doc_str(0)
 
     # -- file hashes (app/file_parser.py:122-130), one batch
     def md5_many(self, docs: Sequence[bytes]) -> "list[str]":

@@ -120,8 +120,7 @@ class FileParser:
 
     # ------------------------------------------------------------------ text (:143-159)
     async def _parse_txt_async(self, file_path: Path) -> str:
-        data = Path(file_path).read_bytes()
-        return self.engine.parse_text_many([data])[0]
+        return self.engine.parse_text_file(file_path)
 
     # ------------------------------------------------------------------ csv (:288-313)
     async def _parse_csv_async(self, file_path: Path) -> str:
@@ -130,8 +129,7 @@ class FileParser:
 
     def _parse_csv_sync(self, file_path: Path) -> str:
         try:
-            data = Path(file_path).read_bytes()
-            text = self.engine.parse_csv_many([data], self.max_excel_rows)[0]
+            text = self.engine.parse_csv_file(file_path, self.max_excel_rows)   # read straight into pinned memory
             if text is None:
                 raise FileParsingError(_CSV_FAIL)
             return text
