@@ -190,6 +190,43 @@ RFQ_HD XCell xlsx_parse_cell(const uint8_t* doc, uint32_t len, uint32_t cpos, co
       int dstyle = 0;
       for (uint32_t i = 0; i < n_date; ++i)
         if ((date_ids[i] & 0x7FFFFFFFu) == style) dstyle = (date_ids[i] >> 31) ? 2 : 1;
+      // The spellings writers emit — [-]digits[.digits], at most 18 digits in all — are read in ONE pass:
+      // an integer as it stands, a fraction as (double)digits / 10^k (both exact doubles, one correctly
+      // rounded division: what float(text) gives).  Everything else goes through the general parsers below.
+      {
+        uint32_t i = 0, nd = 0, nfrac = 0;
+        const bool neg = val_n && val_b[0] == '-';
+        if (neg) i = 1;
+        uint64_t w = 0;
+        bool frac = false, plain = i < val_n;
+        for (; i < val_n; ++i) {
+          const uint32_t ch = val_b[i];
+          if (ch == '.' && !frac && nd) { frac = true; continue; }
+          const uint32_t dg = ch - '0';
+          if (dg > 9u || nd == 18u) { plain = false; break; }
+          w = w * 10u + dg; ++nd;
+          if (frac) ++nfrac;
+        }
+        if (plain && nd && !(frac && nfrac == 0)) {
+          if (!frac) {
+            const int64_t iv = neg ? -(int64_t)w : (int64_t)w;
+            if (dstyle == 2) return xlsx_timedelta_cell(x, (double)iv, iv > -(1ll << 53) && iv < (1ll << 53), flags);
+            if (dstyle) return xlsx_date_cell(x, (double)iv, date1904, flags);
+            x.mode = CM_INT; x.bits = (uint64_t)iv;
+            return x;
+          }
+          if (w < (1ull << 53)) {
+            double v = RFQ_DDIV((double)w, RFQ_POW10((int)nfrac));
+            if (neg) v = -v;
+            if (dstyle == 2) return xlsx_timedelta_cell(x, v, true, flags);
+            if (dstyle) return xlsx_date_cell(x, v, date1904, flags);
+            const int64_t iv = (int64_t)v;                       // pandas _convert_cell: integral floats become ints
+            if ((double)iv == v) { x.mode = CM_INT; x.bits = (uint64_t)iv; return x; }
+            x.mode = CM_FLOAT; x.bits = dbl_bits(v);
+            return x;
+          }
+        }
+      }
       bool is_float = false;
       for (uint32_t i = 0; i < val_n; ++i) if (val_b[i] == '.' || val_b[i] == 'e' || val_b[i] == 'E') is_float = true;
       if (!is_float) {
