@@ -455,12 +455,19 @@ def main():
     if not args.no_cpu_baseline:
         rows = min(args.cpu_sample_rows, args.rows)
         sample = make_doc(rows, seed=0)
+        from oracle import ref_runner
+        use_ref = ref_runner.available()          # oracle/_ref: the reference's own file, travelled with the snapshot
         t0 = time.perf_counter()
-        O.parse_csv_bytes(sample, rows)
+        if use_ref:
+            ref_runner.parse_csv_bytes(sample, rows)
+        else:
+            O.parse_csv_bytes(sample, rows)
         dt = time.perf_counter() - t0
-        line["cpu_baseline"] = {"value": len(sample) / 1e6 / dt, "unit": UNIT, "cores": 1, "kind": "port",
-                                "sample": f"first {rows} rows of the C2 CSV through the oracle port of "
-                                          "FileParser._parse_csv_sync (pandas read_csv + to_string), "
+        what = ("the reference's own FileParser._parse_csv_sync (oracle/_ref/app/file_parser.py, unmodified)" if use_ref
+                else "the oracle port of FileParser._parse_csv_sync (pandas read_csv + to_string)")
+        line["cpu_baseline"] = {"value": len(sample) / 1e6 / dt, "unit": UNIT, "cores": 1,
+                                "kind": "reference" if use_ref else "port",
+                                "sample": f"first {rows} rows of the C2 CSV through {what}, "
                                           f"{dt:.2f} s on one host core of {os.cpu_count()}",
                                 "cells_per_s": rows * 8 / dt}
     sys.stdout.flush()
