@@ -38,7 +38,7 @@ constexpr size_t kOffDesc = 0;                                   // doc_off, doc
 constexpr size_t kOffTileCnt = 256;                              // uint32[kMaxTiles + 1]
 constexpr size_t kOffTilePre = kOffTileCnt + ((4 * (kMaxTiles + 1) + 255) & ~255u);
 constexpr size_t kOffSmall = kOffTilePre + ((4 * (kMaxTiles + 1) + 255) & ~255u);
-// small block: first_pos, last_end, skip (uint32 each, 256 B apart), out_off, out_total (u64)
+// small block: first_key, last_key (u64), skip (uint32), 256 B apart, out_off, out_total (u64)
 constexpr size_t kOffScan32 = kOffSmall + 6 * 256;               // scan partials (uint32[8])
 constexpr size_t kOffScan64 = kOffScan32 + 256;                  // scan partials (u64[8])
 constexpr size_t kUsed = kOffScan64 + 256;
@@ -102,8 +102,8 @@ extern "C" int rfq_text_normalise_noalloc(int device, const uint8_t* d_in, uint6
     a.n_docs = 1; a.n_tiles = n_tiles;
     a.tile_cnt = (uint32_t*)(base + kOffTileCnt);
     a.tile_pre = (uint32_t*)(base + kOffTilePre);
-    a.first_pos = (uint32_t*)(base + kOffSmall);
-    a.last_end = (uint32_t*)(base + kOffSmall + 256);
+    a.first_key = (unsigned long long*)(base + kOffSmall);
+    a.last_key = (unsigned long long*)(base + kOffSmall + 256);
     a.skip = (uint32_t*)(base + kOffSmall + 512);
     a.out_off = (unsigned long long*)(base + kOffSmall + 768);
     a.out_total = (unsigned long long*)(base + kOffSmall + 1024);
@@ -111,7 +111,7 @@ extern "C" int rfq_text_normalise_noalloc(int device, const uint8_t* d_in, uint6
     a.scan_tmp32 = (uint32_t*)(base + kOffScan32);
     a.scan_tmp64 = (unsigned long long*)(base + kOffScan64);
     // The array keeps whatever the previous call left.  What must start from a known value is
-    // reset here on the same stream: first_pos / last_end (inside txt_pipeline) — everything
+    // reset here on the same stream: first_key / last_key (inside txt_pipeline) — everything
     // else is fully overwritten before it is read.
     rfq::txt_pipeline(a, s);
     rfq::txt_emit(a, d_out, s);

@@ -16,8 +16,11 @@ struct TxtArgs {
   uint32_t n_docs, n_tiles;
   uint32_t* tile_cnt;         // [n_tiles]
   uint32_t* tile_pre;         // [n_tiles]
-  uint32_t* first_pos;        // [n_docs]
-  uint32_t* last_end;         // [n_docs]
+  // strip extents, reduced over the tiles of a document with 64-bit atomics so that the winning tile also
+  // hands over what the extent step needs from it (no second look at the bytes):
+  unsigned long long* first_key;  // [n_docs] min of (first visible byte << 32 | bytes the tile emits before it)
+  unsigned long long* last_key;   // [n_docs] max of (end of the last visible character << 32 | bytes of it in the
+                                  //          next tile << 10 | bytes the tile emits before that end)
   unsigned long long* out_len;  // [n_docs]
   unsigned long long* out_off;  // [n_docs]
   unsigned long long* out_total;  // [1]

@@ -193,8 +193,8 @@ int rfq_text_run(rfq_ctx* c) {
   a.n_docs = n; a.n_tiles = nt;
   a.tile_cnt = c->pool.alloc<uint32_t>(nt + 1);
   a.tile_pre = c->pool.alloc<uint32_t>(nt + 1);
-  a.first_pos = c->pool.alloc<uint32_t>(n + 1);
-  a.last_end = c->pool.alloc<uint32_t>(n + 1);
+  a.first_key = c->pool.alloc<unsigned long long>(n + 1);
+  a.last_key = c->pool.alloc<unsigned long long>(n + 1);
   a.out_len = c->pool.alloc<unsigned long long>(n + 1);
   a.out_off = c->pool.alloc<unsigned long long>(n + 1);
   a.out_total = c->pool.alloc<unsigned long long>(1);
@@ -202,7 +202,8 @@ int rfq_text_run(rfq_ctx* c) {
   a.scan_tmp32 = c->pool.alloc<uint32_t>(scan_partials_needed(nt));
   a.scan_tmp64 = c->pool.alloc<unsigned long long>(scan_partials_needed(n));
   if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
-  c->prof.mark("txt_count+extent", s);
+  g_prof = &c->prof;
+  struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
   txt_pipeline(a, s);
   unsigned long long total = 0;
   if (n) {

@@ -129,15 +129,33 @@ __device__ __forceinline__ uint32_t find_doc(const uint32_t* __restrict__ tile_b
   return lo;
 }
 
+// The same with the whole warp: 32 probes per step, so a table of a million documents takes four dependent
+// loads instead of twenty (a batch of small bodies spends its time in this look-up, not in the bytes).
+__device__ __forceinline__ uint32_t find_doc_warp(const uint32_t* __restrict__ tile_base, uint32_t n, uint32_t t, int lane) {
+  uint32_t lo = 0, hi = n;                 // tile_base[lo] <= t < tile_base[hi]
+  while (hi - lo > 1) {
+    const uint32_t step = (hi - lo + 31u) / 32u;
+    const uint32_t idx = lo + (uint32_t)lane * step;
+    const uint32_t v = idx < hi ? __ldg(tile_base + idx) : 0xFFFFFFFFu;
+    const unsigned le = __ballot_sync(0xffffffffu, v <= t);   // a prefix of the lanes (lane 0 always)
+    const uint32_t k = (uint32_t)__popc(le) - 1u;
+    lo += k * step;
+    hi = min(hi, lo + step);
+  }
+  return lo;
+}
+
+__device__ __forceinline__ uint32_t below16(int64_t x) { return x <= 0 ? 0u : x >= 16 ? 0xFFFFu : ((1u << x) - 1u); }
+
 __global__ void __launch_bounds__(256) txt_count_kernel(
     const uint8_t* __restrict__ arena, const uint32_t* __restrict__ doc_off,
     const uint32_t* __restrict__ doc_len, const uint32_t* __restrict__ tile_base, uint32_t n_docs,
-    uint32_t n_tiles, uint32_t* __restrict__ tile_cnt, uint32_t* __restrict__ first_pos,
-    uint32_t* __restrict__ last_end) {
+    uint32_t n_tiles, uint32_t* __restrict__ tile_cnt, unsigned long long* __restrict__ first_key,
+    unsigned long long* __restrict__ last_key) {
   uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
   int lane = threadIdx.x & 31;
   if (t >= n_tiles) return;
-  uint32_t d = find_doc(tile_base, n_docs, t);
+  uint32_t d = find_doc_warp(tile_base, n_docs, t, lane);
   uint32_t tile = t - tile_base[d];
   uint32_t len = doc_len[d];
   const uint8_t* doc = arena + doc_off[d];
@@ -159,65 +177,50 @@ __global__ void __launch_bounds__(256) txt_count_kernel(
     fp = min(fp, __shfl_xor_sync(0xffffffffu, fp, o));
     le = max(le, __shfl_xor_sync(0xffffffffu, le, o));
   }
+  if (fp == 0xFFFFFFFFu) { if (lane == 0) tile_cnt[t] = cnt; return; }   // nothing visible in this tile
+  // what the extent step needs from the tiles that win: the bytes this tile emits before its first visible
+  // byte and before the end of its last visible character (which may reach into the next tile)
+  const uint32_t tile_end = (tile + 1) * RFQ_TILE;
+  uint32_t lead = __popc(emit & below16((int64_t)fp - base));
+  uint32_t trail = __popc(emit & below16((int64_t)min(le, tile_end) - base));
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    lead += __shfl_xor_sync(0xffffffffu, lead, o);
+    trail += __shfl_xor_sync(0xffffffffu, trail, o);
+  }
   if (lane == 0) {
     tile_cnt[t] = cnt;
-    if (fp != 0xFFFFFFFFu) {
-      atomicMin(first_pos + d, fp);
-      atomicMax(last_end + d, le);
-    }
+    const uint32_t spill = le > tile_end ? le - tile_end : 0u;           // at most 3
+    atomicMin(first_key + d, ((unsigned long long)fp << 32) | lead);
+    atomicMax(last_key + d, ((unsigned long long)le << 32) | (spill << 10) | trail);
   }
 }
 
-// rank (number of emitted bytes before doc-relative position p) inside document d
-__device__ __forceinline__ uint32_t txt_rank_before(const uint8_t* doc, uint32_t len,
-                                                    const uint32_t* __restrict__ tile_pre,
-                                                    uint32_t tb, uint32_t p, int lane) {
-  uint32_t tile = p / RFQ_TILE;
-  if (tile * RFQ_TILE >= len) return 0xFFFFFFFFu;  // caller handles p == end-of-last-tile
-  Win win; uint32_t emit, nsp;
-  txt_lane_eval(doc, len, tile, lane, win, emit, nsp);
-  uint32_t base = tile * RFQ_TILE + lane * 16;
-  uint32_t c = 0;
-  if (p > base) c = (p - base >= 16) ? __popc(emit) : __popc(emit & ((1u << (p - base)) - 1u));
-#pragma unroll
-  for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-  return tile_pre[tb + tile] + c;
-}
-
-// One warp per document: out_len and skip (global rank of the first emitted output byte).
+// One thread per document: out_len and skip (global rank of the first emitted output byte), from the keys
+// the count pass left (no second look at the bytes).
 __global__ void __launch_bounds__(256) txt_extent_kernel(
-    const uint8_t* __restrict__ arena, const uint32_t* __restrict__ doc_off,
-    const uint32_t* __restrict__ doc_len, const uint32_t* __restrict__ tile_base, uint32_t n_docs,
-    const uint32_t* __restrict__ tile_pre, const uint32_t* __restrict__ tile_cnt,
-    const uint32_t* __restrict__ first_pos, const uint32_t* __restrict__ last_end,
+    const uint32_t* __restrict__ tile_base, uint32_t n_docs, const uint32_t* __restrict__ tile_pre,
+    const unsigned long long* __restrict__ first_key, const unsigned long long* __restrict__ last_key,
     unsigned long long* __restrict__ out_len, uint32_t* __restrict__ skip) {
-  uint32_t d = blockIdx.x * 8 + (threadIdx.x >> 5);
-  int lane = threadIdx.x & 31;
+  const uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
   if (d >= n_docs) return;
-  uint32_t fp = first_pos[d];
-  if (fp == 0xFFFFFFFFu) {
-    if (lane == 0) { out_len[d] = 0; skip[d] = 0; }
-    return;
-  }
-  uint32_t len = doc_len[d], tb = tile_base[d];
-  const uint8_t* doc = arena + doc_off[d];
-  uint32_t r0 = txt_rank_before(doc, len, tile_pre, tb, fp, lane);
-  uint32_t le = last_end[d];
-  uint32_t r1;
-  if (le >= len && (le % RFQ_TILE) == 0) {  // ends exactly at the end of the last tile
-    uint32_t lt = tile_base[d + 1] - 1;
-    r1 = tile_pre[lt] + tile_cnt[lt];
-  } else {
-    r1 = txt_rank_before(doc, len, tile_pre, tb, le, lane);
-  }
-  if (lane == 0) { out_len[d] = r1 - r0; skip[d] = r0; }
+  const unsigned long long fk = first_key[d];
+  if ((uint32_t)(fk >> 32) == 0xFFFFFFFFu) { out_len[d] = 0; skip[d] = 0; return; }
+  const unsigned long long lk = last_key[d];
+  const uint32_t tb = tile_base[d];
+  const uint32_t fp = (uint32_t)(fk >> 32), le = (uint32_t)(lk >> 32);
+  const uint32_t spill = ((uint32_t)lk >> 10) & 3u, trail = (uint32_t)lk & 1023u;
+  const uint32_t r0 = tile_pre[tb + fp / RFQ_TILE] + (uint32_t)fk;
+  const uint32_t r1 = tile_pre[tb + (le - spill - 1u) / RFQ_TILE] + trail + spill;
+  out_len[d] = r1 - r0;
+  skip[d] = r0;
 }
 
 __global__ void __launch_bounds__(256) txt_emit_kernel(
     const uint8_t* __restrict__ arena, const uint32_t* __restrict__ doc_off,
     const uint32_t* __restrict__ doc_len, const uint32_t* __restrict__ tile_base, uint32_t n_docs,
     uint32_t n_tiles, const uint32_t* __restrict__ tile_pre,
-    const uint32_t* __restrict__ first_pos, const uint32_t* __restrict__ last_end,
+    const unsigned long long* __restrict__ first_key, const unsigned long long* __restrict__ last_key,
     const unsigned long long* __restrict__ out_off, const uint32_t* __restrict__ skip,
     uint8_t* __restrict__ out) {
   __shared__ uint8_t stage[8][RFQ_TILE];
@@ -225,10 +228,10 @@ __global__ void __launch_bounds__(256) txt_emit_kernel(
   uint32_t t = blockIdx.x * 8 + wib;
   int lane = threadIdx.x & 31;
   if (t >= n_tiles) return;
-  uint32_t d = find_doc(tile_base, n_docs, t);
-  uint32_t fp = first_pos[d];
+  uint32_t d = find_doc_warp(tile_base, n_docs, t, lane);
+  uint32_t fp = (uint32_t)(first_key[d] >> 32);
   if (fp == 0xFFFFFFFFu) return;
-  uint32_t le = last_end[d];
+  uint32_t le = (uint32_t)(last_key[d] >> 32);
   uint32_t tile = t - tile_base[d];
   uint32_t tb0 = tile * RFQ_TILE;
   if (tb0 + RFQ_TILE <= fp || tb0 >= le) return;  // tile entirely stripped
@@ -273,17 +276,20 @@ __global__ void __launch_bounds__(256) txt_emit_kernel(
 // ---------------------------------------------------------------------------------------------
 void txt_pipeline(const TxtArgs& a, cudaStream_t s) {
   if (a.n_docs == 0) return;
-  cudaMemsetAsync(a.first_pos, 0xFF, sizeof(uint32_t) * a.n_docs, s);
-  cudaMemsetAsync(a.last_end, 0, sizeof(uint32_t) * a.n_docs, s);
+  cudaMemsetAsync(a.first_key, 0xFF, sizeof(unsigned long long) * a.n_docs, s);
+  cudaMemsetAsync(a.last_key, 0, sizeof(unsigned long long) * a.n_docs, s);
   if (a.n_tiles) {
     uint32_t nb = (a.n_tiles + 7) / 8;
+    prof_mark("txt_count_kernel", s);
     RFQ_LAUNCH(txt_count_kernel, nb, 256, 0, s, a.arena, a.doc_off, a.doc_len, a.tile_base,
-               a.n_docs, a.n_tiles, a.tile_cnt, a.first_pos, a.last_end);
+               a.n_docs, a.n_tiles, a.tile_cnt, a.first_key, a.last_key);
+    prof_mark("scan(tile counts)", s);
     exclusive_scan<SumU32>(a.tile_cnt, a.tile_pre, a.n_tiles, a.scan_tmp32, nullptr, s);
   }
-  RFQ_LAUNCH(txt_extent_kernel, (a.n_docs + 7) / 8, 256, 0, s, a.arena, a.doc_off, a.doc_len,
-             a.tile_base, a.n_docs, a.tile_pre, a.tile_cnt, a.first_pos, a.last_end, a.out_len,
-             a.skip);
+  prof_mark("txt_extent_kernel", s);
+  RFQ_LAUNCH(txt_extent_kernel, (a.n_docs + 255) / 256, 256, 0, s, a.tile_base, a.n_docs, a.tile_pre, a.first_key,
+             a.last_key, a.out_len, a.skip);
+  prof_mark("scan(document sizes)", s);
   exclusive_scan<SumU64>(a.out_len, a.out_off, a.n_docs, a.scan_tmp64, a.out_total, s);
 }
 
@@ -291,7 +297,7 @@ void txt_emit(const TxtArgs& a, uint8_t* out, cudaStream_t s) {
   if (a.n_tiles == 0) return;
   uint32_t nb = (a.n_tiles + 7) / 8;
   RFQ_LAUNCH(txt_emit_kernel, nb, 256, 0, s, a.arena, a.doc_off, a.doc_len, a.tile_base, a.n_docs,
-             a.n_tiles, a.tile_pre, a.first_pos, a.last_end, a.out_off, a.skip, out);
+             a.n_tiles, a.tile_pre, a.first_key, a.last_key, a.out_off, a.skip, out);
 }
 
 }  // namespace rfq
