@@ -214,8 +214,12 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
     bool ok = true; std::vector<std::string> disp; std::vector<uint32_t> ncp; std::string empty;
     uint32_t empty_off = 0, hdr_extra = 0; std::vector<uint32_t> off;   // where the texts sit in `names`
   };
+  // looked up by a 64-bit hash of the header row computed on the threads (the row itself is compared on a hit;
+  // two rows with one hash go through the string-keyed map)
+  std::unordered_map<uint64_t, std::pair<std::string, HdrTexts>> hdr_fast;
   std::unordered_map<std::string, HdrTexts> hdr_cache;
   std::vector<std::string> hkeys(n);
+  std::vector<uint64_t> hhash(n, 0);
   parallel_for(n, [&](uint32_t d) {
     const TDoc& T = td[d];
     if (!T.active) return;
@@ -226,12 +230,20 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
       if (len != 0xFFFFFFFFu) hkey.append((const char*)h_hdr + (size_t)g * 256, std::min<uint32_t>(len, 256));
       if (h_hmeta[2 * g] == CM_FLOAT) hkey.append((const char*)h_hdr + (size_t)g * 256 + 240, 8);   // the value itself
     }
+    uint64_t h = 1469598103934665603ull;                 // FNV-1a
+    for (unsigned char ch : hkey) { h ^= ch; h *= 1099511628211ull; }
+    hhash[d] = h;
   });
+  lap("5 header keys (threads)");
   std::vector<const HdrTexts*> hdr_of(n, nullptr);
   for (uint32_t d = 0; d < n; ++d) {
     TDoc& T = td[d];
     if (!T.active) continue;
     const std::string& hkey = hkeys[d];
+    {
+      auto f = hdr_fast.find(hhash[d]);
+      if (f != hdr_fast.end() && f->second.first == hkey) { hdr_of[d] = &f->second.second; continue; }
+    }
     auto hit = hdr_cache.find(hkey);
     if (hit == hdr_cache.end()) {
       HdrTexts H;
@@ -296,10 +308,16 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
           names += H.disp[j];
         }
       }
+      if (!hdr_fast.count(hhash[d])) {       // first row with this hash: the fast map owns it
+        auto ins = hdr_fast.emplace(hhash[d], std::make_pair(hkey, std::move(H))).first;
+        hdr_of[d] = &ins->second.second;
+        continue;
+      }
       hit = hdr_cache.emplace(hkey, std::move(H)).first;
     }
     hdr_of[d] = &hit->second;       // (node addresses of an unordered_map are stable)
   }
+  lap("5 distinct headers");
   parallel_for(n, [&](uint32_t d) {
     TDoc& T = td[d];
     if (!T.active) return;
