@@ -218,20 +218,21 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
   // two rows with one hash go through the string-keyed map)
   std::unordered_map<uint64_t, std::pair<std::string, HdrTexts>> hdr_fast;
   std::unordered_map<std::string, HdrTexts> hdr_cache;
-  std::vector<std::string> hkeys(n);
-  std::vector<uint64_t> hhash(n, 0);
-  parallel_for(n, [&](uint32_t d) {
+  // the header row as bytes (type + text of every label), walked without being copied
+  auto key_walk = [&](uint32_t d, auto&& sink) {
     const TDoc& T = td[d];
-    if (!T.active) return;
-    std::string& hkey = hkeys[d];
     for (uint32_t j = 0; j < T.W; ++j) {
       const uint32_t g = T.col_base + j, len = h_hmeta[2 * g + 1];
-      hkey.append((const char*)&h_hmeta[2 * g], 8);
-      if (len != 0xFFFFFFFFu) hkey.append((const char*)h_hdr + (size_t)g * 256, std::min<uint32_t>(len, 256));
-      if (h_hmeta[2 * g] == CM_FLOAT) hkey.append((const char*)h_hdr + (size_t)g * 256 + 240, 8);   // the value itself
+      sink((const char*)&h_hmeta[2 * g], (size_t)8);
+      if (len != 0xFFFFFFFFu) sink((const char*)h_hdr + (size_t)g * 256, (size_t)std::min<uint32_t>(len, 256));
+      if (h_hmeta[2 * g] == CM_FLOAT) sink((const char*)h_hdr + (size_t)g * 256 + 240, (size_t)8);   // the value itself
     }
+  };
+  std::vector<uint64_t> hhash(n, 0);
+  parallel_for(n, [&](uint32_t d) {
+    if (!td[d].active) return;
     uint64_t h = 1469598103934665603ull;                 // FNV-1a
-    for (unsigned char ch : hkey) { h ^= ch; h *= 1099511628211ull; }
+    key_walk(d, [&](const char* p, size_t k) { for (size_t q = 0; q < k; ++q) { h ^= (unsigned char)p[q]; h *= 1099511628211ull; } });
     hhash[d] = h;
   });
   lap("5 header keys (threads)");
@@ -239,11 +240,20 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
   for (uint32_t d = 0; d < n; ++d) {
     TDoc& T = td[d];
     if (!T.active) continue;
-    const std::string& hkey = hkeys[d];
     {
       auto f = hdr_fast.find(hhash[d]);
-      if (f != hdr_fast.end() && f->second.first == hkey) { hdr_of[d] = &f->second.second; continue; }
+      if (f != hdr_fast.end()) {
+        const std::string& have = f->second.first;
+        size_t pos = 0; bool same = true;
+        key_walk(d, [&](const char* p, size_t k) {
+          if (same && (pos + k > have.size() || memcmp(have.data() + pos, p, k) != 0)) same = false;
+          pos += k;
+        });
+        if (same && pos == have.size()) { hdr_of[d] = &f->second.second; continue; }
+      }
     }
+    std::string hkey;
+    key_walk(d, [&](const char* p, size_t k) { hkey.append(p, k); });
     auto hit = hdr_cache.find(hkey);
     if (hit == hdr_cache.end()) {
       HdrTexts H;
