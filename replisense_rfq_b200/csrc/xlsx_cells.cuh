@@ -31,6 +31,10 @@ RFQ_HD bool xu_rows_by_position(uint32_t f) { return (f & XU_ROW_NOREF) && !(f &
 RFQ_HD bool xu_cells_by_position(uint32_t f) { return (f & XU_C_NOREF) && !(f & XU_C_HASREF); }
 RFQ_HD bool xu_problem(uint32_t f) { return (f & ~(uint32_t)RFQ_XU_INFO) != 0; }
 
+// bit 31 of a shared string's length (sst table, and the length half of a CM_RAW cell record): the string is
+// plain ASCII without control bytes (span_is_clean), decided once by the kernel that decoded it
+#define RFQ_SST_CLEAN 0x80000000u
+
 struct XCell {
   uint32_t col;     // 1-based column
   uint32_t mode;    // CM_*
@@ -252,8 +256,8 @@ RFQ_HD XCell xlsx_parse_cell(const uint8_t* doc, uint32_t len, uint32_t cpos, co
     case 's': {
       int64_t idx;
       if (parse_int64(RawIter(val_b, val_n), &idx) != INT_OK || idx < 0 || (uint64_t)idx >= sst.n) { *flags |= XU_BAD_SST; return x; }
-      uint32_t l = sst.len[idx];
-      if (l == 0) return x;  // "" prints and trims like an empty cell
+      uint32_t l = sst.len[idx];   // bit 31 = RFQ_SST_CLEAN, kept in the cell record
+      if ((l & ~RFQ_SST_CLEAN) == 0) return x;  // "" prints and trims like an empty cell
       x.mode = CM_RAW; x.bits = ((uint64_t)sst.off[idx] << 32) | l;
       return x;
     }

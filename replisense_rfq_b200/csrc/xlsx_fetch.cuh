@@ -22,8 +22,8 @@ __device__ __forceinline__ CellSrc xfetch(const TableArgs& a, const TDoc& D, uin
   XCell x = xc[k];
   s.mode = (uint8_t)x.mode; s.bits = x.bits;
   if (x.mode == CM_RAW) {
-    s.p = a.x_str_arena + (uint32_t)(x.bits >> 32); s.n = (uint32_t)x.bits;
-    s.clean = span_is_clean(s.p, s.n, 0xFF);   // plain ASCII text takes the inline paths of measure / emit
+    s.p = a.x_str_arena + (uint32_t)(x.bits >> 32); s.n = (uint32_t)x.bits & ~RFQ_SST_CLEAN;
+    s.clean = ((uint32_t)x.bits & RFQ_SST_CLEAN) != 0;   // plain ASCII text takes the inline paths of measure / emit
   }
   else if (x.mode == CM_XML) { s.p = a.arena + D.off + (uint32_t)(x.bits >> 32); s.n = (uint32_t)x.bits; }
   return s;

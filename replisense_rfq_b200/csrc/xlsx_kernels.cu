@@ -120,7 +120,14 @@ __global__ void __launch_bounds__(128) sst_kernel(XmlArgs a) {
     a.si_len[i] = sst_decode_si(doc + a.sipos[i], doc + a.doc_len[d], nullptr, &flags);
     if (flags) atomicOr(&a.shape[d].flags, flags);
   } else if (a.si_len[i]) {
-    sst_decode_si(doc + a.sipos[i], doc + a.doc_len[d], a.str_arena + a.si_off[i], &flags);
+    uint8_t* out = a.str_arena + a.si_off[i];
+    const uint32_t n = a.si_len[i];
+    sst_decode_si(doc + a.sipos[i], doc + a.doc_len[d], out, &flags);
+    // plain ASCII without control bytes, decided once per shared string (bit 31 of its length): every cell
+    // that refers to it is fetched three times, and each fetch used to scan the string for exactly this
+    bool clean = true;
+    for (uint32_t k = 0; k < n; ++k) if (out[k] < 0x0E || out[k] >= 0x80) { clean = false; break; }
+    if (clean) a.si_len[i] = n | RFQ_SST_CLEAN;
   }
 }
 

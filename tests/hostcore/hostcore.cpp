@@ -559,7 +559,7 @@ int hc_sheet_parse(const uint8_t* doc, uint32_t len, const uint8_t* sst_doc, uin
     for (uint32_t q = rows[k].c0; q < rows[k].c1; ++q) if (cells[q].col == c + 1) {
       const XCell& x = cells[q];
       s.mode = (uint8_t)x.mode; s.bits = x.bits;
-      if (x.mode == CM_RAW) { s.p = s_arena.data() + (x.bits >> 32); s.n = (uint32_t)x.bits; }
+      if (x.mode == CM_RAW) { s.p = s_arena.data() + (x.bits >> 32); s.n = (uint32_t)x.bits & ~RFQ_SST_CLEAN; }
       if (x.mode == CM_XML) { s.p = doc + (x.bits >> 32); s.n = (uint32_t)x.bits; }
       break;
     }
