@@ -13,11 +13,20 @@ __device__ __forceinline__ CellSrc xfetch(const TableArgs& a, const TDoc& D, uin
   uint32_t c0 = __ldg(a.x_row_c0 + e), c1 = __ldg(a.x_row_c0 + e + 1);
   const XCell* xc = (const XCell*)a.xcells;
   uint32_t k = c0 + c;
-  if (!(k < c1 && xc[k].col == c + 1)) {   // sparse row: binary search on the column
-    uint32_t lo = c0, hi = c1;
-    while (lo < hi) { uint32_t mid = (lo + hi) >> 1; if (xc[mid].col < c + 1) lo = mid + 1; else hi = mid; }
-    if (lo >= c1 || xc[lo].col != c + 1) return s;
-    k = lo;
+  if (!(k < c1 && xc[k].col == c + 1)) {
+    // a row with gaps: columns are increasing and column c + 1 cannot sit after position c, so the cell is a
+    // few records before the dense guess (one step per gap before it); a very sparse row is bisected
+    if (c1 == c0) return s;
+    uint32_t hi = min(k, c1 - 1u);
+    int steps = 0;
+    while (hi > c0 && xc[hi].col > c + 1 && steps < 4) { --hi; ++steps; }
+    if (xc[hi].col > c + 1) {
+      uint32_t lo = c0, h2 = hi;
+      while (lo < h2) { uint32_t mid = (lo + h2) >> 1; if (xc[mid].col < c + 1) lo = mid + 1; else h2 = mid; }
+      hi = lo;
+    }
+    if (xc[hi].col != c + 1) return s;
+    k = hi;
   }
   XCell x = xc[k];
   s.mode = (uint8_t)x.mode; s.bits = x.bits;
