@@ -237,6 +237,8 @@ struct XmlArgs {
   const uint32_t* date_off;     // [n_docs+1] into date_ids
   const uint32_t* date_ids;
   uint32_t* tile_cnt[3];        // [n_tiles+1] per tile: rows, cells, si
+  uint32_t* lane_kinds;         // [n_tiles * 32] what the count pass found in a lane's 16 bytes (2 bits per byte:
+                                // 1 <row, 2 <c, 3 <si): the index pass reads this instead of the document
   uint32_t* tile_pre[3];        // [n_tiles+1]
   uint32_t* scan_tmp;
   XDocShape* shape;             // [n_docs]

@@ -87,6 +87,7 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
   xa.n_docs = n; xa.n_tiles = c->n_tiles;
   const uint32_t nt = c->n_tiles;
   for (int q = 0; q < 3; ++q) {
+    if (q == 0) xa.lane_kinds = c->pool.alloc<uint32_t>(32ull * nt + 32);
     xa.tile_cnt[q] = c->pool.alloc<uint32_t>(nt + 1);
     xa.tile_pre[q] = c->pool.alloc<uint32_t>(nt + 1);
   }

@@ -49,18 +49,25 @@ __global__ void __launch_bounds__(256) xml_tags_kernel(XmlArgs a) {
   uint32_t len = a.doc_len[d];
   const uint8_t* doc = a.arena + a.doc_off[d];
   uint32_t base = tile * RFQ_TILE + lane * 16;
-  uint32_t m = lt_mask(doc, len, base);
-  bool is_sst = (a.kind[d] & 1) != 0;
   uint32_t nr = 0, nc = 0, ns = 0, bang = 0;
   uint32_t kinds = 0;  // 2 bits per byte: 1 row, 2 cell, 3 si
-  for (uint32_t mm = m; mm; mm &= mm - 1) {
-    int k = __ffs(mm) - 1;
-    int tg = xml_classify(doc + base + k, doc + len);
-    if (tg == XT_BANG) bang = 1;
-    if (!is_sst) {
-      if (tg == XT_ROW) { ++nr; kinds |= 1u << (2 * k); }
-      else if (tg == XT_C) { ++nc; kinds |= 2u << (2 * k); }
-    } else if (tg == XT_SI) { ++ns; kinds |= 3u << (2 * k); }
+  if (!WRITE) {
+    const uint32_t m = lt_mask(doc, len, base);
+    const bool is_sst = (a.kind[d] & 1) != 0;
+    for (uint32_t mm = m; mm; mm &= mm - 1) {
+      int k = __ffs(mm) - 1;
+      int tg = xml_classify(doc + base + k, doc + len);
+      if (tg == XT_BANG) bang = 1;
+      if (!is_sst) {
+        if (tg == XT_ROW) { ++nr; kinds |= 1u << (2 * k); }
+        else if (tg == XT_C) { ++nc; kinds |= 2u << (2 * k); }
+      } else if (tg == XT_SI) { ++ns; kinds |= 3u << (2 * k); }
+    }
+    a.lane_kinds[(size_t)t * 32 + lane] = kinds;      // coalesced; the index pass never looks at the bytes again
+  } else {
+    kinds = __ldg(a.lane_kinds + (size_t)t * 32 + lane);
+    const uint32_t lo = kinds & 0x55555555u, hi = (kinds >> 1) & 0x55555555u;
+    nr = (uint32_t)__popc(lo & ~hi); nc = (uint32_t)__popc(hi & ~lo); ns = (uint32_t)__popc(lo & hi);
   }
   if (!WRITE) {
     if (bang) atomicOr(&a.shape[d].flags, XU_BANG);
@@ -81,8 +88,8 @@ __global__ void __launch_bounds__(256) xml_tags_kernel(XmlArgs a) {
       if (lane >= o) { pr += x; pc += y; ps += z; }
     }
     uint32_t ir = a.tile_pre[0][t] + pr - nr, ic = a.tile_pre[1][t] + pc - nc, is = a.tile_pre[2][t] + ps - ns;
-    for (uint32_t mm = m; mm; mm &= mm - 1) {
-      int k = __ffs(mm) - 1;
+    for (uint32_t mm = (kinds | (kinds >> 1)) & 0x55555555u; mm; mm &= mm - 1) {
+      int k = (__ffs(mm) - 1) >> 1;
       uint32_t kd = (kinds >> (2 * k)) & 3u;
       if (kd == 1) { a.rowpos[ir] = base + k; a.row_c0[ir] = ic; ++ir; }
       else if (kd == 2) {   // its document and the <row> element it follows are known right here
