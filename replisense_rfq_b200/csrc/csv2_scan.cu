@@ -114,12 +114,14 @@ __global__ void __launch_bounds__(RFQ2_SCAN_WARPS * 32) csv2_scan_kernel(Csv2Arg
     unsigned long long cls[4];
     uint32_t efn[4], tfn[4], dq[4];    // per tile: the lane's exclusive function, the tile's function, its document
     uint32_t wf = RFQ_FN_IDENTITY;
+    uint32_t d_run = t0 < a.n_tiles ? warp_find_doc(a.tile_base, a.n_docs, t0, lane) : 0u;   // the warp's four tiles follow each other
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const uint32_t t = t0 + q;
       cls[q] = 0ull; efn[q] = RFQ_FN_IDENTITY; tfn[q] = RFQ_FN_IDENTITY; dq[q] = 0;
       if (t < a.n_tiles) {
-        const uint32_t d = scan_find_doc(a.tile_base, a.n_docs, t);
+        while (d_run + 1 < a.n_docs && __ldg(a.tile_base + d_run + 1) <= t) ++d_run;
+        const uint32_t d = d_run;
         const uint32_t tile = t - __ldg(a.tile_base + d);
         const uint32_t len = a.docs[d].len;
         const uint8_t* doc = a.arena + a.docs[d].off;

@@ -129,22 +129,6 @@ __device__ __forceinline__ uint32_t find_doc(const uint32_t* __restrict__ tile_b
   return lo;
 }
 
-// The same with the whole warp: 32 probes per step, so a table of a million documents takes four dependent
-// loads instead of twenty (a batch of small bodies spends its time in this look-up, not in the bytes).
-__device__ __forceinline__ uint32_t find_doc_warp(const uint32_t* __restrict__ tile_base, uint32_t n, uint32_t t, int lane) {
-  uint32_t lo = 0, hi = n;                 // tile_base[lo] <= t < tile_base[hi]
-  while (hi - lo > 1) {
-    const uint32_t step = (hi - lo + 31u) / 32u;
-    const uint32_t idx = lo + (uint32_t)lane * step;
-    const uint32_t v = idx < hi ? __ldg(tile_base + idx) : 0xFFFFFFFFu;
-    const unsigned le = __ballot_sync(0xffffffffu, v <= t);   // a prefix of the lanes (lane 0 always)
-    const uint32_t k = (uint32_t)__popc(le) - 1u;
-    lo += k * step;
-    hi = min(hi, lo + step);
-  }
-  return lo;
-}
-
 __device__ __forceinline__ uint32_t below16(int64_t x) { return x <= 0 ? 0u : x >= 16 ? 0xFFFFu : ((1u << x) - 1u); }
 
 __global__ void __launch_bounds__(256) txt_count_kernel(
@@ -155,7 +139,7 @@ __global__ void __launch_bounds__(256) txt_count_kernel(
   uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
   int lane = threadIdx.x & 31;
   if (t >= n_tiles) return;
-  uint32_t d = find_doc_warp(tile_base, n_docs, t, lane);
+  uint32_t d = warp_find_doc(tile_base, n_docs, t, lane);
   uint32_t tile = t - tile_base[d];
   uint32_t len = doc_len[d];
   const uint8_t* doc = arena + doc_off[d];
@@ -228,7 +212,7 @@ __global__ void __launch_bounds__(256) txt_emit_kernel(
   uint32_t t = blockIdx.x * 8 + wib;
   int lane = threadIdx.x & 31;
   if (t >= n_tiles) return;
-  uint32_t d = find_doc_warp(tile_base, n_docs, t, lane);
+  uint32_t d = warp_find_doc(tile_base, n_docs, t, lane);
   uint32_t fp = (uint32_t)(first_key[d] >> 32);
   if (fp == 0xFFFFFFFFu) return;
   uint32_t le = (uint32_t)(last_key[d] >> 32);

@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(256) xml_tags_kernel(XmlArgs a) {
   uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
   int lane = threadIdx.x & 31;
   if (t >= a.n_tiles) return;
-  uint32_t d = x_find(a.tile_base, a.n_docs, t);
+  uint32_t d = warp_find_doc(a.tile_base, a.n_docs, t, lane);
   uint32_t tile = t - a.tile_base[d];
   uint32_t len = a.doc_len[d];
   const uint8_t* doc = a.arena + a.doc_off[d];
