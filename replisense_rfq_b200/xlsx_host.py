@@ -12,6 +12,8 @@ from __future__ import annotations
 import io
 import posixpath
 import re
+import struct
+import zlib
 import zipfile
 import xml.etree.ElementTree as ET
 
@@ -82,6 +84,62 @@ class Member:
         self.raw, self.method, self.size, self.crc = raw, method, size, crc
 
 
+class _ZipDir:
+    """The central directory of a zip container, read with `struct` (the stdlib `zipfile` builds a ZipInfo object
+    per member and a file object per read: most of the host time of a batch of small workbooks).  Same verdicts
+    as zipfile for what an .xlsx is made of; zip64, multi-disk and encrypted archives are refused."""
+    __slots__ = ("data", "entries")
+    _EOCD = struct.Struct("<4s4H2LH")
+    _CEN = struct.Struct("<4s6H3L5H2L")
+
+    def __init__(self, data: bytes):
+        self.data = data
+        n = len(data)
+        pos = data.rfind(b"PK\x05\x06", max(0, n - 65557))
+        if pos < 0 or pos + 22 > n:
+            raise zipfile.BadZipFile("File is not a zip file")
+        _, disk, cd_disk, n_here, n_total, cd_size, cd_off, _ = self._EOCD.unpack_from(data, pos)
+        if disk or cd_disk or n_here != n_total or n_total == 0xFFFF or cd_off == 0xFFFFFFFF:
+            raise zipfile.BadZipFile("zip64 / multi-disk archives are not supported")
+        if cd_off + cd_size > pos:
+            raise zipfile.BadZipFile("Bad central directory")
+        self.entries = ent = {}
+        p = cd_off
+        for _ in range(n_total):
+            if data[p:p + 4] != b"PK\x01\x02":
+                raise zipfile.BadZipFile("Bad magic number for central directory")
+            (_, _, _, flags, method, _, _, crc, csize, usize, fn, ex, cm, _, _, _, hoff) = self._CEN.unpack_from(data, p)
+            raw = data[p + 46:p + 46 + fn]
+            name = raw.decode("utf-8" if flags & 0x800 else "cp437")
+            ent[name] = (flags, method, crc, csize, usize, hoff)
+            p += 46 + fn + ex + cm
+
+    def member(self, name: str) -> Member:
+        flags, method, crc, csize, usize, ho = self.entries[name]
+        if flags & 0x1:
+            raise zipfile.BadZipFile("encrypted member %r" % name)
+        data = self.data
+        if data[ho:ho + 4] != b"PK\x03\x04":
+            raise zipfile.BadZipFile("bad local header of %r" % name)
+        fnlen = int.from_bytes(data[ho + 26:ho + 28], "little")
+        exlen = int.from_bytes(data[ho + 28:ho + 30], "little")
+        start = ho + 30 + fnlen + exlen
+        return Member(memoryview(data)[start:start + csize], method, usize, crc)
+
+    def read(self, name: str) -> bytes:
+        """A small member, inflated here (workbook.xml, its rels, styles.xml)."""
+        m = self.member(name)
+        if m.method == 0:
+            out = bytes(m.raw)
+        elif m.method == 8:
+            out = zlib.decompressobj(-15).decompress(m.raw)
+        else:
+            raise NotImplementedError("That compression method is not supported")
+        if len(out) != m.size or (zlib.crc32(out) & 0xFFFFFFFF) != m.crc:
+            raise zipfile.BadZipFile("Bad CRC-32 for file %r" % name)
+        return out
+
+
 def _member(z: zipfile.ZipFile, data: bytes, name: str) -> Member:
     zi = z.getinfo(name)
     if zi.flag_bits & 0x1:
@@ -95,36 +153,69 @@ def _member(z: zipfile.ZipFile, data: bytes, name: str) -> Member:
     return Member(memoryview(data)[start:start + zi.compress_size], zi.compress_type, zi.file_size, zi.CRC)
 
 
+# workbooks written by one program share their workbook.xml / rels / styles.xml byte for byte: what those parts
+# say is kept per distinct content (bounded), so a batch parses each of them once
+_plan_cache: dict = {}
+_style_cache: dict = {}
+_CACHE_MAX = 512
+
+
+def _workbook_plan(rels_xml, workbook_xml):
+    """(date1904, [(sheet name, part path)], [sharedStrings part paths named by the rels])."""
+    key = (rels_xml, workbook_xml)
+    hit = _plan_cache.get(key)
+    if hit is not None:
+        return hit
+    rels = {}
+    if rels_xml is not None:
+        for r in ET.fromstring(rels_xml).findall("{%s}Relationship" % _NS_PKG):
+            t = r.get("Target")
+            t = t[1:] if t.startswith("/") else posixpath.normpath(posixpath.join("xl", t))
+            rels[r.get("Id")] = (r.get("Type"), t)
+    root = ET.fromstring(workbook_xml)
+    pr = root.find("{%s}workbookPr" % _NS)
+    date1904 = pr is not None and pr.get("date1904") in ("1", "true")
+    sheets = []
+    for sh in root.find("{%s}sheets" % _NS).findall("{%s}sheet" % _NS):
+        typ, target = rels[sh.get("{%s}id" % _NS_REL)]
+        if typ.endswith("/worksheet"):
+            sheets.append((sh.get("name"), target))
+    sst_targets = [target for typ, target in rels.values() if typ.endswith("/sharedStrings")]
+    plan = (date1904, sheets, sst_targets)
+    if len(_plan_cache) >= _CACHE_MAX:
+        _plan_cache.clear()
+    _plan_cache[key] = plan
+    return plan
+
+
+def _date_styles_cached(styles_xml):
+    hit = _style_cache.get(styles_xml)
+    if hit is None:
+        hit = _date_style_ids(styles_xml)
+        if len(_style_cache) >= _CACHE_MAX:
+            _style_cache.clear()
+        _style_cache[styles_xml] = hit
+    return hit
+
+
 def scan_workbook(data: bytes) -> Workbook:
     """open_workbook without inflating the big parts: worksheet and sharedStrings parts come back as
     `Member`s (raw zip data for the GPU); only workbook.xml, its rels and styles.xml — a few KB that
     decide names, order and date styles — are inflated here."""
-    z = zipfile.ZipFile(io.BytesIO(data))
-    names = set(z.namelist())
-    rels = {}
-    if "xl/_rels/workbook.xml.rels" in names:
-        for r in ET.fromstring(z.read("xl/_rels/workbook.xml.rels")).findall("{%s}Relationship" % _NS_PKG):
-            t = r.get("Target")
-            t = t[1:] if t.startswith("/") else posixpath.normpath(posixpath.join("xl", t))
-            rels[r.get("Id")] = (r.get("Type"), t)
-    root = ET.fromstring(z.read("xl/workbook.xml"))
-    pr = root.find("{%s}workbookPr" % _NS)
-    date1904 = pr is not None and pr.get("date1904") in ("1", "true")
-    sheet_names, sheets = [], []
-    for sh in root.find("{%s}sheets" % _NS).findall("{%s}sheet" % _NS):
-        typ, target = rels[sh.get("{%s}id" % _NS_REL)]
-        if not typ.endswith("/worksheet"):
-            continue
-        sheet_names.append(sh.get("name"))
-        sheets.append(_member(z, data, target))
+    z = _ZipDir(data)
+    names = z.entries
+    rels_xml = z.read("xl/_rels/workbook.xml.rels") if "xl/_rels/workbook.xml.rels" in names else None
+    date1904, plan, sst_targets = _workbook_plan(rels_xml, z.read("xl/workbook.xml"))
+    sheet_names = [nm for nm, _ in plan]
+    sheets = [z.member(target) for _, target in plan]
     sst = None
-    for typ, target in rels.values():
-        if typ.endswith("/sharedStrings") and target in names:
-            sst = _member(z, data, target)
+    for target in sst_targets:
+        if target in names:
+            sst = z.member(target)
     if sst is None and "xl/sharedStrings.xml" in names:
-        sst = _member(z, data, "xl/sharedStrings.xml")
+        sst = z.member("xl/sharedStrings.xml")
     styles = z.read("xl/styles.xml") if "xl/styles.xml" in names else None
-    return Workbook(sheet_names, sheets, sst, _date_style_ids(styles), date1904)
+    return Workbook(sheet_names, sheets, sst, _date_styles_cached(styles), date1904)
 
 
 def open_workbook(data: bytes) -> Workbook:
