@@ -17,7 +17,8 @@ namespace rfq {
 // (span = between the outer quotes, bits = decoded length)
 enum { CM_CSV = 0, CM_RAW = 1, CM_INT = 2, CM_FLOAT = 3, CM_BOOL = 4, CM_XML = 5, CM_NULL = 6, CM_CSVQ = 7,
        CM_DATE = 8, CM_TIME = 9,     // sheet cells: ms since 0001-01-01 / ms of the day (datetime_fmt.cuh)
-       CM_TDELTA = 10 };             // a timedelta-styled number: signed microseconds
+       CM_TDELTA = 10,               // a timedelta-styled number: signed microseconds
+       CM_NUM_PENDING = 11 };        // (between two kernels of the sheet path only) a number still to be parsed
 
 // decoded bytes of a CM_CSVQ span: every "" is one "
 struct PairIter {

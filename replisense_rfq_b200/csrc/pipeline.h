@@ -249,6 +249,7 @@ struct XmlArgs {
   uint32_t* cpos;                                        // [n_cells]
   uint32_t* cell_doc; uint32_t* cell_row;                // [n_cells] document / <row> element of each <c> (~0u = none)
   void* xcells;                                          // XCell[n_cells]
+  uint2* num_list; uint32_t* num_count;                  // cells whose number needs the general parsers: {cell, date style}
   uint32_t* sipos; uint32_t* si_len; uint32_t* si_off;   // [n_si+1]
   uint8_t* str_arena;                                    // decoded shared strings
 };

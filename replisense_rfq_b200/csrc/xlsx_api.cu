@@ -126,6 +126,8 @@ extern "C" int rfq_sheets_run(rfq_ctx* c, const uint8_t* kind, const int32_t* ss
   xa.cell_doc = c->pool.alloc<uint32_t>((size_t)xa.n_cells + 1);
   xa.cell_row = c->pool.alloc<uint32_t>((size_t)xa.n_cells + 1);
   xa.xcells = c->pool.alloc<XCell>((size_t)xa.n_cells + 1);
+  xa.num_list = c->pool.alloc<uint2>((size_t)xa.n_cells + 1);
+  xa.num_count = c->pool.alloc<uint32_t>(4);
   xa.sipos = c->pool.alloc<uint32_t>((size_t)xa.n_si + 1);
   xa.si_len = c->pool.alloc<uint32_t>((size_t)xa.n_si + 1);
   xa.si_off = c->pool.alloc<uint32_t>((size_t)xa.n_si + 1);

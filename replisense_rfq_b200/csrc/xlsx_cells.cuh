@@ -128,11 +128,38 @@ RFQ_HD XCell xlsx_timedelta_cell(XCell x, double v, bool exact, uint32_t* flags)
   return x;
 }
 
+// A numeric <v> that is not a plain decimal literal: int when it has no '.', 'e' or 'E' (openpyxl _cast_number),
+// else float(text) exactly; date / timedelta styles applied.  x.col is kept.
+RFQ_HD XCell xlsx_number_general(XCell x, const uint8_t* val_b, uint32_t val_n, int dstyle, bool date1904, uint32_t* flags) {
+  x.mode = CM_NULL; x.bits = 0;
+  bool is_float = false;
+  for (uint32_t i = 0; i < val_n; ++i) if (val_b[i] == '.' || val_b[i] == 'e' || val_b[i] == 'E') is_float = true;
+  if (!is_float) {
+    int64_t iv;
+    if (parse_int64(RawIter(val_b, val_n), &iv) != INT_OK) { *flags |= XU_BAD_NUMBER; return x; }
+    if (dstyle == 2) return xlsx_timedelta_cell(x, (double)iv, iv > -(1ll << 53) && iv < (1ll << 53), flags);
+    if (dstyle) return xlsx_date_cell(x, (double)iv, date1904, flags);
+    x.mode = CM_INT; x.bits = (uint64_t)iv;
+    return x;
+  }
+  double v;
+  if (!strtod_exact(val_b, val_n, &v) || dbl_is_inf(v) || dbl_is_nan(v)) { *flags |= XU_BAD_NUMBER; return x; }
+  if (dstyle == 2) return xlsx_timedelta_cell(x, v, true, flags);
+  if (dstyle) return xlsx_date_cell(x, v, date1904, flags);
+  // pandas _convert_cell: integral floats become ints
+  if (v > -9.2e18 && v < 9.2e18) {
+    int64_t iv = (int64_t)v;
+    if ((double)iv == v) { x.mode = CM_INT; x.bits = (uint64_t)iv; return x; }
+  } else { *flags |= XU_BAD_NUMBER; return x; }  // would be a Python big int
+  x.mode = CM_FLOAT; x.bits = dbl_bits(v);
+  return x;
+}
+
 // ---- <c ...>...</c> -----------------------------------------------------------------------------
 // doc/len: the sheet part; cpos: offset of "<c". date_ids: sorted style ids that are dates.
 RFQ_HD XCell xlsx_parse_cell(const uint8_t* doc, uint32_t len, uint32_t cpos, const SstView& sst,
                              const uint32_t* date_ids, uint32_t n_date, bool date1904,
-                             uint32_t* flags) {
+                             uint32_t* flags, uint32_t* defer = nullptr) {
   XCell x; x.col = 0; x.mode = CM_NULL; x.bits = 0;
   const uint8_t* p = doc + cpos;
   const uint8_t* e = doc + len;
@@ -231,27 +258,15 @@ RFQ_HD XCell xlsx_parse_cell(const uint8_t* doc, uint32_t len, uint32_t cpos, co
           }
         }
       }
-      bool is_float = false;
-      for (uint32_t i = 0; i < val_n; ++i) if (val_b[i] == '.' || val_b[i] == 'e' || val_b[i] == 'E') is_float = true;
-      if (!is_float) {
-        int64_t iv;
-        if (parse_int64(RawIter(val_b, val_n), &iv) != INT_OK) { *flags |= XU_BAD_NUMBER; return x; }
-        if (dstyle == 2) return xlsx_timedelta_cell(x, (double)iv, iv > -(1ll << 53) && iv < (1ll << 53), flags);
-        if (dstyle) return xlsx_date_cell(x, (double)iv, date1904, flags);
-        x.mode = CM_INT; x.bits = (uint64_t)iv;
+      // everything else (exponents, 19+ digits, signs, blanks): the general parsers.  A caller that gave a
+      // `defer` slot gets the literal back instead (mode CM_NUM_PENDING, bits = offset << 32 | length, *defer =
+      // 1 + date style) and runs xlsx_number_general over all such cells together, with full warps.
+      if (defer) {
+        x.mode = CM_NUM_PENDING; x.bits = ((uint64_t)(uint32_t)(val_b - doc) << 32) | val_n;
+        *defer = 1u + (uint32_t)dstyle;
         return x;
       }
-      double v;
-      if (!strtod_exact(val_b, val_n, &v) || dbl_is_inf(v) || dbl_is_nan(v)) { *flags |= XU_BAD_NUMBER; return x; }
-      if (dstyle == 2) return xlsx_timedelta_cell(x, v, true, flags);
-      if (dstyle) return xlsx_date_cell(x, v, date1904, flags);
-      // pandas _convert_cell: integral floats become ints
-      if (v > -9.2e18 && v < 9.2e18) {
-        int64_t iv = (int64_t)v;
-        if ((double)iv == v) { x.mode = CM_INT; x.bits = (uint64_t)iv; return x; }
-      } else { *flags |= XU_BAD_NUMBER; return x; }  // would be a Python big int
-      x.mode = CM_FLOAT; x.bits = dbl_bits(v);
-      return x;
+      return xlsx_number_general(x, val_b, val_n, dstyle, date1904, flags);
     }
     case 's': {
       int64_t idx;

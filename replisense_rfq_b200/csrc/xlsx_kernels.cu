@@ -182,10 +182,12 @@ __global__ void __launch_bounds__(128) xcell_kernel(XmlArgs a) {
     uint32_t sb = a.si_base[sd];
     sv.off = a.si_off + sb; sv.len = a.si_len + sb; sv.n = a.si_base[sd + 1] - sb;
   }
-  uint32_t flags = 0;
+  uint32_t flags = 0, defer = 0;
   XCell x = xlsx_parse_cell(doc, a.doc_len[d], a.cpos[k], sv, a.date_ids + a.date_off[d],
-                            a.date_off[d + 1] - a.date_off[d], (a.kind[d] & 2) != 0, &flags);
-  if (x.mode == CM_RAW) x.bits += 0;  // offsets are already global into the string arena
+                            a.date_off[d + 1] - a.date_off[d], (a.kind[d] & 2) != 0, &flags, &defer);
+  // a number that needs the general parsers (exponent, 19+ digits, ...) is finished by xnum_kernel: there every
+  // lane has one, here it would be two lanes of the warp running a long path while thirty wait
+  if (defer) a.num_list[atomicAdd(a.num_count, 1u)] = make_uint2(k, defer - 1u);
   // row element of this cell, ordering checks
   uint32_t rb = a.row_base[d], nr = a.row_base[d + 1] - rb;
   uint32_t e = a.cell_row[k];
@@ -234,6 +236,22 @@ __global__ void __launch_bounds__(128) xcell_fix_kernel(XmlArgs a) {
       if (!xcell_is_empty(xc[k]) && r >= 1 && r <= a.cap_rows[d] && col > a.shape[d].W) atomicMax(&a.shape[d].W, col);
       return;
     }
+  }
+}
+
+// the numbers xcell_kernel put aside, densely: one per thread
+__global__ void __launch_bounds__(128) xnum_kernel(XmlArgs a) {
+  const uint32_t n = *a.num_count;
+  XCell* xc = (XCell*)a.xcells;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint2 e = a.num_list[i];
+    const uint32_t k = e.x, d = a.cell_doc[k];
+    XCell x = xc[k];
+    const uint8_t* lit = a.arena + a.doc_off[d] + (uint32_t)(x.bits >> 32);
+    uint32_t flags = 0;
+    x = xlsx_number_general(x, lit, (uint32_t)x.bits, (int)e.y, (a.kind[d] & 2) != 0, &flags);
+    xc[k] = x;
+    if (flags) atomicOr(&a.shape[d].flags, flags);
   }
 }
 
@@ -395,7 +413,9 @@ void xml_decode(const XmlArgs& a, cudaStream_t s) {
   }
   prof_mark("xcell_kernel", s);
   if (a.n_cells) {
+    cudaMemsetAsync(a.num_count, 0, 4, s);
     RFQ_LAUNCH(xcell_kernel, (a.n_cells + 127) / 128, 128, 0, s, a);
+    RFQ_LAUNCH(xnum_kernel, 148 * 8, 128, 0, s, a);
     RFQ_LAUNCH(xcell_fix_kernel, (a.n_cells + 127) / 128, 128, 0, s, a);
     RFQ_LAUNCH(xcell_order_kernel, (a.n_cells + 127) / 128, 128, 0, s, a);
   }
