@@ -108,6 +108,11 @@ struct Csv2Args {
   uint32_t in_stage, out_stage;   // shared-memory bytes of the emit sweep's input / output stage (multiples of 16)
 };
 
+// The first two records of many documents, one thread each (header_names.h scan_header on the device): for
+// batches of thousands of small files, where walking every file's first bytes in pinned host memory is the
+// largest host cost of an attempt.  out[i] (a HeaderScan) describes document sel[i].
+void csv2_header_scan(const uint8_t* arena, const uint32_t* doc_off, const uint32_t* doc_len, const uint32_t* sel,
+                      uint32_t n, uint32_t sep, bool latin1, void* out, cudaStream_t s);
 void csv2_scan(const Csv2Args& a, cudaStream_t s);
 void csv2_type(const Csv2Args& a, cudaStream_t s);     // hot sweep + fix-up of the cold cells
 void csv2_plan(const Csv2Args& a, cudaStream_t s);     // decide / layout / item bytes / offsets

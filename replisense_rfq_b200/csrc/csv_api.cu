@@ -3,6 +3,8 @@
 // O(documents + columns) bookkeeping (header names, table shapes, buffer carving); every pass
 // over document bytes or cells is a kernel.
 #include <cuda_runtime.h>
+#include <stdio.h>
+#include <chrono>
 #include <stdlib.h>
 #include <string.h>
 #include <algorithm>
@@ -326,39 +328,100 @@ static int csv_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8
 // the whole attempt and synchronises ONCE, when it reads the results.  Documents whose header already
 // decides the attempt (no header, one column) never reach the device.  Documents whose chunk types the
 // one-sweep candidates do not cover come back in `general` and go through csv_attempt above.
+namespace rfq {
+__global__ void __launch_bounds__(128) csv2_header_scan_kernel(const uint8_t* __restrict__ arena, const uint32_t* __restrict__ doc_off,
+                                                               const uint32_t* __restrict__ doc_len, const uint32_t* __restrict__ sel,
+                                                               uint32_t n, uint32_t sep, bool latin1, HeaderScan* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t d = sel[i];
+  out[i] = scan_header(arena + doc_off[d], (uint64_t)doc_len[d], DfaDirect{sep}, latin1);
+}
+void csv2_header_scan(const uint8_t* arena, const uint32_t* doc_off, const uint32_t* doc_len, const uint32_t* sel,
+                      uint32_t n, uint32_t sep, bool latin1, void* out, cudaStream_t s) {
+  if (n == 0) return;
+  prof_mark("csv2_header_scan_kernel", s);
+  RFQ_LAUNCH(csv2_header_scan_kernel, (n + 127) / 128, 128, 0, s, arena, doc_off, doc_len, sel, n, sep, latin1, (HeaderScan*)out);
+}
+}  // namespace rfq
+
 static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint8_t* d_arena,
                         const std::vector<uint32_t>& off, const std::vector<uint32_t>& len,
                         int enc, int sep_i, const std::vector<int64_t>& max_rows,
                         std::vector<uint8_t>& resolved, std::vector<uint32_t>& general) {
   cudaStream_t s = c->stream;
   const uint32_t sep = kSeps[sep_i];
+  static const bool host_prof = getenv("RFQ_HOST_PROFILE") != nullptr;   // host time of every stage on stderr
+  auto t_prev = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what) {
+    if (!host_prof) return;
+    const auto t = std::chrono::steady_clock::now();
+    fprintf(stderr, "csv2_attempt host %-22s %8.3f ms (%u documents)\n", what,
+            std::chrono::duration<double, std::milli>(t - t_prev).count(), (unsigned)sel.size());
+    t_prev = t;
+  };
   // ---- 1. headers on the host; documents the header already decides.  The scan of the first two
   // records allocates nothing; names are built once per DISTINCT header record (batches of files made
   // from one template share it), and their texts are stored once in the names arena.
-  struct HeaderTexts { HeaderInfo info; uint32_t banner_off, banner_len, empty_off, empty_len, hdr_extra, name_base; };
-  std::unordered_map<std::string, uint32_t> seen;   // header record bytes -> index into hts
+  struct HeaderTexts {
+    HeaderInfo info; uint32_t banner_off, banner_len, empty_off, empty_len, hdr_extra, name_base;
+    const uint8_t* key_p; size_t key_n;             // the header record it was built from (in the caller's arena)
+  };
+  std::unordered_map<uint64_t, uint32_t> seen_hash; // hash of the header record (computed on the threads) -> hts
+  std::unordered_map<std::string, uint32_t> seen;   // header record bytes -> hts, for records that share a hash
   std::vector<HeaderTexts> hts;
   std::vector<uint32_t> act, act_ht, act_first_nf;  // indices into sel / hts, second-record fields
   std::vector<uint32_t> name_off, name_len, name_cp;
   std::string names, key;
-  std::vector<HeaderScan> scans(sel.size());
-  {
+  std::vector<HeaderScan> scans_host;
+  const HeaderScan* scans = nullptr;
+  if (sel.size() >= 4096) {
+    // thousands of documents: their first bytes are already on the device, one thread each reads them there
+    // (on the host this walk misses the cache once per document: 5-7 ms for 40 000 files)
+    const uint32_t ns = (uint32_t)sel.size();
+    RFQ_CK(c, c->h_up.reserve(4ull * ns + 64));
+    memcpy(c->h_up.p, sel.data(), 4ull * ns);
+    uint32_t* d_sel = c->pool.alloc<uint32_t>(ns + 1);
+    HeaderScan* d_scans = c->pool.alloc<HeaderScan>(ns + 1);
+    if (c->pool.failed) { c->err = "device pool allocation failed"; return RFQ_ERR_CUDA; }
+    RFQ_CK(c, c->h_down.reserve(sizeof(HeaderScan) * (ns + 1) + 64));
+    RFQ_CK(c, cudaMemcpyAsync(d_sel, c->h_up.p, 4ull * ns, cudaMemcpyHostToDevice, s));
+    csv2_header_scan((const uint8_t*)c->d_arena.p, c->d_doc_off, c->d_doc_len, d_sel, ns, sep, enc == 1, d_scans, s);
+    RFQ_CK(c, cudaMemcpyAsync(c->h_down.p, d_scans, sizeof(HeaderScan) * ns, cudaMemcpyDeviceToHost, s));
+    RFQ_CK(c, cudaStreamSynchronize(s));
+    scans_host.assign((const HeaderScan*)c->h_down.p, (const HeaderScan*)c->h_down.p + ns);   // h_down is reused below
+    scans = scans_host.data();
+  } else {
+    scans_host.resize(sel.size());
     const DfaTables dfa(sep);
     parallel_for((uint32_t)sel.size(), [&](uint32_t i) {
       const uint32_t d = sel[i];
-      scans[i] = scan_header(c->h_arena + c->h_doc_off[d], c->h_doc_len[d], dfa, enc == 1);
+      scans_host[i] = scan_header(c->h_arena + c->h_doc_off[d], c->h_doc_len[d], dfa, enc == 1);
     });
+    scans = scans_host.data();
   }
   for (uint32_t i = 0; i < sel.size(); ++i) {
     const uint32_t d = sel[i];
     const uint8_t* hdoc = c->h_arena + c->h_doc_off[d];
     const HeaderScan& hs = scans[i];
     if (!hs.found || hs.h <= 1) continue;                       // EmptyDataError / len(df.columns) <= 1
-    key.assign((const char*)hdoc + hs.begin, (size_t)(hs.end - hs.begin));
-    auto it = seen.find(key);
-    uint32_t hi;
-    if (it != seen.end()) hi = it->second;
-    else {
+    const size_t key_n = (size_t)(hs.end - hs.begin);
+    uint32_t hi = 0xFFFFFFFFu;
+    bool hash_taken = false;
+    {
+      auto f = seen_hash.find(hs.hash);
+      if (f != seen_hash.end()) {
+        hash_taken = true;
+        const HeaderTexts& T0 = hts[f->second];
+        if (T0.key_n == key_n && memcmp(T0.key_p, hdoc + hs.begin, key_n) == 0) hi = f->second;
+      }
+    }
+    if (hi == 0xFFFFFFFFu && hash_taken) {
+      key.assign((const char*)hdoc + hs.begin, key_n);
+      auto it = seen.find(key);
+      if (it != seen.end()) hi = it->second;
+    }
+    if (hi == 0xFFFFFFFFu) {
       HeaderTexts T;
       T.info = parse_header(hdoc, c->h_doc_len[d], sep, enc == 1);
       T.banner_off = T.banner_len = T.empty_off = T.empty_len = T.hdr_extra = T.name_base = 0;
@@ -379,9 +442,11 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
           names += H.disp[j];
         }
       }
+      T.key_p = hdoc + hs.begin; T.key_n = key_n;
       hi = (uint32_t)hts.size();
       hts.push_back(std::move(T));
-      seen.emplace(key, hi);
+      if (!hash_taken) seen_hash.emplace(hs.hash, hi);
+      else { key.assign((const char*)hdoc + hs.begin, key_n); seen.emplace(key, hi); }
     }
     const HeaderInfo& H = hts[hi].info;
     if (!H.found || !H.utf8_ok || H.names.size() <= 1) continue;   // decode error in a label
@@ -391,6 +456,7 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
   }
   const uint32_t m = (uint32_t)act.size();
   if (m == 0) return RFQ_OK;
+  lap("1 headers");
   // ---- 2. carve
   std::vector<Doc2> docs(m);
   std::vector<uint32_t> tile_base(m + 1), item_base(m + 1);
@@ -435,6 +501,7 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
   a.n_tiles = (uint32_t)tiles; a.n_chunks = (uint32_t)((tiles + RFQ2_SCAN_TILES - 1) / RFQ2_SCAN_TILES);
   a.n_items = (uint32_t)n_items; a.n_slots = (uint32_t)n_slots; a.n_stat = (uint32_t)n_stat; a.n_cols = (uint32_t)n_cols;
   a.max_w = max_w;
+  lap("2 carve");
   // ---- 3. upload the description
   RFQ_CK(c, c->h_up.reserve(sizeof(Doc2) * (m + 1) + 8ull * (m + 2) + 12ull * (name_off.size() + 1) + names.size() + 8192));
   Uploader up((uint8_t*)c->h_up.p);
@@ -492,6 +559,7 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
     out_st = std::min<uint64_t>(std::max<uint64_t>(out_st, 8192), 96u << 10);
     a.in_stage = (uint32_t)((in_st + 15) & ~15ull); a.out_stage = (uint32_t)((out_st + 15) & ~15ull);
   }
+  lap("3-4 upload, scratch");
   // ---- 5. the whole attempt, one synchronisation
   csv2_scan(a, s);
   csv2_type(a, s);
@@ -506,7 +574,9 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
   const unsigned long long* h_olen = (const unsigned long long*)(hd + (z_olen - z_cntr));
   RFQ_CK(c, cudaMemcpyAsync(hd, z + z_cntr, z_down_end - z_cntr, cudaMemcpyDeviceToHost, s));
   c->prof.mark("host+sync", s);
+  lap("5 enqueue");
   RFQ_CK(c, cudaStreamSynchronize(s));
+  lap("5 wait for the GPU");
   unsigned long long total = *h_total;
   if (total > cap) {   // the output did not fit: larger buffer, emit again
     cap = total + total / 16 + (64u << 10);

@@ -140,31 +140,44 @@ struct HeaderScan {
   uint64_t begin = 0, end = 0; // bytes of the header record: [begin, end), end = its terminator (or len)
   uint32_t h = 0;              // its fields
   uint32_t first_nf = 0;       // fields of the second record (0 = none)
+  uint64_t hash = 0;           // FNV-1a of the header record's bytes (which documents share a header)
 };
 // the DFA as tables: byte -> class for one separator, (state, class) -> next state / events
 struct DfaTables {
-  uint8_t cls[256];
-  uint8_t next[8][8], ev[8][8];
+  uint8_t cls_[256];
+  uint8_t next_[8][8], ev_[8][8];
   explicit DfaTables(uint32_t sep) {
-    for (int b = 0; b < 256; ++b) cls[b] = (uint8_t)csv_class((uint32_t)b, sep);
+    for (int b = 0; b < 256; ++b) cls_[b] = (uint8_t)csv_class((uint32_t)b, sep);
     for (int st = 0; st < 8; ++st)
       for (int c = 0; c < 8; ++c) {
-        next[st][c] = c < N_CLASSES ? (uint8_t)csv_next(st, c) : (uint8_t)st;
-        ev[st][c] = c < N_CLASSES ? (uint8_t)csv_events(st, c) : 0;
+        next_[st][c] = c < N_CLASSES ? (uint8_t)csv_next(st, c) : (uint8_t)st;
+        ev_[st][c] = c < N_CLASSES ? (uint8_t)csv_events(st, c) : 0;
       }
   }
+  int cls(uint32_t b) const { return cls_[b]; }
+  int next(int st, int c) const { return next_[st][c]; }
+  int ev(int st, int c) const { return ev_[st][c]; }
 };
-inline HeaderScan scan_header(const uint8_t* doc, uint64_t len, const DfaTables& T, bool latin1 = false) {
+// the same automaton straight from its definition (csv_dfa.cuh): what a GPU thread uses
+struct DfaDirect {
+  uint32_t sep;
+  RFQ_HD int cls(uint32_t b) const { return csv_class(b, sep); }
+  RFQ_HD int next(int st, int c) const { return csv_next(st, c); }
+  RFQ_HD int ev(int st, int c) const { return csv_events(st, c); }
+};
+template <class Dfa>
+RFQ_HD HeaderScan scan_header(const uint8_t* doc, uint64_t len, const Dfa& T, bool latin1 = false) {
   HeaderScan r;
+  r.found = false; r.begin = 0; r.end = 0; r.h = 0; r.first_nf = 0; r.hash = 0;
   uint64_t i = 0;
   if (!latin1 && len >= 3 && doc[0] == 0xEF && doc[1] == 0xBB && doc[2] == 0xBF) i = 3;
   int st = ST_R;
   uint64_t ws_start = 0;
   bool open = false, done = false;
   for (; i <= len && !done; ++i) {
-    const int cl = (i == len) ? CL_LF : T.cls[doc[i]];
-    const int ev = T.ev[st][cl];
-    const int ns = T.next[st][cl];
+    const int cl = (i == len) ? CL_LF : T.cls(doc[i]);
+    const int ev = T.ev(st, cl);
+    const int ns = T.next(st, cl);
     if (st != ST_W && ns == ST_W) ws_start = i;
     if (ev) {
       if (ev & EV_REC_START) { open = true; r.begin = i; }
@@ -179,13 +192,16 @@ inline HeaderScan scan_header(const uint8_t* doc, uint64_t len, const DfaTables&
   bool done2 = false;
   uint32_t nf2 = 0;
   for (; i <= len && !done2; ++i) {
-    const int cl = (i == len) ? CL_LF : T.cls[doc[i]];
-    const int ev = T.ev[st][cl];
+    const int cl = (i == len) ? CL_LF : T.cls(doc[i]);
+    const int ev = T.ev(st, cl);
     if (ev & EV_FIELD_END) ++nf2;
     if (ev & EV_LINE_END) done2 = true;
-    st = T.next[st][cl];
+    st = T.next(st, cl);
   }
   r.first_nf = done2 ? nf2 : 0;
+  uint64_t h = 1469598103934665603ull;
+  for (uint64_t q = r.begin; q < r.end; ++q) { h ^= doc[q]; h *= 1099511628211ull; }
+  r.hash = h;
   return r;
 }
 inline HeaderScan scan_header(const uint8_t* doc, uint64_t len, uint32_t sep, bool latin1 = false) {
