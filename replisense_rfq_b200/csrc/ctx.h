@@ -146,6 +146,10 @@ struct rfq_ctx {
   bool inflated_valid = false;
   uint32_t out_n = 0;   // documents of the last run's output when it differs from the staged count (0 = n_docs)
   bool nested = false;
+  // rfq_mixed_run gives the sheet documents to a second context of its own (own stream, scratch pool and pinned
+  // buffers; it borrows the staged arena) and runs it on a host thread beside the CSV run
+  rfq_ctx* helper = nullptr;
+  cudaEvent_t ev_staged = nullptr, ev_helper = nullptr;
   rfq::DevBuf d_viewtab;
   rfq::HostBuf h_viewtab;
   float last_ms = 0.f;

@@ -8,6 +8,7 @@
 #include <string.h>
 #include <chrono>
 #include <algorithm>
+#include <thread>
 #include <vector>
 
 #include "../../include/rfq_parse.h"
@@ -94,9 +95,63 @@ extern "C" int rfq_mixed_run(rfq_ctx* c, const uint8_t* kind, const int64_t* max
   int rc = RFQ_OK;
   c->nested = true;
   lap("views");
+  // ---- the sheet documents on a second context, beside the CSV run: the sheet path is a chain of small
+  // kernels and host stages between synchronisations, the CSV path one long run of kernels, and neither
+  // needs anything of the other but the staged arena
+  static const bool serial = getenv("RFQ_MIXED_SERIAL") != nullptr;
+  const bool side = !serial && !idx[1].empty() && idx[2].size() >= 256;
+  std::vector<uint8_t> sk; std::vector<int32_t> so; std::vector<int64_t> smr; std::vector<uint32_t> sdoff, sdids;
+  int rc_side = RFQ_OK;
+  std::thread side_thread;
+  rfq_ctx* h = nullptr;
+  struct Joiner {            // an early return (a CUDA error on this thread) still waits for the other one
+    std::thread& t; rfq_ctx*& hh;
+    ~Joiner() { if (t.joinable()) t.join(); if (hh) { hh->d_arena.p = nullptr; hh->d_arena.cap = 0; } }
+  } joiner{side_thread, h};
+  auto sheet_args = [&]() -> int {
+    const uint32_t m = (uint32_t)idx[2].size();
+    sk.assign(m, 0); so.assign(m, -1); smr.assign(m, 1000); sdoff.assign(m + 1, 0); sdids.clear();
+    for (uint32_t i = 0; i < m; ++i) {
+      const uint32_t d = idx[2][i];
+      sk[i] = kind[d] == RFQ_KIND_SST ? 1 : kind[d] == RFQ_KIND_SHEET_1904 ? 2 : 0;
+      if (sk[i] != 1 && sst_of && sst_of[d] >= 0) {
+        if ((uint32_t)sst_of[d] >= n || pos_in_sheets[sst_of[d]] < 0) { c->err = "rfq_mixed_run: sst_of must point at a sharedStrings document"; return RFQ_ERR_ARG; }
+        so[i] = pos_in_sheets[sst_of[d]];
+      }
+      if (max_rows) smr[i] = max_rows[d];
+      if (date_off && date_ids) sdids.insert(sdids.end(), date_ids + date_off[d], date_ids + date_off[d + 1]);
+      sdoff[i + 1] = (uint32_t)sdids.size();
+    }
+    if (sdids.empty()) sdids.push_back(0);
+    return RFQ_OK;
+  };
+  if (side) {
+    if (!c->helper) {
+      if (rfq_create(c->device, &c->helper) != RFQ_OK) { c->nested = false; c->err = "rfq_mixed_run: second context"; return RFQ_ERR_CUDA; }
+      cudaEventCreateWithFlags(&c->ev_staged, cudaEventDisableTiming);
+      cudaEventCreateWithFlags(&c->ev_helper, cudaEventDisableTiming);
+    }
+    h = c->helper;
+    rc = sheet_args();
+    if (rc != RFQ_OK) { c->nested = false; return rc; }
+    const uint32_t m = (uint32_t)idx[2].size();
+    cudaEventRecord(c->ev_staged, s);                       // the arena and the views are on the device after this
+    cudaStreamWaitEvent(h->stream, c->ev_staged, 0);
+    h->staged = true; h->nested = false;
+    h->n_docs = m; h->n_tiles = view_tiles[2]; h->arena_bytes = c->arena_bytes; h->h_arena = c->h_arena;
+    h->h_doc_off.assign(hv + base[2], hv + base[2] + m);
+    h->h_doc_len.assign(hv + base[2] + m, hv + base[2] + 2 * m);
+    h->h_tile_base.assign(hv + base[2] + 2 * m, hv + base[2] + 3 * m + 1);
+    h->d_doc_off = dv + base[2]; h->d_doc_len = dv + base[2] + m; h->d_tile_base = dv + base[2] + 2 * m;
+    h->d_arena.p = c->d_arena.p; h->d_arena.cap = 0;       // borrowed
+    side_thread = std::thread([&, h]() {
+      rc_side = rfq_sheets_run(h, sk.data(), so.data(), smr.data(), sdoff.data(), sdids.data());
+      if (rc_side == RFQ_OK) cudaEventRecord(c->ev_helper, h->stream);
+    });
+  }
   for (int k = 0; k < 3 && rc == RFQ_OK; ++k) {
     const uint32_t m = (uint32_t)idx[k].size();
-    if (m == 0) continue;
+    if (m == 0 || (k == 2 && side)) continue;
     // the view: same arena, this kind's documents only
     c->n_docs = m; c->n_tiles = view_tiles[k];
     c->h_doc_off.assign(hv + base[k], hv + base[k] + m);
@@ -125,23 +180,8 @@ extern "C" int rfq_mixed_run(rfq_ctx* c, const uint8_t* kind, const int64_t* max
           m_rows[d] = c->r_rows[i]; m_cols[d] = c->r_cols[i]; m_attempt[d] = c->r_attempt[i]; m_chars[d] = c->r_chars[i];
         }
     } else {
-      std::vector<uint8_t> sk(m);
-      std::vector<int32_t> so(m, -1);
-      std::vector<int64_t> mr(m, 1000);
-      std::vector<uint32_t> doff(m + 1, 0), dids;
-      for (uint32_t i = 0; i < m; ++i) {
-        const uint32_t d = idx[2][i];
-        sk[i] = kind[d] == RFQ_KIND_SST ? 1 : kind[d] == RFQ_KIND_SHEET_1904 ? 2 : 0;
-        if (sk[i] != 1 && sst_of && sst_of[d] >= 0) {
-          if ((uint32_t)sst_of[d] >= n || pos_in_sheets[sst_of[d]] < 0) { c->err = "rfq_mixed_run: sst_of must point at a sharedStrings document"; rc = RFQ_ERR_ARG; break; }
-          so[i] = pos_in_sheets[sst_of[d]];
-        }
-        if (max_rows) mr[i] = max_rows[d];
-        if (date_off && date_ids) dids.insert(dids.end(), date_ids + date_off[d], date_ids + date_off[d + 1]);
-        doff[i + 1] = (uint32_t)dids.size();
-      }
-      if (dids.empty()) dids.push_back(0);
-      if (rc == RFQ_OK) rc = rfq_sheets_run(c, sk.data(), so.data(), mr.data(), doff.data(), dids.data());
+      rc = sheet_args();
+      if (rc == RFQ_OK) rc = rfq_sheets_run(c, sk.data(), so.data(), smr.data(), sdoff.data(), sdids.data());
       if (rc == RFQ_OK)
         for (uint32_t i = 0; i < m; ++i) {
           const uint32_t d = idx[2][i];
@@ -154,6 +194,23 @@ extern "C" int rfq_mixed_run(rfq_ctx* c, const uint8_t* kind, const int64_t* max
       m_total += c->out_total;
     }
     lap(k == 0 ? "text run + merge" : k == 1 ? "csv run + merge" : "sheets run + merge");
+  }
+  if (side) {
+    side_thread.join();
+    h->d_arena.p = nullptr; h->d_arena.cap = 0;
+    if (rc == RFQ_OK && rc_side != RFQ_OK) { rc = rc_side; c->err = h->err; }
+    if (rc == RFQ_OK) {
+      cudaStreamWaitEvent(s, c->ev_helper, 0);             // this stream's later copies read what the helper wrote
+      const uint32_t m = (uint32_t)idx[2].size();
+      for (uint32_t i = 0; i < m; ++i) {
+        const uint32_t d = idx[2][i];
+        m_off[d] = m_total + h->r_off[i]; m_len[d] = h->r_len[i]; m_status[d] = h->r_status[i];
+        m_rows[d] = h->r_rows[i]; m_cols[d] = h->r_cols[i];
+      }
+      for (auto sg : h->segs) { sg.host_base += m_total; sg.copied = false; m_segs.push_back(sg); }
+      m_total += h->out_total;
+    }
+    lap("sheets on the second context: join + merge");
   }
   c->nested = false;
   // ---- back to the full batch

@@ -58,7 +58,10 @@ int rfq_create(int device, rfq_ctx** out) {
 
 void rfq_destroy(rfq_ctx* c) {
   if (!c) return;
+  if (c->helper) { c->helper->d_arena.p = nullptr; c->helper->d_arena.cap = 0; rfq_destroy(c->helper); c->helper = nullptr; }
   cudaSetDevice(c->device);
+  if (c->ev_staged) cudaEventDestroy(c->ev_staged);
+  if (c->ev_helper) cudaEventDestroy(c->ev_helper);
   cudaStreamSynchronize(c->stream);
   c->release_all();
   if (c->ev0) cudaEventDestroy(c->ev0);
