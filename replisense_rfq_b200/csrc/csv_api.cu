@@ -630,6 +630,7 @@ extern "C" int rfq_csv_run(rfq_ctx* c, const int64_t* max_rows_in) {
   g_prof = &c->prof;
   struct ProfGuard { ~ProfGuard() { g_prof = nullptr; } } prof_guard;
   if (!c->nested) { RFQ_CK(c, cudaEventRecord(c->ev0, s)); c->pool.reset(); }
+  c->prof.mark("host prep + upload", s);
   c->status_override.clear(); c->out_n = 0;
   c->segs.clear();
   c->out_total = 0;
