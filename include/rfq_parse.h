@@ -256,6 +256,12 @@ const uint8_t* rfq_out_attempt(const rfq_ctx* ctx);
  * a few threads: the conversion at the language boundary, not part of the parse. */
 int rfq_out_maxchar(const rfq_ctx* ctx, uint32_t d, uint32_t* maxchar);
 int rfq_out_widen(const rfq_ctx* ctx, uint32_t d, int unit, void* dst, uint64_t n_chars);
+/* The same two steps for many documents of the fetched result at once (the texts of a batch of sheets, bodies or
+ * small files), spread over host threads: n_chars[i] / maxchar[i] of document docs[i]; then every text widened
+ * into dsts[i] (units[i] = 1, 2 or 4 bytes per character, room for n_chars[i] characters). */
+int rfq_out_plan_many(const rfq_ctx* ctx, uint32_t n_list, const uint32_t* docs, uint64_t* n_chars, uint32_t* maxchar);
+int rfq_out_widen_many(const rfq_ctx* ctx, uint32_t n_list, const uint32_t* docs, const uint8_t* units, void* const* dsts,
+                       const uint64_t* n_chars);
 
 /* ---- measurement helpers (bench.py): device time of the last *_run, and launch counters ---- */
 float rfq_last_run_ms(const rfq_ctx* ctx);

@@ -41,6 +41,8 @@ SIGNATURES = {
     "rfq_numeric_run": (C.c_int, [C.c_void_p, C.c_void_p]),
     "rfq_json_spans_run": (C.c_int, [C.c_void_p]),
     "rfq_json_run": (C.c_int, [C.c_void_p]),
+    "rfq_out_plan_many": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "rfq_out_widen_many": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "rfq_frame_run": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "rfq_inflate_run": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "rfq_restage_output": (C.c_int, [C.c_void_p]),

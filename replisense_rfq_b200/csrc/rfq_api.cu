@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <string.h>
 #include <algorithm>
+#include <atomic>
 #include <string>
 #include <thread>
 #include <vector>
@@ -823,6 +824,82 @@ int rfq_out_widen(const rfq_ctx* c, uint32_t d, int unit, void* dst, uint64_t n_
   };
   if (nt == 1) widen(0); else { for (unsigned t = 0; t < nt; ++t) th.emplace_back(widen, t); for (auto& x : th) x.join(); }
   return RFQ_OK;
+}
+
+// Many documents at once (a batch of sheets, bodies, small files): the two steps above for every listed
+// document, spread over host threads by bytes.  plan: code points and widest code point of each; fill: each
+// text widened into the buffer the caller allocated for it (units[i] bytes per character, n_chars[i] of them).
+int rfq_out_plan_many(const rfq_ctx* c, uint32_t n_list, const uint32_t* docs, uint64_t* n_chars, uint32_t* maxchar) {
+  const uint32_t n = c ? (c->out_n ? c->out_n : c->n_docs) : 0;
+  if (!c || !c->fetched || (n_list && (!docs || !n_chars || !maxchar))) return RFQ_ERR_ARG;
+  for (uint32_t i = 0; i < n_list; ++i) if (docs[i] >= n) return RFQ_ERR_ARG;
+  std::atomic<uint32_t> next{0};
+  auto work = [&]() {
+    for (;;) {
+      const uint32_t i = next.fetch_add(1);
+      if (i >= n_list) return;
+      const uint8_t* p = (const uint8_t*)c->h_out.p + c->h_out_off[docs[i]];
+      const uint64_t len = c->h_out_len[docs[i]];
+      uint64_t k = 0, q = 0; uint8_t m = 0;
+      for (; q + 8 <= len; q += 8) {
+        uint64_t x; memcpy(&x, p + q, 8);
+        k += 8 - (uint64_t)__builtin_popcountll((x >> 7) & ~(x >> 6) & 0x0101010101010101ull);
+        if (x & 0x8080808080808080ull) for (int b = 0; b < 8; ++b) m = std::max<uint8_t>(m, (uint8_t)(x >> (8 * b)));
+      }
+      for (; q < len; ++q) { k += (p[q] & 0xC0) != 0x80; m = std::max(m, p[q]); }
+      n_chars[i] = k;
+      maxchar[i] = m < 0x80 ? 0x7Fu : m < 0xC4 ? 0xFFu : m < 0xF0 ? 0xFFFFu : 0x10FFFFu;
+    }
+  };
+  unsigned hw = std::thread::hardware_concurrency();
+  const unsigned nt = n_list < 64 ? 1u : std::min<unsigned>(hw ? hw : 4u, 16u);
+  if (nt <= 1) { work(); return RFQ_OK; }
+  std::vector<std::thread> th;
+  for (unsigned t = 0; t < nt; ++t) th.emplace_back(work);
+  for (auto& x : th) x.join();
+  return RFQ_OK;
+}
+
+int rfq_out_widen_many(const rfq_ctx* c, uint32_t n_list, const uint32_t* docs, const uint8_t* units, void* const* dsts,
+                       const uint64_t* n_chars) {
+  const uint32_t n = c ? (c->out_n ? c->out_n : c->n_docs) : 0;
+  if (!c || !c->fetched || (n_list && (!docs || !units || !dsts || !n_chars))) return RFQ_ERR_ARG;
+  for (uint32_t i = 0; i < n_list; ++i)
+    if (docs[i] >= n || !dsts[i] || (units[i] != 1 && units[i] != 2 && units[i] != 4)) return RFQ_ERR_ARG;
+  std::atomic<uint32_t> next{0};
+  std::atomic<int> bad{0};
+  auto work = [&]() {
+    for (;;) {
+      const uint32_t i = next.fetch_add(1);
+      if (i >= n_list) return;
+      const uint8_t* p = (const uint8_t*)c->h_out.p + c->h_out_off[docs[i]];
+      const uint64_t len = c->h_out_len[docs[i]];
+      const int unit = units[i];
+      if (unit == 1 && n_chars[i] == len) { memcpy(dsts[i], p, len); continue; }   // ASCII: the str is a copy
+      uint8_t* d1 = (uint8_t*)dsts[i]; uint16_t* d2 = (uint16_t*)dsts[i]; uint32_t* d4 = (uint32_t*)dsts[i];
+      uint64_t o = 0;
+      for (uint64_t q = 0; q < len;) {
+        uint32_t b = p[q], cp; int l;
+        if (b < 0x80) { cp = b; l = 1; }
+        else if (b < 0xE0) { cp = ((b & 0x1Fu) << 6) | (p[q + 1] & 0x3Fu); l = 2; }
+        else if (b < 0xF0) { cp = ((b & 0x0Fu) << 12) | ((p[q + 1] & 0x3Fu) << 6) | (p[q + 2] & 0x3Fu); l = 3; }
+        else { cp = ((b & 0x07u) << 18) | ((p[q + 1] & 0x3Fu) << 12) | ((p[q + 2] & 0x3Fu) << 6) | (p[q + 3] & 0x3Fu); l = 4; }
+        if (o >= n_chars[i]) { bad = 1; break; }
+        if (unit == 1) d1[o] = (uint8_t)cp; else if (unit == 2) d2[o] = (uint16_t)cp; else d4[o] = cp;
+        ++o; q += l;
+      }
+      if (o != n_chars[i]) bad = 1;
+    }
+  };
+  unsigned hw = std::thread::hardware_concurrency();
+  const unsigned nt = n_list < 64 ? 1u : std::min<unsigned>(hw ? hw : 4u, 16u);
+  if (nt <= 1) work();
+  else {
+    std::vector<std::thread> th;
+    for (unsigned t = 0; t < nt; ++t) th.emplace_back(work);
+    for (auto& x : th) x.join();
+  }
+  return bad ? RFQ_ERR_ARG : RFQ_OK;
 }
 
 float rfq_last_run_ms(const rfq_ctx* c) { return c ? c->last_ms : 0.f; }

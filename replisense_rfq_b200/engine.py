@@ -170,6 +170,36 @@ class BatchResult:
         return _decode_utf8(self.text_ptr + int(self.offsets[d]), ln, None)
 
 
+    def doc_strs(self, ds) -> "list[str]":
+        """doc_str for many documents of this result: the texts are sized and filled by library threads
+        (rfq_out_plan_many / rfq_out_widen_many), Python only allocates the str objects.  For a batch of sheets,
+        bodies or small files the one-at-a-time decode is the largest host cost of the call."""
+        ds = [int(d) for d in ds]
+        lens = self.lengths
+        if _STR_OFFSETS is None or len(ds) < 8 or sum(int(lens[d]) for d in ds) < (1 << 20):
+            return [self.doc_str(d) for d in ds]
+        live = [d for d in ds if int(lens[d]) > 0]
+        n = len(live)
+        idx = np.asarray(live, dtype=np.uint32)
+        nch = np.zeros(n, dtype=np.uint64)
+        mc = np.zeros(n, dtype=np.uint32)
+        if self._lib.rfq_out_plan_many(self._ctx, n, idx.ctypes.data, nch.ctypes.data, mc.ctypes.data) != 0:
+            return [self.doc_str(d) for d in ds]
+        units = np.empty(n, dtype=np.uint8)
+        dsts = np.empty(n, dtype=np.uint64)
+        objs = []
+        off_a, off_c = _STR_OFFSETS
+        for i, (k, m) in enumerate(zip(nch.tolist(), mc.tolist())):
+            o = _py_new(k, m)
+            objs.append(o)
+            units[i] = 1 if m <= 0xFF else 2 if m <= 0xFFFF else 4
+            dsts[i] = id(o) + (off_a if m <= 0x7F else off_c)
+        if self._lib.rfq_out_widen_many(self._ctx, n, idx.ctypes.data, units.ctypes.data, dsts.ctypes.data, nch.ctypes.data) != 0:
+            return [self.doc_str(d) for d in ds]
+        texts = dict(zip(live, objs))
+        return [texts.get(d, "") for d in ds]
+
+
 class Engine:
     """One CUDA device, one stream. Thread-safe (calls are serialised per engine)."""
 
@@ -256,7 +286,7 @@ class Engine:
             self._check(self.lib.rfq_text_parse(self.ctx, a.ptr, off.ctypes.data, ln.ctypes.data,
                                                 len(docs)), "rfq_text_parse")
             r = BatchResult(self)
-            return [r.doc_str(d) for d in range(r.n)]
+            return r.doc_strs(range(r.n))
 
     def parse_text_file(self, path) -> str:
         """raw_text of one .txt file, read straight into pinned memory."""
@@ -342,10 +372,12 @@ class Engine:
             self._check(self.lib.rfq_fetch(self.ctx), "rfq_fetch")
             r = BatchResult(self)
             out: "list[Any]" = []
+            ok = [d for d in range(r.n) if int(r.status[d]) == _lib.DOC_OK]
+            texts = dict(zip(ok, r.doc_strs(ok)))
             for d in range(r.n):
                 st = int(r.status[d])
                 if st == _lib.DOC_OK:
-                    out.append(r.doc_str(d))
+                    out.append(texts[d])
                 elif st == _lib.DOC_JSON_INVALID:
                     e = EngineError("invalid JSON")
                     e.json_error = "%s: line %d column %d (char %d)" % (_lib.JSON_ERRORS[int(r.attempt[d])], int(r.rows[d]),
@@ -392,10 +424,12 @@ class Engine:
         with self.lock:
             r = self.csv_batch(docs, max_rows)
             out = []
+            ok = [d for d in range(r.n) if int(r.status[d]) == _lib.DOC_OK]
+            texts = dict(zip(ok, r.doc_strs(ok)))
             for d in range(r.n):
                 st = int(r.status[d])
                 if st == _lib.DOC_OK:
-                    out.append(r.doc_str(d))
+                    out.append(texts[d])
                 elif st == _lib.DOC_CSV_UNPARSEABLE:
                     out.append(None)
                 else:

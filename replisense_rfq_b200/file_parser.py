@@ -201,12 +201,14 @@ class FileParser:
         if flat:
             with eng.lock:   # the pinned output is ours until every text has been built
                 r = eng.mixed_batch(flat, fkind, self.max_excel_rows)
+                ok = [d for d in range(len(owner)) if fkind[d] == _lib.KIND_TEXT or int(r.status[d]) == _lib.DOC_OK]
+                texts = dict(zip(ok, r.doc_strs(ok)))
                 for d, i in enumerate(owner):
                     st = int(r.status[d])
                     if fkind[d] == _lib.KIND_TEXT:
-                        out[i] = r.doc_str(d)
+                        out[i] = texts[d]
                     else:
-                        out[i] = (r.doc_str(d) if st == _lib.DOC_OK
+                        out[i] = (texts[d] if st == _lib.DOC_OK
                                   else FileParsingError(f"CSV parsing failed: {_CSV_FAIL}") if st == _lib.DOC_CSV_UNPARSEABLE
                                   else FileParsingError("CSV parsing failed: unsupported construct on the GPU path "
                                                         f"(status {st})"))

@@ -272,6 +272,7 @@ def parse_workbooks(engine, books, max_rows: int = 1000) -> "list":
                     failed[b] = EngineError("zip member is corrupt (bad DEFLATE stream, size or CRC-32)")
         else:
             res = engine.sheets_batch(docs, kind, sst_of, max_rows, dates) if docs else None
+        want = []
         for d, (b, k) in enumerate(owner):
             if k is None or b in failed:
                 continue
@@ -281,5 +282,9 @@ def parse_workbooks(engine, books, max_rows: int = 1000) -> "list":
             if st != _lib.DOC_OK:
                 failed[b] = EngineError(f"sheet {books[b].sheet_names[k]!r}: construct not decoded on the GPU path")
                 continue
-            parts[b].append(f"=== Sheet: {books[b].sheet_names[k]} ===\n" + res.doc_str(d))
+            want.append(d)
+        for d, text in zip(want, res.doc_strs(want) if want else []):   # all sheet texts built in one go (library threads)
+            b, k = owner[d]
+            if b not in failed:
+                parts[b].append(f"=== Sheet: {books[b].sheet_names[k]} ===\n" + text)
     return [failed[b] if b in failed else ("\n\n".join(p) if p else _EMPTY) for b, p in enumerate(parts)]
