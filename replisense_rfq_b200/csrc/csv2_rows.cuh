@@ -329,23 +329,26 @@ RFQ_HD bool canonical_decimal(const uint8_t* p, uint32_t n, int dec) {
 
 // ---- the cells the hot emit sweep prints itself -------------------------------------------------
 // n bytes from src (any address space, any alignment) to dst (byte stores)
+RFQ_HD void copy_span8(uint8_t* d, uint64_t x) {
+  const uint32_t lo = (uint32_t)x, hi = (uint32_t)(x >> 32);
+  d[0] = (uint8_t)lo; d[1] = (uint8_t)(lo >> 8); d[2] = (uint8_t)(lo >> 16); d[3] = (uint8_t)(lo >> 24);
+  d[4] = (uint8_t)hi; d[5] = (uint8_t)(hi >> 8); d[6] = (uint8_t)(hi >> 16); d[7] = (uint8_t)(hi >> 24);
+}
 RFQ_HD void copy_span(uint8_t* dst, const uint8_t* src, uint32_t n) {
-  uint32_t i = 0;
-  for (; i + 8 <= n; i += 8) {
-    const uint64_t x = load8_masked(src + i, 8);
-    const uint32_t lo = (uint32_t)x, hi = (uint32_t)(x >> 32);
-    uint8_t* d = dst + i;
-    d[0] = (uint8_t)lo; d[1] = (uint8_t)(lo >> 8); d[2] = (uint8_t)(lo >> 16); d[3] = (uint8_t)(lo >> 24);
-    d[4] = (uint8_t)hi; d[5] = (uint8_t)(hi >> 8); d[6] = (uint8_t)(hi >> 16); d[7] = (uint8_t)(hi >> 24);
+  if (n >= 8) {
+    uint32_t i = 0;
+    for (; i + 8 <= n; i += 8) copy_span8(dst + i, load8_masked(src + i, 8));
+    // the last 1-7 bytes as one more group of eight that ends at n (it rewrites bytes of the group before with
+    // the same values): no loop whose length differs from lane to lane
+    if (i < n) copy_span8(dst + (n - 8), load8_masked(src + (n - 8), 8));
+    return;
   }
-  if (i < n) {
 #ifdef __CUDA_ARCH__
-    const uint64_t x = load8_masked(src + i, 8);      // only the n - i low bytes are stored
+  const uint64_t x = load8_masked(src, 8);      // only the n low bytes are stored
 #else
-    const uint64_t x = load8_masked(src + i, n - i);
+  const uint64_t x = load8_masked(src, n);
 #endif
-    for (uint32_t q = 0; i + q < n; ++q) dst[i + q] = (uint8_t)(x >> (8 * q));
-  }
+  for (uint32_t q = 0; q < n; ++q) dst[q] = (uint8_t)(x >> (8 * q));
 }
 
 // What the typing sweep found out about a cell, 16 bits, so that the emit sweep neither looks for
