@@ -106,6 +106,9 @@ struct Csv2Args {
   // emit
   uint8_t* out; unsigned long long out_cap;
   uint32_t in_stage, out_stage;   // shared-memory bytes of the emit sweep's input / output stage (multiples of 16)
+  // a small result block (counters, per-document results) is written to pinned host memory by the last kernel
+  // of the attempt instead of being fetched by a copy of its own (export_words = 0: the host copies it)
+  uint32_t* export_dst; const uint32_t* export_src; uint32_t export_words;
 };
 
 // The first two records of many documents, one thread each (header_names.h scan_header on the device): for

@@ -41,6 +41,8 @@ __device__ __noinline__ uint32_t emit_cell_general(CellSrc src, int ct, int kind
 }
 
 __global__ void __launch_bounds__(128) csv2_emit_cold_kernel(Csv2Args a) {
+  if (blockIdx.x == 0)   // everything in the block was final before this kernel started (it only reads it)
+    for (uint32_t i = threadIdx.x; i < a.export_words; i += blockDim.x) a.export_dst[i] = a.export_src[i];
   const uint32_t n = min(a.counters[1], a.cold_rows_cap);
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const ColdRow cr = a.cold_rows[i];
