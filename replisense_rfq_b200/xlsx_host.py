@@ -140,19 +140,6 @@ class _ZipDir:
         return out
 
 
-def _member(z: zipfile.ZipFile, data: bytes, name: str) -> Member:
-    zi = z.getinfo(name)
-    if zi.flag_bits & 0x1:
-        raise zipfile.BadZipFile("encrypted member %r" % name)
-    ho = zi.header_offset
-    if data[ho:ho + 4] != b"PK\x03\x04":
-        raise zipfile.BadZipFile("bad local header of %r" % name)
-    fnlen = int.from_bytes(data[ho + 26:ho + 28], "little")
-    exlen = int.from_bytes(data[ho + 28:ho + 30], "little")
-    start = ho + 30 + fnlen + exlen
-    return Member(memoryview(data)[start:start + zi.compress_size], zi.compress_type, zi.file_size, zi.CRC)
-
-
 # workbooks written by one program share their workbook.xml / rels / styles.xml byte for byte: what those parts
 # say is kept per distinct content (bounded), so a batch parses each of them once
 _plan_cache: dict = {}
