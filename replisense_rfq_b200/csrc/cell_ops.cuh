@@ -205,7 +205,8 @@ RFQ_HD TextInfo scan_text_raw(const uint8_t* p, uint32_t n) {
 #else
     cont += (uint32_t)__builtin_popcountll(cb);
 #endif
-    for (uint32_t q = 0; q < m; ++q) {
+#pragma unroll 1
+    for (uint32_t q = 0; q < m; ++q) {   // kept rolled: eight copies of this state machine would be 8 KB of code
       const uint32_t c = (uint32_t)(x >> (8 * q)) & 0xFFu;
       if (need) {
         if (c < lo || c > hi) { t.utf8_ok = false; need = 0; }

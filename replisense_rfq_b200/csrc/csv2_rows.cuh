@@ -201,72 +201,135 @@ struct HotCand {
 //   word(flags, str_len, extra, bool_len)        not a number (int64 status: invalid)
 //   integer(flags, str_len, int_len, neg, large) an int64 of magnitude <= 2^53 (float view: digits + ".000000")
 //   decimal(flags, str_len, ip_len, tz, obj_len, neg, large)   [+-]d{1,8}.d{1,6}
+// A decision of the hot classifier, packed so that the rarely-run general part can live out of line:
+//   bits 0-2 outcome, 3 neg, 4 large, 5-9 int_len / ip_len, 10-12 tz, 13-17 obj_len, 32-63 SF_* flags
+enum { HD_COLD = 0, HD_WORD = 2, HD_INT = 3, HD_DEC = 4 };
+RFQ_HD uint64_t hd_pack(uint32_t kind, uint32_t f, uint32_t len, uint32_t tz, uint32_t obj_len, bool neg, bool large) {
+  return (uint64_t)kind | (neg ? 8ull : 0ull) | (large ? 16ull : 0ull) | ((uint64_t)len << 5) | ((uint64_t)tz << 10) |
+         ((uint64_t)obj_len << 13) | ((uint64_t)f << 32);
+}
+
+// Numeric-looking clean ASCII tokens the eight-byte shortcuts of classify_hot do not settle: the parsers'
+// own byte loops.  Out of line on the device: C2-like tables (quantities, prices, dates) never come
+// here, and the hot sweep's code stays inside the instruction cache.
+RFQ_HD_COLD uint64_t classify_hot_rest(const uint8_t* p, uint32_t n, uint64_t first8, uint32_t f) {
+  const uint32_t c0 = (uint32_t)(first8 & 0xFFu);
+  int64_t iv;
+  const int st = parse_int64(RawIter(p, n), &iv);
+  if (st == INT_OK) {
+    const uint64_t mag = iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv;
+    if (mag > (1ull << 53) || (iv == 0 && c0 != '0')) return HD_COLD;   // float view needs the exact parser; "-0", " 0", "+0"
+    if (iv < 0) f |= SF_NEG;
+    f |= SF_BOOL_BAD;
+    return hd_pack(HD_INT, f, (uint32_t)int64_len(iv), 0, 0, iv < 0, mag > 1000000ull);
+  }
+  if (st == INT_OVERFLOW) return HD_COLD;
+  Fixed6 d6;
+  if (!decimal_literal(p, n, &d6)) {
+    // not an integer: a date, a part number that starts with a digit, ... decided here when no
+    // grammar takes it; real floats beyond the literal shape go to the fix-up kernel
+    const uint32_t c1 = (c0 == '+' || c0 == '-') ? (uint32_t)((first8 >> 8) & 0xFFu) : c0;
+    if ((c1 | 0x20u) == 'i') {                 // INR, item, -inf: only the inf words are numbers
+      if (inf_word(p, n)) return HD_COLD;
+    } else if (float_shape(p, n) != 0) return HD_COLD;
+    uint32_t i = 0;
+    while (i < n && is_space_ascii(p[i])) ++i;
+    if (i < n && p[i] == '-') f |= SF_NEG; else f |= SF_UINT_INVALID;   // str_to_uint64: a leading '-' is "negative", not an error
+    f |= SF_FLOAT_BAD | SF_BOOL_BAD;           // no bool word starts like a number
+    const int pp = pyint_prefix(first8, n);
+    if (pp == 2) return HD_COLD;
+    if (pp == 0) f |= SF_PYINT_BAD;
+    return hd_pack(HD_WORD, f, 0, 0, 0, false, false);
+  }
+  // [+-]d{1,8}.d{1,6}: not an int64, not a uint64 (invalid, or "negative" for a leading '-'), never
+  // int()-parsable, not a bool; as float64 its "%.6f" digits are its own (cell_format.cuh)
+  if (c0 == '-') f |= SF_NEG; else f |= SF_UINT_INVALID;
+  f |= SF_PYINT_BAD | SF_BOOL_BAD;
+  return hd_pack(HD_DEC, f, (d6.neg ? 1u : 0u) + (uint32_t)d6.ip_digits, (uint32_t)d6.tz, (uint32_t)objfloat_len(d6), d6.neg,
+                 d6.ip > 1000000ull || (d6.ip == 1000000ull && d6.frac));
+}
+
+RFQ_HD_COLD bool is_na_word(uint32_t n, uint64_t first8) { return is_na_token(n, first8); }
+
 template <class Sink>
 RFQ_HD void classify_hot(const CellSrc& s, Sink& k) {
   if (s.missing) { k.na(); return; }
   if (s.mode == CM_CSV) { k.cold(); return; }
+  const uint64_t ones = 0x0101010101010101ull, highs = 0x8080808080808080ull;
   uint32_t nbytes, ncp, f = SF_ANY_NONNA;
   uint64_t first8;
   if (s.clean) { nbytes = s.n; ncp = s.n; first8 = s.n ? load8_masked(s.p, s.n) : 0; }
   else if (s.mode == CM_CSVQ) {
     nbytes = (uint32_t)s.bits; ncp = nbytes;
-    first8 = 0;
-    PairIter it(s.p, s.n);
-    for (int q = 0; q < 8; ++q) { int c = it.next(); if (c < 0) break; first8 |= (uint64_t)c << (8 * q); }
+    const uint64_t raw8 = load8_masked(s.p, s.n < 8u ? s.n : 8u);
+    if (s.n >= 8u && !zero_bytes(raw8 ^ (ones * '"'))) first8 = raw8;   // no "" among the first eight bytes: they are the first eight characters
+    else {
+      first8 = 0;
+      PairIter it(s.p, s.n);
+      for (int q = 0; q < 8; ++q) { int c = it.next(); if (c < 0) break; first8 |= (uint64_t)c << (8 * q); }
+    }
   } else {   // plain span with non-ASCII bytes
     TextInfo t = scan_text_raw(s.p, s.n);
     if (!t.utf8_ok) f |= SF_BAD_UTF8;
     if (t.nesc) { k.cold(); return; }   // cannot happen (no control bytes), kept for safety
     nbytes = t.nbytes; ncp = t.ncp; first8 = t.first8;
   }
-  if (is_na_token(nbytes, first8)) { k.na(); return; }
-  const int bt = bool_token(nbytes, first8);
-  const uint32_t bool_len = bt < 0 ? 0u : bt == 1 ? 4u : 5u;
   const uint32_t c0 = (uint32_t)(first8 & 0xFFu);
+  if (nbytes == 0) { k.na(); return; }
+  // every NA word starts with one of # - 1 < N n and has at most eight bytes; the comparison with the
+  // nineteen words is out of line
+  if (nbytes <= 8u && (c0 == 'N' || c0 == 'n' || c0 == '#' || c0 == '-' || c0 == '1' || c0 == '<') &&
+      is_na_word(nbytes, first8)) { k.na(); return; }
+  uint64_t dec;
   if (!(is_digit_ascii((int)c0) || c0 == '+' || c0 == '-' || c0 == '.' || is_space_ascii((int)c0) ||
         (c0 | 0x20u) == 'i')) {          // a plain word: no numeric grammar starts like this
+    const int bt = bool_token(nbytes, first8);
     f |= SF_UINT_INVALID | SF_FLOAT_BAD | SF_PYINT_BAD;
     if (bt < 0) f |= SF_BOOL_BAD;
-    k.word(f, ncp, nbytes - ncp, bool_len);
+    k.word(f, ncp, nbytes - ncp, bt < 0 ? 0u : bt == 1 ? 4u : 5u);
     return;
   }
   if (!s.clean || s.mode != CM_RAW) { k.cold(); return; }   // numeric-looking but quoted-with-pairs / non-ASCII
-  int64_t iv;
-  const int st = parse_int64(RawIter(s.p, s.n), &iv);
-  if (st == INT_OK) {
-    const uint64_t mag = iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv;
-    if (mag > (1ull << 53) || (iv == 0 && c0 != '0')) { k.cold(); return; }   // float view needs the exact parser; "-0", " 0", "+0"
-    if (iv < 0) f |= SF_NEG;
-    f |= SF_BOOL_BAD;
-    k.integer(f, ncp, (uint32_t)int64_len(iv), iv < 0, mag > 1000000ull);
-    return;
+  // ---- decided from the first eight bytes alone (quantities, prices, dates): the same answers as the
+  // parsers of classify_hot_rest, without their byte loops
+  {
+    const uint64_t live = s.n >= 8u ? ~0ull : ((1ull << (8u * s.n)) - 1ull);
+    const uint64_t y = first8 ^ (ones * 0x30u);                              // '0'..'9' -> 0..9 (clean ASCII: no byte carries)
+    const uint64_t nondig = ((y + ones * 0x76u) | y) & highs & live;         // 0x80 where the byte is not a digit
+    const bool d0 = (uint32_t)(c0 - '1') < 9u;                               // starts with 1..9
+    const uint64_t dot = zero_bytes(first8 ^ (ones * '.')) & live;
+    const uint64_t sg = (zero_bytes(first8 ^ (ones * '-')) | zero_bytes(first8 ^ (ones * '+'))) & live;
+    if (s.n <= 8u && !nondig && (d0 || s.n == 1u)) {
+      // d{1,8} without a leading zero: an int64 that prints as itself
+      dec = hd_pack(HD_INT, f | SF_BOOL_BAD, s.n, 0, 0, false,
+                    s.n == 8u || (s.n == 7u && first8 != RFQ_P8('1', '0', '0', '0', '0', '0', '0', 0)));
+    } else if (s.n <= 8u && d0 && nondig && nondig == dot && !(dot & (dot - 1ull)) && first_flag_byte(dot) + 1u < s.n) {
+      // [1-9]d*.d+ in at most eight bytes: one '.', at least one decimal (at most six)
+      const uint32_t kd = first_flag_byte(dot);                              // digits before the point
+      const uint64_t nz = ~zero_bytes(first8 ^ (ones * '0')) & highs & live; // bytes other than '0' (the point is one)
+#ifdef __CUDA_ARCH__
+      const uint32_t hb = (uint32_t)(63 - __clzll((long long)nz)) >> 3;
+#else
+      const uint32_t hb = (uint32_t)(63 - __builtin_clzll(nz)) >> 3;
+#endif
+      const uint32_t nf = s.n - 1u - kd;
+      const uint32_t tz = hb == kd ? 6u : (6u - nf) + (s.n - 1u - hb);       // trailing zeros of the six-digit fraction
+      dec = hd_pack(HD_DEC, f | SF_UINT_INVALID | SF_PYINT_BAD | SF_BOOL_BAD, kd, tz, 2u + kd + (tz >= 6u ? 1u : 6u - tz), false, false);
+    } else if (is_digit_ascii((int)c0) && (sg & ((~((y + ones * 0x76u) | y) & highs & live) << 8))) {
+      // 2025-09-12, 10-32UNF: a sign right after a digit ends every numeric grammar
+      dec = hd_pack(HD_WORD, f | SF_UINT_INVALID | SF_FLOAT_BAD | SF_BOOL_BAD | SF_PYINT_BAD, 0, 0, 0, false, false);
+    } else {
+      dec = classify_hot_rest(s.p, s.n, first8, f);
+    }
   }
-  if (st == INT_OVERFLOW) { k.cold(); return; }
-  Fixed6 d6;
-  if (!decimal_literal(s.p, s.n, &d6)) {
-    // not an integer: a date, a part number that starts with a digit, ... decided here when no
-    // grammar takes it; real floats beyond the literal shape go to the fix-up kernel
-    const uint32_t c1 = (c0 == '+' || c0 == '-') ? (uint32_t)((first8 >> 8) & 0xFFu) : c0;
-    if ((c1 | 0x20u) == 'i') {                 // INR, item, -inf: only the inf words are numbers
-      if (inf_word(s.p, s.n)) { k.cold(); return; }
-    } else if (float_shape(s.p, s.n) != 0) { k.cold(); return; }
-    uint32_t i = 0;
-    while (i < s.n && is_space_ascii(s.p[i])) ++i;
-    if (i < s.n && s.p[i] == '-') f |= SF_NEG; else f |= SF_UINT_INVALID;   // str_to_uint64: a leading '-' is "negative", not an error
-    f |= SF_FLOAT_BAD;
-    if (bt < 0) f |= SF_BOOL_BAD;
-    const int pp = pyint_prefix(first8, nbytes);
-    if (pp == 2) { k.cold(); return; }
-    if (pp == 0) f |= SF_PYINT_BAD;
-    k.word(f, ncp, nbytes - ncp, bool_len);
-    return;
+  const uint32_t df = (uint32_t)(dec >> 32), len = (uint32_t)(dec >> 5) & 31u;
+  const bool neg = (dec & 8ull) != 0, large = (dec & 16ull) != 0;
+  switch ((uint32_t)dec & 7u) {
+    case HD_WORD: k.word(df, ncp, 0u, 0u); return;
+    case HD_INT: k.integer(df, ncp, len, neg, large); return;
+    case HD_DEC: k.decimal(df, ncp, len, (uint32_t)(dec >> 10) & 7u, (uint32_t)(dec >> 13) & 31u, neg, large); return;
+    default: k.cold(); return;
   }
-  // [+-]d{1,8}.d{1,6}: not an int64, not a uint64 (invalid, or "negative" for a leading '-'), never
-  // int()-parsable, not a bool; as float64 its "%.6f" digits are its own (cell_format.cuh)
-  if (c0 == '-') f |= SF_NEG; else f |= SF_UINT_INVALID;
-  f |= SF_PYINT_BAD | SF_BOOL_BAD;
-  k.decimal(f, ncp, (d6.neg ? 1u : 0u) + (uint32_t)d6.ip_digits, (uint32_t)d6.tz, (uint32_t)objfloat_len(d6), d6.neg,
-            d6.ip > 1000000ull || (d6.ip == 1000000ull && d6.frac));
 }
 
 // the calls collected into the candidates classify_measure_cell() reports (CPU cross-check, fix-ups)

@@ -410,6 +410,38 @@ def test_row_walker_and_hot_paths_agree_with_general():
     assert s1[3] == s0[3] and s1[6] == s0[6]
 
 
+def test_hot_classifier_short_numeric_tokens():
+    """classify_hot decides d{1,8}, [1-9]d*.d+ and digit-then-sign tokens from their first eight bytes
+    (csv2_rows.cuh): every such answer must be the general classifier's, on tokens drawn from the
+    alphabet of the numeric grammars."""
+    r = random.Random(77)
+    alpha = "0123456789" * 3 + ".-+eE _ "
+    fixed = ["0", "7", "00", "007", "1000000", "1000001", "999999", "9999999", "10000000", "12345678", "99999999",
+             "123456789", "1.5", "1.50", "1.500000", "1.000000", "10.0", "1234567.", "1.", ".5", "1..2", "1.2.3",
+             "0.5", "0.000001", "100000.5", "999999.9", "1234.5678", "2025-09-12", "1-2", "1+2", "12-", "1e5-3", "1e-5",
+             "1e+5", "1 -2", "1_0", "1_-2", "10-32UNF", "5-", "1234567-", "12345678-9", "3e5", "1E5"]
+    toks = fixed + ["".join(r.choice(alpha) for _ in range(r.randint(1, 10))) for _ in range(60000)]
+    toks = [t for t in toks if t.strip() and t[0] in "0123456789"]
+    docs = []
+    for i in range(0, len(toks), 400):
+        rows = toks[i:i + 400]
+        docs.append(("v,w\n" + "".join("%s,x\n" % t for t in rows)).encode())
+    try:
+        H.set_fused(True)
+        plain = [H.csv_parse(d, 10 ** 6) for d in docs]
+        H.set_walk(True)
+        s0 = H.walk_stats()
+        walked = [H.csv_parse(d, 10 ** 6) for d in docs]
+        s1 = H.walk_stats()
+    finally:
+        H.set_walk(False)
+        H.set_fused(False)
+    assert plain == walked
+    d = [b - a for a, b in zip(s0, s1)]
+    assert d[0] == 0 and d[1] == 0 and d[4] == 0, d
+    assert d[2] > 20000, d
+
+
 def test_scan_visits_only_what_matters():
     """The row scan replays a lane's 16 bytes visiting only the bytes visit_mask16 (csv_dfa.cuh) selects:
     record starts and record ends must be exactly those of the full state-machine walk."""
