@@ -375,6 +375,14 @@ RFQ_HD HotCand classify_measure_hot(const CellSrc& s) {
 // `dec` decimals — so the printed field is the token itself.
 RFQ_HD bool canonical_decimal(const uint8_t* p, uint32_t n, int dec) {
   if (n < (uint32_t)dec + 2u || n > 17u) return false;
+  if (n <= 8u && (uint32_t)(p[0] - '1') < 9u) {   // [1-9]d*.d{dec} in eight bytes: the only non-digit is the point, in its place
+    const uint64_t ones = 0x0101010101010101ull, highs = 0x8080808080808080ull;
+    const uint64_t x = load8_masked(p, n);
+    const uint64_t y = x ^ (ones * 0x30u);
+    const uint64_t live = n >= 8u ? ~0ull : ((1ull << (8u * n)) - 1ull);
+    const uint64_t nondig = ((y + ones * 0x76u) | y | x) & highs & live;
+    return nondig == (0x80ull << (8u * (n - 1u - (uint32_t)dec))) && p[n - 1u - (uint32_t)dec] == '.';
+  }
   uint32_t i = p[0] == '-' ? 1u : 0u;
   const uint32_t dot = n - 1u - (uint32_t)dec;
   if (dot <= i || dot - i > 8u || p[dot] != '.') return false;
@@ -426,6 +434,40 @@ RFQ_HD uint32_t cell_meta(const CellSrc& s, bool quoted, bool cold, bool na) {
   if (cold || s.mode == CM_CSV || s.n > 2046u) return 3u << CMETA_MODE_SHIFT;
   if (s.mode == CM_CSVQ) return (2u << CMETA_MODE_SHIFT) | (na ? CMETA_NA : 0u);
   return s.n | (quoted ? CMETA_QUOTED : 0u) | ((s.clean ? 0u : 1u) << CMETA_MODE_SHIFT) | (na ? CMETA_NA : 0u);
+}
+
+// Numeric cells that do not print as their own token ("+5", "007", "1.5" in a two-decimal column, integers
+// of a float column): parsed and formatted.  Out of line on the device, like classify_hot_rest.
+RFQ_HD_COLD int emit_hot_number(const uint8_t* p, uint32_t n, int ct, int kind, int dec, uint32_t width, uint8_t* field) {
+  if (kind == PR_INT) {
+    int64_t iv = 0;
+    if (parse_int64(RawIter(p, n), &iv) != INT_OK) return 1;
+    const uint32_t len = (uint32_t)int64_len(iv);
+    uint8_t* o = field + (width - len);
+    write_u64_rev(iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv, o + len);
+    if (iv < 0) o[0] = '-';
+    return 0;
+  }
+  Fixed6 d6;
+  if (ct == CT_INT || ct == CT_INTNA) {   // integer tokens of a float column: digits + ".000000"
+    int64_t iv = 0;
+    if (parse_int64(RawIter(p, n), &iv) != INT_OK) return 1;
+    const uint64_t mag = iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv;
+    if (mag > (1ull << 53)) return 1;
+    d6.neg = iv < 0; d6.inf = false; d6.big = false; d6.ip = mag; d6.frac = 0; d6.ip_digits = ndigits_u64(mag); d6.tz = 6;
+  } else if (!decimal_literal(p, n, &d6)) {   // a short decimal literal prints its own digits (cell_format.cuh)
+    int64_t iv = 0;                           // "100" next to "99.5": xstrtod makes the same value of it
+    if (parse_int64(RawIter(p, n), &iv) != INT_OK) return 1;
+    const uint64_t mag = iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv;
+    if (mag > (1ull << 53) || (iv == 0 && p[0] != '0')) return 1;   // beyond exact doubles; "-0"
+    d6.neg = iv < 0; d6.inf = false; d6.big = false; d6.ip = mag; d6.frac = 0; d6.ip_digits = ndigits_u64(mag); d6.tz = 6;
+  }
+  uint8_t buf[24];
+  const int dd = kind == PR_FIXED ? dec : objfloat_dec(d6);
+  const int len = fixed_write(d6, 0., dd, kind == PR_OBJFLOAT, buf);
+  uint8_t* o = field + (width - (uint32_t)len);
+  for (int q = 0; q < len; ++q) o[q] = buf[q];
+  return 0;
 }
 
 // One cell printed right-justified into its (blank-filled) field.  Returns 0 = done, 1 = the row
@@ -491,39 +533,15 @@ RFQ_HD int emit_hot(const CellSrc& s, int ct, int kind, int dec, uint32_t width,
       const bool canon = (uint32_t)(last - '0') < 10u &&
                          ((uint32_t)(b0 - '1') < 9u || (b0 == '-' && (uint32_t)(b1 - '1') < 9u) || (s.n == 1 && b0 == '0'));
       if (canon) { copy_span(field + (width - s.n), s.p, s.n); return 0; }   // an int64 token in canonical form prints as itself
-      int64_t iv = 0;
-      if (parse_int64(RawIter(s.p, s.n), &iv) != INT_OK) return 1;
-      const uint32_t n = (uint32_t)int64_len(iv);
-      uint8_t* o = field + (width - n);
-      write_u64_rev(iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv, o + n);
-      if (iv < 0) o[0] = '-';
-      return 0;
+      return emit_hot_number(s.p, s.n, ct, kind, dec, width, field);
     }
     case PR_FIXED: case PR_OBJFLOAT: {
       if (!s.clean || s.mode != CM_RAW) return 1;
-      Fixed6 d6;
-      if (ct == CT_INT || ct == CT_INTNA) {   // integer tokens of a float column: digits + ".000000"
-        int64_t iv = 0;
-        if (parse_int64(RawIter(s.p, s.n), &iv) != INT_OK) return 1;
-        const uint64_t mag = iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv;
-        if (mag > (1ull << 53)) return 1;
-        d6.neg = iv < 0; d6.inf = false; d6.big = false; d6.ip = mag; d6.frac = 0; d6.ip_digits = ndigits_u64(mag); d6.tz = 6;
-      } else if (kind == PR_FIXED && canonical_decimal(s.p, s.n, dec)) {
+      if (kind == PR_FIXED && ct != CT_INT && ct != CT_INTNA && canonical_decimal(s.p, s.n, dec)) {
         copy_span(field + (width - s.n), s.p, s.n);   // "959.40" in a two-decimal column is its own "%.2f"
         return 0;
-      } else if (!decimal_literal(s.p, s.n, &d6)) {   // a short decimal literal prints its own digits (cell_format.cuh)
-        int64_t iv = 0;                               // "100" next to "99.5": xstrtod makes the same value of it
-        if (parse_int64(RawIter(s.p, s.n), &iv) != INT_OK) return 1;
-        const uint64_t mag = iv < 0 ? 0ull - (uint64_t)iv : (uint64_t)iv;
-        if (mag > (1ull << 53) || (iv == 0 && s.p[0] != '0')) return 1;   // beyond exact doubles; "-0"
-        d6.neg = iv < 0; d6.inf = false; d6.big = false; d6.ip = mag; d6.frac = 0; d6.ip_digits = ndigits_u64(mag); d6.tz = 6;
       }
-      uint8_t buf[24];
-      const int dd = kind == PR_FIXED ? dec : objfloat_dec(d6);
-      const int n = fixed_write(d6, 0., dd, kind == PR_OBJFLOAT, buf);
-      uint8_t* o = field + (width - (uint32_t)n);
-      for (int q = 0; q < n; ++q) o[q] = buf[q];
-      return 0;
+      return emit_hot_number(s.p, s.n, ct, kind, dec, width, field);
     }
     default: return 1;   // uint64, "%.6e", Python ints
   }
