@@ -104,26 +104,34 @@ RFQ_HD FieldScan scan_field(const uint8_t* p, uint32_t pos, uint32_t limit, uint
     i = body;
   }
   // unquoted bytes up to the delimiter / LF / CR / limit
+  // One test per window finds the delimiter and every byte below 0x0E (LF and CR end the field, the other
+  // control bytes only mark it); the record's limit counts as a terminator at its own position, so the
+  // window itself is read unmasked (every buffer carries 16 bytes of slack).
   for (;;) {
-    const uint64_t x = row_window(p, i, limit);
-    const uint64_t t = zero_bytes(x ^ sep8) | zero_bytes(x ^ (ones * 0x0A)) | zero_bytes(x ^ (ones * 0x0D));
-    if (!t) {
-      acc |= (x & highs) | (((x - ones * 0x0E) & ~x & highs) ? 1ull : 0ull);
-      i += 8;
-      continue;
+    const uint32_t rem = limit > i ? limit - i : 0u;
+    const uint64_t x = load8_masked(p + i, 8);
+    uint64_t t = zero_bytes(x ^ sep8) | (~((x | highs) - ones * 0x0Eu) & ~x & highs);
+    if (rem < 8u) t |= 0x80ull << (8u * rem);
+    while (t) {
+      const uint32_t k = first_flag_byte(t);
+      const uint32_t tb = (uint32_t)(x >> (8 * k)) & 0xFFu;
+      const bool virt = k >= rem;
+      if (virt || tb == sep || tb == '\n' || tb == '\r') {
+        acc |= x & highs & ((1ull << (8u * k)) - 1ull);
+        const uint32_t e = i + k;
+        r.next = e + 1;
+        r.eol = virt || tb != sep;
+        r.src.n = e - pos;
+        if (quoted || junk || (acc & 1ull)) { r.src.mode = CM_CSV; r.src.clean = false; }
+        else r.src.clean = !(acc & highs);
+        (void)close;
+        return r;
+      }
+      acc |= 1ull;       // TAB, NUL, VT, ...: a control byte inside the field
+      t &= t - 1ull;
     }
-    const uint32_t k = first_flag_byte(t);
-    const uint64_t xm = keep_below(x, k);
-    acc |= (xm & highs) | (((xm - ones * 0x0E) & ~xm & highs) ? 1ull : 0ull);
-    const uint32_t e = i + k;
-    const uint32_t tb = (uint32_t)(x >> (8 * k)) & 0xFFu;
-    r.next = e + 1;
-    r.eol = tb != sep;
-    r.src.n = e - pos;
-    if (quoted || junk || (acc & 1ull)) { r.src.mode = CM_CSV; r.src.clean = false; }
-    else r.src.clean = !(acc & highs);
-    (void)close;
-    return r;
+    acc |= x & highs;
+    i += 8;
   }
 }
 
@@ -315,6 +323,14 @@ RFQ_HD void classify_hot(const CellSrc& s, Sink& k) {
       const uint32_t nf = s.n - 1u - kd;
       const uint32_t tz = hb == kd ? 6u : (6u - nf) + (s.n - 1u - hb);       // trailing zeros of the six-digit fraction
       dec = hd_pack(HD_DEC, f | SF_UINT_INVALID | SF_PYINT_BAD | SF_BOOL_BAD, kd, tz, 2u + kd + (tz >= 6u ? 1u : 6u - tz), false, false);
+    } else if ((c0 | 0x20u) == 'i') {
+      // INR, item, Infinity: only the inf words ([+-]?inf / infinity, any case) are numbers; the others fail
+      // every grammar at their first byte
+      const uint64_t lw = first8 | (ones * 0x20u);
+      const bool infw = (s.n == 3u && (lw & 0xFFFFFFull) == RFQ_P8('i', 'n', 'f', 0, 0, 0, 0, 0)) ||
+                        (s.n == 8u && lw == RFQ_P8('i', 'n', 'f', 'i', 'n', 'i', 't', 'y'));
+      dec = infw ? (uint64_t)HD_COLD
+                 : hd_pack(HD_WORD, f | SF_UINT_INVALID | SF_FLOAT_BAD | SF_BOOL_BAD | SF_PYINT_BAD, 0, 0, 0, false, false);
     } else if (is_digit_ascii((int)c0) && (sg & ((~((y + ones * 0x76u) | y) & highs & live) << 8))) {
       // 2025-09-12, 10-32UNF: a sign right after a digit ends every numeric grammar
       dec = hd_pack(HD_WORD, f | SF_UINT_INVALID | SF_FLOAT_BAD | SF_BOOL_BAD | SF_PYINT_BAD, 0, 0, 0, false, false);
