@@ -10,7 +10,9 @@
 // bytes from the now-known states (only bytes that can change the state are visited), record starts
 // and record ends are kept as bit masks in registers, the number of records since the start of the
 // document is carried across chunks by a second (segmented) look-back, and every record start is
-// written to its slot.  Documents begin on 16-byte boundaries and tiles never span documents; the end
+// written to its slot.  The first look-back is rarely walked: warp 0 also reads the tile BEFORE the chunk, and
+// when that tile's function is constant (the automaton forgets its start within a record or two) the
+// chunk's start state is known on the spot and published as an inclusive prefix at once.  Documents begin on 16-byte boundaries and tiles never span documents; the end
 // of a document is a virtual LF.  The bytes are read from HBM exactly once: no tensor cores, by design.
 #include <cuda_runtime.h>
 #include <algorithm>
@@ -146,14 +148,47 @@ __global__ void __launch_bounds__(RFQ2_SCAN_WARPS * 32) csv2_scan_kernel(Csv2Arg
       }
     }
     if (lane == 0) s_wfn[w] = wf;
+    // pandas' automaton forgets where it started within a record or two (a quote opens a field only at the
+    // field's first byte): when the function of the tile BEFORE the chunk is constant, the chunk's start
+    // state is that constant and nobody has to be waited for.
+    uint32_t behind = 0xFFFFFFFFu;
+    if (w == 0) {
+      const uint32_t d = dq[0];
+      const uint32_t tile = t0 - __ldg(a.tile_base + d);
+      if (tile == 0) behind = ST_R;               // a document starts here: what came before does not matter
+      else {
+        const uint32_t len = a.docs[d].len;
+        const uint8_t* doc = a.arena + a.docs[d].off;
+        const bool bom = tile == 1 && doc_has_bom(doc, len);
+        const LaneBytes lb = load_lane_classes(doc, len, (tile - 1) * RFQ_TILE + lane * 16, a.docs[d].sep, bom);
+        uint32_t f = lane_function(lb.cls, pair_fn);
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {          // lane l + o holds later bytes
+          const uint32_t g = __shfl_down_sync(0xffffffffu, f, o);
+          if (lane + o < 32) f = fn_compose(f, g);
+        }
+        f = __shfl_sync(0xffffffffu, f, 0);
+        if (tile == 1) f = fn_const(fn_apply(f, ST_R));
+        if (f == (f & 0xFu) * 0x11111111u) behind = f & 0xFu;
+      }
+    }
     __syncthreads();
     // ---- 2. the state this chunk starts in
     if (w == 0) {
       uint32_t cf = RFQ_FN_IDENTITY;
 #pragma unroll
       for (int v = 0; v < (int)RFQ2_SCAN_WARPS; ++v) cf = fn_compose(cf, s_wfn[v]);
-      const uint32_t pre = lookback_fn(a.fn_desc, chunk, cf, lane);
-      if (lane == 0) s_start_state = (uint32_t)fn_apply(pre, ST_R);
+      if (behind != 0xFFFFFFFFu) {
+        // known without a look-back: the chunk's inclusive prefix, as far as anybody can tell from applying it
+        // to a document's start state, is the constant function "ends in cf(behind)"
+        if (lane == 0) {
+          st_desc(a.fn_desc + chunk, (RFQ2_INC << 62) | fn_const(fn_apply(cf, (int)behind)));
+          s_start_state = behind;
+        }
+      } else {
+        const uint32_t pre = lookback_fn(a.fn_desc, chunk, cf, lane);
+        if (lane == 0) s_start_state = (uint32_t)fn_apply(pre, ST_R);
+      }
     }
     __syncthreads();
     int st = (int)s_start_state;
@@ -261,7 +296,7 @@ void csv2_scan(const Csv2Args& a, cudaStream_t s) {
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  static const int per_sm = getenv("RFQ2_SCAN_CTAS") ? atoi(getenv("RFQ2_SCAN_CTAS")) : 6;   // 48 of 64 warps: the look-back waits of one CTA are another's issue slots
+  static const int per_sm = getenv("RFQ2_SCAN_CTAS") ? atoi(getenv("RFQ2_SCAN_CTAS")) : 5;   // 40 of 64 warps (48 registers): the look-back waits of one CTA are another's issue slots
   const uint32_t grid = std::min<uint32_t>(a.n_chunks, (uint32_t)sms * (uint32_t)per_sm);
   prof_mark("csv2_scan_kernel", s);
   RFQ_LAUNCH(csv2_scan_kernel, grid, RFQ2_SCAN_WARPS * 32, 0, s, a);
