@@ -11,6 +11,7 @@
 //   txt_emit_kernel    compaction through shared memory, coalesced stores
 // HBM-bound byte work: no tensor cores.
 #include <cuda_runtime.h>
+#include <algorithm>
 #include "rfq_common.cuh"
 #include "utf8.cuh"
 #include "scan.cuh"
@@ -26,6 +27,29 @@ struct Win {
     return (w[j >> 2] >> ((j & 3) * 8)) & 0xFFu;
   }
 };
+
+// Eight bytes around a character, pulled out of the window ONCE (a dynamic index into the register
+// window costs a select chain per byte): B(i) for i in [base, base + 8), offsets constant after inlining.
+struct Near {
+  uint64_t x;
+  int base;
+  __device__ __forceinline__ uint32_t operator()(int64_t i) const {
+    return (uint32_t)(x >> (8 * ((int)i - base))) & 0xFFu;
+  }
+};
+__device__ __forceinline__ Near near_at(const Win& w, int k) {   // bytes k .. k + 7, k in [-4, 15]; past byte 19: zero
+  const int j = k + 4, q = j >> 2;
+  const uint32_t sh = (uint32_t)(j & 3) * 8u;
+  uint32_t a = w.w[0], b = w.w[1], c = w.w[2];
+  if (q == 1) { a = w.w[1]; b = w.w[2]; c = w.w[3]; }
+  else if (q == 2) { a = w.w[2]; b = w.w[3]; c = w.w[4]; }
+  else if (q == 3) { a = w.w[3]; b = w.w[4]; c = w.w[5]; }
+  else if (q >= 4) { a = w.w[4]; b = w.w[5]; c = 0u; }
+  Near n;
+  n.x = (unsigned long long)__funnelshift_r(a, b, sh) | ((unsigned long long)__funnelshift_r(b, c, sh) << 32);
+  n.base = k;
+  return n;
+}
 
 struct GlobalAcc {  // slow path: doc-relative accessor into global memory
   const uint8_t* p;
@@ -53,10 +77,13 @@ __device__ __forceinline__ void txt_lane_eval(const uint8_t* __restrict__ doc, u
   int64_t base = (int64_t)tile * RFQ_TILE + lane * 16;
   uint4 v = make_uint4(0, 0, 0, 0);
   if (base < len) v = __ldg(reinterpret_cast<const uint4*>(doc + base));
-  v.x = mask_word(v.x, base, len);
-  v.y = mask_word(v.y, base + 4, len);
-  v.z = mask_word(v.z, base + 8, len);
-  v.w = mask_word(v.w, base + 12, len);
+  const int64_t left = (int64_t)len - base;
+  const uint32_t valid = left >= 16 ? 0xFFFFu : left > 0 ? ((1u << left) - 1u) : 0u;
+  if (valid != 0xFFFFu) {   // bytes beyond the document read as zero: four mask bits -> four mask bytes
+#define RFQ_EXP4(m4) (((((m4) & 0xFu) * 0x00204081u) & 0x01010101u) * 0xFFu)
+    v.x &= RFQ_EXP4(valid); v.y &= RFQ_EXP4(valid >> 4); v.z &= RFQ_EXP4(valid >> 8); v.w &= RFQ_EXP4(valid >> 12);
+#undef RFQ_EXP4
+  }
   uint32_t prev = __shfl_up_sync(0xffffffffu, v.w, 1);
   uint32_t next = __shfl_down_sync(0xffffffffu, v.x, 1);
   if (lane == 0)
@@ -79,16 +106,14 @@ __device__ __forceinline__ void txt_lane_eval(const uint8_t* __restrict__ doc, u
   for (int q = 0; q < 4; ++q) {
     const uint32_t w = ww[q];
     uint32_t mlf = __vcmpeq4(w, 0x0A0A0A0Au), mcr = __vcmpeq4(w, 0x0D0D0D0Du);
-    uint32_t msp = (__vcmpgeu4(w, 0x09090909u) & __vcmpleu4(w, 0x0D0D0D0Du)) |
-                   (__vcmpgeu4(w, 0x1C1C1C1Cu) & __vcmpleu4(w, 0x20202020u));
+    uint32_t msp = __vcmpleu4(__vsub4(w, 0x09090909u), 0x04040404u) |      // \t .. \r
+                   __vcmpleu4(__vsub4(w, 0x1C1C1C1Cu), 0x04040404u);       // \x1c .. space
     uint32_t mhi = __vcmpgeu4(w, 0x80808080u);
     lf |= (((mlf & 0x08040201u) * 0x01010101u) >> 24) << (4 * q);
     cr |= (((mcr & 0x08040201u) * 0x01010101u) >> 24) << (4 * q);
     sp |= (((msp & 0x08040201u) * 0x01010101u) >> 24) << (4 * q);
     hi |= (((mhi & 0x08040201u) * 0x01010101u) >> 24) << (4 * q);
   }
-  const int64_t left = (int64_t)len - base;
-  const uint32_t valid = left >= 16 ? 0xFFFFu : left > 0 ? ((1u << left) - 1u) : 0u;
   const uint32_t pb = prev >> 24;
   const uint32_t after_cr = ((cr << 1) | (pb == '\r' ? 1u : 0u)) & 0xFFFFu;
   const uint32_t after_hi = ((hi << 1) | (pb >= 0x80u ? 1u : 0u)) & 0xFFFFu;
@@ -103,17 +128,18 @@ __device__ __forceinline__ void txt_lane_eval(const uint8_t* __restrict__ doc, u
   for (uint32_t m = hi & valid; m;) {
     const int k = __ffs(m) - 1;
     m &= m - 1;
-    const uint32_t b = win(k);
+    const Near nb = near_at(win, k - 3);   // bytes k - 3 .. k + 4: all a lead or a continuation byte at k can ask for
+    const uint32_t b = nb(k);
     if (u8_is_cont(b)) {              // only reached when no valid lead in this lane covers it
-      if (k < 3 && u8_keep(win, k)) emit |= 1u << k;
+      if (k < 3 && u8_keep(nb, k)) emit |= 1u << k;
       continue;
     }
     const int n = u8_lead_len(b);
-    if (n && u8_seq_valid(win, k)) {
+    if (n && u8_seq_valid(nb, k)) {
       const uint32_t span = (((1u << n) - 1u) << k) & 0xFFFFu;
       emit |= span;
       m &= ~span;
-      if (!u8_is_space_at(win, k)) nsp |= 1u << k;
+      if (!u8_is_space_at(nb, k)) nsp |= 1u << k;
     }
   }
 }
@@ -136,11 +162,19 @@ __global__ void __launch_bounds__(256) txt_count_kernel(
     const uint32_t* __restrict__ doc_len, const uint32_t* __restrict__ tile_base, uint32_t n_docs,
     uint32_t n_tiles, uint32_t* __restrict__ tile_cnt, unsigned long long* __restrict__ first_key,
     unsigned long long* __restrict__ last_key) {
-  uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
-  int lane = threadIdx.x & 31;
-  if (t >= n_tiles) return;
+  // A warp owns a run of consecutive tiles (the grid is sized for the machine, not for the batch): the
+  // document of a tile is found once per run and advanced from there, and no CTA lives for one tile only.
+  const int lane = threadIdx.x & 31;
+  const uint32_t nwarps = gridDim.x * 8u, gw = blockIdx.x * 8u + (threadIdx.x >> 5);
+  const uint32_t per = (n_tiles + nwarps - 1u) / nwarps;
+  uint32_t t = gw * per;
+  const uint32_t t_end = min(t + per, n_tiles);
+  if (t >= t_end) return;
   uint32_t d = warp_find_doc(tile_base, n_docs, t, lane);
-  uint32_t tile = t - tile_base[d];
+  uint32_t next_tb = __ldg(tile_base + d + 1);
+  for (; t < t_end; ++t) {
+  while (t >= next_tb) { ++d; next_tb = __ldg(tile_base + d + 1); }
+  uint32_t tile = t - __ldg(tile_base + d);
   uint32_t len = doc_len[d];
   const uint8_t* doc = arena + doc_off[d];
   Win win; uint32_t emit, nsp;
@@ -151,7 +185,7 @@ __global__ void __launch_bounds__(256) txt_count_kernel(
   if (nsp) {
     fp = base + (__ffs(nsp) - 1);
     int k = 31 - __clz(nsp);
-    uint32_t b = win(k);
+    uint32_t b = near_at(win, k)(k);
     int cl = b < 0x80u ? 1 : u8_lead_len(b);
     le = base + k + cl;
   }
@@ -161,7 +195,7 @@ __global__ void __launch_bounds__(256) txt_count_kernel(
     fp = min(fp, __shfl_xor_sync(0xffffffffu, fp, o));
     le = max(le, __shfl_xor_sync(0xffffffffu, le, o));
   }
-  if (fp == 0xFFFFFFFFu) { if (lane == 0) tile_cnt[t] = cnt; return; }   // nothing visible in this tile
+  if (fp == 0xFFFFFFFFu) { if (lane == 0) tile_cnt[t] = cnt; continue; }   // nothing visible in this tile
   // what the extent step needs from the tiles that win: the bytes this tile emits before its first visible
   // byte and before the end of its last visible character (which may reach into the next tile)
   const uint32_t tile_end = (tile + 1) * RFQ_TILE;
@@ -177,6 +211,7 @@ __global__ void __launch_bounds__(256) txt_count_kernel(
     const uint32_t spill = le > tile_end ? le - tile_end : 0u;           // at most 3
     atomicMin(first_key + d, ((unsigned long long)fp << 32) | lead);
     atomicMax(last_key + d, ((unsigned long long)le << 32) | (spill << 10) | trail);
+  }
   }
 }
 
@@ -208,17 +243,23 @@ __global__ void __launch_bounds__(256) txt_emit_kernel(
     const unsigned long long* __restrict__ out_off, const uint32_t* __restrict__ skip,
     uint8_t* __restrict__ out) {
   __shared__ uint8_t stage[8][RFQ_TILE];
-  int wib = threadIdx.x >> 5;
-  uint32_t t = blockIdx.x * 8 + wib;
-  int lane = threadIdx.x & 31;
-  if (t >= n_tiles) return;
+  const int wib = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t nwarps = gridDim.x * 8u, gw = blockIdx.x * 8u + (uint32_t)wib;
+  const uint32_t per = (n_tiles + nwarps - 1u) / nwarps;
+  uint32_t t = gw * per;
+  const uint32_t t_end = min(t + per, n_tiles);
+  if (t >= t_end) return;
   uint32_t d = warp_find_doc(tile_base, n_docs, t, lane);
+  uint32_t next_tb = __ldg(tile_base + d + 1);
+  for (; t < t_end; ++t) {
+  while (t >= next_tb) { ++d; next_tb = __ldg(tile_base + d + 1); }
   uint32_t fp = (uint32_t)(first_key[d] >> 32);
-  if (fp == 0xFFFFFFFFu) return;
+  if (fp == 0xFFFFFFFFu) continue;
   uint32_t le = (uint32_t)(last_key[d] >> 32);
-  uint32_t tile = t - tile_base[d];
+  uint32_t tile = t - __ldg(tile_base + d);
   uint32_t tb0 = tile * RFQ_TILE;
-  if (tb0 + RFQ_TILE <= fp || tb0 >= le) return;  // tile entirely stripped
+  if (tb0 + RFQ_TILE <= fp || tb0 >= le) continue;  // tile entirely stripped
   uint32_t len = doc_len[d];
   const uint8_t* doc = arena + doc_off[d];
   Win win; uint32_t emit, nsp;
@@ -255,15 +296,24 @@ __global__ void __launch_bounds__(256) txt_emit_kernel(
   __syncwarp();
   unsigned long long dst0 = out_off[d] + (unsigned long long)(tile_pre[t] + stripped_lead - skip[d]);
   for (uint32_t i = lane; i < total; i += 32) out[dst0 + i] = st[i];
+  __syncwarp();   // the stage is the next tile's
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
+static uint32_t txt_grid() {   // CTAs of 256 threads that fill the device once
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  return (uint32_t)sms * 8u;
+}
+
 void txt_pipeline(const TxtArgs& a, cudaStream_t s) {
   if (a.n_docs == 0) return;
   cudaMemsetAsync(a.first_key, 0xFF, sizeof(unsigned long long) * a.n_docs, s);
   cudaMemsetAsync(a.last_key, 0, sizeof(unsigned long long) * a.n_docs, s);
   if (a.n_tiles) {
-    uint32_t nb = (a.n_tiles + 7) / 8;
+    const uint32_t nb = std::min<uint32_t>((a.n_tiles + 7) / 8, txt_grid());
     prof_mark("txt_count_kernel", s);
     RFQ_LAUNCH(txt_count_kernel, nb, 256, 0, s, a.arena, a.doc_off, a.doc_len, a.tile_base,
                a.n_docs, a.n_tiles, a.tile_cnt, a.first_key, a.last_key);
@@ -279,7 +329,7 @@ void txt_pipeline(const TxtArgs& a, cudaStream_t s) {
 
 void txt_emit(const TxtArgs& a, uint8_t* out, cudaStream_t s) {
   if (a.n_tiles == 0) return;
-  uint32_t nb = (a.n_tiles + 7) / 8;
+  const uint32_t nb = std::min<uint32_t>((a.n_tiles + 7) / 8, txt_grid());
   RFQ_LAUNCH(txt_emit_kernel, nb, 256, 0, s, a.arena, a.doc_off, a.doc_len, a.tile_base, a.n_docs,
              a.n_tiles, a.tile_pre, a.first_key, a.last_key, a.out_off, a.skip, out);
 }
