@@ -242,7 +242,7 @@ __global__ void __launch_bounds__(256) txt_emit_kernel(
     const unsigned long long* __restrict__ first_key, const unsigned long long* __restrict__ last_key,
     const unsigned long long* __restrict__ out_off, const uint32_t* __restrict__ skip,
     uint8_t* __restrict__ out) {
-  __shared__ uint8_t stage[8][RFQ_TILE];
+  __shared__ __align__(16) uint8_t stage[8][RFQ_TILE + 16];
   const int wib = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const uint32_t nwarps = gridDim.x * 8u, gw = blockIdx.x * 8u + (uint32_t)wib;
@@ -284,7 +284,11 @@ __global__ void __launch_bounds__(256) txt_emit_kernel(
     stripped_lead = (fp - base >= 16) ? __popc(emit) : __popc(emit & ((1u << (fp - base)) - 1u));
 #pragma unroll
   for (int o = 16; o; o >>= 1) stripped_lead += __shfl_xor_sync(0xffffffffu, stripped_lead, o);
-  uint8_t* st = stage[wib];
+  // the tile's kept bytes are gathered in shared memory at the same 16-byte phase as their place in the
+  // output, so that all but the ends leave as 16-byte vectors
+  uint8_t* g = out + out_off[d] + (unsigned long long)(tile_pre[t] + stripped_lead - skip[d]);
+  const uint32_t mis = (uint32_t)((uintptr_t)g & 15u);
+  uint8_t* st = stage[wib] + mis;
   uint32_t pos = excl;
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
@@ -294,8 +298,15 @@ __global__ void __launch_bounds__(256) txt_emit_kernel(
     }
   }
   __syncwarp();
-  unsigned long long dst0 = out_off[d] + (unsigned long long)(tile_pre[t] + stripped_lead - skip[d]);
-  for (uint32_t i = lane; i < total; i += 32) out[dst0 + i] = st[i];
+  {
+    const uint32_t head = min(total, (16u - mis) & 15u);
+    const uint32_t nvec = (total - head) >> 4, tail = (total - head) & 15u;
+    if ((uint32_t)lane < head) g[lane] = st[lane];
+    if ((uint32_t)lane < nvec)
+      *reinterpret_cast<uint4*>(g + head + 16u * lane) = *reinterpret_cast<const uint4*>(st + head + 16u * lane);
+    if ((uint32_t)lane >= 16u && (uint32_t)lane - 16u < tail)
+      g[head + 16u * nvec + lane - 16u] = st[head + 16u * nvec + lane - 16u];
+  }
   __syncwarp();   // the stage is the next tile's
   }
 }
