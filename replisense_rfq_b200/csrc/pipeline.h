@@ -16,6 +16,8 @@ struct TxtArgs {
   uint32_t n_docs, n_tiles;
   uint32_t* tile_cnt;         // [n_tiles]
   uint32_t* tile_pre;         // [n_tiles]
+  uint16_t* lane_emit;        // [32 * n_tiles] or null: which of a lane's 16 bytes the count pass found emitted, so that
+                              // the emit pass does not decide them again (2 B per 16 input bytes)
   // strip extents, reduced over the tiles of a document with 64-bit atomics so that the winning tile also
   // hands over what the extent step needs from it (no second look at the bytes):
   unsigned long long* first_key;  // [n_docs] min of (first visible byte << 32 | bytes the tile emits before it)

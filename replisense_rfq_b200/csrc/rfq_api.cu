@@ -197,6 +197,7 @@ int rfq_text_run(rfq_ctx* c) {
   a.n_docs = n; a.n_tiles = nt;
   a.tile_cnt = c->pool.alloc<uint32_t>(nt + 1);
   a.tile_pre = c->pool.alloc<uint32_t>(nt + 1);
+  a.lane_emit = c->pool.alloc<uint16_t>(32ull * nt + 32);
   a.first_key = c->pool.alloc<unsigned long long>(n + 1);
   a.last_key = c->pool.alloc<unsigned long long>(n + 1);
   a.out_len = c->pool.alloc<unsigned long long>(n + 1);

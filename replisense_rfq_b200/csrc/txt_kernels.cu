@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(256) txt_count_kernel(
     const uint8_t* __restrict__ arena, const uint32_t* __restrict__ doc_off,
     const uint32_t* __restrict__ doc_len, const uint32_t* __restrict__ tile_base, uint32_t n_docs,
     uint32_t n_tiles, uint32_t* __restrict__ tile_cnt, unsigned long long* __restrict__ first_key,
-    unsigned long long* __restrict__ last_key) {
+    unsigned long long* __restrict__ last_key, uint16_t* __restrict__ lane_emit) {
   // A warp owns a run of consecutive tiles (the grid is sized for the machine, not for the batch): the
   // document of a tile is found once per run and advanced from there, and no CTA lives for one tile only.
   const int lane = threadIdx.x & 31;
@@ -179,6 +179,7 @@ __global__ void __launch_bounds__(256) txt_count_kernel(
   const uint8_t* doc = arena + doc_off[d];
   Win win; uint32_t emit, nsp;
   txt_lane_eval(doc, len, tile, lane, win, emit, nsp);
+  if (lane_emit) lane_emit[(size_t)t * 32u + lane] = (uint16_t)emit;
   uint32_t cnt = __popc(emit);
   uint32_t base = tile * RFQ_TILE + lane * 16;
   uint32_t fp = 0xFFFFFFFFu, le = 0u;
@@ -241,7 +242,7 @@ __global__ void __launch_bounds__(256) txt_emit_kernel(
     uint32_t n_tiles, const uint32_t* __restrict__ tile_pre,
     const unsigned long long* __restrict__ first_key, const unsigned long long* __restrict__ last_key,
     const unsigned long long* __restrict__ out_off, const uint32_t* __restrict__ skip,
-    uint8_t* __restrict__ out) {
+    uint8_t* __restrict__ out, const uint16_t* __restrict__ lane_emit) {
   __shared__ __align__(16) uint8_t stage[8][RFQ_TILE + 16];
   const int wib = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -263,8 +264,15 @@ __global__ void __launch_bounds__(256) txt_emit_kernel(
   uint32_t len = doc_len[d];
   const uint8_t* doc = arena + doc_off[d];
   Win win; uint32_t emit, nsp;
-  txt_lane_eval(doc, len, tile, lane, win, emit, nsp);
   uint32_t base = tb0 + lane * 16;
+  if (lane_emit) {   // decided by the count pass: only the bytes themselves are needed
+    emit = lane_emit[(size_t)t * 32u + lane];
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (base < len) v = __ldg(reinterpret_cast<const uint4*>(doc + base));
+    win.w[0] = 0; win.w[1] = v.x; win.w[2] = v.y; win.w[3] = v.z; win.w[4] = v.w; win.w[5] = 0;
+  } else {
+    txt_lane_eval(doc, len, tile, lane, win, emit, nsp);
+  }
   // restrict to [fp, le)
   uint32_t keep = emit;
   if (base < fp) keep &= (fp - base >= 16) ? 0u : ~((1u << (fp - base)) - 1u);
@@ -327,7 +335,7 @@ void txt_pipeline(const TxtArgs& a, cudaStream_t s) {
     const uint32_t nb = std::min<uint32_t>((a.n_tiles + 7) / 8, txt_grid());
     prof_mark("txt_count_kernel", s);
     RFQ_LAUNCH(txt_count_kernel, nb, 256, 0, s, a.arena, a.doc_off, a.doc_len, a.tile_base,
-               a.n_docs, a.n_tiles, a.tile_cnt, a.first_key, a.last_key);
+               a.n_docs, a.n_tiles, a.tile_cnt, a.first_key, a.last_key, a.lane_emit);
     prof_mark("scan(tile counts)", s);
     exclusive_scan<SumU32>(a.tile_cnt, a.tile_pre, a.n_tiles, a.scan_tmp32, nullptr, s);
   }
@@ -342,7 +350,7 @@ void txt_emit(const TxtArgs& a, uint8_t* out, cudaStream_t s) {
   if (a.n_tiles == 0) return;
   const uint32_t nb = std::min<uint32_t>((a.n_tiles + 7) / 8, txt_grid());
   RFQ_LAUNCH(txt_emit_kernel, nb, 256, 0, s, a.arena, a.doc_off, a.doc_len, a.tile_base, a.n_docs,
-             a.n_tiles, a.tile_pre, a.first_key, a.last_key, a.out_off, a.skip, out);
+             a.n_tiles, a.tile_pre, a.first_key, a.last_key, a.out_off, a.skip, out, a.lane_emit);
 }
 
 }  // namespace rfq
