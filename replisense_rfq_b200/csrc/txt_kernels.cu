@@ -70,7 +70,8 @@ __device__ __forceinline__ uint32_t mask_word(uint32_t v, int64_t pos, int64_t l
 }
 
 // Evaluate one lane's 16 bytes. `doc` points at the document start (16-byte aligned).
-// emit: bit k = byte k is emitted; nsp: bit k = byte k starts an emitted non-space character.
+// emit: bit k = byte k is emitted; nsp: bit k = byte k starts an emitted non-space character (exact in its lowest
+// and highest set bit, which is all anybody asks; non-ASCII characters between visible ASCII are not marked).
 __device__ __forceinline__ void txt_lane_eval(const uint8_t* __restrict__ doc, uint32_t len,
                                               uint32_t tile, int lane, Win& win, uint32_t& emit,
                                               uint32_t& nsp) {
@@ -139,7 +140,10 @@ __device__ __forceinline__ void txt_lane_eval(const uint8_t* __restrict__ doc, u
       const uint32_t span = (((1u << n) - 1u) << k) & 0xFFFFu;
       emit |= span;
       m &= ~span;
-      if (!u8_is_space_at(nb, k)) nsp |= 1u << k;
+      // nsp is only ever asked for its lowest and highest bit: a character with visible ASCII on both sides in
+      // this lane changes neither, whatever it is
+      const uint32_t below = nsp & ((1u << k) - 1u), above = nsp >> k;
+      if (!(below && above) && !u8_is_space_at(nb, k)) nsp |= 1u << k;
     }
   }
 }
@@ -190,23 +194,17 @@ __global__ void __launch_bounds__(256) txt_count_kernel(
     int cl = b < 0x80u ? 1 : u8_lead_len(b);
     le = base + k + cl;
   }
-#pragma unroll
-  for (int o = 16; o; o >>= 1) {
-    cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-    fp = min(fp, __shfl_xor_sync(0xffffffffu, fp, o));
-    le = max(le, __shfl_xor_sync(0xffffffffu, le, o));
-  }
+  cnt = __reduce_add_sync(0xffffffffu, cnt);     // one warp-wide reduction instruction each (redux.sync)
+  fp = __reduce_min_sync(0xffffffffu, fp);
+  le = __reduce_max_sync(0xffffffffu, le);
   if (fp == 0xFFFFFFFFu) { if (lane == 0) tile_cnt[t] = cnt; continue; }   // nothing visible in this tile
   // what the extent step needs from the tiles that win: the bytes this tile emits before its first visible
   // byte and before the end of its last visible character (which may reach into the next tile)
   const uint32_t tile_end = (tile + 1) * RFQ_TILE;
   uint32_t lead = __popc(emit & below16((int64_t)fp - base));
   uint32_t trail = __popc(emit & below16((int64_t)min(le, tile_end) - base));
-#pragma unroll
-  for (int o = 16; o; o >>= 1) {
-    lead += __shfl_xor_sync(0xffffffffu, lead, o);
-    trail += __shfl_xor_sync(0xffffffffu, trail, o);
-  }
+  lead = __reduce_add_sync(0xffffffffu, lead);
+  trail = __reduce_add_sync(0xffffffffu, trail);
   if (lane == 0) {
     tile_cnt[t] = cnt;
     const uint32_t spill = le > tile_end ? le - tile_end : 0u;           // at most 3
@@ -290,8 +288,7 @@ __global__ void __launch_bounds__(256) txt_emit_kernel(
   uint32_t stripped_lead = 0u;
   if (base < fp)
     stripped_lead = (fp - base >= 16) ? __popc(emit) : __popc(emit & ((1u << (fp - base)) - 1u));
-#pragma unroll
-  for (int o = 16; o; o >>= 1) stripped_lead += __shfl_xor_sync(0xffffffffu, stripped_lead, o);
+  stripped_lead = __reduce_add_sync(0xffffffffu, stripped_lead);
   // the tile's kept bytes are gathered in shared memory at the same 16-byte phase as their place in the
   // output, so that all but the ends leave as 16-byte vectors
   uint8_t* g = out + out_off[d] + (unsigned long long)(tile_pre[t] + stripped_lead - skip[d]);
