@@ -79,6 +79,12 @@ struct Csv2Args {
   unsigned long long* fn_desc;    // [n_chunks] look-back descriptors (transition functions)
   unsigned long long* cnt_desc;   // [n_chunks] (records since the document start)
   uint32_t* ticket;               // [2]
+  // three-launch scan (csv2_scan.cu): what the marks kernel leaves for the write kernel; null = one-launch scan
+  uint2* lane_marks;              // [32 * n_tiles] {record starts | starts after blanks << 16, record ends} of a lane's 16 bytes
+  uint32_t* tile_tot;             // [n_tiles] records that end in the tile, bit 31: a document starts here
+  uint32_t* tile_doc;             // [n_tiles]
+  unsigned long long* chunk_seg;  // [n_chunks] segmented record count of a chunk
+  unsigned long long* chunk_pre;  // [n_chunks] records since the document start, before the chunk
   uint32_t* rec_start;            // [n_slots]
   DocRun* run;                    // [n_docs]
   // rows

@@ -521,6 +521,16 @@ static int csv2_attempt(rfq_ctx* c, const std::vector<uint32_t>& sel, const uint
   uint8_t* d_up = c->pool.alloc<uint8_t>(up_al + z_end + 256);
   uint8_t* z = d_up ? d_up + up_al : nullptr;
   a.rec_start = c->pool.alloc<uint32_t>(n_slots + 2);
+  {   // scratch of the three-launch scan (half the input size for the lanes' marks)
+    static const bool split = getenv("RFQ2_SCAN_SPLIT") ? atoi(getenv("RFQ2_SCAN_SPLIT")) != 0 : true;   // RFQ2_SCAN_SPLIT=0: the one-launch scan with its count look-back
+    if (split) {
+      a.lane_marks = c->pool.alloc<uint2>(32ull * a.n_tiles + 32);
+      a.tile_tot = c->pool.alloc<uint32_t>((size_t)a.n_tiles + 32);
+      a.tile_doc = c->pool.alloc<uint32_t>((size_t)a.n_tiles + 32);
+      a.chunk_seg = c->pool.alloc<unsigned long long>((size_t)a.n_chunks + 1);
+      a.chunk_pre = c->pool.alloc<unsigned long long>((size_t)a.n_chunks + 1);
+    }
+  }
   a.row_na = c->pool.alloc<uint32_t>(n_slots + 2);
   a.row_extra = c->pool.alloc<uint32_t>(n_slots + 2);
   a.cell_meta = (uint16_t*)c->pool.alloc<uint4>(meta_vecs + 1);
