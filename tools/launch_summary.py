@@ -15,7 +15,7 @@ for r in rows[hdr + 2:]:
         k = r[ki].split("(")[0].replace("void ", "")
         tot[k] += float(r[vi].replace(",", ""))
         cnt[k] += 1
-runs = max(cnt.get("rfq::csv2_scan_kernel", cnt.get("rfq::csv_tilefn_kernel", 1)), 1)
+runs = max(cnt.get("rfq::csv2_scan_marks_kernel", cnt.get("rfq::csv2_scan_kernel", cnt.get("rfq::csv_tilefn_kernel", 1))), 1)
 T = sum(v for k, v in tot.items() if k.startswith("rfq::"))
 print("%d launches, %d pipeline runs (warm-up, timed, parity gate, e2e)" % (len(rows) - hdr - 2, runs))
 print("per-launch times are cold-cache and serialised under ncu: compare SHARES with bench.py's "

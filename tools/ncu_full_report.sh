@@ -6,7 +6,7 @@ set -e
 rep=$1; out=$2; traffic=$3
 here=$(dirname "$0")
 python "$here/ncu_summary.py" "$rep" "$out" "$traffic" > /dev/null
-for k in csv2_scan_kernel csv2_type_kernel csv2_emit_kernel; do
+for k in csv2_scan_marks_kernel csv2_scan_write_kernel csv2_type_kernel csv2_emit_kernel; do
   echo "== $k: source hot spots (share of executed warp instructions, share of stall samples, active lanes)" >> "$out"
   python "$here/ncu_hotspots.py" "$rep" "$k" 14 >> "$out"
 done
