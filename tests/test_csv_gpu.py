@@ -230,3 +230,42 @@ def test_big_texts_become_python_strings_at_every_width(eng):
         got = eng.parse_csv_many([d], 10 ** 6)[0]
         want = oracle(d, 10 ** 6)
         assert len(got) == len(want) > (1 << 20) and got == want, word
+
+
+def test_one_launch_scan_gives_the_same_texts(eng):
+    """RFQ2_SCAN_SPLIT=0 selects the one-launch row scan (count look-back inside the kernel) instead of the
+    marks / prefix / write launches: both must print the same bytes.  The switch is read once per process,
+    so the other variant runs in a child."""
+    import hashlib
+    import os
+    import subprocess
+    import sys
+    docs = [base64.b64decode(c["data"]) for c in json.loads((G / "ref_csv.json").read_text())]
+    docs += [corpus.fuzz_csv(s) for s in range(41000, 41400)] + [corpus.rfq_csv(30000, seed=3)]
+
+    def digest(texts):
+        h = hashlib.sha256()
+        for t in texts:
+            h.update(b"\x00" if isinstance(t, Exception) else b"\x02" if t is None else b"\x01" + t.encode("utf-8"))
+        return h.hexdigest()
+
+    here = digest(eng.parse_csv_many(docs, 100000, on_unsupported="return"))
+    child = (
+        "import base64, json, hashlib, sys\n"
+        "from pathlib import Path\n"
+        "sys.path.insert(0, %r)\n"
+        "from tests import corpus\n"
+        "from replisense_rfq_b200 import Engine\n"
+        "G = Path(%r)\n"
+        "docs = [base64.b64decode(c['data']) for c in json.loads((G / 'ref_csv.json').read_text())]\n"
+        "docs += [corpus.fuzz_csv(s) for s in range(41000, 41400)] + [corpus.rfq_csv(30000, seed=3)]\n"
+        "h = hashlib.sha256()\n"
+        "for t in Engine(0).parse_csv_many(docs, 100000, on_unsupported='return'):\n"
+        "    h.update(b'\\x00' if isinstance(t, Exception) else b'\\x02' if t is None else b'\\x01' + t.encode('utf-8'))\n"
+        "print('DIGEST', h.hexdigest())\n"
+    ) % (str(Path(__file__).resolve().parent.parent), str(G))
+    env = dict(os.environ, RFQ2_SCAN_SPLIT="0")
+    out = subprocess.run([sys.executable, "-c", child], env=env, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = [ln for ln in out.stdout.splitlines() if ln.startswith("DIGEST ")]
+    assert line and line[-1].split()[1] == here
