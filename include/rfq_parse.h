@@ -72,10 +72,12 @@ void rfq_destroy(rfq_ctx* ctx);
 const char* rfq_last_error(const rfq_ctx* ctx);
 const char* rfq_version(void);
 int rfq_device_count(void);
-/* run on a caller-owned CUDA stream (e.g. torch's current stream) instead of the ctx's own */
+/* run on a caller-owned CUDA stream (e.g. torch's current stream) instead of the ctx's own
+ * (plumbing of the boundary: the reference has no counterpart) */
 int rfq_set_stream(rfq_ctx* ctx, void* cuda_stream);
 void* rfq_get_stream(rfq_ctx* ctx);
-/* pinned host memory for input arenas */
+/* pinned host memory for input arenas (plumbing of the boundary: the reference reads files into Python objects,
+ * app/file_parser.py:146,225,301) */
 void* rfq_host_alloc(rfq_ctx* ctx, uint64_t bytes);
 void rfq_host_free(rfq_ctx* ctx, void* p);
 
@@ -223,10 +225,12 @@ int rfq_inflate_run(rfq_ctx* ctx, const uint8_t* method, const uint64_t* out_len
 int rfq_restage_output(rfq_ctx* ctx);
 int rfq_fetch_tables(rfq_ctx* ctx);
 
-/* ---- device → host copy of the last run's output ---- */
+/* ---- device → host copy of the last run's output (plumbing of the boundary: no reference counterpart) ---- */
 int rfq_fetch(rfq_ctx* ctx);
 
-/* convenience: stage + run + fetch */
+/* convenience: stage + run + fetch.  rfq_text_parse = _parse_txt_async (app/file_parser.py:143-148),
+ * rfq_csv_parse = _parse_csv_sync (app/file_parser.py:288-313), rfq_prompt_build = the prompt assembly of
+ * app/rfq_agent.py:138-151 */
 int rfq_prompt_build(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets,
                      const uint64_t* lengths, uint32_t n_docs, const uint8_t* head,
                      uint32_t head_len, const uint8_t* tail, uint32_t tail_len,
@@ -236,7 +240,9 @@ int rfq_text_parse(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets,
 int rfq_csv_parse(rfq_ctx* ctx, const uint8_t* arena, const uint64_t* offsets,
                   const uint64_t* lengths, uint32_t n_docs, const int64_t* max_rows);
 
-/* ---- results of the last run (host pointers, valid after rfq_fetch) ---- */
+/* ---- results of the last run (host pointers, valid after rfq_fetch): what the reference returns as
+ * result["raw_text"] (app/file_parser.py:135-141), per document, plus the status a binding maps to the
+ * reference's exceptions ---- */
 uint32_t rfq_out_count(const rfq_ctx* ctx);
 const uint8_t* rfq_out_text(const rfq_ctx* ctx);     /* UTF-8, all documents */
 const uint64_t* rfq_out_offsets(const rfq_ctx* ctx); /* [n] start of document d in out_text */
@@ -263,7 +269,8 @@ int rfq_out_plan_many(const rfq_ctx* ctx, uint32_t n_list, const uint32_t* docs,
 int rfq_out_widen_many(const rfq_ctx* ctx, uint32_t n_list, const uint32_t* docs, const uint8_t* units, void* const* dsts,
                        const uint64_t* n_chars);
 
-/* ---- measurement helpers (bench.py): device time of the last *_run, and launch counters ---- */
+/* ---- measurement helpers (bench.py): device time of the last *_run, and launch counters (no reference
+ * counterpart) ---- */
 float rfq_last_run_ms(const rfq_ctx* ctx);
 uint64_t rfq_launch_count(const rfq_ctx* ctx);
 /* name/ms of the dominant kernel family of the last CSV run, timed with CUDA events on the
