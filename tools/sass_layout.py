@@ -1,12 +1,14 @@
 """Where a kernel's code comes from, in 2 KB steps of its address range (nvdisasm -g -c line markers),
 and where its out-of-line device functions start.  usage: python tools/sass_layout.py <object.o> <kernel-substring>"""
 import collections
+import signal
 import re
 import subprocess
 import sys
 import tempfile
 from pathlib import Path
 
+signal.signal(signal.SIGPIPE, signal.SIG_DFL)   # quiet when piped into head
 obj, want = Path(sys.argv[1]).resolve(), sys.argv[2]
 with tempfile.TemporaryDirectory() as td:
     subprocess.run(["cuobjdump", "-xelf", "all", str(obj)], cwd=td, check=True, capture_output=True)

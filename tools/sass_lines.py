@@ -2,12 +2,14 @@
 attributed to the `//## File "...", line N` marker above it (innermost inlined location).
 usage: python tools/sass_lines.py <object.o> <kernel-name-substring> [top]"""
 import collections
+import signal
 import re
 import subprocess
 import sys
 import tempfile
 from pathlib import Path
 
+signal.signal(signal.SIGPIPE, signal.SIG_DFL)   # quiet when piped into head
 obj, want = Path(sys.argv[1]).resolve(), sys.argv[2]
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
 with tempfile.TemporaryDirectory() as td:
